@@ -1,0 +1,207 @@
+"""ctypes window onto oracle/liboracle.so (+ oracle/_ref/libref_naive.so).
+
+Checker only: imported by tests/, __graft_entry__.smoke() and bench.py's CPU
+legs.  Never imported by the product package.
+"""
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+ODIR = os.path.join(ROOT, "oracle")
+
+ACT_NONE, ACT_RELU, ACT_RELU6, ACT_LEAKY = 0, 1, 2, 4
+OUT_INT8, OUT_FP32, OUT_INT32 = 0, 1, 2
+ROUND_ARM, ROUND_CUDA = 0, 1
+POOL_MAX, POOL_AVG = 0, 1
+
+_NP_OUT = {OUT_INT8: np.int8, OUT_FP32: np.float32, OUT_INT32: np.int32}
+
+
+def build(ref=True):
+    subprocess.check_call(["make", "-s", "-C", ODIR, "all"])
+    if ref and os.path.isdir("/root/reference"):
+        subprocess.check_call(["make", "-s", "-C", ODIR, "ref"])
+
+
+def _load(path):
+    return C.CDLL(path) if os.path.exists(path) else None
+
+
+_lib = None
+_ref = None
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        p = os.path.join(ODIR, "liboracle.so")
+        if not os.path.exists(p):
+            build(ref=False)
+        _lib = C.CDLL(p)
+        _lib.orc_epilogue_f32.restype = C.c_float
+        _lib.orc_round_sat_i8.restype = C.c_int8
+    return _lib
+
+
+def ref():
+    """The reference's own naive math (None when oracle/_ref was never built)."""
+    global _ref
+    if _ref is None:
+        _ref = _load(os.path.join(ODIR, "_ref", "libref_naive.so"))
+    return _ref
+
+
+def _p(a):
+    return None if a is None else a.ctypes.data_as(C.c_void_p)
+
+
+def _f(v):
+    return C.c_float(float(v))
+
+
+def conv_out_size(i, k, d, p0, p1, s):
+    return (i + p0 + p1 - (d * (k - 1) + 1)) // s + 1
+
+
+def fold_scales(w_scale, n_out, in_scale, out_scale, out_dtype, bias=None,
+                act=ACT_NONE, act_arg=0.0):
+    w_scale = np.ascontiguousarray(w_scale, np.float32)
+    sf = np.empty(n_out, np.float32)
+    bf = np.empty(n_out, np.float32)
+    b = None if bias is None else np.ascontiguousarray(bias, np.float32)
+    aa = C.c_float(0)
+    rc = lib().orc_fold_scales(_p(w_scale), len(w_scale), n_out, _f(in_scale),
+                               _f(out_scale), out_dtype, _p(b), _p(sf), _p(bf),
+                               act, _f(act_arg), C.byref(aa))
+    assert rc == 0
+    return sf, bf, aa.value
+
+
+def conv2d(x, w, scale_f, bias_f, strides=(1, 1), pads=(0, 0, 0, 0),
+           dil=(1, 1), groups=1, act=ACT_NONE, act_arg=0.0, out=OUT_INT8,
+           rnd=ROUND_ARM):
+    """x NHWC int8, w OHWI int8 -> y NHWC."""
+    N, H, W, Cc = x.shape
+    K, R, S, _ = w.shape
+    P = conv_out_size(H, R, dil[0], pads[0], pads[1], strides[0])
+    Q = conv_out_size(W, S, dil[1], pads[2], pads[3], strides[1])
+    y = np.empty((N, P, Q, K), _NP_OUT[out])
+    x = np.ascontiguousarray(x)
+    w = np.ascontiguousarray(w)
+    sf = np.ascontiguousarray(scale_f, np.float32) if out != OUT_INT32 else None
+    bf = None if bias_f is None else np.ascontiguousarray(bias_f, np.float32)
+    rc = lib().orc_conv2d_i8_nhwc(_p(x), _p(w), _p(bf), _p(sf), _p(y), N, H, W,
+                                  Cc, K, R, S, strides[0], strides[1], pads[0],
+                                  pads[1], pads[2], pads[3], dil[0], dil[1],
+                                  groups, act, _f(act_arg), out, rnd)
+    assert rc == 0, rc
+    return y
+
+
+def gemm(A, B, scale_f, bias_f, trans_a=False, b_is_nk=False, act=ACT_NONE,
+         act_arg=0.0, out=OUT_INT8, rnd=ROUND_ARM):
+    A = np.ascontiguousarray(A)
+    B = np.ascontiguousarray(B)
+    M, K = (A.shape[1], A.shape[0]) if trans_a else A.shape
+    N = B.shape[0] if b_is_nk else B.shape[1]
+    y = np.empty((M, N), _NP_OUT[out])
+    sf = np.ascontiguousarray(scale_f, np.float32) if out != OUT_INT32 else None
+    bf = None if bias_f is None else np.ascontiguousarray(bias_f, np.float32)
+    rc = lib().orc_gemm_i8(_p(A), _p(B), _p(bf), _p(sf), _p(y), M, N, K,
+                           int(trans_a), int(b_is_nk), act, _f(act_arg), out,
+                           rnd)
+    assert rc == 0
+    return y
+
+
+def quantize(x, scale, rnd=ROUND_ARM):
+    x = np.ascontiguousarray(x, np.float32)
+    y = np.empty(x.shape, np.int8)
+    lib().orc_quantize_f32_i8(_p(x), _p(y), C.c_int64(x.size), _f(scale), rnd)
+    return y
+
+
+def dequantize(x, scale):
+    x = np.ascontiguousarray(x, np.int8)
+    y = np.empty(x.shape, np.float32)
+    lib().orc_dequantize_i8_f32(_p(x), _p(y), C.c_int64(x.size), _f(scale))
+    return y
+
+
+def nchw_to_nhwc(x):
+    x = np.ascontiguousarray(x)
+    N, Cc, H, W = x.shape
+    y = np.empty((N, H, W, Cc), x.dtype)
+    lib().orc_nchw_to_nhwc(_p(x), _p(y), N, Cc, H, W, x.itemsize)
+    return y
+
+
+def nhwc_to_nchw(x):
+    x = np.ascontiguousarray(x)
+    N, H, W, Cc = x.shape
+    y = np.empty((N, Cc, H, W), x.dtype)
+    lib().orc_nhwc_to_nchw(_p(x), _p(y), N, Cc, H, W, x.itemsize)
+    return y
+
+
+def pool2d(x, ksize, strides, pads, pool_type, exclusive=True, rescale=1.0,
+           out=OUT_INT8, rnd=ROUND_ARM, ceil_mode=False, global_pooling=False):
+    x = np.ascontiguousarray(x, np.int8)
+    N, H, W, Cc = x.shape
+    kh, kw = ksize
+    pt, pb, pl, pr = pads
+    if global_pooling:
+        kh, kw, pt, pb, pl, pr = H, W, 0, 0, 0, 0
+    if ceil_mode:
+        P = -(-(H + pt + pb - kh) // strides[0]) + 1
+        Q = -(-(W + pl + pr - kw) // strides[1]) + 1
+    else:
+        P = (H + pt + pb - kh) // strides[0] + 1
+        Q = (W + pl + pr - kw) // strides[1] + 1
+    y = np.empty((N, P, Q, Cc), _NP_OUT[out])
+    lib().orc_pool2d_i8_nhwc(_p(x), _p(y), N, H, W, Cc, kh, kw, strides[0],
+                             strides[1], pt, pl, P, Q, pool_type,
+                             int(exclusive), _f(rescale), out, rnd)
+    return y
+
+
+def add(a, b, sa, sb, act=ACT_NONE, act_arg=0.0, out=OUT_INT8, rnd=ROUND_ARM):
+    a = np.ascontiguousarray(a, np.int8)
+    b = np.ascontiguousarray(b, np.int8)
+    y = np.empty(a.shape, _NP_OUT[out])
+    lib().orc_add_i8(_p(a), _p(b), _p(y), C.c_int64(a.size), _f(sa), _f(sb),
+                     act, _f(act_arg), out, rnd)
+    return y
+
+
+# ---- the reference's own naive math (oracle/_ref) ---------------------------
+def ref_conv_acc_nchw(x_nchw, w_oihw, strides, pads_hw, dil, groups):
+    r = ref()
+    assert r is not None
+    x = np.ascontiguousarray(x_nchw, np.int8)
+    w = np.ascontiguousarray(w_oihw, np.int8)
+    N, Cc, H, W = x.shape
+    K, _, R, S = w.shape
+    P = conv_out_size(H, R, dil[0], pads_hw[0], pads_hw[0], strides[0])
+    Q = conv_out_size(W, S, dil[1], pads_hw[1], pads_hw[1], strides[1])
+    y = np.zeros((N, K, P, Q), np.int32)
+    r.ref_conv_basic_i8(_p(x), _p(y), N, K, P, Q, Cc, H, W, _p(w), groups, S, R,
+                        strides[1], strides[0], dil[1], dil[0], pads_hw[1],
+                        pads_hw[0])
+    return y
+
+
+def ref_gemm_acc(A, B, trans_a=False, trans_b=False):
+    r = ref()
+    assert r is not None
+    A = np.ascontiguousarray(A, np.int8)
+    B = np.ascontiguousarray(B, np.int8)
+    M, K = (A.shape[1], A.shape[0]) if trans_a else A.shape
+    N = B.shape[0] if trans_b else B.shape[1]
+    c = np.zeros((M, N), np.int32)
+    r.ref_basic_gemm_i8(int(trans_a), int(trans_b), M, N, K, _p(A), A.shape[1],
+                        _p(B), B.shape[1], _p(c), N)
+    return c

@@ -1,0 +1,162 @@
+"""Pins the oracle (CPU, no GPU needed): KATs from the reference's own tests,
+the reference's naive conv_basic/basic_gemm compiled into oracle/_ref, and the
+calib goldens written as plain C in the reference's calib tests."""
+import json
+import os
+
+import numpy as np
+import pytest
+
+import orc
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+KAT = json.load(open(os.path.join(HERE, "golden", "kat_cuda_conv_int8.json")))
+
+
+def test_kat1_all_ones_fp32_out():
+    # lite/kernels/cuda/conv_compute_test.cc:232-298
+    k = KAT["kat1"]
+    x = np.full(k["x_shape"], 1, np.int8)
+    w = np.full(k["w_shape"], 1, np.int8)
+    sf, bf, _ = orc.fold_scales(k["weight_scale"], 4, 1.0, 1.0, orc.OUT_FP32)
+    y = orc.conv2d(x, w, sf, None, out=orc.OUT_FP32, rnd=orc.ROUND_CUDA)
+    assert y.reshape(-1).tolist() == k["expect"]
+
+
+def test_kat2_mt19937_int8_out():
+    # lite/kernels/cuda/conv_compute_test.cc:300-376
+    k = KAT["kat2"]
+    x = np.array(k["x"], np.int8).reshape(k["x_shape"])
+    w = np.array(k["w"], np.int8).reshape(k["w_shape"])
+    acc = orc.conv2d(x, w, None, None, out=orc.OUT_INT32)
+    assert acc.reshape(-1).tolist() == k["acc"]
+    sf, bf, _ = orc.fold_scales(k["weight_scale"], 4, k["input_scale"],
+                                k["output_scale"], orc.OUT_INT8, k["bias"])
+    for rnd in (orc.ROUND_CUDA, orc.ROUND_ARM):
+        y = orc.conv2d(x, w, sf, bf, act=orc.ACT_RELU, out=orc.OUT_INT8, rnd=rnd)
+        assert y.reshape(-1).tolist() == k["expect"]
+
+
+needs_ref = pytest.mark.skipif(orc.ref() is None,
+                               reason="oracle/_ref not built (needs /root/reference)")
+
+CONV_CASES = [
+    # N,H,W,C,K,R,S,stride,pad,dil,groups
+    (1, 8, 8, 16, 16, 3, 3, 1, 1, 1, 1),
+    (2, 9, 7, 8, 12, 3, 3, 2, 1, 1, 1),
+    (1, 10, 10, 6, 4, 1, 1, 1, 0, 1, 1),
+    (1, 11, 11, 4, 8, 5, 5, 2, 2, 1, 1),
+    (1, 12, 12, 8, 8, 3, 3, 1, 2, 2, 1),
+    (2, 9, 9, 16, 16, 3, 3, 1, 1, 1, 16),   # depthwise
+    (1, 9, 9, 12, 12, 5, 5, 2, 2, 1, 12),   # depthwise 5x5 s2
+    (1, 7, 7, 8, 16, 3, 3, 1, 1, 1, 2),     # grouped
+    (1, 15, 15, 3, 32, 3, 3, 2, 1, 1, 1),   # first layer C=3
+    (1, 16, 16, 3, 8, 7, 7, 2, 3, 1, 1),    # resnet stem shape
+]
+
+
+@needs_ref
+@pytest.mark.parametrize("case", CONV_CASES)
+def test_conv_acc_vs_reference_conv_basic(case):
+    N, H, W, Cc, K, R, S, st, pd, dl, g = case
+    rng = np.random.default_rng(hash(case) & 0xFFFF)
+    x = rng.integers(-127, 128, (N, H, W, Cc), dtype=np.int8)
+    w = rng.integers(-127, 128, (K, R, S, Cc // g), dtype=np.int8)
+    mine = orc.conv2d(x, w, None, None, (st, st), (pd, pd, pd, pd), (dl, dl), g,
+                      out=orc.OUT_INT32)
+    theirs = orc.ref_conv_acc_nchw(orc.nhwc_to_nchw(x),
+                                   np.ascontiguousarray(w.transpose(0, 3, 1, 2)),
+                                   (st, st), (pd, pd), (dl, dl), g)
+    assert np.array_equal(mine, orc.nchw_to_nhwc(theirs))
+
+
+@needs_ref
+@pytest.mark.parametrize("mnk", [(1, 8, 16), (5, 7, 33), (16, 32, 64), (3, 1000, 128)])
+@pytest.mark.parametrize("b_is_nk", [False, True])
+def test_gemm_acc_vs_reference_basic_gemm(mnk, b_is_nk):
+    M, N, K = mnk
+    rng = np.random.default_rng(M * 131 + N * 7 + K)
+    A = rng.integers(-127, 128, (M, K), dtype=np.int8)
+    B = rng.integers(-127, 128, (N, K) if b_is_nk else (K, N), dtype=np.int8)
+    mine = orc.gemm(A, B, None, None, b_is_nk=b_is_nk, out=orc.OUT_INT32)
+    theirs = orc.ref_gemm_acc(A, B, trans_b=b_is_nk)
+    assert np.array_equal(mine, theirs)
+    assert np.array_equal(mine, A.astype(np.int32) @ (B.T if b_is_nk else B).astype(np.int32))
+
+
+def test_layout_roundtrip_and_numpy():
+    rng = np.random.default_rng(3)
+    x = rng.integers(-128, 128, (2, 5, 4, 7), dtype=np.int8)  # NCHW
+    y = orc.nchw_to_nhwc(x)
+    assert np.array_equal(y, x.transpose(0, 2, 3, 1))
+    assert np.array_equal(orc.nhwc_to_nchw(y), x)
+    xf = rng.standard_normal((1, 3, 6, 5)).astype(np.float32)
+    assert np.array_equal(orc.nchw_to_nhwc(xf), xf.transpose(0, 2, 3, 1))
+
+
+def test_calib_goldens():
+    rng = np.random.default_rng(11)
+    x = (rng.standard_normal(4096) * 3).astype(np.float32)
+    scale = np.float32(0.0371)
+    # ARM golden: lite/kernels/arm/calib_compute_test.cc:54-69
+    inv = np.float32(1.0) / scale
+    t = (x * inv).astype(np.float32)
+    r = np.where(t >= 0, np.floor(t + np.float32(0.5)), np.ceil(t - np.float32(0.5)))
+    # roundf == half away; recompute exactly to dodge float add error
+    r = np.sign(t) * np.floor(np.abs(t).astype(np.float64) + 0.5)
+    arm = np.clip(r, -127, 127).astype(np.int8)
+    assert np.array_equal(orc.quantize(x, scale, orc.ROUND_ARM), arm)
+    # CUDA kernel: lite/kernels/cuda/calib_compute.cu:27-36 (x/scale, clamp, rint)
+    t = (x / scale).astype(np.float32)
+    cu = np.rint(np.clip(t, -128, 127)).astype(np.int8)
+    assert np.array_equal(orc.quantize(x, scale, orc.ROUND_CUDA), cu)
+    q = rng.integers(-128, 128, 1000, dtype=np.int8)
+    assert np.array_equal(orc.dequantize(q, scale), q.astype(np.float32) * scale)
+
+
+def test_rounding_conventions_on_ties():
+    L = orc.lib()
+    f = lambda v, m: int(L.orc_round_sat_i8(orc._f(v), m))
+    assert [f(v, orc.ROUND_ARM) for v in (0.5, 1.5, 2.5, -0.5, -2.5, 0.49999997, 127.6, -127.6, -500)] == \
+        [1, 2, 3, -1, -3, 0, 127, -127, -127]
+    assert [f(v, orc.ROUND_CUDA) for v in (0.5, 1.5, 2.5, -0.5, -2.5, 127.6, -127.6, -500)] == \
+        [0, 2, 2, 0, -2, 127, -128, -128]
+
+
+def test_epilogue_matches_cvt_kernel_text():
+    # lite/backends/arm/math/conv_block_utils.h:3185-3226 restated in numpy with
+    # an exact fma (float64 product+sum of float32 values rounds once).
+    rng = np.random.default_rng(5)
+    acc = rng.integers(-70_000_000, 70_000_000, (64, 16), dtype=np.int32)
+    acc[0, :4] = [0, 1, -1, 2**24 + 1]
+    sc = (rng.random(16, dtype=np.float32) * 1e-6 + 1e-7).astype(np.float32)
+    bs = (rng.standard_normal(16) * 4).astype(np.float32)
+    accf = acc.astype(np.float32)
+    v = (accf.astype(np.float64) * sc.astype(np.float64) + bs.astype(np.float64)).astype(np.float32)
+    for act, fn in ((orc.ACT_NONE, lambda t: t),
+                    (orc.ACT_RELU, lambda t: np.maximum(t, 0)),
+                    (orc.ACT_RELU6, lambda t: np.minimum(np.maximum(t, 0), np.float32(6.0))),
+                    (orc.ACT_LEAKY, lambda t: np.where(t > 0, t, t * np.float32(0.1)))):
+        want = fn(v).astype(np.float32)
+        y = np.empty_like(want)
+        arg = 6.0 if act == orc.ACT_RELU6 else 0.1
+        orc.lib().orc_epilogue(orc._p(acc), orc.C.c_int64(64), 16, orc._p(sc), orc._p(bs), act,
+                               orc._f(arg), orc.OUT_FP32, orc.ROUND_ARM, orc._p(y))
+        assert np.array_equal(y, want)
+        q = np.empty(want.shape, np.int8)
+        orc.lib().orc_epilogue(orc._p(acc), orc.C.c_int64(64), 16, orc._p(sc), orc._p(bs), act,
+                               orc._f(arg), orc.OUT_INT8, orc.ROUND_ARM, orc._p(q))
+        r = np.sign(want) * np.floor(np.abs(want).astype(np.float64) + 0.5)
+        assert np.array_equal(q, np.clip(r, -127, 127).astype(np.int8))
+
+
+def test_fold_scales_rules():
+    ws = np.array([0.5, 0.25, 2.0], np.float32)
+    b = np.array([1.0, -2.0, 3.0], np.float32)
+    sf, bf, six = orc.fold_scales(ws, 3, 0.1, 0.4, orc.OUT_INT8, b, orc.ACT_RELU6, 6.0)
+    assert np.array_equal(sf, ws * np.float32(0.1) / np.float32(0.4))
+    assert np.array_equal(bf, b / np.float32(0.4))
+    assert six == np.float32(6.0) / np.float32(0.4)
+    sf, bf, six = orc.fold_scales(ws[:1], 3, 0.1, 0.4, orc.OUT_FP32, None, orc.ACT_RELU6, 6.0)
+    assert np.array_equal(sf, np.full(3, ws[0] * np.float32(0.1), np.float32))
+    assert np.array_equal(bf, np.zeros(3, np.float32)) and six == 6.0
