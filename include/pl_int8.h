@@ -1,0 +1,176 @@
+/*
+ * pl_int8.h -- C-ABI of the B200 (sm_100a) int8 conv / GEMM hot path.
+ *
+ * This is the drop-in boundary: the "new lite/backends/cuda/math int8 entry
+ * points" that Paddle-Lite's kCUDA kernel classes call.  Plain C: device
+ * pointers, sizes, POD descriptors and a cudaStream_t; no C++/torch types.
+ * Every function only ENQUEUES work on `stream` (never synchronises), is
+ * re-entrant, keeps no global state, and returns 0 on success, a positive
+ * cudaError_t, or a negative PL_ERR_* code.  There is no CPU fallback.
+ *
+ * Reference interfaces replaced (paths in chenjiaoAngel/Paddle-Lite):
+ *   pl_conv2d_i8_nhwc    lite/backends/cuda/math/cudnn_conv.cc:320-585
+ *                        (CudnnConv2DInt8<P>::{init,create,run}: cuDNN int8
+ *                        NHWC conv + a separate bias/act/requant kernel,
+ *                        lite/backends/cuda/math/activation.cu:91-446)
+ *   pl_dwconv2d_i8_nhwc  lite/backends/arm/math/conv3x3s{1,2}_depthwise_int8.cc,
+ *                        conv5x5s{1,2}_depthwise_int8.cc (no kCUDA kernel exists)
+ *   pl_gemm_i8           lite/backends/arm/math/gemm_s8.cc, gemv_arm_int8.cc:25-143;
+ *                        shape contract of lite/backends/cuda/math/gemm.cc:25-121
+ *   pl_quantize_f32_i8 / pl_dequantize_i8_f32
+ *                        lite/kernels/cuda/calib_compute.cu:27-95,
+ *                        lite/backends/arm/math/type_trans.cc:34-187
+ *   pl_nchw_to_nhwc / pl_nhwc_to_nchw
+ *                        lite/backends/cuda/math/transpose.cu:31-184
+ *   pl_pool2d_i8_nhwc    lite/kernels/cuda/pool_compute.cu:28-447 (fp32 there)
+ *   pl_add_i8            lite/backends/cuda/math/elementwise.cu:127-165
+ *   fold helpers         lite/backends/cuda/math/cudnn_conv.cc:349-372,
+ *                        lite/kernels/arm/conv_gemmlike.cc:207-264
+ *
+ * Layouts: activations NHWC int8 with an explicit pixel pitch `ld*` in
+ * elements (>= channels; multiples of 16 for the tensor-core paths so that
+ * TMA can address them; a channel slice of a wider buffer is a pointer offset
+ * + the wide pitch, which makes concat/split free).  Conv filters arrive in
+ * the reference's kCUDA int8 layout OHWI [K,R,S,C/groups]
+ * (cudnn_conv.cc:329-337) and are re-packed once by pl_pack_conv_weight_i8.
+ *
+ * Epilogue ("ARM convention"): v = fmaf((float)acc, scale[n],
+ * bias[n]); activation; int8 output = clamp(round-half-away(v), -127, 127);
+ * PL_ROUND_CUDA_LEGACY = clamp [-128,127] + round-half-even
+ * (lite/backends/cuda/math/utils.h:61-66).  `scale`/`bias` are the FOLDED
+ * vectors (see pl_fold_scales), bias may be NULL.
+ */
+#ifndef PL_INT8_H_
+#define PL_INT8_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct CUstream_st* pl_stream_t; /* == cudaStream_t */
+
+/* lite_api::ActivationType (lite/api/paddle_place.h:100-114) */
+enum { PL_ACT_NONE = 0, PL_ACT_RELU = 1, PL_ACT_RELU6 = 2, PL_ACT_LEAKY = 4 };
+enum { PL_OUT_INT8 = 0, PL_OUT_FP32 = 1, PL_OUT_INT32 = 2 };
+enum { PL_ROUND_ARM = 0, PL_ROUND_CUDA_LEGACY = 1 };
+enum { PL_POOL_MAX = 0, PL_POOL_AVG = 1 };
+
+enum {
+  PL_OK = 0,
+  PL_ERR_ARG = -1,         /* bad / inconsistent argument */
+  PL_ERR_ALIGN = -2,       /* pointer or pitch not 16-byte aligned */
+  PL_ERR_UNSUPPORTED = -3, /* shape outside what the sm_100a kernels cover */
+  PL_ERR_DRIVER = -4,      /* tensor-map encode / driver entry point failed */
+  PL_ERR_DEVICE = -5       /* device is not sm_100 */
+};
+
+/* Fused epilogue shared by conv / depthwise / gemm. */
+typedef struct pl_epilogue {
+  const float* scale; /* [n_out] folded per-output-channel scale (device) */
+  const float* bias;  /* [n_out] folded bias (device) or NULL */
+  int act;            /* PL_ACT_* */
+  float act_arg;      /* relu6: six (already / out_scale for int8 out); leaky: alpha */
+  int out_dtype;      /* PL_OUT_* ; PL_OUT_INT32 stores the raw accumulator */
+  int round_mode;     /* PL_ROUND_* */
+  /* optional fused residual (ConvParam::residualData, op_params.h:446-502):
+   * v = fmaf((float)res[m,n], res_scale, v) before the activation. */
+  const int8_t* residual;
+  int ld_res;
+  float res_scale;
+} pl_epilogue;
+
+typedef struct pl_conv_desc {
+  int N, H, W, C; /* input NHWC, C = logical channels */
+  int ldx;        /* input pixel pitch (elements) */
+  int K;          /* output channels */
+  int ldy;        /* output pixel pitch (elements of the output dtype) */
+  int R, S;       /* filter height, width */
+  int stride_h, stride_w;
+  int pad_t, pad_b, pad_l, pad_r; /* ConvParam::paddings order */
+  int dil_h, dil_w;
+  int groups;
+} pl_conv_desc;
+
+/* ---- host-side helpers (no device work) ---------------------------------- */
+int pl_conv_out_size(int in, int k, int dil, int pad0, int pad1, int stride);
+/* K-block (bytes of the reduction dim staged per pipeline stage) chosen for C. */
+int pl_conv_block_k(int C);
+/* bytes of the packed filter produced by pl_pack_conv_weight_i8 */
+size_t pl_conv_packed_weight_bytes(int K, int R, int S, int C);
+/* s[c] = w_scale[c]*in_scale (fp32 out) or *in_scale/out_scale (int8 out);
+ * bias[c] /= out_scale for int8 out; relu6 six /= out_scale for int8 out.
+ * HOST pointers.  n_w_scale is 1 or n_out. */
+int pl_fold_scales(const float* w_scale, int n_w_scale, int n_out, float in_scale,
+                   float out_scale, int out_dtype, const float* bias,
+                   float* scale_folded, float* bias_folded, int act,
+                   float act_arg, float* act_arg_folded);
+
+/* ---- one-off transforms (PrepareForRun) ------------------------------------ */
+/* OHWI [K,R,S,C] int8 (device) -> packed [K][R*S][Cb*BK] zero padded (device) */
+int pl_pack_conv_weight_i8(const int8_t* w_ohwi, int8_t* w_packed, int K, int R,
+                           int S, int C, pl_stream_t stream);
+/* [rows, cols] -> [cols, rows] int8 (fc W [K,N] -> [N,K]); pitches in elements */
+int pl_transpose_i8(const int8_t* src, int ld_src, int8_t* dst, int ld_dst,
+                    int rows, int cols, pl_stream_t stream);
+
+/* ---- tensor-core paths (tcgen05 kind::i8, TMEM int32, TMA) ------------------ */
+/* dense conv (groups == 1): implicit GEMM, M = N*P*Q, N = K, K = R*S*C.
+ * x, w_packed 16-byte aligned; ldx % 16 == 0. */
+int pl_conv2d_i8_nhwc(const int8_t* x, const int8_t* w_packed, void* y,
+                      const pl_conv_desc* d, const pl_epilogue* e,
+                      pl_stream_t stream);
+/* C[M,N] = epilogue(A[M,K] . Bt[N,K]^T).  A, Bt K-contiguous ("K-major"),
+ * lda % 16 == 0, ldb % 16 == 0. */
+int pl_gemm_i8(const int8_t* A, int lda, const int8_t* Bt, int ldb, void* C,
+               int ldc, int M, int N, int K, const pl_epilogue* e,
+               pl_stream_t stream);
+
+/* ---- bandwidth-bound paths (16-byte int8 vectors, no tensor cores) --------- */
+/* depthwise conv: groups == C == K, filter [C,R,S,1] as given by the reference */
+int pl_dwconv2d_i8_nhwc(const int8_t* x, const int8_t* w_crs, void* y,
+                        const pl_conv_desc* d, const pl_epilogue* e,
+                        pl_stream_t stream);
+int pl_quantize_f32_i8(const float* x, int8_t* y, int64_t n, float scale,
+                       int round_mode, pl_stream_t stream);
+int pl_dequantize_i8_f32(const int8_t* x, float* y, int64_t n, float scale,
+                         pl_stream_t stream);
+/* fused entry of the int8 region: fp32 NCHW -> int8 NHWC (pitch ldy, pad
+ * channels written as 0) with q = sat(round(x * (1/scale))) */
+int pl_quantize_nchw_f32_to_nhwc_i8(const float* x, int8_t* y, int N, int C,
+                                    int H, int W, int ldy, float scale,
+                                    int round_mode, pl_stream_t stream);
+/* plain layout transforms; elem_bytes 1 or 4; ld = NHWC pixel pitch (elements) */
+int pl_nchw_to_nhwc(const void* x, void* y, int N, int C, int H, int W, int ld,
+                    int elem_bytes, pl_stream_t stream);
+int pl_nhwc_to_nchw(const void* x, void* y, int N, int C, int H, int W, int ld,
+                    int elem_bytes, pl_stream_t stream);
+/* int8 NHWC pooling.  rescale = in_scale/out_scale (int8 out) or in_scale
+ * (fp32 out).  max: v = (float)max * rescale; avg: v = ((float)sum/(float)cnt)
+ * * rescale, cnt = clipped window (exclusive) or kh*kw. */
+int pl_pool2d_i8_nhwc(const int8_t* x, int ldx, void* y, int ldy, int N, int H,
+                      int W, int C, int kh, int kw, int sh, int sw, int pt,
+                      int pl, int P, int Q, int pool_type, int exclusive,
+                      float rescale, int out_dtype, int round_mode,
+                      pl_stream_t stream);
+/* y = q(act(fmaf((float)a, sa, (float)b * sb))) -- the ResNet residual add */
+int pl_add_i8(const int8_t* a, const int8_t* b, void* y, int64_t n, float sa,
+              float sb, int act, float act_arg, int out_dtype, int round_mode,
+              pl_stream_t stream);
+
+/* ---- introspection ---------------------------------------------------------- */
+/* number of kernels this library has launched in this process (bench.py's
+ * gpu_launches claim) */
+int64_t pl_launch_count(void);
+const char* pl_version(void);
+/* tensor-pipe micro-benchmark: issues `iters` back-to-back 128xBNx32
+ * tcgen05.mma kind::i8 per CTA on `ctas` CTAs from resident smem; returns 0
+ * and leaves a checksum in out[0] so the work cannot be elided. */
+int pl_i8_mma_peak(int ctas, int iters, int bn, int32_t* out, pl_stream_t stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* PL_INT8_H_ */

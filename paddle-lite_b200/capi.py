@@ -1,0 +1,277 @@
+"""ctypes window onto libpl_int8_b200.so (the C-ABI in include/pl_int8.h).
+
+torch is used for device memory and streams only; every compute call goes
+through the C-ABI with raw device pointers.  Missing library -> ImportError
+(no fallback of any kind).
+"""
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+import torch
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.dirname(HERE)
+LIB_PATH = os.path.join(HERE, "libpl_int8_b200.so")
+
+ACT_NONE, ACT_RELU, ACT_RELU6, ACT_LEAKY = 0, 1, 2, 4
+OUT_INT8, OUT_FP32, OUT_INT32 = 0, 1, 2
+ROUND_ARM, ROUND_CUDA = 0, 1
+POOL_MAX, POOL_AVG = 0, 1
+_TORCH_OUT = {OUT_INT8: torch.int8, OUT_FP32: torch.float32, OUT_INT32: torch.int32}
+
+
+class Epilogue(C.Structure):
+    _fields_ = [("scale", C.c_void_p), ("bias", C.c_void_p), ("act", C.c_int),
+                ("act_arg", C.c_float), ("out_dtype", C.c_int), ("round_mode", C.c_int),
+                ("residual", C.c_void_p), ("ld_res", C.c_int), ("res_scale", C.c_float)]
+
+
+class ConvDesc(C.Structure):
+    _fields_ = [(n, C.c_int) for n in (
+        "N", "H", "W", "C", "ldx", "K", "ldy", "R", "S", "stride_h", "stride_w",
+        "pad_t", "pad_b", "pad_l", "pad_r", "dil_h", "dil_w", "groups")]
+
+
+def build(verbose=False):
+    """Compile the CUDA library in-tree for sm_100a (nvcc cross-compiles without a GPU)."""
+    out = subprocess.run(["make", "-C", os.path.join(HERE, "csrc"), "-j8"],
+                         capture_output=True, text=True)
+    if out.returncode != 0:
+        raise RuntimeError("nvcc build failed:\n" + out.stdout + out.stderr)
+    if verbose:
+        print(out.stdout)
+
+
+_lib = None
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise ImportError(
+                f"{LIB_PATH} is missing: run __graft_entry__.build() (there is no CPU fallback)")
+        L = C.CDLL(LIB_PATH)
+        L.pl_launch_count.restype = C.c_int64
+        L.pl_version.restype = C.c_char_p
+        L.pl_conv_packed_weight_bytes.restype = C.c_size_t
+        _lib = L
+    return _lib
+
+
+class PlError(RuntimeError):
+    pass
+
+
+def _check(rc, what):
+    if rc != 0:
+        raise PlError(f"{what} failed with code {rc}")
+
+
+def _ptr(t):
+    return None if t is None else C.c_void_p(t.data_ptr())
+
+
+def _stream():
+    return C.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+def _f(v):
+    return C.c_float(float(v))
+
+
+def launch_count():
+    return int(lib().pl_launch_count())
+
+
+def conv_out_size(i, k, d, p0, p1, s):
+    return (i + p0 + p1 - (d * (k - 1) + 1)) // s + 1
+
+
+def fold_scales(w_scale, n_out, in_scale, out_scale, out_dtype, bias=None, act=ACT_NONE, act_arg=0.0):
+    """Host-side scale folding (pl_fold_scales); returns numpy (scale, bias, act_arg)."""
+    ws = np.ascontiguousarray(w_scale, np.float32)
+    sf = np.empty(n_out, np.float32)
+    bf = np.empty(n_out, np.float32)
+    b = None if bias is None else np.ascontiguousarray(bias, np.float32)
+    aa = C.c_float(0)
+    rc = lib().pl_fold_scales(ws.ctypes.data_as(C.c_void_p), len(ws), n_out, _f(in_scale), _f(out_scale),
+                              out_dtype, None if b is None else b.ctypes.data_as(C.c_void_p),
+                              sf.ctypes.data_as(C.c_void_p), bf.ctypes.data_as(C.c_void_p), act,
+                              _f(act_arg), C.byref(aa))
+    _check(rc, "pl_fold_scales")
+    return sf, bf, aa.value
+
+
+def make_epilogue(scale, bias, act=ACT_NONE, act_arg=0.0, out=OUT_INT8, rnd=ROUND_ARM,
+                  residual=None, ld_res=0, res_scale=0.0):
+    e = Epilogue()
+    e.scale = None if scale is None else scale.data_ptr()
+    e.bias = None if bias is None else bias.data_ptr()
+    e.act, e.act_arg, e.out_dtype, e.round_mode = act, float(act_arg), out, rnd
+    e.residual = None if residual is None else residual.data_ptr()
+    e.ld_res, e.res_scale = ld_res, float(res_scale)
+    return e
+
+
+def pack_conv_weight(w_ohwi):
+    """OHWI int8 (device) -> packed filter for pl_conv2d_i8_nhwc."""
+    K, R, S, Cc = w_ohwi.shape
+    nbytes = lib().pl_conv_packed_weight_bytes(K, R, S, Cc)
+    out = torch.empty(nbytes, dtype=torch.int8, device=w_ohwi.device)
+    _check(lib().pl_pack_conv_weight_i8(_ptr(w_ohwi.contiguous()), _ptr(out), K, R, S, Cc, _stream()),
+           "pl_pack_conv_weight_i8")
+    return out
+
+
+def conv_desc(N, H, W, Cc, K, R, S, strides=(1, 1), pads=(0, 0, 0, 0), dil=(1, 1), groups=1,
+              ldx=None, ldy=None):
+    d = ConvDesc()
+    d.N, d.H, d.W, d.C, d.K, d.R, d.S = N, H, W, Cc, K, R, S
+    d.ldx = Cc if ldx is None else ldx
+    d.ldy = K if ldy is None else ldy
+    d.stride_h, d.stride_w = strides
+    d.pad_t, d.pad_b, d.pad_l, d.pad_r = pads
+    d.dil_h, d.dil_w = dil
+    d.groups = groups
+    return d
+
+
+def conv2d(x, w_packed, K, R, S, scale, bias, strides=(1, 1), pads=(0, 0, 0, 0), dil=(1, 1),
+           act=ACT_NONE, act_arg=0.0, out=OUT_INT8, rnd=ROUND_ARM, y=None, Cc=None, ldy=None,
+           residual=None, res_scale=0.0):
+    """x: [N,H,W,ldx] int8 device tensor (logical channels Cc <= ldx)."""
+    N, H, W, ldx = x.shape
+    Cc = ldx if Cc is None else Cc
+    P = conv_out_size(H, R, dil[0], pads[0], pads[1], strides[0])
+    Q = conv_out_size(W, S, dil[1], pads[2], pads[3], strides[1])
+    ldy = K if ldy is None else ldy
+    if y is None:
+        y = torch.empty((N, P, Q, ldy), dtype=_TORCH_OUT[out], device=x.device)
+        if ldy != K:
+            y.zero_()
+    d = conv_desc(N, H, W, Cc, K, R, S, strides, pads, dil, 1, ldx, ldy)
+    e = make_epilogue(scale, bias, act, act_arg, out, rnd, residual,
+                      0 if residual is None else residual.shape[-1], res_scale)
+    _check(lib().pl_conv2d_i8_nhwc(_ptr(x), _ptr(w_packed), _ptr(y), C.byref(d), C.byref(e), _stream()),
+           "pl_conv2d_i8_nhwc")
+    return y
+
+
+def dwconv2d(x, w_crs, scale, bias, R, S, strides=(1, 1), pads=(0, 0, 0, 0), dil=(1, 1), act=ACT_NONE,
+             act_arg=0.0, out=OUT_INT8, rnd=ROUND_ARM, y=None, Cc=None):
+    N, H, W, ldx = x.shape
+    Cc = ldx if Cc is None else Cc
+    P = conv_out_size(H, R, dil[0], pads[0], pads[1], strides[0])
+    Q = conv_out_size(W, S, dil[1], pads[2], pads[3], strides[1])
+    if y is None:
+        y = torch.zeros((N, P, Q, ldx), dtype=_TORCH_OUT[out], device=x.device)
+    d = conv_desc(N, H, W, Cc, Cc, R, S, strides, pads, dil, Cc, ldx, y.shape[-1])
+    e = make_epilogue(scale, bias, act, act_arg, out, rnd)
+    _check(lib().pl_dwconv2d_i8_nhwc(_ptr(x), _ptr(w_crs), _ptr(y), C.byref(d), C.byref(e), _stream()),
+           "pl_dwconv2d_i8_nhwc")
+    return y
+
+
+def gemm(A, Bt, scale, bias, act=ACT_NONE, act_arg=0.0, out=OUT_INT8, rnd=ROUND_ARM, y=None,
+         M=None, N=None, K=None):
+    """C[M,N] = epi(A[M,K] . Bt[N,K]^T); A, Bt int8 row-major device tensors."""
+    M = A.shape[0] if M is None else M
+    K = A.shape[1] if K is None else K
+    N = Bt.shape[0] if N is None else N
+    if y is None:
+        y = torch.empty((M, N), dtype=_TORCH_OUT[out], device=A.device)
+    e = make_epilogue(scale, bias, act, act_arg, out, rnd)
+    _check(lib().pl_gemm_i8(_ptr(A), A.stride(0), _ptr(Bt), Bt.stride(0), _ptr(y), y.stride(0), M, N, K,
+                            C.byref(e), _stream()), "pl_gemm_i8")
+    return y
+
+
+def transpose_i8(src):
+    rows, cols = src.shape
+    dst = torch.empty((cols, rows), dtype=torch.int8, device=src.device)
+    _check(lib().pl_transpose_i8(_ptr(src), src.stride(0), _ptr(dst), rows, rows, cols, _stream()),
+           "pl_transpose_i8")
+    return dst
+
+
+def quantize(x, scale, rnd=ROUND_ARM):
+    x = x.contiguous()
+    y = torch.empty(x.shape, dtype=torch.int8, device=x.device)
+    _check(lib().pl_quantize_f32_i8(_ptr(x), _ptr(y), C.c_int64(x.numel()), _f(scale), rnd, _stream()),
+           "pl_quantize_f32_i8")
+    return y
+
+
+def dequantize(x, scale):
+    x = x.contiguous()
+    y = torch.empty(x.shape, dtype=torch.float32, device=x.device)
+    _check(lib().pl_dequantize_i8_f32(_ptr(x), _ptr(y), C.c_int64(x.numel()), _f(scale), _stream()),
+           "pl_dequantize_i8_f32")
+    return y
+
+
+def quantize_nchw_to_nhwc(x, scale, ld=None, rnd=ROUND_ARM, y=None):
+    N, Cc, H, W = x.shape
+    ld = Cc if ld is None else ld
+    if y is None:
+        y = torch.empty((N, H, W, ld), dtype=torch.int8, device=x.device)
+    _check(lib().pl_quantize_nchw_f32_to_nhwc_i8(_ptr(x.contiguous()), _ptr(y), N, Cc, H, W, ld, _f(scale),
+                                                 rnd, _stream()), "pl_quantize_nchw_f32_to_nhwc_i8")
+    return y
+
+
+def nchw_to_nhwc(x, ld=None):
+    N, Cc, H, W = x.shape
+    ld = Cc if ld is None else ld
+    y = torch.empty((N, H, W, ld), dtype=x.dtype, device=x.device)
+    _check(lib().pl_nchw_to_nhwc(_ptr(x.contiguous()), _ptr(y), N, Cc, H, W, ld, x.element_size(),
+                                 _stream()), "pl_nchw_to_nhwc")
+    return y
+
+
+def nhwc_to_nchw(x, Cc=None):
+    N, H, W, ld = x.shape
+    Cc = ld if Cc is None else Cc
+    y = torch.empty((N, Cc, H, W), dtype=x.dtype, device=x.device)
+    _check(lib().pl_nhwc_to_nchw(_ptr(x.contiguous()), _ptr(y), N, Cc, H, W, ld, x.element_size(),
+                                 _stream()), "pl_nhwc_to_nchw")
+    return y
+
+
+def pool2d(x, ksize, strides, pads, pool_type, exclusive=True, rescale=1.0, out=OUT_INT8,
+           rnd=ROUND_ARM, ceil_mode=False, global_pooling=False, Cc=None, y=None):
+    N, H, W, ldx = x.shape
+    Cc = ldx if Cc is None else Cc
+    kh, kw = ksize
+    pt, pb, pl_, pr = pads
+    if global_pooling:
+        kh, kw, pt, pb, pl_, pr = H, W, 0, 0, 0, 0
+    if ceil_mode:
+        P = -(-(H + pt + pb - kh) // strides[0]) + 1
+        Q = -(-(W + pl_ + pr - kw) // strides[1]) + 1
+    else:
+        P = (H + pt + pb - kh) // strides[0] + 1
+        Q = (W + pl_ + pr - kw) // strides[1] + 1
+    if y is None:
+        y = torch.zeros((N, P, Q, ldx), dtype=_TORCH_OUT[out], device=x.device)
+    _check(lib().pl_pool2d_i8_nhwc(_ptr(x), ldx, _ptr(y), y.shape[-1], N, H, W, Cc, kh, kw, strides[0],
+                                   strides[1], pt, pl_, P, Q, pool_type, int(exclusive), _f(rescale), out,
+                                   rnd, _stream()), "pl_pool2d_i8_nhwc")
+    return y
+
+
+def add(a, b, sa, sb, act=ACT_NONE, act_arg=0.0, out=OUT_INT8, rnd=ROUND_ARM, y=None):
+    if y is None:
+        y = torch.empty(a.shape, dtype=_TORCH_OUT[out], device=a.device)
+    _check(lib().pl_add_i8(_ptr(a), _ptr(b), _ptr(y), C.c_int64(a.numel()), _f(sa), _f(sb), act, _f(act_arg),
+                           out, rnd, _stream()), "pl_add_i8")
+    return y
+
+
+def i8_mma_peak(ctas, iters, bn=256):
+    out = torch.zeros(4, dtype=torch.int32, device="cuda")
+    _check(lib().pl_i8_mma_peak(ctas, iters, bn, _ptr(out), _stream()), "pl_i8_mma_peak")
+    return out

@@ -1,0 +1,255 @@
+// common.cuh -- sm_100a PTX wrappers (mbarrier, TMA, tcgen05/TMEM) and the
+// scalar epilogue shared by every kernel of the int8 hot path.
+//
+// Epilogue semantics follow the reference (file:line in chenjiaoAngel/Paddle-Lite):
+//   v = fma((float)acc, scale, bias)      lite/backends/arm/math/gemm_prepacked_int8.cc:664-700
+//   relu / relu6 / leaky                  lite/backends/arm/math/gemv_arm_int8.cc:111-116
+//   int8: round-half-away, clamp +-127    lite/backends/arm/math/gemv_arm_int8.cc:122-124,
+//                                         lite/backends/arm/math/saturate.h:130-147
+//   legacy: clamp [-128,127] + rint       lite/backends/cuda/math/utils.h:61-66
+// Built with -fmad=false: the only fused multiply-adds are the explicit
+// __fmaf_rn below, so the CPU oracle (fmaf, -ffp-contract=off) matches bit for bit.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "../../include/pl_int8.h"
+
+namespace pl {
+
+extern unsigned long long g_launches;  // host-side launch counter (capi.cu)
+
+#define PL_CUDA_OK(expr)                         \
+  do {                                           \
+    cudaError_t _e = (expr);                     \
+    if (_e != cudaSuccess) return (int)_e;       \
+  } while (0)
+
+static inline int launch_status() {
+  cudaError_t e = cudaGetLastError();
+  return e == cudaSuccess ? PL_OK : (int)e;
+}
+
+// ----------------------------------------------------------------------------
+// epilogue math
+// ----------------------------------------------------------------------------
+__device__ __forceinline__ float apply_act(float v, int act, float arg) {
+  switch (act) {
+    case PL_ACT_RELU: return v > 0.f ? v : 0.f;
+    case PL_ACT_RELU6: return v > 0.f ? (v > arg ? arg : v) : 0.f;
+    case PL_ACT_LEAKY: return v > 0.f ? v : __fmul_rn(v, arg);
+    default: return v;
+  }
+}
+
+// CUDA-legacy activation (activation.cu:91-181): vec4 path fmaxf(v*alpha, v)
+// when the channel count is a multiple of 4, else v>0 ? v : v*alpha.
+__device__ __forceinline__ float apply_act_legacy(float v, int act, float arg, bool vec4) {
+  if (act == PL_ACT_RELU || act == PL_ACT_LEAKY) {
+    const float alpha = act == PL_ACT_RELU ? 0.f : arg;
+    return vec4 ? fmaxf(__fmul_rn(v, alpha), v) : (v > 0.f ? v : __fmul_rn(v, alpha));
+  }
+  if (act == PL_ACT_RELU6) return v > 0.f ? (v > arg ? arg : v) : 0.f;
+  return v;
+}
+
+// round + saturate to int8, returned as int in [-128,127].  No FRND/F2I: the
+// conversion pipe is 4-8x narrower than the FMA pipe and the epilogue runs once
+// per output byte, so both conventions are built from FADDs with explicit
+// rounding modes (bit-exact with roundf()/rintf(), see tests/test_oracle.py):
+//   ARM    : m = floor(RZ(min(|v|,127) + 0.5)) via RD(t + 2^23); sign re-applied
+//   legacy : low byte of RNE(clamp(v,-128,127) + 1.5*2^23)
+__device__ __forceinline__ int round_sat_i8(float v, int round_mode) {
+  if (round_mode == PL_ROUND_CUDA_LEGACY) {
+    const float c = fminf(fmaxf(v, -128.f), 127.f);
+    const int bits = __float_as_int(__fadd_rn(c, 12582912.f));
+    return (int)(int8_t)(bits & 0xff);
+  }
+  const float a = fminf(fabsf(v), 127.f);
+  const float t = __fadd_rz(a, 0.5f);
+  const int m = __float_as_int(__fadd_rd(t, 8388608.f)) & 0xff;
+  return v < 0.f ? -m : m;
+}
+
+// exact int -> float for |acc| < 2^22 without the conversion pipe
+__device__ __forceinline__ float small_int2float(int acc) {
+  return __fadd_rn(__int_as_float(acc + 0x4B400000), -12582912.f);
+}
+
+struct EpiParams {
+  const float* scale;
+  const float* bias;
+  const int8_t* residual;
+  int ld_res;
+  float res_scale;
+  int act;
+  float act_arg;
+  int out_dtype;
+  int round_mode;
+  int vec4;  // legacy activation flavour (n_out % 4 == 0)
+};
+
+static inline EpiParams make_epi(const pl_epilogue* e, int n_out) {
+  EpiParams p;
+  p.scale = e->scale;
+  p.bias = e->bias;
+  p.residual = e->residual;
+  p.ld_res = e->ld_res;
+  p.res_scale = e->res_scale;
+  p.act = e->act;
+  p.act_arg = e->act_arg;
+  p.out_dtype = e->out_dtype;
+  p.round_mode = e->round_mode;
+  p.vec4 = (n_out % 4 == 0);
+  return p;
+}
+
+// one accumulator -> pre-rounding float
+__device__ __forceinline__ float epi_value(int acc, float s, float b, const EpiParams& p) {
+  float v = __fmaf_rn(__int2float_rn(acc), s, b);
+  if (p.round_mode == PL_ROUND_CUDA_LEGACY) return apply_act_legacy(v, p.act, p.act_arg, p.vec4);
+  return apply_act(v, p.act, p.act_arg);
+}
+
+__device__ __forceinline__ uint32_t pack4_i8(int a, int b, int c, int d) {
+  return (uint32_t)(a & 0xff) | ((uint32_t)(b & 0xff) << 8) | ((uint32_t)(c & 0xff) << 16) |
+         ((uint32_t)(d & 0xff) << 24);
+}
+
+// ----------------------------------------------------------------------------
+// mbarrier
+// ----------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t smem_u32(const void* p) {
+  return (uint32_t)__cvta_generic_to_shared(p);
+}
+
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count));
+}
+__device__ __forceinline__ void fence_barrier_init() {
+  asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+__device__ __forceinline__ void fence_proxy_async() {
+  asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+}
+__device__ __forceinline__ void mbar_arrive_expect_tx(uint32_t bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes)
+               : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ bool mbar_try_wait(uint32_t bar, uint32_t parity) {
+  uint32_t ok;
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+      "selp.u32 %0, 1, 0, p;\n\t}"
+      : "=r"(ok)
+      : "r"(bar), "r"(parity)
+      : "memory");
+  return ok != 0;
+}
+// Bounded wait: a protocol bug must end in a trap (launch failure reported to
+// the caller), never in a hung GPU.
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+  if (mbar_try_wait(bar, parity)) return;
+  const long long t0 = clock64();
+  while (!mbar_try_wait(bar, parity)) {
+    if (clock64() - t0 > 4000000000LL) __trap();
+  }
+}
+
+// ----------------------------------------------------------------------------
+// TMA
+// ----------------------------------------------------------------------------
+__device__ __forceinline__ void tma_prefetch_desc(const void* desc) {
+  asm volatile("prefetch.tensormap [%0];" ::"l"(desc) : "memory");
+}
+__device__ __forceinline__ void tma_load_2d(uint32_t dst, const void* desc, uint32_t bar, int c0,
+                                            int c1) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes"
+      " [%0], [%1, {%3, %4}], [%2];" ::"r"(dst),
+      "l"(desc), "r"(bar), "r"(c0), "r"(c1)
+      : "memory");
+}
+// im2col-mode load of `pixelsPerColumn` output pixels starting at base pixel
+// (w,h,n), channels [c, c+channelsPerPixel), filter offset (off_w, off_h).
+__device__ __forceinline__ void tma_load_im2col_4d(uint32_t dst, const void* desc, uint32_t bar,
+                                                   int c, int w, int h, int n, uint16_t off_w,
+                                                   uint16_t off_h) {
+  asm volatile(
+      "cp.async.bulk.tensor.4d.shared::cluster.global.im2col.mbarrier::complete_tx::bytes"
+      " [%0], [%1, {%3, %4, %5, %6}], [%2], {%7, %8};" ::"r"(dst),
+      "l"(desc), "r"(bar), "r"(c), "r"(w), "r"(h), "r"(n), "h"(off_w), "h"(off_h)
+      : "memory");
+}
+
+// ----------------------------------------------------------------------------
+// tcgen05 / TMEM
+// ----------------------------------------------------------------------------
+__device__ __forceinline__ void tmem_alloc(uint32_t smem_dst, uint32_t ncols) {
+  asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_dst),
+               "r"(ncols)
+               : "memory");
+}
+__device__ __forceinline__ void tmem_relinquish() {
+  asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tmem_dealloc(uint32_t taddr, uint32_t ncols) {
+  asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(taddr), "r"(ncols)
+               : "memory");
+}
+__device__ __forceinline__ void tc_fence_before() {
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+}
+__device__ __forceinline__ void tc_fence_after() {
+  asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+}
+// D[tmem] (+)= A[smem] * B[smem]^T, int8 x int8 -> int32, issued by ONE thread
+__device__ __forceinline__ void umma_i8(uint32_t tmem_d, uint64_t desc_a, uint64_t desc_b,
+                                        uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::i8 [%0], %1, %2, %3, p;\n\t}" ::"r"(tmem_d),
+      "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+// arrive on an mbarrier once all previously issued MMAs of this thread are done
+__device__ __forceinline__ void umma_commit(uint32_t bar) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(
+                   bar)
+               : "memory");
+}
+__device__ __forceinline__ void tmem_ld_wait() {
+  asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+}
+// 32 lanes x 16 consecutive 32-bit columns: thread t gets row (lane base + t)
+__device__ __forceinline__ void tmem_ld_32x32b_x16(uint32_t taddr, uint32_t (&r)[16]) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x16.b32 "
+      "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
+      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]),
+        "=r"(r[7]), "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]),
+        "=r"(r[14]), "=r"(r[15])
+      : "r"(taddr)
+      : "memory");
+}
+
+// SM100 shared-memory matrix descriptor for a K-major operand tile whose rows
+// are `row_bytes` (32 / 64 / 128) wide and swizzled with the matching TMA
+// swizzle mode.  Fields (cute/arch/mma_sm100_desc.hpp): start>>4 [0,14),
+// LBO>>4 [16,30), SBO>>4 [32,46), version=1 [46,48), layout [61,64).
+__host__ __device__ __forceinline__ uint64_t make_smem_desc_base(uint32_t row_bytes) {
+  const uint64_t layout = row_bytes == 128 ? 2ull : (row_bytes == 64 ? 4ull : 6ull);
+  const uint64_t sbo = (8ull * row_bytes) >> 4;  // 8-row core-matrix group pitch
+  return (1ull << 16) | (sbo << 32) | (1ull << 46) | (layout << 61);
+}
+// instruction descriptor: D=S32, A=B=signed int8, K-major both, M=128
+__host__ __device__ __forceinline__ uint32_t make_idesc_i8(uint32_t n) {
+  return (2u << 4) | (1u << 7) | (1u << 10) | ((n >> 3) << 17) | ((128u >> 4) << 24);
+}
+
+}  // namespace pl

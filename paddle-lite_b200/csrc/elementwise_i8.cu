@@ -1,0 +1,405 @@
+// elementwise_i8.cu -- the HBM-bound companions of the int8 hot path: calib
+// (quantise / dequantise), NCHW<->NHWC layout, int8 pooling, residual add.
+// All of them move each byte once with 16-byte vectors; no tensor cores.
+//
+// Reference semantics (chenjiaoAngel/Paddle-Lite):
+//   quantise    ARM  q = sat(roundf(x * (1/scale))), floor -127
+//                    lite/backends/arm/math/type_trans.cc:34-187
+//               CUDA q = from_float<int8_t>(x / scale)
+//                    lite/kernels/cuda/calib_compute.cu:27-36, utils.h:61-66
+//   dequantise  x = q * scale   lite/kernels/cuda/calib_compute.cu:38-46
+//   layout      [N,C,HW] <-> [N,HW,C]  lite/backends/cuda/math/transpose.cu:31-184
+//   pool / add  no int8 kernel in the reference;
+//               window rules of lite/kernels/cuda/pool_compute.cu:28-130
+#include "common.cuh"
+
+namespace pl {
+
+static inline int grid_for(long long items, int threads, int per_sm = 8) {
+  int dev = 0, sms = 148;
+  cudaGetDevice(&dev);
+  cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+  long long g = (items + threads - 1) / threads;
+  const long long cap = (long long)sms * per_sm;
+  if (g > cap) g = cap;
+  if (g < 1) g = 1;
+  return (int)g;
+}
+
+__device__ __forceinline__ float quant_pre(float x, float scale, float inv, int round_mode) {
+  return round_mode == PL_ROUND_CUDA_LEGACY ? __fdiv_rn(x, scale) : __fmul_rn(inv, x);
+}
+
+// ---------------------------------------------------------------- quantise
+__global__ void __launch_bounds__(256)
+quantize_kernel(const float* __restrict__ x, int8_t* __restrict__ y, long long n, float scale,
+                float inv, int round_mode, int vec) {
+  const long long stride = (long long)gridDim.x * blockDim.x;
+  long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (vec) {
+    const long long n16 = n >> 4;
+    for (; i < n16; i += stride) {
+      const float4* xp = reinterpret_cast<const float4*>(x) + i * 4;
+      float4 f[4];
+#pragma unroll
+      for (int k = 0; k < 4; ++k) f[k] = __ldg(xp + k);
+      uint32_t o[4];
+#pragma unroll
+      for (int k = 0; k < 4; ++k)
+        o[k] = pack4_i8(round_sat_i8(quant_pre(f[k].x, scale, inv, round_mode), round_mode),
+                        round_sat_i8(quant_pre(f[k].y, scale, inv, round_mode), round_mode),
+                        round_sat_i8(quant_pre(f[k].z, scale, inv, round_mode), round_mode),
+                        round_sat_i8(quant_pre(f[k].w, scale, inv, round_mode), round_mode));
+      reinterpret_cast<uint4*>(y)[i] = make_uint4(o[0], o[1], o[2], o[3]);
+    }
+    i = (n16 << 4) + (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  }
+  for (; i < n; i += stride)
+    y[i] = (int8_t)round_sat_i8(quant_pre(x[i], scale, inv, round_mode), round_mode);
+}
+
+// -------------------------------------------------------------- dequantise
+__global__ void __launch_bounds__(256)
+dequantize_kernel(const int8_t* __restrict__ x, float* __restrict__ y, long long n, float scale,
+                  int vec) {
+  const long long stride = (long long)gridDim.x * blockDim.x;
+  long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (vec) {
+    const long long n16 = n >> 4;
+    for (; i < n16; i += stride) {
+      const uint4 v = __ldg(reinterpret_cast<const uint4*>(x) + i);
+      const uint32_t w[4] = {v.x, v.y, v.z, v.w};
+      float4* yp = reinterpret_cast<float4*>(y) + i * 4;
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        float4 f;
+        f.x = __fmul_rn((float)(int8_t)(w[k] & 0xff), scale);
+        f.y = __fmul_rn((float)(int8_t)((w[k] >> 8) & 0xff), scale);
+        f.z = __fmul_rn((float)(int8_t)((w[k] >> 16) & 0xff), scale);
+        f.w = __fmul_rn((float)(int8_t)(w[k] >> 24), scale);
+        yp[k] = f;
+      }
+    }
+    i = (n16 << 4) + (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  }
+  for (; i < n; i += stride) y[i] = __fmul_rn((float)x[i], scale);
+}
+
+// -------------------------------------------- layout: batched 2-D transposes
+// src [B][rows][cols] (pitch ld_src) -> dst [B][cols][rows] (pitch ld_dst);
+// 64x64 byte tiles through shared memory.  T is the element type.
+template <typename T>
+__global__ void __launch_bounds__(256)
+transpose_kernel(const T* __restrict__ src, T* __restrict__ dst, int rows, int cols,
+                 long long ld_src, long long ld_dst, long long bs_src, long long bs_dst) {
+  __shared__ T tile[64][65];
+  const int b = blockIdx.z;
+  const int r0 = blockIdx.y * 64, c0 = blockIdx.x * 64;
+  const T* s = src + (long long)b * bs_src;
+  T* d = dst + (long long)b * bs_dst;
+  const int tx = threadIdx.x & 63, ty = threadIdx.x >> 6;  // 64 x 4
+#pragma unroll 4
+  for (int i = ty; i < 64; i += 4) {
+    const int r = r0 + i, c = c0 + tx;
+    if (r < rows && c < cols) tile[i][tx] = s[(long long)r * ld_src + c];
+  }
+  __syncthreads();
+#pragma unroll 4
+  for (int i = ty; i < 64; i += 4) {
+    const int c = c0 + i, r = r0 + tx;
+    if (r < rows && c < cols) d[(long long)c * ld_dst + r] = tile[tx][i];
+  }
+}
+
+// zero the pad channels [C, ld) of an NHWC buffer
+__global__ void zero_pad_kernel(int8_t* y, long long npix, int C, int ld, int eb) {
+  const int padb = (ld - C) * eb;
+  const long long total = npix * padb;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total;
+       i += (long long)gridDim.x * blockDim.x) {
+    const long long px = i / padb;
+    const int o = (int)(i - px * padb);
+    y[(px * ld + C) * eb + o] = 0;
+  }
+}
+
+// fused entry of the int8 region: fp32 NCHW -> int8 NHWC(ld), pad channels = 0.
+// One block stages a [C x 64 pixels] slab: reads are coalesced along HW, writes
+// are coalesced along the (padded) channel pitch.
+__global__ void __launch_bounds__(256)
+quant_nchw_to_nhwc_kernel(const float* __restrict__ x, int8_t* __restrict__ y, int C, long long HW,
+                          int ld, float scale, float inv, int round_mode) {
+  extern __shared__ int8_t slab[];  // [64][ld]
+  const int n = blockIdx.y;
+  const long long hw0 = (long long)blockIdx.x * 64;
+  const int npx = (int)((HW - hw0) < 64 ? (HW - hw0) : 64);
+  const float* xs = x + (long long)n * C * HW;
+  for (int i = threadIdx.x; i < 64 * ld; i += 256) {
+    const int c = i >> 6, px = i & 63;  // px fastest: coalesced global reads
+    if (c < ld) {
+      int8_t q = 0;
+      if (c < C && px < npx)
+        q = (int8_t)round_sat_i8(quant_pre(__ldg(xs + (long long)c * HW + hw0 + px), scale, inv, round_mode),
+                                 round_mode);
+      slab[px * ld + c] = q;
+    }
+  }
+  __syncthreads();
+  int8_t* yo = y + ((long long)n * HW + hw0) * ld;
+  const int bytes = npx * ld;
+  if ((ld & 15) == 0 && (reinterpret_cast<uintptr_t>(y) & 15) == 0) {
+    for (int i = threadIdx.x; i < (bytes >> 4); i += 256)
+      reinterpret_cast<uint4*>(yo)[i] = reinterpret_cast<const uint4*>(slab)[i];
+  } else {
+    for (int i = threadIdx.x; i < bytes; i += 256) yo[i] = slab[i];
+  }
+}
+
+// ------------------------------------------------------------------ pooling
+__global__ void __launch_bounds__(256)
+pool_kernel(const int8_t* __restrict__ x, int ldx, void* __restrict__ y, int ldy, int N, int H, int W,
+            int C, int kh, int kw, int sh, int sw, int pt, int pl_, int P, int Q, int pool_type,
+            int exclusive, float rescale, int out_dtype, int round_mode, int vec) {
+  const int CG = vec ? (C + 15) / 16 : C;
+  const long long total = (long long)N * P * Q * CG;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total;
+       i += (long long)gridDim.x * blockDim.x) {
+    const int cg = (int)(i % CG);
+    long long t = i / CG;
+    const int oq = (int)(t % Q);
+    t /= Q;
+    const int op = (int)(t % P);
+    const int n = (int)(t / P);
+    int h0 = op * sh - pt, w0 = oq * sw - pl_;
+    const int h1 = h0 + kh < H ? h0 + kh : H, w1 = w0 + kw < W ? w0 + kw : W;
+    if (h0 < 0) h0 = 0;
+    if (w0 < 0) w0 = 0;
+    const int cnt = exclusive ? (h1 - h0) * (w1 - w0) : kh * kw;
+    const int c0 = vec ? cg * 16 : cg;
+    const int nch = vec ? (C - c0 < 16 ? C - c0 : 16) : 1;
+    int sum[16], mx[16];
+#pragma unroll
+    for (int j = 0; j < 16; ++j) { sum[j] = 0; mx[j] = -128; }
+    for (int h = h0; h < h1; ++h)
+      for (int w = w0; w < w1; ++w) {
+        const int8_t* xp = x + (((long long)n * H + h) * W + w) * ldx + c0;
+        if (vec) {
+          const uint4 v = __ldg(reinterpret_cast<const uint4*>(xp));
+          const uint32_t wd[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+          for (int j = 0; j < 16; ++j) {
+            const int e = (int)(int8_t)((wd[j >> 2] >> (8 * (j & 3))) & 0xff);
+            sum[j] += e;
+            mx[j] = e > mx[j] ? e : mx[j];
+          }
+        } else {
+          const int e = (int)__ldg(xp);
+          sum[0] += e;
+          mx[0] = e > mx[0] ? e : mx[0];
+        }
+      }
+    const long long o = (((long long)n * P + op) * Q + oq) * ldy + c0;
+    float v[16];
+#pragma unroll
+    for (int j = 0; j < 16; ++j) {
+      if (pool_type == PL_POOL_MAX)
+        v[j] = __fmul_rn((float)mx[j], rescale);
+      else
+        v[j] = __fmul_rn(__fdiv_rn((float)sum[j], (float)cnt), rescale);
+    }
+    if (out_dtype == PL_OUT_FP32) {
+      float* out = reinterpret_cast<float*>(y) + o;
+#pragma unroll
+      for (int j = 0; j < 16; ++j)
+        if (j < nch) out[j] = v[j];
+    } else {
+      int8_t* out = reinterpret_cast<int8_t*>(y) + o;
+      int q[16];
+#pragma unroll
+      for (int j = 0; j < 16; ++j) q[j] = round_sat_i8(v[j], round_mode);
+      if (vec && nch == 16 && (ldy & 15) == 0 && (reinterpret_cast<uintptr_t>(y) & 15) == 0) {
+        *reinterpret_cast<uint4*>(out) =
+            make_uint4(pack4_i8(q[0], q[1], q[2], q[3]), pack4_i8(q[4], q[5], q[6], q[7]),
+                       pack4_i8(q[8], q[9], q[10], q[11]), pack4_i8(q[12], q[13], q[14], q[15]));
+      } else {
+#pragma unroll
+        for (int j = 0; j < 16; ++j)
+          if (j < nch) out[j] = (int8_t)q[j];
+      }
+    }
+  }
+}
+
+// ------------------------------------------------------------- residual add
+__device__ __forceinline__ float add_value(int a, int b, float sa, float sb, int act, float arg) {
+  const float v = __fmaf_rn((float)a, sa, __fmul_rn((float)b, sb));
+  return apply_act(v, act, arg);
+}
+
+__global__ void __launch_bounds__(256)
+add_kernel(const int8_t* __restrict__ a, const int8_t* __restrict__ b, void* __restrict__ y,
+           long long n, float sa, float sb, int act, float arg, int out_dtype, int round_mode,
+           int vec) {
+  const long long stride = (long long)gridDim.x * blockDim.x;
+  long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (vec) {
+    const long long n16 = n >> 4;
+    for (; i < n16; i += stride) {
+      const uint4 va = __ldg(reinterpret_cast<const uint4*>(a) + i);
+      const uint4 vb = __ldg(reinterpret_cast<const uint4*>(b) + i);
+      const uint32_t wa[4] = {va.x, va.y, va.z, va.w}, wb[4] = {vb.x, vb.y, vb.z, vb.w};
+      float v[16];
+#pragma unroll
+      for (int j = 0; j < 16; ++j) {
+        const int ea = (int)(int8_t)((wa[j >> 2] >> (8 * (j & 3))) & 0xff);
+        const int eb = (int)(int8_t)((wb[j >> 2] >> (8 * (j & 3))) & 0xff);
+        v[j] = add_value(ea, eb, sa, sb, act, arg);
+      }
+      if (out_dtype == PL_OUT_FP32) {
+        float4* yp = reinterpret_cast<float4*>(y) + i * 4;
+#pragma unroll
+        for (int k = 0; k < 4; ++k) yp[k] = make_float4(v[4 * k], v[4 * k + 1], v[4 * k + 2], v[4 * k + 3]);
+      } else {
+        uint32_t o[4];
+#pragma unroll
+        for (int k = 0; k < 4; ++k)
+          o[k] = pack4_i8(round_sat_i8(v[4 * k], round_mode), round_sat_i8(v[4 * k + 1], round_mode),
+                          round_sat_i8(v[4 * k + 2], round_mode), round_sat_i8(v[4 * k + 3], round_mode));
+        reinterpret_cast<uint4*>(y)[i] = make_uint4(o[0], o[1], o[2], o[3]);
+      }
+    }
+    i = (n16 << 4) + (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  }
+  for (; i < n; i += stride) {
+    const float v = add_value((int)a[i], (int)b[i], sa, sb, act, arg);
+    if (out_dtype == PL_OUT_FP32)
+      reinterpret_cast<float*>(y)[i] = v;
+    else
+      reinterpret_cast<int8_t*>(y)[i] = (int8_t)round_sat_i8(v, round_mode);
+  }
+}
+
+}  // namespace pl
+
+using namespace pl;
+
+static inline bool al16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; }
+
+extern "C" int pl_quantize_f32_i8(const float* x, int8_t* y, int64_t n, float scale, int round_mode,
+                                  pl_stream_t stream) {
+  if (!x || !y || n < 0 || !(scale > 0.f)) return PL_ERR_ARG;
+  if (n == 0) return PL_OK;
+  const int vec = al16(x) && al16(y);
+  quantize_kernel<<<grid_for(vec ? (n + 15) / 16 : n, 256), 256, 0, (cudaStream_t)stream>>>(
+      x, y, n, scale, 1.f / scale, round_mode, vec);
+  ++g_launches;
+  return launch_status();
+}
+
+extern "C" int pl_dequantize_i8_f32(const int8_t* x, float* y, int64_t n, float scale,
+                                    pl_stream_t stream) {
+  if (!x || !y || n < 0) return PL_ERR_ARG;
+  if (n == 0) return PL_OK;
+  const int vec = al16(x) && al16(y);
+  dequantize_kernel<<<grid_for(vec ? (n + 15) / 16 : n, 256), 256, 0, (cudaStream_t)stream>>>(
+      x, y, n, scale, vec);
+  ++g_launches;
+  return launch_status();
+}
+
+template <typename T>
+static int launch_transpose(const T* src, T* dst, int B, int rows, int cols, long long ld_src,
+                            long long ld_dst, long long bs_src, long long bs_dst, cudaStream_t st) {
+  if (B > 65535) return PL_ERR_UNSUPPORTED;
+  dim3 grid((cols + 63) / 64, (rows + 63) / 64, B);
+  transpose_kernel<T><<<grid, 256, 0, st>>>(src, dst, rows, cols, ld_src, ld_dst, bs_src, bs_dst);
+  ++g_launches;
+  return launch_status();
+}
+
+extern "C" int pl_transpose_i8(const int8_t* src, int ld_src, int8_t* dst, int ld_dst, int rows,
+                               int cols, pl_stream_t stream) {
+  if (!src || !dst || rows <= 0 || cols <= 0 || ld_src < cols || ld_dst < rows) return PL_ERR_ARG;
+  return launch_transpose<int8_t>(src, dst, 1, rows, cols, ld_src, ld_dst, 0, 0, (cudaStream_t)stream);
+}
+
+extern "C" int pl_nchw_to_nhwc(const void* x, void* y, int N, int C, int H, int W, int ld,
+                               int elem_bytes, pl_stream_t stream) {
+  if (!x || !y || N <= 0 || C <= 0 || H <= 0 || W <= 0 || ld < C) return PL_ERR_ARG;
+  const long long HW = (long long)H * W;
+  if (HW > 0x7fffffffLL) return PL_ERR_UNSUPPORTED;
+  int rc;
+  // [N][C][HW] -> [N][HW][ld]
+  if (elem_bytes == 1)
+    rc = launch_transpose<int8_t>((const int8_t*)x, (int8_t*)y, N, C, (int)HW, HW, ld, (long long)C * HW,
+                                  HW * ld, (cudaStream_t)stream);
+  else if (elem_bytes == 4)
+    rc = launch_transpose<float>((const float*)x, (float*)y, N, C, (int)HW, HW, ld, (long long)C * HW,
+                                 HW * ld, (cudaStream_t)stream);
+  else
+    return PL_ERR_ARG;
+  if (rc == PL_OK && ld > C) {
+    zero_pad_kernel<<<grid_for((long long)N * HW * (ld - C) * elem_bytes, 256), 256, 0,
+                      (cudaStream_t)stream>>>((int8_t*)y, (long long)N * HW, C, ld, elem_bytes);
+    ++g_launches;
+    rc = launch_status();
+  }
+  return rc;
+}
+
+extern "C" int pl_nhwc_to_nchw(const void* x, void* y, int N, int C, int H, int W, int ld,
+                               int elem_bytes, pl_stream_t stream) {
+  if (!x || !y || N <= 0 || C <= 0 || H <= 0 || W <= 0 || ld < C) return PL_ERR_ARG;
+  const long long HW = (long long)H * W;
+  if (HW > 0x7fffffffLL) return PL_ERR_UNSUPPORTED;
+  // [N][HW][ld] -> [N][C][HW]
+  if (elem_bytes == 1)
+    return launch_transpose<int8_t>((const int8_t*)x, (int8_t*)y, N, (int)HW, C, ld, HW, HW * ld,
+                                    (long long)C * HW, (cudaStream_t)stream);
+  if (elem_bytes == 4)
+    return launch_transpose<float>((const float*)x, (float*)y, N, (int)HW, C, ld, HW, HW * ld,
+                                   (long long)C * HW, (cudaStream_t)stream);
+  return PL_ERR_ARG;
+}
+
+extern "C" int pl_quantize_nchw_f32_to_nhwc_i8(const float* x, int8_t* y, int N, int C, int H, int W,
+                                               int ldy, float scale, int round_mode,
+                                               pl_stream_t stream) {
+  if (!x || !y || N <= 0 || C <= 0 || H <= 0 || W <= 0 || ldy < C || !(scale > 0.f)) return PL_ERR_ARG;
+  if (N > 65535 || (size_t)64 * ldy > 48 * 1024) return PL_ERR_UNSUPPORTED;
+  const long long HW = (long long)H * W;
+  dim3 grid((unsigned)((HW + 63) / 64), (unsigned)N);
+  quant_nchw_to_nhwc_kernel<<<grid, 256, (size_t)64 * ldy, (cudaStream_t)stream>>>(
+      x, y, C, HW, ldy, scale, 1.f / scale, round_mode);
+  ++g_launches;
+  return launch_status();
+}
+
+extern "C" int pl_pool2d_i8_nhwc(const int8_t* x, int ldx, void* y, int ldy, int N, int H, int W, int C,
+                                 int kh, int kw, int sh, int sw, int pt, int pl_, int P, int Q,
+                                 int pool_type, int exclusive, float rescale, int out_dtype,
+                                 int round_mode, pl_stream_t stream) {
+  if (!x || !y || N <= 0 || H <= 0 || W <= 0 || C <= 0 || kh <= 0 || kw <= 0 || sh <= 0 || sw <= 0 ||
+      P <= 0 || Q <= 0 || ldx < C || ldy < C)
+    return PL_ERR_ARG;
+  if (out_dtype != PL_OUT_INT8 && out_dtype != PL_OUT_FP32) return PL_ERR_ARG;
+  const int vec = al16(x) && (ldx % 16 == 0);
+  const long long items = (long long)N * P * Q * (vec ? (C + 15) / 16 : C);
+  pool_kernel<<<grid_for(items, 256), 256, 0, (cudaStream_t)stream>>>(
+      x, ldx, y, ldy, N, H, W, C, kh, kw, sh, sw, pt, pl_, P, Q, pool_type, exclusive, rescale,
+      out_dtype, round_mode, vec);
+  ++g_launches;
+  return launch_status();
+}
+
+extern "C" int pl_add_i8(const int8_t* a, const int8_t* b, void* y, int64_t n, float sa, float sb,
+                         int act, float act_arg, int out_dtype, int round_mode, pl_stream_t stream) {
+  if (!a || !b || !y || n < 0) return PL_ERR_ARG;
+  if (out_dtype != PL_OUT_INT8 && out_dtype != PL_OUT_FP32) return PL_ERR_ARG;
+  if (n == 0) return PL_OK;
+  const int vec = al16(a) && al16(b) && al16(y);
+  add_kernel<<<grid_for(vec ? (n + 15) / 16 : n, 256), 256, 0, (cudaStream_t)stream>>>(
+      a, b, y, n, sa, sb, act, act_arg, out_dtype, round_mode, vec);
+  ++g_launches;
+  return launch_status();
+}

@@ -1,0 +1,567 @@
+// igemm_i8.cu -- dense int8 conv (implicit GEMM over NHWC) and fc/matmul GEMM
+// on the 5th-gen tensor cores: TMA (tiled or im2col mode) -> swizzled smem ring
+// -> tcgen05.mma kind::i8 (M=128, N=BN, K=32/instr) -> int32 accumulators in
+// TMEM (double buffered) -> tcgen05.ld -> fused scale/bias/act/requant epilogue.
+//
+// Replaces lite/backends/cuda/math/cudnn_conv.cc:320-585 (cuDNN int8 conv into
+// an fp32 temporary + a second elementwise kernel, activation.cu:91-446) with
+// ONE kernel and no temporary.  Semantics of the epilogue: common.cuh.
+//
+// Warp roles (192 threads, persistent over output tiles):
+//   warp 0      TMA producer (one lane)
+//   warp 1      TMEM allocator + MMA issuer (one lane)
+//   warps 2..5  epilogue; warp w reads TMEM lanes [32*(w%4), 32*(w%4)+32)
+#include <cuda.h>
+#include <cudaTypedefs.h>
+
+#include "common.cuh"
+
+namespace pl {
+
+static constexpr int kBM = 128;       // rows of D per tile (TMEM lanes)
+static constexpr int kThreads = 192;  // 6 warps
+static constexpr int kMaxStages = 8;
+
+struct IgemmParams {
+  int M, Nout;
+  int m_tiles, n_tiles;
+  int BN, BK, stages;
+  int num_kb, cblocks;
+  int mode;  // 0: A is a [M, K] matrix (tiled TMA); 1: A is NHWC, im2col TMA
+  int Q, PQ, S;
+  int sh, sw, pt, pl_, dh, dw;
+  uint32_t a_stage_bytes, b_stage_bytes, tx_bytes, tmem_cols;
+  void* y;
+  int ldy;
+  int vec_ok;  // 16-byte vector stores allowed
+  EpiParams epi;
+};
+
+// --------------------------------------------------------------------------
+// epilogue for one 16-column chunk held in registers
+// --------------------------------------------------------------------------
+__device__ __forceinline__ void store_chunk16(const IgemmParams& p, const uint32_t (&acc)[16],
+                                              long long row, int n_base) {
+  const EpiParams& e = p.epi;
+  const bool full = (n_base + 16 <= p.Nout);
+  if (e.out_dtype == PL_OUT_INT32) {
+    int* out = reinterpret_cast<int*>(p.y) + row * p.ldy + n_base;
+    if (full && p.vec_ok) {
+#pragma unroll
+      for (int j = 0; j < 16; j += 4)
+        *reinterpret_cast<int4*>(out + j) =
+            make_int4((int)acc[j], (int)acc[j + 1], (int)acc[j + 2], (int)acc[j + 3]);
+    } else {
+#pragma unroll
+      for (int j = 0; j < 16; ++j)
+        if (n_base + j < p.Nout) out[j] = (int)acc[j];
+    }
+    return;
+  }
+  float v[16];
+#pragma unroll
+  for (int j = 0; j < 16; ++j) {
+    const int n = n_base + j;
+    float s = 0.f, b = 0.f;
+    if (n < p.Nout) {
+      s = __ldg(e.scale + n);
+      if (e.bias) b = __ldg(e.bias + n);
+    }
+    float t = __fmaf_rn(__int2float_rn((int)acc[j]), s, b);
+    if (e.residual && n < p.Nout)
+      t = __fmaf_rn((float)e.residual[row * e.ld_res + n], e.res_scale, t);
+    v[j] = (e.round_mode == PL_ROUND_CUDA_LEGACY) ? apply_act_legacy(t, e.act, e.act_arg, e.vec4)
+                                                  : apply_act(t, e.act, e.act_arg);
+  }
+  if (e.out_dtype == PL_OUT_FP32) {
+    float* out = reinterpret_cast<float*>(p.y) + row * p.ldy + n_base;
+    if (full && p.vec_ok) {
+#pragma unroll
+      for (int j = 0; j < 16; j += 4)
+        *reinterpret_cast<float4*>(out + j) = make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]);
+    } else {
+#pragma unroll
+      for (int j = 0; j < 16; ++j)
+        if (n_base + j < p.Nout) out[j] = v[j];
+    }
+  } else {
+    int q[16];
+#pragma unroll
+    for (int j = 0; j < 16; ++j) q[j] = round_sat_i8(v[j], e.round_mode);
+    int8_t* out = reinterpret_cast<int8_t*>(p.y) + row * p.ldy + n_base;
+    if (full && p.vec_ok) {
+      *reinterpret_cast<uint4*>(out) =
+          make_uint4(pack4_i8(q[0], q[1], q[2], q[3]), pack4_i8(q[4], q[5], q[6], q[7]),
+                     pack4_i8(q[8], q[9], q[10], q[11]), pack4_i8(q[12], q[13], q[14], q[15]));
+    } else {
+#pragma unroll
+      for (int j = 0; j < 16; ++j)
+        if (n_base + j < p.Nout) out[j] = (int8_t)q[j];
+    }
+  }
+}
+
+// --------------------------------------------------------------------------
+// the kernel
+// --------------------------------------------------------------------------
+__global__ void __launch_bounds__(kThreads, 1)
+igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
+                const __grid_constant__ CUtensorMap tmap_b, const IgemmParams p) {
+  extern __shared__ uint8_t smem_raw[];
+  __shared__ __align__(8) uint64_t bars[2 * kMaxStages + 4];
+  __shared__ uint32_t tmem_base_slot;
+
+  const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+  const uint32_t smem_a = smem_base;
+  const uint32_t smem_b = smem_base + p.stages * p.a_stage_bytes;
+  const uint32_t bar_full = smem_u32(&bars[0]);
+  const uint32_t bar_empty = smem_u32(&bars[kMaxStages]);
+  const uint32_t bar_tfull = smem_u32(&bars[2 * kMaxStages]);
+  const uint32_t bar_tempty = smem_u32(&bars[2 * kMaxStages + 2]);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const int num_tiles = p.m_tiles * p.n_tiles;
+
+  if (threadIdx.x == 0) {
+    tma_prefetch_desc(&tmap_a);
+    tma_prefetch_desc(&tmap_b);
+    for (int s = 0; s < p.stages; ++s) {
+      mbar_init(bar_full + 8 * s, 1);
+      mbar_init(bar_empty + 8 * s, 1);
+    }
+    for (int s = 0; s < 2; ++s) {
+      mbar_init(bar_tfull + 8 * s, 1);
+      mbar_init(bar_tempty + 8 * s, 128);
+    }
+    fence_barrier_init();
+  }
+  if (warp == 1) {
+    tmem_alloc(smem_u32(&tmem_base_slot), p.tmem_cols);
+    tmem_relinquish();
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = tmem_base_slot;
+
+  if (warp == 0) {
+    // ===================== TMA producer =====================
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      const uint32_t tx = p.tx_bytes;
+      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+        const int tn = tile % p.n_tiles, tm = tile / p.n_tiles;
+        const int m0 = tm * kBM, n0 = tn * p.BN;
+        int bw = 0, bh = 0, bn = 0;
+        if (p.mode == 1) {
+          bn = m0 / p.PQ;
+          const int rem = m0 - bn * p.PQ;
+          const int op = rem / p.Q, oq = rem - op * p.Q;
+          bw = oq * p.sw - p.pl_;
+          bh = op * p.sh - p.pt;
+        }
+        int tap = 0, cb = 0;
+        for (int kb = 0; kb < p.num_kb; ++kb) {
+          mbar_wait(bar_empty + 8 * stage, phase ^ 1);
+          mbar_arrive_expect_tx(bar_full + 8 * stage, tx);
+          const uint32_t dst_a = smem_a + stage * p.a_stage_bytes;
+          const uint32_t dst_b = smem_b + stage * p.b_stage_bytes;
+          if (p.mode == 1) {
+            const int r = tap / p.S, s = tap - r * p.S;
+            tma_load_im2col_4d(dst_a, &tmap_a, bar_full + 8 * stage, cb * p.BK, bw, bh, bn,
+                               (uint16_t)(s * p.dw), (uint16_t)(r * p.dh));
+          } else {
+            tma_load_2d(dst_a, &tmap_a, bar_full + 8 * stage, kb * p.BK, m0);
+          }
+          tma_load_2d(dst_b, &tmap_b, bar_full + 8 * stage, kb * p.BK, n0);
+          if (++cb == p.cblocks) { cb = 0; ++tap; }
+          if (++stage == p.stages) { stage = 0; phase ^= 1; }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ===================== MMA issuer =====================
+    if (lane == 0) {
+      const uint32_t idesc = make_idesc_i8((uint32_t)p.BN);
+      const uint64_t desc_hi = make_smem_desc_base((uint32_t)p.BK);
+      const int ksteps = p.BK / 32;
+      int stage = 0;
+      uint32_t phase = 0;
+      int as = 0;
+      uint32_t aphase = 0;
+      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+        mbar_wait(bar_tempty + 8 * as, aphase ^ 1);
+        tc_fence_after();
+        const uint32_t d_tmem = tmem_base + (uint32_t)(as * p.BN);
+        for (int kb = 0; kb < p.num_kb; ++kb) {
+          mbar_wait(bar_full + 8 * stage, phase);
+          tc_fence_after();
+          const uint64_t da = desc_hi | (uint64_t)(((smem_a + stage * p.a_stage_bytes) >> 4) & 0x3fff);
+          const uint64_t db = desc_hi | (uint64_t)(((smem_b + stage * p.b_stage_bytes) >> 4) & 0x3fff);
+          for (int k = 0; k < ksteps; ++k)
+            umma_i8(d_tmem, da + (uint64_t)(k * 2), db + (uint64_t)(k * 2), idesc,
+                    (uint32_t)((kb | k) != 0));
+          umma_commit(bar_empty + 8 * stage);
+          if (++stage == p.stages) { stage = 0; phase ^= 1; }
+        }
+        umma_commit(bar_tfull + 8 * as);
+        if (++as == 2) { as = 0; aphase ^= 1; }
+      }
+    }
+  } else {
+    // ===================== epilogue (warps 2..5) =====================
+    const int quarter = warp & 3;
+    int as = 0;
+    uint32_t aphase = 0;
+    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+      const int tn = tile % p.n_tiles, tm = tile / p.n_tiles;
+      const long long row = (long long)tm * kBM + quarter * 32 + lane;
+      const int n0 = tn * p.BN;
+      mbar_wait(bar_tfull + 8 * as, aphase);
+      tc_fence_after();
+      const uint32_t t_addr = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(as * p.BN);
+      for (int c0 = 0; c0 < p.BN; c0 += 16) {
+        uint32_t acc[16];
+        tmem_ld_32x32b_x16(t_addr + (uint32_t)c0, acc);
+        tmem_ld_wait();
+        if (row < p.M && n0 + c0 < p.Nout) store_chunk16(p, acc, row, n0 + c0);
+      }
+      tc_fence_before();
+      mbar_arrive(bar_tempty + 8 * as);
+      if (++as == 2) { as = 0; aphase ^= 1; }
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, p.tmem_cols);
+  }
+}
+
+
+// --------------------------------------------------------------------------
+// tensor-pipe micro-benchmark: back-to-back MMAs on resident smem operands
+// --------------------------------------------------------------------------
+__global__ void __launch_bounds__(128, 1) i8_mma_peak_kernel(int iters, int bn, int32_t* out) {
+  extern __shared__ uint8_t smem_raw[];
+  __shared__ __align__(8) uint64_t bar;
+  __shared__ uint32_t tmem_slot;
+  const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+  const uint32_t sa = base, sb = base + 128 * 128;
+  // deterministic small operands so the checksum is reproducible
+  for (uint32_t i = threadIdx.x; i < (128u + (uint32_t)bn) * 128u / 4u; i += blockDim.x)
+    asm volatile("st.shared.b32 [%0], %1;" ::"r"(base + 4 * i), "r"(0x01010101u));
+  fence_proxy_async();
+  const int warp = threadIdx.x >> 5;
+  if (threadIdx.x == 0) {
+    mbar_init(smem_u32(&bar), 1);
+    fence_barrier_init();
+  }
+  if (warp == 0) {
+    tmem_alloc(smem_u32(&tmem_slot), 512);
+    tmem_relinquish();
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = tmem_slot;
+  if (threadIdx.x == 0) {
+    const uint32_t idesc = make_idesc_i8((uint32_t)bn);
+    const uint64_t hi = make_smem_desc_base(128);
+    const uint64_t da = hi | (uint64_t)((sa >> 4) & 0x3fff), db = hi | (uint64_t)((sb >> 4) & 0x3fff);
+    for (int i = 0; i < iters; ++i) {
+      const uint32_t d = tmem + (uint32_t)((i & 1) * bn);
+#pragma unroll
+      for (int k = 0; k < 4; ++k) umma_i8(d, da + 2 * k, db + 2 * k, idesc, (uint32_t)(i > 1 || k > 0));
+    }
+    umma_commit(smem_u32(&bar));
+  }
+  mbar_wait(smem_u32(&bar), 0);
+  tc_fence_after();
+  uint32_t r[16];
+  tmem_ld_32x32b_x16(tmem + ((uint32_t)(warp * 32) << 16), r);
+  tmem_ld_wait();
+  if (threadIdx.x == 0 && blockIdx.x == 0) out[0] = (int32_t)r[0];
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 0) {
+    tc_fence_after();
+    tmem_dealloc(tmem, 512);
+  }
+}
+
+// --------------------------------------------------------------------------
+// filter packing: OHWI [K,R,S,C] -> [K][R*S][Cb*BK], zero padded
+// --------------------------------------------------------------------------
+__global__ void pack_conv_weight_kernel(const int8_t* __restrict__ w, int8_t* __restrict__ out,
+                                        int K, int RS, int C, int cpad) {
+  const long long total = (long long)K * RS * cpad;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
+       i += (long long)gridDim.x * blockDim.x) {
+    const int c = (int)(i % cpad);
+    const long long kt = i / cpad;  // k * RS + tap
+    out[i] = c < C ? w[kt * C + c] : (int8_t)0;
+  }
+}
+
+// --------------------------------------------------------------------------
+// host: tensor maps
+// --------------------------------------------------------------------------
+namespace {
+
+struct DriverFns {
+  PFN_cuTensorMapEncodeTiled_v12000 tiled = nullptr;
+  PFN_cuTensorMapEncodeIm2col_v12000 im2col = nullptr;
+  int sm_count = 0;
+  int cc_major = 0;
+  int driver_version = 0;
+  bool ok = false;
+};
+
+DriverFns& driver() {
+  static DriverFns d = [] {
+    DriverFns f;
+    cudaDriverEntryPointQueryResult q;
+    void* fn = nullptr;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &q) == cudaSuccess &&
+        q == cudaDriverEntryPointSuccess)
+      f.tiled = reinterpret_cast<PFN_cuTensorMapEncodeTiled_v12000>(fn);
+    fn = nullptr;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeIm2col", &fn, cudaEnableDefault, &q) == cudaSuccess &&
+        q == cudaDriverEntryPointSuccess)
+      f.im2col = reinterpret_cast<PFN_cuTensorMapEncodeIm2col_v12000>(fn);
+    int dev = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&f.sm_count, cudaDevAttrMultiProcessorCount, dev);
+    cudaDeviceGetAttribute(&f.cc_major, cudaDevAttrComputeCapabilityMajor, dev);
+    cudaDriverGetVersion(&f.driver_version);
+    f.ok = f.tiled && f.im2col;
+    return f;
+  }();
+  return d;
+}
+
+CUtensorMapSwizzle swizzle_for(int bk) {
+  return bk == 128 ? CU_TENSOR_MAP_SWIZZLE_128B
+                   : (bk == 64 ? CU_TENSOR_MAP_SWIZZLE_64B : CU_TENSOR_MAP_SWIZZLE_32B);
+}
+
+// 2-D K-major byte matrix [rows, cols] with row pitch ld; box = [box_rows, bk]
+int encode_2d(CUtensorMap* m, const void* base, uint64_t cols, uint64_t rows, uint64_t ld, int bk,
+              int box_rows) {
+  cuuint64_t dims[2] = {cols, rows};
+  cuuint64_t strides[1] = {ld};
+  cuuint32_t box[2] = {(cuuint32_t)bk, (cuuint32_t)box_rows};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = driver().tiled(m, CU_TENSOR_MAP_DATA_TYPE_UINT8, 2, const_cast<void*>(base), dims,
+                              strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, swizzle_for(bk),
+                              CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  return r == CUDA_SUCCESS ? PL_OK : PL_ERR_DRIVER;
+}
+
+int encode_im2col(CUtensorMap* m, const void* x, const pl_conv_desc* d, int bk) {
+  cuuint64_t dims[4] = {(cuuint64_t)d->C, (cuuint64_t)d->W, (cuuint64_t)d->H, (cuuint64_t)d->N};
+  cuuint64_t strides[3] = {(cuuint64_t)d->ldx, (cuuint64_t)d->ldx * d->W,
+                           (cuuint64_t)d->ldx * d->W * d->H};
+  int lower[2] = {-d->pad_l, -d->pad_t};
+  int upper[2] = {d->pad_r - (d->S - 1) * d->dil_w, d->pad_b - (d->R - 1) * d->dil_h};
+  cuuint32_t estr[4] = {1, (cuuint32_t)d->stride_w, (cuuint32_t)d->stride_h, 1};
+  CUresult r = driver().im2col(m, CU_TENSOR_MAP_DATA_TYPE_UINT8, 4, const_cast<void*>(x), dims,
+                               strides, lower, upper, (cuuint32_t)bk, (cuuint32_t)kBM, estr,
+                               CU_TENSOR_MAP_INTERLEAVE_NONE, swizzle_for(bk),
+                               CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) return PL_ERR_DRIVER;
+  // Same guard CUTLASS applies (cute/atom/copy_traits_sm90_im2col.hpp): drivers
+  // <= 13.1 mis-encode im2col maps of tensors smaller than 128 KiB.
+  if (driver().driver_version <= 13010 &&
+      (uint64_t)d->ldx * d->W * d->H * d->N < 131072ull)
+    reinterpret_cast<uint64_t*>(m)[1] &= ~(1ull << 21);
+  return PL_OK;
+}
+
+uint32_t pow2_cols(int n) {
+  uint32_t c = 32;
+  while ((int)c < n) c <<= 1;
+  return c;
+}
+
+int pick_bn(int Nout, int m_tiles, int sms) {
+  // widest tile that does not over-cover Nout, narrowed until the grid fills the SMs
+  const int n16 = (Nout + 15) / 16 * 16;
+  int cap = 256;
+  while (cap > 16 && cap / 2 >= n16) cap >>= 1;
+  int bn = cap;
+  while (bn > 16 && m_tiles * ((Nout + bn - 1) / bn) < sms) bn >>= 1;
+  return bn;
+}
+
+int launch_igemm(const CUtensorMap& ta, const CUtensorMap& tb, IgemmParams& p, pl_stream_t stream) {
+  const int smem_budget = 200 * 1024;
+  int stages = smem_budget / (int)(p.a_stage_bytes + p.b_stage_bytes);
+  if (stages > kMaxStages) stages = kMaxStages;
+  if (stages > p.num_kb && p.num_kb >= 2) stages = p.num_kb;
+  if (stages < 2) stages = 2;
+  p.stages = stages;
+  const size_t smem = (size_t)stages * (p.a_stage_bytes + p.b_stage_bytes) + 1024;
+  static size_t configured = 0;
+  if (smem > configured) {
+    PL_CUDA_OK(cudaFuncSetAttribute(igemm_i8_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                    (int)(227 * 1024)));
+    configured = 227 * 1024;
+  }
+  const int tiles = p.m_tiles * p.n_tiles;
+  const int grid = tiles < driver().sm_count ? tiles : driver().sm_count;
+  igemm_i8_kernel<<<grid, kThreads, smem, (cudaStream_t)stream>>>(ta, tb, p);
+  ++g_launches;
+  return launch_status();
+}
+
+int check_epi(const pl_epilogue* e) {
+  if (!e) return PL_ERR_ARG;
+  if (e->out_dtype != PL_OUT_INT8 && e->out_dtype != PL_OUT_FP32 && e->out_dtype != PL_OUT_INT32)
+    return PL_ERR_ARG;
+  if (e->out_dtype != PL_OUT_INT32 && !e->scale) return PL_ERR_ARG;
+  return PL_OK;
+}
+
+int common_setup(IgemmParams& p, long long M, int Nout, void* y, int ldy, const pl_epilogue* e) {
+  if (M <= 0 || Nout <= 0 || M > 0x7fffffffLL) return PL_ERR_ARG;
+  p.M = (int)M;
+  p.Nout = Nout;
+  p.m_tiles = (int)((M + kBM - 1) / kBM);
+  p.BN = pick_bn(Nout, p.m_tiles, driver().sm_count);
+  p.n_tiles = (Nout + p.BN - 1) / p.BN;
+  p.a_stage_bytes = (uint32_t)(kBM * p.BK);
+  p.b_stage_bytes = (uint32_t)((p.BN * p.BK + 1023) / 1024 * 1024);
+  p.tx_bytes = (uint32_t)(kBM * p.BK + p.BN * p.BK);
+  p.tmem_cols = pow2_cols(2 * p.BN);
+  p.y = y;
+  p.ldy = ldy;
+  p.epi = make_epi(e, Nout);
+  const int eb = e->out_dtype == PL_OUT_INT8 ? 1 : 4;
+  p.vec_ok = ((reinterpret_cast<uintptr_t>(y) & 15) == 0) && (((long long)ldy * eb) % 16 == 0);
+  return PL_OK;
+}
+
+}  // namespace
+}  // namespace pl
+
+// ============================================================================
+// C-ABI
+// ============================================================================
+using namespace pl;
+
+extern "C" int pl_conv_block_k(int C) { return C > 64 ? 128 : (C > 32 ? 64 : 32); }
+
+extern "C" size_t pl_conv_packed_weight_bytes(int K, int R, int S, int C) {
+  const int bk = pl_conv_block_k(C);
+  const int cpad = (C + bk - 1) / bk * bk;
+  return (size_t)K * R * S * cpad;
+}
+
+extern "C" int pl_pack_conv_weight_i8(const int8_t* w_ohwi, int8_t* w_packed, int K, int R, int S,
+                                      int C, pl_stream_t stream) {
+  if (!w_ohwi || !w_packed || K <= 0 || R <= 0 || S <= 0 || C <= 0) return PL_ERR_ARG;
+  const int bk = pl_conv_block_k(C);
+  const int cpad = (C + bk - 1) / bk * bk;
+  const long long total = (long long)K * R * S * cpad;
+  const int blocks = (int)((total + 255) / 256 > 4096 ? 4096 : (total + 255) / 256);
+  pack_conv_weight_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(w_ohwi, w_packed, K, R * S, C, cpad);
+  ++g_launches;
+  return launch_status();
+}
+
+extern "C" int pl_conv2d_i8_nhwc(const int8_t* x, const int8_t* w_packed, void* y,
+                                 const pl_conv_desc* d, const pl_epilogue* e, pl_stream_t stream) {
+  if (!x || !w_packed || !y || !d) return PL_ERR_ARG;
+  int rc = check_epi(e);
+  if (rc) return rc;
+  if (!driver().ok) return PL_ERR_DRIVER;
+  if (driver().cc_major != 10) return PL_ERR_DEVICE;
+  if (d->groups != 1) return PL_ERR_UNSUPPORTED;
+  if (d->N <= 0 || d->H <= 0 || d->W <= 0 || d->C <= 0 || d->K <= 0 || d->R <= 0 || d->S <= 0 ||
+      d->stride_h <= 0 || d->stride_w <= 0 || d->dil_h <= 0 || d->dil_w <= 0 || d->ldx < d->C ||
+      d->ldy < d->K)
+    return PL_ERR_ARG;
+  if ((reinterpret_cast<uintptr_t>(x) & 15) || (reinterpret_cast<uintptr_t>(w_packed) & 15) ||
+      (d->ldx % 16))
+    return PL_ERR_ALIGN;
+  const int P = pl_conv_out_size(d->H, d->R, d->dil_h, d->pad_t, d->pad_b, d->stride_h);
+  const int Q = pl_conv_out_size(d->W, d->S, d->dil_w, d->pad_l, d->pad_r, d->stride_w);
+  if (P <= 0 || Q <= 0) return PL_ERR_ARG;
+  const int up_w = d->pad_r - (d->S - 1) * d->dil_w, up_h = d->pad_b - (d->R - 1) * d->dil_h;
+  if (d->pad_l > 128 || d->pad_t > 128 || up_w < -128 || up_w > 127 || up_h < -128 || up_h > 127 ||
+      (d->S - 1) * d->dil_w > 255 || (d->R - 1) * d->dil_h > 255 || d->stride_w > 8 || d->stride_h > 8)
+    return PL_ERR_UNSUPPORTED;
+
+  IgemmParams p{};
+  p.BK = pl_conv_block_k(d->C);
+  p.cblocks = (d->C + p.BK - 1) / p.BK;
+  p.num_kb = d->R * d->S * p.cblocks;
+  rc = common_setup(p, (long long)d->N * P * Q, d->K, y, d->ldy, e);
+  if (rc) return rc;
+  const bool as_gemm = d->R == 1 && d->S == 1 && d->stride_h == 1 && d->stride_w == 1 &&
+                       d->pad_t == 0 && d->pad_b == 0 && d->pad_l == 0 && d->pad_r == 0;
+  CUtensorMap ta, tb;
+  if (as_gemm) {
+    p.mode = 0;
+    rc = encode_2d(&ta, x, (uint64_t)d->C, (uint64_t)p.M, (uint64_t)d->ldx, p.BK, kBM);
+  } else {
+    p.mode = 1;
+    p.Q = Q;
+    p.PQ = P * Q;
+    p.S = d->S;
+    p.sh = d->stride_h;
+    p.sw = d->stride_w;
+    p.pt = d->pad_t;
+    p.pl_ = d->pad_l;
+    p.dh = d->dil_h;
+    p.dw = d->dil_w;
+    rc = encode_im2col(&ta, x, d, p.BK);
+  }
+  if (rc) return rc;
+  const uint64_t wrow = (uint64_t)d->R * d->S * p.cblocks * p.BK;
+  rc = encode_2d(&tb, w_packed, wrow, (uint64_t)d->K, wrow, p.BK, p.BN);
+  if (rc) return rc;
+  return launch_igemm(ta, tb, p, stream);
+}
+
+extern "C" int pl_gemm_i8(const int8_t* A, int lda, const int8_t* Bt, int ldb, void* C, int ldc,
+                          int M, int N, int K, const pl_epilogue* e, pl_stream_t stream) {
+  if (!A || !Bt || !C || M <= 0 || N <= 0 || K <= 0 || lda < K || ldb < K || ldc < N)
+    return PL_ERR_ARG;
+  int rc = check_epi(e);
+  if (rc) return rc;
+  if (!driver().ok) return PL_ERR_DRIVER;
+  if (driver().cc_major != 10) return PL_ERR_DEVICE;
+  if ((reinterpret_cast<uintptr_t>(A) & 15) || (reinterpret_cast<uintptr_t>(Bt) & 15) || (lda % 16) ||
+      (ldb % 16))
+    return PL_ERR_ALIGN;
+  IgemmParams p{};
+  p.BK = pl_conv_block_k(K);
+  p.cblocks = (K + p.BK - 1) / p.BK;
+  p.num_kb = p.cblocks;
+  p.mode = 0;
+  rc = common_setup(p, M, N, C, ldc, e);
+  if (rc) return rc;
+  CUtensorMap ta, tb;
+  rc = encode_2d(&ta, A, (uint64_t)K, (uint64_t)M, (uint64_t)lda, p.BK, kBM);
+  if (rc) return rc;
+  rc = encode_2d(&tb, Bt, (uint64_t)K, (uint64_t)N, (uint64_t)ldb, p.BK, p.BN);
+  if (rc) return rc;
+  return launch_igemm(ta, tb, p, stream);
+}
+
+extern "C" int pl_i8_mma_peak(int ctas, int iters, int bn, int32_t* out, pl_stream_t stream) {
+  if (ctas <= 0 || iters <= 0 || bn < 16 || bn > 256 || (bn % 16) || !out) return PL_ERR_ARG;
+  const size_t smem = (size_t)(128 + bn) * 128 + 1024;
+  PL_CUDA_OK(cudaFuncSetAttribute(i8_mma_peak_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                  (int)smem));
+  i8_mma_peak_kernel<<<ctas, 128, smem, (cudaStream_t)stream>>>(iters, bn, out);
+  ++g_launches;
+  return launch_status();
+}

@@ -29,3 +29,11 @@ def pytest_collection_modifyitems(config, items):
     for it in items:
         if "gpu" in it.keywords:
             it.add_marker(skip)
+
+
+@pytest.fixture(scope="session")
+def pl():
+    """The product's C-ABI wrapper (fails loudly when the CUDA library is missing)."""
+    import __graft_entry__ as ge
+
+    return ge.load_package().capi

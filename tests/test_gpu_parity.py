@@ -1,0 +1,381 @@
+"""GPU parity tests (-m gpu): the sm_100a kernels, called through the C-ABI
+(include/pl_int8.h), against the CPU oracle on the same seeded inputs.
+
+Bar: int32 accumulators and int8 outputs bit-exact; fp32 outputs within 1e-5
+relative (north_star) -- both sides use one explicit fmaf, so they are in fact
+compared for equality and the tolerance is only the documented bound.
+Shapes follow the reference's own sweeps: lite/tests/math/conv_int8_compute_test.cc
+:481-731 (dw 3x3/5x5, 1x1, 3x3 s1/s2, random) and gemm_int8_compute_test.cc.
+"""
+import json
+import os
+
+import numpy as np
+import pytest
+import torch
+
+import orc
+
+pytestmark = pytest.mark.gpu
+HERE = os.path.dirname(os.path.abspath(__file__))
+DEV = "cuda:0"
+FP32_RTOL = 1e-5
+
+
+def dev(a):
+    return torch.from_numpy(np.ascontiguousarray(a)).to(DEV)
+
+
+def host(t):
+    torch.cuda.synchronize()
+    return t.cpu().numpy()
+
+
+def pad_c(x, ld):
+    """NHWC int8 -> channel pitch ld (zero pad)."""
+    if x.shape[-1] == ld:
+        return x
+    out = np.zeros(x.shape[:-1] + (ld,), x.dtype)
+    out[..., : x.shape[-1]] = x
+    return out
+
+
+def rup(v, m):
+    return (v + m - 1) // m * m
+
+
+def conv_inputs(case, seed):
+    N, H, W, Cc, K, R, S, st, pads, dl = case
+    rng = np.random.default_rng(seed)
+    x = rng.integers(-127, 128, (N, H, W, Cc), dtype=np.int8)
+    w = rng.integers(-127, 128, (K, R, S, Cc), dtype=np.int8)
+    ws = ((1 + np.arange(K) % 7) / (7 * 127)).astype(np.float32)
+    bias = rng.uniform(-1, 1, K).astype(np.float32)
+    in_scale = np.float32(1 / 127)
+    out_scale = np.float32(Cc * R * S / 127 / 4)
+    return x, w, ws, bias, in_scale, out_scale
+
+
+def run_conv(pl, case, x, w, sf, bf, act, act_arg, out, rnd):
+    N, H, W, Cc, K, R, S, st, pads, dl = case
+    ldx = rup(Cc, 16)
+    xd = dev(pad_c(x, ldx))
+    wp = pl.pack_conv_weight(dev(w))
+    y = pl.conv2d(xd, wp, K, R, S, None if sf is None else dev(sf), None if bf is None else dev(bf),
+                  (st, st), pads, (dl, dl), act, act_arg, out, rnd, Cc=Cc)
+    return host(y)
+
+
+CONV_CASES = [
+    # N, H, W, C, K, R, S, stride, (pt,pb,pl,pr), dil
+    (1, 56, 56, 64, 64, 3, 3, 1, (1, 1, 1, 1), 1),      # BASELINE config 1
+    (2, 14, 14, 64, 64, 3, 3, 1, (1, 1, 1, 1), 1),
+    (3, 9, 7, 32, 48, 3, 3, 2, (1, 1, 1, 1), 1),        # tiles straddle images, K tail
+    (1, 28, 28, 128, 256, 1, 1, 1, (0, 0, 0, 0), 1),    # pointwise -> plain GEMM path
+    (2, 28, 28, 256, 128, 1, 1, 2, (0, 0, 0, 0), 1),    # 1x1 stride 2 (ResNet projection)
+    (1, 20, 20, 16, 32, 5, 5, 2, (2, 2, 2, 2), 1),
+    (1, 17, 17, 32, 32, 3, 3, 1, (2, 2, 2, 2), 2),      # dilation 2
+    (1, 12, 15, 96, 80, 3, 3, 1, (0, 1, 1, 0), 1),      # asymmetric pads, C=96 -> BK=128 OOB
+    (1, 14, 14, 256, 512, 3, 3, 1, (1, 1, 1, 1), 1),    # 2 channel blocks, 2 n-tiles
+    (2, 32, 32, 3, 32, 3, 3, 2, (1, 1, 1, 1), 1),       # MobileNet conv0: C=3 (pitch 16)
+    (1, 38, 38, 3, 64, 7, 7, 2, (3, 3, 3, 3), 1),       # ResNet stem shape
+    (1, 8, 8, 72, 72, 1, 1, 1, (0, 0, 0, 0), 1),        # humanseg widths (C,K not /16)
+    (1, 7, 7, 512, 1000, 1, 1, 1, (0, 0, 0, 0), 1),
+]
+
+
+@pytest.mark.parametrize("case", CONV_CASES)
+def test_conv_int32_accumulators_exact(pl, case):
+    x, w, *_ = conv_inputs(case, 11)
+    N, H, W, Cc, K, R, S, st, pads, dl = case
+    want = orc.conv2d(x, w, None, None, (st, st), pads, (dl, dl), 1, out=orc.OUT_INT32)
+    got = run_conv(pl, case, x, w, None, None, pl.ACT_NONE, 0.0, pl.OUT_INT32, pl.ROUND_ARM)
+    assert got.shape == want.shape
+    assert np.array_equal(got, want)
+
+
+@pytest.mark.parametrize("case", CONV_CASES)
+@pytest.mark.parametrize("act", ["relu", "none", "relu6", "leaky"])
+def test_conv_int8_out_exact(pl, case, act):
+    x, w, ws, bias, si, so = conv_inputs(case, 23)
+    N, H, W, Cc, K, R, S, st, pads, dl = case
+    a = {"none": orc.ACT_NONE, "relu": orc.ACT_RELU, "relu6": orc.ACT_RELU6, "leaky": orc.ACT_LEAKY}[act]
+    arg = {"none": 0.0, "relu": 0.0, "relu6": 6.0, "leaky": 0.1}[act]
+    if act == "relu6":
+        so = np.float32(6.0 / 127)
+    sf, bf, argf = orc.fold_scales(ws, K, si, so, orc.OUT_INT8, bias, a, arg)
+    want = orc.conv2d(x, w, sf, bf, (st, st), pads, (dl, dl), 1, a, argf, orc.OUT_INT8)
+    got = run_conv(pl, case, x, w, sf, bf, a, argf, pl.OUT_INT8, pl.ROUND_ARM)
+    assert np.array_equal(got, want)
+    assert want.min() < 0 or act != "none"  # the scale recipe really exercises the range
+    assert len(np.unique(want)) > 8
+
+
+@pytest.mark.parametrize("case", CONV_CASES[:6])
+@pytest.mark.parametrize("rnd", ["arm", "cuda"])
+def test_conv_fp32_out(pl, case, rnd):
+    x, w, ws, bias, si, so = conv_inputs(case, 31)
+    N, H, W, Cc, K, R, S, st, pads, dl = case
+    r = orc.ROUND_ARM if rnd == "arm" else orc.ROUND_CUDA
+    sf, bf, _ = orc.fold_scales(ws, K, si, so, orc.OUT_FP32, bias, orc.ACT_LEAKY, 0.2)
+    want = orc.conv2d(x, w, sf, bf, (st, st), pads, (dl, dl), 1, orc.ACT_LEAKY, 0.2, orc.OUT_FP32, r)
+    got = run_conv(pl, case, x, w, sf, bf, pl.ACT_LEAKY, 0.2, pl.OUT_FP32, r)
+    np.testing.assert_allclose(got, want, rtol=FP32_RTOL, atol=0)
+    assert np.array_equal(got, want)
+
+
+def test_conv_cuda_legacy_rounding_int8(pl):
+    case = CONV_CASES[1]
+    x, w, ws, bias, si, so = conv_inputs(case, 5)
+    N, H, W, Cc, K, R, S, st, pads, dl = case
+    sf, bf, _ = orc.fold_scales(ws, K, si, so, orc.OUT_INT8, bias)
+    want = orc.conv2d(x, w, sf, bf, (st, st), pads, (dl, dl), 1, orc.ACT_RELU, 0, orc.OUT_INT8, orc.ROUND_CUDA)
+    got = run_conv(pl, case, x, w, sf, bf, pl.ACT_RELU, 0.0, pl.OUT_INT8, pl.ROUND_CUDA)
+    assert np.array_equal(got, want)
+
+
+def test_reference_kats_on_gpu(pl):
+    """lite/kernels/cuda/conv_compute_test.cc:232-376 (the reference's own kCUDA int8 vectors)."""
+    kat = json.load(open(os.path.join(HERE, "golden", "kat_cuda_conv_int8.json")))
+    k = kat["kat1"]
+    x = np.full(k["x_shape"], 1, np.int8)
+    w = np.full(k["w_shape"], 1, np.int8)
+    sf, bf, _ = orc.fold_scales(k["weight_scale"], 4, 1.0, 1.0, orc.OUT_FP32)
+    case = (1, 3, 3, 4, 4, 3, 3, 1, (0, 0, 0, 0), 1)
+    got = run_conv(pl, case, x, w, sf, None, pl.ACT_NONE, 0.0, pl.OUT_FP32, pl.ROUND_CUDA)
+    assert got.reshape(-1).tolist() == k["expect"]
+    k = kat["kat2"]
+    x = np.array(k["x"], np.int8).reshape(k["x_shape"])
+    w = np.array(k["w"], np.int8).reshape(k["w_shape"])
+    sf, bf, _ = orc.fold_scales(k["weight_scale"], 4, k["input_scale"], k["output_scale"], orc.OUT_INT8, k["bias"])
+    case = (1, 3, 3, 3, 4, 3, 3, 1, (0, 0, 0, 0), 1)
+    acc = run_conv(pl, case, x, w, None, None, pl.ACT_NONE, 0.0, pl.OUT_INT32, pl.ROUND_CUDA)
+    assert acc.reshape(-1).tolist() == k["acc"]
+    for rnd in (pl.ROUND_CUDA, pl.ROUND_ARM):
+        got = run_conv(pl, case, x, w, sf, bf, pl.ACT_RELU, 0.0, pl.OUT_INT8, rnd)
+        assert got.reshape(-1).tolist() == k["expect"]
+
+
+def test_conv_full_size_slices_match_oracle(pl):
+    """ResNet-50 res2 3x3 at batch 64: images are independent, so the first and last
+    image of the big launch must equal the oracle run on those images alone."""
+    case = (64, 56, 56, 64, 64, 3, 3, 1, (1, 1, 1, 1), 1)
+    x, w, ws, bias, si, so = conv_inputs(case, 77)
+    sf, bf, _ = orc.fold_scales(ws, 64, si, so, orc.OUT_INT8, bias)
+    got = run_conv(pl, case, x, w, sf, bf, pl.ACT_RELU, 0.0, pl.OUT_INT8, pl.ROUND_ARM)
+    for n in (0, 31, 63):
+        want = orc.conv2d(x[n:n + 1], w, sf, bf, (1, 1), (1, 1, 1, 1), act=orc.ACT_RELU)
+        assert np.array_equal(got[n:n + 1], want)
+    # linearity of the accumulator in the filter: conv(x, w1) + conv(x, w2) == conv(x, w1 + w2)
+    rng = np.random.default_rng(3)
+    w1 = rng.integers(-60, 61, w.shape, dtype=np.int8)
+    w2 = rng.integers(-60, 61, w.shape, dtype=np.int8)
+    a1 = run_conv(pl, case, x, w1, None, None, 0, 0.0, pl.OUT_INT32, 0)
+    a2 = run_conv(pl, case, x, w2, None, None, 0, 0.0, pl.OUT_INT32, 0)
+    a12 = run_conv(pl, case, x, (w1 + w2).astype(np.int8), None, None, 0, 0.0, pl.OUT_INT32, 0)
+    assert np.array_equal(a1 + a2, a12)
+
+
+def test_conv_writes_into_channel_slice(pl):
+    """ldy > K: the conv writes a channel slice of a wider buffer (free concat)."""
+    case = (1, 10, 10, 32, 32, 3, 3, 1, (1, 1, 1, 1), 1)
+    x, w, ws, bias, si, so = conv_inputs(case, 9)
+    sf, bf, _ = orc.fold_scales(ws, 32, si, so, orc.OUT_INT8, bias)
+    want = orc.conv2d(x, w, sf, bf, (1, 1), (1, 1, 1, 1))
+    buf = torch.full((1, 10, 10, 64), 99, dtype=torch.int8, device=DEV)
+    wp = pl.pack_conv_weight(dev(w))
+    view = buf[..., 32:]  # pointer offset 32, pitch 64
+    d = pl.conv_desc(1, 10, 10, 32, 32, 3, 3, (1, 1), (1, 1, 1, 1), (1, 1), 1, 32, 64)
+    sfd, bfd, xd = dev(sf), dev(bf), dev(x)
+    e = pl.make_epilogue(sfd, bfd)
+    import ctypes as C
+    st = C.c_void_p(torch.cuda.current_stream().cuda_stream)
+    # NULL arguments are rejected, not dereferenced
+    assert pl.lib().pl_conv2d_i8_nhwc(None, None, None, None, None, st) != 0
+    rc = pl.lib().pl_conv2d_i8_nhwc(C.c_void_p(xd.data_ptr()), C.c_void_p(wp.data_ptr()),
+                                    C.c_void_p(view.data_ptr()), C.byref(d), C.byref(e), st)
+    assert rc == 0
+    out = host(buf)
+    assert np.array_equal(out[..., 32:], want)
+    assert np.all(out[..., :32] == 99)
+
+
+def test_conv_error_codes(pl):
+    x = torch.zeros((1, 8, 8, 24), dtype=torch.int8, device=DEV)  # pitch 24: not /16
+    wp = torch.zeros(4096, dtype=torch.int8, device=DEV)
+    s = torch.ones(16, device=DEV)
+    with pytest.raises(pl.PlError):
+        pl.conv2d(x, wp, 16, 3, 3, s, None, (1, 1), (1, 1, 1, 1))
+
+
+GEMM_CASES = [(128, 64, 64), (256, 256, 128), (300, 1000, 1024), (1, 1000, 1024), (64, 1000, 2048),
+              (1024, 512, 2304), (130, 48, 96), (17, 24, 48), (2048, 2048, 512)]
+
+
+@pytest.mark.parametrize("mnk", GEMM_CASES)
+def test_gemm_parity(pl, mnk):
+    M, N, K = mnk
+    rng = np.random.default_rng(M + 3 * N + 7 * K)
+    A = rng.integers(-127, 128, (M, K), dtype=np.int8)
+    Bt = rng.integers(-127, 128, (N, K), dtype=np.int8)
+    s = ((rng.random(N, dtype=np.float32) + 0.5) / 127 / 127 * (64.0 / K) * 8).astype(np.float32)
+    b = rng.standard_normal(N).astype(np.float32)
+    Ad, Bd, sd, bd = dev(A), dev(Bt), dev(s), dev(b)
+    acc = host(pl.gemm(Ad, Bd, None, None, out=pl.OUT_INT32))
+    assert np.array_equal(acc, A.astype(np.int32) @ Bt.astype(np.int32).T)
+    want = orc.gemm(A, Bt, s, b, b_is_nk=True, act=orc.ACT_RELU, out=orc.OUT_INT8)
+    got = host(pl.gemm(Ad, Bd, sd, bd, act=pl.ACT_RELU, out=pl.OUT_INT8))
+    assert np.array_equal(got, want)
+    want = orc.gemm(A, Bt, s, b, b_is_nk=True, out=orc.OUT_FP32)
+    got = host(pl.gemm(Ad, Bd, sd, bd, out=pl.OUT_FP32))
+    np.testing.assert_allclose(got, want, rtol=FP32_RTOL, atol=0)
+    assert np.array_equal(got, want)
+
+
+def test_gemm_fc_weight_layout(pl):
+    """fc keeps W as [K,N] (lite/kernels/cuda/fc_compute.cu:199-353); it is transposed
+    once (PrepareForRun) with pl_transpose_i8 and then used K-major."""
+    rng = np.random.default_rng(2)
+    M, N, K = 32, 1000, 1024
+    A = rng.integers(-127, 128, (M, K), dtype=np.int8)
+    Wkn = rng.integers(-127, 128, (K, N), dtype=np.int8)
+    s = np.full(N, 1e-4, np.float32)
+    Bt = pl.transpose_i8(dev(Wkn))
+    assert np.array_equal(host(Bt), Wkn.T)
+    want = orc.gemm(A, Wkn, s, None, b_is_nk=False, out=orc.OUT_INT8)
+    got = host(pl.gemm(dev(A), Bt, dev(s), None, out=pl.OUT_INT8))
+    assert np.array_equal(got, want)
+
+
+DW_CASES = [
+    # N, H, W, C, R, stride, pad, dil
+    (2, 28, 28, 64, 3, 1, 1, 1),
+    (2, 28, 28, 64, 3, 2, 1, 1),
+    (1, 112, 112, 32, 3, 1, 1, 1),   # MobileNetV1 dw1
+    (1, 15, 13, 128, 3, 2, 1, 1),    # odd sizes
+    (1, 14, 14, 512, 3, 1, 1, 1),
+    (1, 12, 12, 72, 3, 1, 1, 1),     # humanseg widths
+    (1, 24, 24, 36, 3, 2, 1, 1),
+    (1, 9, 9, 9, 3, 1, 1, 1),        # C=9 in a pitch-16 buffer
+    (1, 16, 16, 32, 5, 1, 2, 1),     # 5x5 (generic path)
+    (1, 16, 16, 32, 5, 2, 2, 1),
+    (1, 16, 16, 16, 3, 1, 2, 2),     # dilation (generic path)
+    (1, 7, 7, 1024, 3, 1, 1, 1),
+]
+
+
+@pytest.mark.parametrize("case", DW_CASES)
+@pytest.mark.parametrize("out", ["int8", "fp32", "int32"])
+def test_depthwise_parity(pl, case, out):
+    N, H, W, Cc, R, st, pd, dl = case
+    rng = np.random.default_rng(hash(case) & 0xFFFF)
+    x = rng.integers(-127, 128, (N, H, W, Cc), dtype=np.int8)
+    w = rng.integers(-127, 128, (Cc, R, R), dtype=np.int8)
+    ws = ((1 + np.arange(Cc) % 5) / (5 * 127)).astype(np.float32)
+    bias = rng.uniform(-1, 1, Cc).astype(np.float32)
+    o = {"int8": orc.OUT_INT8, "fp32": orc.OUT_FP32, "int32": orc.OUT_INT32}[out]
+    sf, bf, _ = orc.fold_scales(ws, Cc, 1 / 127, R * R / 127 / 2, o if o != orc.OUT_INT32 else orc.OUT_FP32, bias)
+    want = orc.conv2d(x, w.reshape(Cc, R, R, 1), sf, bf, (st, st), (pd, pd, pd, pd), (dl, dl), Cc,
+                      orc.ACT_RELU, 0.0, o)
+    ld = rup(Cc, 16)
+    got = host(pl.dwconv2d(dev(pad_c(x, ld)), dev(w), dev(sf), dev(bf), R, R, (st, st), (pd, pd, pd, pd),
+                           (dl, dl), pl.ACT_RELU, 0.0, o, Cc=Cc))
+    assert np.array_equal(got[..., :Cc], want)
+    assert not got[..., Cc:].any()
+
+
+@pytest.mark.parametrize("n", [0, 1, 15, 16, 17, 4096, 100003])
+@pytest.mark.parametrize("rnd", ["arm", "cuda"])
+def test_calib_quantize_dequantize(pl, n, rnd):
+    rng = np.random.default_rng(n + 1)
+    x = (rng.standard_normal(n) * 3).astype(np.float32)
+    if n >= 16:
+        x[:8] = np.array([0.5, 1.5, 2.5, -0.5, -2.5, 0.49999997, 1000.0, -1000.0], np.float32) * np.float32(0.0371)
+    r = orc.ROUND_ARM if rnd == "arm" else orc.ROUND_CUDA
+    scale = np.float32(0.0371)
+    got = host(pl.quantize(dev(x), scale, r)) if n else np.zeros(0, np.int8)
+    assert np.array_equal(got, orc.quantize(x, scale, r))
+    q = rng.integers(-128, 128, n, dtype=np.int8)
+    got = host(pl.dequantize(dev(q), scale)) if n else np.zeros(0, np.float32)
+    assert np.array_equal(got, orc.dequantize(q, scale))
+
+
+def test_rounding_every_tie_and_edge(pl):
+    """Every k+0.5 tie, the values next to them, and the clamp edges, both conventions."""
+    base = np.arange(-130, 131, dtype=np.float32)
+    vals = np.concatenate([base, base + np.float32(0.5), np.nextafter(base + np.float32(0.5), np.float32(1e9)),
+                           np.nextafter(base + np.float32(0.5), np.float32(-1e9)),
+                           np.array([1e9, -1e9, 127.49999, -127.5, 126.5, -126.5], np.float32)]).astype(np.float32)
+    for r in (orc.ROUND_ARM, orc.ROUND_CUDA):
+        got = host(pl.quantize(dev(vals), 1.0, r))
+        assert np.array_equal(got, orc.quantize(vals, 1.0, r))
+
+
+@pytest.mark.parametrize("shape", [(2, 3, 17, 19), (1, 64, 56, 56), (3, 72, 12, 12), (1, 1000, 1, 1)])
+def test_layout_transforms(pl, shape):
+    rng = np.random.default_rng(sum(shape))
+    x8 = rng.integers(-128, 128, shape, dtype=np.int8)
+    xf = rng.standard_normal(shape).astype(np.float32)
+    for x in (x8, xf):
+        y = host(pl.nchw_to_nhwc(dev(x)))
+        assert np.array_equal(y, orc.nchw_to_nhwc(x))
+        assert np.array_equal(host(pl.nhwc_to_nchw(dev(y))), x)
+    ld = rup(shape[1], 16)
+    y = host(pl.nchw_to_nhwc(dev(x8), ld))
+    assert np.array_equal(y[..., : shape[1]], orc.nchw_to_nhwc(x8)) and not y[..., shape[1]:].any()
+    assert np.array_equal(host(pl.nhwc_to_nchw(dev(y), shape[1])), x8)
+    # fused calib + layout + channel pad (entry of the int8 region)
+    scale = np.float32(0.02)
+    if 64 * ld <= 48 * 1024:
+        y = host(pl.quantize_nchw_to_nhwc(dev(xf), scale, ld))
+        want = orc.nchw_to_nhwc(orc.quantize(xf, scale))
+        assert np.array_equal(y[..., : shape[1]], want) and not y[..., shape[1]:].any()
+
+
+POOL_CASES = [
+    # N,H,W,C, k, s, pad, type, exclusive, ceil, global
+    (2, 112, 112, 64, 3, 2, 1, "max", True, False, False),   # ResNet-50 maxpool
+    (4, 7, 7, 2048, 7, 1, 0, "avg", True, False, True),      # global average
+    (2, 7, 7, 1024, 7, 1, 0, "avg", True, False, True),
+    (1, 96, 96, 36, 3, 2, 1, "max", True, False, False),     # humanseg
+    (1, 13, 13, 24, 3, 2, 1, "avg", True, True, False),
+    (1, 13, 13, 24, 3, 2, 1, "avg", False, False, False),
+    (1, 10, 10, 9, 2, 2, 0, "max", True, False, False),
+]
+
+
+@pytest.mark.parametrize("case", POOL_CASES)
+@pytest.mark.parametrize("out", ["int8", "fp32"])
+def test_pool_parity(pl, case, out):
+    N, H, W, Cc, k, s, pd, typ, excl, ceil, glob = case
+    rng = np.random.default_rng(hash(case) & 0xFFFF)
+    x = rng.integers(-127, 128, (N, H, W, Cc), dtype=np.int8)
+    t = orc.POOL_MAX if typ == "max" else orc.POOL_AVG
+    o = orc.OUT_INT8 if out == "int8" else orc.OUT_FP32
+    resc = 0.7 if out == "int8" else 0.013
+    want = orc.pool2d(x, (k, k), (s, s), (pd, pd, pd, pd), t, excl, resc, o, ceil_mode=ceil, global_pooling=glob)
+    ld = rup(Cc, 16)
+    got = host(pl.pool2d(dev(pad_c(x, ld)), (k, k), (s, s), (pd, pd, pd, pd), t, excl, resc, o,
+                         ceil_mode=ceil, global_pooling=glob, Cc=Cc))
+    assert np.array_equal(got[..., :Cc], want)
+
+
+@pytest.mark.parametrize("n", [1, 16, 1000, 256 * 56 * 56 * 4 + 5])
+def test_residual_add_parity(pl, n):
+    rng = np.random.default_rng(n)
+    a = rng.integers(-127, 128, n, dtype=np.int8)
+    b = rng.integers(-127, 128, n, dtype=np.int8)
+    for act in (orc.ACT_RELU, orc.ACT_NONE):
+        want = orc.add(a, b, 0.61, 0.47, act)
+        assert np.array_equal(host(pl.add(dev(a), dev(b), 0.61, 0.47, act)), want)
+    want = orc.add(a, b, 0.011, 0.02, orc.ACT_RELU, out=orc.OUT_FP32)
+    assert np.array_equal(host(pl.add(dev(a), dev(b), 0.011, 0.02, pl.ACT_RELU, out=pl.OUT_FP32)), want)
+
+
+def test_launch_counter_and_peak_probe(pl):
+    n0 = pl.launch_count()
+    out = pl.i8_mma_peak(4, 8, 256)
+    torch.cuda.synchronize()
+    assert pl.launch_count() == n0 + 1
+    # operands are all ones: every accumulator of the last-written stage is a multiple of 128
+    assert int(out[0].item()) % 128 == 0 and int(out[0].item()) > 0
