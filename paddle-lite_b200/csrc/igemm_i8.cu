@@ -407,11 +407,12 @@ int launch_igemm(const CUtensorMap& ta, const CUtensorMap& tb, IgemmParams& p, p
   if (stages < 2) stages = 2;
   p.stages = stages;
   const size_t smem = (size_t)stages * (p.a_stage_bytes + p.b_stage_bytes) + 1024;
-  static size_t configured = 0;
-  if (smem > configured) {
+  static bool configured = false;  // one process drives one GPU
+  if (!configured) {
+    // 227 KB is the per-CTA limit for static + dynamic shared memory together
     PL_CUDA_OK(cudaFuncSetAttribute(igemm_i8_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                    (int)(227 * 1024)));
-    configured = 227 * 1024;
+                                    (int)(220 * 1024)));
+    configured = true;
   }
   const int tiles = p.m_tiles * p.n_tiles;
   const int grid = tiles < driver().sm_count ? tiles : driver().sm_count;
