@@ -145,6 +145,46 @@ int orc_epilogue(const int32_t* acc, int64_t M, int n_out, const float* scale,
 }
 
 /*
+ * Epilogue with a fused int8 residual (ConvParam::residualData,
+ * lite/operators/op_params.h:446-502; the reference fuses conv + elementwise_add
+ * only for fp32, lite/core/mir/fusion/conv_elementwise_fuser.cc).  PARITY
+ * UNPINNED: defined here by analogy with orc_add_i8:
+ *   v = fmaf((float)acc, scale, bias); v = fmaf((float)res, res_scale, v); act; round
+ */
+int orc_epilogue_res(const int32_t* acc, int64_t M, int n_out, const float* scale,
+                     const float* bias, const int8_t* res, int ld_res,
+                     float res_scale, int act, float act_arg, int out_dtype,
+                     int round_mode, void* y) {
+  const int vec4 = (n_out % 4 == 0);
+#pragma omp parallel for schedule(static)
+  for (int64_t m = 0; m < M; ++m) {
+    for (int c = 0; c < n_out; ++c) {
+      float v = fmaf((float)acc[m * n_out + c], scale[c], bias ? bias[c] : 0.f);
+      v = fmaf((float)res[m * ld_res + c], res_scale, v);
+      if (round_mode == ORC_ROUND_CUDA_LEGACY) {
+        if (act == ORC_ACT_RELU || act == ORC_ACT_LEAKY) {
+          float alpha = (act == ORC_ACT_RELU) ? 0.f : act_arg;
+          v = vec4 ? fmaxf(v * alpha, v) : (v > 0.f ? v : v * alpha);
+        } else if (act == ORC_ACT_RELU6) {
+          v = v > 0.f ? (v > act_arg ? act_arg : v) : 0.f;
+        }
+      } else if (act == ORC_ACT_RELU) {
+        v = v > 0.f ? v : 0.f;
+      } else if (act == ORC_ACT_RELU6) {
+        v = v > 0.f ? (v > act_arg ? act_arg : v) : 0.f;
+      } else if (act == ORC_ACT_LEAKY) {
+        v = v > 0.f ? v : v * act_arg;
+      }
+      if (out_dtype == ORC_OUT_FP32)
+        ((float*)y)[m * n_out + c] = v;
+      else
+        ((int8_t*)y)[m * n_out + c] = orc_round_sat_i8(v, round_mode);
+    }
+  }
+  return 0;
+}
+
+/*
  * Exact int32 convolution, NHWC activations, OHWI filters, groups, dilation,
  * top/left padding (bottom/right only enter through P,Q).  Same loop nest and
  * index arithmetic as conv_basic<int8_t,int> (naive_math_impl.h:350-453) with

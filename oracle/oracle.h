@@ -74,6 +74,11 @@ int orc_epilogue(const int32_t* acc, int64_t M, int n_out, const float* scale,
                  const float* bias, int act, float act_arg, int out_dtype,
                  int round_mode, void* y);
 
+int orc_epilogue_res(const int32_t* acc, int64_t M, int n_out, const float* scale,
+                     const float* bias, const int8_t* res, int ld_res,
+                     float res_scale, int act, float act_arg, int out_dtype,
+                     int round_mode, void* y);
+
 /* ---- whole ops (contraction + folded epilogue) ----------------------------- */
 int orc_conv2d_i8_nhwc(const int8_t* x, const int8_t* w, const float* bias_f,
                        const float* scale_f, void* y, int N, int H, int W,

@@ -7,10 +7,15 @@
 // an fp32 temporary + a second elementwise kernel, activation.cu:91-446) with
 // ONE kernel and no temporary.  Semantics of the epilogue: common.cuh.
 //
-// Warp roles (192 threads, persistent over output tiles):
+// Warp roles (320 threads, persistent over output tiles):
 //   warp 0      TMA producer (one lane)
 //   warp 1      TMEM allocator + MMA issuer (one lane)
-//   warps 2..5  epilogue; warp w reads TMEM lanes [32*(w%4), 32*(w%4)+32)
+//   warps 2..9  epilogue; warp w reads TMEM lanes [32*(w%4), +32) and the column
+//               half (w-2)/4 of the tile, 32 columns per tcgen05.ld
+// The epilogue runs once per output byte and is ALU-issue bound, so the hot
+// variants are specialised at compile time (EPI_*): packed FFMA2/FADD2, one
+// VIMNMX.RELU for relu+clamp on the float bit pattern, PRMT packing, scale/bias
+// staged in shared memory once per tile.
 #include <cuda.h>
 #include <cudaTypedefs.h>
 
@@ -18,9 +23,12 @@
 
 namespace pl {
 
-static constexpr int kBM = 128;       // rows of D per tile (TMEM lanes)
-static constexpr int kThreads = 192;  // 6 warps
+static constexpr int kBM = 128;            // rows of D per tile (TMEM lanes)
+static constexpr int kEpiWarps = 8;
+static constexpr int kThreads = 64 + 32 * kEpiWarps;  // 10 warps
 static constexpr int kMaxStages = 8;
+
+enum { EPI_GENERIC = 0, EPI_I8_RELU = 1, EPI_I8_SIGNED = 2, EPI_I8_RELU_RES = 3 };
 
 struct IgemmParams {
   int M, Nout;
@@ -30,20 +38,155 @@ struct IgemmParams {
   int mode;  // 0: A is a [M, K] matrix (tiled TMA); 1: A is NHWC, im2col TMA
   int Q, PQ, S;
   int sh, sw, pt, pl_, dh, dw;
-  uint32_t a_stage_bytes, b_stage_bytes, tx_bytes, tmem_cols;
+  uint32_t a_stage_bytes, b_stage_bytes, tx_bytes, tmem_cols, acc_stride;
   void* y;
   int ldy;
-  int vec_ok;  // 16-byte vector stores allowed
+  int vec_ok;      // 16-byte vector stores allowed
+  int res_vec_ok;  // 16-byte vector loads of the residual allowed
+  uint32_t hi_bits;  // float bits of the upper clamp for the relu fast paths
   EpiParams epi;
 };
 
+// ---- packed fp32x2 helpers (FFMA2 / FADD2 on sm_100) ---------------------------
+__device__ __forceinline__ uint64_t pk2(float a, float b) {
+  uint64_t r;
+  asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(a), "f"(b));
+  return r;
+}
+__device__ __forceinline__ void upk2(uint64_t v, float& a, float& b) {
+  asm("mov.b64 {%0, %1}, %2;" : "=f"(a), "=f"(b) : "l"(v));
+}
+__device__ __forceinline__ uint64_t ffma2(uint64_t a, uint64_t b, uint64_t c) {
+  uint64_t d;
+  asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(b), "l"(c));
+  return d;
+}
+__device__ __forceinline__ uint64_t fadd2_rz(uint64_t a, uint64_t b) {
+  uint64_t d;
+  asm("add.rz.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
+  return d;
+}
+__device__ __forceinline__ uint64_t fadd2_rm(uint64_t a, uint64_t b) {
+  uint64_t d;
+  asm("add.rm.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
+  return d;
+}
+__device__ __forceinline__ uint64_t fadd2_rn(uint64_t a, uint64_t b) {
+  uint64_t d;
+  asm("add.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
+  return d;
+}
+__device__ __forceinline__ uint32_t prmt_(uint32_t a, uint32_t b, uint32_t sel) {
+  uint32_t r;
+  asm("prmt.b32 %0, %1, %2, %3;" : "=r"(r) : "r"(a), "r"(b), "r"(sel));
+  return r;
+}
+
+// 4 accumulators -> 4 packed int8, ARM rounding, activation in {relu, relu6}:
+// clamp(v, 0, hi) is ONE integer min-with-relu on the float bit pattern (positive
+// floats order like their bits, negative floats are negative ints), then
+// round-half-away of a non-negative value = floor(RZ(v + 0.5)) read from the
+// mantissa of RD(t + 2^23).  Bit-exact with common.cuh:round_sat_i8.
+template <bool RES>
+__device__ __forceinline__ uint32_t quad_i8_relu(const uint32_t* acc, float4 s, float4 b,
+                                                 uint32_t hi_bits, uint32_t res_word, float res_scale) {
+  uint64_t v01 = ffma2(pk2(__int2float_rn((int)acc[0]), __int2float_rn((int)acc[1])), pk2(s.x, s.y), pk2(b.x, b.y));
+  uint64_t v23 = ffma2(pk2(__int2float_rn((int)acc[2]), __int2float_rn((int)acc[3])), pk2(s.z, s.w), pk2(b.z, b.w));
+  if (RES) {
+    // int8 -> float through the mantissa: 2^23 + (r ^ 0x80) - (2^23 + 128), exact
+    const uint32_t rx = res_word ^ 0x80808080u;
+    const uint32_t magic = 0x4B000000u;
+    const uint64_t off = pk2(-8388736.f, -8388736.f), rs = pk2(res_scale, res_scale);
+    const uint64_t r01 = fadd2_rn(pk2(__uint_as_float(prmt_(rx, magic, 0x7650)), __uint_as_float(prmt_(rx, magic, 0x7651))), off);
+    const uint64_t r23 = fadd2_rn(pk2(__uint_as_float(prmt_(rx, magic, 0x7652)), __uint_as_float(prmt_(rx, magic, 0x7653))), off);
+    v01 = ffma2(r01, rs, v01);
+    v23 = ffma2(r23, rs, v23);
+  }
+  float v0, v1, v2, v3;
+  upk2(v01, v0, v1);
+  upk2(v23, v2, v3);
+  const int c0 = __vimin_s32_relu(__float_as_int(v0), (int)hi_bits);
+  const int c1 = __vimin_s32_relu(__float_as_int(v1), (int)hi_bits);
+  const int c2 = __vimin_s32_relu(__float_as_int(v2), (int)hi_bits);
+  const int c3 = __vimin_s32_relu(__float_as_int(v3), (int)hi_bits);
+  const uint64_t half = pk2(0.5f, 0.5f), big = pk2(8388608.f, 8388608.f);
+  const uint64_t u01 = fadd2_rm(fadd2_rz(pk2(__int_as_float(c0), __int_as_float(c1)), half), big);
+  const uint64_t u23 = fadd2_rm(fadd2_rz(pk2(__int_as_float(c2), __int_as_float(c3)), half), big);
+  const uint32_t p01 = prmt_((uint32_t)u01, (uint32_t)(u01 >> 32), 0x0040);
+  const uint32_t p23 = prmt_((uint32_t)u23, (uint32_t)(u23 >> 32), 0x0040);
+  return prmt_(p01, p23, 0x5410);
+}
+
+// 4 accumulators -> 4 packed int8, ARM rounding, no activation (signed result)
+__device__ __forceinline__ uint32_t quad_i8_signed(const uint32_t* acc, float4 s, float4 b) {
+  const uint64_t v01 = ffma2(pk2(__int2float_rn((int)acc[0]), __int2float_rn((int)acc[1])), pk2(s.x, s.y), pk2(b.x, b.y));
+  const uint64_t v23 = ffma2(pk2(__int2float_rn((int)acc[2]), __int2float_rn((int)acc[3])), pk2(s.z, s.w), pk2(b.z, b.w));
+  float v[4];
+  upk2(v01, v[0], v[1]);
+  upk2(v23, v[2], v[3]);
+  const uint64_t half = pk2(0.5f, 0.5f), big = pk2(8388608.f, 8388608.f);
+  const uint64_t u01 = fadd2_rm(fadd2_rz(pk2(fminf(fabsf(v[0]), 127.f), fminf(fabsf(v[1]), 127.f)), half), big);
+  const uint64_t u23 = fadd2_rm(fadd2_rz(pk2(fminf(fabsf(v[2]), 127.f), fminf(fabsf(v[3]), 127.f)), half), big);
+  const uint32_t m[4] = {(uint32_t)u01, (uint32_t)(u01 >> 32), (uint32_t)u23, (uint32_t)(u23 >> 32)};
+  uint32_t q[4];
+#pragma unroll
+  for (int j = 0; j < 4; ++j) {
+    const int sg = __float_as_int(v[j]) >> 31;               // 0 or -1
+    q[j] = (uint32_t)((int)((m[j] & 0xffu) ^ (uint32_t)sg) - sg);  // conditional negate
+  }
+  return prmt_(prmt_(q[0], q[1], 0x0040), prmt_(q[2], q[3], 0x0040), 0x5410);
+}
+
+// generic element (any dtype / act / rounding / residual)
+__device__ __forceinline__ float generic_value(int acc, float s, float b, const EpiParams& e,
+                                               const int8_t* res_row, int n, bool n_ok) {
+  float t = __fmaf_rn(__int2float_rn(acc), s, b);
+  if (e.residual && n_ok) t = __fmaf_rn((float)res_row[n], e.res_scale, t);
+  return (e.round_mode == PL_ROUND_CUDA_LEGACY) ? apply_act_legacy(t, e.act, e.act_arg, e.vec4)
+                                                : apply_act(t, e.act, e.act_arg);
+}
+
 // --------------------------------------------------------------------------
-// epilogue for one 16-column chunk held in registers
+// epilogue for one 16-column group held in registers (acc[0..15])
 // --------------------------------------------------------------------------
-__device__ __forceinline__ void store_chunk16(const IgemmParams& p, const uint32_t (&acc)[16],
-                                              long long row, int n_base) {
+template <int EPI>
+__device__ __forceinline__ void store_group16(const IgemmParams& p, const uint32_t* acc, long long row,
+                                              int n_base, const float* s_scale, const float* s_bias) {
   const EpiParams& e = p.epi;
   const bool full = (n_base + 16 <= p.Nout);
+  if (EPI != EPI_GENERIC) {
+    if (full && p.vec_ok) {
+      uint32_t w[4];
+      uint4 rw = make_uint4(0, 0, 0, 0);
+      if (EPI == EPI_I8_RELU_RES) {
+        const int8_t* rp = e.residual + row * e.ld_res + n_base;
+        if (p.res_vec_ok) {
+          rw = __ldg(reinterpret_cast<const uint4*>(rp));
+        } else {
+          uint32_t t[4] = {0, 0, 0, 0};
+#pragma unroll
+          for (int j = 0; j < 16; ++j) t[j >> 2] |= (uint32_t)(uint8_t)rp[j] << (8 * (j & 3));
+          rw = make_uint4(t[0], t[1], t[2], t[3]);
+        }
+      }
+      const uint32_t rws[4] = {rw.x, rw.y, rw.z, rw.w};
+#pragma unroll
+      for (int g = 0; g < 4; ++g) {
+        const float4 s = *reinterpret_cast<const float4*>(s_scale + 4 * g);
+        const float4 b = *reinterpret_cast<const float4*>(s_bias + 4 * g);
+        if (EPI == EPI_I8_RELU)
+          w[g] = quad_i8_relu<false>(acc + 4 * g, s, b, p.hi_bits, 0u, 0.f);
+        else if (EPI == EPI_I8_RELU_RES)
+          w[g] = quad_i8_relu<true>(acc + 4 * g, s, b, p.hi_bits, rws[g], e.res_scale);
+        else
+          w[g] = quad_i8_signed(acc + 4 * g, s, b);
+      }
+      int8_t* out = reinterpret_cast<int8_t*>(p.y) + row * p.ldy + n_base;
+      *reinterpret_cast<uint4*>(out) = make_uint4(w[0], w[1], w[2], w[3]);
+      return;
+    }
+    // ragged edge of a fast-path launch: fall through to the generic element code
+  }
   if (e.out_dtype == PL_OUT_INT32) {
     int* out = reinterpret_cast<int*>(p.y) + row * p.ldy + n_base;
     if (full && p.vec_ok) {
@@ -58,21 +201,11 @@ __device__ __forceinline__ void store_chunk16(const IgemmParams& p, const uint32
     }
     return;
   }
+  const int8_t* res_row = e.residual ? e.residual + row * e.ld_res : nullptr;
   float v[16];
 #pragma unroll
-  for (int j = 0; j < 16; ++j) {
-    const int n = n_base + j;
-    float s = 0.f, b = 0.f;
-    if (n < p.Nout) {
-      s = __ldg(e.scale + n);
-      if (e.bias) b = __ldg(e.bias + n);
-    }
-    float t = __fmaf_rn(__int2float_rn((int)acc[j]), s, b);
-    if (e.residual && n < p.Nout)
-      t = __fmaf_rn((float)e.residual[row * e.ld_res + n], e.res_scale, t);
-    v[j] = (e.round_mode == PL_ROUND_CUDA_LEGACY) ? apply_act_legacy(t, e.act, e.act_arg, e.vec4)
-                                                  : apply_act(t, e.act, e.act_arg);
-  }
+  for (int j = 0; j < 16; ++j)
+    v[j] = generic_value((int)acc[j], s_scale[j], s_bias[j], e, res_row, n_base + j, n_base + j < p.Nout);
   if (e.out_dtype == PL_OUT_FP32) {
     float* out = reinterpret_cast<float*>(p.y) + row * p.ldy + n_base;
     if (full && p.vec_ok) {
@@ -104,12 +237,15 @@ __device__ __forceinline__ void store_chunk16(const IgemmParams& p, const uint32
 // --------------------------------------------------------------------------
 // the kernel
 // --------------------------------------------------------------------------
+template <int EPI>
 __global__ void __launch_bounds__(kThreads, 1)
 igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
                 const __grid_constant__ CUtensorMap tmap_b, const IgemmParams p) {
   extern __shared__ uint8_t smem_raw[];
   __shared__ __align__(8) uint64_t bars[2 * kMaxStages + 4];
   __shared__ uint32_t tmem_base_slot;
+  __shared__ __align__(16) float s_scale[2][256];
+  __shared__ __align__(16) float s_bias[2][256];
 
   const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
   const uint32_t smem_a = smem_base;
@@ -132,7 +268,7 @@ igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
     }
     for (int s = 0; s < 2; ++s) {
       mbar_init(bar_tfull + 8 * s, 1);
-      mbar_init(bar_tempty + 8 * s, 128);
+      mbar_init(bar_tempty + 8 * s, 32 * kEpiWarps);
     }
     fence_barrier_init();
   }
@@ -194,7 +330,7 @@ igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
       for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
         mbar_wait(bar_tempty + 8 * as, aphase ^ 1);
         tc_fence_after();
-        const uint32_t d_tmem = tmem_base + (uint32_t)(as * p.BN);
+        const uint32_t d_tmem = tmem_base + (uint32_t)as * p.acc_stride;
         for (int kb = 0; kb < p.num_kb; ++kb) {
           mbar_wait(bar_full + 8 * stage, phase);
           tc_fence_after();
@@ -211,22 +347,39 @@ igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
       }
     }
   } else {
-    // ===================== epilogue (warps 2..5) =====================
+    // ===================== epilogue (warps 2..9) =====================
     const int quarter = warp & 3;
+    const int half = (warp - 2) >> 2;
+    const int etid = threadIdx.x - 64;
     int as = 0;
     uint32_t aphase = 0;
     for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
       const int tn = tile % p.n_tiles, tm = tile / p.n_tiles;
       const long long row = (long long)tm * kBM + quarter * 32 + lane;
       const int n0 = tn * p.BN;
+      // stage this tile's scale / bias (buffer `as` was last read two tiles ago)
+      if (etid < p.BN) {
+        const int n = n0 + etid;
+        const bool ok = n < p.Nout && p.epi.scale != nullptr;
+        s_scale[as][etid] = ok ? __ldg(p.epi.scale + n) : 0.f;
+        s_bias[as][etid] = (ok && p.epi.bias) ? __ldg(p.epi.bias + n) : 0.f;
+      }
+      asm volatile("bar.sync 1, %0;" ::"n"(32 * kEpiWarps) : "memory");
       mbar_wait(bar_tfull + 8 * as, aphase);
       tc_fence_after();
-      const uint32_t t_addr = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(as * p.BN);
-      for (int c0 = 0; c0 < p.BN; c0 += 16) {
-        uint32_t acc[16];
-        tmem_ld_32x32b_x16(t_addr + (uint32_t)c0, acc);
+      const uint32_t t_addr = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)as * p.acc_stride;
+      for (int c0 = half * 32; c0 < p.BN; c0 += 64) {
+        uint32_t acc[32];
+        tmem_ld_32x32b_x32(t_addr + (uint32_t)c0, acc);
         tmem_ld_wait();
-        if (row < p.M && n0 + c0 < p.Nout) store_chunk16(p, acc, row, n0 + c0);
+        if (row < p.M) {
+#pragma unroll
+          for (int g = 0; g < 2; ++g) {
+            const int c = c0 + 16 * g;
+            if (c < p.BN && n0 + c < p.Nout)
+              store_group16<EPI>(p, acc + 16 * g, row, n0 + c, &s_scale[as][c], &s_bias[as][c]);
+          }
+        }
       }
       tc_fence_before();
       mbar_arrive(bar_tempty + 8 * as);
@@ -241,7 +394,6 @@ igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
     tmem_dealloc(tmem_base, p.tmem_cols);
   }
 }
-
 
 // --------------------------------------------------------------------------
 // tensor-pipe micro-benchmark: back-to-back MMAs on resident smem operands
@@ -399,6 +551,21 @@ int pick_bn(int Nout, int m_tiles, int sms) {
   return bn;
 }
 
+template <int EPI>
+int launch_one(const CUtensorMap& ta, const CUtensorMap& tb, const IgemmParams& p, int grid, size_t smem,
+               pl_stream_t stream) {
+  static bool configured = false;  // one process drives one GPU
+  if (!configured) {
+    // 227 KB is the per-CTA limit for static + dynamic shared memory together
+    PL_CUDA_OK(cudaFuncSetAttribute(igemm_i8_kernel<EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                    (int)(216 * 1024)));
+    configured = true;
+  }
+  igemm_i8_kernel<EPI><<<grid, kThreads, smem, (cudaStream_t)stream>>>(ta, tb, p);
+  ++g_launches;
+  return launch_status();
+}
+
 int launch_igemm(const CUtensorMap& ta, const CUtensorMap& tb, IgemmParams& p, pl_stream_t stream) {
   const int smem_budget = 200 * 1024;
   int stages = smem_budget / (int)(p.a_stage_bytes + p.b_stage_bytes);
@@ -407,18 +574,31 @@ int launch_igemm(const CUtensorMap& ta, const CUtensorMap& tb, IgemmParams& p, p
   if (stages < 2) stages = 2;
   p.stages = stages;
   const size_t smem = (size_t)stages * (p.a_stage_bytes + p.b_stage_bytes) + 1024;
-  static bool configured = false;  // one process drives one GPU
-  if (!configured) {
-    // 227 KB is the per-CTA limit for static + dynamic shared memory together
-    PL_CUDA_OK(cudaFuncSetAttribute(igemm_i8_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                    (int)(220 * 1024)));
-    configured = true;
-  }
   const int tiles = p.m_tiles * p.n_tiles;
   const int grid = tiles < driver().sm_count ? tiles : driver().sm_count;
-  igemm_i8_kernel<<<grid, kThreads, smem, (cudaStream_t)stream>>>(ta, tb, p);
-  ++g_launches;
-  return launch_status();
+  // epilogue specialisation (ragged edges inside a fast-path launch use the generic code)
+  const EpiParams& e = p.epi;
+  int epi = EPI_GENERIC;
+  if (e.out_dtype == PL_OUT_INT8 && e.round_mode == PL_ROUND_ARM && p.vec_ok && e.scale) {
+    if (e.act == PL_ACT_RELU || e.act == PL_ACT_RELU6) {
+      float hi = 127.f;
+      if (e.act == PL_ACT_RELU6 && e.act_arg < hi) hi = e.act_arg;
+      if (hi > 0.f) {
+        union { float f; uint32_t u; } cv;
+        cv.f = hi;
+        p.hi_bits = cv.u;
+        epi = e.residual ? EPI_I8_RELU_RES : EPI_I8_RELU;
+      }
+    } else if (e.act == PL_ACT_NONE && !e.residual) {
+      epi = EPI_I8_SIGNED;
+    }
+  }
+  switch (epi) {
+    case EPI_I8_RELU: return launch_one<EPI_I8_RELU>(ta, tb, p, grid, smem, stream);
+    case EPI_I8_RELU_RES: return launch_one<EPI_I8_RELU_RES>(ta, tb, p, grid, smem, stream);
+    case EPI_I8_SIGNED: return launch_one<EPI_I8_SIGNED>(ta, tb, p, grid, smem, stream);
+    default: return launch_one<EPI_GENERIC>(ta, tb, p, grid, smem, stream);
+  }
 }
 
 int check_epi(const pl_epilogue* e) {
@@ -439,12 +619,14 @@ int common_setup(IgemmParams& p, long long M, int Nout, void* y, int ldy, const 
   p.a_stage_bytes = (uint32_t)(kBM * p.BK);
   p.b_stage_bytes = (uint32_t)((p.BN * p.BK + 1023) / 1024 * 1024);
   p.tx_bytes = (uint32_t)(kBM * p.BK + p.BN * p.BK);
-  p.tmem_cols = pow2_cols(2 * p.BN);
+  p.acc_stride = (uint32_t)(p.BN < 32 ? 32 : p.BN);
+  p.tmem_cols = pow2_cols(2 * (int)p.acc_stride);
   p.y = y;
   p.ldy = ldy;
   p.epi = make_epi(e, Nout);
   const int eb = e->out_dtype == PL_OUT_INT8 ? 1 : 4;
   p.vec_ok = ((reinterpret_cast<uintptr_t>(y) & 15) == 0) && (((long long)ldy * eb) % 16 == 0);
+  p.res_vec_ok = e->residual && ((reinterpret_cast<uintptr_t>(e->residual) & 15) == 0) && (e->ld_res % 16 == 0);
   return PL_OK;
 }
 

@@ -1,0 +1,349 @@
+"""Synthetic int8 programs (MobileNetV1, ResNet-50) and their device executor.
+
+A *program* is a plain list of op records (numpy weights, scales, shapes) -- the
+state Paddle-Lite's optimiser leaves behind after quant_dequant_fuse / conv_bn_fuse
+/ conv_activation_fuse / static_kernel_pick: every conv carries
+`input_scale`, per-channel `weight_scale`, `output_scale`, folded-BN bias and a
+fused activation; consecutive int8 ops keep their tensors int8 + NHWC + on device.
+`DeviceNet` binds a program to pre-allocated device buffers and enqueues the whole
+network through the C-ABI on the current stream (optionally as one CUDA graph).
+tests/ walk the same program with the CPU oracle.
+
+Model files for MobileNetV1/ResNet-50 int8 are not in the reference repo
+(lite/api/mobilenetv1_int8_test.cc needs --model_dir), so weights are random-init
+with seeded generators, as BASELINE.json says.
+"""
+import numpy as np
+import torch
+
+from . import capi as pl
+
+
+def rup(v, m):
+    return (v + m - 1) // m * m
+
+
+class Op(dict):
+    __getattr__ = dict.__getitem__
+    __setattr__ = dict.__setitem__
+
+
+class Builder:
+    """Builds a program; activation scales are filled in later by calibration."""
+
+    def __init__(self, name, seed, in_shape):
+        self.name = name
+        self.rng = np.random.default_rng(seed)
+        self.ops = []
+        self.shapes = {"input": in_shape}  # name -> (H, W, C)   (per image)
+        self.n_tensors = 0
+
+    def _new(self, shape):
+        self.n_tensors += 1
+        name = f"t{self.n_tensors}"
+        self.shapes[name] = shape
+        return name
+
+    def quant_in(self):
+        H, W, C = self.shapes["input"]
+        out = self._new((H, W, C))
+        self.ops.append(Op(kind="quant_in", src="input", dst=out, out_scale=None))
+        return out
+
+    def conv(self, src, K, k, stride, pad, act="relu", depthwise=False, out_fp32=False, res=None):
+        H, W, C = self.shapes[src]
+        P = (H + 2 * pad - k) // stride + 1
+        Q = (W + 2 * pad - k) // stride + 1
+        cg = 1 if depthwise else C
+        w = self.rng.integers(-127, 128, (K, k, k, cg), dtype=np.int8)
+        w_scale = (self.rng.uniform(0.5, 2.0, K) / 127.0 / np.sqrt(k * k * cg)).astype(np.float32)
+        bias = self.rng.uniform(-0.5, 0.5, K).astype(np.float32)
+        out = self._new((P, Q, K))
+        self.ops.append(Op(kind="dwconv" if depthwise else "conv", src=src, dst=out, w=w, w_scale=w_scale,
+                           bias=bias, k=k, stride=stride, pad=pad, act=act, K=K, C=C,
+                           in_scale=None, out_scale=None, out_fp32=out_fp32, res=res, res_scale=None))
+        return out
+
+    def pool(self, src, k, stride, pad, typ, global_pooling=False):
+        H, W, C = self.shapes[src]
+        if global_pooling:
+            k, stride, pad = H, 1, 0
+        P = (H + 2 * pad - k) // stride + 1
+        Q = (W + 2 * pad - k) // stride + 1
+        out = self._new((P, Q, C))
+        self.ops.append(Op(kind="pool", src=src, dst=out, k=k, stride=stride, pad=pad, typ=typ,
+                           in_scale=None, out_scale=None))
+        return out
+
+    def add(self, a, b, act="relu"):
+        out = self._new(self.shapes[a])
+        self.ops.append(Op(kind="add", src=a, src2=b, dst=out, act=act, a_scale=None, b_scale=None,
+                           out_scale=None))
+        return out
+
+    def fc(self, src, N):
+        H, W, C = self.shapes[src]
+        Kd = H * W * C
+        w = self.rng.integers(-127, 128, (Kd, N), dtype=np.int8)  # fc W is [K, N]
+        w_scale = (self.rng.uniform(0.5, 2.0, N) / 127.0 / np.sqrt(Kd)).astype(np.float32)
+        bias = self.rng.uniform(-0.5, 0.5, N).astype(np.float32)
+        out = self._new((1, 1, N))
+        self.ops.append(Op(kind="fc", src=src, dst=out, w=w, w_scale=w_scale, bias=bias, K=Kd, N=N,
+                           in_scale=None, out_fp32=True))
+        return out
+
+
+def mobilenet_v1(seed=1234, act="relu", res=224):
+    """MobileNetV1 1.0: conv0 3x3 s2 + 13 x (dw3x3 + pw1x1) + gap + fc."""
+    b = Builder("mobilenet_v1", seed, (res, res, 3))
+    t = b.quant_in()
+    t = b.conv(t, 32, 3, 2, 1, act)
+    cfg = [(64, 1), (128, 2), (128, 1), (256, 2), (256, 1), (512, 2), (512, 1), (512, 1), (512, 1),
+           (512, 1), (512, 1), (1024, 2), (1024, 1)]
+    for K, s in cfg:
+        C = b.shapes[t][2]
+        t = b.conv(t, C, 3, s, 1, act, depthwise=True)
+        t = b.conv(t, K, 1, 1, 0, act)
+    t = b.pool(t, 7, 1, 0, "avg", global_pooling=True)
+    b.fc(t, 1000)
+    return b
+
+
+def resnet50(seed=1234, res=224, fuse_residual=True):
+    """ResNet-50 v1: 7x7 s2 stem, 3x3 s2 max pool, [3,4,6,3] bottlenecks (stride on the 3x3), gap, fc.
+    fuse_residual: the shortcut add + relu runs in the epilogue of the block's last 1x1 conv
+    (ConvParam::residualData; the reference's conv_elementwise fuse pass does this for fp32)
+    instead of a separate int8 elementwise_add."""
+    b = Builder("resnet50", seed, (res, res, 3))
+    t = b.quant_in()
+    t = b.conv(t, 64, 7, 2, 3, "relu")
+    t = b.pool(t, 3, 2, 1, "max")
+    for stage, (mid, blocks) in enumerate([(64, 3), (128, 4), (256, 6), (512, 3)]):
+        for blk in range(blocks):
+            stride = 2 if (blk == 0 and stage > 0) else 1
+            short = t
+            if blk == 0:
+                short = b.conv(t, mid * 4, 1, stride, 0, "none")
+            u = b.conv(t, mid, 1, 1, 0, "relu")
+            u = b.conv(u, mid, 3, stride, 1, "relu")
+            if fuse_residual:
+                t = b.conv(u, mid * 4, 1, 1, 0, "relu", res=short)
+            else:
+                u = b.conv(u, mid * 4, 1, 1, 0, "none")
+                t = b.add(u, short, "relu")
+    t = b.pool(t, 7, 1, 0, "avg", global_pooling=True)
+    b.fc(t, 1000)
+    return b
+
+
+def program_macs(prog):
+    """MACs per image by op kind (the reference's OpCharacter formula, lite/operators/conv_op.h:43-62)."""
+    tot = {"conv": 0, "dwconv": 0, "fc": 0}
+    for op in prog.ops:
+        if op.kind in ("conv", "dwconv"):
+            P, Q, K = prog.shapes[op.dst]
+            cg = 1 if op.kind == "dwconv" else op.C
+            tot[op.kind] += P * Q * K * op.k * op.k * cg
+        elif op.kind == "fc":
+            tot["fc"] += op.K * op.N
+    return tot
+
+
+def program_bytes(prog):
+    """Algorithmic bytes per image: every activation read/written once at its storage width,
+    weights + scale/bias once per batch (returned separately)."""
+    act = 0
+    wts = 0
+    for op in prog.ops:
+        H, W, C = prog.shapes[op.src]
+        P, Q, K = prog.shapes[op.dst]
+        if op.kind == "quant_in":
+            act += H * W * C * 4 + P * Q * K
+        elif op.kind in ("conv", "dwconv"):
+            act += H * W * C + P * Q * K * (4 if op.out_fp32 else 1) + (P * Q * K if op.get("res") else 0)
+            wts += op.w.size + 8 * K
+        elif op.kind == "pool":
+            act += H * W * C + P * Q * K
+        elif op.kind == "add":
+            act += 3 * H * W * C
+        elif op.kind == "fc":
+            act += op.K + op.N * 4
+            wts += op.w.size + 8 * op.N
+    return act, wts
+
+
+_ACT = {"none": pl.ACT_NONE, "relu": pl.ACT_RELU, "relu6": pl.ACT_RELU6, "leaky": pl.ACT_LEAKY}
+
+
+class DeviceNet:
+    """A program bound to device buffers for a fixed batch.  `calibrate()` fixes the
+    activation scales (abs-max / 127 on a calibration batch, computed with the fp32-out
+    kernels); `run()` enqueues the int8 network on the current stream."""
+
+    def __init__(self, prog, batch, device="cuda"):
+        self.prog = prog
+        self.batch = batch
+        self.dev = device
+        self.bufs = {}
+        self.layers = []
+        self.graph = None
+        H, W, C = prog.shapes["input"]
+        self.input = torch.zeros((batch, C, H, W), dtype=torch.float32, device=device)  # NCHW fp32
+        self.calibrated = all(op.get("out_scale", 1.0) is not None or op.kind == "fc" for op in prog.ops)
+        self._weights_to_device()
+
+    # -- one-off (PrepareForRun) ------------------------------------------------
+    def _weights_to_device(self):
+        for op in self.prog.ops:
+            if op.kind == "conv":
+                op["_wp"] = pl.pack_conv_weight(torch.from_numpy(op.w).to(self.dev))
+            elif op.kind == "dwconv":
+                op["_wp"] = torch.from_numpy(np.ascontiguousarray(op.w.reshape(op.K, op.k, op.k))).to(self.dev)
+            elif op.kind == "fc":
+                op["_wp"] = pl.transpose_i8(torch.from_numpy(op.w).to(self.dev))  # [K,N] -> [N,K]
+        torch.cuda.synchronize()
+
+    def _buf(self, name, dtype=torch.int8):
+        key = (name, dtype)
+        if key not in self.bufs:
+            H, W, C = self.prog.shapes[name]
+            ld = rup(C, 16) if dtype == torch.int8 else C
+            self.bufs[key] = torch.zeros((self.batch, H, W, ld), dtype=dtype, device=self.dev)
+        return self.bufs[key]
+
+    def _fold(self, op, n_out, out_fp32):
+        out_dtype = pl.OUT_FP32 if out_fp32 else pl.OUT_INT8
+        arg = 6.0 if op.get("act") == "relu6" else 0.1
+        sf, bf, argf = pl.fold_scales(op.w_scale, n_out, op.in_scale, 1.0 if out_fp32 else op.out_scale,
+                                      out_dtype, op.bias, _ACT[op.get("act", "none")], arg)
+        return torch.from_numpy(sf).to(self.dev), torch.from_numpy(bf).to(self.dev), argf
+
+    # -- scale calibration ------------------------------------------------------
+    def calibrate(self, x_nchw):
+        """Propagates scales layer by layer: out_scale = absmax(fp32 output)/127."""
+        assert x_nchw.shape[0] <= self.batch
+        n = x_nchw.shape[0]
+        scales = {}
+        vals = {}
+        for op in self.prog.ops:
+            if op.kind == "quant_in":
+                op.out_scale = float(x_nchw.abs().max().item()) / 127.0
+                vals[op.dst] = pl.quantize_nchw_to_nhwc(x_nchw.contiguous(), op.out_scale,
+                                                        rup(x_nchw.shape[1], 16))
+                scales[op.dst] = op.out_scale
+            elif op.kind in ("conv", "dwconv"):
+                op.in_scale = scales[op.src]
+                res = vals[op.res] if op.get("res") else None
+                if res is not None:
+                    op.res_scale = scales[op.res]
+                sf, bf, argf = self._fold(op, op.K, True)
+                y = self._exec_conv(op, vals[op.src], sf, bf, argf, pl.OUT_FP32, None, res, op.res_scale)
+                op.out_scale = max(float(y.abs().max().item()), 1e-6) / 127.0
+                sf, bf, argf = self._fold(op, op.K, op.out_fp32)
+                vals[op.dst] = self._exec_conv(op, vals[op.src], sf, bf, argf,
+                                               pl.OUT_FP32 if op.out_fp32 else pl.OUT_INT8, None, res,
+                                               self._res_scale(op))
+                scales[op.dst] = op.out_scale
+            elif op.kind == "pool":
+                op.in_scale = scales[op.src]
+                op.out_scale = op.in_scale  # pooling keeps the scale (max exact; avg requantised 1:1)
+                vals[op.dst] = self._exec_pool(op, vals[op.src], None)
+                scales[op.dst] = op.out_scale
+            elif op.kind == "add":
+                op.a_scale, op.b_scale = scales[op.src], scales[op.src2]
+                y = pl.add(vals[op.src], vals[op.src2], op.a_scale, op.b_scale, _ACT[op.act], out=pl.OUT_FP32)
+                op.out_scale = max(float(y.abs().max().item()), 1e-6) / 127.0
+                vals[op.dst] = pl.add(vals[op.src], vals[op.src2], op.a_scale / op.out_scale,
+                                      op.b_scale / op.out_scale, _ACT[op.act])
+                scales[op.dst] = op.out_scale
+            elif op.kind == "fc":
+                op.in_scale = scales[op.src]
+                vals[op.dst] = None
+        torch.cuda.synchronize()
+        self.calibrated = True
+        del vals
+        return self
+
+    # -- per-op launchers -------------------------------------------------------
+    def _res_scale(self, op):
+        if not op.get("res"):
+            return 0.0
+        return op.res_scale if op.out_fp32 else op.res_scale / op.out_scale
+
+    def _exec_conv(self, op, x, sf, bf, argf, out, y, res=None, res_scale=0.0):
+        C = op.C
+        if op.kind == "dwconv":
+            return pl.dwconv2d(x, op._wp, sf, bf, op.k, op.k, (op.stride, op.stride), (op.pad,) * 4,
+                               (1, 1), _ACT[op.act], argf, out, y=y, Cc=C)
+        K = op.K
+        return pl.conv2d(x, op._wp, K, op.k, op.k, sf, bf, (op.stride, op.stride), (op.pad,) * 4, (1, 1),
+                         _ACT[op.act], argf, out, y=y, Cc=C, ldy=(rup(K, 16) if out == pl.OUT_INT8 else K),
+                         residual=res, res_scale=res_scale or 0.0)
+
+    def _exec_pool(self, op, x, y):
+        H, W, C = self.prog.shapes[op.src]
+        typ = pl.POOL_MAX if op.typ == "max" else pl.POOL_AVG
+        return pl.pool2d(x, (op.k, op.k), (op.stride, op.stride), (op.pad,) * 4, typ, True,
+                         op.in_scale / op.out_scale, pl.OUT_INT8, Cc=C, y=y)
+
+    # -- bind + run ---------------------------------------------------------------
+    def bind(self):
+        """Pre-computes folded scales and output buffers; builds the launch list."""
+        assert self.calibrated, "calibrate() or load scales first"
+        self.layers = []
+        for op in self.prog.ops:
+            if op.kind == "quant_in":
+                y = self._buf(op.dst)
+                self.layers.append((op, lambda op=op, y=y: pl.quantize_nchw_to_nhwc(
+                    self.input, op.out_scale, y.shape[-1], y=y)))
+            elif op.kind in ("conv", "dwconv"):
+                sf, bf, argf = self._fold(op, op.K, op.out_fp32)
+                x = self._buf(op.src)
+                y = self._buf(op.dst, torch.float32 if op.out_fp32 else torch.int8)
+                out = pl.OUT_FP32 if op.out_fp32 else pl.OUT_INT8
+                res = self._buf(op.res) if op.get("res") else None
+                rs = self._res_scale(op)
+                self.layers.append((op, lambda op=op, x=x, y=y, sf=sf, bf=bf, argf=argf, out=out, res=res, rs=rs:
+                                    self._exec_conv(op, x, sf, bf, argf, out, y, res, rs)))
+            elif op.kind == "pool":
+                x, y = self._buf(op.src), self._buf(op.dst)
+                self.layers.append((op, lambda op=op, x=x, y=y: self._exec_pool(op, x, y)))
+            elif op.kind == "add":
+                a, b2, y = self._buf(op.src), self._buf(op.src2), self._buf(op.dst)
+                sa, sb = op.a_scale / op.out_scale, op.b_scale / op.out_scale
+                self.layers.append((op, lambda op=op, a=a, b2=b2, y=y, sa=sa, sb=sb:
+                                    pl.add(a, b2, sa, sb, _ACT[op.act], y=y)))
+            elif op.kind == "fc":
+                sf, bf, _ = pl.fold_scales(op.w_scale, op.N, op.in_scale, 1.0, pl.OUT_FP32, op.bias)
+                sf, bf = torch.from_numpy(sf).to(self.dev), torch.from_numpy(bf).to(self.dev)
+                x = self._buf(op.src)
+                A = x.view(self.batch, -1)
+                y = self._buf(op.dst, torch.float32).view(self.batch, op.N)
+                self.output = y
+                self.layers.append((op, lambda op=op, A=A, y=y, sf=sf, bf=bf:
+                                    pl.gemm(A, op._wp, sf, bf, out=pl.OUT_FP32, y=y, K=op.K)))
+        return self
+
+    def run(self):
+        for _, fn in self.layers:
+            fn()
+        return self.output
+
+    def capture(self):
+        """One CUDA graph for the whole network (launch-bound at small batch)."""
+        self.run()
+        torch.cuda.synchronize()
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g):
+            self.run()
+        self.graph = g
+        return self
+
+    def replay(self):
+        self.graph.replay()
+        return self.output
+
+    def forward(self, x_nchw):
+        """Public call: fp32 NCHW device tensor in, fp32 logits out (device)."""
+        self.input.copy_(x_nchw, non_blocking=True)
+        return self.replay() if self.graph is not None else self.run()

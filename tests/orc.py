@@ -82,8 +82,21 @@ def fold_scales(w_scale, n_out, in_scale, out_scale, out_dtype, bias=None,
 
 def conv2d(x, w, scale_f, bias_f, strides=(1, 1), pads=(0, 0, 0, 0),
            dil=(1, 1), groups=1, act=ACT_NONE, act_arg=0.0, out=OUT_INT8,
-           rnd=ROUND_ARM):
-    """x NHWC int8, w OHWI int8 -> y NHWC."""
+           rnd=ROUND_ARM, residual=None, res_scale=0.0):
+    """x NHWC int8, w OHWI int8 -> y NHWC.  residual: int8 NHWC of the output
+    shape, fused as v = fmaf(res, res_scale, v) before the activation."""
+    if residual is not None:
+        acc = conv2d(x, w, None, None, strides, pads, dil, groups, out=OUT_INT32)
+        N_, P_, Q_, K_ = acc.shape
+        y = np.empty(acc.shape, _NP_OUT[out])
+        res = np.ascontiguousarray(residual, np.int8)
+        assert res.shape == acc.shape
+        sf = np.ascontiguousarray(scale_f, np.float32)
+        bf = None if bias_f is None else np.ascontiguousarray(bias_f, np.float32)
+        rc = lib().orc_epilogue_res(_p(acc), C.c_int64(N_ * P_ * Q_), K_, _p(sf), _p(bf), _p(res), K_,
+                                    _f(res_scale), act, _f(act_arg), out, rnd, _p(y))
+        assert rc == 0
+        return y
     N, H, W, Cc = x.shape
     K, R, S, _ = w.shape
     P = conv_out_size(H, R, dil[0], pads[0], pads[1], strides[0])

@@ -176,6 +176,26 @@ def test_conv_full_size_slices_match_oracle(pl):
     assert np.array_equal(a1 + a2, a12)
 
 
+@pytest.mark.parametrize("case", [CONV_CASES[1], CONV_CASES[3], CONV_CASES[11], CONV_CASES[12]])
+@pytest.mark.parametrize("out", ["int8", "fp32"])
+def test_conv_fused_residual(pl, case, out):
+    """conv + int8 shortcut + relu in one epilogue (ConvParam::residualData)."""
+    x, w, ws, bias, si, so = conv_inputs(case, 41)
+    N, H, W, Cc, K, R, S, st, pads, dl = case
+    o = orc.OUT_INT8 if out == "int8" else orc.OUT_FP32
+    sf, bf, _ = orc.fold_scales(ws, K, si, so, o, bias)
+    P = orc.conv_out_size(H, R, dl, pads[0], pads[1], st)
+    Q = orc.conv_out_size(W, S, dl, pads[2], pads[3], st)
+    res = np.random.default_rng(8).integers(-127, 128, (N, P, Q, K), dtype=np.int8)
+    rs = 0.37 if out == "int8" else 0.011
+    want = orc.conv2d(x, w, sf, bf, (st, st), pads, (dl, dl), 1, orc.ACT_RELU, 0.0, o, residual=res, res_scale=rs)
+    ldx = rup(Cc, 16)
+    wp = pl.pack_conv_weight(dev(w))
+    got = host(pl.conv2d(dev(pad_c(x, ldx)), wp, K, R, S, dev(sf), dev(bf), (st, st), pads, (dl, dl),
+                         pl.ACT_RELU, 0.0, o, Cc=Cc, residual=dev(res), res_scale=rs))
+    assert np.array_equal(got, want)
+
+
 def test_conv_writes_into_channel_slice(pl):
     """ldy > K: the conv writes a channel slice of a wider buffer (free concat)."""
     case = (1, 10, 10, 32, 32, 3, 3, 1, (1, 1, 1, 1), 1)
