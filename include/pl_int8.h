@@ -142,6 +142,13 @@ int pl_dequantize_i8_f32(const int8_t* x, float* y, int64_t n, float scale,
 int pl_quantize_nchw_f32_to_nhwc_i8(const float* x, int8_t* y, int N, int C,
                                     int H, int W, int ldy, float scale,
                                     int round_mode, pl_stream_t stream);
+/* pack transform for thin-channel first layers (C <= 4 per 32-bit word): explicit
+ * im2col A[N*P*Q, ldA] with A[m][(r*S+s)*cbytes + j] = x[n, ih, iw, j] (0 outside the
+ * image and in the row pad), so that the conv runs as pl_gemm_i8 with fat K rows
+ * instead of R*S thin TMA im2col loads.  cbytes % 4 == 0, ldx % 4 == 0, ldA % 16 == 0. */
+int pl_im2col_i8_nhwc(const int8_t* x, int ldx, int8_t* A, int ldA, int N, int H,
+                      int W, int cbytes, int R, int S, int sh, int sw, int pt,
+                      int pl, int dh, int dw, int P, int Q, pl_stream_t stream);
 /* plain layout transforms; elem_bytes 1 or 4; ld = NHWC pixel pitch (elements) */
 int pl_nchw_to_nhwc(const void* x, void* y, int N, int C, int H, int W, int ld,
                     int elem_bytes, pl_stream_t stream);

@@ -223,6 +223,22 @@ def quantize_nchw_to_nhwc(x, scale, ld=None, rnd=ROUND_ARM, y=None):
     return y
 
 
+def im2col(x, R, S, strides=(1, 1), pads=(0, 0, 0, 0), dil=(1, 1), A=None, cbytes=None):
+    """Explicit im2col of a thin-channel NHWC int8 tensor [N,H,W,ld] (ld % 4 == 0) ->
+    A [N*P*Q, ldA], ldA = roundup(R*S*cbytes, 16)."""
+    N, H, W, ld = x.shape
+    cbytes = ld if cbytes is None else cbytes
+    P = conv_out_size(H, R, dil[0], pads[0], pads[1], strides[0])
+    Q = conv_out_size(W, S, dil[1], pads[2], pads[3], strides[1])
+    ldA = (R * S * cbytes + 15) // 16 * 16
+    if A is None:
+        A = torch.empty((N * P * Q, ldA), dtype=torch.int8, device=x.device)
+    _check(lib().pl_im2col_i8_nhwc(_ptr(x), ld, _ptr(A), A.stride(0), N, H, W, cbytes, R, S, strides[0],
+                                   strides[1], pads[0], pads[2], dil[0], dil[1], P, Q, _stream()),
+           "pl_im2col_i8_nhwc")
+    return A
+
+
 def nchw_to_nhwc(x, ld=None):
     N, Cc, H, W = x.shape
     ld = Cc if ld is None else ld

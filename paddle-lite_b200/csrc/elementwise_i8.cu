@@ -129,7 +129,7 @@ __global__ void zero_pad_kernel(int8_t* y, long long npix, int C, int ld, int eb
 __global__ void __launch_bounds__(256)
 quant_nchw_to_nhwc_kernel(const float* __restrict__ x, int8_t* __restrict__ y, int C, long long HW,
                           int ld, float scale, float inv, int round_mode) {
-  extern __shared__ int8_t slab[];  // [64][ld]
+  extern __shared__ __align__(16) int8_t slab[];  // [64][ld]
   const int n = blockIdx.y;
   const long long hw0 = (long long)blockIdx.x * 64;
   const int npx = (int)((HW - hw0) < 64 ? (HW - hw0) : 64);
@@ -150,8 +150,47 @@ quant_nchw_to_nhwc_kernel(const float* __restrict__ x, int8_t* __restrict__ y, i
   if ((ld & 15) == 0 && (reinterpret_cast<uintptr_t>(y) & 15) == 0) {
     for (int i = threadIdx.x; i < (bytes >> 4); i += 256)
       reinterpret_cast<uint4*>(yo)[i] = reinterpret_cast<const uint4*>(slab)[i];
+  } else if ((ld & 3) == 0 && (reinterpret_cast<uintptr_t>(y) & 3) == 0) {
+    for (int i = threadIdx.x; i < (bytes >> 2); i += 256)
+      reinterpret_cast<uint32_t*>(yo)[i] = reinterpret_cast<const uint32_t*>(slab)[i];
   } else {
     for (int i = threadIdx.x; i < bytes; i += 256) yo[i] = slab[i];
+  }
+}
+
+// ------------------------------------------------------------------ im2col
+// Explicit im2col for thin-channel first layers (C <= 4 stored as one 32-bit word
+// per pixel): A[m][(r*S+s)*cw + j] = x[n, ih, iw, j], zero outside the image and in
+// the [R*S*cw*4, ldA) pad.  One thread produces 16 output bytes (4 words).  The conv
+// then runs as a plain tensor-core GEMM with fat 128-byte K rows instead of 49 TMA
+// im2col loads of 16 useful bytes each.
+__global__ void __launch_bounds__(256)
+im2col_words_kernel(const uint32_t* __restrict__ x, uint4* __restrict__ A, int H, int W, int ldxw,
+                    int cw, int R, int S, int sh, int sw, int pt, int pl_, int dh, int dw, int P, int Q,
+                    long long M, int groups, int kwords) {
+  const long long total = M * groups;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total;
+       i += (long long)gridDim.x * blockDim.x) {
+    const int g = (int)(i % groups);
+    const long long m = i / groups;
+    const int oq = (int)(m % Q);
+    const long long t = m / Q;
+    const int op = (int)(t % P);
+    const long long n = t / P;
+    uint32_t o[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const int kw = g * 4 + j;  // word index inside the row
+      uint32_t v = 0;
+      if (kw < kwords) {
+        const int tap = kw / cw, c = kw - tap * cw;
+        const int r = tap / S, s = tap - r * S;
+        const int ih = op * sh - pt + r * dh, iw = oq * sw - pl_ + s * dw;
+        if (ih >= 0 && ih < H && iw >= 0 && iw < W) v = __ldg(x + ((n * H + ih) * W + iw) * ldxw + c);
+      }
+      o[j] = v;
+    }
+    A[i] = make_uint4(o[0], o[1], o[2], o[3]);
   }
 }
 
@@ -400,6 +439,23 @@ extern "C" int pl_add_i8(const int8_t* a, const int8_t* b, void* y, int64_t n, f
   const int vec = al16(a) && al16(b) && al16(y);
   add_kernel<<<grid_for(vec ? (n + 15) / 16 : n, 256), 256, 0, (cudaStream_t)stream>>>(
       a, b, y, n, sa, sb, act, act_arg, out_dtype, round_mode, vec);
+  ++g_launches;
+  return launch_status();
+}
+
+extern "C" int pl_im2col_i8_nhwc(const int8_t* x, int ldx, int8_t* A, int ldA, int N, int H, int W, int cbytes,
+                                 int R, int S, int sh, int sw, int pt, int pl_, int dh, int dw, int P, int Q,
+                                 pl_stream_t stream) {
+  if (!x || !A || N <= 0 || H <= 0 || W <= 0 || cbytes <= 0 || R <= 0 || S <= 0 || sh <= 0 || sw <= 0 ||
+      dh <= 0 || dw <= 0 || P <= 0 || Q <= 0)
+    return PL_ERR_ARG;
+  if ((cbytes % 4) || (ldx % 4) || ldx < cbytes || (ldA % 16) || ldA < R * S * cbytes) return PL_ERR_ALIGN;
+  if ((reinterpret_cast<uintptr_t>(x) & 3) || !al16(A)) return PL_ERR_ALIGN;
+  const long long M = (long long)N * P * Q;
+  const int groups = ldA / 16;
+  im2col_words_kernel<<<grid_for(M * groups, 256, 16), 256, 0, (cudaStream_t)stream>>>(
+      reinterpret_cast<const uint32_t*>(x), reinterpret_cast<uint4*>(A), H, W, ldx / 4, cbytes / 4, R, S, sh,
+      sw, pt, pl_, dh, dw, P, Q, M, groups, R * S * (cbytes / 4));
   ++g_launches;
   return launch_status();
 }

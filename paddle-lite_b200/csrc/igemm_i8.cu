@@ -26,7 +26,7 @@ namespace pl {
 static constexpr int kBM = 128;            // rows of D per tile (TMEM lanes)
 static constexpr int kEpiWarps = 8;
 static constexpr int kThreads = 64 + 32 * kEpiWarps;  // 10 warps
-static constexpr int kMaxStages = 8;
+static constexpr int kMaxStages = 12;
 
 enum { EPI_GENERIC = 0, EPI_I8_RELU = 1, EPI_I8_SIGNED = 2, EPI_I8_RELU_RES = 3 };
 
@@ -365,19 +365,59 @@ igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
         s_bias[as][etid] = (ok && p.epi.bias) ? __ldg(p.epi.bias + n) : 0.f;
       }
       asm volatile("bar.sync 1, %0;" ::"n"(32 * kEpiWarps) : "memory");
+      // interior tiles of a specialised launch run branch-free: no N/M edge checks per group
+      const bool interior = (EPI != EPI_GENERIC) && (n0 + p.BN <= p.Nout) && (row < p.M);
+      uint4 rres[4][2];
+      if (EPI == EPI_I8_RELU_RES) {
+        // issue every residual load of this warp's columns BEFORE waiting for the MMA:
+        // the (row-strided) loads are in flight while the accumulator is produced
+        if (interior) {
+          const int8_t* rp = p.epi.residual + row * p.epi.ld_res + n0 + half * 32;
+#pragma unroll
+          for (int i = 0; i < 4; ++i)
+            if (half * 32 + 64 * i < p.BN) {
+              rres[i][0] = __ldg(reinterpret_cast<const uint4*>(rp + 64 * i));
+              rres[i][1] = __ldg(reinterpret_cast<const uint4*>(rp + 64 * i + 16));
+            }
+        }
+      }
       mbar_wait(bar_tfull + 8 * as, aphase);
       tc_fence_after();
       const uint32_t t_addr = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)as * p.acc_stride;
-      for (int c0 = half * 32; c0 < p.BN; c0 += 64) {
-        uint32_t acc[32];
-        tmem_ld_32x32b_x32(t_addr + (uint32_t)c0, acc);
-        tmem_ld_wait();
-        if (row < p.M) {
 #pragma unroll
-          for (int g = 0; g < 2; ++g) {
-            const int c = c0 + 16 * g;
-            if (c < p.BN && n0 + c < p.Nout)
-              store_group16<EPI>(p, acc + 16 * g, row, n0 + c, &s_scale[as][c], &s_bias[as][c]);
+      for (int i = 0; i < 4; ++i) {
+        const int c0 = half * 32 + 64 * i;
+        if (c0 < p.BN) {  // warp-uniform
+          uint32_t acc[32];
+          tmem_ld_32x32b_x32(t_addr + (uint32_t)c0, acc);
+          tmem_ld_wait();
+          if (interior) {
+            int8_t* out = reinterpret_cast<int8_t*>(p.y) + row * p.ldy + n0 + c0;
+#pragma unroll
+            for (int g = 0; g < 2; ++g) {
+              const uint4 rw = (EPI == EPI_I8_RELU_RES) ? rres[i][g] : make_uint4(0, 0, 0, 0);
+              const uint32_t rws[4] = {rw.x, rw.y, rw.z, rw.w};
+              uint32_t w[4];
+#pragma unroll
+              for (int q4 = 0; q4 < 4; ++q4) {
+                const float4 sc = *reinterpret_cast<const float4*>(&s_scale[as][c0 + 16 * g + 4 * q4]);
+                const float4 bi = *reinterpret_cast<const float4*>(&s_bias[as][c0 + 16 * g + 4 * q4]);
+                if (EPI == EPI_I8_RELU)
+                  w[q4] = quad_i8_relu<false>(acc + 16 * g + 4 * q4, sc, bi, p.hi_bits, 0u, 0.f);
+                else if (EPI == EPI_I8_RELU_RES)
+                  w[q4] = quad_i8_relu<true>(acc + 16 * g + 4 * q4, sc, bi, p.hi_bits, rws[q4], p.epi.res_scale);
+                else
+                  w[q4] = quad_i8_signed(acc + 16 * g + 4 * q4, sc, bi);
+              }
+              *reinterpret_cast<uint4*>(out + 16 * g) = make_uint4(w[0], w[1], w[2], w[3]);
+            }
+          } else if (row < p.M) {
+#pragma unroll
+            for (int g = 0; g < 2; ++g) {
+              const int c = c0 + 16 * g;
+              if (c < p.BN && n0 + c < p.Nout)
+                store_group16<EPI>(p, acc + 16 * g, row, n0 + c, &s_scale[as][c], &s_bias[as][c]);
+            }
           }
         }
       }
@@ -587,7 +627,7 @@ int launch_igemm(const CUtensorMap& ta, const CUtensorMap& tb, IgemmParams& p, p
         union { float f; uint32_t u; } cv;
         cv.f = hi;
         p.hi_bits = cv.u;
-        epi = e.residual ? EPI_I8_RELU_RES : EPI_I8_RELU;
+        epi = e.residual ? (p.res_vec_ok ? EPI_I8_RELU_RES : EPI_GENERIC) : EPI_I8_RELU;
       }
     } else if (e.act == PL_ACT_NONE && !e.residual) {
       epi = EPI_I8_SIGNED;

@@ -195,7 +195,17 @@ class DeviceNet:
     # -- one-off (PrepareForRun) ------------------------------------------------
     def _weights_to_device(self):
         for op in self.prog.ops:
-            if op.kind == "conv":
+            if op.kind == "conv" and op.C <= 4:
+                # thin first layer: explicit im2col (one 32-bit word per pixel) + tensor-core GEMM
+                K, R, S, C = op.w.shape
+                w4 = np.zeros((K, R, S, 4), np.int8)
+                w4[..., :C] = op.w
+                ldA = rup(R * S * 4, 16)
+                bt = np.zeros((K, ldA), np.int8)
+                bt[:, : R * S * 4] = w4.reshape(K, -1)
+                op["_wp"] = torch.from_numpy(bt).to(self.dev)
+                op["_ldA"] = ldA
+            elif op.kind == "conv":
                 op["_wp"] = pl.pack_conv_weight(torch.from_numpy(op.w).to(self.dev))
             elif op.kind == "dwconv":
                 op["_wp"] = torch.from_numpy(np.ascontiguousarray(op.w.reshape(op.K, op.k, op.k))).to(self.dev)
@@ -207,7 +217,7 @@ class DeviceNet:
         key = (name, dtype)
         if key not in self.bufs:
             H, W, C = self.prog.shapes[name]
-            ld = rup(C, 16) if dtype == torch.int8 else C
+            ld = (4 if C <= 4 else rup(C, 16)) if dtype == torch.int8 else C
             self.bufs[key] = torch.zeros((self.batch, H, W, ld), dtype=dtype, device=self.dev)
         return self.bufs[key]
 
@@ -228,8 +238,9 @@ class DeviceNet:
         for op in self.prog.ops:
             if op.kind == "quant_in":
                 op.out_scale = float(x_nchw.abs().max().item()) / 127.0
+                C_in = x_nchw.shape[1]
                 vals[op.dst] = pl.quantize_nchw_to_nhwc(x_nchw.contiguous(), op.out_scale,
-                                                        rup(x_nchw.shape[1], 16))
+                                                        4 if C_in <= 4 else rup(C_in, 16))
                 scales[op.dst] = op.out_scale
             elif op.kind in ("conv", "dwconv"):
                 op.in_scale = scales[op.src]
@@ -276,9 +287,29 @@ class DeviceNet:
             return pl.dwconv2d(x, op._wp, sf, bf, op.k, op.k, (op.stride, op.stride), (op.pad,) * 4,
                                (1, 1), _ACT[op.act], argf, out, y=y, Cc=C)
         K = op.K
+        if C <= 4:
+            N_, H_, W_, _ = x.shape
+            P = (H_ + 2 * op.pad - op.k) // op.stride + 1
+            Q = (W_ + 2 * op.pad - op.k) // op.stride + 1
+            A = self._im2col_buf(op, N_ * P * Q)
+            pl.im2col(x, op.k, op.k, (op.stride, op.stride), (op.pad,) * 4, A=A)
+            ldy = rup(K, 16) if out == pl.OUT_INT8 else K
+            if y is None:
+                y = torch.zeros((N_, P, Q, ldy), dtype=pl._TORCH_OUT[out], device=x.device)
+            pl.gemm(A, op._wp, sf, bf, _ACT[op.act], argf, out, y=y.view(N_ * P * Q, ldy), M=N_ * P * Q, N=K,
+                    K=op._ldA)
+            return y
         return pl.conv2d(x, op._wp, K, op.k, op.k, sf, bf, (op.stride, op.stride), (op.pad,) * 4, (1, 1),
                          _ACT[op.act], argf, out, y=y, Cc=C, ldy=(rup(K, 16) if out == pl.OUT_INT8 else K),
                          residual=res, res_scale=res_scale or 0.0)
+
+    def _im2col_buf(self, op, rows):
+        key = ("im2col", id(op))
+        buf = self.bufs.get(key)
+        if buf is None or buf.shape[0] < rows:
+            buf = torch.empty((rows, op._ldA), dtype=torch.int8, device=self.dev)
+            self.bufs[key] = buf
+        return buf[:rows]
 
     def _exec_pool(self, op, x, y):
         H, W, C = self.prog.shapes[op.src]

@@ -29,7 +29,8 @@ def _check(builder, batch, res, graph):
     got = got.cpu().numpy().copy()
     want, vals = net_oracle.run_program(prog, x.numpy(), keep=True)
     # every intermediate int8 tensor is bit-exact, not only the logits
-    for (name, dtype), buf in net.bufs.items():
+    for key, buf in net.bufs.items():
+        name, dtype = key
         if dtype == torch.int8 and name in vals:
             C = prog.shapes[name][2]
             assert np.array_equal(buf.cpu().numpy()[..., :C], vals[name]), f"tensor {name} differs"

@@ -399,3 +399,34 @@ def test_launch_counter_and_peak_probe(pl):
     assert pl.launch_count() == n0 + 1
     # operands are all ones: every accumulator of the last-written stage is a multiple of 128
     assert int(out[0].item()) % 128 == 0 and int(out[0].item()) > 0
+
+
+@pytest.mark.parametrize("case", [(2, 20, 22, 3, 32, 3, 2, 1), (1, 38, 38, 3, 64, 7, 2, 3), (1, 9, 9, 4, 16, 5, 1, 2)])
+def test_thin_first_layer_im2col_gemm(pl, case):
+    """C <= 4 first layers: pack transform (explicit im2col, one word per pixel) + GEMM
+    equals the oracle's direct convolution."""
+    N, H, W, Cc, K, k, st, pd = case
+    rng = np.random.default_rng(sum(case))
+    x = rng.integers(-127, 128, (N, H, W, Cc), dtype=np.int8)
+    w = rng.integers(-127, 128, (K, k, k, Cc), dtype=np.int8)
+    ws = ((1 + np.arange(K) % 7) / (7 * 127)).astype(np.float32)
+    bias = rng.uniform(-1, 1, K).astype(np.float32)
+    sf, bf, _ = orc.fold_scales(ws, K, 1 / 127, Cc * k * k / 127 / 4, orc.OUT_INT8, bias)
+    want = orc.conv2d(x, w, sf, bf, (st, st), (pd,) * 4, act=orc.ACT_RELU)
+    A = pl.im2col(dev(pad_c(x, 4)), k, k, (st, st), (pd,) * 4)
+    P = orc.conv_out_size(H, k, 1, pd, pd, st)
+    Q = orc.conv_out_size(W, k, 1, pd, pd, st)
+    # the packed rows are the (r, s, c4) patches
+    a = host(A).reshape(N, P, Q, -1)
+    xp = np.zeros((N, H + 2 * pd, W + 2 * pd, 4), np.int8)
+    xp[:, pd:pd + H, pd:pd + W, :Cc] = x
+    for (n, p_, q_) in ((0, 0, 0), (N - 1, P - 1, Q - 1), (0, P // 2, Q // 3)):
+        patch = xp[n, p_ * st:p_ * st + k, q_ * st:q_ * st + k, :].reshape(-1)
+        assert np.array_equal(a[n, p_, q_, : k * k * 4], patch)
+        assert not a[n, p_, q_, k * k * 4:].any()
+    w4 = np.zeros((K, k, k, 4), np.int8)
+    w4[..., :Cc] = w
+    bt = np.zeros((K, A.shape[1]), np.int8)
+    bt[:, : k * k * 4] = w4.reshape(K, -1)
+    got = host(pl.gemm(A, dev(bt), dev(sf), dev(bf), act=pl.ACT_RELU)).reshape(N, P, Q, K)
+    assert np.array_equal(got, want)
