@@ -395,6 +395,7 @@ igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
             int8_t* out = reinterpret_cast<int8_t*>(p.y) + row * p.ldy + n0 + c0;
 #pragma unroll
             for (int g = 0; g < 2; ++g) {
+              if (c0 + 16 * g >= p.BN) break;  // BN == 16: the second half of the chunk is not ours
               const uint4 rw = (EPI == EPI_I8_RELU_RES) ? rres[i][g] : make_uint4(0, 0, 0, 0);
               const uint32_t rws[4] = {rw.x, rw.y, rw.z, rw.w};
               uint32_t w[4];
