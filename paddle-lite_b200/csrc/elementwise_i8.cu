@@ -164,33 +164,92 @@ quant_nchw_to_nhwc_kernel(const float* __restrict__ x, int8_t* __restrict__ y, i
 // the [R*S*cw*4, ldA) pad.  One thread produces 16 output bytes (4 words).  The conv
 // then runs as a plain tensor-core GEMM with fat 128-byte K rows instead of 49 TMA
 // im2col loads of 16 useful bytes each.
+struct FastDiv {  // q = (n * mul) >> (32 + sh), exact for n < 2^31 (round-up magic)
+  uint32_t mul, sh, d;
+};
+static inline FastDiv make_fastdiv(uint32_t d) {
+  FastDiv f;
+  f.d = d;
+  if (d == 1) {
+    f.mul = 0;
+    f.sh = 0;
+    return f;
+  }
+  uint32_t l = 0;
+  while ((1u << l) < d) ++l;  // ceil(log2 d)
+  const uint64_t m = ((1ull << (32 + l)) + d - 1) / d;  // 33-bit magic, top bit implicit
+  f.mul = (uint32_t)(m - (1ull << 32));
+  f.sh = l;
+  return f;
+}
+__device__ __forceinline__ uint32_t fdiv(uint32_t n, const FastDiv f) {
+  if (f.d == 1) return n;
+  const uint32_t t = __umulhi(n, f.mul);
+  return (t + ((n - t) >> 1)) >> (f.sh - 1);
+}
+
 __global__ void __launch_bounds__(256)
 im2col_words_kernel(const uint32_t* __restrict__ x, uint4* __restrict__ A, int H, int W, int ldxw,
-                    int cw, int R, int S, int sh, int sw, int pt, int pl_, int dh, int dw, int P, int Q,
-                    long long M, int groups, int kwords) {
-  const long long total = M * groups;
-  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total;
-       i += (long long)gridDim.x * blockDim.x) {
-    const int g = (int)(i % groups);
-    const long long m = i / groups;
-    const int oq = (int)(m % Q);
-    const long long t = m / Q;
-    const int op = (int)(t % P);
-    const long long n = t / P;
+                    int cw, int S, int sh, int sw, int pt, int pl_, int dh, int dw, FastDiv dP, FastDiv dQ,
+                    FastDiv dG, uint32_t total, int kwords) {
+  // per-word lookup (r*dh, s*dw, c) built once per block
+  __shared__ int tab[256];
+  for (int kw = threadIdx.x; kw < 256; kw += 256) {
+    int v = -1;
+    if (kw < kwords) {
+      const int tap = kw / cw, c = kw - tap * cw;
+      const int r = tap / S, s = tap - r * S;
+      v = (r * dh) | ((s * dw) << 10) | (c << 20);
+    }
+    tab[kw] = v;
+  }
+  __syncthreads();
+  for (uint32_t i = blockIdx.x * 256u + threadIdx.x; i < total; i += gridDim.x * 256u) {
+    const uint32_t m = fdiv(i, dG);
+    const int g = (int)(i - m * dG.d);
+    const uint32_t t = fdiv(m, dQ);
+    const int oq = (int)(m - t * dQ.d);
+    const uint32_t n = fdiv(t, dP);
+    const int op = (int)(t - n * dP.d);
+    const int ih0 = op * sh - pt, iw0 = oq * sw - pl_;
+    const uint32_t* xn = x + (size_t)n * H * W * ldxw;
     uint32_t o[4];
 #pragma unroll
     for (int j = 0; j < 4; ++j) {
-      const int kw = g * 4 + j;  // word index inside the row
+      const int e = tab[g * 4 + j];
       uint32_t v = 0;
-      if (kw < kwords) {
-        const int tap = kw / cw, c = kw - tap * cw;
-        const int r = tap / S, s = tap - r * S;
-        const int ih = op * sh - pt + r * dh, iw = oq * sw - pl_ + s * dw;
-        if (ih >= 0 && ih < H && iw >= 0 && iw < W) v = __ldg(x + ((n * H + ih) * W + iw) * ldxw + c);
+      if (e >= 0) {
+        const int ih = ih0 + (e & 1023), iw = iw0 + ((e >> 10) & 1023);
+        if ((unsigned)ih < (unsigned)H && (unsigned)iw < (unsigned)W)
+          v = __ldg(xn + ((size_t)ih * W + iw) * ldxw + (e >> 20));
       }
       o[j] = v;
     }
     A[i] = make_uint4(o[0], o[1], o[2], o[3]);
+  }
+}
+
+// fp32 NCHW -> int8 NHWC with one 32-bit word per pixel (C <= 4): thread = 4 pixels
+__global__ void __launch_bounds__(256)
+quant_nchw_to_word_kernel(const float* __restrict__ x, uint4* __restrict__ y, int C, long long HW4,
+                          float scale, float inv, int round_mode) {
+  const int n = blockIdx.y;
+  const float* xs = x + (long long)n * C * HW4 * 4;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < HW4;
+       i += (long long)gridDim.x * blockDim.x) {
+    int q[4][4];
+#pragma unroll
+    for (int c = 0; c < 4; ++c) {
+      float4 f = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (c < C) f = __ldg(reinterpret_cast<const float4*>(xs + (long long)c * HW4 * 4) + i);
+      q[0][c] = c < C ? round_sat_i8(quant_pre(f.x, scale, inv, round_mode), round_mode) : 0;
+      q[1][c] = c < C ? round_sat_i8(quant_pre(f.y, scale, inv, round_mode), round_mode) : 0;
+      q[2][c] = c < C ? round_sat_i8(quant_pre(f.z, scale, inv, round_mode), round_mode) : 0;
+      q[3][c] = c < C ? round_sat_i8(quant_pre(f.w, scale, inv, round_mode), round_mode) : 0;
+    }
+    y[(long long)n * HW4 + i] =
+        make_uint4(pack4_i8(q[0][0], q[0][1], q[0][2], q[0][3]), pack4_i8(q[1][0], q[1][1], q[1][2], q[1][3]),
+                   pack4_i8(q[2][0], q[2][1], q[2][2], q[2][3]), pack4_i8(q[3][0], q[3][1], q[3][2], q[3][3]));
   }
 }
 
@@ -407,6 +466,13 @@ extern "C" int pl_quantize_nchw_f32_to_nhwc_i8(const float* x, int8_t* y, int N,
   if (!x || !y || N <= 0 || C <= 0 || H <= 0 || W <= 0 || ldy < C || !(scale > 0.f)) return PL_ERR_ARG;
   if (N > 65535 || (size_t)64 * ldy > 48 * 1024) return PL_ERR_UNSUPPORTED;
   const long long HW = (long long)H * W;
+  if (ldy == 4 && C <= 4 && (HW % 4) == 0 && al16(x) && al16(y)) {
+    dim3 grid((unsigned)((HW / 4 + 255) / 256 > 64 ? 64 : (HW / 4 + 255) / 256), (unsigned)N);
+    quant_nchw_to_word_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(x, reinterpret_cast<uint4*>(y), C, HW / 4,
+                                                                      scale, 1.f / scale, round_mode);
+    ++g_launches;
+    return launch_status();
+  }
   dim3 grid((unsigned)((HW + 63) / 64), (unsigned)N);
   quant_nchw_to_nhwc_kernel<<<grid, 256, (size_t)64 * ldy, (cudaStream_t)stream>>>(
       x, y, C, HW, ldy, scale, 1.f / scale, round_mode);
@@ -453,9 +519,13 @@ extern "C" int pl_im2col_i8_nhwc(const int8_t* x, int ldx, int8_t* A, int ldA, i
   if ((reinterpret_cast<uintptr_t>(x) & 3) || !al16(A)) return PL_ERR_ALIGN;
   const long long M = (long long)N * P * Q;
   const int groups = ldA / 16;
+  const int kwords = R * S * (cbytes / 4);
+  if (M * groups >= (1ll << 31) || kwords > 256 || (R - 1) * dh > 1023 || (S - 1) * dw > 1023)
+    return PL_ERR_UNSUPPORTED;
   im2col_words_kernel<<<grid_for(M * groups, 256, 16), 256, 0, (cudaStream_t)stream>>>(
-      reinterpret_cast<const uint32_t*>(x), reinterpret_cast<uint4*>(A), H, W, ldx / 4, cbytes / 4, R, S, sh,
-      sw, pt, pl_, dh, dw, P, Q, M, groups, R * S * (cbytes / 4));
+      reinterpret_cast<const uint32_t*>(x), reinterpret_cast<uint4*>(A), H, W, ldx / 4, cbytes / 4, S, sh, sw,
+      pt, pl_, dh, dw, make_fastdiv((uint32_t)P), make_fastdiv((uint32_t)Q), make_fastdiv((uint32_t)groups),
+      (uint32_t)(M * groups), kwords);
   ++g_launches;
   return launch_status();
 }

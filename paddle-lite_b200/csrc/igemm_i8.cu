@@ -384,13 +384,17 @@ igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
       mbar_wait(bar_tfull + 8 * as, aphase);
       tc_fence_after();
       const uint32_t t_addr = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)as * p.acc_stride;
+      // TMEM reads are double buffered: the load of chunk i+1 is in flight while chunk i
+      // runs through the ALU epilogue
+      uint32_t accb[2][32];
+      if (half * 32 < p.BN) tmem_ld_32x32b_x32(t_addr + (uint32_t)(half * 32), accb[0]);
 #pragma unroll
       for (int i = 0; i < 4; ++i) {
         const int c0 = half * 32 + 64 * i;
         if (c0 < p.BN) {  // warp-uniform
-          uint32_t acc[32];
-          tmem_ld_32x32b_x32(t_addr + (uint32_t)c0, acc);
           tmem_ld_wait();
+          if (i < 3 && c0 + 64 < p.BN) tmem_ld_32x32b_x32(t_addr + (uint32_t)(c0 + 64), accb[(i + 1) & 1]);
+          uint32_t(&acc)[32] = accb[i & 1];
           if (interior) {
             int8_t* out = reinterpret_cast<int8_t*>(p.y) + row * p.ldy + n0 + c0;
 #pragma unroll
