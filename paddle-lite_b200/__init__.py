@@ -9,3 +9,4 @@ importlib -- see `load()` in tests/conftest.py / __graft_entry__.py).
 There is no CPU fallback: importing `capi` without the built library raises.
 """
 from . import capi  # noqa: F401
+from . import lite_harness  # noqa: F401

@@ -1,0 +1,320 @@
+// C window onto the C++ plugin mirror so that tests can drive the kernel classes the
+// way the reference's own CUDA kernel tests do (lite/kernels/cuda/conv_compute_test.cc
+// :232-298): build tensors, create the kernel through the registry (or the miniature
+// static_kernel_pick), SetParam -> SetContext -> Launch(), sync, read back.
+// Test / integration aid only: a Paddle-Lite build links the kernel classes directly.
+#include <cstring>
+#include <memory>
+#include <string>
+#include <vector>
+
+#include "lite/core/mir/static_kernel_pick.h"
+#include "lite/core/op_registry.h"
+#include "lite/kernels/cuda/int8_common.h"
+
+using namespace paddle::lite;  // NOLINT
+namespace ops = paddle::lite::operators;
+
+static thread_local std::string g_err;
+
+#define PLK_TRY try {
+#define PLK_CATCH                  \
+  }                                \
+  catch (const std::exception& e) { \
+    g_err = e.what();              \
+    cudaGetLastError();            \
+    return -1;                     \
+  }                                \
+  return 0;
+
+static Tensor* T(void* h) { return static_cast<Tensor*>(h); }
+
+static std::unique_ptr<KernelBase> CreateKernel(const std::string& op, TargetType t, PrecisionType p, DataLayoutType l,
+                                                PrecisionType out_prec, const std::string& alias = "") {
+  auto ks = KernelRegistry::Global().Create(op, t, p, l);
+  for (auto& k : ks) {
+    if (!alias.empty()) {
+      if (k->alias() == alias) return std::move(k);
+      continue;
+    }
+    const auto* decl = ParamTypeRegistry::Global().Find(k->key_with_alias(), k->place());
+    if (!decl) continue;
+    for (const char* name : {"Output", "Out"}) {
+      auto it = decl->outputs.find(name);
+      if (it != decl->outputs.end() && it->second.precision == out_prec) return std::move(k);
+    }
+  }
+  LITE_FATAL("no kernel") << op << " out_prec=" << static_cast<int>(out_prec) << " alias=" << alias;
+  return nullptr;
+}
+
+static void LaunchAndSync(KernelBase* k, int launches) {
+  std::unique_ptr<KernelContext> ctx(new KernelContext);
+  auto& cuda = ctx->As<CUDAContext>();
+  cudaStream_t s;
+  TargetWrapperCuda::CreateStream(&s);
+  cuda.SetExecStream(s);
+  k->SetContext(std::move(ctx));
+  try {
+    for (int i = 0; i < launches; ++i) k->Launch();
+    TargetWrapperCuda::StreamSync(s);
+  } catch (...) {
+    cudaStreamDestroy(s);
+    throw;
+  }
+  TargetWrapperCuda::DestroyStream(s);
+}
+
+extern "C" {
+
+const char* plk_last_error() { return g_err.c_str(); }
+
+void* plk_tensor_create() { return new Tensor; }
+void plk_tensor_destroy(void* t) { delete T(t); }
+
+int plk_tensor_assign(void* t, int precision, int target, const int64_t* dims, int ndim, const void* host) {
+  PLK_TRY
+  DDim d(std::vector<int64_t>(dims, dims + ndim));
+  const bool cuda = target == static_cast<int>(TARGET(kCUDA));
+  switch (static_cast<PrecisionType>(precision)) {
+    case PRECISION(kInt8):
+      cuda ? T(t)->Assign<int8_t, TARGET(kCUDA)>(static_cast<const int8_t*>(host), d)
+           : T(t)->Assign<int8_t, TARGET(kHost)>(static_cast<const int8_t*>(host), d);
+      break;
+    case PRECISION(kInt32):
+      cuda ? T(t)->Assign<int32_t, TARGET(kCUDA)>(static_cast<const int32_t*>(host), d)
+           : T(t)->Assign<int32_t, TARGET(kHost)>(static_cast<const int32_t*>(host), d);
+      break;
+    case PRECISION(kFloat):
+      cuda ? T(t)->Assign<float, TARGET(kCUDA)>(static_cast<const float*>(host), d)
+           : T(t)->Assign<float, TARGET(kHost)>(static_cast<const float*>(host), d);
+      break;
+    default: LITE_FATAL("precision") << precision;
+  }
+  PLK_CATCH
+}
+int plk_tensor_ndim(void* t) { return static_cast<int>(T(t)->dims().size()); }
+void plk_tensor_dims(void* t, int64_t* out) {
+  for (size_t i = 0; i < T(t)->dims().size(); ++i) out[i] = T(t)->dims()[i];
+}
+int plk_tensor_precision(void* t) { return static_cast<int>(T(t)->precision()); }
+int plk_tensor_target(void* t) { return static_cast<int>(T(t)->target()); }
+int64_t plk_tensor_bytes(void* t) { return static_cast<int64_t>(T(t)->memory_size()); }
+int plk_tensor_to_host(void* t, void* dst, int64_t cap) {
+  PLK_TRY
+  CHECK_LE(static_cast<int64_t>(T(t)->memory_size()), cap);
+  TargetWrapperCuda::DeviceSync();
+  T(t)->CopyToHost(dst);
+  PLK_CATCH
+}
+
+// newline separated "op/alias/target/precision/layout"
+int plk_list_kernels(char* buf, int cap) {
+  std::string s;
+  for (auto& k : KernelRegistry::Global().DebugKeys()) s += k + "\n";
+  if (static_cast<int>(s.size()) + 1 > cap) return -static_cast<int>(s.size()) - 1;
+  std::memcpy(buf, s.c_str(), s.size() + 1);
+  return static_cast<int>(s.size());
+}
+
+// the static_kernel_pick rule: valid_places = {kCUDA/kInt8/kNHWC, kCUDA/kInt8/kNCHW, kCUDA/kFloat/kNCHW}
+int plk_pick(const char* op, int enable_int8, int n_cons, const int* cons_int8, const float* cons_scale, char* out_key,
+             int cap, float* out_scale) {
+  PLK_TRY
+  std::vector<mir::ConsumerInfo> cons(n_cons);
+  for (int i = 0; i < n_cons; ++i) {
+    cons[i].enable_int8 = cons_int8[i] != 0;
+    cons[i].input_scale = cons_scale ? cons_scale[i] : 1.f;
+  }
+  std::vector<Place> places = {Place(TARGET(kCUDA), PRECISION(kInt8), DATALAYOUT(kNHWC)),
+                               Place(TARGET(kCUDA), PRECISION(kInt8), DATALAYOUT(kNCHW)),
+                               Place(TARGET(kCUDA), PRECISION(kFloat), DATALAYOUT(kNCHW))};
+  float os = 0.f;
+  auto k = mir::StaticKernelPick(op, places, enable_int8 != 0, cons, &os);
+  std::string key = k ? k->SerializedKernelType() : std::string("");
+  CHECK_LT(static_cast<int>(key.size()), cap);
+  std::memcpy(out_key, key.c_str(), key.size() + 1);
+  if (out_scale) *out_scale = os;
+  PLK_CATCH
+}
+
+int plk_run_conv(const char* op, void* x, void* filter, void* bias, void* residual, void* out, const int* strides,
+                 const int* pads, const int* dil, int groups, int act_type, float act_coef, float input_scale,
+                 const float* wscale, int n_ws, float output_scale, float residual_scale, int out_int8, int launches) {
+  PLK_TRY
+  ops::ConvParam p;
+  p.x = T(x);
+  p.filter = T(filter);
+  p.bias = bias ? T(bias) : nullptr;
+  p.output = T(out);
+  p.strides = {strides[0], strides[1]};
+  p.paddings = std::make_shared<std::vector<int>>(pads, pads + 4);
+  p.dilations = std::make_shared<std::vector<int>>(dil, dil + 2);
+  p.groups = groups;
+  if (residual) {
+    p.residualData = T(residual);
+    p.fuse_residual_connection = true;
+    p.scale_in_eltwise = residual_scale;
+  }
+  if (act_type) {
+    p.activation_param.has_active = true;
+    p.activation_param.active_type = static_cast<paddle::lite_api::ActivationType>(act_type);
+    p.activation_param.Relu_clipped_coef = act_coef;
+    p.activation_param.Leaky_relu_alpha = act_coef;
+  }
+  p.enable_int8 = true;
+  p.input_scale = input_scale;
+  p.weight_scale.assign(wscale, wscale + n_ws);
+  p.output_scale = output_scale;
+  auto k = CreateKernel(op, TARGET(kCUDA), PRECISION(kInt8), DATALAYOUT(kNHWC),
+                        out_int8 ? PRECISION(kInt8) : PRECISION(kFloat));
+  k->SetParam(p);
+  LaunchAndSync(k.get(), launches);
+  PLK_CATCH
+}
+
+int plk_run_fc(void* x, void* w, void* bias, void* out, int in_num_col_dims, const char* act, float input_scale,
+               const float* wscale, int n_ws, float output_scale, int out_int8, int launches) {
+  PLK_TRY
+  ops::FcParam p;
+  p.input = T(x);
+  p.w = T(w);
+  p.bias = bias ? T(bias) : nullptr;
+  p.output = T(out);
+  p.in_num_col_dims = in_num_col_dims;
+  p.activation_type = act ? act : "";
+  p.enable_int8 = true;
+  p.input_scale = input_scale;
+  p.weight_scale.assign(wscale, wscale + n_ws);
+  p.output_scale = output_scale;
+  auto k = CreateKernel("fc", TARGET(kCUDA), PRECISION(kInt8), DATALAYOUT(kNCHW),
+                        out_int8 ? PRECISION(kInt8) : PRECISION(kFloat));
+  k->SetParam(p);
+  LaunchAndSync(k.get(), launches);
+  PLK_CATCH
+}
+
+int plk_run_mul(void* x, void* y, void* out, int x_cols, int y_cols, float input_scale, const float* wscale, int n_ws,
+                float output_scale, int out_int8) {
+  PLK_TRY
+  ops::MulParam p;
+  p.x = T(x);
+  p.y = T(y);
+  p.output = T(out);
+  p.x_num_col_dims = x_cols;
+  p.y_num_col_dims = y_cols;
+  p.enable_int8 = true;
+  p.input_scale = input_scale;
+  p.weight_scale.assign(wscale, wscale + n_ws);
+  p.output_scale = output_scale;
+  auto k = CreateKernel("mul", TARGET(kCUDA), PRECISION(kInt8), DATALAYOUT(kNCHW),
+                        out_int8 ? PRECISION(kInt8) : PRECISION(kFloat));
+  k->SetParam(p);
+  LaunchAndSync(k.get(), 1);
+  PLK_CATCH
+}
+
+int plk_run_matmul(void* x, void* y, void* out, int tx, int ty, float alpha, float input_scale, const float* wscale,
+                   int n_ws, float output_scale, int out_int8) {
+  PLK_TRY
+  ops::MatMulParam p;
+  p.X = T(x);
+  p.Y = T(y);
+  p.Out = T(out);
+  p.transpose_X = tx != 0;
+  p.transpose_Y = ty != 0;
+  p.alpha = alpha;
+  p.enable_int8 = true;
+  p.input_scale = input_scale;
+  p.weight_scale.assign(wscale, wscale + n_ws);
+  p.output_scale = output_scale;
+  auto k = CreateKernel("matmul", TARGET(kCUDA), PRECISION(kInt8), DATALAYOUT(kNCHW),
+                        out_int8 ? PRECISION(kInt8) : PRECISION(kFloat));
+  k->SetParam(p);
+  LaunchAndSync(k.get(), 1);
+  PLK_CATCH
+}
+
+int plk_run_calib(void* in, void* out, float scale, int to_int8) {
+  PLK_TRY
+  ops::CalibParam p;
+  p.input = T(in);
+  p.output = T(out);
+  p.scale = scale;
+  auto k = CreateKernel("calib", TARGET(kCUDA), PRECISION(kInt8), DATALAYOUT(kNCHW), PRECISION(kUnk),
+                        to_int8 ? "fp32_to_int8" : "int8_to_fp32");
+  k->SetParam(p);
+  LaunchAndSync(k.get(), 1);
+  PLK_CATCH
+}
+
+int plk_run_layout(void* in, void* out, int to_nhwc) {
+  PLK_TRY
+  ops::LayoutParam p;
+  p.x = T(in);
+  p.y = T(out);
+  const bool i8 = T(in)->precision() == PRECISION(kInt8);
+  auto k = CreateKernel("layout", TARGET(kCUDA), i8 ? PRECISION(kInt8) : PRECISION(kFloat), DATALAYOUT(kNCHW),
+                        PRECISION(kUnk),
+                        std::string(i8 ? "int8_" : "") + (to_nhwc ? "nchw2nhwc" : "nhwc2nchw"));
+  k->SetParam(p);
+  LaunchAndSync(k.get(), 1);
+  PLK_CATCH
+}
+
+int plk_run_io_copy(void* in, void* out, int h2d) {
+  PLK_TRY
+  ops::IoCopyParam p;
+  p.x = T(in);
+  p.y = T(out);
+  auto k = CreateKernel("io_copy", TARGET(kCUDA), PRECISION(kAny), DATALAYOUT(kAny), PRECISION(kUnk),
+                        h2d ? "host_to_device" : "device_to_host");
+  k->SetParam(p);
+  LaunchAndSync(k.get(), 1);
+  PLK_CATCH
+}
+
+int plk_run_pool(void* x, void* out, const char* type, const int* ksize, const int* strides, const int* pads,
+                 int global_pooling, int exclusive, int ceil_mode, float input_scale, float output_scale,
+                 int out_int8) {
+  PLK_TRY
+  ops::PoolParam p;
+  p.x = T(x);
+  p.output = T(out);
+  p.pooling_type = type;
+  p.ksize = {ksize[0], ksize[1]};
+  p.strides = {strides[0], strides[1]};
+  p.paddings = std::make_shared<std::vector<int>>(pads, pads + 4);
+  p.global_pooling = global_pooling != 0;
+  p.exclusive = exclusive != 0;
+  p.ceil_mode = ceil_mode != 0;
+  p.enable_int8 = true;
+  p.input_scale = input_scale;
+  p.output_scale = output_scale;
+  auto k = CreateKernel("pool2d", TARGET(kCUDA), PRECISION(kInt8), DATALAYOUT(kNHWC),
+                        out_int8 ? PRECISION(kInt8) : PRECISION(kFloat));
+  k->SetParam(p);
+  LaunchAndSync(k.get(), 1);
+  PLK_CATCH
+}
+
+int plk_run_add(void* x, void* y, void* out, float x_scale, float y_scale, float out_scale, const char* act,
+                int out_int8) {
+  PLK_TRY
+  ops::ElementwiseParam p;
+  p.X = T(x);
+  p.Y = T(y);
+  p.Out = T(out);
+  p.enable_int8 = true;
+  p.x_input_scale = x_scale;
+  p.y_input_scale = y_scale;
+  p.output_scale = out_scale;
+  p.act_type = act ? act : "";
+  auto k = CreateKernel("elementwise_add", TARGET(kCUDA), PRECISION(kInt8), DATALAYOUT(kNHWC),
+                        out_int8 ? PRECISION(kInt8) : PRECISION(kFloat));
+  k->SetParam(p);
+  LaunchAndSync(k.get(), 1);
+  PLK_CATCH
+}
+
+}  // extern "C"
