@@ -10,3 +10,4 @@ There is no CPU fallback: importing `capi` without the built library raises.
 """
 from . import capi  # noqa: F401
 from . import lite_harness  # noqa: F401
+from . import nsplit  # noqa: F401

@@ -291,3 +291,17 @@ def i8_mma_peak(ctas, iters, bn=256):
     out = torch.zeros(4, dtype=torch.int32, device="cuda")
     _check(lib().pl_i8_mma_peak(ctas, iters, bn, _ptr(out), _stream()), "pl_i8_mma_peak")
     return out
+
+
+def measure_i8_mma_peak(iters=20000, bn=256):
+    """attainable tcgen05 kind::i8 rate in TOPS: back-to-back 128 x bn x 32 MMAs from
+    resident smem on one CTA per SM, timed with CUDA events."""
+    ctas = torch.cuda.get_device_properties(torch.cuda.current_device()).multi_processor_count
+    i8_mma_peak(ctas, 1000, bn)
+    torch.cuda.synchronize()
+    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    a.record()
+    i8_mma_peak(ctas, iters, bn)
+    b.record()
+    torch.cuda.synchronize()
+    return ctas * iters * 2.0 * 128 * bn * 32 / (a.elapsed_time(b) * 1e-3) / 1e12
