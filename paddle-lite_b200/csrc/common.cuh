@@ -174,6 +174,23 @@ __device__ __forceinline__ void tma_load_2d(uint32_t dst, const void* desc, uint
       "l"(desc), "r"(bar), "r"(c0), "r"(c1)
       : "memory");
 }
+// smem -> global tiled store (bulk async-group completion); rows/cols outside the
+// tensor map's extent are clipped by the hardware
+__device__ __forceinline__ void tma_store_2d(const void* desc, uint32_t src, int c0, int c1) {
+  asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%2, %3}], [%1];" ::"l"(desc),
+               "r"(src), "r"(c0), "r"(c1)
+               : "memory");
+}
+__device__ __forceinline__ void bulk_commit_group() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+// all but the N most recent bulk groups have finished READING their smem source
+template <int N>
+__device__ __forceinline__ void bulk_wait_group_read() {
+  asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(N) : "memory");
+}
+template <int N>
+__device__ __forceinline__ void bulk_wait_group() {
+  asm volatile("cp.async.bulk.wait_group %0;" ::"n"(N) : "memory");
+}
 // im2col-mode load of `pixelsPerColumn` output pixels starting at base pixel
 // (w,h,n), channels [c, c+channelsPerPixel), filter offset (off_w, off_h).
 __device__ __forceinline__ void tma_load_im2col_4d(uint32_t dst, const void* desc, uint32_t bar,

@@ -7,16 +7,19 @@
 // an fp32 temporary + a second elementwise kernel, activation.cu:91-446) with
 // ONE kernel and no temporary.  Semantics of the epilogue: common.cuh.
 //
-// Warp roles (320 threads, persistent over output tiles):
+// Warp roles (576 threads, persistent over output tiles):
 //   warp 0      TMA producer (one lane)
 //   warp 1      TMEM allocator + MMA issuer (one lane)
-//   warps 2..9  epilogue; warp w reads TMEM lanes [32*(w%4), +32) and the column
-//               half (w-2)/4 of the tile, 32 columns per tcgen05.ld
+//   warps 2..17 epilogue; warp w reads TMEM lanes [32*(w%4), +32) and the 16-column
+//               units (w-2)/4 + 4i of the tile, 16 columns per tcgen05.ld.  int8
+//               outputs are staged in swizzled smem panels and leave by TMA store;
+//               the fused residual arrives through a TMA ring fed by warp 0
 // The epilogue runs once per output byte and is ALU-issue bound, so the hot
 // variants are specialised at compile time (EPI_*): packed FFMA2/FADD2, one
 // VIMNMX.RELU for relu+clamp on the float bit pattern, PRMT packing, scale/bias
 // staged in shared memory once per tile.
 #include <cuda.h>
+#include <cstdlib>
 #include <cudaTypedefs.h>
 
 #include "common.cuh"
@@ -24,9 +27,10 @@
 namespace pl {
 
 static constexpr int kBM = 128;            // rows of D per tile (TMEM lanes)
-static constexpr int kEpiWarps = 8;
-static constexpr int kThreads = 64 + 32 * kEpiWarps;  // 10 warps
+static constexpr int kEpiWarps = 16;
+static constexpr int kThreads = 64 + 32 * kEpiWarps;  // 18 warps
 static constexpr int kMaxStages = 12;
+static constexpr int kMaxResBufs = 6;   // depth of the TMA residual ring
 
 enum { EPI_GENERIC = 0, EPI_I8_RELU = 1, EPI_I8_SIGNED = 2, EPI_I8_RELU_RES = 3 };
 
@@ -44,6 +48,13 @@ struct IgemmParams {
   int vec_ok;      // 16-byte vector stores allowed
   int res_vec_ok;  // 16-byte vector loads of the residual allowed
   uint32_t hi_bits;  // float bits of the upper clamp for the relu fast paths
+  // int8 fast paths: the tile is staged in swizzled smem panels of PW = min(BN,128)
+  // columns and written by TMA (full-line stores, hardware edge clipping); the fused
+  // residual arrives the same way, loaded by the producer warp
+  int tma_out, tma_res, res_bufs;
+  int PW, panels, pw_shift;
+  uint32_t swz_mask;                 // 7 / 3 / 1 / 0 for 128 / 64 / 32 / 16-byte panel rows
+  uint32_t out_stage_off, res_stage_off;  // byte offsets from the 1024-aligned smem base
   EpiParams epi;
 };
 
@@ -80,6 +91,15 @@ __device__ __forceinline__ uint32_t prmt_(uint32_t a, uint32_t b, uint32_t sel) 
   uint32_t r;
   asm("prmt.b32 %0, %1, %2, %3;" : "=r"(r) : "r"(a), "r"(b), "r"(sel));
   return r;
+}
+
+__device__ __forceinline__ void st_shared_v4(uint32_t addr, uint32_t a, uint32_t b, uint32_t c, uint32_t d) {
+  asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(a), "r"(b), "r"(c), "r"(d) : "memory");
+}
+__device__ __forceinline__ uint4 ld_shared_v4(uint32_t addr) {
+  uint4 v;
+  asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(addr));
+  return v;
 }
 
 // 4 accumulators -> 4 packed int8, ARM rounding, activation in {relu, relu6}:
@@ -147,46 +167,13 @@ __device__ __forceinline__ float generic_value(int acc, float s, float b, const 
 }
 
 // --------------------------------------------------------------------------
-// epilogue for one 16-column group held in registers (acc[0..15])
+// generic epilogue for one 16-column group held in registers (acc[0..15]): any
+// dtype / activation / rounding / residual, ragged edges, unaligned outputs
 // --------------------------------------------------------------------------
-template <int EPI>
-__device__ __forceinline__ void store_group16(const IgemmParams& p, const uint32_t* acc, long long row,
-                                              int n_base, const float* s_scale, const float* s_bias) {
+__device__ __noinline__ void store_group16(const IgemmParams& p, const uint32_t* acc, long long row,
+                                           int n_base, const float* s_scale, const float* s_bias) {
   const EpiParams& e = p.epi;
   const bool full = (n_base + 16 <= p.Nout);
-  if (EPI != EPI_GENERIC) {
-    if (full && p.vec_ok) {
-      uint32_t w[4];
-      uint4 rw = make_uint4(0, 0, 0, 0);
-      if (EPI == EPI_I8_RELU_RES) {
-        const int8_t* rp = e.residual + row * e.ld_res + n_base;
-        if (p.res_vec_ok) {
-          rw = __ldg(reinterpret_cast<const uint4*>(rp));
-        } else {
-          uint32_t t[4] = {0, 0, 0, 0};
-#pragma unroll
-          for (int j = 0; j < 16; ++j) t[j >> 2] |= (uint32_t)(uint8_t)rp[j] << (8 * (j & 3));
-          rw = make_uint4(t[0], t[1], t[2], t[3]);
-        }
-      }
-      const uint32_t rws[4] = {rw.x, rw.y, rw.z, rw.w};
-#pragma unroll
-      for (int g = 0; g < 4; ++g) {
-        const float4 s = *reinterpret_cast<const float4*>(s_scale + 4 * g);
-        const float4 b = *reinterpret_cast<const float4*>(s_bias + 4 * g);
-        if (EPI == EPI_I8_RELU)
-          w[g] = quad_i8_relu<false>(acc + 4 * g, s, b, p.hi_bits, 0u, 0.f);
-        else if (EPI == EPI_I8_RELU_RES)
-          w[g] = quad_i8_relu<true>(acc + 4 * g, s, b, p.hi_bits, rws[g], e.res_scale);
-        else
-          w[g] = quad_i8_signed(acc + 4 * g, s, b);
-      }
-      int8_t* out = reinterpret_cast<int8_t*>(p.y) + row * p.ldy + n_base;
-      *reinterpret_cast<uint4*>(out) = make_uint4(w[0], w[1], w[2], w[3]);
-      return;
-    }
-    // ragged edge of a fast-path launch: fall through to the generic element code
-  }
   if (e.out_dtype == PL_OUT_INT32) {
     int* out = reinterpret_cast<int*>(p.y) + row * p.ldy + n_base;
     if (full && p.vec_ok) {
@@ -240,9 +227,11 @@ __device__ __forceinline__ void store_group16(const IgemmParams& p, const uint32
 template <int EPI>
 __global__ void __launch_bounds__(kThreads, 1)
 igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
-                const __grid_constant__ CUtensorMap tmap_b, const IgemmParams p) {
+                const __grid_constant__ CUtensorMap tmap_b,
+                const __grid_constant__ CUtensorMap tmap_y,
+                const __grid_constant__ CUtensorMap tmap_r, const IgemmParams p) {
   extern __shared__ uint8_t smem_raw[];
-  __shared__ __align__(8) uint64_t bars[2 * kMaxStages + 4];
+  __shared__ __align__(8) uint64_t bars[2 * kMaxStages + 4 + 2 * kMaxResBufs];
   __shared__ uint32_t tmem_base_slot;
   __shared__ __align__(16) float s_scale[2][256];
   __shared__ __align__(16) float s_bias[2][256];
@@ -254,6 +243,11 @@ igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
   const uint32_t bar_empty = smem_u32(&bars[kMaxStages]);
   const uint32_t bar_tfull = smem_u32(&bars[2 * kMaxStages]);
   const uint32_t bar_tempty = smem_u32(&bars[2 * kMaxStages + 2]);
+  const uint32_t bar_rfull = smem_u32(&bars[2 * kMaxStages + 4]);
+  const uint32_t bar_rempty = smem_u32(&bars[2 * kMaxStages + 4 + kMaxResBufs]);
+  const uint32_t smem_out = smem_base + p.out_stage_off;
+  const uint32_t smem_res = smem_base + p.res_stage_off;
+  const uint32_t tile_bytes = (uint32_t)(kBM * p.BN);
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -262,6 +256,8 @@ igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
   if (threadIdx.x == 0) {
     tma_prefetch_desc(&tmap_a);
     tma_prefetch_desc(&tmap_b);
+    if (EPI != EPI_GENERIC) tma_prefetch_desc(&tmap_y);
+    if (EPI == EPI_I8_RELU_RES) tma_prefetch_desc(&tmap_r);
     for (int s = 0; s < p.stages; ++s) {
       mbar_init(bar_full + 8 * s, 1);
       mbar_init(bar_empty + 8 * s, 1);
@@ -269,6 +265,10 @@ igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
     for (int s = 0; s < 2; ++s) {
       mbar_init(bar_tfull + 8 * s, 1);
       mbar_init(bar_tempty + 8 * s, 32 * kEpiWarps);
+    }
+    for (int s = 0; s < kMaxResBufs; ++s) {
+      mbar_init(bar_rfull + 8 * s, 1);
+      mbar_init(bar_rempty + 8 * s, 32 * kEpiWarps);
     }
     fence_barrier_init();
   }
@@ -287,9 +287,20 @@ igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
       int stage = 0;
       uint32_t phase = 0;
       const uint32_t tx = p.tx_bytes;
+      int rb = 0;
+      uint32_t rphase = 0;
       for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
         const int tn = tile % p.n_tiles, tm = tile / p.n_tiles;
         const int m0 = tm * kBM, n0 = tn * p.BN;
+        if (EPI == EPI_I8_RELU_RES) {
+          // residual tile first: it is the largest load of a 1x1 expand layer
+          mbar_wait(bar_rempty + 8 * rb, rphase ^ 1);
+          mbar_arrive_expect_tx(bar_rfull + 8 * rb, tile_bytes);
+          for (int j = 0; j < p.panels; ++j)
+            tma_load_2d(smem_res + rb * tile_bytes + j * (kBM * p.PW), &tmap_r, bar_rfull + 8 * rb,
+                        n0 + j * p.PW, m0);
+          if (++rb == p.res_bufs) { rb = 0; rphase ^= 1; }
+        }
         int bw = 0, bh = 0, bn = 0;
         if (p.mode == 1) {
           bn = m0 / p.PQ;
@@ -347,12 +358,20 @@ igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
       }
     }
   } else {
-    // ===================== epilogue (warps 2..9) =====================
+    // ===================== epilogue (warps 2..17) =====================
+    // warp w owns TMEM lanes [32*(w%4), +32) (hardware rule) and the 16-column units
+    // cq, cq+4, cq+8, cq+12 of the tile
     const int quarter = warp & 3;
-    const int half = (warp - 2) >> 2;
+    const int cq = (warp - 2) >> 2;
     const int etid = threadIdx.x - 64;
+    constexpr bool kFast = (EPI != EPI_GENERIC);  // int8 paths: swizzled smem staging + TMA store
+    const int units = p.BN >> 4;
+    const uint32_t rowoff = (uint32_t)((quarter * 32 + lane) * p.PW);
+    const uint32_t swx = (rowoff >> 7) & p.swz_mask;
     int as = 0;
     uint32_t aphase = 0;
+    int rb = 0;
+    uint32_t rphase = 0;
     for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
       const int tn = tile % p.n_tiles, tm = tile / p.n_tiles;
       const long long row = (long long)tm * kBM + quarter * 32 + lane;
@@ -364,72 +383,71 @@ igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
         s_scale[as][etid] = ok ? __ldg(p.epi.scale + n) : 0.f;
         s_bias[as][etid] = (ok && p.epi.bias) ? __ldg(p.epi.bias + n) : 0.f;
       }
+      // the previous tile's TMA store must have drained the staging buffer
+      if (kFast && etid == 0) bulk_wait_group_read<0>();
       asm volatile("bar.sync 1, %0;" ::"n"(32 * kEpiWarps) : "memory");
-      // interior tiles of a specialised launch run branch-free: no N/M edge checks per group
-      const bool interior = (EPI != EPI_GENERIC) && (n0 + p.BN <= p.Nout) && (row < p.M);
-      uint4 rres[4][2];
-      if (EPI == EPI_I8_RELU_RES) {
-        // issue every residual load of this warp's columns BEFORE waiting for the MMA:
-        // the (row-strided) loads are in flight while the accumulator is produced
-        if (interior) {
-          const int8_t* rp = p.epi.residual + row * p.epi.ld_res + n0 + half * 32;
-#pragma unroll
-          for (int i = 0; i < 4; ++i)
-            if (half * 32 + 64 * i < p.BN) {
-              rres[i][0] = __ldg(reinterpret_cast<const uint4*>(rp + 64 * i));
-              rres[i][1] = __ldg(reinterpret_cast<const uint4*>(rp + 64 * i + 16));
-            }
-        }
-      }
+      if (EPI == EPI_I8_RELU_RES) mbar_wait(bar_rfull + 8 * rb, rphase);
       mbar_wait(bar_tfull + 8 * as, aphase);
       tc_fence_after();
       const uint32_t t_addr = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)as * p.acc_stride;
-      // TMEM reads are double buffered: the load of chunk i+1 is in flight while chunk i
-      // runs through the ALU epilogue
-      uint32_t accb[2][32];
-      if (half * 32 < p.BN) tmem_ld_32x32b_x32(t_addr + (uint32_t)(half * 32), accb[0]);
+      const uint32_t res_base = smem_res + (uint32_t)rb * tile_bytes + rowoff;
+      const uint32_t out_base = smem_out + rowoff;
+      // TMEM reads are double buffered: unit i+1 is in flight while unit i runs through the ALUs
+      uint32_t accb[2][16];
+      if (cq < units) tmem_ld_32x32b_x16(t_addr + (uint32_t)(cq * 16), accb[0]);
 #pragma unroll
       for (int i = 0; i < 4; ++i) {
-        const int c0 = half * 32 + 64 * i;
-        if (c0 < p.BN) {  // warp-uniform
+        const int u = cq + 4 * i;
+        if (u < units) {  // warp-uniform
           tmem_ld_wait();
-          if (i < 3 && c0 + 64 < p.BN) tmem_ld_32x32b_x32(t_addr + (uint32_t)(c0 + 64), accb[(i + 1) & 1]);
-          uint32_t(&acc)[32] = accb[i & 1];
-          if (interior) {
-            int8_t* out = reinterpret_cast<int8_t*>(p.y) + row * p.ldy + n0 + c0;
+          if (i < 3 && u + 4 < units) tmem_ld_32x32b_x16(t_addr + (uint32_t)((u + 4) * 16), accb[(i + 1) & 1]);
+          uint32_t(&acc)[16] = accb[i & 1];
+          const uint32_t col = (uint32_t)(u * 16);
+          if (kFast) {
+            // position of this 16-byte chunk inside the swizzled staging panels; rows >= M
+            // and columns >= Nout are computed on zero-filled operands and clipped by the store
+            const uint32_t soff = (col >> p.pw_shift) * (uint32_t)(kBM * p.PW) +
+                                  ((((col & (uint32_t)(p.PW - 1)) >> 4) ^ swx) << 4);
+            uint4 rw = make_uint4(0, 0, 0, 0);
+            if (EPI == EPI_I8_RELU_RES) rw = ld_shared_v4(res_base + soff);
+            const uint32_t rws[4] = {rw.x, rw.y, rw.z, rw.w};
+            uint32_t w[4];
 #pragma unroll
-            for (int g = 0; g < 2; ++g) {
-              if (c0 + 16 * g >= p.BN) break;  // BN == 16: the second half of the chunk is not ours
-              const uint4 rw = (EPI == EPI_I8_RELU_RES) ? rres[i][g] : make_uint4(0, 0, 0, 0);
-              const uint32_t rws[4] = {rw.x, rw.y, rw.z, rw.w};
-              uint32_t w[4];
-#pragma unroll
-              for (int q4 = 0; q4 < 4; ++q4) {
-                const float4 sc = *reinterpret_cast<const float4*>(&s_scale[as][c0 + 16 * g + 4 * q4]);
-                const float4 bi = *reinterpret_cast<const float4*>(&s_bias[as][c0 + 16 * g + 4 * q4]);
-                if (EPI == EPI_I8_RELU)
-                  w[q4] = quad_i8_relu<false>(acc + 16 * g + 4 * q4, sc, bi, p.hi_bits, 0u, 0.f);
-                else if (EPI == EPI_I8_RELU_RES)
-                  w[q4] = quad_i8_relu<true>(acc + 16 * g + 4 * q4, sc, bi, p.hi_bits, rws[q4], p.epi.res_scale);
-                else
-                  w[q4] = quad_i8_signed(acc + 16 * g + 4 * q4, sc, bi);
-              }
-              *reinterpret_cast<uint4*>(out + 16 * g) = make_uint4(w[0], w[1], w[2], w[3]);
+            for (int q4 = 0; q4 < 4; ++q4) {
+              const float4 sc = *reinterpret_cast<const float4*>(&s_scale[as][col + 4 * q4]);
+              const float4 bi = *reinterpret_cast<const float4*>(&s_bias[as][col + 4 * q4]);
+              if (EPI == EPI_I8_RELU)
+                w[q4] = quad_i8_relu<false>(acc + 4 * q4, sc, bi, p.hi_bits, 0u, 0.f);
+              else if (EPI == EPI_I8_RELU_RES)
+                w[q4] = quad_i8_relu<true>(acc + 4 * q4, sc, bi, p.hi_bits, rws[q4], p.epi.res_scale);
+              else
+                w[q4] = quad_i8_signed(acc + 4 * q4, sc, bi);
             }
-          } else if (row < p.M) {
-#pragma unroll
-            for (int g = 0; g < 2; ++g) {
-              const int c = c0 + 16 * g;
-              if (c < p.BN && n0 + c < p.Nout)
-                store_group16<EPI>(p, acc + 16 * g, row, n0 + c, &s_scale[as][c], &s_bias[as][c]);
-            }
+            st_shared_v4(out_base + soff, w[0], w[1], w[2], w[3]);
+          } else if (row < p.M && n0 + (int)col < p.Nout) {
+            store_group16(p, acc, row, n0 + (int)col, &s_scale[as][col], &s_bias[as][col]);
           }
         }
       }
       tc_fence_before();
       mbar_arrive(bar_tempty + 8 * as);
       if (++as == 2) { as = 0; aphase ^= 1; }
+      if (EPI == EPI_I8_RELU_RES) {
+        mbar_arrive(bar_rempty + 8 * rb);
+        if (++rb == p.res_bufs) { rb = 0; rphase ^= 1; }
+      }
+      if (kFast) {
+        // generic-proxy smem writes -> visible to the TMA engine, then one thread stores
+        fence_proxy_async();
+        asm volatile("bar.sync 2, %0;" ::"n"(32 * kEpiWarps) : "memory");
+        if (etid == 0) {
+          for (int j = 0; j < p.panels; ++j)
+            tma_store_2d(&tmap_y, smem_out + (uint32_t)(j * kBM * p.PW), n0 + j * p.PW, tm * kBM);
+          bulk_commit_group();
+        }
+      }
     }
+    if (kFast && etid == 0) bulk_wait_group<0>();
   }
 
   tc_fence_before();
@@ -544,7 +562,8 @@ DriverFns& driver() {
 
 CUtensorMapSwizzle swizzle_for(int bk) {
   return bk == 128 ? CU_TENSOR_MAP_SWIZZLE_128B
-                   : (bk == 64 ? CU_TENSOR_MAP_SWIZZLE_64B : CU_TENSOR_MAP_SWIZZLE_32B);
+                   : (bk == 64 ? CU_TENSOR_MAP_SWIZZLE_64B
+                               : (bk == 32 ? CU_TENSOR_MAP_SWIZZLE_32B : CU_TENSOR_MAP_SWIZZLE_NONE));
 }
 
 // 2-D K-major byte matrix [rows, cols] with row pitch ld; box = [box_rows, bk]
@@ -597,8 +616,8 @@ int pick_bn(int Nout, int m_tiles, int sms) {
 }
 
 template <int EPI>
-int launch_one(const CUtensorMap& ta, const CUtensorMap& tb, const IgemmParams& p, int grid, size_t smem,
-               pl_stream_t stream) {
+int launch_one(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& ty, const CUtensorMap& tr,
+               const IgemmParams& p, int grid, size_t smem, pl_stream_t stream) {
   static bool configured = false;  // one process drives one GPU
   if (!configured) {
     // 227 KB is the per-CTA limit for static + dynamic shared memory together
@@ -606,25 +625,32 @@ int launch_one(const CUtensorMap& ta, const CUtensorMap& tb, const IgemmParams& 
                                     (int)(216 * 1024)));
     configured = true;
   }
-  igemm_i8_kernel<EPI><<<grid, kThreads, smem, (cudaStream_t)stream>>>(ta, tb, p);
+  igemm_i8_kernel<EPI><<<grid, kThreads, smem, (cudaStream_t)stream>>>(ta, tb, ty, tr, p);
   ++g_launches;
   return launch_status();
 }
 
+int env_int(const char* name, int dflt) {
+  const char* v = getenv(name);
+  return (v && *v) ? atoi(v) : dflt;
+}
+
+bool tma_epilogue_enabled() {
+  static const bool on = [] {
+    const char* v = getenv("PL_IGEMM_NO_TMA_EPI");
+    return !(v && v[0] == '1');
+  }();
+  return on;
+}
+
 int launch_igemm(const CUtensorMap& ta, const CUtensorMap& tb, IgemmParams& p, pl_stream_t stream) {
-  const int smem_budget = 200 * 1024;
-  int stages = smem_budget / (int)(p.a_stage_bytes + p.b_stage_bytes);
-  if (stages > kMaxStages) stages = kMaxStages;
-  if (stages > p.num_kb && p.num_kb >= 2) stages = p.num_kb;
-  if (stages < 2) stages = 2;
-  p.stages = stages;
-  const size_t smem = (size_t)stages * (p.a_stage_bytes + p.b_stage_bytes) + 1024;
   const int tiles = p.m_tiles * p.n_tiles;
   const int grid = tiles < driver().sm_count ? tiles : driver().sm_count;
   // epilogue specialisation (ragged edges inside a fast-path launch use the generic code)
   const EpiParams& e = p.epi;
   int epi = EPI_GENERIC;
-  if (e.out_dtype == PL_OUT_INT8 && e.round_mode == PL_ROUND_ARM && p.vec_ok && e.scale) {
+  if (e.out_dtype == PL_OUT_INT8 && e.round_mode == PL_ROUND_ARM && p.vec_ok && e.scale &&
+      tma_epilogue_enabled()) {
     if (e.act == PL_ACT_RELU || e.act == PL_ACT_RELU6) {
       float hi = 127.f;
       if (e.act == PL_ACT_RELU6 && e.act_arg < hi) hi = e.act_arg;
@@ -638,11 +664,53 @@ int launch_igemm(const CUtensorMap& ta, const CUtensorMap& tb, IgemmParams& p, p
       epi = EPI_I8_SIGNED;
     }
   }
+  // int8 fast paths leave through swizzled smem panels + TMA stores (and take the
+  // residual in through TMA loads): vec_ok already guarantees the 16-byte rules
+  CUtensorMap ty{}, tr{};
+  p.PW = p.BN < 128 ? p.BN : 128;
+  p.panels = p.BN / p.PW;
+  p.pw_shift = 0;
+  while ((1 << p.pw_shift) < p.PW) ++p.pw_shift;
+  p.swz_mask = p.PW == 128 ? 7u : (p.PW == 64 ? 3u : (p.PW == 32 ? 1u : 0u));
+  p.tma_out = (epi != EPI_GENERIC);
+  p.tma_res = p.tma_out && epi == EPI_I8_RELU_RES;
+  uint32_t extra = 0;
+  if (p.tma_out) {
+    int rc = encode_2d(&ty, p.y, (uint64_t)p.Nout, (uint64_t)p.M, (uint64_t)p.ldy, p.PW, kBM);
+    if (rc) return rc;
+    extra += (uint32_t)(kBM * p.BN);
+    if (p.tma_res) {
+      rc = encode_2d(&tr, e.residual, (uint64_t)p.Nout, (uint64_t)p.M, (uint64_t)e.ld_res, p.PW, kBM);
+      if (rc) return rc;
+    }
+  }
+  const int stage_bytes = (int)(p.a_stage_bytes + p.b_stage_bytes);
+  p.res_bufs = 2;
+  if (p.tma_res) {
+    // the residual is the biggest stream of an expand layer: keep enough tiles in
+    // flight to cover DRAM latency, but leave the mainloop at least 3 stages
+    const int tile = kBM * p.BN;
+    int want = env_int("PL_IGEMM_RES_BUFS", 4);
+    int fit = (215 * 1024 - (int)extra - 3 * stage_bytes) / tile;
+    if (fit < want) want = fit;
+    if (want > kMaxResBufs) want = kMaxResBufs;
+    if (want < 2) want = 2;
+    p.res_bufs = want;
+    extra += (uint32_t)(want * tile);
+  }
+  const int smem_budget = 215 * 1024 - (int)extra;
+  int stages = smem_budget / stage_bytes;
+  if (stages > kMaxStages) stages = kMaxStages;
+  if (stages < 2) return PL_ERR_UNSUPPORTED;
+  p.stages = stages;
+  p.out_stage_off = (uint32_t)(stages * stage_bytes);
+  p.res_stage_off = p.out_stage_off + (uint32_t)(kBM * p.BN);
+  const size_t smem = (size_t)stages * stage_bytes + extra + 1024;
   switch (epi) {
-    case EPI_I8_RELU: return launch_one<EPI_I8_RELU>(ta, tb, p, grid, smem, stream);
-    case EPI_I8_RELU_RES: return launch_one<EPI_I8_RELU_RES>(ta, tb, p, grid, smem, stream);
-    case EPI_I8_SIGNED: return launch_one<EPI_I8_SIGNED>(ta, tb, p, grid, smem, stream);
-    default: return launch_one<EPI_GENERIC>(ta, tb, p, grid, smem, stream);
+    case EPI_I8_RELU: return launch_one<EPI_I8_RELU>(ta, tb, ty, tr, p, grid, smem, stream);
+    case EPI_I8_RELU_RES: return launch_one<EPI_I8_RELU_RES>(ta, tb, ty, tr, p, grid, smem, stream);
+    case EPI_I8_SIGNED: return launch_one<EPI_I8_SIGNED>(ta, tb, ty, tr, p, grid, smem, stream);
+    default: return launch_one<EPI_GENERIC>(ta, tb, ty, tr, p, grid, smem, stream);
   }
 }
 
@@ -660,6 +728,12 @@ int common_setup(IgemmParams& p, long long M, int Nout, void* y, int ldy, const 
   p.Nout = Nout;
   p.m_tiles = (int)((M + kBM - 1) / kBM);
   p.BN = pick_bn(Nout, p.m_tiles, driver().sm_count);
+  // fused-residual launches are bandwidth bound: narrower tiles leave shared memory
+  // for a deeper residual ring
+  if (e->residual) {
+    const int cap = env_int("PL_IGEMM_RES_BN", 128);
+    while (p.BN > cap && p.BN > 16) p.BN >>= 1;
+  }
   p.n_tiles = (Nout + p.BN - 1) / p.BN;
   p.a_stage_bytes = (uint32_t)(kBM * p.BK);
   p.b_stage_bytes = (uint32_t)((p.BN * p.BK + 1023) / 1024 * 1024);

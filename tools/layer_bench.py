@@ -25,6 +25,7 @@ LAYERS = {
     "r3_3x3_128": (28, 28, 128, 128, 3, 1, 1, "relu", False),
     "r3_1x1_128_512_res": (28, 28, 128, 512, 1, 1, 0, "relu", True),
     "r4_3x3_256": (14, 14, 256, 256, 3, 1, 1, "relu", False),
+    "r4_1x1_256_1024_res": (14, 14, 256, 1024, 1, 1, 0, "relu", True),
     "r4_1x1_1024_256": (14, 14, 1024, 256, 1, 1, 0, "relu", False),
     "r5_3x3_512": (7, 7, 512, 512, 3, 1, 1, "relu", False),
     "r5_1x1_512_2048_res": (7, 7, 512, 2048, 1, 1, 0, "relu", True),
