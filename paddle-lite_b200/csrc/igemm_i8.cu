@@ -51,7 +51,7 @@ struct IgemmParams {
   // int8 fast paths: the tile is staged in swizzled smem panels of PW = min(BN,128)
   // columns and written by TMA (full-line stores, hardware edge clipping); the fused
   // residual arrives the same way, loaded by the producer warp
-  int tma_out, tma_res, res_bufs;
+  int tma_out, tma_res, res_bufs, out_bufs;
   int PW, panels, pw_shift;
   uint32_t swz_mask;                 // 7 / 3 / 1 / 0 for 128 / 64 / 32 / 16-byte panel rows
   uint32_t out_stage_off, res_stage_off;  // byte offsets from the 1024-aligned smem base
@@ -105,8 +105,8 @@ __device__ __forceinline__ uint4 ld_shared_v4(uint32_t addr) {
 // 4 accumulators -> 4 packed int8, ARM rounding, activation in {relu, relu6}:
 // clamp(v, 0, hi) is ONE integer min-with-relu on the float bit pattern (positive
 // floats order like their bits, negative floats are negative ints), then
-// round-half-away of a non-negative value = floor(RZ(v + 0.5)) read from the
-// mantissa of RD(t + 2^23).  Bit-exact with common.cuh:round_sat_i8.
+// round-half-away of a non-negative value = floor(v + 0.5) read from the mantissa of
+// RD(v + 32768.5).  Bit-exact with common.cuh:round_sat_i8.
 template <bool RES>
 __device__ __forceinline__ uint32_t quad_i8_relu(const uint32_t* acc, float4 s, float4 b,
                                                  uint32_t hi_bits, uint32_t res_word, float res_scale) {
@@ -129,11 +129,15 @@ __device__ __forceinline__ uint32_t quad_i8_relu(const uint32_t* acc, float4 s, 
   const int c1 = __vimin_s32_relu(__float_as_int(v1), (int)hi_bits);
   const int c2 = __vimin_s32_relu(__float_as_int(v2), (int)hi_bits);
   const int c3 = __vimin_s32_relu(__float_as_int(v3), (int)hi_bits);
-  const uint64_t half = pk2(0.5f, 0.5f), big = pk2(8388608.f, 8388608.f);
-  const uint64_t u01 = fadd2_rm(fadd2_rz(pk2(__int_as_float(c0), __int_as_float(c1)), half), big);
-  const uint64_t u23 = fadd2_rm(fadd2_rz(pk2(__int_as_float(c2), __int_as_float(c3)), half), big);
-  const uint32_t p01 = prmt_((uint32_t)u01, (uint32_t)(u01 >> 32), 0x0040);
-  const uint32_t p23 = prmt_((uint32_t)u23, (uint32_t)(u23 >> 32), 0x0040);
+  // round-half-away of v in [0, 127] = floor(v + 0.5): ONE add, rounded down, to
+  // 2^15 + 0.5 lands in the binade with ulp 2^-8, so the integer part sits in byte 1 of
+  // the result (the exact sum is floored to a multiple of 2^-8, which never crosses an
+  // integer)
+  const uint64_t big = pk2(32768.5f, 32768.5f);
+  const uint64_t u01 = fadd2_rm(pk2(__int_as_float(c0), __int_as_float(c1)), big);
+  const uint64_t u23 = fadd2_rm(pk2(__int_as_float(c2), __int_as_float(c3)), big);
+  const uint32_t p01 = prmt_((uint32_t)u01, (uint32_t)(u01 >> 32), 0x0051);
+  const uint32_t p23 = prmt_((uint32_t)u23, (uint32_t)(u23 >> 32), 0x0051);
   return prmt_(p01, p23, 0x5410);
 }
 
@@ -144,15 +148,15 @@ __device__ __forceinline__ uint32_t quad_i8_signed(const uint32_t* acc, float4 s
   float v[4];
   upk2(v01, v[0], v[1]);
   upk2(v23, v[2], v[3]);
-  const uint64_t half = pk2(0.5f, 0.5f), big = pk2(8388608.f, 8388608.f);
-  const uint64_t u01 = fadd2_rm(fadd2_rz(pk2(fminf(fabsf(v[0]), 127.f), fminf(fabsf(v[1]), 127.f)), half), big);
-  const uint64_t u23 = fadd2_rm(fadd2_rz(pk2(fminf(fabsf(v[2]), 127.f), fminf(fabsf(v[3]), 127.f)), half), big);
+  const uint64_t big = pk2(32768.5f, 32768.5f);  // see quad_i8_relu: integer part lands in byte 1
+  const uint64_t u01 = fadd2_rm(pk2(fminf(fabsf(v[0]), 127.f), fminf(fabsf(v[1]), 127.f)), big);
+  const uint64_t u23 = fadd2_rm(pk2(fminf(fabsf(v[2]), 127.f), fminf(fabsf(v[3]), 127.f)), big);
   const uint32_t m[4] = {(uint32_t)u01, (uint32_t)(u01 >> 32), (uint32_t)u23, (uint32_t)(u23 >> 32)};
   uint32_t q[4];
 #pragma unroll
   for (int j = 0; j < 4; ++j) {
-    const int sg = __float_as_int(v[j]) >> 31;               // 0 or -1
-    q[j] = (uint32_t)((int)((m[j] & 0xffu) ^ (uint32_t)sg) - sg);  // conditional negate
+    const int sg = __float_as_int(v[j]) >> 31;                       // 0 or -1
+    q[j] = (uint32_t)((int)((m[j] >> 8) ^ (uint32_t)sg) - sg);       // conditional negate; low byte is the result
   }
   return prmt_(prmt_(q[0], q[1], 0x0040), prmt_(q[2], q[3], 0x0040), 0x5410);
 }
@@ -372,26 +376,30 @@ igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
     uint32_t aphase = 0;
     int rb = 0;
     uint32_t rphase = 0;
+    int ob = 0;
+    // scale / bias of a tile are staged in smem (double buffered) during the previous
+    // tile, so one barrier per tile orders both the staging and the TMA store
+    auto stage_scale_bias = [&](int t, int buf) {
+      if (etid < p.BN) {
+        const int n = (t % p.n_tiles) * p.BN + etid;
+        const bool ok = n < p.Nout && p.epi.scale != nullptr;
+        s_scale[buf][etid] = ok ? __ldg(p.epi.scale + n) : 0.f;
+        s_bias[buf][etid] = (ok && p.epi.bias) ? __ldg(p.epi.bias + n) : 0.f;
+      }
+    };
+    if ((int)blockIdx.x < num_tiles) stage_scale_bias(blockIdx.x, 0);
+    asm volatile("bar.sync 1, %0;" ::"n"(32 * kEpiWarps) : "memory");
     for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
       const int tn = tile % p.n_tiles, tm = tile / p.n_tiles;
       const long long row = (long long)tm * kBM + quarter * 32 + lane;
       const int n0 = tn * p.BN;
-      // stage this tile's scale / bias (buffer `as` was last read two tiles ago)
-      if (etid < p.BN) {
-        const int n = n0 + etid;
-        const bool ok = n < p.Nout && p.epi.scale != nullptr;
-        s_scale[as][etid] = ok ? __ldg(p.epi.scale + n) : 0.f;
-        s_bias[as][etid] = (ok && p.epi.bias) ? __ldg(p.epi.bias + n) : 0.f;
-      }
-      // the previous tile's TMA store must have drained the staging buffer
-      if (kFast && etid == 0) bulk_wait_group_read<0>();
-      asm volatile("bar.sync 1, %0;" ::"n"(32 * kEpiWarps) : "memory");
       if (EPI == EPI_I8_RELU_RES) mbar_wait(bar_rfull + 8 * rb, rphase);
       mbar_wait(bar_tfull + 8 * as, aphase);
       tc_fence_after();
       const uint32_t t_addr = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)as * p.acc_stride;
       const uint32_t res_base = smem_res + (uint32_t)rb * tile_bytes + rowoff;
-      const uint32_t out_base = smem_out + rowoff;
+      const uint32_t out_tile = smem_out + (uint32_t)ob * tile_bytes;
+      const uint32_t out_base = out_tile + rowoff;
       // TMEM reads are double buffered: unit i+1 is in flight while unit i runs through the ALUs
       uint32_t accb[2][16];
       if (cq < units) tmem_ld_32x32b_x16(t_addr + (uint32_t)(cq * 16), accb[0]);
@@ -436,14 +444,29 @@ igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
         mbar_arrive(bar_rempty + 8 * rb);
         if (++rb == p.res_bufs) { rb = 0; rphase ^= 1; }
       }
+      // next tile's scale / bias into the other buffer (last read one tile ago, before
+      // that tile's barrier)
+      if (tile + (int)gridDim.x < num_tiles) stage_scale_bias(tile + gridDim.x, as);
       if (kFast) {
+        // the store issued one tile ago has long drained its staging buffer: after the
+        // barrier every thread may write it again
+        if (etid == 0 && p.out_bufs == 2) bulk_wait_group_read<0>();
         // generic-proxy smem writes -> visible to the TMA engine, then one thread stores
         fence_proxy_async();
-        asm volatile("bar.sync 2, %0;" ::"n"(32 * kEpiWarps) : "memory");
+      }
+      asm volatile("bar.sync 2, %0;" ::"n"(32 * kEpiWarps) : "memory");
+      if (kFast) {
         if (etid == 0) {
           for (int j = 0; j < p.panels; ++j)
-            tma_store_2d(&tmap_y, smem_out + (uint32_t)(j * kBM * p.PW), n0 + j * p.PW, tm * kBM);
+            tma_store_2d(&tmap_y, out_tile + (uint32_t)(j * kBM * p.PW), n0 + j * p.PW, tm * kBM);
           bulk_commit_group();
+        }
+        if (p.out_bufs == 2) {
+          ob ^= 1;
+        } else {
+          // single staging buffer (smem-tight launches): drain it before the next tile
+          if (etid == 0) bulk_wait_group_read<0>();
+          asm volatile("bar.sync 1, %0;" ::"n"(32 * kEpiWarps) : "memory");
         }
       }
     }
@@ -674,37 +697,46 @@ int launch_igemm(const CUtensorMap& ta, const CUtensorMap& tb, IgemmParams& p, p
   p.swz_mask = p.PW == 128 ? 7u : (p.PW == 64 ? 3u : (p.PW == 32 ? 1u : 0u));
   p.tma_out = (epi != EPI_GENERIC);
   p.tma_res = p.tma_out && epi == EPI_I8_RELU_RES;
-  uint32_t extra = 0;
+  const int budget = 215 * 1024;
+  const int tile = kBM * p.BN;
+  const int stage_bytes = (int)(p.a_stage_bytes + p.b_stage_bytes);
+  p.out_bufs = 0;
+  p.res_bufs = 2;
+  int extra = 0;
   if (p.tma_out) {
     int rc = encode_2d(&ty, p.y, (uint64_t)p.Nout, (uint64_t)p.M, (uint64_t)p.ldy, p.PW, kBM);
     if (rc) return rc;
-    extra += (uint32_t)(kBM * p.BN);
     if (p.tma_res) {
       rc = encode_2d(&tr, e.residual, (uint64_t)p.Nout, (uint64_t)p.M, (uint64_t)e.ld_res, p.PW, kBM);
       if (rc) return rc;
     }
+    // shared-memory policy: at least min_stages mainloop stages, then a second staging
+    // buffer (the TMA store of tile i drains while tile i+1 is written), then a deeper
+    // residual ring, the rest goes back to the mainloop
+    const int min_stages = env_int("PL_IGEMM_MIN_STAGES", 3);
+    int left = budget - min_stages * stage_bytes - tile - (p.tma_res ? 2 * tile : 0);
+    if (left < 0) left = 0;
+    p.out_bufs = 1;
+    if (left >= tile && env_int("PL_IGEMM_OUT_BUFS", 2) >= 2) {
+      p.out_bufs = 2;
+      left -= tile;
+    }
+    if (p.tma_res) {
+      int want = env_int("PL_IGEMM_RES_BUFS", 3);
+      if (want > kMaxResBufs) want = kMaxResBufs;
+      while (p.res_bufs < want && left >= tile) {
+        ++p.res_bufs;
+        left -= tile;
+      }
+    }
+    extra = p.out_bufs * tile + (p.tma_res ? p.res_bufs * tile : 0);
   }
-  const int stage_bytes = (int)(p.a_stage_bytes + p.b_stage_bytes);
-  p.res_bufs = 2;
-  if (p.tma_res) {
-    // the residual is the biggest stream of an expand layer: keep enough tiles in
-    // flight to cover DRAM latency, but leave the mainloop at least 3 stages
-    const int tile = kBM * p.BN;
-    int want = env_int("PL_IGEMM_RES_BUFS", 4);
-    int fit = (215 * 1024 - (int)extra - 3 * stage_bytes) / tile;
-    if (fit < want) want = fit;
-    if (want > kMaxResBufs) want = kMaxResBufs;
-    if (want < 2) want = 2;
-    p.res_bufs = want;
-    extra += (uint32_t)(want * tile);
-  }
-  const int smem_budget = 215 * 1024 - (int)extra;
-  int stages = smem_budget / stage_bytes;
+  int stages = (budget - extra) / stage_bytes;
   if (stages > kMaxStages) stages = kMaxStages;
   if (stages < 2) return PL_ERR_UNSUPPORTED;
   p.stages = stages;
   p.out_stage_off = (uint32_t)(stages * stage_bytes);
-  p.res_stage_off = p.out_stage_off + (uint32_t)(kBM * p.BN);
+  p.res_stage_off = p.out_stage_off + (uint32_t)(p.out_bufs * tile);
   const size_t smem = (size_t)stages * stage_bytes + extra + 1024;
   switch (epi) {
     case EPI_I8_RELU: return launch_one<EPI_I8_RELU>(ta, tb, ty, tr, p, grid, smem, stream);
@@ -722,18 +754,27 @@ int check_epi(const pl_epilogue* e) {
   return PL_OK;
 }
 
-int common_setup(IgemmParams& p, long long M, int Nout, void* y, int ldy, const pl_epilogue* e) {
+// p.BK holds the packing K-block of the reduction dim (pl_conv_block_k); the launch may
+// use a smaller one (the packed rows are plain zero-padded K-major bytes)
+int common_setup(IgemmParams& p, long long M, int Nout, void* y, int ldy, const pl_epilogue* e, int Kc,
+                 int taps) {
   if (M <= 0 || Nout <= 0 || M > 0x7fffffffLL) return PL_ERR_ARG;
+  const int cpad = (Kc + p.BK - 1) / p.BK * p.BK;
   p.M = (int)M;
   p.Nout = Nout;
   p.m_tiles = (int)((M + kBM - 1) / kBM);
   p.BN = pick_bn(Nout, p.m_tiles, driver().sm_count);
-  // fused-residual launches are bandwidth bound: narrower tiles leave shared memory
-  // for a deeper residual ring
   if (e->residual) {
-    const int cap = env_int("PL_IGEMM_RES_BN", 128);
+    // fused-residual launches are bandwidth bound and need smem for the residual ring and
+    // the staging buffers: thin reductions take a finer K-block so that three mainloop
+    // stages still fit beside them (measured on B200: tools/gpu_sweep_res.sh)
+    const int cap = env_int("PL_IGEMM_RES_BN", 256);
     while (p.BN > cap && p.BN > 16) p.BN >>= 1;
+    const int bk_cap = env_int("PL_IGEMM_RES_BK", cpad <= 128 ? 64 : 128);
+    while (p.BK > bk_cap && p.BK > 32) p.BK >>= 1;
   }
+  p.cblocks = cpad / p.BK;
+  p.num_kb = taps * p.cblocks;
   p.n_tiles = (Nout + p.BN - 1) / p.BN;
   p.a_stage_bytes = (uint32_t)(kBM * p.BK);
   p.b_stage_bytes = (uint32_t)((p.BN * p.BK + 1023) / 1024 * 1024);
@@ -802,9 +843,8 @@ extern "C" int pl_conv2d_i8_nhwc(const int8_t* x, const int8_t* w_packed, void* 
 
   IgemmParams p{};
   p.BK = pl_conv_block_k(d->C);
-  p.cblocks = (d->C + p.BK - 1) / p.BK;
-  p.num_kb = d->R * d->S * p.cblocks;
-  rc = common_setup(p, (long long)d->N * P * Q, d->K, y, d->ldy, e);
+  const int cpad = (d->C + p.BK - 1) / p.BK * p.BK;
+  rc = common_setup(p, (long long)d->N * P * Q, d->K, y, d->ldy, e, d->C, d->R * d->S);
   if (rc) return rc;
   const bool as_gemm = d->R == 1 && d->S == 1 && d->stride_h == 1 && d->stride_w == 1 &&
                        d->pad_t == 0 && d->pad_b == 0 && d->pad_l == 0 && d->pad_r == 0;
@@ -826,7 +866,7 @@ extern "C" int pl_conv2d_i8_nhwc(const int8_t* x, const int8_t* w_packed, void* 
     rc = encode_im2col(&ta, x, d, p.BK);
   }
   if (rc) return rc;
-  const uint64_t wrow = (uint64_t)d->R * d->S * p.cblocks * p.BK;
+  const uint64_t wrow = (uint64_t)d->R * d->S * cpad;
   rc = encode_2d(&tb, w_packed, wrow, (uint64_t)d->K, wrow, p.BK, p.BN);
   if (rc) return rc;
   return launch_igemm(ta, tb, p, stream);
@@ -845,10 +885,8 @@ extern "C" int pl_gemm_i8(const int8_t* A, int lda, const int8_t* Bt, int ldb, v
     return PL_ERR_ALIGN;
   IgemmParams p{};
   p.BK = pl_conv_block_k(K);
-  p.cblocks = (K + p.BK - 1) / p.BK;
-  p.num_kb = p.cblocks;
   p.mode = 0;
-  rc = common_setup(p, M, N, C, ldc, e);
+  rc = common_setup(p, M, N, C, ldc, e, K, 1);
   if (rc) return rc;
   CUtensorMap ta, tb;
   rc = encode_2d(&ta, A, (uint64_t)K, (uint64_t)M, (uint64_t)lda, p.BK, kBM);
