@@ -76,6 +76,31 @@ __device__ __forceinline__ float small_int2float(int acc) {
   return __fadd_rn(__int_as_float(acc + 0x4B400000), -12582912.f);
 }
 
+// division by a launch-time constant: Granlund-Montgomery round-up magic
+struct FastDiv {  // q = (n * mul) >> (32 + sh), exact for n < 2^31 (round-up magic)
+  uint32_t mul, sh, d;
+};
+static inline FastDiv make_fastdiv(uint32_t d) {
+  FastDiv f;
+  f.d = d;
+  if (d == 1) {
+    f.mul = 0;
+    f.sh = 0;
+    return f;
+  }
+  uint32_t l = 0;
+  while ((1u << l) < d) ++l;  // ceil(log2 d)
+  const uint64_t m = ((1ull << (32 + l)) + d - 1) / d;  // 33-bit magic, top bit implicit
+  f.mul = (uint32_t)(m - (1ull << 32));
+  f.sh = l;
+  return f;
+}
+__device__ __forceinline__ uint32_t fdiv(uint32_t n, const FastDiv f) {
+  if (f.d == 1) return n;
+  const uint32_t t = __umulhi(n, f.mul);
+  return (t + ((n - t) >> 1)) >> (f.sh - 1);
+}
+
 struct EpiParams {
   const float* scale;
   const float* bias;

@@ -7,13 +7,7 @@
 // conv5x5s{1,2}_depthwise_int8.cc: exact int32 accumulation, then the common
 // epilogue (common.cuh).  Filter layout as the reference stores it: [C][R][S].
 //
-// Fast path (3x3, stride 1 or 2, dilation 1): one thread owns 4 channels (one
-// 32-bit word per pixel, so a warp reads 128 contiguous bytes) and two adjacent
-// output columns.  The 4 (s1) or 5 (s2) input words of a filter row are byte
-// transposed with 8 PRMTs into one word per channel holding 4 consecutive
-// columns; a 3-tap row of the filter is then ONE dp4a against a pre-shifted
-// weight word.  Filter words, scale and bias live in registers for the whole
-// grid-stride loop.
+// Fast path (3x3, stride 1 or 2, dilation 1): see dw3x3s1_kernel / dw3x3s2_kernel.
 // Generic path (any R,S,stride,dilation): one dp4a per MAC against a byte-masked
 // weight word.
 #include "common.cuh"
@@ -27,8 +21,12 @@ struct DwParams {
   int N, H, W, C, ldx, ldy, P, Q;
   int R, S, sh, sw, pt, pl_, dh, dw;
   int CG;       // channel groups of 4
-  long long npairs;  // N * P * ceil(Q/2)   (fast path)
   long long npix;    // N * P * Q           (generic path)
+  long long items;   // fast path: N * bands * strips * CG work items
+  int strips, bands;
+  FastDiv dCG, dStrips, dBands;
+  int ldxw, rowpitch_w;  // pixel / row pitch of the input in 32-bit words
+  uint32_t hi_bits;  // float bits of the upper clamp (fast int8 relu epilogue)
   EpiParams epi;
 };
 
@@ -78,86 +76,279 @@ __device__ __forceinline__ void dw_store4(const DwParams& p, const int (&acc)[4]
 }
 
 // ---------------------------------------------------------------------------
-// fast path: 3x3, stride STRIDE in {1,2}, dilation 1
-// block = (CGB channel groups) x (256/CGB pixel pairs); grid.y = channel-group blocks
+// fast path: 3x3, dilation 1, stride 1 or 2.
+//
+// One thread = one work item = 4 channels x (RB output rows) x (T output columns),
+// T = 4 (stride 1) or 2 (stride 2).  Consecutive lanes take consecutive channel quads,
+// so every warp-level 32-bit load/store covers up to 128 contiguous bytes of a pixel.
+// All input words of the item are requested up front (memory-level parallelism comes
+// from the loads in flight, not from occupancy); each 4-pixel row segment is byte
+// transposed ONCE (8 PRMT) and then reused by the three filter rows, so a 3-tap filter
+// row costs one dp4a per output and channel.  The accumulators start at the float
+// magic 0x4B400000, which makes int -> float a single (packed) add.
 // ---------------------------------------------------------------------------
-template <int STRIDE>
-__global__ void __launch_bounds__(256) dw3x3_kernel(const DwParams p, int CGB) {
-  const int cg = blockIdx.y * CGB + (threadIdx.x % CGB);
-  const int pslot = threadIdx.x / CGB;
-  const int pper = 256 / CGB;
-  if (cg >= p.CG) return;
-  const int c0 = cg * 4;
+__device__ __forceinline__ uint64_t dw_pk2(float a, float b) {
+  uint64_t r;
+  asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(a), "f"(b));
+  return r;
+}
+__device__ __forceinline__ void dw_upk2(uint64_t v, float& a, float& b) {
+  asm("mov.b64 {%0, %1}, %2;" : "=f"(a), "=f"(b) : "l"(v));
+}
+__device__ __forceinline__ uint64_t dw_ffma2(uint64_t a, uint64_t b, uint64_t c) {
+  uint64_t d;
+  asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(b), "l"(c));
+  return d;
+}
+__device__ __forceinline__ uint64_t dw_fadd2_rn(uint64_t a, uint64_t b) {
+  uint64_t d;
+  asm("add.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
+  return d;
+}
+__device__ __forceinline__ uint64_t dw_fadd2_rm(uint64_t a, uint64_t b) {
+  uint64_t d;
+  asm("add.rm.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
+  return d;
+}
 
-  // filter words: wa[r][c] = {w0,w1,w2,0}; wb = taps shifted for the 2nd column
-  // (s1: {0,w0,w1,w2}; s2: {0,0,w0,w1} plus w2 against the 5th word).
-  uint32_t wa[3][4], wb[3][4], wc[3][4];
-  float sc[4], bs[4];
+static constexpr int kDwMagic = 0x4B400000;  // float 12582912 = 1.5 * 2^23
+
+// 4x4 byte transpose: t[c] = {x0.c, x1.c, x2.c, x3.c}
+__device__ __forceinline__ void dw_transpose(uint32_t x0, uint32_t x1, uint32_t x2, uint32_t x3, uint32_t (&t)[4]) {
+  const uint32_t a = prmt(x0, x1, 0x5140), b = prmt(x2, x3, 0x5140);
+  const uint32_t c = prmt(x0, x1, 0x7362), d = prmt(x2, x3, 0x7362);
+  t[0] = prmt(a, b, 0x5410);
+  t[1] = prmt(a, b, 0x7632);
+  t[2] = prmt(c, d, 0x5410);
+  t[3] = prmt(c, d, 0x7632);
+}
+
+// epilogue of 4 channels of one output pixel (accumulators carry the magic offset).
+// FAST: int8 out, ARM rounding, relu / relu6 (hi_bits = float bits of the upper clamp).
+template <bool FAST>
+__device__ __forceinline__ void dw_finish4(const DwParams& p, const int (&acc)[4], const float4 sc, const float4 bs,
+                                           uint32_t hi_bits, long long pix, int c0) {
+  if (FAST) {
+    const uint64_t off = dw_pk2(-12582912.f, -12582912.f);
+    const uint64_t f01 = dw_fadd2_rn(dw_pk2(__int_as_float(acc[0]), __int_as_float(acc[1])), off);
+    const uint64_t f23 = dw_fadd2_rn(dw_pk2(__int_as_float(acc[2]), __int_as_float(acc[3])), off);
+    const uint64_t v01 = dw_ffma2(f01, dw_pk2(sc.x, sc.y), dw_pk2(bs.x, bs.y));
+    const uint64_t v23 = dw_ffma2(f23, dw_pk2(sc.z, sc.w), dw_pk2(bs.z, bs.w));
+    float v0, v1, v2, v3;
+    dw_upk2(v01, v0, v1);
+    dw_upk2(v23, v2, v3);
+    // clamp to [0, hi] on the float bit pattern, then floor(v + 0.5) from byte 1 of
+    // RD(v + 32768.5) (see igemm_i8.cu:quad_i8_relu)
+    const int c0_ = __vimin_s32_relu(__float_as_int(v0), (int)hi_bits);
+    const int c1_ = __vimin_s32_relu(__float_as_int(v1), (int)hi_bits);
+    const int c2_ = __vimin_s32_relu(__float_as_int(v2), (int)hi_bits);
+    const int c3_ = __vimin_s32_relu(__float_as_int(v3), (int)hi_bits);
+    const uint64_t big = dw_pk2(32768.5f, 32768.5f);
+    const uint64_t u01 = dw_fadd2_rm(dw_pk2(__int_as_float(c0_), __int_as_float(c1_)), big);
+    const uint64_t u23 = dw_fadd2_rm(dw_pk2(__int_as_float(c2_), __int_as_float(c3_)), big);
+    const uint32_t p01 = prmt((uint32_t)u01, (uint32_t)(u01 >> 32), 0x0051);
+    const uint32_t p23 = prmt((uint32_t)u23, (uint32_t)(u23 >> 32), 0x0051);
+    *reinterpret_cast<uint32_t*>(reinterpret_cast<int8_t*>(p.y) + pix * p.ldy + c0) = prmt(p01, p23, 0x5410);
+  } else {
+    const int raw[4] = {acc[0] - kDwMagic, acc[1] - kDwMagic, acc[2] - kDwMagic, acc[3] - kDwMagic};
+    const float s4[4] = {sc.x, sc.y, sc.z, sc.w}, b4[4] = {bs.x, bs.y, bs.z, bs.w};
+    dw_store4(p, raw, s4, b4, pix, c0);
+  }
+}
+
+struct DwItem {
+  int n, p0, q0, c0;
+};
+
+__device__ __forceinline__ DwItem dw_item(const DwParams& p, uint32_t idx, int RB, int T) {
+  DwItem it;
+  uint32_t rest = fdiv(idx, p.dCG);
+  it.c0 = (int)(idx - rest * p.dCG.d) * 4;
+  uint32_t t = fdiv(rest, p.dStrips);
+  it.q0 = (int)(rest - t * p.dStrips.d) * T;
+  rest = t;
+  t = fdiv(rest, p.dBands);
+  it.p0 = (int)(rest - t * p.dBands.d) * RB;
+  it.n = (int)t;
+  return it;
+}
+
+// filter words of 4 channels: the reference layout [C][3][3] makes them 36 contiguous,
+// 4-byte aligned bytes.  wa[r][j] = {w0, w1, w2, 0} of channel c0+j, filter row r.
+__device__ __forceinline__ void dw_load_filter(const DwParams& p, int c0, uint32_t (&wa)[3][4]) {
+  if (c0 + 4 <= p.C && (reinterpret_cast<uintptr_t>(p.w) & 3) == 0) {
+    uint32_t w[10];
+#pragma unroll
+    for (int i = 0; i < 9; ++i) w[i] = __ldg(reinterpret_cast<const uint32_t*>(p.w + (long long)c0 * 9) + i);
+    w[9] = 0;
+#pragma unroll
+    for (int j = 0; j < 4; ++j)
+#pragma unroll
+      for (int r = 0; r < 3; ++r) {
+        const int byte = j * 9 + r * 3, k = byte >> 2, sh = byte & 3;
+        // bytes sh, sh+1, sh+2 of the pair (w[k], w[k+1])
+        const uint32_t sel = (uint32_t)(sh | ((sh + 1) << 4) | ((sh + 2) << 8) | ((sh + 3) << 12));
+        wa[r][j] = prmt(w[k], w[k + 1], sel) & 0x00ffffffu;
+      }
+  } else {
+#pragma unroll
+    for (int j = 0; j < 4; ++j)
+#pragma unroll
+      for (int r = 0; r < 3; ++r) {
+        uint32_t v = 0;
+        if (c0 + j < p.C) {
+          const int8_t* wp = p.w + (long long)(c0 + j) * 9 + r * 3;
+          v = (uint32_t)(uint8_t)__ldg(wp) | ((uint32_t)(uint8_t)__ldg(wp + 1) << 8) |
+              ((uint32_t)(uint8_t)__ldg(wp + 2) << 16);
+        }
+        wa[r][j] = v;
+      }
+  }
+}
+
+__device__ __forceinline__ void dw_load_scale_bias(const DwParams& p, int c0, float4& sc, float4& bs) {
+  float s[4], b[4];
 #pragma unroll
   for (int j = 0; j < 4; ++j) {
-    const int c = c0 + j;
-    const bool ok = c < p.C;
-    sc[j] = (ok && p.epi.scale) ? __ldg(p.epi.scale + c) : 0.f;
-    bs[j] = (ok && p.epi.bias) ? __ldg(p.epi.bias + c) : 0.f;
+    const bool ok = c0 + j < p.C;
+    s[j] = (ok && p.epi.scale) ? __ldg(p.epi.scale + c0 + j) : 0.f;
+    b[j] = (ok && p.epi.bias) ? __ldg(p.epi.bias + c0 + j) : 0.f;
+  }
+  sc = make_float4(s[0], s[1], s[2], s[3]);
+  bs = make_float4(b[0], b[1], b[2], b[3]);
+}
+
+// window geometry shared by both strides: clamped word offsets of the NC window columns
+// plus an all-ones / all-zeros mask per column (zero padding = load a valid neighbour,
+// then AND it away; one LOP3 per word also applies the row mask)
+template <int NC>
+__device__ __forceinline__ void dw_columns(const DwParams& p, int iw0, int (&colw)[NC], uint32_t (&cm)[NC]) {
+#pragma unroll
+  for (int k = 0; k < NC; ++k) {
+    const int iw = iw0 + k;
+    const int c = min(max(iw, 0), p.W - 1);
+    colw[k] = c * p.ldxw;
+    cm[k] = (iw == c) ? 0xffffffffu : 0u;
+  }
+}
+
+// ---- stride 1: T = 4 output columns, RB output rows, window (RB+2) x 6 words ----
+template <int RB, bool FAST>
+__global__ void __launch_bounds__(256, RB <= 2 ? 4 : 2) dw3x3s1_kernel(const DwParams p) {
+  const uint32_t idx = blockIdx.x * 256u + threadIdx.x;
+  if (idx >= (uint32_t)p.items) return;
+  const DwItem it = dw_item(p, idx, RB, 4);
+  const int c0 = it.c0;
+  const int ih0 = it.p0 - p.pt;
+  int colw[6];
+  uint32_t cm[6];
+  dw_columns<6>(p, it.q0 - p.pl_, colw, cm);
+  const uint32_t* img = reinterpret_cast<const uint32_t*>(p.x + c0) + (long long)it.n * p.H * p.rowpitch_w;
+  uint32_t wa[3][4];
+  dw_load_filter(p, c0, wa);
+  int acc[RB][4][4];
+#pragma unroll
+  for (int o = 0; o < RB; ++o)
+#pragma unroll
+    for (int q = 0; q < 4; ++q)
+#pragma unroll
+      for (int j = 0; j < 4; ++j) acc[o][q][j] = kDwMagic;
+#pragma unroll
+  for (int i = 0; i < RB + 2; ++i) {
+    const int ih = ih0 + i;
+    const int ihc = min(max(ih, 0), p.H - 1);
+    const uint32_t rm = (ih == ihc) ? 0xffffffffu : 0u;
+    const uint32_t* row = img + (long long)ihc * p.rowpitch_w;
+    uint32_t xw[6];
+#pragma unroll
+    for (int k = 0; k < 6; ++k) xw[k] = __ldg(row + colw[k]) & cm[k] & rm;
+    uint32_t ta[4], tb[4];
+    dw_transpose(xw[0], xw[1], xw[2], xw[3], ta);  // columns 0..3 -> outputs 0, 1
+    dw_transpose(xw[2], xw[3], xw[4], xw[5], tb);  // columns 2..5 -> outputs 2, 3
 #pragma unroll
     for (int r = 0; r < 3; ++r) {
-      uint32_t w0 = 0, w1 = 0, w2 = 0;
-      if (ok) {
-        const int8_t* wp = p.w + (long long)c * 9 + r * 3;
-        w0 = (uint8_t)__ldg(wp);
-        w1 = (uint8_t)__ldg(wp + 1);
-        w2 = (uint8_t)__ldg(wp + 2);
-      }
-      wa[r][j] = w0 | (w1 << 8) | (w2 << 16);
-      if (STRIDE == 1) {
-        wb[r][j] = (w0 << 8) | (w1 << 16) | (w2 << 24);
-        wc[r][j] = 0;
-      } else {
-        wb[r][j] = (w0 << 16) | (w1 << 24);
-        wc[r][j] = w2 << (8 * j);  // masked: picks channel j of the raw 5th word
+      const int o = i - r;
+      if (o < 0 || o >= RB) continue;
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const int w0 = (int)wa[r][j], w1 = (int)(wa[r][j] << 8);
+        acc[o][0][j] = __dp4a((int)ta[j], w0, acc[o][0][j]);
+        acc[o][1][j] = __dp4a((int)ta[j], w1, acc[o][1][j]);
+        acc[o][2][j] = __dp4a((int)tb[j], w0, acc[o][2][j]);
+        acc[o][3][j] = __dp4a((int)tb[j], w1, acc[o][3][j]);
       }
     }
   }
+  float4 sc, bs;
+  dw_load_scale_bias(p, c0, sc, bs);
+#pragma unroll
+  for (int o = 0; o < RB; ++o) {
+    const int op = it.p0 + o;
+    if (op >= p.P) break;
+    const long long pix = ((long long)it.n * p.P + op) * p.Q + it.q0;
+#pragma unroll
+    for (int q = 0; q < 4; ++q)
+      if (it.q0 + q < p.Q) dw_finish4<FAST>(p, acc[o][q], sc, bs, p.hi_bits, pix + q, c0);
+  }
+}
 
-  const int Q2 = (p.Q + 1) >> 1;
-  for (long long pp = (long long)blockIdx.x * pper + pslot; pp < p.npairs;
-       pp += (long long)gridDim.x * pper) {
-    const int q0 = (int)(pp % Q2) * 2;
-    const long long t = pp / Q2;
-    const int op = (int)(t % p.P);
-    const int n = (int)(t / p.P);
-    const int iw0 = q0 * STRIDE - p.pl_;
-    const int ih0 = op * STRIDE - p.pt;
-    int acc0[4] = {0, 0, 0, 0}, acc1[4] = {0, 0, 0, 0};
+// ---- stride 2: T = 2 output columns, RB output rows, window (2*RB+1) x 5 words ----
+template <int RB, bool FAST>
+__global__ void __launch_bounds__(256, 4) dw3x3s2_kernel(const DwParams p) {
+  const uint32_t idx = blockIdx.x * 256u + threadIdx.x;
+  if (idx >= (uint32_t)p.items) return;
+  const DwItem it = dw_item(p, idx, RB, 2);
+  const int c0 = it.c0;
+  const int ih0 = it.p0 * 2 - p.pt;
+  int colw[5];
+  uint32_t cm[5];
+  dw_columns<5>(p, it.q0 * 2 - p.pl_, colw, cm);
+  const uint32_t* img = reinterpret_cast<const uint32_t*>(p.x + c0) + (long long)it.n * p.H * p.rowpitch_w;
+  uint32_t wa[3][4];
+  dw_load_filter(p, c0, wa);
+  constexpr int NR = 2 * RB + 1;
+  int acc[RB][2][4];
+#pragma unroll
+  for (int o = 0; o < RB; ++o)
+#pragma unroll
+    for (int q = 0; q < 2; ++q)
+#pragma unroll
+      for (int j = 0; j < 4; ++j) acc[o][q][j] = kDwMagic;
+#pragma unroll
+  for (int i = 0; i < NR; ++i) {
+    const int ih = ih0 + i;
+    const int ihc = min(max(ih, 0), p.H - 1);
+    const uint32_t rm = (ih == ihc) ? 0xffffffffu : 0u;
+    const uint32_t* row = img + (long long)ihc * p.rowpitch_w;
+    uint32_t xw[5];
+#pragma unroll
+    for (int k = 0; k < 5; ++k) xw[k] = __ldg(row + colw[k]) & cm[k] & rm;
+    uint32_t ta[4];
+    dw_transpose(xw[0], xw[1], xw[2], xw[3], ta);
 #pragma unroll
     for (int r = 0; r < 3; ++r) {
-      const int ih = ih0 + r;
-      if (ih < 0 || ih >= p.H) continue;
-      const int8_t* row = p.x + ((long long)n * p.H + ih) * p.W * p.ldx + c0;
-      uint32_t xw[5];
-#pragma unroll
-      for (int i = 0; i < (STRIDE == 1 ? 4 : 5); ++i) {
-        const int iw = iw0 + i;
-        xw[i] = (iw >= 0 && iw < p.W) ? ldg_u32(row + (long long)iw * p.ldx) : 0u;
-      }
-      // 4x4 byte transpose: t[c] = {x0.c, x1.c, x2.c, x3.c}
-      const uint32_t a = prmt(xw[0], xw[1], 0x5140), b = prmt(xw[2], xw[3], 0x5140);
-      const uint32_t c_ = prmt(xw[0], xw[1], 0x7362), d = prmt(xw[2], xw[3], 0x7362);
-      uint32_t tr[4];
-      tr[0] = prmt(a, b, 0x5410);
-      tr[1] = prmt(a, b, 0x7632);
-      tr[2] = prmt(c_, d, 0x5410);
-      tr[3] = prmt(c_, d, 0x7632);
+      if (((i - r) & 1) != 0 || i - r < 0) continue;
+      const int o = (i - r) >> 1;
+      if (o >= RB) continue;
 #pragma unroll
       for (int j = 0; j < 4; ++j) {
-        acc0[j] = __dp4a((int)tr[j], (int)wa[r][j], acc0[j]);
-        acc1[j] = __dp4a((int)tr[j], (int)wb[r][j], acc1[j]);
-        if (STRIDE == 2) acc1[j] = __dp4a((int)xw[4], (int)wc[r][j], acc1[j]);
+        // output 0: columns 0,1,2; output 1: columns 2,3 of the transposed word + column 4
+        acc[o][0][j] = __dp4a((int)ta[j], (int)wa[r][j], acc[o][0][j]);
+        acc[o][1][j] = __dp4a((int)ta[j], (int)(wa[r][j] << 16), acc[o][1][j]);
+        acc[o][1][j] = __dp4a((int)xw[4], (int)(((wa[r][j] >> 16) & 0xffu) << (8 * j)), acc[o][1][j]);
       }
     }
-    const long long pix = ((long long)n * p.P + op) * p.Q + q0;
-    dw_store4(p, acc0, sc, bs, pix, c0);
-    if (q0 + 1 < p.Q) dw_store4(p, acc1, sc, bs, pix + 1, c0);
+  }
+  float4 sc, bs;
+  dw_load_scale_bias(p, c0, sc, bs);
+#pragma unroll
+  for (int o = 0; o < RB; ++o) {
+    const int op = it.p0 + o;
+    if (op >= p.P) break;
+    const long long pix = ((long long)it.n * p.P + op) * p.Q + it.q0;
+#pragma unroll
+    for (int q = 0; q < 2; ++q)
+      if (it.q0 + q < p.Q) dw_finish4<FAST>(p, acc[o][q], sc, bs, p.hi_bits, pix + q, c0);
   }
 }
 
@@ -238,31 +429,67 @@ extern "C" int pl_dwconv2d_i8_nhwc(const int8_t* x, const int8_t* w_crs, void* y
   p.dh = d->dil_h; p.dw = d->dil_w;
   p.CG = (d->C + 3) / 4;
   p.npix = (long long)d->N * P * Q;
-  p.npairs = (long long)d->N * P * ((Q + 1) / 2);
   p.epi = make_epi(e, d->C);
   if (e->residual) return PL_ERR_UNSUPPORTED;
 
-  int CGB = 1;
-  while (CGB < p.CG && CGB < 256) CGB <<= 1;
-  const int pper = 256 / CGB;
-  const int gy = (p.CG + CGB - 1) / CGB;
   const bool aligned = ((reinterpret_cast<uintptr_t>(x) & 3) == 0) && (d->ldx % 4 == 0);
   const bool fast = aligned && d->R == 3 && d->S == 3 && d->dil_h == 1 && d->dil_w == 1 &&
                     d->stride_h == d->stride_w && (d->stride_h == 1 || d->stride_h == 2);
   int dev = 0, sms = 148;
   cudaGetDevice(&dev);
   cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-  const long long items = fast ? p.npairs : p.npix;
-  long long gx = (items + pper - 1) / pper;
-  const long long cap = (long long)sms * 8 / gy > 0 ? (long long)sms * 8 / gy : 1;
-  if (gx > cap) gx = cap;
-  dim3 grid((unsigned)gx, (unsigned)gy);
-  if (fast && d->stride_h == 1)
-    dw3x3_kernel<1><<<grid, 256, 0, (cudaStream_t)stream>>>(p, CGB);
-  else if (fast)
-    dw3x3_kernel<2><<<grid, 256, 0, (cudaStream_t)stream>>>(p, CGB);
-  else
-    dw_generic_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(p, CGB, aligned ? 1 : 0);
+  cudaStream_t st = (cudaStream_t)stream;
+  if (fast) {
+    // specialised epilogue: int8 out, ARM rounding, relu / relu6 with a positive clamp,
+    // whole channel quads and word-aligned output pixels
+    bool fe = e->out_dtype == PL_OUT_INT8 && e->round_mode == PL_ROUND_ARM && e->scale &&
+              (e->act == PL_ACT_RELU || e->act == PL_ACT_RELU6) && d->C % 4 == 0 && d->ldy % 4 == 0 &&
+              (reinterpret_cast<uintptr_t>(y) & 3) == 0;
+    float hi = 127.f;
+    if (e->act == PL_ACT_RELU6 && e->act_arg < hi) hi = e->act_arg;
+    if (!(hi > 0.f)) fe = false;
+    union { float f; uint32_t u; } cv;
+    cv.f = hi;
+    p.hi_bits = cv.u;
+    const int s1 = d->stride_h == 1;
+    const int T = s1 ? 4 : 2;
+    p.strips = (Q + T - 1) / T;
+    // taller bands reuse more rows per thread; keep at least ~2 full waves of threads
+    auto items_for = [&](int rb) { return (long long)d->N * ((P + rb - 1) / rb) * p.strips * p.CG; };
+    int RB = 2;
+    if (s1 && items_for(4) >= (long long)sms * 2048 * 2) RB = 4;
+    p.bands = (P + RB - 1) / RB;
+    p.items = items_for(RB);
+    if (p.items >= (1ll << 31) || (long long)d->N * d->H * d->W * d->ldx >= (1ll << 33)) return PL_ERR_UNSUPPORTED;
+    p.dCG = make_fastdiv((uint32_t)p.CG);
+    p.dStrips = make_fastdiv((uint32_t)p.strips);
+    p.dBands = make_fastdiv((uint32_t)p.bands);
+    p.ldxw = d->ldx / 4;
+    p.rowpitch_w = d->W * p.ldxw;
+    const unsigned grid = (unsigned)((p.items + 255) / 256);
+    if (s1) {
+      if (RB == 4) {
+        if (fe) dw3x3s1_kernel<4, true><<<grid, 256, 0, st>>>(p);
+        else dw3x3s1_kernel<4, false><<<grid, 256, 0, st>>>(p);
+      } else {
+        if (fe) dw3x3s1_kernel<2, true><<<grid, 256, 0, st>>>(p);
+        else dw3x3s1_kernel<2, false><<<grid, 256, 0, st>>>(p);
+      }
+    } else {
+      if (fe) dw3x3s2_kernel<2, true><<<grid, 256, 0, st>>>(p);
+      else dw3x3s2_kernel<2, false><<<grid, 256, 0, st>>>(p);
+    }
+  } else {
+    int CGB = 1;
+    while (CGB < p.CG && CGB < 256) CGB <<= 1;
+    const int pper = 256 / CGB;
+    const int gy = (p.CG + CGB - 1) / CGB;
+    long long gx = (p.npix + pper - 1) / pper;
+    const long long cap = (long long)sms * 8 / gy > 0 ? (long long)sms * 8 / gy : 1;
+    if (gx > cap) gx = cap;
+    dim3 grid((unsigned)gx, (unsigned)gy);
+    dw_generic_kernel<<<grid, 256, 0, st>>>(p, CGB, aligned ? 1 : 0);
+  }
   ++g_launches;
   return launch_status();
 }

@@ -164,30 +164,6 @@ quant_nchw_to_nhwc_kernel(const float* __restrict__ x, int8_t* __restrict__ y, i
 // the [R*S*cw*4, ldA) pad.  One thread produces 16 output bytes (4 words).  The conv
 // then runs as a plain tensor-core GEMM with fat 128-byte K rows instead of 49 TMA
 // im2col loads of 16 useful bytes each.
-struct FastDiv {  // q = (n * mul) >> (32 + sh), exact for n < 2^31 (round-up magic)
-  uint32_t mul, sh, d;
-};
-static inline FastDiv make_fastdiv(uint32_t d) {
-  FastDiv f;
-  f.d = d;
-  if (d == 1) {
-    f.mul = 0;
-    f.sh = 0;
-    return f;
-  }
-  uint32_t l = 0;
-  while ((1u << l) < d) ++l;  // ceil(log2 d)
-  const uint64_t m = ((1ull << (32 + l)) + d - 1) / d;  // 33-bit magic, top bit implicit
-  f.mul = (uint32_t)(m - (1ull << 32));
-  f.sh = l;
-  return f;
-}
-__device__ __forceinline__ uint32_t fdiv(uint32_t n, const FastDiv f) {
-  if (f.d == 1) return n;
-  const uint32_t t = __umulhi(n, f.mul);
-  return (t + ((n - t) >> 1)) >> (f.sh - 1);
-}
-
 __global__ void __launch_bounds__(256)
 im2col_words_kernel(const uint32_t* __restrict__ x, uint4* __restrict__ A, int H, int W, int ldxw,
                     int cw, int S, int sh, int sw, int pt, int pl_, int dh, int dw, FastDiv dP, FastDiv dQ,
