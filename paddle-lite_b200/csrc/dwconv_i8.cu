@@ -127,7 +127,7 @@ __device__ __forceinline__ void dw_transpose(uint32_t x0, uint32_t x1, uint32_t 
 // FAST: int8 out, ARM rounding, relu / relu6 (hi_bits = float bits of the upper clamp).
 template <bool FAST>
 __device__ __forceinline__ void dw_finish4(const DwParams& p, const int (&acc)[4], const float4 sc, const float4 bs,
-                                           uint32_t hi_bits, long long pix, int c0) {
+                                           uint32_t hi_bits, uint32_t pix, int c0) {
   if (FAST) {
     const uint64_t off = dw_pk2(-12582912.f, -12582912.f);
     const uint64_t f01 = dw_fadd2_rn(dw_pk2(__int_as_float(acc[0]), __int_as_float(acc[1])), off);
@@ -148,11 +148,12 @@ __device__ __forceinline__ void dw_finish4(const DwParams& p, const int (&acc)[4
     const uint64_t u23 = dw_fadd2_rm(dw_pk2(__int_as_float(c2_), __int_as_float(c3_)), big);
     const uint32_t p01 = prmt((uint32_t)u01, (uint32_t)(u01 >> 32), 0x0051);
     const uint32_t p23 = prmt((uint32_t)u23, (uint32_t)(u23 >> 32), 0x0051);
-    *reinterpret_cast<uint32_t*>(reinterpret_cast<int8_t*>(p.y) + pix * p.ldy + c0) = prmt(p01, p23, 0x5410);
+    // FAST launches have ldy % 4 == 0: the output is addressed in 32-bit words
+    reinterpret_cast<uint32_t*>(reinterpret_cast<int8_t*>(p.y) + c0)[pix * (uint32_t)(p.ldy >> 2)] = prmt(p01, p23, 0x5410);
   } else {
     const int raw[4] = {acc[0] - kDwMagic, acc[1] - kDwMagic, acc[2] - kDwMagic, acc[3] - kDwMagic};
     const float s4[4] = {sc.x, sc.y, sc.z, sc.w}, b4[4] = {bs.x, bs.y, bs.z, bs.w};
-    dw_store4(p, raw, s4, b4, pix, c0);
+    dw_store4(p, raw, s4, b4, (long long)pix, c0);
   }
 }
 
@@ -222,12 +223,13 @@ __device__ __forceinline__ void dw_load_scale_bias(const DwParams& p, int c0, fl
 // plus an all-ones / all-zeros mask per column (zero padding = load a valid neighbour,
 // then AND it away; one LOP3 per word also applies the row mask)
 template <int NC>
-__device__ __forceinline__ void dw_columns(const DwParams& p, int iw0, int (&colw)[NC], uint32_t (&cm)[NC]) {
+__device__ __forceinline__ void dw_columns(const DwParams& p, const uint32_t* img, int iw0,
+                                           const uint32_t* (&cp)[NC], uint32_t (&cm)[NC]) {
 #pragma unroll
   for (int k = 0; k < NC; ++k) {
     const int iw = iw0 + k;
     const int c = min(max(iw, 0), p.W - 1);
-    colw[k] = c * p.ldxw;
+    cp[k] = img + (uint32_t)(c * p.ldxw);
     cm[k] = (iw == c) ? 0xffffffffu : 0u;
   }
 }
@@ -240,10 +242,10 @@ __global__ void __launch_bounds__(256, RB <= 2 ? 4 : 2) dw3x3s1_kernel(const DwP
   const DwItem it = dw_item(p, idx, RB, 4);
   const int c0 = it.c0;
   const int ih0 = it.p0 - p.pt;
-  int colw[6];
+  const uint32_t* img = reinterpret_cast<const uint32_t*>(p.x + c0) + (uint32_t)(it.n * p.H) * (uint32_t)p.rowpitch_w;
+  const uint32_t* cp[6];
   uint32_t cm[6];
-  dw_columns<6>(p, it.q0 - p.pl_, colw, cm);
-  const uint32_t* img = reinterpret_cast<const uint32_t*>(p.x + c0) + (long long)it.n * p.H * p.rowpitch_w;
+  dw_columns<6>(p, img, it.q0 - p.pl_, cp, cm);
   uint32_t wa[3][4];
   dw_load_filter(p, c0, wa);
   int acc[RB][4][4];
@@ -258,10 +260,10 @@ __global__ void __launch_bounds__(256, RB <= 2 ? 4 : 2) dw3x3s1_kernel(const DwP
     const int ih = ih0 + i;
     const int ihc = min(max(ih, 0), p.H - 1);
     const uint32_t rm = (ih == ihc) ? 0xffffffffu : 0u;
-    const uint32_t* row = img + (long long)ihc * p.rowpitch_w;
+    const uint32_t roff = (uint32_t)(ihc * p.rowpitch_w);
     uint32_t xw[6];
 #pragma unroll
-    for (int k = 0; k < 6; ++k) xw[k] = __ldg(row + colw[k]) & cm[k] & rm;
+    for (int k = 0; k < 6; ++k) xw[k] = __ldg(cp[k] + roff) & cm[k] & rm;
     uint32_t ta[4], tb[4];
     dw_transpose(xw[0], xw[1], xw[2], xw[3], ta);  // columns 0..3 -> outputs 0, 1
     dw_transpose(xw[2], xw[3], xw[4], xw[5], tb);  // columns 2..5 -> outputs 2, 3
@@ -285,7 +287,7 @@ __global__ void __launch_bounds__(256, RB <= 2 ? 4 : 2) dw3x3s1_kernel(const DwP
   for (int o = 0; o < RB; ++o) {
     const int op = it.p0 + o;
     if (op >= p.P) break;
-    const long long pix = ((long long)it.n * p.P + op) * p.Q + it.q0;
+    const uint32_t pix = (uint32_t)((it.n * p.P + op) * p.Q + it.q0);
 #pragma unroll
     for (int q = 0; q < 4; ++q)
       if (it.q0 + q < p.Q) dw_finish4<FAST>(p, acc[o][q], sc, bs, p.hi_bits, pix + q, c0);
@@ -300,10 +302,10 @@ __global__ void __launch_bounds__(256, 4) dw3x3s2_kernel(const DwParams p) {
   const DwItem it = dw_item(p, idx, RB, 2);
   const int c0 = it.c0;
   const int ih0 = it.p0 * 2 - p.pt;
-  int colw[5];
+  const uint32_t* img = reinterpret_cast<const uint32_t*>(p.x + c0) + (uint32_t)(it.n * p.H) * (uint32_t)p.rowpitch_w;
+  const uint32_t* cp[5];
   uint32_t cm[5];
-  dw_columns<5>(p, it.q0 * 2 - p.pl_, colw, cm);
-  const uint32_t* img = reinterpret_cast<const uint32_t*>(p.x + c0) + (long long)it.n * p.H * p.rowpitch_w;
+  dw_columns<5>(p, img, it.q0 * 2 - p.pl_, cp, cm);
   uint32_t wa[3][4];
   dw_load_filter(p, c0, wa);
   constexpr int NR = 2 * RB + 1;
@@ -319,10 +321,10 @@ __global__ void __launch_bounds__(256, 4) dw3x3s2_kernel(const DwParams p) {
     const int ih = ih0 + i;
     const int ihc = min(max(ih, 0), p.H - 1);
     const uint32_t rm = (ih == ihc) ? 0xffffffffu : 0u;
-    const uint32_t* row = img + (long long)ihc * p.rowpitch_w;
+    const uint32_t roff = (uint32_t)(ihc * p.rowpitch_w);
     uint32_t xw[5];
 #pragma unroll
-    for (int k = 0; k < 5; ++k) xw[k] = __ldg(row + colw[k]) & cm[k] & rm;
+    for (int k = 0; k < 5; ++k) xw[k] = __ldg(cp[k] + roff) & cm[k] & rm;
     uint32_t ta[4];
     dw_transpose(xw[0], xw[1], xw[2], xw[3], ta);
 #pragma unroll
@@ -345,7 +347,7 @@ __global__ void __launch_bounds__(256, 4) dw3x3s2_kernel(const DwParams p) {
   for (int o = 0; o < RB; ++o) {
     const int op = it.p0 + o;
     if (op >= p.P) break;
-    const long long pix = ((long long)it.n * p.P + op) * p.Q + it.q0;
+    const uint32_t pix = (uint32_t)((it.n * p.P + op) * p.Q + it.q0);
 #pragma unroll
     for (int q = 0; q < 2; ++q)
       if (it.q0 + q < p.Q) dw_finish4<FAST>(p, acc[o][q], sc, bs, p.hi_bits, pix + q, c0);
@@ -433,7 +435,10 @@ extern "C" int pl_dwconv2d_i8_nhwc(const int8_t* x, const int8_t* w_crs, void* y
   if (e->residual) return PL_ERR_UNSUPPORTED;
 
   const bool aligned = ((reinterpret_cast<uintptr_t>(x) & 3) == 0) && (d->ldx % 4 == 0);
-  const bool fast = aligned && d->R == 3 && d->S == 3 && d->dil_h == 1 && d->dil_w == 1 &&
+  // the fast kernels address both tensors with 32-bit offsets
+  const bool small = (long long)d->N * d->H * d->W * d->ldx < (1ll << 31) &&
+                     (long long)d->N * P * Q * d->ldy < (1ll << 31) && (long long)d->N * P * Q * p.CG < (1ll << 31);
+  const bool fast = aligned && small && d->R == 3 && d->S == 3 && d->dil_h == 1 && d->dil_w == 1 &&
                     d->stride_h == d->stride_w && (d->stride_h == 1 || d->stride_h == 2);
   int dev = 0, sms = 148;
   cudaGetDevice(&dev);
@@ -460,7 +465,6 @@ extern "C" int pl_dwconv2d_i8_nhwc(const int8_t* x, const int8_t* w_crs, void* y
     if (s1 && items_for(4) >= (long long)sms * 2048 * 2) RB = 4;
     p.bands = (P + RB - 1) / RB;
     p.items = items_for(RB);
-    if (p.items >= (1ll << 31) || (long long)d->N * d->H * d->W * d->ldx >= (1ll << 33)) return PL_ERR_UNSUPPORTED;
     p.dCG = make_fastdiv((uint32_t)p.CG);
     p.dStrips = make_fastdiv((uint32_t)p.strips);
     p.dBands = make_fastdiv((uint32_t)p.bands);

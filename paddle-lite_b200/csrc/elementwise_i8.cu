@@ -304,6 +304,146 @@ pool_kernel(const int8_t* __restrict__ x, int ldx, void* __restrict__ y, int ldy
   }
 }
 
+// word-granular pooling: one thread = 4 channels (one 32-bit word) of one output pixel, so
+// a warp reads up to 128 contiguous bytes per window tap.  max runs on sign-extended
+// s16x2 pairs (PRMT + VIMNMX.S16x2), avg on zero-extended biased u16x2 pairs (plain adds,
+// the bias 128*cnt is removed at the end).  Index math uses launch-time magic division.
+__device__ __forceinline__ uint32_t prmt_e(uint32_t a, uint32_t b, uint32_t sel) {
+  uint32_t r;
+  asm("prmt.b32 %0, %1, %2, %3;" : "=r"(r) : "r"(a), "r"(b), "r"(sel));
+  return r;
+}
+
+// V = words per thread (1, or 4 = one 16-byte load per tap); KF = compile-time window edge
+// (3 -> fully unrolled 3x3 with every load issued before the first use, 0 -> runtime loops)
+template <int POOL, int V, int KF>
+__global__ void __launch_bounds__(256)
+pool4_kernel(const uint32_t* __restrict__ x, int ldxw, void* __restrict__ y, int ldy, int H, int W, int C,
+             int kh, int kw, int sh, int sw, int pt, int pl_, FastDiv dCw, FastDiv dQ, FastDiv dP,
+             uint32_t total, int exclusive, float rescale, int out_dtype, int round_mode, int word_store) {
+  const uint32_t idx = blockIdx.x * 256u + threadIdx.x;
+  if (idx >= total) return;
+  uint32_t t = fdiv(idx, dCw);
+  const int cw = (int)(idx - t * dCw.d) * V;
+  uint32_t u = fdiv(t, dQ);
+  const int oq = (int)(t - u * dQ.d);
+  const uint32_t n = fdiv(u, dP);
+  const int op = (int)(u - n * dP.d);
+  const int hs = op * sh - pt, ws = oq * sw - pl_;
+  const int h1 = min(hs + kh, H), w1 = min(ws + kw, W);
+  const int h0 = max(hs, 0), w0 = max(ws, 0);
+  const uint32_t* img = x + (size_t)n * (size_t)(H * W) * (size_t)ldxw + cw;
+  uint32_t a01[V], a23[V];  // channel pairs (0,1) and (2,3) of each word as 16-bit lanes
+#pragma unroll
+  for (int v = 0; v < V; ++v) a01[v] = a23[v] = (POOL == PL_POOL_MAX) ? 0xff80ff80u : 0u;
+  auto load = [&](int h, int w, uint32_t (&d)[V]) {
+    const uint32_t* p = img + (uint32_t)((h * W + w) * ldxw);
+    if (V == 4) {
+      const uint4 q = __ldg(reinterpret_cast<const uint4*>(p));
+      d[0] = q.x; d[V > 1 ? 1 : 0] = q.y; d[V > 2 ? 2 : 0] = q.z; d[V > 3 ? 3 : 0] = q.w;
+    } else {
+      d[0] = __ldg(p);
+    }
+  };
+  auto reduce = [&](const uint32_t (&d)[V]) {
+#pragma unroll
+    for (int v = 0; v < V; ++v) {
+      if (POOL == PL_POOL_MAX) {
+        a01[v] = __vmaxs2(a01[v], prmt_e(d[v], 0u, 0x9180));  // {b0, sign, b1, sign}
+        a23[v] = __vmaxs2(a23[v], prmt_e(d[v], 0u, 0xB3A2));
+      } else {
+        const uint32_t b = d[v] ^ 0x80808080u;  // biased to unsigned: lanes cannot carry into each other
+        a01[v] += prmt_e(b, 0u, 0x4140);
+        a23[v] += prmt_e(b, 0u, 0x4342);
+      }
+    }
+  };
+  if (KF > 0) {
+    // clamp the tap coordinates (always a valid address), issue all loads, then drop the
+    // taps that fell outside the image
+    uint32_t d[KF > 0 ? KF * KF : 1][V];
+#pragma unroll
+    for (int r = 0; r < KF; ++r)
+#pragma unroll
+      for (int c = 0; c < KF; ++c) load(min(max(hs + r, 0), H - 1), min(max(ws + c, 0), W - 1), d[r * KF + c]);
+#pragma unroll
+    for (int r = 0; r < KF; ++r)
+#pragma unroll
+      for (int c = 0; c < KF; ++c) {
+        const bool ok = hs + r >= 0 && hs + r < H && ws + c >= 0 && ws + c < W;
+        if (ok) reduce(d[r * KF + c]);
+      }
+  } else {
+    for (int h = h0; h < h1; ++h) {
+#pragma unroll 4
+      for (int w = w0; w < w1; ++w) {
+        uint32_t d[V];
+        load(h, w, d);
+        reduce(d);
+      }
+    }
+  }
+  const int cnt_in = (h1 - h0) * (w1 - w0);
+  const int cnt = exclusive ? cnt_in : kh * kw;
+  const size_t obase = ((size_t)u * dQ.d + oq) * (size_t)ldy;  // u = n * P + op
+#pragma unroll
+  for (int v = 0; v < V; ++v) {
+    int e[4];
+    if (POOL == PL_POOL_MAX) {
+      e[0] = (int)(short)(a01[v] & 0xffffu);
+      e[1] = (int)(short)(a01[v] >> 16);
+      e[2] = (int)(short)(a23[v] & 0xffffu);
+      e[3] = (int)(short)(a23[v] >> 16);
+    } else {
+      e[0] = (int)(a01[v] & 0xffffu) - 128 * cnt_in;
+      e[1] = (int)(a01[v] >> 16) - 128 * cnt_in;
+      e[2] = (int)(a23[v] & 0xffffu) - 128 * cnt_in;
+      e[3] = (int)(a23[v] >> 16) - 128 * cnt_in;
+    }
+    float f[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j)
+      f[j] = (POOL == PL_POOL_MAX) ? __fmul_rn((float)e[j], rescale)
+                                   : __fmul_rn(__fdiv_rn((float)e[j], (float)cnt), rescale);
+    const int c0 = (cw + v) * 4;
+    if (c0 >= C) break;
+    const size_t o = obase + c0;
+    const int nch = C - c0 < 4 ? C - c0 : 4;
+    if (out_dtype == PL_OUT_FP32) {
+      float* out = reinterpret_cast<float*>(y) + o;
+      if (word_store && nch == 4) {
+        *reinterpret_cast<float4*>(out) = make_float4(f[0], f[1], f[2], f[3]);
+      } else {
+        for (int j = 0; j < nch; ++j) out[j] = f[j];
+      }
+    } else {
+      int q[4];
+#pragma unroll
+      for (int j = 0; j < 4; ++j) q[j] = round_sat_i8(f[j], round_mode);
+      int8_t* out = reinterpret_cast<int8_t*>(y) + o;
+      if (word_store) {
+        *reinterpret_cast<uint32_t*>(out) = pack4_i8(q[0], q[1], q[2], q[3]);
+      } else {
+        for (int j = 0; j < nch; ++j) out[j] = (int8_t)q[j];
+      }
+    }
+  }
+}
+
+template <int POOL>
+static void launch_pool4(int V, int KF, unsigned grid, cudaStream_t st, const uint32_t* x, int ldxw, void* y, int ldy,
+                         int H, int W, int C, int kh, int kw, int sh, int sw, int pt, int pl_, FastDiv dCw, FastDiv dQ,
+                         FastDiv dP, uint32_t total, int exclusive, float rescale, int out_dtype, int round_mode,
+                         int word_store) {
+#define PL_POOL_ARGS x, ldxw, y, ldy, H, W, C, kh, kw, sh, sw, pt, pl_, dCw, dQ, dP, total, exclusive, rescale, \
+                     out_dtype, round_mode, word_store
+  if (V == 4 && KF == 3) pool4_kernel<POOL, 4, 3><<<grid, 256, 0, st>>>(PL_POOL_ARGS);
+  else if (V == 4) pool4_kernel<POOL, 4, 0><<<grid, 256, 0, st>>>(PL_POOL_ARGS);
+  else if (KF == 3) pool4_kernel<POOL, 1, 3><<<grid, 256, 0, st>>>(PL_POOL_ARGS);
+  else pool4_kernel<POOL, 1, 0><<<grid, 256, 0, st>>>(PL_POOL_ARGS);
+#undef PL_POOL_ARGS
+}
+
 // ------------------------------------------------------------- residual add
 __device__ __forceinline__ float add_value(int a, int b, float sa, float sb, int act, float arg) {
   const float v = __fmaf_rn((float)a, sa, __fmul_rn((float)b, sb));
@@ -464,6 +604,36 @@ extern "C" int pl_pool2d_i8_nhwc(const int8_t* x, int ldx, void* y, int ldy, int
       P <= 0 || Q <= 0 || ldx < C || ldy < C)
     return PL_ERR_ARG;
   if (out_dtype != PL_OUT_INT8 && out_dtype != PL_OUT_FP32) return PL_ERR_ARG;
+  // word-granular fast path: 4-byte aligned input pixels, window small enough for the
+  // 16-bit lane sums, 32-bit item index
+  const int Cw = (C + 3) / 4;
+  if ((reinterpret_cast<uintptr_t>(x) & 3) == 0 && ldx % 4 == 0 && ldx >= Cw * 4 && kh * kw <= 255 &&
+      (long long)N * P * Q * Cw < (1ll << 31) && (long long)H * W * (ldx / 4) < (1ll << 31)) {
+    // 16-byte taps when every pixel is 16-byte aligned and covers whole 4-word groups
+    // (only when that still leaves a few waves of threads: global pooling stays word-wide)
+    const int V = (al16(x) && ldx % 16 == 0 && ldx >= (C + 15) / 16 * 16 && C >= 16 &&
+                   (long long)N * P * Q * ((Cw + 3) / 4) >= 148ll * 2048 * 2)
+                      ? 4
+                      : 1;
+    const int KF = (kh == 3 && kw == 3) ? 3 : 0;
+    const int groups = (Cw + V - 1) / V;
+    const long long witems = (long long)N * P * Q * groups;
+    // whole-word stores need the pad channels of the last word to be addressable
+    const int word_store = (ldy >= Cw * 4) && (ldy % 4 == 0) &&
+                           ((reinterpret_cast<uintptr_t>(y) & (out_dtype == PL_OUT_INT8 ? 3 : 15)) == 0);
+    const unsigned grid = (unsigned)((witems + 255) / 256);
+    const FastDiv dCw = make_fastdiv((uint32_t)groups), dQ = make_fastdiv((uint32_t)Q), dP = make_fastdiv((uint32_t)P);
+    if (pool_type == PL_POOL_MAX)
+      launch_pool4<PL_POOL_MAX>(V, KF, grid, (cudaStream_t)stream, reinterpret_cast<const uint32_t*>(x), ldx / 4, y,
+                                ldy, H, W, C, kh, kw, sh, sw, pt, pl_, dCw, dQ, dP, (uint32_t)witems, exclusive,
+                                rescale, out_dtype, round_mode, word_store);
+    else
+      launch_pool4<PL_POOL_AVG>(V, KF, grid, (cudaStream_t)stream, reinterpret_cast<const uint32_t*>(x), ldx / 4, y,
+                                ldy, H, W, C, kh, kw, sh, sw, pt, pl_, dCw, dQ, dP, (uint32_t)witems, exclusive,
+                                rescale, out_dtype, round_mode, word_store);
+    ++g_launches;
+    return launch_status();
+  }
   const int vec = al16(x) && (ldx % 16 == 0);
   const long long items = (long long)N * P * Q * (vec ? (C + 15) / 16 : C);
   pool_kernel<<<grid_for(items, 256), 256, 0, (cudaStream_t)stream>>>(
