@@ -149,6 +149,17 @@ int pl_quantize_nchw_f32_to_nhwc_i8(const float* x, int8_t* y, int N, int C,
 int pl_im2col_i8_nhwc(const int8_t* x, int ldx, int8_t* A, int ldA, int N, int H,
                       int W, int cbytes, int R, int S, int sh, int sw, int pt,
                       int pl, int dh, int dw, int P, int Q, pl_stream_t stream);
+/* thin first layers, direct: input with C <= 4 stored as ONE 32-bit word per pixel
+ * (ldx == 4, e.g. from pl_quantize_nchw_f32_to_nhwc_i8 with ldy = 4).  Extra warps of the
+ * tensor-core kernel gather the R x S window of every output pixel on chip, so no im2col
+ * matrix is written to HBM.  dilation 1; windows: R in {3,5,7} with S <= 8 (see
+ * pl_thin_conv_supported).  w_thin comes from pl_pack_thin_conv_weight_i8 (OHWI in). */
+int pl_thin_conv_supported(int R, int S, int C, int dil_h, int dil_w);
+size_t pl_thin_conv_packed_weight_bytes(int K, int R, int S);
+int pl_pack_thin_conv_weight_i8(const int8_t* w_ohwi, int8_t* w_thin, int K, int R, int S,
+                                int C, pl_stream_t stream);
+int pl_thin_conv2d_i8_nhwc(const int8_t* x, const int8_t* w_thin, void* y,
+                           const pl_conv_desc* d, const pl_epilogue* e, pl_stream_t stream);
 /* plain layout transforms; elem_bytes 1 or 4; ld = NHWC pixel pitch (elements) */
 int pl_nchw_to_nhwc(const void* x, void* y, int N, int C, int H, int W, int ld,
                     int elem_bytes, pl_stream_t stream);

@@ -239,6 +239,40 @@ def im2col(x, R, S, strides=(1, 1), pads=(0, 0, 0, 0), dil=(1, 1), A=None, cbyte
     return A
 
 
+def thin_conv_supported(R, S, Cc, dil=(1, 1)):
+    return bool(lib().pl_thin_conv_supported(R, S, Cc, dil[0], dil[1]))
+
+
+def pack_thin_conv_weight(w_ohwi):
+    """OHWI int8 (device, C <= 4) -> packed filter for thin_conv2d."""
+    K, R, S, Cc = w_ohwi.shape
+    nbytes = lib().pl_thin_conv_packed_weight_bytes(K, R, S)
+    out = torch.empty(nbytes, dtype=torch.int8, device=w_ohwi.device)
+    _check(lib().pl_pack_thin_conv_weight_i8(_ptr(w_ohwi.contiguous()), _ptr(out), K, R, S, Cc, _stream()),
+           "pl_pack_thin_conv_weight_i8")
+    return out
+
+
+def thin_conv2d(x, w_thin, K, R, S, Cc, scale, bias, strides=(1, 1), pads=(0, 0, 0, 0), act=ACT_NONE,
+                act_arg=0.0, out=OUT_INT8, rnd=ROUND_ARM, y=None, ldy=None):
+    """x: [N,H,W,4] int8 (one word per pixel, Cc <= 4 logical channels): direct conv, A tiles
+    gathered on chip."""
+    N, H, W, ldx = x.shape
+    assert ldx == 4
+    P = conv_out_size(H, R, 1, pads[0], pads[1], strides[0])
+    Q = conv_out_size(W, S, 1, pads[2], pads[3], strides[1])
+    ldy = K if ldy is None else ldy
+    if y is None:
+        y = torch.empty((N, P, Q, ldy), dtype=_TORCH_OUT[out], device=x.device)
+        if ldy != K:
+            y.zero_()
+    d = conv_desc(N, H, W, Cc, K, R, S, strides, pads, (1, 1), 1, 4, ldy)
+    e = make_epilogue(scale, bias, act, act_arg, out, rnd)
+    _check(lib().pl_thin_conv2d_i8_nhwc(_ptr(x), _ptr(w_thin), _ptr(y), C.byref(d), C.byref(e), _stream()),
+           "pl_thin_conv2d_i8_nhwc")
+    return y
+
+
 def nchw_to_nhwc(x, ld=None):
     N, Cc, H, W = x.shape
     ld = Cc if ld is None else ld

@@ -39,7 +39,12 @@ struct IgemmParams {
   int m_tiles, n_tiles;
   int BN, BK, stages;
   int num_kb, cblocks;
-  int mode;  // 0: A is a [M, K] matrix (tiled TMA); 1: A is NHWC, im2col TMA
+  int mode;  // 0: A is a [M, K] matrix (tiled TMA); 1: A is NHWC, im2col TMA;
+             // 2: thin input (C <= 4, one word per pixel): A tiles are gathered by producer warps
+  const uint32_t* xw;  // mode 2: input words [N][H][W]
+  int thin_r, thin_sw;
+  int H, W;
+  FastDiv dQ, dPQ;
   int Q, PQ, S;
   int sh, sw, pt, pl_, dh, dw;
   uint32_t a_stage_bytes, b_stage_bytes, tx_bytes, tmem_cols, acc_stride;
@@ -228,8 +233,14 @@ __device__ __noinline__ void store_group16(const IgemmParams& p, const uint32_t*
 // --------------------------------------------------------------------------
 // the kernel
 // --------------------------------------------------------------------------
-template <int EPI>
-__global__ void __launch_bounds__(kThreads, 1)
+// TR / TSW > 0 selects the thin-input mode for an R x (<= TSW words) filter window: four extra
+// warps (one thread per A row) gather the window words of every filter row straight from the
+// one-word-per-pixel input, all loads of a tile in flight at once, and store them into the
+// stage buffers in the 32-byte-swizzled K-major layout the MMA descriptors expect.  One
+// k-block (32 bytes) = 32 / (4 * TSW) filter rows.  No im2col matrix ever exists in HBM.
+static constexpr int kThinWarps = 4;
+template <int EPI, int TR = 0, int TSW = 0>
+__global__ void __launch_bounds__(kThreads + (TR > 0 ? 32 * kThinWarps : 0), 1)
 igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
                 const __grid_constant__ CUtensorMap tmap_b,
                 const __grid_constant__ CUtensorMap tmap_y,
@@ -263,7 +274,7 @@ igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
     if (EPI != EPI_GENERIC) tma_prefetch_desc(&tmap_y);
     if (EPI == EPI_I8_RELU_RES) tma_prefetch_desc(&tmap_r);
     for (int s = 0; s < p.stages; ++s) {
-      mbar_init(bar_full + 8 * s, 1);
+      mbar_init(bar_full + 8 * s, TR > 0 ? 1 + 32 * kThinWarps : 1);  // TMA (B) + one arrival per A row
       mbar_init(bar_empty + 8 * s, 1);
     }
     for (int s = 0; s < 2; ++s) {
@@ -319,7 +330,9 @@ igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
           mbar_arrive_expect_tx(bar_full + 8 * stage, tx);
           const uint32_t dst_a = smem_a + stage * p.a_stage_bytes;
           const uint32_t dst_b = smem_b + stage * p.b_stage_bytes;
-          if (p.mode == 1) {
+          if (TR > 0) {
+            // A arrives from the gather warps
+          } else if (p.mode == 1) {
             const int r = tap / p.S, s = tap - r * p.S;
             tma_load_im2col_4d(dst_a, &tmap_a, bar_full + 8 * stage, cb * p.BK, bw, bh, bn,
                                (uint16_t)(s * p.dw), (uint16_t)(r * p.dh));
@@ -359,6 +372,60 @@ igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
         }
         umma_commit(bar_tfull + 8 * as);
         if (++as == 2) { as = 0; aphase ^= 1; }
+      }
+    }
+  } else if (TR > 0 && warp >= 2 + kEpiWarps) {
+    // ===================== thin-input gather (warps 18..21) =====================
+    constexpr int R_ = TR > 0 ? TR : 1, SW_ = TSW > 0 ? TSW : 4;
+    constexpr int RPK = 8 / SW_;                  // filter rows per 32-byte k-block
+    constexpr int NKB = (R_ + RPK - 1) / RPK;
+    const int prow = (int)threadIdx.x - (64 + 32 * kEpiWarps);  // A row of this thread
+    const uint32_t rowoff = (uint32_t)prow * 32u;
+    const uint32_t swx = (rowoff >> 7) & 1u;      // 32-byte swizzle: chunk ^= bit 7 of the offset
+    int stage = 0;
+    uint32_t phase = 0;
+    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+      const int tm = tile / p.n_tiles;
+      const uint32_t m = (uint32_t)(tm * kBM + prow);
+      const bool mok = m < (uint32_t)p.M;
+      const uint32_t n = fdiv(mok ? m : 0u, p.dPQ);
+      const uint32_t rem = (mok ? m : 0u) - n * (uint32_t)p.PQ;
+      const uint32_t op = fdiv(rem, p.dQ);
+      const int oq = (int)(rem - op * (uint32_t)p.Q);
+      const int ih0 = (int)op * p.sh - p.pt, iw0 = oq * p.sw - p.pl_;
+      const uint32_t* img = p.xw + (size_t)n * (size_t)(p.H * p.W);
+      // the whole window first: R_ x SW_ independent loads in flight per thread
+      uint32_t xr[R_][SW_];
+#pragma unroll
+      for (int r = 0; r < R_; ++r) {
+        const int ih = ih0 + r;
+        const bool rok = mok && ih >= 0 && ih < p.H;
+        const uint32_t* row = img + ih * p.W;
+#pragma unroll
+        for (int j = 0; j < SW_; ++j) {
+          const int iw = iw0 + j;
+          xr[r][j] = (rok && iw >= 0 && iw < p.W) ? __ldg(row + iw) : 0u;
+        }
+      }
+#pragma unroll
+      for (int kb = 0; kb < NKB; ++kb) {
+        mbar_wait(bar_empty + 8 * stage, phase ^ 1);
+        const uint32_t dst = smem_a + stage * p.a_stage_bytes + rowoff;
+#pragma unroll
+        for (int c = 0; c < 2; ++c) {
+          uint32_t w0, w1, w2, w3;
+          if constexpr (SW_ == 8) {
+            w0 = xr[kb][4 * c]; w1 = xr[kb][4 * c + 1]; w2 = xr[kb][4 * c + 2]; w3 = xr[kb][4 * c + 3];
+          } else {
+            const int r = 2 * kb + c;
+            if (r < R_) { w0 = xr[r < R_ ? r : 0][0]; w1 = xr[r < R_ ? r : 0][1]; w2 = xr[r < R_ ? r : 0][2]; w3 = xr[r < R_ ? r : 0][3]; }
+            else { w0 = w1 = w2 = w3 = 0u; }
+          }
+          st_shared_v4(dst + (((uint32_t)c ^ swx) << 4), w0, w1, w2, w3);
+        }
+        fence_proxy_async();  // generic-proxy stores -> visible to the tensor core's async proxy
+        mbar_arrive(bar_full + 8 * stage);
+        if (++stage == p.stages) { stage = 0; phase ^= 1; }
       }
     }
   } else {
@@ -546,6 +613,20 @@ __global__ void pack_conv_weight_kernel(const int8_t* __restrict__ w, int8_t* __
   }
 }
 
+// thin-input filter packing: OHWI [K,R,S,C<=4] -> [K][NKB][32 bytes]; k-block kb holds
+// 32/(4*SW) filter rows of SW words, word j of a row = the 4 channel weights of tap s = j
+__global__ void pack_thin_weight_kernel(const int8_t* __restrict__ w, int8_t* __restrict__ out, int K, int R,
+                                        int S, int C, int SW, int row_bytes) {
+  const long long total = (long long)K * row_bytes;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
+       i += (long long)gridDim.x * blockDim.x) {
+    const int k = (int)(i / row_bytes), b = (int)(i % row_bytes);
+    const int word = b >> 2, c = b & 3;
+    const int r = word / SW, s_ = word % SW;
+    out[i] = (r < R && s_ < S && c < C) ? w[(((long long)k * R + r) * S + s_) * C + c] : (int8_t)0;
+  }
+}
+
 // --------------------------------------------------------------------------
 // host: tensor maps
 // --------------------------------------------------------------------------
@@ -638,17 +719,18 @@ int pick_bn(int Nout, int m_tiles, int sms) {
   return bn;
 }
 
-template <int EPI>
+template <int EPI, int TR = 0, int TSW = 0>
 int launch_one(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& ty, const CUtensorMap& tr,
                const IgemmParams& p, int grid, size_t smem, pl_stream_t stream) {
   static bool configured = false;  // one process drives one GPU
   if (!configured) {
     // 227 KB is the per-CTA limit for static + dynamic shared memory together
-    PL_CUDA_OK(cudaFuncSetAttribute(igemm_i8_kernel<EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    PL_CUDA_OK(cudaFuncSetAttribute(igemm_i8_kernel<EPI, TR, TSW>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                     (int)(216 * 1024)));
     configured = true;
   }
-  igemm_i8_kernel<EPI><<<grid, kThreads, smem, (cudaStream_t)stream>>>(ta, tb, ty, tr, p);
+  const int threads = kThreads + (TR > 0 ? 32 * kThinWarps : 0);
+  igemm_i8_kernel<EPI, TR, TSW><<<grid, threads, smem, (cudaStream_t)stream>>>(ta, tb, ty, tr, p);
   ++g_launches;
   return launch_status();
 }
@@ -738,6 +820,27 @@ int launch_igemm(const CUtensorMap& ta, const CUtensorMap& tb, IgemmParams& p, p
   p.out_stage_off = (uint32_t)(stages * stage_bytes);
   p.res_stage_off = p.out_stage_off + (uint32_t)(p.out_bufs * tile);
   const size_t smem = (size_t)stages * stage_bytes + extra + 1024;
+  if (p.mode == 2) {
+    // thin-input gather mode: (filter rows, window words) instantiations
+    const int key = p.thin_r * 16 + p.thin_sw;
+    const bool relu = (epi == EPI_I8_RELU);
+    if (!relu) {  // everything else (fp32 / signed / legacy) takes the generic epilogue
+      p.tma_out = 0;
+      p.tma_res = 0;
+    }
+#define PL_THIN_CASE(R_, SW_)                                                                                   \
+  case R_ * 16 + SW_:                                                                                            \
+    return relu ? launch_one<EPI_I8_RELU, R_, SW_>(ta, tb, ty, tr, p, grid, smem, stream)                        \
+                : launch_one<EPI_GENERIC, R_, SW_>(ta, tb, ty, tr, p, grid, smem, stream);
+    switch (key) {
+      PL_THIN_CASE(7, 8)
+      PL_THIN_CASE(5, 8)
+      PL_THIN_CASE(3, 4)
+      PL_THIN_CASE(3, 8)
+      default: return PL_ERR_UNSUPPORTED;
+    }
+#undef PL_THIN_CASE
+  }
   switch (epi) {
     case EPI_I8_RELU: return launch_one<EPI_I8_RELU>(ta, tb, ty, tr, p, grid, smem, stream);
     case EPI_I8_RELU_RES: return launch_one<EPI_I8_RELU_RES>(ta, tb, ty, tr, p, grid, smem, stream);
@@ -870,6 +973,79 @@ extern "C" int pl_conv2d_i8_nhwc(const int8_t* x, const int8_t* w_packed, void* 
   rc = encode_2d(&tb, w_packed, wrow, (uint64_t)d->K, wrow, p.BK, p.BN);
   if (rc) return rc;
   return launch_igemm(ta, tb, p, stream);
+}
+
+// ---- thin first layers: direct conv on one-word-per-pixel input ------------------
+static int thin_sw(int S) { return S <= 4 ? 4 : 8; }
+static int thin_nkb(int R, int S) {
+  const int rpk = 8 / thin_sw(S);
+  return (R + rpk - 1) / rpk;
+}
+
+extern "C" int pl_thin_conv_supported(int R, int S, int C, int dil_h, int dil_w) {
+  if (C < 1 || C > 4 || dil_h != 1 || dil_w != 1 || S < 1 || S > 8) return 0;
+  const int sw = thin_sw(S);
+  return (R == 7 && sw == 8) || (R == 5 && sw == 8) || (R == 3 && sw == 4) || (R == 3 && sw == 8);
+}
+
+extern "C" size_t pl_thin_conv_packed_weight_bytes(int K, int R, int S) {
+  if (K <= 0 || R <= 0 || S <= 0 || S > 8) return 0;
+  return (size_t)K * thin_nkb(R, S) * 32;
+}
+
+extern "C" int pl_pack_thin_conv_weight_i8(const int8_t* w_ohwi, int8_t* w_thin, int K, int R, int S, int C,
+                                           pl_stream_t stream) {
+  if (!w_ohwi || !w_thin || K <= 0 || !pl_thin_conv_supported(R, S, C, 1, 1)) return PL_ERR_ARG;
+  const int row_bytes = thin_nkb(R, S) * 32;
+  const long long total = (long long)K * row_bytes;
+  const int blocks = (int)((total + 255) / 256 > 1024 ? 1024 : (total + 255) / 256);
+  pack_thin_weight_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(w_ohwi, w_thin, K, R, S, C, thin_sw(S),
+                                                                    row_bytes);
+  ++g_launches;
+  return launch_status();
+}
+
+extern "C" int pl_thin_conv2d_i8_nhwc(const int8_t* x, const int8_t* w_thin, void* y, const pl_conv_desc* d,
+                                      const pl_epilogue* e, pl_stream_t stream) {
+  if (!x || !w_thin || !y || !d) return PL_ERR_ARG;
+  int rc = check_epi(e);
+  if (rc) return rc;
+  if (!driver().ok) return PL_ERR_DRIVER;
+  if (driver().cc_major != 10) return PL_ERR_DEVICE;
+  if (d->groups != 1 || e->residual) return PL_ERR_UNSUPPORTED;
+  if (d->N <= 0 || d->H <= 0 || d->W <= 0 || d->K <= 0 || d->stride_h <= 0 || d->stride_w <= 0 || d->ldy < d->K)
+    return PL_ERR_ARG;
+  if (!pl_thin_conv_supported(d->R, d->S, d->C, d->dil_h, d->dil_w)) return PL_ERR_UNSUPPORTED;
+  if (d->ldx != 4 || (reinterpret_cast<uintptr_t>(x) & 3) || (reinterpret_cast<uintptr_t>(w_thin) & 15))
+    return PL_ERR_ALIGN;
+  const int P = pl_conv_out_size(d->H, d->R, 1, d->pad_t, d->pad_b, d->stride_h);
+  const int Q = pl_conv_out_size(d->W, d->S, 1, d->pad_l, d->pad_r, d->stride_w);
+  if (P <= 0 || Q <= 0) return PL_ERR_ARG;
+  if ((long long)d->N * P * Q >= (1ll << 31) || (long long)d->H * d->W >= (1ll << 31)) return PL_ERR_UNSUPPORTED;
+  IgemmParams p{};
+  p.mode = 2;
+  p.BK = 32;
+  const int nkb = thin_nkb(d->R, d->S);
+  rc = common_setup(p, (long long)d->N * P * Q, d->K, y, d->ldy, e, nkb * 32, 1);
+  if (rc) return rc;
+  p.xw = reinterpret_cast<const uint32_t*>(x);
+  p.H = d->H;
+  p.W = d->W;
+  p.Q = Q;
+  p.PQ = P * Q;
+  p.sh = d->stride_h;
+  p.sw = d->stride_w;
+  p.pt = d->pad_t;
+  p.pl_ = d->pad_l;
+  p.dQ = make_fastdiv((uint32_t)Q);
+  p.dPQ = make_fastdiv((uint32_t)(P * Q));
+  p.thin_r = d->R;
+  p.thin_sw = thin_sw(d->S);
+  p.tx_bytes = (uint32_t)(p.BN * p.BK);  // only the filter tile arrives by TMA
+  CUtensorMap tb;
+  rc = encode_2d(&tb, w_thin, (uint64_t)nkb * 32, (uint64_t)d->K, (uint64_t)nkb * 32, p.BK, p.BN);
+  if (rc) return rc;
+  return launch_igemm(tb, tb, p, stream);
 }
 
 extern "C" int pl_gemm_i8(const int8_t* A, int lda, const int8_t* Bt, int ldb, void* C, int ldc,

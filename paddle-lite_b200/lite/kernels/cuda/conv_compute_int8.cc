@@ -40,8 +40,20 @@ void ConvComputeInt8<Ptype_out>::PrepareForRun() {
   epi_.Fold(param.weight_scale, static_cast<int>(K), param.input_scale, param.output_scale, out_int8, param.bias, act,
             arg);
 
-  if (param.groups == 1 && C <= 4) {
-    // thin first layer: one 32-bit word per pixel, explicit im2col + GEMM
+  if (param.groups == 1 && C <= 4 &&
+      pl_thin_conv_supported(static_cast<int>(R), static_cast<int>(S), static_cast<int>(C), (*param.dilations)[0],
+                             (*param.dilations)[1]) &&
+      !param.residualData) {
+    // thin first layer, direct: one 32-bit word per pixel, the kernel gathers the windows on chip
+    path_ = kThinDirect;
+    packed_filter_.Resize(DDim({static_cast<int64_t>(
+        pl_thin_conv_packed_weight_bytes(static_cast<int>(K), static_cast<int>(R), static_cast<int>(S)))}));
+    PL_CALL(pl_pack_thin_conv_weight_i8(param.filter->data<int8_t>(),
+                                        packed_filter_.mutable_data<int8_t>(TARGET(kCUDA)), static_cast<int>(K),
+                                        static_cast<int>(R), static_cast<int>(S), static_cast<int>(C),
+                                        reinterpret_cast<pl_stream_t>(stream)));
+  } else if (param.groups == 1 && C <= 4) {
+    // thin first layer, other windows: one 32-bit word per pixel, explicit im2col + GEMM
     path_ = kThinIm2col;
     ldA_ = static_cast<int>(RoundUp(R * S * 4, 16));
     std::vector<int8_t> w(static_cast<size_t>(param.filter->numel()));
@@ -107,13 +119,22 @@ void ConvComputeInt8<Ptype_out>::Run() {
     return;
   }
   const int64_t pixels = N * xd[1] * xd[2];
-  if (path_ == kThinIm2col) {
-    // widen the pixel pitch to one word, pack patches, run the GEMM
+  if (path_ == kThinIm2col || path_ == kThinDirect) {
+    // widen the pixel pitch to one word
     x_padded_.Resize(DDim({pixels, 4}));
     int8_t* xp = x_padded_.mutable_data<int8_t>(TARGET(kCUDA));
-    CUDA_CALL(cudaMemsetAsync(xp, 0, static_cast<size_t>(pixels) * 4, ctx.exec_stream()));
-    CUDA_CALL(cudaMemcpy2DAsync(xp, 4, x, static_cast<size_t>(C), static_cast<size_t>(C), static_cast<size_t>(pixels),
-                                cudaMemcpyDeviceToDevice, ctx.exec_stream()));
+    if (C == 4) {
+      xp = const_cast<int8_t*>(x);
+    } else {
+      CUDA_CALL(cudaMemsetAsync(xp, 0, static_cast<size_t>(pixels) * 4, ctx.exec_stream()));
+      CUDA_CALL(cudaMemcpy2DAsync(xp, 4, x, static_cast<size_t>(C), static_cast<size_t>(C),
+                                  static_cast<size_t>(pixels), cudaMemcpyDeviceToDevice, ctx.exec_stream()));
+    }
+    if (path_ == kThinDirect) {
+      d.ldx = 4;
+      PL_CALL(pl_thin_conv2d_i8_nhwc(xp, packed_filter_.data<int8_t>(), y, &d, &e, stream));
+      return;
+    }
     im2col_.Resize(DDim({N * P * Q, ldA_}));
     int8_t* A = im2col_.mutable_data<int8_t>(TARGET(kCUDA));
     PL_CALL(pl_im2col_i8_nhwc(xp, 4, A, ldA_, d.N, d.H, d.W, 4, d.R, d.S, d.stride_h, d.stride_w, d.pad_t, d.pad_l,

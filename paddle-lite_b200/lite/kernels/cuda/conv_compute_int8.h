@@ -19,10 +19,10 @@ class ConvComputeInt8 : public KernelLite<TARGET(kCUDA), PRECISION(kInt8), DATAL
   virtual ~ConvComputeInt8() = default;
 
  private:
-  enum Path { kDense, kDepthwise, kThinIm2col };
+  enum Path { kDense, kDepthwise, kThinIm2col, kThinDirect };
   Path path_{kDense};
   FoldedEpilogue epi_;
-  Tensor packed_filter_;  // dense: tcgen05 K-blocked packing; thin: [K, ldA]
+  Tensor packed_filter_;  // dense: tcgen05 K-blocked packing; thin: [K, ldA] or the direct-kernel packing
   Tensor x_padded_;       // input copied to a 16-byte channel pitch when C % 16 != 0
   Tensor im2col_;         // thin first layers (C <= 4)
   int ldA_{0};

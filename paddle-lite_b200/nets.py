@@ -13,6 +13,8 @@ Model files for MobileNetV1/ResNet-50 int8 are not in the reference repo
 (lite/api/mobilenetv1_int8_test.cc needs --model_dir), so weights are random-init
 with seeded generators, as BASELINE.json says.
 """
+import os
+
 import numpy as np
 import torch
 
@@ -172,6 +174,7 @@ def program_bytes(prog):
     return act, wts
 
 
+_FORCE_IM2COL = os.environ.get("PL_THIN_IM2COL", "0") == "1"  # A/B switch: old explicit-im2col first layer
 _ACT = {"none": pl.ACT_NONE, "relu": pl.ACT_RELU, "relu6": pl.ACT_RELU6, "leaky": pl.ACT_LEAKY}
 
 
@@ -195,8 +198,12 @@ class DeviceNet:
     # -- one-off (PrepareForRun) ------------------------------------------------
     def _weights_to_device(self):
         for op in self.prog.ops:
-            if op.kind == "conv" and op.C <= 4:
-                # thin first layer: explicit im2col (one 32-bit word per pixel) + tensor-core GEMM
+            if op.kind == "conv" and op.C <= 4 and pl.thin_conv_supported(op.k, op.k, op.C) and not _FORCE_IM2COL:
+                # thin first layer, direct: window words gathered on chip by the conv kernel
+                op["_wp"] = pl.pack_thin_conv_weight(torch.from_numpy(op.w).to(self.dev))
+                op["_thin"] = True
+            elif op.kind == "conv" and op.C <= 4:
+                # thin first layer, fallback: explicit im2col (one word per pixel) + tensor-core GEMM
                 K, R, S, C = op.w.shape
                 w4 = np.zeros((K, R, S, 4), np.int8)
                 w4[..., :C] = op.w
@@ -287,6 +294,9 @@ class DeviceNet:
             return pl.dwconv2d(x, op._wp, sf, bf, op.k, op.k, (op.stride, op.stride), (op.pad,) * 4,
                                (1, 1), _ACT[op.act], argf, out, y=y, Cc=C)
         K = op.K
+        if C <= 4 and op.get("_thin"):
+            return pl.thin_conv2d(x, op._wp, K, op.k, op.k, C, sf, bf, (op.stride, op.stride), (op.pad,) * 4,
+                                  _ACT[op.act], argf, out, y=y, ldy=(rup(K, 16) if out == pl.OUT_INT8 else K))
         if C <= 4:
             N_, H_, W_, _ = x.shape
             P = (H_ + 2 * op.pad - op.k) // op.stride + 1

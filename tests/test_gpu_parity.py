@@ -430,3 +430,70 @@ def test_thin_first_layer_im2col_gemm(pl, case):
     bt[:, : k * k * 4] = w4.reshape(K, -1)
     got = host(pl.gemm(A, dev(bt), dev(sf), dev(bf), act=pl.ACT_RELU)).reshape(N, P, Q, K)
     assert np.array_equal(got, want)
+
+
+# ---- thin first layers, direct (on-chip window gather, no im2col matrix) -------------
+THIN_DIRECT = [
+    # N, H, W, C, K, R, S, stride, pads(t,b,l,r)
+    (2, 32, 32, 3, 64, 7, 7, 2, (3, 3, 3, 3)),     # ResNet stem shape (scaled down)
+    (3, 30, 34, 3, 32, 3, 3, 2, (1, 1, 1, 1)),     # MobileNet stem shape
+    (1, 19, 23, 4, 24, 5, 5, 1, (2, 2, 2, 2)),
+    (2, 17, 16, 1, 16, 3, 3, 1, (1, 1, 1, 1)),
+    (1, 21, 20, 2, 40, 3, 7, 2, (1, 0, 3, 2)),     # 3 x 7 window, asymmetric pads
+    (1, 9, 9, 3, 8, 7, 5, 1, (3, 3, 2, 2)),
+    (5, 13, 11, 3, 130, 3, 3, 1, (0, 0, 0, 0)),    # N tail + two N tiles
+]
+
+
+@pytest.mark.parametrize("case", THIN_DIRECT)
+@pytest.mark.parametrize("mode", ["int8_relu", "int8_none", "fp32", "int32"])
+def test_thin_direct_conv(pl, case, mode):
+    N, H, W, Cc, K, R, S, st, pads = case
+    rng = np.random.default_rng(sum(case[:8]) + len(mode))
+    x = rng.integers(-128, 128, (N, H, W, Cc), dtype=np.int8)
+    w = rng.integers(-127, 128, (K, R, S, Cc), dtype=np.int8)
+    assert pl.thin_conv_supported(R, S, Cc)
+    ws = ((1 + np.arange(K) % 7) / (7 * 127)).astype(np.float32)
+    bias = rng.uniform(-1, 1, K).astype(np.float32)
+    out = {"int8_relu": orc.OUT_INT8, "int8_none": orc.OUT_INT8, "fp32": orc.OUT_FP32, "int32": orc.OUT_INT32}[mode]
+    act = orc.ACT_RELU if mode == "int8_relu" else orc.ACT_NONE
+    sf, bf, _ = orc.fold_scales(ws, K, 1 / 127, Cc * R * S / 127 / 4, orc.OUT_INT8 if out == orc.OUT_INT8 else orc.OUT_FP32, bias)
+    want = orc.conv2d(x, w, sf, bf, (st, st), pads, act=act, out=out)
+    x4 = np.full((N, H, W, 4), 77, np.int8)  # junk in the pad channels: the packed filter zeroes them
+    x4[..., :Cc] = x
+    wt = pl.pack_thin_conv_weight(dev(w))
+    got = host(pl.thin_conv2d(dev(x4), wt, K, R, S, Cc, dev(sf), dev(bf), (st, st), pads, act=act, out=out))
+    if out == orc.OUT_FP32:
+        np.testing.assert_allclose(got, want, rtol=1e-5, atol=1e-6)
+    else:
+        assert np.array_equal(got, want)
+
+
+def test_thin_direct_full_size_stem(pl):
+    """ResNet-50 stem at full spatial size, batch 8: direct kernel == explicit im2col + GEMM."""
+    rng = np.random.default_rng(5)
+    N, H, W, Cc, K = 8, 224, 224, 3, 64
+    x4 = np.zeros((N, H, W, 4), np.int8)
+    x4[..., :Cc] = rng.integers(-127, 128, (N, H, W, Cc), dtype=np.int8)
+    w = rng.integers(-127, 128, (K, 7, 7, Cc), dtype=np.int8)
+    sf = np.full(K, 1e-3, np.float32)
+    bf = rng.uniform(-1, 1, K).astype(np.float32)
+    xd = dev(x4)
+    got = pl.thin_conv2d(xd, pl.pack_thin_conv_weight(dev(w)), K, 7, 7, Cc, dev(sf), dev(bf), (2, 2), (3, 3, 3, 3),
+                         act=pl.ACT_RELU)
+    A = pl.im2col(xd, 7, 7, (2, 2), (3, 3, 3, 3))
+    w4 = np.zeros((K, 7, 7, 4), np.int8)
+    w4[..., :Cc] = w
+    bt = np.zeros((K, A.shape[1]), np.int8)
+    bt[:, : 49 * 4] = w4.reshape(K, -1)
+    ref = pl.gemm(A, dev(bt), dev(sf), dev(bf), act=pl.ACT_RELU).reshape(got.shape)
+    assert torch.equal(got, ref)
+    # and a slice against the oracle
+    want = orc.conv2d(x4[:1, :, :, :Cc], w, sf, bf, (2, 2), (3, 3, 3, 3), act=orc.ACT_RELU)
+    assert np.array_equal(host(got[:1]), want)
+
+
+def test_thin_direct_rejects_unsupported(pl):
+    assert not pl.thin_conv_supported(3, 3, 8)
+    assert not pl.thin_conv_supported(9, 9, 3)
+    assert not pl.thin_conv_supported(3, 3, 3, (2, 2))
