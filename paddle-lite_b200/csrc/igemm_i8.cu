@@ -27,8 +27,12 @@
 namespace pl {
 
 static constexpr int kBM = 128;            // rows of D per tile (TMEM lanes)
-static constexpr int kEpiWarps = 16;
+static constexpr int kEpiWarps = 16;                   // TMA-fed launches
 static constexpr int kThreads = 64 + 32 * kEpiWarps;  // 18 warps
+// thin-input launches: 8 epilogue warps + 8 gather warps (two threads per A row)
+static constexpr int kThinEpiWarps = 8;
+static constexpr int kThinWarps = 8;
+static constexpr int kThinThreads = 64 + 32 * (kThinEpiWarps + kThinWarps);
 static constexpr int kMaxStages = 12;
 static constexpr int kMaxResBufs = 6;   // depth of the TMA residual ring
 
@@ -43,6 +47,7 @@ struct IgemmParams {
              // 2: thin input (C <= 4, one word per pixel): A tiles are gathered by producer warps
   const uint32_t* xw;  // mode 2: input words [N][H][W]
   int thin_r, thin_sw;
+  int b_resident;  // mode 2, one N tile: the whole packed filter stays in smem for the kernel's lifetime
   int H, W;
   FastDiv dQ, dPQ;
   int Q, PQ, S;
@@ -238,9 +243,8 @@ __device__ __noinline__ void store_group16(const IgemmParams& p, const uint32_t*
 // one-word-per-pixel input, all loads of a tile in flight at once, and store them into the
 // stage buffers in the 32-byte-swizzled K-major layout the MMA descriptors expect.  One
 // k-block (32 bytes) = 32 / (4 * TSW) filter rows.  No im2col matrix ever exists in HBM.
-static constexpr int kThinWarps = 4;
 template <int EPI, int TR = 0, int TSW = 0>
-__global__ void __launch_bounds__(kThreads + (TR > 0 ? 32 * kThinWarps : 0), 1)
+__global__ void __launch_bounds__(TR > 0 ? kThinThreads : kThreads, 1)
 igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
                 const __grid_constant__ CUtensorMap tmap_b,
                 const __grid_constant__ CUtensorMap tmap_y,
@@ -264,6 +268,7 @@ igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
   const uint32_t smem_res = smem_base + p.res_stage_off;
   const uint32_t tile_bytes = (uint32_t)(kBM * p.BN);
 
+  constexpr int EW = TR > 0 ? kThinEpiWarps : kEpiWarps;  // epilogue warps of this instantiation
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
   const int num_tiles = p.m_tiles * p.n_tiles;
@@ -274,16 +279,17 @@ igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
     if (EPI != EPI_GENERIC) tma_prefetch_desc(&tmap_y);
     if (EPI == EPI_I8_RELU_RES) tma_prefetch_desc(&tmap_r);
     for (int s = 0; s < p.stages; ++s) {
-      mbar_init(bar_full + 8 * s, TR > 0 ? 1 + 32 * kThinWarps : 1);  // TMA (B) + one arrival per A row
+      // TMA arrival (B, and A in the TMA modes) + one arrival per gathered A row
+      mbar_init(bar_full + 8 * s, TR > 0 ? (p.b_resident ? 0 : 1) + kBM : 1);
       mbar_init(bar_empty + 8 * s, 1);
     }
     for (int s = 0; s < 2; ++s) {
       mbar_init(bar_tfull + 8 * s, 1);
-      mbar_init(bar_tempty + 8 * s, 32 * kEpiWarps);
+      mbar_init(bar_tempty + 8 * s, 32 * EW);
     }
     for (int s = 0; s < kMaxResBufs; ++s) {
       mbar_init(bar_rfull + 8 * s, 1);
-      mbar_init(bar_rempty + 8 * s, 32 * kEpiWarps);
+      mbar_init(bar_rempty + 8 * s, 32 * EW);
     }
     fence_barrier_init();
   }
@@ -296,94 +302,117 @@ igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
   tc_fence_after();
   const uint32_t tmem_base = tmem_base_slot;
 
+  // Warps 0 and 1 run their loops CONVERGED (all 32 lanes wait on the barriers and keep
+  // the loop state, which therefore lives in uniform registers) and hand the issue
+  // instructions to one elected lane.  Wrapping the whole loop in `if (lane == 0)` instead
+  // makes the compiler re-uniformise every TMA / MMA operand with an ELECT + BRA.U.ANY
+  // loop: ~85 instructions and ~640 cycles per k-block, which bounded every 3x3 layer.
   if (warp == 0) {
     // ===================== TMA producer =====================
-    if (lane == 0) {
-      int stage = 0;
-      uint32_t phase = 0;
-      const uint32_t tx = p.tx_bytes;
-      int rb = 0;
-      uint32_t rphase = 0;
-      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
-        const int tn = tile % p.n_tiles, tm = tile / p.n_tiles;
-        const int m0 = tm * kBM, n0 = tn * p.BN;
-        if (EPI == EPI_I8_RELU_RES) {
-          // residual tile first: it is the largest load of a 1x1 expand layer
-          mbar_wait(bar_rempty + 8 * rb, rphase ^ 1);
+    int stage = 0;
+    uint32_t phase = 0;
+    const uint32_t tx = p.tx_bytes;
+    int rb = 0;
+    uint32_t rphase = 0;
+    if (TR > 0 && p.b_resident) {
+      // thin mode, single N tile: every k-block of the filter is loaded exactly once
+      if (elect_one()) {
+        mbar_arrive_expect_tx(bar_rfull, (uint32_t)p.num_kb * (uint32_t)(p.BN * p.BK));
+        for (int kb = 0; kb < p.num_kb; ++kb)
+          tma_load_2d(smem_b + kb * p.b_stage_bytes, &tmap_b, bar_rfull, kb * p.BK, 0);
+      }
+      __syncwarp();
+    }
+    for (int tile = blockIdx.x; tile < num_tiles && !(TR > 0 && p.b_resident); tile += gridDim.x) {
+      const int tn = tile % p.n_tiles, tm = tile / p.n_tiles;
+      const int m0 = tm * kBM, n0 = tn * p.BN;
+      if (EPI == EPI_I8_RELU_RES) {
+        // residual tile first: it is the largest load of a 1x1 expand layer
+        mbar_wait(bar_rempty + 8 * rb, rphase ^ 1);
+        if (elect_one()) {
           mbar_arrive_expect_tx(bar_rfull + 8 * rb, tile_bytes);
           for (int j = 0; j < p.panels; ++j)
             tma_load_2d(smem_res + rb * tile_bytes + j * (kBM * p.PW), &tmap_r, bar_rfull + 8 * rb,
                         n0 + j * p.PW, m0);
-          if (++rb == p.res_bufs) { rb = 0; rphase ^= 1; }
         }
-        int bw = 0, bh = 0, bn = 0;
-        if (p.mode == 1) {
-          bn = m0 / p.PQ;
-          const int rem = m0 - bn * p.PQ;
-          const int op = rem / p.Q, oq = rem - op * p.Q;
-          bw = oq * p.sw - p.pl_;
-          bh = op * p.sh - p.pt;
-        }
-        int tap = 0, cb = 0;
-        for (int kb = 0; kb < p.num_kb; ++kb) {
-          mbar_wait(bar_empty + 8 * stage, phase ^ 1);
+        __syncwarp();
+        if (++rb == p.res_bufs) { rb = 0; rphase ^= 1; }
+      }
+      int bw = 0, bh = 0, bn = 0;
+      if (p.mode == 1) {
+        bn = m0 / p.PQ;
+        const int rem = m0 - bn * p.PQ;
+        const int op = rem / p.Q, oq = rem - op * p.Q;
+        bw = oq * p.sw - p.pl_;
+        bh = op * p.sh - p.pt;
+      }
+      int r = 0, sx = 0, cb = 0;  // filter tap (r, sx) and channel block of the k-block
+      for (int kb = 0; kb < p.num_kb; ++kb) {
+        mbar_wait(bar_empty + 8 * stage, phase ^ 1);
+        if (elect_one()) {
           mbar_arrive_expect_tx(bar_full + 8 * stage, tx);
           const uint32_t dst_a = smem_a + stage * p.a_stage_bytes;
           const uint32_t dst_b = smem_b + stage * p.b_stage_bytes;
           if (TR > 0) {
             // A arrives from the gather warps
           } else if (p.mode == 1) {
-            const int r = tap / p.S, s = tap - r * p.S;
             tma_load_im2col_4d(dst_a, &tmap_a, bar_full + 8 * stage, cb * p.BK, bw, bh, bn,
-                               (uint16_t)(s * p.dw), (uint16_t)(r * p.dh));
+                               (uint16_t)(sx * p.dw), (uint16_t)(r * p.dh));
           } else {
             tma_load_2d(dst_a, &tmap_a, bar_full + 8 * stage, kb * p.BK, m0);
           }
           tma_load_2d(dst_b, &tmap_b, bar_full + 8 * stage, kb * p.BK, n0);
-          if (++cb == p.cblocks) { cb = 0; ++tap; }
-          if (++stage == p.stages) { stage = 0; phase ^= 1; }
         }
+        __syncwarp();
+        if (++cb == p.cblocks) {
+          cb = 0;
+          if (++sx == p.S) { sx = 0; ++r; }
+        }
+        if (++stage == p.stages) { stage = 0; phase ^= 1; }
       }
     }
   } else if (warp == 1) {
     // ===================== MMA issuer =====================
-    if (lane == 0) {
-      const uint32_t idesc = make_idesc_i8((uint32_t)p.BN);
-      const uint64_t desc_hi = make_smem_desc_base((uint32_t)p.BK);
-      const int ksteps = p.BK / 32;
-      int stage = 0;
-      uint32_t phase = 0;
-      int as = 0;
-      uint32_t aphase = 0;
-      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
-        mbar_wait(bar_tempty + 8 * as, aphase ^ 1);
+    const uint32_t idesc = make_idesc_i8((uint32_t)p.BN);
+    const uint64_t desc_hi = make_smem_desc_base((uint32_t)p.BK);
+    const int ksteps = p.BK / 32;
+    int stage = 0;
+    uint32_t phase = 0;
+    int as = 0;
+    uint32_t aphase = 0;
+    const bool bres = TR > 0 && p.b_resident;
+    if (bres) mbar_wait(bar_rfull, 0);
+    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+      mbar_wait(bar_tempty + 8 * as, aphase ^ 1);
+      tc_fence_after();
+      const uint32_t d_tmem = tmem_base + (uint32_t)as * p.acc_stride;
+      for (int kb = 0; kb < p.num_kb; ++kb) {
+        mbar_wait(bar_full + 8 * stage, phase);
         tc_fence_after();
-        const uint32_t d_tmem = tmem_base + (uint32_t)as * p.acc_stride;
-        for (int kb = 0; kb < p.num_kb; ++kb) {
-          mbar_wait(bar_full + 8 * stage, phase);
-          tc_fence_after();
+        if (elect_one()) {
           const uint64_t da = desc_hi | (uint64_t)(((smem_a + stage * p.a_stage_bytes) >> 4) & 0x3fff);
-          const uint64_t db = desc_hi | (uint64_t)(((smem_b + stage * p.b_stage_bytes) >> 4) & 0x3fff);
+          const uint64_t db = desc_hi | (uint64_t)(((smem_b + (bres ? kb : stage) * p.b_stage_bytes) >> 4) & 0x3fff);
           for (int k = 0; k < ksteps; ++k)
-            umma_i8(d_tmem, da + (uint64_t)(k * 2), db + (uint64_t)(k * 2), idesc,
-                    (uint32_t)((kb | k) != 0));
+            umma_i8(d_tmem, da + (uint64_t)(k * 2), db + (uint64_t)(k * 2), idesc, (uint32_t)((kb | k) != 0));
           umma_commit(bar_empty + 8 * stage);
-          if (++stage == p.stages) { stage = 0; phase ^= 1; }
+          if (kb == p.num_kb - 1) umma_commit(bar_tfull + 8 * as);
         }
-        umma_commit(bar_tfull + 8 * as);
-        if (++as == 2) { as = 0; aphase ^= 1; }
+        __syncwarp();
+        if (++stage == p.stages) { stage = 0; phase ^= 1; }
       }
+      if (++as == 2) { as = 0; aphase ^= 1; }
     }
-  } else if (TR > 0 && warp >= 2 + kEpiWarps) {
-    // ===================== thin-input gather (warps 18..21) =====================
+  } else if (TR > 0 && warp >= 2 + EW) {
+    // ===================== thin-input gather (8 warps, two threads per A row) =====================
     constexpr int R_ = TR > 0 ? TR : 1, SW_ = TSW > 0 ? TSW : 4;
     constexpr int RPK = 8 / SW_;                  // filter rows per 32-byte k-block
     constexpr int NKB = (R_ + RPK - 1) / RPK;
-    const int prow = (int)threadIdx.x - (64 + 32 * kEpiWarps);  // A row of this thread
+    constexpr int MYKB = (NKB + 1) / 2;           // k-blocks per thread: kb = half, half + 2, ...
+    const int g = (int)threadIdx.x - (64 + 32 * EW);
+    const int prow = g & (kBM - 1), half = g >> 7;
     const uint32_t rowoff = (uint32_t)prow * 32u;
     const uint32_t swx = (rowoff >> 7) & 1u;      // 32-byte swizzle: chunk ^= bit 7 of the offset
-    int stage = 0;
-    uint32_t phase = 0;
+    uint32_t base = 0;                            // running k-block count -> ring stage and phase
     for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
       const int tm = tile / p.n_tiles;
       const uint32_t m = (uint32_t)(tm * kBM + prow);
@@ -394,48 +423,65 @@ igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
       const int oq = (int)(rem - op * (uint32_t)p.Q);
       const int ih0 = (int)op * p.sh - p.pt, iw0 = oq * p.sw - p.pl_;
       const uint32_t* img = p.xw + (size_t)n * (size_t)(p.H * p.W);
-      // the whole window first: R_ x SW_ independent loads in flight per thread
-      uint32_t xr[R_][SW_];
+      // zero padding = load a clamped (always valid) address and AND the word away: one
+      // mask per window column, one per row, a single LOP3 applies both
+      const uint32_t* cp[SW_];
+      uint32_t cm[SW_];
 #pragma unroll
-      for (int r = 0; r < R_; ++r) {
-        const int ih = ih0 + r;
-        const bool rok = mok && ih >= 0 && ih < p.H;
-        const uint32_t* row = img + ih * p.W;
+      for (int j = 0; j < SW_; ++j) {
+        const int iw = iw0 + j, c = min(max(iw, 0), p.W - 1);
+        cp[j] = img + c;
+        cm[j] = (iw == c && mok) ? 0xffffffffu : 0u;
+      }
+      // this thread's words: all loads in flight before the first use
+      uint32_t xr[MYKB * RPK][SW_];
 #pragma unroll
-        for (int j = 0; j < SW_; ++j) {
-          const int iw = iw0 + j;
-          xr[r][j] = (rok && iw >= 0 && iw < p.W) ? __ldg(row + iw) : 0u;
+      for (int t = 0; t < MYKB * RPK; ++t) {
+        const int r = (half + 2 * (t / RPK)) * RPK + (t % RPK);  // filter row of slot t
+        const int ih = ih0 + r, hc = min(max(ih, 0), p.H - 1);
+        const uint32_t rm = (ih == hc && r < R_) ? 0xffffffffu : 0u;
+        const uint32_t roff = (uint32_t)(hc * p.W);
+#pragma unroll
+        for (int j = 0; j < SW_; ++j) xr[t][j] = __ldg(cp[j] + roff) & cm[j] & rm;
+      }
+      // write this thread's k-blocks behind ONE proxy fence, then publish them
+      bool mine[MYKB];
+#pragma unroll
+      for (int i = 0; i < MYKB; ++i) {
+        const int kb = half + 2 * i;
+        mine[i] = kb < NKB;
+        if (!mine[i]) continue;
+        const uint32_t cnt = base + (uint32_t)kb;
+        const uint32_t st = cnt % (uint32_t)p.stages, ph = (cnt / (uint32_t)p.stages) & 1u;
+        mbar_wait(bar_empty + 8 * st, ph ^ 1);
+        const uint32_t dst = smem_a + st * p.a_stage_bytes + rowoff;
+        if constexpr (SW_ == 8) {
+          st_shared_v4(dst + ((0u ^ swx) << 4), xr[i][0], xr[i][1], xr[i][2], xr[i][3]);
+          st_shared_v4(dst + ((1u ^ swx) << 4), xr[i][4], xr[i][5], xr[i][6], xr[i][7]);
+        } else {
+          st_shared_v4(dst + ((0u ^ swx) << 4), xr[2 * i][0], xr[2 * i][1], xr[2 * i][2], xr[2 * i][3]);
+          st_shared_v4(dst + ((1u ^ swx) << 4), xr[2 * i + 1][0], xr[2 * i + 1][1], xr[2 * i + 1][2],
+                       xr[2 * i + 1][3]);
         }
       }
+      fence_proxy_async();  // generic-proxy stores -> visible to the tensor core's async proxy
 #pragma unroll
-      for (int kb = 0; kb < NKB; ++kb) {
-        mbar_wait(bar_empty + 8 * stage, phase ^ 1);
-        const uint32_t dst = smem_a + stage * p.a_stage_bytes + rowoff;
-#pragma unroll
-        for (int c = 0; c < 2; ++c) {
-          uint32_t w0, w1, w2, w3;
-          if constexpr (SW_ == 8) {
-            w0 = xr[kb][4 * c]; w1 = xr[kb][4 * c + 1]; w2 = xr[kb][4 * c + 2]; w3 = xr[kb][4 * c + 3];
-          } else {
-            const int r = 2 * kb + c;
-            if (r < R_) { w0 = xr[r < R_ ? r : 0][0]; w1 = xr[r < R_ ? r : 0][1]; w2 = xr[r < R_ ? r : 0][2]; w3 = xr[r < R_ ? r : 0][3]; }
-            else { w0 = w1 = w2 = w3 = 0u; }
-          }
-          st_shared_v4(dst + (((uint32_t)c ^ swx) << 4), w0, w1, w2, w3);
-        }
-        fence_proxy_async();  // generic-proxy stores -> visible to the tensor core's async proxy
-        mbar_arrive(bar_full + 8 * stage);
-        if (++stage == p.stages) { stage = 0; phase ^= 1; }
+      for (int i = 0; i < MYKB; ++i) {
+        if (!mine[i]) continue;
+        const uint32_t cnt = base + (uint32_t)(half + 2 * i);
+        mbar_arrive(bar_full + 8 * (cnt % (uint32_t)p.stages));
       }
+      base += NKB;
     }
   } else {
     // ===================== epilogue (warps 2..17) =====================
     // warp w owns TMEM lanes [32*(w%4), +32) (hardware rule) and the 16-column units
-    // cq, cq+4, cq+8, cq+12 of the tile
+    // cq, cq+CQ, cq+2CQ, ... of the tile (CQ = epilogue warps / 4)
     const int quarter = warp & 3;
     const int cq = (warp - 2) >> 2;
     const int etid = threadIdx.x - 64;
     constexpr bool kFast = (EPI != EPI_GENERIC);  // int8 paths: swizzled smem staging + TMA store
+    constexpr int CQ = EW / 4;  // warps per TMEM lane quarter = column groups
     const int units = p.BN >> 4;
     const uint32_t rowoff = (uint32_t)((quarter * 32 + lane) * p.PW);
     const uint32_t swx = (rowoff >> 7) & p.swz_mask;
@@ -455,7 +501,7 @@ igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
       }
     };
     if ((int)blockIdx.x < num_tiles) stage_scale_bias(blockIdx.x, 0);
-    asm volatile("bar.sync 1, %0;" ::"n"(32 * kEpiWarps) : "memory");
+    asm volatile("bar.sync 1, %0;" ::"n"(32 * EW) : "memory");
     for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
       const int tn = tile % p.n_tiles, tm = tile / p.n_tiles;
       const long long row = (long long)tm * kBM + quarter * 32 + lane;
@@ -471,11 +517,12 @@ igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
       uint32_t accb[2][16];
       if (cq < units) tmem_ld_32x32b_x16(t_addr + (uint32_t)(cq * 16), accb[0]);
 #pragma unroll
-      for (int i = 0; i < 4; ++i) {
-        const int u = cq + 4 * i;
+      for (int i = 0; i < 16 / CQ; ++i) {
+        const int u = cq + CQ * i;
         if (u < units) {  // warp-uniform
           tmem_ld_wait();
-          if (i < 3 && u + 4 < units) tmem_ld_32x32b_x16(t_addr + (uint32_t)((u + 4) * 16), accb[(i + 1) & 1]);
+          if (i < 16 / CQ - 1 && u + CQ < units)
+            tmem_ld_32x32b_x16(t_addr + (uint32_t)((u + CQ) * 16), accb[(i + 1) & 1]);
           uint32_t(&acc)[16] = accb[i & 1];
           const uint32_t col = (uint32_t)(u * 16);
           if (kFast) {
@@ -517,27 +564,39 @@ igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
       if (kFast) {
         // the store issued one tile ago has long drained its staging buffer: after the
         // barrier every thread may write it again
-        if (etid == 0 && p.out_bufs == 2) bulk_wait_group_read<0>();
+        if (warp == 2 && p.out_bufs == 2) {  // same (elected) lane that committed the store
+          if (elect_one()) bulk_wait_group_read<0>();
+          __syncwarp();
+        }
         // generic-proxy smem writes -> visible to the TMA engine, then one thread stores
         fence_proxy_async();
       }
-      asm volatile("bar.sync 2, %0;" ::"n"(32 * kEpiWarps) : "memory");
+      asm volatile("bar.sync 2, %0;" ::"n"(32 * EW) : "memory");
       if (kFast) {
-        if (etid == 0) {
-          for (int j = 0; j < p.panels; ++j)
-            tma_store_2d(&tmap_y, out_tile + (uint32_t)(j * kBM * p.PW), n0 + j * p.PW, tm * kBM);
-          bulk_commit_group();
+        if (warp == 2) {
+          if (elect_one()) {
+            for (int j = 0; j < p.panels; ++j)
+              tma_store_2d(&tmap_y, out_tile + (uint32_t)(j * kBM * p.PW), n0 + j * p.PW, tm * kBM);
+            bulk_commit_group();
+          }
+          __syncwarp();
         }
         if (p.out_bufs == 2) {
           ob ^= 1;
         } else {
           // single staging buffer (smem-tight launches): drain it before the next tile
-          if (etid == 0) bulk_wait_group_read<0>();
-          asm volatile("bar.sync 1, %0;" ::"n"(32 * kEpiWarps) : "memory");
+          if (warp == 2) {
+            if (elect_one()) bulk_wait_group_read<0>();
+            __syncwarp();
+          }
+          asm volatile("bar.sync 1, %0;" ::"n"(32 * EW) : "memory");
         }
       }
     }
-    if (kFast && etid == 0) bulk_wait_group<0>();
+    if (kFast && warp == 2) {
+      if (elect_one()) bulk_wait_group<0>();
+      __syncwarp();
+    }
   }
 
   tc_fence_before();
@@ -729,7 +788,7 @@ int launch_one(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& 
                                     (int)(216 * 1024)));
     configured = true;
   }
-  const int threads = kThreads + (TR > 0 ? 32 * kThinWarps : 0);
+  const int threads = TR > 0 ? kThinThreads : kThreads;
   igemm_i8_kernel<EPI, TR, TSW><<<grid, threads, smem, (cudaStream_t)stream>>>(ta, tb, ty, tr, p);
   ++g_launches;
   return launch_status();
@@ -813,13 +872,23 @@ int launch_igemm(const CUtensorMap& ta, const CUtensorMap& tb, IgemmParams& p, p
     }
     extra = p.out_bufs * tile + (p.tma_res ? p.res_bufs * tile : 0);
   }
-  int stages = (budget - extra) / stage_bytes;
-  if (stages > kMaxStages) stages = kMaxStages;
-  if (stages < 2) return PL_ERR_UNSUPPORTED;
+  p.b_resident = (p.mode == 2 && p.n_tiles == 1) ? 1 : 0;
+  int stages;
+  size_t ring_bytes;
+  if (p.b_resident) {
+    stages = (budget - extra - p.num_kb * (int)p.b_stage_bytes) / (int)p.a_stage_bytes;
+    if (stages > kMaxStages) stages = kMaxStages;
+    ring_bytes = (size_t)stages * p.a_stage_bytes + (size_t)p.num_kb * p.b_stage_bytes;
+  } else {
+    stages = (budget - extra) / stage_bytes;
+    if (stages > kMaxStages) stages = kMaxStages;
+    ring_bytes = (size_t)stages * stage_bytes;
+  }
+  if (stages < 2 || (p.mode == 2 && stages < p.num_kb)) return PL_ERR_UNSUPPORTED;
   p.stages = stages;
-  p.out_stage_off = (uint32_t)(stages * stage_bytes);
+  p.out_stage_off = (uint32_t)ring_bytes;
   p.res_stage_off = p.out_stage_off + (uint32_t)(p.out_bufs * tile);
-  const size_t smem = (size_t)stages * stage_bytes + extra + 1024;
+  const size_t smem = ring_bytes + extra + 1024;
   if (p.mode == 2) {
     // thin-input gather mode: (filter rows, window words) instantiations
     const int key = p.thin_r * 16 + p.thin_sw;

@@ -17,6 +17,7 @@ pl = ge.load_package().capi
 LAYERS = {
     # name: (H, W, C, K, k, stride, pad, act, residual)
     "stem7x7": (224, 224, 3, 64, 7, 2, 3, "relu", False),
+    "stem3x3": (224, 224, 3, 32, 3, 2, 1, "relu", False),
     "r2_1x1_64_256": (56, 56, 64, 256, 1, 1, 0, "none", False),
     "r2_1x1_64_256_res": (56, 56, 64, 256, 1, 1, 0, "relu", True),
     "r2_1x1_64_64": (56, 56, 64, 64, 1, 1, 0, "relu", False),
@@ -40,7 +41,7 @@ ACT = {"none": pl.ACT_NONE, "relu": pl.ACT_RELU}
 def bench(name, batch, iters, nsets):
     H, W, C, K, k, st, pad, act, res = LAYERS[name]
     dev = "cuda"
-    ld = (C + 15) // 16 * 16
+    ld = 4 if C <= 4 else (C + 15) // 16 * 16
     P = (H + 2 * pad - k) // st + 1
     g = torch.Generator(device=dev).manual_seed(1)
     xs = [torch.randint(-127, 128, (batch, H, W, ld), dtype=torch.int8, device=dev, generator=g) for _ in range(nsets)]
@@ -48,8 +49,11 @@ def bench(name, batch, iters, nsets):
     sc = torch.full((K,), 1e-3, device=dev)
     bs = torch.zeros((K,), device=dev)
     dw = res == "dw"
+    thin = (not dw) and C <= 4
     if dw:
         w = torch.randint(-127, 128, (K, k, k), dtype=torch.int8, device=dev, generator=g)
+    elif thin:
+        w = pl.pack_thin_conv_weight(torch.randint(-127, 128, (K, k, k, C), dtype=torch.int8, device=dev, generator=g))
     else:
         w = pl.pack_conv_weight(torch.randint(-127, 128, (K, k, k, C), dtype=torch.int8, device=dev, generator=g))
     rs = [torch.randint(-127, 128, (batch, P, P, K), dtype=torch.int8, device=dev, generator=g) for _ in range(nsets)] if res is True else None
@@ -58,6 +62,8 @@ def bench(name, batch, iters, nsets):
         j = i % nsets
         if dw:
             pl.dwconv2d(xs[j], w, sc, bs, k, k, (st, st), (pad,) * 4, act=ACT[act], y=ys[j], Cc=C)
+        elif thin:
+            pl.thin_conv2d(xs[j], w, K, k, k, C, sc, bs, (st, st), (pad,) * 4, act=ACT[act], y=ys[j])
         else:
             pl.conv2d(xs[j], w, K, k, k, sc, bs, (st, st), (pad,) * 4, act=ACT[act], y=ys[j], Cc=C,
                       residual=None if rs is None else rs[j], res_scale=0.5)
