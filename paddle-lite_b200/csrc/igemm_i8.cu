@@ -47,6 +47,7 @@ struct IgemmParams {
              // 2: thin input (C <= 4, one word per pixel): A tiles are gathered by producer warps
   const uint32_t* xw;  // mode 2: input words [N][H][W]
   int thin_r, thin_sw;
+  int dbg_ashift, dbg_baseoff;  // experiment: MMA A-descriptor starts `dbg_ashift` rows into the stage
   int b_resident;  // mode 2, one N tile: the whole packed filter stays in smem for the kernel's lifetime
   int H, W;
   FastDiv dQ, dPQ;
@@ -309,23 +310,28 @@ igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
   // loop: ~85 instructions and ~640 cycles per k-block, which bounded every 3x3 layer.
   if (warp == 0) {
     // ===================== TMA producer =====================
+    // all loop state is incremental (no multiplies, no parameter reloads per k-block):
+    // this warp's issue latency per k-block bounds the short-K 3x3 layers
+    const uint32_t tx = p.tx_bytes, a_bytes = p.a_stage_bytes, b_bytes = p.b_stage_bytes;
+    const int stages = p.stages, num_kb = p.num_kb, BK = p.BK, S = p.S, cspan = p.cblocks * p.BK;
+    const int mode = p.mode, n_tiles = p.n_tiles, BN = p.BN;
+    const uint16_t dwv = (uint16_t)p.dw, dhv = (uint16_t)p.dh;
     int stage = 0;
     uint32_t phase = 0;
-    const uint32_t tx = p.tx_bytes;
+    uint32_t full_b = bar_full, empty_b = bar_empty, dst_a = smem_a, dst_b = smem_b;
     int rb = 0;
     uint32_t rphase = 0;
     if (TR > 0 && p.b_resident) {
       // thin mode, single N tile: every k-block of the filter is loaded exactly once
       if (elect_one()) {
-        mbar_arrive_expect_tx(bar_rfull, (uint32_t)p.num_kb * (uint32_t)(p.BN * p.BK));
-        for (int kb = 0; kb < p.num_kb; ++kb)
-          tma_load_2d(smem_b + kb * p.b_stage_bytes, &tmap_b, bar_rfull, kb * p.BK, 0);
+        mbar_arrive_expect_tx(bar_rfull, (uint32_t)num_kb * (uint32_t)(BN * BK));
+        for (int kb = 0; kb < num_kb; ++kb)
+          tma_load_2d(smem_b + kb * b_bytes, &tmap_b, bar_rfull, kb * BK, 0);
       }
-      __syncwarp();
     }
     for (int tile = blockIdx.x; tile < num_tiles && !(TR > 0 && p.b_resident); tile += gridDim.x) {
-      const int tn = tile % p.n_tiles, tm = tile / p.n_tiles;
-      const int m0 = tm * kBM, n0 = tn * p.BN;
+      const int tn = tile % n_tiles, tm = tile / n_tiles;
+      const int m0 = tm * kBM, n0 = tn * BN;
       if (EPI == EPI_I8_RELU_RES) {
         // residual tile first: it is the largest load of a 1x1 expand layer
         mbar_wait(bar_rempty + 8 * rb, rphase ^ 1);
@@ -335,70 +341,86 @@ igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
             tma_load_2d(smem_res + rb * tile_bytes + j * (kBM * p.PW), &tmap_r, bar_rfull + 8 * rb,
                         n0 + j * p.PW, m0);
         }
-        __syncwarp();
         if (++rb == p.res_bufs) { rb = 0; rphase ^= 1; }
       }
       int bw = 0, bh = 0, bn = 0;
-      if (p.mode == 1) {
+      if (mode == 1) {
         bn = m0 / p.PQ;
         const int rem = m0 - bn * p.PQ;
         const int op = rem / p.Q, oq = rem - op * p.Q;
         bw = oq * p.sw - p.pl_;
         bh = op * p.sh - p.pt;
       }
-      int r = 0, sx = 0, cb = 0;  // filter tap (r, sx) and channel block of the k-block
-      for (int kb = 0; kb < p.num_kb; ++kb) {
-        mbar_wait(bar_empty + 8 * stage, phase ^ 1);
+      int kc = 0, cbk = 0, sx = 0;      // K coordinate of B, channel offset inside the tap, tap column
+      uint16_t offw = 0, offh = 0;      // im2col filter offsets of the tap
+      for (int kb = 0; kb < num_kb; ++kb) {
+        mbar_wait(empty_b, phase ^ 1);
         if (elect_one()) {
-          mbar_arrive_expect_tx(bar_full + 8 * stage, tx);
-          const uint32_t dst_a = smem_a + stage * p.a_stage_bytes;
-          const uint32_t dst_b = smem_b + stage * p.b_stage_bytes;
+          mbar_arrive_expect_tx(full_b, tx);
           if (TR > 0) {
             // A arrives from the gather warps
-          } else if (p.mode == 1) {
-            tma_load_im2col_4d(dst_a, &tmap_a, bar_full + 8 * stage, cb * p.BK, bw, bh, bn,
-                               (uint16_t)(sx * p.dw), (uint16_t)(r * p.dh));
+          } else if (mode == 1) {
+            tma_load_im2col_4d(dst_a, &tmap_a, full_b, cbk, bw, bh, bn, offw, offh);
           } else {
-            tma_load_2d(dst_a, &tmap_a, bar_full + 8 * stage, kb * p.BK, m0);
+            tma_load_2d(dst_a, &tmap_a, full_b, kc, m0);
           }
-          tma_load_2d(dst_b, &tmap_b, bar_full + 8 * stage, kb * p.BK, n0);
+          tma_load_2d(dst_b, &tmap_b, full_b, kc, n0);
         }
-        __syncwarp();
-        if (++cb == p.cblocks) {
-          cb = 0;
-          if (++sx == p.S) { sx = 0; ++r; }
+        kc += BK;
+        cbk += BK;
+        if (cbk == cspan) {
+          cbk = 0;
+          offw += dwv;
+          if (++sx == S) { sx = 0; offw = 0; offh += dhv; }
         }
-        if (++stage == p.stages) { stage = 0; phase ^= 1; }
+        ++stage; full_b += 8; empty_b += 8; dst_a += a_bytes; dst_b += b_bytes;
+        if (stage == stages) {
+          stage = 0; phase ^= 1;
+          full_b = bar_full; empty_b = bar_empty; dst_a = smem_a; dst_b = smem_b;
+        }
       }
     }
   } else if (warp == 1) {
     // ===================== MMA issuer =====================
     const uint32_t idesc = make_idesc_i8((uint32_t)p.BN);
     const uint64_t desc_hi = make_smem_desc_base((uint32_t)p.BK);
-    const int ksteps = p.BK / 32;
+    const int ksteps = p.BK / 32, stages = p.stages, num_kb = p.num_kb;
+    const uint32_t a_step = p.a_stage_bytes >> 4, b_step = p.b_stage_bytes >> 4;
+    const uint32_t a_lo0 = smem_a >> 4, b_lo0 = smem_b >> 4;  // shared addresses < 256 KB: 14 bits
+    const bool bres = TR > 0 && p.b_resident;
     int stage = 0;
     uint32_t phase = 0;
+    uint32_t full_b = bar_full, empty_b = bar_empty, a_lo = a_lo0, b_lo = b_lo0;
     int as = 0;
     uint32_t aphase = 0;
-    const bool bres = TR > 0 && p.b_resident;
     if (bres) mbar_wait(bar_rfull, 0);
     for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
       mbar_wait(bar_tempty + 8 * as, aphase ^ 1);
       tc_fence_after();
       const uint32_t d_tmem = tmem_base + (uint32_t)as * p.acc_stride;
-      for (int kb = 0; kb < p.num_kb; ++kb) {
-        mbar_wait(bar_full + 8 * stage, phase);
+      if (bres) b_lo = b_lo0;
+      for (int kb = 0; kb < num_kb; ++kb) {
+        mbar_wait(full_b, phase);
         tc_fence_after();
         if (elect_one()) {
-          const uint64_t da = desc_hi | (uint64_t)(((smem_a + stage * p.a_stage_bytes) >> 4) & 0x3fff);
-          const uint64_t db = desc_hi | (uint64_t)(((smem_b + (bres ? kb : stage) * p.b_stage_bytes) >> 4) & 0x3fff);
+          uint64_t da = desc_hi | (uint64_t)a_lo;
+          const uint64_t db = desc_hi | (uint64_t)b_lo;
+          if (p.dbg_ashift) {  // descriptor-semantics experiment (tools/dbg_rowshift.py)
+            const uint32_t start = (a_lo << 4) + (uint32_t)(p.dbg_ashift * p.BK);
+            da = desc_hi | (uint64_t)((start >> 4) & 0x3fff);
+            if (p.dbg_baseoff) da |= (uint64_t)((start >> 7) & 7u) << 49;
+          }
           for (int k = 0; k < ksteps; ++k)
             umma_i8(d_tmem, da + (uint64_t)(k * 2), db + (uint64_t)(k * 2), idesc, (uint32_t)((kb | k) != 0));
-          umma_commit(bar_empty + 8 * stage);
-          if (kb == p.num_kb - 1) umma_commit(bar_tfull + 8 * as);
+          umma_commit(empty_b);
+          if (kb == num_kb - 1) umma_commit(bar_tfull + 8 * as);
         }
-        __syncwarp();
-        if (++stage == p.stages) { stage = 0; phase ^= 1; }
+        ++stage; full_b += 8; empty_b += 8; a_lo += a_step; b_lo += b_step;
+        if (stage == stages) {
+          stage = 0; phase ^= 1;
+          full_b = bar_full; empty_b = bar_empty; a_lo = a_lo0;
+          if (!bres) b_lo = b_lo0;
+        }
       }
       if (++as == 2) { as = 0; aphase ^= 1; }
     }
@@ -873,6 +895,8 @@ int launch_igemm(const CUtensorMap& ta, const CUtensorMap& tb, IgemmParams& p, p
     extra = p.out_bufs * tile + (p.tma_res ? p.res_bufs * tile : 0);
   }
   p.b_resident = (p.mode == 2 && p.n_tiles == 1) ? 1 : 0;
+  p.dbg_ashift = env_int("PL_DBG_ASHIFT", 0);
+  p.dbg_baseoff = env_int("PL_DBG_BASEOFF", 0);
   int stages;
   size_t ring_bytes;
   if (p.b_resident) {
