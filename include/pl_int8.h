@@ -187,6 +187,9 @@ const char* pl_version(void);
  * tcgen05.mma kind::i8 per CTA on `ctas` CTAs from resident smem; returns 0
  * and leaves a checksum in out[0] so the work cannot be elided. */
 int pl_i8_mma_peak(int ctas, int iters, int bn, int32_t* out, pl_stream_t stream);
+/* same, with the operand layout of a 32 / 64 / 128-byte K block (one iteration = row_bytes/32
+ * MMAs): measures how the smem swizzle mode and N change the cost of one tcgen05.mma */
+int pl_i8_mma_probe(int ctas, int iters, int bn, int row_bytes, int32_t* out, pl_stream_t stream);
 
 #ifdef __cplusplus
 }

@@ -338,4 +338,4 @@ def measure_i8_mma_peak(iters=20000, bn=256):
     i8_mma_peak(ctas, iters, bn)
     b.record()
     torch.cuda.synchronize()
-    return ctas * iters * 4 * 2.0 * 128 * bn * 32 / (a.elapsed_time(b) * 1e-3) / 1e12  # 4 K=32 MMAs per iteration
+    return ctas * iters * 8 * 2.0 * 128 * bn * 32 / (a.elapsed_time(b) * 1e-3) / 1e12  # 8 K=32 MMAs per iteration

@@ -35,6 +35,7 @@ static constexpr int kThinWarps = 8;
 static constexpr int kThinThreads = 64 + 32 * (kThinEpiWarps + kThinWarps);
 static constexpr int kMaxStages = 12;
 static constexpr int kMaxResBufs = 6;   // depth of the TMA residual ring
+static constexpr int kHaloBufs = 2;     // mode 3: input halo tiles in flight
 
 enum { EPI_GENERIC = 0, EPI_I8_RELU = 1, EPI_I8_SIGNED = 2, EPI_I8_RELU_RES = 3 };
 
@@ -45,8 +46,18 @@ struct IgemmParams {
   int num_kb, cblocks;
   int mode;  // 0: A is a [M, K] matrix (tiled TMA); 1: A is NHWC, im2col TMA;
              // 2: thin input (C <= 4, one word per pixel): A tiles are gathered by producer warps
+             // 3: halo reuse (stride-1 R x S conv): a tile is `hk` whole output rows of one image on
+             //    the padded grid (width WP = Q + S - 1); ONE tiled TMA load per channel block brings
+             //    the (hk + R - 1) x WP input pixels, and tap (r, s) is the same smem tile read
+             //    through an MMA descriptor that starts (r * WP + s) rows later
+  int hk, WP, bands, R, P;   // mode 3
+  int halo_m_tiles;          // set before common_setup: tiles along M in halo mode
+  uint32_t a_halo_bytes, a_halo_tx;
+  uint32_t a_region_bytes;   // bytes of the A stage ring / halo buffers in front of the B ring
+  FastDiv dBands, dWP;
   const uint32_t* xw;  // mode 2: input words [N][H][W]
   int thin_r, thin_sw;
+  int dbg_flags;  // timing experiments (PL_DBG_FLAGS): 1 skip epilogue body, 2 skip MMA issue, 4 skip B loads, 8 skip A loads
   int dbg_ashift, dbg_baseoff;  // experiment: MMA A-descriptor starts `dbg_ashift` rows into the stage
   int b_resident;  // mode 2, one N tile: the whole packed filter stays in smem for the kernel's lifetime
   int H, W;
@@ -66,6 +77,10 @@ struct IgemmParams {
   int PW, panels, pw_shift;
   uint32_t swz_mask;                 // 7 / 3 / 1 / 0 for 128 / 64 / 32 / 16-byte panel rows
   uint32_t out_stage_off, res_stage_off;  // byte offsets from the 1024-aligned smem base
+  // folded scale / bias in smem: the vectors of ALL n-tiles staged once per CTA (sb_all), or,
+  // for very wide outputs, two 256-entry buffers refilled per tile
+  uint32_t sb_off;
+  int sb_all, sb_n;
   EpiParams epi;
 };
 
@@ -251,23 +266,25 @@ igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
                 const __grid_constant__ CUtensorMap tmap_y,
                 const __grid_constant__ CUtensorMap tmap_r, const IgemmParams p) {
   extern __shared__ uint8_t smem_raw[];
-  __shared__ __align__(8) uint64_t bars[2 * kMaxStages + 4 + 2 * kMaxResBufs];
+  __shared__ __align__(8) uint64_t bars[2 * kMaxStages + 4 + 2 * kMaxResBufs + 2 * kHaloBufs];
   __shared__ uint32_t tmem_base_slot;
-  __shared__ __align__(16) float s_scale[2][256];
-  __shared__ __align__(16) float s_bias[2][256];
 
   const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
   const uint32_t smem_a = smem_base;
-  const uint32_t smem_b = smem_base + p.stages * p.a_stage_bytes;
+  const uint32_t smem_b = smem_base + p.a_region_bytes;
   const uint32_t bar_full = smem_u32(&bars[0]);
   const uint32_t bar_empty = smem_u32(&bars[kMaxStages]);
   const uint32_t bar_tfull = smem_u32(&bars[2 * kMaxStages]);
   const uint32_t bar_tempty = smem_u32(&bars[2 * kMaxStages + 2]);
   const uint32_t bar_rfull = smem_u32(&bars[2 * kMaxStages + 4]);
   const uint32_t bar_rempty = smem_u32(&bars[2 * kMaxStages + 4 + kMaxResBufs]);
+  const uint32_t bar_afull = smem_u32(&bars[2 * kMaxStages + 4 + 2 * kMaxResBufs]);
+  const uint32_t bar_aempty = smem_u32(&bars[2 * kMaxStages + 4 + 2 * kMaxResBufs + kHaloBufs]);
   const uint32_t smem_out = smem_base + p.out_stage_off;
   const uint32_t smem_res = smem_base + p.res_stage_off;
   const uint32_t tile_bytes = (uint32_t)(kBM * p.BN);
+  float* const s_scale = reinterpret_cast<float*>(smem_raw + (smem_base - smem_u32(smem_raw)) + p.sb_off);
+  float* const s_bias = s_scale + p.sb_n;
 
   constexpr int EW = TR > 0 ? kThinEpiWarps : kEpiWarps;  // epilogue warps of this instantiation
   const int warp = threadIdx.x >> 5;
@@ -281,16 +298,20 @@ igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
     if (EPI == EPI_I8_RELU_RES) tma_prefetch_desc(&tmap_r);
     for (int s = 0; s < p.stages; ++s) {
       // TMA arrival (B, and A in the TMA modes) + one arrival per gathered A row
-      mbar_init(bar_full + 8 * s, TR > 0 ? (p.b_resident ? 0 : 1) + kBM : 1);
+      mbar_init(bar_full + 8 * s, TR > 0 ? (p.b_resident ? 0 : 1) + kBM / 32 : 1);  // + one per gather warp of the half
       mbar_init(bar_empty + 8 * s, 1);
     }
     for (int s = 0; s < 2; ++s) {
       mbar_init(bar_tfull + 8 * s, 1);
-      mbar_init(bar_tempty + 8 * s, 32 * EW);
+      mbar_init(bar_tempty + 8 * s, EW);  // one arrival per epilogue warp
+    }
+    for (int s = 0; s < kHaloBufs; ++s) {
+      mbar_init(bar_afull + 8 * s, 1);
+      mbar_init(bar_aempty + 8 * s, 1);
     }
     for (int s = 0; s < kMaxResBufs; ++s) {
       mbar_init(bar_rfull + 8 * s, 1);
-      mbar_init(bar_rempty + 8 * s, 32 * EW);
+      mbar_init(bar_rempty + 8 * s, EW);
     }
     fence_barrier_init();
   }
@@ -303,13 +324,14 @@ igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
   tc_fence_after();
   const uint32_t tmem_base = tmem_base_slot;
 
-  // Warps 0 and 1 run their loops CONVERGED (all 32 lanes wait on the barriers and keep
-  // the loop state, which therefore lives in uniform registers) and hand the issue
-  // instructions to one elected lane.  Wrapping the whole loop in `if (lane == 0)` instead
-  // makes the compiler re-uniformise every TMA / MMA operand with an ELECT + BRA.U.ANY
-  // loop: ~85 instructions and ~640 cycles per k-block, which bounded every 3x3 layer.
+  // Warps 0 and 1 hand their whole loop nest to ONE lane chosen by elect.sync: the compiler
+  // then knows a single thread is active and keeps the loop state and every TMA / MMA operand
+  // on the uniform datapath.  Wrapping the loops in `if (lane == 0)` instead makes it
+  // re-uniformise each operand with an ELECT + BRA.U.ANY loop: ~85 instructions and ~640
+  // cycles per k-block, which bounded every 3x3 layer.
   if (warp == 0) {
     // ===================== TMA producer =====================
+    if (elect_one()) {  // ONE lane runs the whole loop nest: the compiler keeps it on the uniform datapath
     // all loop state is incremental (no multiplies, no parameter reloads per k-block):
     // this warp's issue latency per k-block bounds the short-K 3x3 layers
     const uint32_t tx = p.tx_bytes, a_bytes = p.a_stage_bytes, b_bytes = p.b_stage_bytes;
@@ -323,19 +345,68 @@ igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
     uint32_t rphase = 0;
     if (TR > 0 && p.b_resident) {
       // thin mode, single N tile: every k-block of the filter is loaded exactly once
-      if (elect_one()) {
+      {
         mbar_arrive_expect_tx(bar_rfull, (uint32_t)num_kb * (uint32_t)(BN * BK));
         for (int kb = 0; kb < num_kb; ++kb)
           tma_load_2d(smem_b + kb * b_bytes, &tmap_b, bar_rfull, kb * BK, 0);
       }
     }
-    for (int tile = blockIdx.x; tile < num_tiles && !(TR > 0 && p.b_resident); tile += gridDim.x) {
+    if (TR == 0 && mode == 3) {
+      // halo reuse: one tiled 4-D load per (tile, channel block), then the filter taps
+      const int RS = p.R * S;
+      int ab = 0;
+      uint32_t aph = 0;
+      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+        const int tn = tile % n_tiles, tm = tile / n_tiles;
+        const int n0 = tn * BN;
+        const int img = (int)fdiv((uint32_t)tm, p.dBands);
+        const int p0 = (tm - img * p.bands) * p.hk;
+        if (EPI == EPI_I8_RELU_RES) {
+          mbar_wait(bar_rempty + 8 * rb, rphase ^ 1);
+          {
+            mbar_arrive_expect_tx(bar_rfull + 8 * rb, (uint32_t)(p.hk * p.Q * BN));
+            for (int j = 0; j < p.panels; ++j)
+              tma_load_4d(smem_res + rb * tile_bytes + j * (kBM * p.PW), &tmap_r, bar_rfull + 8 * rb,
+                          n0 + j * p.PW, 0, p0, img);
+          }
+          if (++rb == p.res_bufs) { rb = 0; rphase ^= 1; }
+        }
+        for (int cbk = 0; cbk < cspan; cbk += BK) {
+          mbar_wait(bar_aempty + 8 * ab, aph ^ 1);
+          {
+            if (p.dbg_flags & 8) {
+              mbar_arrive(bar_afull + 8 * ab);
+            } else {
+              mbar_arrive_expect_tx(bar_afull + 8 * ab, p.a_halo_tx);
+              tma_load_4d(smem_a + ab * p.a_halo_bytes, &tmap_a, bar_afull + 8 * ab, cbk, -p.pl_, p0 - p.pt, img);
+            }
+          }
+          if (++ab == kHaloBufs) { ab = 0; aph ^= 1; }
+          int kc = cbk;  // K coordinate of the filter block: tap * cspan + channel offset
+          for (int tap = 0; tap < RS; ++tap) {
+            mbar_wait(empty_b, phase ^ 1);
+            {
+              if (p.dbg_flags & 4) {
+                mbar_arrive(full_b);
+              } else {
+                mbar_arrive_expect_tx(full_b, tx);
+                tma_load_2d(dst_b, &tmap_b, full_b, kc, n0);
+              }
+            }
+            kc += cspan;
+            ++stage; full_b += 8; empty_b += 8; dst_b += b_bytes;
+            if (stage == stages) { stage = 0; phase ^= 1; full_b = bar_full; empty_b = bar_empty; dst_b = smem_b; }
+          }
+        }
+      }
+    }
+    for (int tile = blockIdx.x; tile < num_tiles && !(TR > 0 && p.b_resident) && mode != 3; tile += gridDim.x) {
       const int tn = tile % n_tiles, tm = tile / n_tiles;
       const int m0 = tm * kBM, n0 = tn * BN;
       if (EPI == EPI_I8_RELU_RES) {
         // residual tile first: it is the largest load of a 1x1 expand layer
         mbar_wait(bar_rempty + 8 * rb, rphase ^ 1);
-        if (elect_one()) {
+        {
           mbar_arrive_expect_tx(bar_rfull + 8 * rb, tile_bytes);
           for (int j = 0; j < p.panels; ++j)
             tma_load_2d(smem_res + rb * tile_bytes + j * (kBM * p.PW), &tmap_r, bar_rfull + 8 * rb,
@@ -355,7 +426,7 @@ igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
       uint16_t offw = 0, offh = 0;      // im2col filter offsets of the tap
       for (int kb = 0; kb < num_kb; ++kb) {
         mbar_wait(empty_b, phase ^ 1);
-        if (elect_one()) {
+        {
           mbar_arrive_expect_tx(full_b, tx);
           if (TR > 0) {
             // A arrives from the gather warps
@@ -380,8 +451,10 @@ igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
         }
       }
     }
+    }
   } else if (warp == 1) {
     // ===================== MMA issuer =====================
+    if (elect_one()) {
     const uint32_t idesc = make_idesc_i8((uint32_t)p.BN);
     const uint64_t desc_hi = make_smem_desc_base((uint32_t)p.BK);
     const int ksteps = p.BK / 32, stages = p.stages, num_kb = p.num_kb;
@@ -394,7 +467,47 @@ igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
     int as = 0;
     uint32_t aphase = 0;
     if (bres) mbar_wait(bar_rfull, 0);
-    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+    if (TR == 0 && p.mode == 3) {
+      const int S = p.S, RS = p.R * p.S, cblocks = p.cblocks;
+      const uint32_t tap_step = (uint32_t)p.BK >> 4;                       // next tap column: one pixel
+      const uint32_t row_step = (uint32_t)((p.WP - S) * p.BK) >> 4;        // extra step at the end of a filter row
+      const uint32_t halo_step = p.a_halo_bytes >> 4;
+      int ab = 0;
+      uint32_t aph = 0;
+      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+        mbar_wait(bar_tempty + 8 * as, aphase ^ 1);
+        tc_fence_after();
+        const uint32_t d_tmem = tmem_base + (uint32_t)as * p.acc_stride;
+        for (int cb = 0; cb < cblocks; ++cb) {
+          mbar_wait(bar_afull + 8 * ab, aph);
+          uint32_t t_lo = a_lo0 + (uint32_t)ab * halo_step;  // descriptor start of tap (0, 0)
+          int sx = 0;
+          for (int tap = 0; tap < RS; ++tap) {
+            mbar_wait(full_b, phase);
+            tc_fence_after();
+            {
+              const uint64_t da = desc_hi | (uint64_t)t_lo, db = desc_hi | (uint64_t)b_lo;
+              if (!(p.dbg_flags & 2))
+                for (int k = 0; k < ksteps; ++k)
+                  umma_i8(d_tmem, da + (uint64_t)(k * 2), db + (uint64_t)(k * 2), idesc,
+                          (uint32_t)((cb | tap | k) != 0));
+              umma_commit(empty_b);
+              if (tap == RS - 1) {
+                umma_commit(bar_aempty + 8 * ab);
+                if (cb == cblocks - 1) umma_commit(bar_tfull + 8 * as);
+              }
+            }
+            t_lo += tap_step;
+            if (++sx == S) { sx = 0; t_lo += row_step; }
+            ++stage; full_b += 8; empty_b += 8; b_lo += b_step;
+            if (stage == stages) { stage = 0; phase ^= 1; full_b = bar_full; empty_b = bar_empty; b_lo = b_lo0; }
+          }
+          if (++ab == kHaloBufs) { ab = 0; aph ^= 1; }
+        }
+        if (++as == 2) { as = 0; aphase ^= 1; }
+      }
+    }
+    for (int tile = blockIdx.x; tile < num_tiles && !(TR == 0 && p.mode == 3); tile += gridDim.x) {
       mbar_wait(bar_tempty + 8 * as, aphase ^ 1);
       tc_fence_after();
       const uint32_t d_tmem = tmem_base + (uint32_t)as * p.acc_stride;
@@ -402,7 +515,7 @@ igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
       for (int kb = 0; kb < num_kb; ++kb) {
         mbar_wait(full_b, phase);
         tc_fence_after();
-        if (elect_one()) {
+        {
           uint64_t da = desc_hi | (uint64_t)a_lo;
           const uint64_t db = desc_hi | (uint64_t)b_lo;
           if (p.dbg_ashift) {  // descriptor-semantics experiment (tools/dbg_rowshift.py)
@@ -423,6 +536,7 @@ igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
         }
       }
       if (++as == 2) { as = 0; aphase ^= 1; }
+    }
     }
   } else if (TR > 0 && warp >= 2 + EW) {
     // ===================== thin-input gather (8 warps, two threads per A row) =====================
@@ -487,11 +601,12 @@ igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
         }
       }
       fence_proxy_async();  // generic-proxy stores -> visible to the tensor core's async proxy
+      __syncwarp();         // every lane's stores are fenced before the warp's single arrival
 #pragma unroll
       for (int i = 0; i < MYKB; ++i) {
         if (!mine[i]) continue;
         const uint32_t cnt = base + (uint32_t)(half + 2 * i);
-        mbar_arrive(bar_full + 8 * (cnt % (uint32_t)p.stages));
+        if (lane == 0) mbar_arrive(bar_full + 8 * (cnt % (uint32_t)p.stages));
       }
       base += NKB;
     }
@@ -505,29 +620,62 @@ igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
     constexpr bool kFast = (EPI != EPI_GENERIC);  // int8 paths: swizzled smem staging + TMA store
     constexpr int CQ = EW / 4;  // warps per TMEM lane quarter = column groups
     const int units = p.BN >> 4;
-    const uint32_t rowoff = (uint32_t)((quarter * 32 + lane) * p.PW);
+    // accumulator row of this thread -> row of the (dense) output tile.  Halo mode computes
+    // on the padded grid: row i is output (i / WP, i % WP) of the band, rows in the pad
+    // columns or beyond the band carry garbage and are dropped here
+    const int arow = quarter * 32 + lane;
+    const bool halo = (TR == 0) && p.mode == 3;
+    int orow = 0, jrow = arow;
+    bool rvalid = true;
+    if (halo) {
+      orow = (int)fdiv((uint32_t)arow, p.dWP);
+      const int ocol = arow - orow * p.WP;
+      rvalid = ocol < p.Q && orow < p.hk;
+      jrow = rvalid ? orow * p.Q + ocol : 0;
+    }
+    const uint32_t rowoff = (uint32_t)(jrow * p.PW);
     const uint32_t swx = (rowoff >> 7) & p.swz_mask;
     int as = 0;
     uint32_t aphase = 0;
     int rb = 0;
     uint32_t rphase = 0;
     int ob = 0;
-    // scale / bias of a tile are staged in smem (double buffered) during the previous
-    // tile, so one barrier per tile orders both the staging and the TMA store
+    // folded scale / bias live in smem.  Normally the vectors of every n-tile are staged once
+    // here; a global load per tile would sit on the epilogue's critical path (the tile rate of
+    // short-K layers is 1 / epilogue latency).  Very wide outputs fall back to per-tile staging
+    // into two 256-entry buffers, filled during the previous tile.
     auto stage_scale_bias = [&](int t, int buf) {
       if (etid < p.BN) {
         const int n = (t % p.n_tiles) * p.BN + etid;
         const bool ok = n < p.Nout && p.epi.scale != nullptr;
-        s_scale[buf][etid] = ok ? __ldg(p.epi.scale + n) : 0.f;
-        s_bias[buf][etid] = (ok && p.epi.bias) ? __ldg(p.epi.bias + n) : 0.f;
+        s_scale[buf * 256 + etid] = ok ? __ldg(p.epi.scale + n) : 0.f;
+        s_bias[buf * 256 + etid] = (ok && p.epi.bias) ? __ldg(p.epi.bias + n) : 0.f;
       }
     };
-    if ((int)blockIdx.x < num_tiles) stage_scale_bias(blockIdx.x, 0);
+    if (p.sb_all) {
+      for (int n = etid; n < p.sb_n; n += 32 * EW) {
+        const bool ok = n < p.Nout && p.epi.scale != nullptr;
+        s_scale[n] = ok ? __ldg(p.epi.scale + n) : 0.f;
+        s_bias[n] = (ok && p.epi.bias) ? __ldg(p.epi.bias + n) : 0.f;
+      }
+    } else if ((int)blockIdx.x < num_tiles) {
+      stage_scale_bias(blockIdx.x, 0);
+    }
     asm volatile("bar.sync 1, %0;" ::"n"(32 * EW) : "memory");
     for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
       const int tn = tile % p.n_tiles, tm = tile / p.n_tiles;
-      const long long row = (long long)tm * kBM + quarter * 32 + lane;
+      long long row = (long long)tm * kBM + arow;  // output pixel index (generic epilogue)
+      int himg = 0, hp0 = 0;
+      if (halo) {
+        himg = (int)fdiv((uint32_t)tm, p.dBands);
+        hp0 = (tm - himg * p.bands) * p.hk;
+        const int prow = hp0 + orow;
+        // an out-of-band row is parked beyond M so that the generic path skips it
+        row = (rvalid && prow < p.P) ? ((long long)himg * p.PQ + (long long)prow * p.Q + (jrow - orow * p.Q))
+                                            : (long long)p.M;
+      }
       const int n0 = tn * p.BN;
+      const uint32_t sb0 = p.sb_all ? (uint32_t)n0 : (uint32_t)(as * 256);
       if (EPI == EPI_I8_RELU_RES) mbar_wait(bar_rfull + 8 * rb, rphase);
       mbar_wait(bar_tfull + 8 * as, aphase);
       tc_fence_after();
@@ -537,17 +685,20 @@ igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
       const uint32_t out_base = out_tile + rowoff;
       // TMEM reads are double buffered: unit i+1 is in flight while unit i runs through the ALUs
       uint32_t accb[2][16];
-      if (cq < units) tmem_ld_32x32b_x16(t_addr + (uint32_t)(cq * 16), accb[0]);
+      const bool skip_epi = (p.dbg_flags & 1) != 0;
+      if (cq < units && !skip_epi) tmem_ld_32x32b_x16(t_addr + (uint32_t)(cq * 16), accb[0]);
 #pragma unroll
       for (int i = 0; i < 16 / CQ; ++i) {
         const int u = cq + CQ * i;
-        if (u < units) {  // warp-uniform
+        if (u < units && !skip_epi) {  // warp-uniform
           tmem_ld_wait();
           if (i < 16 / CQ - 1 && u + CQ < units)
             tmem_ld_32x32b_x16(t_addr + (uint32_t)((u + CQ) * 16), accb[(i + 1) & 1]);
           uint32_t(&acc)[16] = accb[i & 1];
           const uint32_t col = (uint32_t)(u * 16);
-          if (kFast) {
+          if (kFast && !rvalid) {
+            // padded-grid row without an output pixel
+          } else if (kFast) {
             // position of this 16-byte chunk inside the swizzled staging panels; rows >= M
             // and columns >= Nout are computed on zero-filled operands and clipped by the store
             const uint32_t soff = (col >> p.pw_shift) * (uint32_t)(kBM * p.PW) +
@@ -558,8 +709,8 @@ igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
             uint32_t w[4];
 #pragma unroll
             for (int q4 = 0; q4 < 4; ++q4) {
-              const float4 sc = *reinterpret_cast<const float4*>(&s_scale[as][col + 4 * q4]);
-              const float4 bi = *reinterpret_cast<const float4*>(&s_bias[as][col + 4 * q4]);
+              const float4 sc = *reinterpret_cast<const float4*>(&s_scale[sb0 + col + 4 * q4]);
+              const float4 bi = *reinterpret_cast<const float4*>(&s_bias[sb0 + col + 4 * q4]);
               if (EPI == EPI_I8_RELU)
                 w[q4] = quad_i8_relu<false>(acc + 4 * q4, sc, bi, p.hi_bits, 0u, 0.f);
               else if (EPI == EPI_I8_RELU_RES)
@@ -569,20 +720,24 @@ igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
             }
             st_shared_v4(out_base + soff, w[0], w[1], w[2], w[3]);
           } else if (row < p.M && n0 + (int)col < p.Nout) {
-            store_group16(p, acc, row, n0 + (int)col, &s_scale[as][col], &s_bias[as][col]);
+            store_group16(p, acc, row, n0 + (int)col, &s_scale[sb0 + col], &s_bias[sb0 + col]);
           }
         }
       }
+      // the warp's TMEM reads (tcgen05.wait::ld) and residual reads are complete: one lane
+      // per warp releases the accumulator / residual buffer (512 single arrivals on one
+      // mbarrier cost more than the whole epilogue of a narrow tile)
       tc_fence_before();
-      mbar_arrive(bar_tempty + 8 * as);
+      __syncwarp();
+      if (lane == 0) mbar_arrive(bar_tempty + 8 * as);
       if (++as == 2) { as = 0; aphase ^= 1; }
       if (EPI == EPI_I8_RELU_RES) {
-        mbar_arrive(bar_rempty + 8 * rb);
+        if (lane == 0) mbar_arrive(bar_rempty + 8 * rb);
         if (++rb == p.res_bufs) { rb = 0; rphase ^= 1; }
       }
       // next tile's scale / bias into the other buffer (last read one tile ago, before
       // that tile's barrier)
-      if (tile + (int)gridDim.x < num_tiles) stage_scale_bias(tile + gridDim.x, as);
+      if (!p.sb_all && tile + (int)gridDim.x < num_tiles) stage_scale_bias(tile + gridDim.x, as);
       if (kFast) {
         // the store issued one tile ago has long drained its staging buffer: after the
         // barrier every thread may write it again
@@ -596,9 +751,13 @@ igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
       asm volatile("bar.sync 2, %0;" ::"n"(32 * EW) : "memory");
       if (kFast) {
         if (warp == 2) {
-          if (elect_one()) {
-            for (int j = 0; j < p.panels; ++j)
-              tma_store_2d(&tmap_y, out_tile + (uint32_t)(j * kBM * p.PW), n0 + j * p.PW, tm * kBM);
+          if (elect_one() && !(p.dbg_flags & 16)) {
+            for (int j = 0; j < p.panels; ++j) {
+              if (halo)  // box = PW channels x Q pixels x hk rows of image himg; rows >= P are clipped
+                tma_store_4d(&tmap_y, out_tile + (uint32_t)(j * kBM * p.PW), n0 + j * p.PW, 0, hp0, himg);
+              else
+                tma_store_2d(&tmap_y, out_tile + (uint32_t)(j * kBM * p.PW), n0 + j * p.PW, tm * kBM);
+            }
             bulk_commit_group();
           }
           __syncwarp();
@@ -632,7 +791,7 @@ igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
 // --------------------------------------------------------------------------
 // tensor-pipe micro-benchmark: back-to-back MMAs on resident smem operands
 // --------------------------------------------------------------------------
-__global__ void __launch_bounds__(128, 1) i8_mma_peak_kernel(int iters, int bn, int32_t* out) {
+__global__ void __launch_bounds__(128, 1) i8_mma_peak_kernel(int iters, int bn, int32_t* out, int row_bytes) {
   extern __shared__ uint8_t smem_raw[];
   __shared__ __align__(8) uint64_t bar;
   __shared__ uint32_t tmem_slot;
@@ -655,14 +814,20 @@ __global__ void __launch_bounds__(128, 1) i8_mma_peak_kernel(int iters, int bn, 
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem = tmem_slot;
-  if (threadIdx.x == 0) {
+  if (warp == 0 && elect_one()) {
     const uint32_t idesc = make_idesc_i8((uint32_t)bn);
-    const uint64_t hi = make_smem_desc_base(128);
+    // row_bytes selects the operand layout (swizzle mode); one iteration = 8 MMAs cycling over
+    // the row_bytes / 32 K-steps of the tile, issued from the uniform datapath
+    const uint64_t hi = make_smem_desc_base((uint32_t)row_bytes);
     const uint64_t da = hi | (uint64_t)((sa >> 4) & 0x3fff), db = hi | (uint64_t)((sb >> 4) & 0x3fff);
+    const uint32_t kmask = (uint32_t)(row_bytes / 32 - 1);
     for (int i = 0; i < iters; ++i) {
       const uint32_t d = tmem + (uint32_t)((i & 1) * bn);
 #pragma unroll
-      for (int k = 0; k < 4; ++k) umma_i8(d, da + 2 * k, db + 2 * k, idesc, (uint32_t)(i > 1 || k > 0));
+      for (uint32_t k = 0; k < 8; ++k) {
+        const uint64_t ko = (uint64_t)(2u * (k & kmask));
+        umma_i8(d, da + ko, db + ko, idesc, (uint32_t)(i > 1 || k > 0));
+      }
     }
     umma_commit(smem_u32(&bar));
   }
@@ -764,6 +929,19 @@ int encode_2d(CUtensorMap* m, const void* base, uint64_t cols, uint64_t rows, ui
   return r == CUDA_SUCCESS ? PL_OK : PL_ERR_DRIVER;
 }
 
+// 4-D tiled map over an NHWC byte tensor {C, W, H, N} (pixel pitch ld); box {bc, bw, bh, 1};
+// out-of-bounds box elements read as zero / are not written
+int encode_4d(CUtensorMap* m, const void* base, int C, int W, int H, int N, int ld, int bc, int bw, int bh) {
+  cuuint64_t dims[4] = {(cuuint64_t)C, (cuuint64_t)W, (cuuint64_t)H, (cuuint64_t)N};
+  cuuint64_t strides[3] = {(cuuint64_t)ld, (cuuint64_t)ld * W, (cuuint64_t)ld * W * H};
+  cuuint32_t box[4] = {(cuuint32_t)bc, (cuuint32_t)bw, (cuuint32_t)bh, 1};
+  cuuint32_t estr[4] = {1, 1, 1, 1};
+  CUresult r = driver().tiled(m, CU_TENSOR_MAP_DATA_TYPE_UINT8, 4, const_cast<void*>(base), dims, strides, box,
+                              estr, CU_TENSOR_MAP_INTERLEAVE_NONE, swizzle_for(bc),
+                              CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  return r == CUDA_SUCCESS ? PL_OK : PL_ERR_DRIVER;
+}
+
 int encode_im2col(CUtensorMap* m, const void* x, const pl_conv_desc* d, int bk) {
   cuuint64_t dims[4] = {(cuuint64_t)d->C, (cuuint64_t)d->W, (cuuint64_t)d->H, (cuuint64_t)d->N};
   cuuint64_t strides[3] = {(cuuint64_t)d->ldx, (cuuint64_t)d->ldx * d->W,
@@ -807,7 +985,7 @@ int launch_one(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& 
   if (!configured) {
     // 227 KB is the per-CTA limit for static + dynamic shared memory together
     PL_CUDA_OK(cudaFuncSetAttribute(igemm_i8_kernel<EPI, TR, TSW>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                    (int)(216 * 1024)));
+                                    (int)(221 * 1024)));
     configured = true;
   }
   const int threads = TR > 0 ? kThinThreads : kThreads;
@@ -860,24 +1038,37 @@ int launch_igemm(const CUtensorMap& ta, const CUtensorMap& tb, IgemmParams& p, p
   p.swz_mask = p.PW == 128 ? 7u : (p.PW == 64 ? 3u : (p.PW == 32 ? 1u : 0u));
   p.tma_out = (epi != EPI_GENERIC);
   p.tma_res = p.tma_out && epi == EPI_I8_RELU_RES;
-  const int budget = 215 * 1024;
+  const int n_cover = p.n_tiles * p.BN;
+  p.sb_all = n_cover <= 2048 ? 1 : 0;
+  p.sb_n = p.sb_all ? n_cover : 512;
+  const int sb_bytes = (p.sb_n * 8 + 1023) / 1024 * 1024;
+  const int budget = 219 * 1024 - sb_bytes;  // static smem is now only the barriers
   const int tile = kBM * p.BN;
   const int stage_bytes = (int)(p.a_stage_bytes + p.b_stage_bytes);
   p.out_bufs = 0;
   p.res_bufs = 2;
   int extra = 0;
   if (p.tma_out) {
-    int rc = encode_2d(&ty, p.y, (uint64_t)p.Nout, (uint64_t)p.M, (uint64_t)p.ldy, p.PW, kBM);
+    int rc;
+    if (p.mode == 3)  // dense band of hk output rows x Q pixels
+      rc = encode_4d(&ty, p.y, p.Nout, p.Q, p.P, p.M / p.PQ, p.ldy, p.PW, p.Q, p.hk);
+    else
+      rc = encode_2d(&ty, p.y, (uint64_t)p.Nout, (uint64_t)p.M, (uint64_t)p.ldy, p.PW, kBM);
     if (rc) return rc;
     if (p.tma_res) {
-      rc = encode_2d(&tr, e.residual, (uint64_t)p.Nout, (uint64_t)p.M, (uint64_t)e.ld_res, p.PW, kBM);
+      if (p.mode == 3)
+        rc = encode_4d(&tr, e.residual, p.Nout, p.Q, p.P, p.M / p.PQ, e.ld_res, p.PW, p.Q, p.hk);
+      else
+        rc = encode_2d(&tr, e.residual, (uint64_t)p.Nout, (uint64_t)p.M, (uint64_t)e.ld_res, p.PW, kBM);
       if (rc) return rc;
     }
     // shared-memory policy: at least min_stages mainloop stages, then a second staging
     // buffer (the TMA store of tile i drains while tile i+1 is written), then a deeper
     // residual ring, the rest goes back to the mainloop
     const int min_stages = env_int("PL_IGEMM_MIN_STAGES", 3);
-    int left = budget - min_stages * stage_bytes - tile - (p.tma_res ? 2 * tile : 0);
+    const int main_min = p.mode == 3 ? kHaloBufs * (int)p.a_halo_bytes + 4 * (int)p.b_stage_bytes
+                                     : min_stages * stage_bytes;
+    int left = budget - main_min - tile - (p.tma_res ? 2 * tile : 0);
     if (left < 0) left = 0;
     p.out_bufs = 1;
     if (left >= tile && env_int("PL_IGEMM_OUT_BUFS", 2) >= 2) {
@@ -895,11 +1086,17 @@ int launch_igemm(const CUtensorMap& ta, const CUtensorMap& tb, IgemmParams& p, p
     extra = p.out_bufs * tile + (p.tma_res ? p.res_bufs * tile : 0);
   }
   p.b_resident = (p.mode == 2 && p.n_tiles == 1) ? 1 : 0;
+  p.dbg_flags = env_int("PL_DBG_FLAGS", 0);
   p.dbg_ashift = env_int("PL_DBG_ASHIFT", 0);
   p.dbg_baseoff = env_int("PL_DBG_BASEOFF", 0);
   int stages;
   size_t ring_bytes;
-  if (p.b_resident) {
+  if (p.mode == 3) {
+    p.a_region_bytes = (uint32_t)kHaloBufs * p.a_halo_bytes;
+    stages = (budget - extra - (int)p.a_region_bytes) / (int)p.b_stage_bytes;
+    if (stages > kMaxStages) stages = kMaxStages;
+    ring_bytes = (size_t)p.a_region_bytes + (size_t)stages * p.b_stage_bytes;
+  } else if (p.b_resident) {
     stages = (budget - extra - p.num_kb * (int)p.b_stage_bytes) / (int)p.a_stage_bytes;
     if (stages > kMaxStages) stages = kMaxStages;
     ring_bytes = (size_t)stages * p.a_stage_bytes + (size_t)p.num_kb * p.b_stage_bytes;
@@ -910,9 +1107,11 @@ int launch_igemm(const CUtensorMap& ta, const CUtensorMap& tb, IgemmParams& p, p
   }
   if (stages < 2 || (p.mode == 2 && stages < p.num_kb)) return PL_ERR_UNSUPPORTED;
   p.stages = stages;
+  if (p.mode != 3) p.a_region_bytes = (uint32_t)stages * p.a_stage_bytes;
   p.out_stage_off = (uint32_t)ring_bytes;
   p.res_stage_off = p.out_stage_off + (uint32_t)(p.out_bufs * tile);
-  const size_t smem = ring_bytes + extra + 1024;
+  p.sb_off = (uint32_t)(ring_bytes + extra);
+  const size_t smem = ring_bytes + extra + sb_bytes + 1024;
   if (p.mode == 2) {
     // thin-input gather mode: (filter rows, window words) instantiations
     const int key = p.thin_r * 16 + p.thin_sw;
@@ -958,7 +1157,7 @@ int common_setup(IgemmParams& p, long long M, int Nout, void* y, int ldy, const 
   const int cpad = (Kc + p.BK - 1) / p.BK * p.BK;
   p.M = (int)M;
   p.Nout = Nout;
-  p.m_tiles = (int)((M + kBM - 1) / kBM);
+  p.m_tiles = p.halo_m_tiles > 0 ? p.halo_m_tiles : (int)((M + kBM - 1) / kBM);
   p.BN = pick_bn(Nout, p.m_tiles, driver().sm_count);
   if (e->residual) {
     // fused-residual launches are bandwidth bound and need smem for the residual ring and
@@ -1040,12 +1239,47 @@ extern "C" int pl_conv2d_i8_nhwc(const int8_t* x, const int8_t* w_packed, void* 
   IgemmParams p{};
   p.BK = pl_conv_block_k(d->C);
   const int cpad = (d->C + p.BK - 1) / p.BK * p.BK;
-  rc = common_setup(p, (long long)d->N * P * Q, d->K, y, d->ldy, e, d->C, d->R * d->S);
-  if (rc) return rc;
   const bool as_gemm = d->R == 1 && d->S == 1 && d->stride_h == 1 && d->stride_w == 1 &&
                        d->pad_t == 0 && d->pad_b == 0 && d->pad_l == 0 && d->pad_r == 0;
+  // halo reuse (mode 3): stride-1, undilated windows whose padded-grid bands fill the 128-row
+  // tile well enough; everything else keeps the im2col TMA path
+  const int WP = Q + d->S - 1;
+  const int hk = WP <= kBM ? kBM / WP : 0;
+  bool halo = !as_gemm && d->stride_h == 1 && d->stride_w == 1 && d->dil_h == 1 && d->dil_w == 1 && hk >= 1 &&
+              WP <= 256 && hk + d->R - 1 <= 256 && Q <= 256 && env_int("PL_IGEMM_NO_HALO", 0) == 0 &&
+              d->W + d->pad_l + d->pad_r == WP;
+  int bands = 0;
+  if (halo) {
+    bands = (P + hk - 1) / hk;
+    const double eff = (double)P * Q / ((double)bands * kBM);  // useful rows per MMA tile
+    if (eff < 0.6) halo = false;
+  }
+  if (halo) p.halo_m_tiles = d->N * bands;
+  rc = common_setup(p, (long long)d->N * P * Q, d->K, y, d->ldy, e, d->C, d->R * d->S);
+  if (rc) return rc;
   CUtensorMap ta, tb;
-  if (as_gemm) {
+  if (halo) {
+    p.mode = 3;
+    p.Q = Q;
+    p.P = P;
+    p.PQ = P * Q;
+    p.S = d->S;
+    p.R = d->R;
+    p.pt = d->pad_t;
+    p.pl_ = d->pad_l;
+    p.hk = hk;
+    p.WP = WP;
+    p.bands = bands;
+    p.dBands = make_fastdiv((uint32_t)bands);
+    p.dWP = make_fastdiv((uint32_t)WP);
+    const int rows_loaded = (hk + d->R - 1) * WP;
+    const int rows_read = kBM + (d->R - 1) * WP + d->S - 1;  // furthest row an MMA descriptor touches
+    const int rows_alloc = rows_loaded > rows_read ? rows_loaded : rows_read;
+    p.a_halo_tx = (uint32_t)(rows_loaded * p.BK);
+    p.a_halo_bytes = (uint32_t)((rows_alloc * p.BK + 1023) / 1024 * 1024);
+    p.tx_bytes = (uint32_t)(p.BN * p.BK);  // the stage ring carries only filter blocks
+    rc = encode_4d(&ta, x, d->C, d->W, d->H, d->N, d->ldx, p.BK, WP, hk + d->R - 1);
+  } else if (as_gemm) {
     p.mode = 0;
     rc = encode_2d(&ta, x, (uint64_t)d->C, (uint64_t)p.M, (uint64_t)d->ldx, p.BK, kBM);
   } else {
@@ -1165,12 +1399,25 @@ extern "C" int pl_gemm_i8(const int8_t* A, int lda, const int8_t* Bt, int ldb, v
   return launch_igemm(ta, tb, p, stream);
 }
 
+// same probe with the operand layout of a 32 / 64 / 128-byte K-block (SWIZZLE_32B / 64B / 128B
+// descriptors): one iteration issues row_bytes / 32 MMAs of 128 x bn x 32
+extern "C" int pl_i8_mma_probe(int ctas, int iters, int bn, int row_bytes, int32_t* out, pl_stream_t stream) {
+  if (ctas <= 0 || iters <= 0 || bn < 16 || bn > 256 || (bn % 16) || !out ||
+      (row_bytes != 32 && row_bytes != 64 && row_bytes != 128))
+    return PL_ERR_ARG;
+  const size_t smem = (size_t)(128 + bn) * 128 + 1024;
+  PL_CUDA_OK(cudaFuncSetAttribute(i8_mma_peak_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  i8_mma_peak_kernel<<<ctas, 128, smem, (cudaStream_t)stream>>>(iters, bn, out, row_bytes);
+  ++g_launches;
+  return launch_status();
+}
+
 extern "C" int pl_i8_mma_peak(int ctas, int iters, int bn, int32_t* out, pl_stream_t stream) {
   if (ctas <= 0 || iters <= 0 || bn < 16 || bn > 256 || (bn % 16) || !out) return PL_ERR_ARG;
   const size_t smem = (size_t)(128 + bn) * 128 + 1024;
   PL_CUDA_OK(cudaFuncSetAttribute(i8_mma_peak_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                   (int)smem));
-  i8_mma_peak_kernel<<<ctas, 128, smem, (cudaStream_t)stream>>>(iters, bn, out);
+  i8_mma_peak_kernel<<<ctas, 128, smem, (cudaStream_t)stream>>>(iters, bn, out, 128);
   ++g_launches;
   return launch_status();
 }
