@@ -278,7 +278,8 @@ def run_b200(args):
             "scaling": "weak", "vs_baseline": None, "dtype": "int8", "data": "synthetic",
             "config": {"workload": workload_name(args.net, batch), "global_batch": batch * world,
                        "parallelism": f"batch-sharded x{world}, no collective", "cuda_graph": True,
-                       "l2": "per-step working set (activations > 1 GB at batch 256) exceeds the 126 MB L2; no flush needed",
+                       "l2": f"per-step working set ({(nets.program_bytes(prog)[0] * batch + nets.program_bytes(prog)[1]) / 1e6:.0f} MB of activations + weights) "
+                             "exceeds the 126 MB L2; consecutive steps replay the whole network, no flush needed",
                        "gmac_per_image": sum(macs.values()) / 1e9},
             "tops": 2 * sum(macs.values()) * batch * world * args.steps / (ms_max * 1e-3) / 1e12,
             "clocks": clocks,
@@ -323,6 +324,8 @@ def layer_roofline(net, prog, batch, nets, torch):
         if op.kind == "conv":
             ops = 2 * P * Q * K * op.k * op.k * op.C * batch
             byts = batch * (H * W * C + P * Q * K * (4 if op.out_fp32 else 1)) + op.w.size + 8 * K
+            if op.get("res"):
+                byts += batch * P * Q * K  # fused residual read
         elif op.kind == "dwconv":
             ops = 2 * P * Q * K * op.k * op.k * batch
             byts = batch * (H * W * C + P * Q * K) + op.w.size + 8 * K
@@ -357,7 +360,15 @@ def layer_roofline(net, prog, batch, nets, torch):
     else:
         achieved = tc_ops / (tc_ms * 1e-3) / 1e12
         roof = {"bound": "tensor", "achieved": achieved, "peak": i8_peak, "unit": "TOP/s", "frac": achieved / i8_peak}
-    roof.update({"traffic": None, "kernel": "igemm_i8_kernel", "launches_per_step": n_tc,
+    # measured DRAM bytes per launch of this kernel: ncu dram__bytes_read.sum + dram__bytes_write.sum of
+    # the same command (tools/gpu_profile_round.sh -> profiles/rNN_traffic.json), when captured
+    traffic = None
+    tpath = os.path.join(ROOT, "profiles", "traffic.json")
+    if os.path.exists(tpath):
+        tj = json.load(open(tpath)).get(f"{prog.name}_b{batch}")
+        if tj:
+            traffic = tj["igemm_dram_bytes_per_launch"]
+    roof.update({"traffic": traffic, "algorithmic_bytes_per_launch": tc_bytes / n_tc, "kernel": "igemm_i8_kernel", "launches_per_step": n_tc,
                  "avg_launch_ms": tc_ms / n_tc, "share_of_step": tc_ms / total_ms, "peak_source": src,
                  "tensor_tops": tc_ops / (tc_ms * 1e-3) / 1e12, "tensor_peak_tops_2x_bf16": i8_peak,
                  "hbm_gbs": tc_bytes / (tc_ms * 1e-3) / 1e9,

@@ -196,6 +196,54 @@ def test_conv_fused_residual(pl, case, out):
     assert np.array_equal(got, want)
 
 
+HALO_CASES = [
+    # stride-1 undilated windows that take the halo-reuse path (mode 3): WP = Q + S - 1 <= 128
+    (2, 28, 28, 128, 128, 3, 3, 1, (1, 1, 1, 1), 1),    # WP=30, 4 rows per band, 7 full bands
+    (3, 30, 30, 32, 48, 3, 3, 1, (1, 1, 1, 1), 1),      # WP=32: last band of every image is a 2-row tail
+    (1, 9, 9, 48, 24, 3, 3, 1, (1, 1, 1, 1), 1),        # whole image in one band, C=48 < BK, K tail
+    (2, 20, 20, 16, 32, 5, 5, 1, (2, 2, 2, 2), 1),      # 5x5 window
+    (1, 56, 56, 64, 320, 3, 3, 1, (1, 1, 1, 1), 1),     # two n-tiles (256 + 64) over the same halo tiles
+    (1, 13, 40, 32, 32, 3, 1, 1, (1, 1, 0, 0), 1),      # 3x1 window: WP == Q
+    (2, 10, 10, 192, 64, 2, 2, 1, (0, 1, 0, 1), 1),     # even window, asymmetric pads, 2 channel blocks
+    (1, 7, 7, 512, 512, 3, 3, 1, (1, 1, 1, 1), 1),      # res5 3x3 shape
+]
+
+
+@pytest.mark.parametrize("case", HALO_CASES)
+@pytest.mark.parametrize("mode", ["int32", "int8_relu", "fp32_res", "int8_res"])
+def test_conv_halo_reuse_path(pl, case, mode, monkeypatch):
+    """Halo-reuse tiles vs the oracle, and vs the im2col path (PL_IGEMM_NO_HALO=1) on the same input."""
+    x, w, ws, bias, si, so = conv_inputs(case, 53)
+    N, H, W, Cc, K, R, S, st, pads, dl = case
+    P = orc.conv_out_size(H, R, dl, pads[0], pads[1], st)
+    Q = orc.conv_out_size(W, S, dl, pads[2], pads[3], st)
+    res = rs = None
+    if mode == "int32":
+        o, sf, bf, act = orc.OUT_INT32, None, None, orc.ACT_NONE
+    else:
+        o = orc.OUT_FP32 if mode.startswith("fp32") else orc.OUT_INT8
+        sf, bf, _ = orc.fold_scales(ws, K, si, so, o, bias)
+        act = orc.ACT_RELU
+        if mode.endswith("res"):
+            res = np.random.default_rng(9).integers(-127, 128, (N, P, Q, K), dtype=np.int8)
+            rs = 0.41 if o == orc.OUT_INT8 else 0.013
+    kw = {} if res is None else {"residual": res, "res_scale": rs}
+    want = orc.conv2d(x, w, sf, bf, (st, st), pads, (dl, dl), 1, act, 0.0, o, **kw)
+    xd = dev(pad_c(x, rup(Cc, 16)))
+    wp = pl.pack_conv_weight(dev(w))
+
+    def go():
+        kw2 = {} if res is None else {"residual": dev(res), "res_scale": rs}
+        return host(pl.conv2d(xd, wp, K, R, S, None if sf is None else dev(sf), None if bf is None else dev(bf),
+                              (st, st), pads, (dl, dl), act, 0.0, o, Cc=Cc, **kw2))
+
+    got = go()
+    assert got.shape == want.shape
+    assert np.array_equal(got, want)
+    monkeypatch.setenv("PL_IGEMM_NO_HALO", "1")
+    assert np.array_equal(go(), want)
+
+
 def test_conv_writes_into_channel_slice(pl):
     """ldy > K: the conv writes a channel slice of a wider buffer (free concat)."""
     case = (1, 10, 10, 32, 32, 3, 3, 1, (1, 1, 1, 1), 1)
