@@ -13,7 +13,9 @@ import torch
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 ROOT = os.path.dirname(HERE)
-LIB_PATH = os.path.join(HERE, "libpl_int8_b200.so")
+# PL_INT8_LIB: developer knob, points the loader at an experimental build of the same C-ABI
+# (tools/build_variant.sh); never a different implementation
+LIB_PATH = os.environ.get("PL_INT8_LIB") or os.path.join(HERE, "libpl_int8_b200.so")
 
 ACT_NONE, ACT_RELU, ACT_RELU6, ACT_LEAKY = 0, 1, 2, 4
 OUT_INT8, OUT_FP32, OUT_INT32 = 0, 1, 2

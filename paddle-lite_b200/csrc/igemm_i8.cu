@@ -19,7 +19,9 @@
 // VIMNMX.RELU for relu+clamp on the float bit pattern, PRMT packing, scale/bias
 // staged in shared memory once per tile.
 #include <cuda.h>
+#include <cstdio>
 #include <cstdlib>
+#include <vector>
 #include <cudaTypedefs.h>
 
 #include "common.cuh"
@@ -35,7 +37,7 @@ static constexpr int kThinWarps = 8;
 static constexpr int kThinThreads = 64 + 32 * (kThinEpiWarps + kThinWarps);
 static constexpr int kMaxStages = 12;
 static constexpr int kMaxResBufs = 6;   // depth of the TMA residual ring
-static constexpr int kHaloBufs = 2;     // mode 3: input halo tiles in flight
+static constexpr int kMaxHaloBufs = 4;  // mode 3: input halo tiles in flight (p.halo_bufs of them)
 
 enum { EPI_GENERIC = 0, EPI_I8_RELU = 1, EPI_I8_SIGNED = 2, EPI_I8_RELU_RES = 3 };
 
@@ -58,8 +60,10 @@ struct IgemmParams {
   const uint32_t* xw;  // mode 2: input words [N][H][W]
   int thin_r, thin_sw;
   int dbg_flags;  // timing experiments (PL_DBG_FLAGS): 1 skip epilogue body, 2 skip MMA issue, 4 skip B loads, 8 skip A loads
+  long long* trace;  // PL_DBG_TRACE: per-role clock64 timeline of CTA 0 (tools/trace_timeline.py)
   int dbg_ashift, dbg_baseoff;  // experiment: MMA A-descriptor starts `dbg_ashift` rows into the stage
-  int b_resident;  // mode 2, one N tile: the whole packed filter stays in smem for the kernel's lifetime
+  int b_resident;  // modes 2 and 3, one N tile: the whole packed filter stays in smem for the kernel's lifetime
+  int halo_bufs;   // mode 3: halo buffers in the A region
   int H, W;
   FastDiv dQ, dPQ;
   int Q, PQ, S;
@@ -259,6 +263,54 @@ __device__ __noinline__ void store_group16(const IgemmParams& p, const uint32_t*
 // one-word-per-pixel input, all loads of a tile in flight at once, and store them into the
 // stage buffers in the 32-byte-swizzled K-major layout the MMA descriptors expect.  One
 // k-block (32 bytes) = 32 / (4 * TSW) filter rows.  No im2col matrix ever exists in HBM.
+// k-steps of one k-block, unrolled: descriptors advance by 32 bytes (2 x 16-byte units)
+template <int KS>
+__device__ __forceinline__ void issue_kblock(uint32_t d_tmem, uint64_t da, uint64_t db, uint32_t idesc,
+                                             bool fresh) {
+#pragma unroll
+  for (int k = 0; k < KS; ++k)
+    umma_i8(d_tmem, da + (uint64_t)(k * 2), db + (uint64_t)(k * 2), idesc, (uint32_t)(!(fresh && k == 0)));
+}
+__device__ __forceinline__ void issue_kblock_n(int ksteps, uint32_t d_tmem, uint64_t da, uint64_t db,
+                                               uint32_t idesc, bool fresh) {
+  if (ksteps == 4) issue_kblock<4>(d_tmem, da, db, idesc, fresh);
+  else if (ksteps == 2) issue_kblock<2>(d_tmem, da, db, idesc, fresh);
+  else issue_kblock<1>(d_tmem, da, db, idesc, fresh);
+}
+// all taps of a resident R x S filter against one halo tile: one straight run of MMAs
+template <int R_, int S_, int KS>
+__device__ __forceinline__ void issue_taps(uint32_t d_tmem, uint64_t da0, uint64_t db0, uint32_t idesc,
+                                           uint32_t tap_step, uint32_t row_pitch, uint32_t b_step, bool fresh) {
+#pragma unroll
+  for (int r = 0; r < R_; ++r)
+#pragma unroll
+    for (int sx = 0; sx < S_; ++sx)
+      issue_kblock<KS>(d_tmem, da0 + (uint64_t)(r * row_pitch + sx * tap_step),
+                       db0 + (uint64_t)((r * S_ + sx) * b_step), idesc, fresh && r == 0 && sx == 0);
+}
+
+// timeline tracing: role r, local tile t (first 64 tiles of CTA 0), event e (0..7)
+// Debug knobs (timeline trace, PL_DBG_FLAGS ablations, descriptor experiments) exist only in
+// builds made with -DPL_DEBUG_KNOBS (tools/build_variant.sh dbg "-DPL_DEBUG_KNOBS"): even
+// never-taken checks in the role loops cost 5-10% on the short-K layers.
+#ifdef PL_DEBUG_KNOBS
+#define PL_DBG_FLAGS_V p.dbg_flags
+#define PL_DBG_ASHIFT_V p.dbg_ashift
+#define PL_DBG_BASEOFF_V p.dbg_baseoff
+#else
+#define PL_DBG_FLAGS_V 0
+#define PL_DBG_ASHIFT_V 0
+#define PL_DBG_BASEOFF_V 0
+#endif
+#ifndef PL_DEBUG_KNOBS
+#define PL_TRACE(r, t, e) do { } while (0)
+#else
+#define PL_TRACE(r, t, e)                                                                   \
+  do {                                                                                      \
+    if (p.trace != nullptr && blockIdx.x == 0 && (t) < 64) p.trace[((r) * 64 + (t)) * 8 + (e)] = clock64(); \
+  } while (0)
+#endif
+
 template <int EPI, int TR = 0, int TSW = 0>
 __global__ void __launch_bounds__(TR > 0 ? kThinThreads : kThreads, 1)
 igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
@@ -266,7 +318,7 @@ igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
                 const __grid_constant__ CUtensorMap tmap_y,
                 const __grid_constant__ CUtensorMap tmap_r, const IgemmParams p) {
   extern __shared__ uint8_t smem_raw[];
-  __shared__ __align__(8) uint64_t bars[2 * kMaxStages + 4 + 2 * kMaxResBufs + 2 * kHaloBufs];
+  __shared__ __align__(8) uint64_t bars[2 * kMaxStages + 4 + 2 * kMaxResBufs + 2 * kMaxHaloBufs + 1];
   __shared__ uint32_t tmem_base_slot;
 
   const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
@@ -279,7 +331,8 @@ igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
   const uint32_t bar_rfull = smem_u32(&bars[2 * kMaxStages + 4]);
   const uint32_t bar_rempty = smem_u32(&bars[2 * kMaxStages + 4 + kMaxResBufs]);
   const uint32_t bar_afull = smem_u32(&bars[2 * kMaxStages + 4 + 2 * kMaxResBufs]);
-  const uint32_t bar_aempty = smem_u32(&bars[2 * kMaxStages + 4 + 2 * kMaxResBufs + kHaloBufs]);
+  const uint32_t bar_aempty = smem_u32(&bars[2 * kMaxStages + 4 + 2 * kMaxResBufs + kMaxHaloBufs]);
+  const uint32_t bar_bres = smem_u32(&bars[2 * kMaxStages + 4 + 2 * kMaxResBufs + 2 * kMaxHaloBufs]);
   const uint32_t smem_out = smem_base + p.out_stage_off;
   const uint32_t smem_res = smem_base + p.res_stage_off;
   const uint32_t tile_bytes = (uint32_t)(kBM * p.BN);
@@ -287,9 +340,24 @@ igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
   float* const s_bias = s_scale + p.sb_n;
 
   constexpr int EW = TR > 0 ? kThinEpiWarps : kEpiWarps;  // epilogue warps of this instantiation
+  // shfl from lane 0: the compiler then knows the role index is warp-uniform (uniform branches and
+  // uniform registers for the role loops)
+#ifdef PL_EXP_NO_SHFL
   const int warp = threadIdx.x >> 5;
+#else
+  const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0);
+#endif
   const int lane = threadIdx.x & 31;
   const int num_tiles = p.m_tiles * p.n_tiles;
+#if defined(PL_EXP_POLL) && defined(PL_DEBUG_KNOBS)
+  const bool poll_waits = (PL_DBG_FLAGS_V & 256) != 0;
+  auto WAIT = [&](uint32_t bar, uint32_t parity) {
+    if (poll_waits) mbar_wait_poll(bar, parity);
+    else mbar_wait(bar, parity);
+  };
+#else
+#define WAIT(bar, parity) mbar_wait(bar, parity)
+#endif
 
   if (threadIdx.x == 0) {
     tma_prefetch_desc(&tmap_a);
@@ -305,10 +373,11 @@ igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
       mbar_init(bar_tfull + 8 * s, 1);
       mbar_init(bar_tempty + 8 * s, EW);  // one arrival per epilogue warp
     }
-    for (int s = 0; s < kHaloBufs; ++s) {
+    for (int s = 0; s < kMaxHaloBufs; ++s) {
       mbar_init(bar_afull + 8 * s, 1);
       mbar_init(bar_aempty + 8 * s, 1);
     }
+    mbar_init(bar_bres, 1);
     for (int s = 0; s < kMaxResBufs; ++s) {
       mbar_init(bar_rfull + 8 * s, 1);
       mbar_init(bar_rempty + 8 * s, EW);
@@ -353,16 +422,28 @@ igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
     }
     if (TR == 0 && mode == 3) {
       // halo reuse: one tiled 4-D load per (tile, channel block), then the filter taps
-      const int RS = p.R * S;
+      const int RS = p.R * S, halo_bufs = p.halo_bufs;
+      const bool hres = p.b_resident != 0;
+      if (hres) {
+        // single N tile and the packed filter fits: every filter block is loaded exactly once
+        // (channel block major, tap minor: the order the MMA loop walks them)
+        mbar_arrive_expect_tx(bar_bres, (uint32_t)num_kb * tx);
+        uint32_t d = smem_b;
+        for (int cbk = 0; cbk < cspan; cbk += BK)
+          for (int tap = 0, kc = cbk; tap < RS; ++tap, kc += cspan, d += b_bytes)
+            tma_load_2d(d, &tmap_b, bar_bres, kc, 0);
+      }
       int ab = 0;
       uint32_t aph = 0;
-      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+      int lt = 0;
+      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++lt) {
+        PL_TRACE(0, lt, 0);
         const int tn = tile % n_tiles, tm = tile / n_tiles;
         const int n0 = tn * BN;
         const int img = (int)fdiv((uint32_t)tm, p.dBands);
         const int p0 = (tm - img * p.bands) * p.hk;
         if (EPI == EPI_I8_RELU_RES) {
-          mbar_wait(bar_rempty + 8 * rb, rphase ^ 1);
+          WAIT(bar_rempty + 8 * rb, rphase ^ 1);
           {
             mbar_arrive_expect_tx(bar_rfull + 8 * rb, (uint32_t)(p.hk * p.Q * BN));
             for (int j = 0; j < p.panels; ++j)
@@ -372,21 +453,23 @@ igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
           if (++rb == p.res_bufs) { rb = 0; rphase ^= 1; }
         }
         for (int cbk = 0; cbk < cspan; cbk += BK) {
-          mbar_wait(bar_aempty + 8 * ab, aph ^ 1);
+          WAIT(bar_aempty + 8 * ab, aph ^ 1);
+          PL_TRACE(0, lt, 1);
           {
-            if (p.dbg_flags & 8) {
+            if (PL_DBG_FLAGS_V & 8) {
               mbar_arrive(bar_afull + 8 * ab);
             } else {
               mbar_arrive_expect_tx(bar_afull + 8 * ab, p.a_halo_tx);
               tma_load_4d(smem_a + ab * p.a_halo_bytes, &tmap_a, bar_afull + 8 * ab, cbk, -p.pl_, p0 - p.pt, img);
             }
           }
-          if (++ab == kHaloBufs) { ab = 0; aph ^= 1; }
+          PL_TRACE(0, lt, 2);
+          if (++ab == halo_bufs) { ab = 0; aph ^= 1; }
           int kc = cbk;  // K coordinate of the filter block: tap * cspan + channel offset
-          for (int tap = 0; tap < RS; ++tap) {
-            mbar_wait(empty_b, phase ^ 1);
+          for (int tap = 0; tap < RS && !hres; ++tap) {
+            WAIT(empty_b, phase ^ 1);
             {
-              if (p.dbg_flags & 4) {
+              if (PL_DBG_FLAGS_V & 4) {
                 mbar_arrive(full_b);
               } else {
                 mbar_arrive_expect_tx(full_b, tx);
@@ -400,12 +483,15 @@ igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
         }
       }
     }
-    for (int tile = blockIdx.x; tile < num_tiles && !(TR > 0 && p.b_resident) && mode != 3; tile += gridDim.x) {
+    int lt = 0;
+    for (int tile = blockIdx.x; tile < num_tiles && !(TR > 0 && p.b_resident) && mode != 3; tile += gridDim.x, ++lt) {
+      PL_TRACE(0, lt, 0);
       const int tn = tile % n_tiles, tm = tile / n_tiles;
       const int m0 = tm * kBM, n0 = tn * BN;
       if (EPI == EPI_I8_RELU_RES) {
         // residual tile first: it is the largest load of a 1x1 expand layer
-        mbar_wait(bar_rempty + 8 * rb, rphase ^ 1);
+        WAIT(bar_rempty + 8 * rb, rphase ^ 1);
+        PL_TRACE(0, lt, 3);
         {
           mbar_arrive_expect_tx(bar_rfull + 8 * rb, tile_bytes);
           for (int j = 0; j < p.panels; ++j)
@@ -425,7 +511,8 @@ igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
       int kc = 0, cbk = 0, sx = 0;      // K coordinate of B, channel offset inside the tap, tap column
       uint16_t offw = 0, offh = 0;      // im2col filter offsets of the tap
       for (int kb = 0; kb < num_kb; ++kb) {
-        mbar_wait(empty_b, phase ^ 1);
+        WAIT(empty_b, phase ^ 1);
+        if (kb == 0) PL_TRACE(0, lt, 1);
         {
           mbar_arrive_expect_tx(full_b, tx);
           if (TR > 0) {
@@ -450,48 +537,75 @@ igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
           full_b = bar_full; empty_b = bar_empty; dst_a = smem_a; dst_b = smem_b;
         }
       }
+      PL_TRACE(0, lt, 2);
     }
     }
   } else if (warp == 1) {
     // ===================== MMA issuer =====================
+    // ONE elected lane runs the whole nest.  (Measured alternative: all 32 lanes walking the
+    // nest with warp-uniform state in uniform registers and only the MMA under the elected
+    // lane is ~30% slower on the 3x3 layers.)  The issue cost per MMA is what bounds the
+    // short-K layers, so the k-steps of a block and the taps of a resident 3x3 filter are
+    // fully unrolled (issue_kblock / issue_taps).
     if (elect_one()) {
+    constexpr bool leader = true;
+#define PL_MTRACE(t, e) do { if (leader) PL_TRACE(1, t, e); } while (0)
     const uint32_t idesc = make_idesc_i8((uint32_t)p.BN);
     const uint64_t desc_hi = make_smem_desc_base((uint32_t)p.BK);
     const int ksteps = p.BK / 32, stages = p.stages, num_kb = p.num_kb;
     const uint32_t a_step = p.a_stage_bytes >> 4, b_step = p.b_stage_bytes >> 4;
     const uint32_t a_lo0 = smem_a >> 4, b_lo0 = smem_b >> 4;  // shared addresses < 256 KB: 14 bits
     const bool bres = TR > 0 && p.b_resident;
+    const bool skip_mma = (PL_DBG_FLAGS_V & 2) != 0;
     int stage = 0;
     uint32_t phase = 0;
     uint32_t full_b = bar_full, empty_b = bar_empty, a_lo = a_lo0, b_lo = b_lo0;
     int as = 0;
     uint32_t aphase = 0;
-    if (bres) mbar_wait(bar_rfull, 0);
+    if (bres) WAIT(bar_rfull, 0);
     if (TR == 0 && p.mode == 3) {
       const int S = p.S, RS = p.R * p.S, cblocks = p.cblocks;
       const uint32_t tap_step = (uint32_t)p.BK >> 4;                       // next tap column: one pixel
       const uint32_t row_step = (uint32_t)((p.WP - S) * p.BK) >> 4;        // extra step at the end of a filter row
       const uint32_t halo_step = p.a_halo_bytes >> 4;
+      const int halo_bufs = p.halo_bufs;
+      const bool hres = p.b_resident != 0;
       int ab = 0;
       uint32_t aph = 0;
-      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
-        mbar_wait(bar_tempty + 8 * as, aphase ^ 1);
+      if (hres) WAIT(bar_bres, 0);
+      int lt = 0;
+      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++lt) {
+        PL_MTRACE(lt, 0);
+        WAIT(bar_tempty + 8 * as, aphase ^ 1);
+        PL_MTRACE(lt, 1);
         tc_fence_after();
         const uint32_t d_tmem = tmem_base + (uint32_t)as * p.acc_stride;
+        if (hres) b_lo = b_lo0;
         for (int cb = 0; cb < cblocks; ++cb) {
-          mbar_wait(bar_afull + 8 * ab, aph);
+          WAIT(bar_afull + 8 * ab, aph);
+          if (cb == 0) PL_MTRACE(lt, 2);
+          tc_fence_after();
           uint32_t t_lo = a_lo0 + (uint32_t)ab * halo_step;  // descriptor start of tap (0, 0)
           int sx = 0;
-          for (int tap = 0; tap < RS; ++tap) {
-            mbar_wait(full_b, phase);
-            tc_fence_after();
-            {
-              const uint64_t da = desc_hi | (uint64_t)t_lo, db = desc_hi | (uint64_t)b_lo;
-              if (!(p.dbg_flags & 2))
-                for (int k = 0; k < ksteps; ++k)
-                  umma_i8(d_tmem, da + (uint64_t)(k * 2), db + (uint64_t)(k * 2), idesc,
-                          (uint32_t)((cb | tap | k) != 0));
-              umma_commit(empty_b);
+          if (hres && RS == 9 && S == 3 && !skip_mma) {
+            const uint64_t da0 = desc_hi | (uint64_t)t_lo, db0 = desc_hi | (uint64_t)b_lo;
+            const uint32_t row_pitch = (uint32_t)(p.WP * p.BK) >> 4;
+            if (ksteps == 4) issue_taps<3, 3, 4>(d_tmem, da0, db0, idesc, tap_step, row_pitch, b_step, cb == 0);
+            else if (ksteps == 2) issue_taps<3, 3, 2>(d_tmem, da0, db0, idesc, tap_step, row_pitch, b_step, cb == 0);
+            else issue_taps<3, 3, 1>(d_tmem, da0, db0, idesc, tap_step, row_pitch, b_step, cb == 0);
+            b_lo += 9 * b_step;
+            umma_commit(bar_aempty + 8 * ab);
+            if (cb == cblocks - 1) umma_commit(bar_tfull + 8 * as);
+          }
+          for (int tap = 0; tap < RS && !(hres && RS == 9 && S == 3 && !skip_mma); ++tap) {
+            if (!hres) {  // streamed filter: one ring stage per tap
+              WAIT(full_b, phase);
+              tc_fence_after();
+            }
+            const uint64_t da = desc_hi | (uint64_t)t_lo, db = desc_hi | (uint64_t)b_lo;
+            if (leader) {
+              if (!skip_mma) issue_kblock_n(ksteps, d_tmem, da, db, idesc, (cb | tap) == 0);
+              if (!hres) umma_commit(empty_b);
               if (tap == RS - 1) {
                 umma_commit(bar_aempty + 8 * ab);
                 if (cb == cblocks - 1) umma_commit(bar_tfull + 8 * as);
@@ -499,34 +613,43 @@ igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
             }
             t_lo += tap_step;
             if (++sx == S) { sx = 0; t_lo += row_step; }
-            ++stage; full_b += 8; empty_b += 8; b_lo += b_step;
-            if (stage == stages) { stage = 0; phase ^= 1; full_b = bar_full; empty_b = bar_empty; b_lo = b_lo0; }
+            b_lo += b_step;
+            if (!hres) {
+              ++stage; full_b += 8; empty_b += 8;
+              if (stage == stages) { stage = 0; phase ^= 1; full_b = bar_full; empty_b = bar_empty; b_lo = b_lo0; }
+            }
           }
-          if (++ab == kHaloBufs) { ab = 0; aph ^= 1; }
+          if (++ab == halo_bufs) { ab = 0; aph ^= 1; }
         }
+        PL_MTRACE(lt, 4);
         if (++as == 2) { as = 0; aphase ^= 1; }
       }
     }
-    for (int tile = blockIdx.x; tile < num_tiles && !(TR == 0 && p.mode == 3); tile += gridDim.x) {
-      mbar_wait(bar_tempty + 8 * as, aphase ^ 1);
+    int lt = 0;
+    for (int tile = blockIdx.x; tile < num_tiles && !(TR == 0 && p.mode == 3); tile += gridDim.x, ++lt) {
+      PL_MTRACE(lt, 0);
+      WAIT(bar_tempty + 8 * as, aphase ^ 1);
+      PL_MTRACE(lt, 1);
       tc_fence_after();
       const uint32_t d_tmem = tmem_base + (uint32_t)as * p.acc_stride;
       if (bres) b_lo = b_lo0;
       for (int kb = 0; kb < num_kb; ++kb) {
-        mbar_wait(full_b, phase);
+        WAIT(full_b, phase);
+        if (kb == 0) PL_MTRACE(lt, 2);
         tc_fence_after();
         {
           uint64_t da = desc_hi | (uint64_t)a_lo;
           const uint64_t db = desc_hi | (uint64_t)b_lo;
-          if (p.dbg_ashift) {  // descriptor-semantics experiment (tools/dbg_rowshift.py)
-            const uint32_t start = (a_lo << 4) + (uint32_t)(p.dbg_ashift * p.BK);
+          if (PL_DBG_ASHIFT_V) {  // descriptor-semantics experiment (tools/dbg_rowshift.py)
+            const uint32_t start = (a_lo << 4) + (uint32_t)(PL_DBG_ASHIFT_V * p.BK);
             da = desc_hi | (uint64_t)((start >> 4) & 0x3fff);
-            if (p.dbg_baseoff) da |= (uint64_t)((start >> 7) & 7u) << 49;
+            if (PL_DBG_BASEOFF_V) da |= (uint64_t)((start >> 7) & 7u) << 49;
           }
-          for (int k = 0; k < ksteps; ++k)
-            umma_i8(d_tmem, da + (uint64_t)(k * 2), db + (uint64_t)(k * 2), idesc, (uint32_t)((kb | k) != 0));
-          umma_commit(empty_b);
-          if (kb == num_kb - 1) umma_commit(bar_tfull + 8 * as);
+          if (leader) {
+            if (!skip_mma) issue_kblock_n(ksteps, d_tmem, da, db, idesc, kb == 0);
+            umma_commit(empty_b);
+            if (kb == num_kb - 1) umma_commit(bar_tfull + 8 * as);
+          }
         }
         ++stage; full_b += 8; empty_b += 8; a_lo += a_step; b_lo += b_step;
         if (stage == stages) {
@@ -535,9 +658,11 @@ igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
           if (!bres) b_lo = b_lo0;
         }
       }
+      PL_MTRACE(lt, 4);
       if (++as == 2) { as = 0; aphase ^= 1; }
     }
     }
+    __syncwarp();
   } else if (TR > 0 && warp >= 2 + EW) {
     // ===================== thin-input gather (8 warps, two threads per A row) =====================
     constexpr int R_ = TR > 0 ? TR : 1, SW_ = TSW > 0 ? TSW : 4;
@@ -589,7 +714,7 @@ igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
         if (!mine[i]) continue;
         const uint32_t cnt = base + (uint32_t)kb;
         const uint32_t st = cnt % (uint32_t)p.stages, ph = (cnt / (uint32_t)p.stages) & 1u;
-        mbar_wait(bar_empty + 8 * st, ph ^ 1);
+        WAIT(bar_empty + 8 * st, ph ^ 1);
         const uint32_t dst = smem_a + st * p.a_stage_bytes + rowoff;
         if constexpr (SW_ == 8) {
           st_shared_v4(dst + ((0u ^ swx) << 4), xr[i][0], xr[i][1], xr[i][2], xr[i][3]);
@@ -662,7 +787,11 @@ igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
       stage_scale_bias(blockIdx.x, 0);
     }
     asm volatile("bar.sync 1, %0;" ::"n"(32 * EW) : "memory");
-    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+    int lt = 0;
+    const int trole = (warp == 2 && lane == 0) ? 2 : ((warp == 1 + EW && lane == 0) ? 3 : -1);
+#define PL_ETRACE(e) do { if (trole >= 0) PL_TRACE(trole, lt, e); } while (0)
+    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++lt) {
+      PL_ETRACE(0);
       const int tn = tile % p.n_tiles, tm = tile / p.n_tiles;
       long long row = (long long)tm * kBM + arow;  // output pixel index (generic epilogue)
       int himg = 0, hp0 = 0;
@@ -676,8 +805,17 @@ igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
       }
       const int n0 = tn * p.BN;
       const uint32_t sb0 = p.sb_all ? (uint32_t)n0 : (uint32_t)(as * 256);
-      if (EPI == EPI_I8_RELU_RES) mbar_wait(bar_rfull + 8 * rb, rphase);
-      mbar_wait(bar_tfull + 8 * as, aphase);
+      if (PL_DBG_FLAGS_V & 32) {
+        if (lane == 0) {
+          if (EPI == EPI_I8_RELU_RES) WAIT(bar_rfull + 8 * rb, rphase);
+          WAIT(bar_tfull + 8 * as, aphase);
+        }
+        __syncwarp();
+      } else {
+        if (EPI == EPI_I8_RELU_RES) WAIT(bar_rfull + 8 * rb, rphase);
+        WAIT(bar_tfull + 8 * as, aphase);
+      }
+      PL_ETRACE(1);
       tc_fence_after();
       const uint32_t t_addr = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)as * p.acc_stride;
       const uint32_t res_base = smem_res + (uint32_t)rb * tile_bytes + rowoff;
@@ -685,7 +823,7 @@ igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
       const uint32_t out_base = out_tile + rowoff;
       // TMEM reads are double buffered: unit i+1 is in flight while unit i runs through the ALUs
       uint32_t accb[2][16];
-      const bool skip_epi = (p.dbg_flags & 1) != 0;
+      const bool skip_epi = (PL_DBG_FLAGS_V & 1) != 0;
       if (cq < units && !skip_epi) tmem_ld_32x32b_x16(t_addr + (uint32_t)(cq * 16), accb[0]);
 #pragma unroll
       for (int i = 0; i < 16 / CQ; ++i) {
@@ -727,9 +865,11 @@ igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
       // the warp's TMEM reads (tcgen05.wait::ld) and residual reads are complete: one lane
       // per warp releases the accumulator / residual buffer (512 single arrivals on one
       // mbarrier cost more than the whole epilogue of a narrow tile)
+      PL_ETRACE(2);
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(bar_tempty + 8 * as);
+      PL_ETRACE(3);
       if (++as == 2) { as = 0; aphase ^= 1; }
       if (EPI == EPI_I8_RELU_RES) {
         if (lane == 0) mbar_arrive(bar_rempty + 8 * rb);
@@ -746,12 +886,14 @@ igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
           __syncwarp();
         }
         // generic-proxy smem writes -> visible to the TMA engine, then one thread stores
-        fence_proxy_async();
+        if (!(PL_DBG_FLAGS_V & 64)) fence_proxy_async();
       }
-      asm volatile("bar.sync 2, %0;" ::"n"(32 * EW) : "memory");
+      PL_ETRACE(4);
+      if (!(PL_DBG_FLAGS_V & 128)) asm volatile("bar.sync 2, %0;" ::"n"(32 * EW) : "memory");
+      PL_ETRACE(5);
       if (kFast) {
         if (warp == 2) {
-          if (elect_one() && !(p.dbg_flags & 16)) {
+          if (elect_one() && !(PL_DBG_FLAGS_V & 16)) {
             for (int j = 0; j < p.panels; ++j) {
               if (halo)  // box = PW channels x Q pixels x hk rows of image himg; rows >= P are clipped
                 tma_store_4d(&tmap_y, out_tile + (uint32_t)(j * kBM * p.PW), n0 + j * p.PW, 0, hp0, himg);
@@ -773,6 +915,7 @@ igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
           asm volatile("bar.sync 1, %0;" ::"n"(32 * EW) : "memory");
         }
       }
+      PL_ETRACE(6);
     }
     if (kFast && warp == 2) {
       if (elect_one()) bulk_wait_group<0>();
@@ -989,6 +1132,33 @@ int launch_one(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& 
     configured = true;
   }
   const int threads = TR > 0 ? kThinThreads : kThreads;
+  const char* trace_path = getenv("PL_DBG_TRACE");
+  if (trace_path && *trace_path) {
+    // debugging aid: synchronous launch, CTA 0's timeline written as text (role tile e0..e7)
+    static long long* dbuf = nullptr;
+    const size_t n = 4 * 64 * 8;
+    if (!dbuf) PL_CUDA_OK(cudaMalloc(&dbuf, n * sizeof(long long)));
+    PL_CUDA_OK(cudaMemsetAsync(dbuf, 0, n * sizeof(long long), (cudaStream_t)stream));
+    IgemmParams q = p;
+    q.trace = dbuf;
+    igemm_i8_kernel<EPI, TR, TSW><<<grid, threads, smem, (cudaStream_t)stream>>>(ta, tb, ty, tr, q);
+    ++g_launches;
+    PL_CUDA_OK(cudaStreamSynchronize((cudaStream_t)stream));
+    std::vector<long long> h(n);
+    PL_CUDA_OK(cudaMemcpy(h.data(), dbuf, n * sizeof(long long), cudaMemcpyDeviceToHost));
+    if (FILE* fp = fopen(trace_path, "w")) {
+      fprintf(fp, "# mode %d BN %d BK %d num_kb %d tiles %d grid %d stages %d out_bufs %d res_bufs %d halo_bufs %d b_resident %d\n",
+              p.mode, p.BN, p.BK, p.num_kb, p.m_tiles * p.n_tiles, grid, p.stages, p.out_bufs, p.res_bufs, p.halo_bufs, p.b_resident);
+      for (int r = 0; r < 4; ++r)
+        for (int t = 0; t < 64; ++t) {
+          fprintf(fp, "%d %d", r, t);
+          for (int e = 0; e < 8; ++e) fprintf(fp, " %lld", h[(r * 64 + t) * 8 + e]);
+          fprintf(fp, "\n");
+        }
+      fclose(fp);
+    }
+    return launch_status();
+  }
   igemm_i8_kernel<EPI, TR, TSW><<<grid, threads, smem, (cudaStream_t)stream>>>(ta, tb, ty, tr, p);
   ++g_launches;
   return launch_status();
@@ -1048,6 +1218,9 @@ int launch_igemm(const CUtensorMap& ta, const CUtensorMap& tb, IgemmParams& p, p
   p.out_bufs = 0;
   p.res_bufs = 2;
   int extra = 0;
+  // halo mode with a single N tile keeps the whole packed filter in smem when it fits
+  bool hres = p.mode == 3 && p.n_tiles == 1 && env_int("PL_IGEMM_NO_HRES", 0) == 0 &&
+              2 * (int)p.a_halo_bytes + p.num_kb * (int)p.b_stage_bytes <= budget;
   if (p.tma_out) {
     int rc;
     if (p.mode == 3)  // dense band of hk output rows x Q pixels
@@ -1066,9 +1239,14 @@ int launch_igemm(const CUtensorMap& ta, const CUtensorMap& tb, IgemmParams& p, p
     // buffer (the TMA store of tile i drains while tile i+1 is written), then a deeper
     // residual ring, the rest goes back to the mainloop
     const int min_stages = env_int("PL_IGEMM_MIN_STAGES", 3);
-    const int main_min = p.mode == 3 ? kHaloBufs * (int)p.a_halo_bytes + 4 * (int)p.b_stage_bytes
-                                     : min_stages * stage_bytes;
+    int main_min = p.mode == 3 ? 2 * (int)p.a_halo_bytes + 4 * (int)p.b_stage_bytes : min_stages * stage_bytes;
+    if (hres) main_min = 2 * (int)p.a_halo_bytes + p.num_kb * (int)p.b_stage_bytes;
     int left = budget - main_min - tile - (p.tma_res ? 2 * tile : 0);
+    if (hres && left < 0) {  // the filter does not fit beside the staging buffers: stream it
+      hres = false;
+      main_min = 2 * (int)p.a_halo_bytes + 4 * (int)p.b_stage_bytes;
+      left = budget - main_min - tile - (p.tma_res ? 2 * tile : 0);
+    }
     if (left < 0) left = 0;
     p.out_bufs = 1;
     if (left >= tile && env_int("PL_IGEMM_OUT_BUFS", 2) >= 2) {
@@ -1085,14 +1263,23 @@ int launch_igemm(const CUtensorMap& ta, const CUtensorMap& tb, IgemmParams& p, p
     }
     extra = p.out_bufs * tile + (p.tma_res ? p.res_bufs * tile : 0);
   }
-  p.b_resident = (p.mode == 2 && p.n_tiles == 1) ? 1 : 0;
+  p.b_resident = ((p.mode == 2 && p.n_tiles == 1) || hres) ? 1 : 0;
   p.dbg_flags = env_int("PL_DBG_FLAGS", 0);
   p.dbg_ashift = env_int("PL_DBG_ASHIFT", 0);
   p.dbg_baseoff = env_int("PL_DBG_BASEOFF", 0);
   int stages;
   size_t ring_bytes;
-  if (p.mode == 3) {
-    p.a_region_bytes = (uint32_t)kHaloBufs * p.a_halo_bytes;
+  if (p.mode == 3 && hres) {
+    // resident filter; what is left goes to halo buffers (deeper input prefetch)
+    const int bbytes = p.num_kb * (int)p.b_stage_bytes;
+    int hb = (budget - extra - bbytes) / (int)p.a_halo_bytes;
+    p.halo_bufs = hb > kMaxHaloBufs ? kMaxHaloBufs : hb;
+    p.a_region_bytes = (uint32_t)p.halo_bufs * p.a_halo_bytes;
+    stages = 2;  // the stage ring and its barriers are unused
+    ring_bytes = (size_t)p.a_region_bytes + (size_t)bbytes;
+  } else if (p.mode == 3) {
+    p.halo_bufs = 2;
+    p.a_region_bytes = 2u * p.a_halo_bytes;
     stages = (budget - extra - (int)p.a_region_bytes) / (int)p.b_stage_bytes;
     if (stages > kMaxStages) stages = kMaxStages;
     ring_bytes = (size_t)p.a_region_bytes + (size_t)stages * p.b_stage_bytes;

@@ -1,2 +1,4 @@
 #!/bin/bash
-for f in 0 1 2 3 4 6 7 8 12 14 15; do echo "flags=$f"; PL_DBG_FLAGS=$f timeout 120 python tools/layer_bench.py r2_3x3_64 r3_3x3_128 2>&1 | grep b256; done
+# usage: gpu_dbgflags.sh "layers" flags...
+L=$1; shift
+for f in "$@"; do echo "flags=$f"; PL_INT8_LIB=$PWD/paddle-lite_b200/variants/libpl_dbg.so PL_DBG_FLAGS=$f timeout 120 python tools/layer_bench.py $L 2>&1 | grep b256; done
