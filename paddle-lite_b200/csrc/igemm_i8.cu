@@ -30,11 +30,13 @@ namespace pl {
 
 static constexpr int kBM = 128;            // rows of D per tile (TMEM lanes)
 static constexpr int kEpiWarps = 16;                   // TMA-fed launches
-static constexpr int kThreads = 64 + 32 * kEpiWarps;  // 18 warps
+static constexpr int kThreads = 64 + 32 * kEpiWarps + 32;  // producer, MMA, 16 epilogue warps, store warp
 // thin-input launches: 8 epilogue warps + 8 gather warps (two threads per A row)
 static constexpr int kThinEpiWarps = 8;
 static constexpr int kThinWarps = 8;
-static constexpr int kThinThreads = 64 + 32 * (kThinEpiWarps + kThinWarps);
+static constexpr int kThinThreads = 64 + 32 * (kThinEpiWarps + kThinWarps) + 32;  // + store warp
+static constexpr int kStoreWarp = 18;     // same index in both layouts
+static constexpr int kMaxAccStages = 4;   // TMEM accumulators in flight (512 columns / BN, at most 4)
 static constexpr int kMaxStages = 12;
 static constexpr int kMaxResBufs = 6;   // depth of the TMA residual ring
 static constexpr int kMaxHaloBufs = 4;  // mode 3: input halo tiles in flight (p.halo_bufs of them)
@@ -64,6 +66,7 @@ struct IgemmParams {
   int dbg_ashift, dbg_baseoff;  // experiment: MMA A-descriptor starts `dbg_ashift` rows into the stage
   int b_resident;  // modes 2 and 3, one N tile: the whole packed filter stays in smem for the kernel's lifetime
   int halo_bufs;   // mode 3: halo buffers in the A region
+  int acc_stages;  // TMEM accumulator ring depth
   int H, W;
   FastDiv dQ, dPQ;
   int Q, PQ, S;
@@ -318,7 +321,11 @@ igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
                 const __grid_constant__ CUtensorMap tmap_y,
                 const __grid_constant__ CUtensorMap tmap_r, const IgemmParams p) {
   extern __shared__ uint8_t smem_raw[];
-  __shared__ __align__(8) uint64_t bars[2 * kMaxStages + 4 + 2 * kMaxResBufs + 2 * kMaxHaloBufs + 1];
+  constexpr int kBarTFull = 2 * kMaxStages, kBarTEmpty = kBarTFull + kMaxAccStages;
+  constexpr int kBarRFull = kBarTEmpty + kMaxAccStages, kBarREmpty = kBarRFull + kMaxResBufs;
+  constexpr int kBarAFull = kBarREmpty + kMaxResBufs, kBarAEmpty = kBarAFull + kMaxHaloBufs;
+  constexpr int kBarBRes = kBarAEmpty + kMaxHaloBufs, kBarStaged = kBarBRes + 1, kBarOFree = kBarStaged + 2;
+  __shared__ __align__(8) uint64_t bars[kBarOFree + 2];
   __shared__ uint32_t tmem_base_slot;
 
   const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
@@ -326,13 +333,15 @@ igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
   const uint32_t smem_b = smem_base + p.a_region_bytes;
   const uint32_t bar_full = smem_u32(&bars[0]);
   const uint32_t bar_empty = smem_u32(&bars[kMaxStages]);
-  const uint32_t bar_tfull = smem_u32(&bars[2 * kMaxStages]);
-  const uint32_t bar_tempty = smem_u32(&bars[2 * kMaxStages + 2]);
-  const uint32_t bar_rfull = smem_u32(&bars[2 * kMaxStages + 4]);
-  const uint32_t bar_rempty = smem_u32(&bars[2 * kMaxStages + 4 + kMaxResBufs]);
-  const uint32_t bar_afull = smem_u32(&bars[2 * kMaxStages + 4 + 2 * kMaxResBufs]);
-  const uint32_t bar_aempty = smem_u32(&bars[2 * kMaxStages + 4 + 2 * kMaxResBufs + kMaxHaloBufs]);
-  const uint32_t bar_bres = smem_u32(&bars[2 * kMaxStages + 4 + 2 * kMaxResBufs + 2 * kMaxHaloBufs]);
+  const uint32_t bar_tfull = smem_u32(&bars[kBarTFull]);
+  const uint32_t bar_tempty = smem_u32(&bars[kBarTEmpty]);
+  const uint32_t bar_rfull = smem_u32(&bars[kBarRFull]);
+  const uint32_t bar_rempty = smem_u32(&bars[kBarREmpty]);
+  const uint32_t bar_afull = smem_u32(&bars[kBarAFull]);
+  const uint32_t bar_aempty = smem_u32(&bars[kBarAEmpty]);
+  const uint32_t bar_bres = smem_u32(&bars[kBarBRes]);
+  const uint32_t bar_staged = smem_u32(&bars[kBarStaged]);  // staging buffer written by every epilogue warp
+  const uint32_t bar_ofree = smem_u32(&bars[kBarOFree]);    // staging buffer read out by its TMA store
   const uint32_t smem_out = smem_base + p.out_stage_off;
   const uint32_t smem_res = smem_base + p.res_stage_off;
   const uint32_t tile_bytes = (uint32_t)(kBM * p.BN);
@@ -369,9 +378,13 @@ igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
       mbar_init(bar_full + 8 * s, TR > 0 ? (p.b_resident ? 0 : 1) + kBM / 32 : 1);  // + one per gather warp of the half
       mbar_init(bar_empty + 8 * s, 1);
     }
-    for (int s = 0; s < 2; ++s) {
+    for (int s = 0; s < kMaxAccStages; ++s) {
       mbar_init(bar_tfull + 8 * s, 1);
       mbar_init(bar_tempty + 8 * s, EW);  // one arrival per epilogue warp
+    }
+    for (int s = 0; s < 2; ++s) {
+      mbar_init(bar_staged + 8 * s, EW);
+      mbar_init(bar_ofree + 8 * s, 1);
     }
     for (int s = 0; s < kMaxHaloBufs; ++s) {
       mbar_init(bar_afull + 8 * s, 1);
@@ -622,7 +635,7 @@ igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
           if (++ab == halo_bufs) { ab = 0; aph ^= 1; }
         }
         PL_MTRACE(lt, 4);
-        if (++as == 2) { as = 0; aphase ^= 1; }
+        if (++as == p.acc_stages) { as = 0; aphase ^= 1; }
       }
     }
     int lt = 0;
@@ -659,11 +672,11 @@ igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
         }
       }
       PL_MTRACE(lt, 4);
-      if (++as == 2) { as = 0; aphase ^= 1; }
+      if (++as == p.acc_stages) { as = 0; aphase ^= 1; }
     }
     }
     __syncwarp();
-  } else if (TR > 0 && warp >= 2 + EW) {
+  } else if (TR > 0 && warp >= 2 + EW && warp < kStoreWarp) {
     // ===================== thin-input gather (8 warps, two threads per A row) =====================
     constexpr int R_ = TR > 0 ? TR : 1, SW_ = TSW > 0 ? TSW : 4;
     constexpr int RPK = 8 / SW_;                  // filter rows per 32-byte k-block
@@ -735,6 +748,39 @@ igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
       }
       base += NKB;
     }
+  } else if (warp == kStoreWarp) {
+    // ===================== output store warp =====================
+    // One elected lane turns every staged tile into TMA stores.  The epilogue warps never
+    // meet at a block barrier: they hand a staging buffer over through `staged` (one arrival
+    // per warp) and get it back through `ofree` once the store has read it out.
+    if (EPI != EPI_GENERIC && p.tma_out && elect_one()) {
+      const bool halo = (TR == 0) && p.mode == 3;
+      int ob = 0;
+      uint32_t ophase = 0;
+      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+        const int tn = tile % p.n_tiles, tm = tile / p.n_tiles;
+        const int n0 = tn * p.BN;
+        const uint32_t out_tile = smem_out + (uint32_t)ob * tile_bytes;
+        WAIT(bar_staged + 8 * ob, ophase);
+        if (!(PL_DBG_FLAGS_V & 16)) {
+          if (halo) {  // box = PW channels x Q pixels x hk rows of one image; rows >= P are clipped
+            const int himg = (int)fdiv((uint32_t)tm, p.dBands);
+            const int hp0 = (tm - himg * p.bands) * p.hk;
+            for (int j = 0; j < p.panels; ++j)
+              tma_store_4d(&tmap_y, out_tile + (uint32_t)(j * kBM * p.PW), n0 + j * p.PW, 0, hp0, himg);
+          } else {
+            for (int j = 0; j < p.panels; ++j)
+              tma_store_2d(&tmap_y, out_tile + (uint32_t)(j * kBM * p.PW), n0 + j * p.PW, tm * kBM);
+          }
+          bulk_commit_group();
+          bulk_wait_group_read<0>();
+        }
+        mbar_arrive(bar_ofree + 8 * ob);
+        if (++ob == p.out_bufs) { ob = 0; ophase ^= 1; }
+      }
+      bulk_wait_group<0>();
+    }
+    __syncwarp();
   } else {
     // ===================== epilogue (warps 2..17) =====================
     // warp w owns TMEM lanes [32*(w%4), +32) (hardware rule) and the 16-column units
@@ -765,6 +811,8 @@ igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
     int rb = 0;
     uint32_t rphase = 0;
     int ob = 0;
+    uint32_t ophase = 0;
+    int sbuf = 0;  // per-tile scale / bias buffer (very wide outputs only)
     // folded scale / bias live in smem.  Normally the vectors of every n-tile are staged once
     // here; a global load per tile would sit on the epilogue's critical path (the tile rate of
     // short-K layers is 1 / epilogue latency).  Very wide outputs fall back to per-tile staging
@@ -804,17 +852,15 @@ igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
                                             : (long long)p.M;
       }
       const int n0 = tn * p.BN;
-      const uint32_t sb0 = p.sb_all ? (uint32_t)n0 : (uint32_t)(as * 256);
-      if (PL_DBG_FLAGS_V & 32) {
-        if (lane == 0) {
-          if (EPI == EPI_I8_RELU_RES) WAIT(bar_rfull + 8 * rb, rphase);
-          WAIT(bar_tfull + 8 * as, aphase);
-        }
-        __syncwarp();
-      } else {
+      const uint32_t sb0 = p.sb_all ? (uint32_t)n0 : (uint32_t)(sbuf * 256);
+      // one lane per warp polls (512 threads polling one mbarrier serialise); the warp-level
+      // sync hands the acquired state to the other lanes
+      if (lane == 0) {
         if (EPI == EPI_I8_RELU_RES) WAIT(bar_rfull + 8 * rb, rphase);
         WAIT(bar_tfull + 8 * as, aphase);
+        if (kFast) WAIT(bar_ofree + 8 * ob, ophase ^ 1);
       }
+      __syncwarp();
       PL_ETRACE(1);
       tc_fence_after();
       const uint32_t t_addr = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)as * p.acc_stride;
@@ -862,64 +908,35 @@ igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
           }
         }
       }
-      // the warp's TMEM reads (tcgen05.wait::ld) and residual reads are complete: one lane
-      // per warp releases the accumulator / residual buffer (512 single arrivals on one
-      // mbarrier cost more than the whole epilogue of a narrow tile)
+      // the warp's TMEM reads (tcgen05.wait::ld), residual reads and staging writes are complete:
+      // one lane per warp releases the accumulator and the residual buffer and hands the
+      // staging buffer to the store warp.  No block-level barrier: warps drift apart freely,
+      // a fast warp is already reading the next accumulator while a slow one finishes.
       PL_ETRACE(2);
       tc_fence_before();
+      if (kFast && !(PL_DBG_FLAGS_V & 64)) fence_proxy_async();  // this thread's st.shared -> visible to the TMA engine
       __syncwarp();
-      if (lane == 0) mbar_arrive(bar_tempty + 8 * as);
+      if (lane == 0) {
+        mbar_arrive(bar_tempty + 8 * as);
+        if (EPI == EPI_I8_RELU_RES) mbar_arrive(bar_rempty + 8 * rb);
+        if (kFast) mbar_arrive(bar_staged + 8 * ob);
+      }
       PL_ETRACE(3);
-      if (++as == 2) { as = 0; aphase ^= 1; }
+      if (++as == p.acc_stages) { as = 0; aphase ^= 1; }
       if (EPI == EPI_I8_RELU_RES) {
-        if (lane == 0) mbar_arrive(bar_rempty + 8 * rb);
         if (++rb == p.res_bufs) { rb = 0; rphase ^= 1; }
       }
-      // next tile's scale / bias into the other buffer (last read one tile ago, before
-      // that tile's barrier)
-      if (!p.sb_all && tile + (int)gridDim.x < num_tiles) stage_scale_bias(tile + gridDim.x, as);
       if (kFast) {
-        // the store issued one tile ago has long drained its staging buffer: after the
-        // barrier every thread may write it again
-        if (warp == 2 && p.out_bufs == 2) {  // same (elected) lane that committed the store
-          if (elect_one()) bulk_wait_group_read<0>();
-          __syncwarp();
-        }
-        // generic-proxy smem writes -> visible to the TMA engine, then one thread stores
-        if (!(PL_DBG_FLAGS_V & 64)) fence_proxy_async();
+        if (++ob == p.out_bufs) { ob = 0; ophase ^= 1; }
       }
-      PL_ETRACE(4);
-      if (!(PL_DBG_FLAGS_V & 128)) asm volatile("bar.sync 2, %0;" ::"n"(32 * EW) : "memory");
-      PL_ETRACE(5);
-      if (kFast) {
-        if (warp == 2) {
-          if (elect_one() && !(PL_DBG_FLAGS_V & 16)) {
-            for (int j = 0; j < p.panels; ++j) {
-              if (halo)  // box = PW channels x Q pixels x hk rows of image himg; rows >= P are clipped
-                tma_store_4d(&tmap_y, out_tile + (uint32_t)(j * kBM * p.PW), n0 + j * p.PW, 0, hp0, himg);
-              else
-                tma_store_2d(&tmap_y, out_tile + (uint32_t)(j * kBM * p.PW), n0 + j * p.PW, tm * kBM);
-            }
-            bulk_commit_group();
-          }
-          __syncwarp();
-        }
-        if (p.out_bufs == 2) {
-          ob ^= 1;
-        } else {
-          // single staging buffer (smem-tight launches): drain it before the next tile
-          if (warp == 2) {
-            if (elect_one()) bulk_wait_group_read<0>();
-            __syncwarp();
-          }
-          asm volatile("bar.sync 1, %0;" ::"n"(32 * EW) : "memory");
-        }
+      if (!p.sb_all) {
+        // very wide outputs: next tile's scale / bias into the other buffer, published by a
+        // barrier of the epilogue warps (this mode keeps the warps in step)
+        sbuf ^= 1;
+        if (tile + (int)gridDim.x < num_tiles) stage_scale_bias(tile + gridDim.x, sbuf);
+        asm volatile("bar.sync 2, %0;" ::"n"(32 * EW) : "memory");
       }
       PL_ETRACE(6);
-    }
-    if (kFast && warp == 2) {
-      if (elect_one()) bulk_wait_group<0>();
-      __syncwarp();
     }
   }
 
@@ -1362,7 +1379,9 @@ int common_setup(IgemmParams& p, long long M, int Nout, void* y, int ldy, const 
   p.b_stage_bytes = (uint32_t)((p.BN * p.BK + 1023) / 1024 * 1024);
   p.tx_bytes = (uint32_t)(kBM * p.BK + p.BN * p.BK);
   p.acc_stride = (uint32_t)(p.BN < 32 ? 32 : p.BN);
-  p.tmem_cols = pow2_cols(2 * (int)p.acc_stride);
+  p.acc_stages = 512 / (int)p.acc_stride;
+  if (p.acc_stages > kMaxAccStages) p.acc_stages = kMaxAccStages;
+  p.tmem_cols = pow2_cols(p.acc_stages * (int)p.acc_stride);
   p.y = y;
   p.ldy = ldy;
   p.epi = make_epi(e, Nout);
