@@ -117,8 +117,8 @@ def cpu_reference_rate(net_name, seconds, steps=1, warmup=0):
     # scales: fixed synthetic values (timing does not depend on them)
     s = 0.02
     for op in prog.ops:
-        for k in ("in_scale", "out_scale", "a_scale", "b_scale"):
-            if k in op and op[k] is None:
+        for k in ("in_scale", "out_scale", "a_scale", "b_scale", "res_scale"):
+            if k in op and op[k] is None and (k != "res_scale" or op.get("res")):
                 op[k] = s
     kind = "reference" if orc.ref() is not None else "port"
     engine = "reference" if kind == "reference" else "oracle"

@@ -103,3 +103,20 @@ def test_nsplit_gather_world2_gloo(M, K, N, out_fp32):
         assert p.exitcode == 0
     res = [q.get(timeout=10) for _ in range(2 * world)]
     assert all(ok for _, ok, _ in res), res
+
+
+def test_bench_reference_arm_runs_every_net():
+    """`bench.py --impl reference` (the CPU leg the driver times first) must fill every scale the
+    program leaves to calibration -- including the fused-residual scale of ResNet-50."""
+    import json
+    import subprocess
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    for net in ("resnet50", "mobilenet_v1"):
+        out = subprocess.run([sys.executable, os.path.join(root, "bench.py"), "--impl", "reference", "--net", net,
+                              "--steps", "1", "--warmup", "0"], capture_output=True, text=True, timeout=300)
+        assert out.returncode == 0, out.stderr[-2000:]
+        line = json.loads(out.stdout.strip().splitlines()[-1])
+        assert line["impl"] == "reference" and line["value"] > 0
+        assert line["cpu_baseline"]["kind"] in ("reference", "port")
+        assert line["e2e"]["h2d_bytes_per_step"] == 0
