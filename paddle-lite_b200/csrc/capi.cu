@@ -7,9 +7,19 @@
 //   out size:   lite/operators/conv_op.cc:42-53
 #include "common.cuh"
 
+#include <cstdlib>
+
 namespace pl {
 unsigned long long g_launches = 0;
+
+bool pdl_enabled() {
+  static const bool on = [] {
+    const char* v = getenv("PL_PDL");
+    return !(v && v[0] == '0');
+  }();
+  return on;
 }
+}  // namespace pl
 
 extern "C" int64_t pl_launch_count(void) { return (int64_t)pl::g_launches; }
 

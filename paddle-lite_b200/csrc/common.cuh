@@ -31,6 +31,36 @@ static inline int launch_status() {
 }
 
 // ----------------------------------------------------------------------------
+// programmatic dependent launch: consecutive layers of a network are launched with
+// programmaticStreamSerialization so that the next kernel's CTAs become resident (barrier
+// init, TMEM allocation, descriptor prefetch, scale/bias staging) while the tail of the
+// previous kernel drains.  Every kernel calls pdl_launch_dependents() at its top and
+// pdl_wait() before it first touches memory another kernel may have produced or may still
+// be reading (the wait returns once the whole previous grid has completed and flushed).
+// PL_PDL=0 launches everything fully serialised (A/B switch).
+// ----------------------------------------------------------------------------
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+
+bool pdl_enabled();  // capi.cu
+
+template <typename... KArgs, typename... Args>
+static inline void launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st,
+                              Args&&... args) {
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = st;
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  at[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = at;
+  cfg.numAttrs = pdl_enabled() ? 1 : 0;
+  cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);  // errors surface through launch_status()
+}
+
+// ----------------------------------------------------------------------------
 // epilogue math
 // ----------------------------------------------------------------------------
 __device__ __forceinline__ float apply_act(float v, int act, float arg) {
@@ -192,6 +222,16 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
   while (!mbar_try_wait(bar, parity)) {
     if (clock64() - t0 > 4000000000LL) __trap();
   }
+}
+
+// 4-byte asynchronous global -> shared copy (LDGSTS); src_bytes < 4 zero-fills the rest
+__device__ __forceinline__ void cp_async_4(uint32_t dst, const void* src, uint32_t src_bytes) {
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 4, %2;" ::"r"(dst), "l"(src), "r"(src_bytes) : "memory");
+}
+// this thread's arrival on `bar` happens when all its earlier cp.async copies have landed
+// (.noinc: the arrival is one of the barrier's expected arrivals)
+__device__ __forceinline__ void cp_async_mbar_arrive_noinc(uint32_t bar) {
+  asm volatile("cp.async.mbarrier.arrive.noinc.shared::cta.b64 [%0];" ::"r"(bar) : "memory");
 }
 
 // pure polling variant (mbarrier.test_wait never suspends the thread)

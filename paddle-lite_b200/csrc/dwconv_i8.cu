@@ -237,6 +237,7 @@ __device__ __forceinline__ void dw_columns(const DwParams& p, const uint32_t* im
 // ---- stride 1: T = 4 output columns, RB output rows, window (RB+2) x 6 words ----
 template <int RB, bool FAST>
 __global__ void __launch_bounds__(256, RB <= 2 ? 4 : 2) dw3x3s1_kernel(const DwParams p) {
+  pdl_launch_dependents();
   const uint32_t idx = blockIdx.x * 256u + threadIdx.x;
   if (idx >= (uint32_t)p.items) return;
   const DwItem it = dw_item(p, idx, RB, 4);
@@ -248,6 +249,7 @@ __global__ void __launch_bounds__(256, RB <= 2 ? 4 : 2) dw3x3s1_kernel(const DwP
   dw_columns<6>(p, img, it.q0 - p.pl_, cp, cm);
   uint32_t wa[3][4];
   dw_load_filter(p, c0, wa);
+  pdl_wait();  // the filter is constant; the input comes from the previous kernel
   int acc[RB][4][4];
 #pragma unroll
   for (int o = 0; o < RB; ++o)
@@ -297,6 +299,7 @@ __global__ void __launch_bounds__(256, RB <= 2 ? 4 : 2) dw3x3s1_kernel(const DwP
 // ---- stride 2: T = 2 output columns, RB output rows, window (2*RB+1) x 5 words ----
 template <int RB, bool FAST>
 __global__ void __launch_bounds__(256, 4) dw3x3s2_kernel(const DwParams p) {
+  pdl_launch_dependents();
   const uint32_t idx = blockIdx.x * 256u + threadIdx.x;
   if (idx >= (uint32_t)p.items) return;
   const DwItem it = dw_item(p, idx, RB, 2);
@@ -308,6 +311,7 @@ __global__ void __launch_bounds__(256, 4) dw3x3s2_kernel(const DwParams p) {
   dw_columns<5>(p, img, it.q0 * 2 - p.pl_, cp, cm);
   uint32_t wa[3][4];
   dw_load_filter(p, c0, wa);
+  pdl_wait();
   constexpr int NR = 2 * RB + 1;
   int acc[RB][2][4];
 #pragma unroll
@@ -473,15 +477,15 @@ extern "C" int pl_dwconv2d_i8_nhwc(const int8_t* x, const int8_t* w_crs, void* y
     const unsigned grid = (unsigned)((p.items + 255) / 256);
     if (s1) {
       if (RB == 4) {
-        if (fe) dw3x3s1_kernel<4, true><<<grid, 256, 0, st>>>(p);
-        else dw3x3s1_kernel<4, false><<<grid, 256, 0, st>>>(p);
+        if (fe) launch_pdl(dw3x3s1_kernel<4, true>, dim3(grid), dim3(256), 0, st, p);
+        else launch_pdl(dw3x3s1_kernel<4, false>, dim3(grid), dim3(256), 0, st, p);
       } else {
-        if (fe) dw3x3s1_kernel<2, true><<<grid, 256, 0, st>>>(p);
-        else dw3x3s1_kernel<2, false><<<grid, 256, 0, st>>>(p);
+        if (fe) launch_pdl(dw3x3s1_kernel<2, true>, dim3(grid), dim3(256), 0, st, p);
+        else launch_pdl(dw3x3s1_kernel<2, false>, dim3(grid), dim3(256), 0, st, p);
       }
     } else {
-      if (fe) dw3x3s2_kernel<2, true><<<grid, 256, 0, st>>>(p);
-      else dw3x3s2_kernel<2, false><<<grid, 256, 0, st>>>(p);
+      if (fe) launch_pdl(dw3x3s2_kernel<2, true>, dim3(grid), dim3(256), 0, st, p);
+      else launch_pdl(dw3x3s2_kernel<2, false>, dim3(grid), dim3(256), 0, st, p);
     }
   } else {
     int CGB = 1;

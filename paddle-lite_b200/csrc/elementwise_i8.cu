@@ -321,6 +321,8 @@ __global__ void __launch_bounds__(256)
 pool4_kernel(const uint32_t* __restrict__ x, int ldxw, void* __restrict__ y, int ldy, int H, int W, int C,
              int kh, int kw, int sh, int sw, int pt, int pl_, FastDiv dCw, FastDiv dQ, FastDiv dP,
              uint32_t total, int exclusive, float rescale, int out_dtype, int round_mode, int word_store) {
+  pdl_launch_dependents();
+  pdl_wait();
   const uint32_t idx = blockIdx.x * 256u + threadIdx.x;
   if (idx >= total) return;
   uint32_t t = fdiv(idx, dCw);
@@ -437,10 +439,10 @@ static void launch_pool4(int V, int KF, unsigned grid, cudaStream_t st, const ui
                          int word_store) {
 #define PL_POOL_ARGS x, ldxw, y, ldy, H, W, C, kh, kw, sh, sw, pt, pl_, dCw, dQ, dP, total, exclusive, rescale, \
                      out_dtype, round_mode, word_store
-  if (V == 4 && KF == 3) pool4_kernel<POOL, 4, 3><<<grid, 256, 0, st>>>(PL_POOL_ARGS);
-  else if (V == 4) pool4_kernel<POOL, 4, 0><<<grid, 256, 0, st>>>(PL_POOL_ARGS);
-  else if (KF == 3) pool4_kernel<POOL, 1, 3><<<grid, 256, 0, st>>>(PL_POOL_ARGS);
-  else pool4_kernel<POOL, 1, 0><<<grid, 256, 0, st>>>(PL_POOL_ARGS);
+  if (V == 4 && KF == 3) launch_pdl(pool4_kernel<POOL, 4, 3>, dim3(grid), dim3(256), 0, st, PL_POOL_ARGS);
+  else if (V == 4) launch_pdl(pool4_kernel<POOL, 4, 0>, dim3(grid), dim3(256), 0, st, PL_POOL_ARGS);
+  else if (KF == 3) launch_pdl(pool4_kernel<POOL, 1, 3>, dim3(grid), dim3(256), 0, st, PL_POOL_ARGS);
+  else launch_pdl(pool4_kernel<POOL, 1, 0>, dim3(grid), dim3(256), 0, st, PL_POOL_ARGS);
 #undef PL_POOL_ARGS
 }
 

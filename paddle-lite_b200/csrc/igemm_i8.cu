@@ -37,7 +37,8 @@ static constexpr int kThinWarps = 8;
 static constexpr int kThinThreads = 64 + 32 * (kThinEpiWarps + kThinWarps) + 32;  // + store warp
 static constexpr int kStoreWarp = 18;     // same index in both layouts
 static constexpr int kMaxAccStages = 4;   // TMEM accumulators in flight (512 columns / BN, at most 4)
-static constexpr int kMaxStages = 12;
+static constexpr int kMaxTmaStages = 12;  // TMA-fed modes
+static constexpr int kMaxStages = 28;  // thin mode: 4 KB A stages, the gather runs up to 4 tiles ahead
 static constexpr int kMaxResBufs = 6;   // depth of the TMA residual ring
 static constexpr int kMaxHaloBufs = 4;  // mode 3: input halo tiles in flight (p.halo_bufs of them)
 
@@ -368,6 +369,7 @@ igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
 #define WAIT(bar, parity) mbar_wait(bar, parity)
 #endif
 
+  pdl_launch_dependents();  // the next layer's CTAs may become resident as ours retire (common.cuh)
   if (threadIdx.x == 0) {
     tma_prefetch_desc(&tmap_a);
     tma_prefetch_desc(&tmap_b);
@@ -375,7 +377,11 @@ igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
     if (EPI == EPI_I8_RELU_RES) tma_prefetch_desc(&tmap_r);
     for (int s = 0; s < p.stages; ++s) {
       // TMA arrival (B, and A in the TMA modes) + one arrival per gathered A row
+#ifndef PL_THIN_REG_GATHER
+      mbar_init(bar_full + 8 * s, TR > 0 ? (p.b_resident ? 0 : 1) + kBM : 1);  // + one per gathered A row
+#else
       mbar_init(bar_full + 8 * s, TR > 0 ? (p.b_resident ? 0 : 1) + kBM / 32 : 1);  // + one per gather warp of the half
+#endif
       mbar_init(bar_empty + 8 * s, 1);
     }
     for (int s = 0; s < kMaxAccStages; ++s) {
@@ -433,6 +439,9 @@ igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
           tma_load_2d(smem_b + kb * b_bytes, &tmap_b, bar_rfull, kb * BK, 0);
       }
     }
+    // the filter is constant: resident-filter loads above (and in halo mode below) are issued
+    // before the wait; activations / residual come from the previous kernels
+    if (!(TR == 0 && mode == 3)) pdl_wait();
     if (TR == 0 && mode == 3) {
       // halo reuse: one tiled 4-D load per (tile, channel block), then the filter taps
       const int RS = p.R * S, halo_bufs = p.halo_bufs;
@@ -446,6 +455,7 @@ igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
           for (int tap = 0, kc = cbk; tap < RS; ++tap, kc += cspan, d += b_bytes)
             tma_load_2d(d, &tmap_b, bar_bres, kc, 0);
       }
+      pdl_wait();
       int ab = 0;
       uint32_t aph = 0;
       int lt = 0;
@@ -649,6 +659,9 @@ igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
       for (int kb = 0; kb < num_kb; ++kb) {
         WAIT(full_b, phase);
         if (kb == 0) PL_MTRACE(lt, 2);
+#ifndef PL_THIN_REG_GATHER
+        if (TR > 0) fence_proxy_async();  // cp.async (generic proxy) writes of the gather -> tensor core reads
+#endif
         tc_fence_after();
         {
           uint64_t da = desc_hi | (uint64_t)a_lo;
@@ -687,6 +700,7 @@ igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
     const uint32_t rowoff = (uint32_t)prow * 32u;
     const uint32_t swx = (rowoff >> 7) & 1u;      // 32-byte swizzle: chunk ^= bit 7 of the offset
     uint32_t base = 0;                            // running k-block count -> ring stage and phase
+    pdl_wait();
     for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
       const int tm = tile / p.n_tiles;
       const uint32_t m = (uint32_t)(tm * kBM + prow);
@@ -697,6 +711,46 @@ igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
       const int oq = (int)(rem - op * (uint32_t)p.Q);
       const int ih0 = (int)op * p.sh - p.pt, iw0 = oq * p.sw - p.pl_;
       const uint32_t* img = p.xw + (size_t)n * (size_t)(p.H * p.W);
+#ifndef PL_THIN_REG_GATHER
+      // The window words go global -> shared with 4-byte cp.async (LDGSTS): nothing is held in
+      // registers and nothing waits for the loads, so the gather runs ahead of the tensor core by
+      // the whole stage ring (several tiles of loads in flight per SM; the register version had
+      // one tile in flight and was bound by twice the memory latency per tile).  Zero padding =
+      // a clamped (always valid) address with src-size 0, which cp.async zero-fills.  Each
+      // thread's copies of a k-block complete its own arrival on the stage's `full` barrier
+      // (cp.async.mbarrier.arrive.noinc); the MMA thread orders them against the tensor core's
+      // async-proxy reads with a proxy fence after its wait.
+      const uint32_t* cp[SW_];
+      uint32_t csz[SW_];
+#pragma unroll
+      for (int j = 0; j < SW_; ++j) {
+        const int iw = iw0 + j, c = min(max(iw, 0), p.W - 1);
+        cp[j] = img + c;
+        csz[j] = (iw == c && mok) ? 4u : 0u;
+      }
+#pragma unroll
+      for (int i = 0; i < MYKB; ++i) {
+        const int kb = half + 2 * i;
+        if (kb >= NKB) continue;
+        const uint32_t cnt = base + (uint32_t)kb;
+        const uint32_t st = cnt % (uint32_t)p.stages, ph = (cnt / (uint32_t)p.stages) & 1u;
+        WAIT(bar_empty + 8 * st, ph ^ 1);
+        const uint32_t dst = smem_a + st * p.a_stage_bytes + rowoff;
+#pragma unroll
+        for (int t = 0; t < RPK; ++t) {
+          const int r = kb * RPK + t;  // filter row
+          const int ih = ih0 + r, hc = min(max(ih, 0), p.H - 1);
+          const bool rok = (ih == hc) && r < R_;
+          const uint32_t roff = (uint32_t)(hc * p.W);
+#pragma unroll
+          for (int j = 0; j < SW_; ++j) {
+            const uint32_t wi = (uint32_t)(t * SW_ + j);  // word of the 32-byte row
+            cp_async_4(dst + (((wi >> 2) ^ swx) << 4) + ((wi & 3u) << 2), cp[j] + roff, rok ? csz[j] : 0u);
+          }
+        }
+        cp_async_mbar_arrive_noinc(bar_full + 8 * st);
+      }
+#else
       // zero padding = load a clamped (always valid) address and AND the word away: one
       // mask per window column, one per row, a single LOP3 applies both
       const uint32_t* cp[SW_];
@@ -746,6 +800,7 @@ igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
         const uint32_t cnt = base + (uint32_t)(half + 2 * i);
         if (lane == 0) mbar_arrive(bar_full + 8 * (cnt % (uint32_t)p.stages));
       }
+#endif
       base += NKB;
     }
   } else if (warp == kStoreWarp) {
@@ -754,6 +809,7 @@ igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
     // meet at a block barrier: they hand a staging buffer over through `staged` (one arrival
     // per warp) and get it back through `ofree` once the store has read it out.
     if (EPI != EPI_GENERIC && p.tma_out && elect_one()) {
+      pdl_wait();
       const bool halo = (TR == 0) && p.mode == 3;
       int ob = 0;
       uint32_t ophase = 0;
@@ -834,6 +890,7 @@ igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
     } else if ((int)blockIdx.x < num_tiles) {
       stage_scale_bias(blockIdx.x, 0);
     }
+    pdl_wait();  // the generic path reads the residual / writes y with plain global accesses
     asm volatile("bar.sync 1, %0;" ::"n"(32 * EW) : "memory");
     int lt = 0;
     const int trole = (warp == 2 && lane == 0) ? 2 : ((warp == 1 + EW && lane == 0) ? 3 : -1);
@@ -1176,7 +1233,7 @@ int launch_one(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& 
     }
     return launch_status();
   }
-  igemm_i8_kernel<EPI, TR, TSW><<<grid, threads, smem, (cudaStream_t)stream>>>(ta, tb, ty, tr, p);
+  launch_pdl(igemm_i8_kernel<EPI, TR, TSW>, dim3(grid), dim3(threads), smem, (cudaStream_t)stream, ta, tb, ty, tr, p);
   ++g_launches;
   return launch_status();
 }
@@ -1298,7 +1355,7 @@ int launch_igemm(const CUtensorMap& ta, const CUtensorMap& tb, IgemmParams& p, p
     p.halo_bufs = 2;
     p.a_region_bytes = 2u * p.a_halo_bytes;
     stages = (budget - extra - (int)p.a_region_bytes) / (int)p.b_stage_bytes;
-    if (stages > kMaxStages) stages = kMaxStages;
+    if (stages > kMaxTmaStages) stages = kMaxTmaStages;
     ring_bytes = (size_t)p.a_region_bytes + (size_t)stages * p.b_stage_bytes;
   } else if (p.b_resident) {
     stages = (budget - extra - p.num_kb * (int)p.b_stage_bytes) / (int)p.a_stage_bytes;
@@ -1306,7 +1363,7 @@ int launch_igemm(const CUtensorMap& ta, const CUtensorMap& tb, IgemmParams& p, p
     ring_bytes = (size_t)stages * p.a_stage_bytes + (size_t)p.num_kb * p.b_stage_bytes;
   } else {
     stages = (budget - extra) / stage_bytes;
-    if (stages > kMaxStages) stages = kMaxStages;
+    if (stages > (p.mode == 2 ? kMaxStages : kMaxTmaStages)) stages = p.mode == 2 ? kMaxStages : kMaxTmaStages;
     ring_bytes = (size_t)stages * stage_bytes;
   }
   if (stages < 2 || (p.mode == 2 && stages < p.num_kb)) return PL_ERR_UNSUPPORTED;

@@ -1,4 +1,11 @@
 #!/bin/bash
-# conv/gemm parity then the main layer timings
-timeout 900 python -m pytest tests/test_gpu_parity.py -m gpu -q -x --timeout 300 -k "conv or gemm or thin" 2>&1 | tail -3
-timeout 300 python tools/layer_bench.py ${@:-r2_3x3_64 r3_3x3_128 r4_3x3_256 r5_3x3_512 r2_1x1_64_256_res r3_1x1_128_512_res r4_1x1_256_1024_res r5_1x1_512_2048_res r2_1x1_256_64 r2_1x1_64_64 r4_1x1_1024_256 stem7x7} 2>&1 | grep b256
+# quick check of a change: GPU suite, both network benches (short), optional layer list
+mkdir -p gpurun_out
+timeout 900 python -m pytest tests -m gpu -q --timeout 300 -x 2>&1 | tail -4
+for net in resnet50 mobilenet_v1; do
+  timeout 600 python bench.py --net $net --steps 30 --warmup 5 --no-cpu-baseline --breakdown gpurun_out/bd_$net.json 2> gpurun_out/q_err_$net.log | python -c "
+import json,sys
+l=json.loads(sys.stdin.read().strip().splitlines()[-1]); print('$net', 'ms/step %.4f'%l['ms_per_step'], 'img/s %.0f'%l['value'], 'e2e %.0f'%l['e2e']['value'], l['clocks']['sm_mhz'], l['roofline']['by_kind_ms'])"
+  tail -3 gpurun_out/q_err_$net.log
+done
+if [ $# -gt 0 ]; then python tools/layer_bench.py "$@" --iters 20; fi
