@@ -325,7 +325,7 @@ igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
   constexpr int kBarTFull = 2 * kMaxStages, kBarTEmpty = kBarTFull + kMaxAccStages;
   constexpr int kBarRFull = kBarTEmpty + kMaxAccStages, kBarREmpty = kBarRFull + kMaxResBufs;
   constexpr int kBarAFull = kBarREmpty + kMaxResBufs, kBarAEmpty = kBarAFull + kMaxHaloBufs;
-  constexpr int kBarBRes = kBarAEmpty + kMaxHaloBufs, kBarStaged = kBarBRes + 1, kBarOFree = kBarStaged + 2;
+  constexpr int kBarBRes = kBarAEmpty + kMaxHaloBufs, kBarStaged = kBarBRes + 1, kBarOFree = kBarStaged + kMaxResBufs;
   __shared__ __align__(8) uint64_t bars[kBarOFree + 2];
   __shared__ uint32_t tmem_base_slot;
 
@@ -388,10 +388,8 @@ igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
       mbar_init(bar_tfull + 8 * s, 1);
       mbar_init(bar_tempty + 8 * s, EW);  // one arrival per epilogue warp
     }
-    for (int s = 0; s < 2; ++s) {
-      mbar_init(bar_staged + 8 * s, EW);
-      mbar_init(bar_ofree + 8 * s, 1);
-    }
+    for (int s = 0; s < kMaxResBufs; ++s) mbar_init(bar_staged + 8 * s, EW);
+    for (int s = 0; s < 2; ++s) mbar_init(bar_ofree + 8 * s, 1);
     for (int s = 0; s < kMaxHaloBufs; ++s) {
       mbar_init(bar_afull + 8 * s, 1);
       mbar_init(bar_aempty + 8 * s, 1);
@@ -399,7 +397,9 @@ igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
     mbar_init(bar_bres, 1);
     for (int s = 0; s < kMaxResBufs; ++s) {
       mbar_init(bar_rfull + 8 * s, 1);
-      mbar_init(bar_rempty + 8 * s, EW);
+      // fused residual: the output tile is written IN PLACE over the residual tile, so the buffer
+      // is released by the store warp (one arrival) once its TMA store has read it out
+      mbar_init(bar_rempty + 8 * s, EPI == EPI_I8_RELU_RES ? 1 : EW);
     }
     fence_barrier_init();
   }
@@ -441,6 +441,14 @@ igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
     }
     // the filter is constant: resident-filter loads above (and in halo mode below) are issued
     // before the wait; activations / residual come from the previous kernels
+    const bool bres01 = TR == 0 && mode != 3 && p.b_resident;
+    if (bres01) {
+      // the grid is a multiple of n_tiles: this CTA only ever sees N tile blockIdx.x % n_tiles, whose
+      // whole K extent stays in smem (no per-tile filter re-read from L2, A-only ring stages)
+      mbar_arrive_expect_tx(bar_bres, (uint32_t)num_kb * (uint32_t)(BN * BK));
+      const int n0r = ((int)blockIdx.x % n_tiles) * BN;
+      for (int kb = 0; kb < num_kb; ++kb) tma_load_2d(smem_b + kb * b_bytes, &tmap_b, bar_bres, kb * BK, n0r);
+    }
     if (!(TR == 0 && mode == 3)) pdl_wait();
     if (TR == 0 && mode == 3) {
       // halo reuse: one tiled 4-D load per (tile, channel block), then the filter taps
@@ -545,7 +553,7 @@ igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
           } else {
             tma_load_2d(dst_a, &tmap_a, full_b, kc, m0);
           }
-          tma_load_2d(dst_b, &tmap_b, full_b, kc, n0);
+          if (!bres01) tma_load_2d(dst_b, &tmap_b, full_b, kc, n0);
         }
         kc += BK;
         cbk += BK;
@@ -578,14 +586,14 @@ igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
     const int ksteps = p.BK / 32, stages = p.stages, num_kb = p.num_kb;
     const uint32_t a_step = p.a_stage_bytes >> 4, b_step = p.b_stage_bytes >> 4;
     const uint32_t a_lo0 = smem_a >> 4, b_lo0 = smem_b >> 4;  // shared addresses < 256 KB: 14 bits
-    const bool bres = TR > 0 && p.b_resident;
+    const bool bres = (TR > 0 || p.mode != 3) && p.b_resident;
     const bool skip_mma = (PL_DBG_FLAGS_V & 2) != 0;
     int stage = 0;
     uint32_t phase = 0;
     uint32_t full_b = bar_full, empty_b = bar_empty, a_lo = a_lo0, b_lo = b_lo0;
     int as = 0;
     uint32_t aphase = 0;
-    if (bres) WAIT(bar_rfull, 0);
+    if (bres) WAIT(TR > 0 ? bar_rfull : bar_bres, 0);
     if (TR == 0 && p.mode == 3) {
       const int S = p.S, RS = p.R * p.S, cblocks = p.cblocks;
       const uint32_t tap_step = (uint32_t)p.BK >> 4;                       // next tap column: one pixel
@@ -811,12 +819,14 @@ igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
     if (EPI != EPI_GENERIC && p.tma_out && elect_one()) {
       pdl_wait();
       const bool halo = (TR == 0) && p.mode == 3;
+      constexpr bool kInPlace = EPI == EPI_I8_RELU_RES;  // the output sits in the residual ring
+      const int nbufs = kInPlace ? p.res_bufs : p.out_bufs;
       int ob = 0;
       uint32_t ophase = 0;
       for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
         const int tn = tile % p.n_tiles, tm = tile / p.n_tiles;
         const int n0 = tn * p.BN;
-        const uint32_t out_tile = smem_out + (uint32_t)ob * tile_bytes;
+        const uint32_t out_tile = (kInPlace ? smem_res : smem_out) + (uint32_t)ob * tile_bytes;
         WAIT(bar_staged + 8 * ob, ophase);
         if (!(PL_DBG_FLAGS_V & 16)) {
           if (halo) {  // box = PW channels x Q pixels x hk rows of one image; rows >= P are clipped
@@ -831,8 +841,8 @@ igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
           bulk_commit_group();
           bulk_wait_group_read<0>();
         }
-        mbar_arrive(bar_ofree + 8 * ob);
-        if (++ob == p.out_bufs) { ob = 0; ophase ^= 1; }
+        mbar_arrive(kInPlace ? bar_rempty + 8 * ob : bar_ofree + 8 * ob);
+        if (++ob == nbufs) { ob = 0; ophase ^= 1; }
       }
       bulk_wait_group<0>();
     }
@@ -915,7 +925,7 @@ igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
       if (lane == 0) {
         if (EPI == EPI_I8_RELU_RES) WAIT(bar_rfull + 8 * rb, rphase);
         WAIT(bar_tfull + 8 * as, aphase);
-        if (kFast) WAIT(bar_ofree + 8 * ob, ophase ^ 1);
+        if (kFast && EPI != EPI_I8_RELU_RES) WAIT(bar_ofree + 8 * ob, ophase ^ 1);
       }
       __syncwarp();
       PL_ETRACE(1);
@@ -923,7 +933,8 @@ igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
       const uint32_t t_addr = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)as * p.acc_stride;
       const uint32_t res_base = smem_res + (uint32_t)rb * tile_bytes + rowoff;
       const uint32_t out_tile = smem_out + (uint32_t)ob * tile_bytes;
-      const uint32_t out_base = out_tile + rowoff;
+      // fused residual: each 16-byte chunk of the output replaces the residual chunk it was computed from
+      const uint32_t out_base = EPI == EPI_I8_RELU_RES ? res_base : out_tile + rowoff;
       // TMEM reads are double buffered: unit i+1 is in flight while unit i runs through the ALUs
       uint32_t accb[2][16];
       const bool skip_epi = (PL_DBG_FLAGS_V & 1) != 0;
@@ -975,8 +986,8 @@ igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
       __syncwarp();
       if (lane == 0) {
         mbar_arrive(bar_tempty + 8 * as);
-        if (EPI == EPI_I8_RELU_RES) mbar_arrive(bar_rempty + 8 * rb);
-        if (kFast) mbar_arrive(bar_staged + 8 * ob);
+        if (EPI == EPI_I8_RELU_RES) mbar_arrive(bar_staged + 8 * rb);
+        else if (kFast) mbar_arrive(bar_staged + 8 * ob);
       }
       PL_ETRACE(3);
       if (++as == p.acc_stages) { as = 0; aphase ^= 1; }
@@ -1253,7 +1264,7 @@ bool tma_epilogue_enabled() {
 
 int launch_igemm(const CUtensorMap& ta, const CUtensorMap& tb, IgemmParams& p, pl_stream_t stream) {
   const int tiles = p.m_tiles * p.n_tiles;
-  const int grid = tiles < driver().sm_count ? tiles : driver().sm_count;
+  int grid = tiles < driver().sm_count ? tiles : driver().sm_count;
   // epilogue specialisation (ragged edges inside a fast-path launch use the generic code)
   const EpiParams& e = p.epi;
   int epi = EPI_GENERIC;
@@ -1295,6 +1306,17 @@ int launch_igemm(const CUtensorMap& ta, const CUtensorMap& tb, IgemmParams& p, p
   // halo mode with a single N tile keeps the whole packed filter in smem when it fits
   bool hres = p.mode == 3 && p.n_tiles == 1 && env_int("PL_IGEMM_NO_HRES", 0) == 0 &&
               2 * (int)p.a_halo_bytes + p.num_kb * (int)p.b_stage_bytes <= budget;
+  // TMA-fed GEMM / im2col modes: when the grid is a multiple of n_tiles every CTA keeps seeing the
+  // same N tile, so that filter slice can stay in smem for the kernel's lifetime (the per-tile
+  // re-read of B from L2 is what bounds the short-K layers: B is 2x the A bytes at BN = 256)
+  bool bres01 = (p.mode == 0 || p.mode == 1) && epi != EPI_GENERIC && env_int("PL_IGEMM_NO_BRES01", 0) == 0 &&
+                tiles >= 2 * grid && p.n_tiles <= 16;
+  if (bres01) {
+    const int g = grid - grid % p.n_tiles;
+    const int bbytes = p.num_kb * (int)p.b_stage_bytes;
+    if (g * 20 < grid * 19 || bbytes > env_int("PL_IGEMM_BRES_MAX_KB", 64) * 1024) bres01 = false;
+    else grid = g;
+  }
   if (p.tma_out) {
     int rc;
     if (p.mode == 3)  // dense band of hk output rows x Q pixels
@@ -1315,29 +1337,43 @@ int launch_igemm(const CUtensorMap& ta, const CUtensorMap& tb, IgemmParams& p, p
     const int min_stages = env_int("PL_IGEMM_MIN_STAGES", 3);
     int main_min = p.mode == 3 ? 2 * (int)p.a_halo_bytes + 4 * (int)p.b_stage_bytes : min_stages * stage_bytes;
     if (hres) main_min = 2 * (int)p.a_halo_bytes + p.num_kb * (int)p.b_stage_bytes;
-    int left = budget - main_min - tile - (p.tma_res ? 2 * tile : 0);
+    if (bres01) main_min = min_stages * (int)p.a_stage_bytes + p.num_kb * (int)p.b_stage_bytes;
+    // fused residual: the output tile is written in place over the residual tile (one ring of
+    // res_bufs tiles, no separate staging buffer); otherwise one or two staging buffers
+    const int fixed = p.tma_res ? 2 * tile : tile;
+    int left = budget - main_min - fixed;
     if (hres && left < 0) {  // the filter does not fit beside the staging buffers: stream it
       hres = false;
       main_min = 2 * (int)p.a_halo_bytes + 4 * (int)p.b_stage_bytes;
-      left = budget - main_min - tile - (p.tma_res ? 2 * tile : 0);
+      left = budget - main_min - fixed;
+    }
+    if (bres01 && left < 0) {
+      bres01 = false;
+      grid = tiles < driver().sm_count ? tiles : driver().sm_count;
+      main_min = min_stages * stage_bytes;
+      left = budget - main_min - fixed;
     }
     if (left < 0) left = 0;
-    p.out_bufs = 1;
-    if (left >= tile && env_int("PL_IGEMM_OUT_BUFS", 2) >= 2) {
-      p.out_bufs = 2;
-      left -= tile;
-    }
     if (p.tma_res) {
-      int want = env_int("PL_IGEMM_RES_BUFS", 3);
+      p.out_bufs = 0;
+      int want = env_int("PL_IGEMM_RES_BUFS", 4);
       if (want > kMaxResBufs) want = kMaxResBufs;
       while (p.res_bufs < want && left >= tile) {
         ++p.res_bufs;
         left -= tile;
       }
+    } else {
+      p.out_bufs = 1;
+      if (left >= tile && env_int("PL_IGEMM_OUT_BUFS", 2) >= 2) {
+        p.out_bufs = 2;
+        left -= tile;
+      }
     }
     extra = p.out_bufs * tile + (p.tma_res ? p.res_bufs * tile : 0);
   }
-  p.b_resident = ((p.mode == 2 && p.n_tiles == 1) || hres) ? 1 : 0;
+  if (!p.tma_out) bres01 = false;
+  p.b_resident = ((p.mode == 2 && p.n_tiles == 1) || hres || bres01) ? 1 : 0;
+  if (bres01) p.tx_bytes = p.a_stage_bytes;  // the stage ring carries only A blocks
   p.dbg_flags = env_int("PL_DBG_FLAGS", 0);
   p.dbg_ashift = env_int("PL_DBG_ASHIFT", 0);
   p.dbg_baseoff = env_int("PL_DBG_BASEOFF", 0);
@@ -1359,7 +1395,7 @@ int launch_igemm(const CUtensorMap& ta, const CUtensorMap& tb, IgemmParams& p, p
     ring_bytes = (size_t)p.a_region_bytes + (size_t)stages * p.b_stage_bytes;
   } else if (p.b_resident) {
     stages = (budget - extra - p.num_kb * (int)p.b_stage_bytes) / (int)p.a_stage_bytes;
-    if (stages > kMaxStages) stages = kMaxStages;
+    if (stages > (p.mode == 2 ? kMaxStages : kMaxTmaStages)) stages = p.mode == 2 ? kMaxStages : kMaxTmaStages;
     ring_bytes = (size_t)stages * p.a_stage_bytes + (size_t)p.num_kb * p.b_stage_bytes;
   } else {
     stages = (budget - extra) / stage_bytes;

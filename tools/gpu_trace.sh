@@ -1,5 +1,8 @@
 #!/bin/bash
-# usage: gpu_trace.sh layer [flags]   -> gpurun_out/trace_<layer>_<flags>.txt
+# CTA-0 role timelines of a few layers (needs the dbg variant: tools/build_variant.sh dbg "-DPL_DEBUG_KNOBS")
 mkdir -p gpurun_out
-L=$1; F=${2:-0}
-PL_INT8_LIB=$PWD/paddle-lite_b200/variants/libpl_dbg.so PL_DBG_FLAGS=$F PL_DBG_TRACE=gpurun_out/trace_${L}_$F.txt timeout 120 python tools/layer_bench.py $L --iters 2 --nsets 1 2>&1 | grep b256
+export PL_INT8_LIB=$PWD/paddle-lite_b200/variants/libpl_dbg.so
+for l in "$@"; do
+  PL_DBG_TRACE=gpurun_out/trace_$l.txt timeout 120 python tools/layer_bench.py $l --iters 1 --nsets 1 > /dev/null 2>&1
+  echo "=== $l"; python tools/trace_timeline.py gpurun_out/trace_$l.txt 10 4
+done
