@@ -62,6 +62,10 @@ struct IgemmParams {
   FastDiv dBands, dWP;
   const uint32_t* xw;  // mode 2: input words [N][H][W]
   int thin_r, thin_sw;
+  int thin_group;  // thin mode with a resident filter: a ring stage holds all k-blocks of a tile
+  int thin_shift;  // window starts `thin_shift` (0 / 1) words left of the first tap: the spare word of the
+                   // SW-word window leads, which makes the start even for odd left pads at stride 2
+  int thin_pairs;  // every window starts on an even word of an 8-byte aligned row: 8-byte cp.async
   int dbg_flags;  // timing experiments (PL_DBG_FLAGS): 1 skip epilogue body, 2 skip MMA issue, 4 skip B loads, 8 skip A loads
   long long* trace;  // PL_DBG_TRACE: per-role clock64 timeline of CTA 0 (tools/trace_timeline.py)
   int dbg_ashift, dbg_baseoff;  // experiment: MMA A-descriptor starts `dbg_ashift` rows into the stage
@@ -352,10 +356,15 @@ igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
   constexpr int EW = TR > 0 ? kThinEpiWarps : kEpiWarps;  // epilogue warps of this instantiation
   // shfl from lane 0: the compiler then knows the role index is warp-uniform (uniform branches and
   // uniform registers for the role loops)
-#ifdef PL_EXP_NO_SHFL
-  const int warp = threadIdx.x >> 5;
+  // Role index = REVERSED hardware warp index: the SM's issue arbiter favours the highest warp id
+  // of an SMSP, so the two single-lane roles every tile waits on (TMA producer = role 0, MMA issuer
+  // = role 1) take the top warp ids; with the natural order they queued behind 16 busy epilogue
+  // warps (measured: ~300 cycles from `full` to the commit of a 2-MMA k-block).
+  const int hw_warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0);
+#ifdef PL_EXP_NATURAL_WARP_ORDER
+  const int warp = hw_warp;
 #else
-  const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0);
+  const int warp = kStoreWarp - hw_warp;  // both layouts have kStoreWarp + 1 warps
 #endif
   const int lane = threadIdx.x & 31;
   const int num_tiles = p.m_tiles * p.n_tiles;
@@ -377,11 +386,8 @@ igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
     if (EPI == EPI_I8_RELU_RES) tma_prefetch_desc(&tmap_r);
     for (int s = 0; s < p.stages; ++s) {
       // TMA arrival (B, and A in the TMA modes) + one arrival per gathered A row
-#ifndef PL_THIN_REG_GATHER
-      mbar_init(bar_full + 8 * s, TR > 0 ? (p.b_resident ? 0 : 1) + kBM : 1);  // + one per gathered A row
-#else
-      mbar_init(bar_full + 8 * s, TR > 0 ? (p.b_resident ? 0 : 1) + kBM / 32 : 1);  // + one per gather warp of the half
-#endif
+      // TMA arrival (B when streamed, A in the TMA modes) + one arrival per gather thread
+      mbar_init(bar_full + 8 * s, TR > 0 ? (p.b_resident ? 0 : 1) + (p.thin_group ? 2 * kBM : kBM) : 1);
       mbar_init(bar_empty + 8 * s, 1);
     }
     for (int s = 0; s < kMaxAccStages; ++s) {
@@ -657,7 +663,36 @@ igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
       }
     }
     int lt = 0;
-    for (int tile = blockIdx.x; tile < num_tiles && !(TR == 0 && p.mode == 3); tile += gridDim.x, ++lt) {
+    if (TR > 0 && p.thin_group) {
+      // thin mode, resident filter: a ring stage is a whole tile (all k-blocks): one wait, one proxy
+      // fence, a straight run of MMAs, two commits per tile
+      constexpr int RPK_ = 8 / (TSW > 0 ? TSW : 8), NKB_ = ((TR > 0 ? TR : 1) + RPK_ - 1) / RPK_;
+      constexpr uint32_t kb_step = (uint32_t)(kBM * 32) >> 4;
+      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++lt) {
+        PL_MTRACE(lt, 0);
+        WAIT(bar_tempty + 8 * as, aphase ^ 1);
+        PL_MTRACE(lt, 1);
+        WAIT(full_b, phase);
+        PL_MTRACE(lt, 2);
+        fence_proxy_async();  // cp.async (generic proxy) writes of the gather -> tensor core reads
+        tc_fence_after();
+        const uint32_t d_tmem = tmem_base + (uint32_t)as * p.acc_stride;
+        if (!skip_mma) {
+#pragma unroll
+          for (int kb = 0; kb < NKB_; ++kb)
+            umma_i8(d_tmem, desc_hi | (uint64_t)(a_lo + (uint32_t)kb * kb_step),
+                    desc_hi | (uint64_t)(b_lo0 + (uint32_t)kb * b_step), idesc, (uint32_t)(kb > 0));
+        }
+        umma_commit(empty_b);
+        umma_commit(bar_tfull + 8 * as);
+        ++stage; full_b += 8; empty_b += 8; a_lo += a_step;
+        if (stage == stages) { stage = 0; phase ^= 1; full_b = bar_full; empty_b = bar_empty; a_lo = a_lo0; }
+        PL_MTRACE(lt, 4);
+        if (++as == p.acc_stages) { as = 0; aphase ^= 1; }
+      }
+    }
+    for (int tile = blockIdx.x; tile < num_tiles && !(TR == 0 && p.mode == 3) && !(TR > 0 && p.thin_group);
+         tile += gridDim.x, ++lt) {
       PL_MTRACE(lt, 0);
       WAIT(bar_tempty + 8 * as, aphase ^ 1);
       PL_MTRACE(lt, 1);
@@ -667,9 +702,9 @@ igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
       for (int kb = 0; kb < num_kb; ++kb) {
         WAIT(full_b, phase);
         if (kb == 0) PL_MTRACE(lt, 2);
-#ifndef PL_THIN_REG_GATHER
+        if (kb == 1) PL_MTRACE(lt, 5);
+        if (kb == num_kb - 1) PL_MTRACE(lt, 3);
         if (TR > 0) fence_proxy_async();  // cp.async (generic proxy) writes of the gather -> tensor core reads
-#endif
         tc_fence_after();
         {
           uint64_t da = desc_hi | (uint64_t)a_lo;
@@ -703,13 +738,15 @@ igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
     constexpr int RPK = 8 / SW_;                  // filter rows per 32-byte k-block
     constexpr int NKB = (R_ + RPK - 1) / RPK;
     constexpr int MYKB = (NKB + 1) / 2;           // k-blocks per thread: kb = half, half + 2, ...
-    const int g = (int)threadIdx.x - (64 + 32 * EW);
+    const int g = (warp - 2 - EW) * 32 + lane;
     const int prow = g & (kBM - 1), half = g >> 7;
     const uint32_t rowoff = (uint32_t)prow * 32u;
     const uint32_t swx = (rowoff >> 7) & 1u;      // 32-byte swizzle: chunk ^= bit 7 of the offset
-    uint32_t base = 0;                            // running k-block count -> ring stage and phase
     pdl_wait();
-    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+    uint32_t base_st = 0, base_ph = 0;  // ring stage / phase of this tile's k-block 0
+    int glt = 0;
+    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++glt) {
+      if (g == 0) PL_TRACE(0, glt, 0);
       const int tm = tile / p.n_tiles;
       const uint32_t m = (uint32_t)(tm * kBM + prow);
       const bool mok = m < (uint32_t)p.M;
@@ -717,99 +754,79 @@ igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
       const uint32_t rem = (mok ? m : 0u) - n * (uint32_t)p.PQ;
       const uint32_t op = fdiv(rem, p.dQ);
       const int oq = (int)(rem - op * (uint32_t)p.Q);
-      const int ih0 = (int)op * p.sh - p.pt, iw0 = oq * p.sw - p.pl_;
+      const int ih0 = (int)op * p.sh - p.pt, iw0 = oq * p.sw - p.pl_ - p.thin_shift;
       const uint32_t* img = p.xw + (size_t)n * (size_t)(p.H * p.W);
-#ifndef PL_THIN_REG_GATHER
-      // The window words go global -> shared with 4-byte cp.async (LDGSTS): nothing is held in
-      // registers and nothing waits for the loads, so the gather runs ahead of the tensor core by
-      // the whole stage ring (several tiles of loads in flight per SM; the register version had
-      // one tile in flight and was bound by twice the memory latency per tile).  Zero padding =
-      // a clamped (always valid) address with src-size 0, which cp.async zero-fills.  Each
-      // thread's copies of a k-block complete its own arrival on the stage's `full` barrier
-      // (cp.async.mbarrier.arrive.noinc); the MMA thread orders them against the tensor core's
-      // async-proxy reads with a proxy fence after its wait.
+      // The window words go global -> shared with cp.async (LDGSTS): nothing is held in registers
+      // and nothing waits for the loads, so the gather runs ahead of the tensor core by the whole
+      // stage ring.  Zero padding = a clamped (always valid) address with src-size 0, which
+      // cp.async zero-fills.  A thread's copies complete its own arrival on the stage's `full`
+      // barrier (cp.async.mbarrier.arrive.noinc); the MMA thread orders them against the tensor
+      // core's async-proxy reads with a proxy fence after its wait.
+      // With a resident filter (p.thin_group) a ring stage holds ALL k-blocks of a tile: one
+      // empty-wait and one arrival per thread and tile, one full-wait and one commit per tile in
+      // the MMA thread (its try_wait / fence / commit latencies, ~450 cycles per k-block, were
+      // the whole cost of this mode when every 4 KB k-block was a stage of its own).
       const uint32_t* cp[SW_];
       uint32_t csz[SW_];
 #pragma unroll
       for (int j = 0; j < SW_; ++j) {
         const int iw = iw0 + j, c = min(max(iw, 0), p.W - 1);
-        cp[j] = img + c;
+        cp[j] = img + (p.thin_pairs ? (c & ~1) : c);  // 8-byte copies need an aligned (if unread) address
         csz[j] = (iw == c && mok) ? 4u : 0u;
+      }
+      const bool grouped = p.thin_group != 0;
+      if (grouped) {
+        if (lane == 0) WAIT(bar_empty + 8 * base_st, base_ph ^ 1);
+        __syncwarp();
+        if (g == 0) PL_TRACE(0, glt, 1);
       }
 #pragma unroll
       for (int i = 0; i < MYKB; ++i) {
         const int kb = half + 2 * i;
         if (kb >= NKB) continue;
-        const uint32_t cnt = base + (uint32_t)kb;
-        const uint32_t st = cnt % (uint32_t)p.stages, ph = (cnt / (uint32_t)p.stages) & 1u;
-        WAIT(bar_empty + 8 * st, ph ^ 1);
-        const uint32_t dst = smem_a + st * p.a_stage_bytes + rowoff;
+        // ring position, kept incrementally (a runtime % and / per k-block is expensive here)
+        uint32_t st = base_st, ph = base_ph;
+        uint32_t dst;
+        if (grouped) {
+          dst = smem_a + st * p.a_stage_bytes + (uint32_t)kb * (uint32_t)(kBM * 32) + rowoff;
+        } else {
+          st += (uint32_t)kb;
+          if (st >= (uint32_t)p.stages) { st -= (uint32_t)p.stages; ph ^= 1u; }
+          // one lane per warp polls; the warp sync hands the result over
+          if (lane == 0) WAIT(bar_empty + 8 * st, ph ^ 1);
+          __syncwarp();
+          if (g == 0 && i == 0) PL_TRACE(0, glt, 1);
+          dst = smem_a + st * p.a_stage_bytes + rowoff;
+        }
 #pragma unroll
         for (int t = 0; t < RPK; ++t) {
           const int r = kb * RPK + t;  // filter row
           const int ih = ih0 + r, hc = min(max(ih, 0), p.H - 1);
           const bool rok = (ih == hc) && r < R_;
           const uint32_t roff = (uint32_t)(hc * p.W);
+          if (PL_DBG_FLAGS_V & 32) {
+            // ablation: no copies at all (garbage operands)
+          } else if (p.thin_pairs) {
+            // even window start, even W: a pair of words is inside or outside the row together
 #pragma unroll
-          for (int j = 0; j < SW_; ++j) {
-            const uint32_t wi = (uint32_t)(t * SW_ + j);  // word of the 32-byte row
-            cp_async_4(dst + (((wi >> 2) ^ swx) << 4) + ((wi & 3u) << 2), cp[j] + roff, rok ? csz[j] : 0u);
+            for (int j = 0; j < SW_; j += 2) {
+              const uint32_t wi = (uint32_t)(t * SW_ + j);
+              cp_async_8(dst + (((wi >> 2) ^ swx) << 4) + ((wi & 3u) << 2), cp[j] + roff, rok ? 2u * csz[j] : 0u);
+            }
+          } else {
+#pragma unroll
+            for (int j = 0; j < SW_; ++j) {
+              const uint32_t wi = (uint32_t)(t * SW_ + j);  // word of the 32-byte row
+              cp_async_4(dst + (((wi >> 2) ^ swx) << 4) + ((wi & 3u) << 2), cp[j] + roff, rok ? csz[j] : 0u);
+            }
           }
         }
-        cp_async_mbar_arrive_noinc(bar_full + 8 * st);
+        if (!grouped) cp_async_mbar_arrive_noinc(bar_full + 8 * st);
       }
-#else
-      // zero padding = load a clamped (always valid) address and AND the word away: one
-      // mask per window column, one per row, a single LOP3 applies both
-      const uint32_t* cp[SW_];
-      uint32_t cm[SW_];
-#pragma unroll
-      for (int j = 0; j < SW_; ++j) {
-        const int iw = iw0 + j, c = min(max(iw, 0), p.W - 1);
-        cp[j] = img + c;
-        cm[j] = (iw == c && mok) ? 0xffffffffu : 0u;
-      }
-      // this thread's words: all loads in flight before the first use
-      uint32_t xr[MYKB * RPK][SW_];
-#pragma unroll
-      for (int t = 0; t < MYKB * RPK; ++t) {
-        const int r = (half + 2 * (t / RPK)) * RPK + (t % RPK);  // filter row of slot t
-        const int ih = ih0 + r, hc = min(max(ih, 0), p.H - 1);
-        const uint32_t rm = (ih == hc && r < R_) ? 0xffffffffu : 0u;
-        const uint32_t roff = (uint32_t)(hc * p.W);
-#pragma unroll
-        for (int j = 0; j < SW_; ++j) xr[t][j] = __ldg(cp[j] + roff) & cm[j] & rm;
-      }
-      // write this thread's k-blocks behind ONE proxy fence, then publish them
-      bool mine[MYKB];
-#pragma unroll
-      for (int i = 0; i < MYKB; ++i) {
-        const int kb = half + 2 * i;
-        mine[i] = kb < NKB;
-        if (!mine[i]) continue;
-        const uint32_t cnt = base + (uint32_t)kb;
-        const uint32_t st = cnt % (uint32_t)p.stages, ph = (cnt / (uint32_t)p.stages) & 1u;
-        WAIT(bar_empty + 8 * st, ph ^ 1);
-        const uint32_t dst = smem_a + st * p.a_stage_bytes + rowoff;
-        if constexpr (SW_ == 8) {
-          st_shared_v4(dst + ((0u ^ swx) << 4), xr[i][0], xr[i][1], xr[i][2], xr[i][3]);
-          st_shared_v4(dst + ((1u ^ swx) << 4), xr[i][4], xr[i][5], xr[i][6], xr[i][7]);
-        } else {
-          st_shared_v4(dst + ((0u ^ swx) << 4), xr[2 * i][0], xr[2 * i][1], xr[2 * i][2], xr[2 * i][3]);
-          st_shared_v4(dst + ((1u ^ swx) << 4), xr[2 * i + 1][0], xr[2 * i + 1][1], xr[2 * i + 1][2],
-                       xr[2 * i + 1][3]);
-        }
-      }
-      fence_proxy_async();  // generic-proxy stores -> visible to the tensor core's async proxy
-      __syncwarp();         // every lane's stores are fenced before the warp's single arrival
-#pragma unroll
-      for (int i = 0; i < MYKB; ++i) {
-        if (!mine[i]) continue;
-        const uint32_t cnt = base + (uint32_t)(half + 2 * i);
-        if (lane == 0) mbar_arrive(bar_full + 8 * (cnt % (uint32_t)p.stages));
-      }
-#endif
-      base += NKB;
+      if (grouped) cp_async_mbar_arrive_noinc(bar_full + 8 * base_st);
+      if (g == 0) PL_TRACE(0, glt, 2);
+      base_st += grouped ? 1u : (uint32_t)NKB;  // NKB <= stages (checked on the host)
+      if (base_st >= (uint32_t)p.stages) { base_st -= (uint32_t)p.stages; base_ph ^= 1u; }
     }
   } else if (warp == kStoreWarp) {
     // ===================== output store warp =====================
@@ -851,9 +868,9 @@ igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
     // ===================== epilogue (warps 2..17) =====================
     // warp w owns TMEM lanes [32*(w%4), +32) (hardware rule) and the 16-column units
     // cq, cq+CQ, cq+2CQ, ... of the tile (CQ = epilogue warps / 4)
-    const int quarter = warp & 3;
+    const int quarter = hw_warp & 3;  // TMEM lane quarter is a property of the hardware warp id
     const int cq = (warp - 2) >> 2;
-    const int etid = threadIdx.x - 64;
+    const int etid = (warp - 2) * 32 + lane;
     constexpr bool kFast = (EPI != EPI_GENERIC);  // int8 paths: swizzled smem staging + TMA store
     constexpr int CQ = EW / 4;  // warps per TMEM lane quarter = column groups
     const int units = p.BN >> 4;
@@ -1090,14 +1107,14 @@ __global__ void pack_conv_weight_kernel(const int8_t* __restrict__ w, int8_t* __
 // thin-input filter packing: OHWI [K,R,S,C<=4] -> [K][NKB][32 bytes]; k-block kb holds
 // 32/(4*SW) filter rows of SW words, word j of a row = the 4 channel weights of tap s = j
 __global__ void pack_thin_weight_kernel(const int8_t* __restrict__ w, int8_t* __restrict__ out, int K, int R,
-                                        int S, int C, int SW, int row_bytes) {
+                                        int S, int C, int SW, int row_bytes, int shift) {
   const long long total = (long long)K * row_bytes;
   for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
        i += (long long)gridDim.x * blockDim.x) {
     const int k = (int)(i / row_bytes), b = (int)(i % row_bytes);
     const int word = b >> 2, c = b & 3;
-    const int r = word / SW, s_ = word % SW;
-    out[i] = (r < R && s_ < S && c < C) ? w[(((long long)k * R + r) * S + s_) * C + c] : (int8_t)0;
+    const int r = word / SW, s_ = word % SW - shift;
+    out[i] = (r < R && s_ >= 0 && s_ < S && c < C) ? w[(((long long)k * R + r) * S + s_) * C + c] : (int8_t)0;
   }
 }
 
@@ -1373,6 +1390,10 @@ int launch_igemm(const CUtensorMap& ta, const CUtensorMap& tb, IgemmParams& p, p
   }
   if (!p.tma_out) bres01 = false;
   p.b_resident = ((p.mode == 2 && p.n_tiles == 1) || hres || bres01) ? 1 : 0;
+  if (p.mode == 2 && p.b_resident && env_int("PL_THIN_NO_GROUP", 0) == 0) {
+    p.thin_group = 1;
+    p.a_stage_bytes = (uint32_t)p.num_kb * (uint32_t)(kBM * p.BK);  // a stage = every k-block of a tile
+  }
   if (bres01) p.tx_bytes = p.a_stage_bytes;  // the stage ring carries only A blocks
   p.dbg_flags = env_int("PL_DBG_FLAGS", 0);
   p.dbg_ashift = env_int("PL_DBG_ASHIFT", 0);
@@ -1402,7 +1423,7 @@ int launch_igemm(const CUtensorMap& ta, const CUtensorMap& tb, IgemmParams& p, p
     if (stages > (p.mode == 2 ? kMaxStages : kMaxTmaStages)) stages = p.mode == 2 ? kMaxStages : kMaxTmaStages;
     ring_bytes = (size_t)stages * stage_bytes;
   }
-  if (stages < 2 || (p.mode == 2 && stages < p.num_kb)) return PL_ERR_UNSUPPORTED;
+  if (stages < 2 || (p.mode == 2 && !p.thin_group && stages < p.num_kb)) return PL_ERR_UNSUPPORTED;
   p.stages = stages;
   if (p.mode != 3) p.a_region_bytes = (uint32_t)stages * p.a_stage_bytes;
   p.out_stage_off = (uint32_t)ring_bytes;
@@ -1603,6 +1624,7 @@ extern "C" int pl_conv2d_i8_nhwc(const int8_t* x, const int8_t* w_packed, void* 
 
 // ---- thin first layers: direct conv on one-word-per-pixel input ------------------
 static int thin_sw(int S) { return S <= 4 ? 4 : 8; }
+static int thin_shift(int S) { return S < thin_sw(S) ? 1 : 0; }  // spare window word in front (see IgemmParams)
 static int thin_nkb(int R, int S) {
   const int rpk = 8 / thin_sw(S);
   return (R + rpk - 1) / rpk;
@@ -1626,7 +1648,7 @@ extern "C" int pl_pack_thin_conv_weight_i8(const int8_t* w_ohwi, int8_t* w_thin,
   const long long total = (long long)K * row_bytes;
   const int blocks = (int)((total + 255) / 256 > 1024 ? 1024 : (total + 255) / 256);
   pack_thin_weight_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(w_ohwi, w_thin, K, R, S, C, thin_sw(S),
-                                                                    row_bytes);
+                                                                    row_bytes, thin_shift(S));
   ++g_launches;
   return launch_status();
 }
@@ -1667,6 +1689,9 @@ extern "C" int pl_thin_conv2d_i8_nhwc(const int8_t* x, const int8_t* w_thin, voi
   p.dPQ = make_fastdiv((uint32_t)(P * Q));
   p.thin_r = d->R;
   p.thin_sw = thin_sw(d->S);
+  p.thin_shift = thin_shift(d->S);
+  p.thin_pairs = (d->stride_w % 2 == 0) && ((d->pad_l + p.thin_shift) % 2 == 0) && (d->W % 2 == 0) &&
+                 ((reinterpret_cast<uintptr_t>(x) & 7) == 0) && env_int("PL_THIN_NO_PAIRS", 0) == 0;
   p.tx_bytes = (uint32_t)(p.BN * p.BK);  // only the filter tile arrives by TMA
   CUtensorMap tb;
   rc = encode_2d(&tb, w_thin, (uint64_t)nkb * 32, (uint64_t)d->K, (uint64_t)nkb * 32, p.BK, p.BN);

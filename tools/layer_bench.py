@@ -29,6 +29,13 @@ LAYERS = {
     "r4_1x1_256_1024_res": (14, 14, 256, 1024, 1, 1, 0, "relu", True),
     "r4_1x1_1024_256": (14, 14, 1024, 256, 1, 1, 0, "relu", False),
     "r5_3x3_512": (7, 7, 512, 512, 3, 1, 1, "relu", False),
+    "r3_1x1_512_128": (28, 28, 512, 128, 1, 1, 0, "relu", False),
+    "r3_1x1_256_128": (56, 56, 256, 128, 1, 1, 0, "relu", False),
+    "r5_1x1_2048_512": (7, 7, 2048, 512, 1, 1, 0, "relu", False),
+    "r3_3x3s2_128": (56, 56, 128, 128, 3, 2, 1, "relu", False),
+    "r4_3x3s2_256": (28, 28, 256, 256, 3, 2, 1, "relu", False),
+    "m_pw_112_32_64": (112, 112, 32, 64, 1, 1, 0, "relu", False),
+    "m_pw_14_512_512": (14, 14, 512, 512, 1, 1, 0, "relu", False),
     "r5_1x1_512_2048_res": (7, 7, 512, 2048, 1, 1, 0, "relu", True),
     "dw_112_32_s1": (112, 112, 32, 32, 3, 1, 1, "relu", "dw"),
     "dw_112_64_s2": (112, 112, 64, 64, 3, 2, 1, "relu", "dw"),

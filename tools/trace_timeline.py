@@ -3,8 +3,8 @@ usage: trace_timeline.py trace.txt [first_tile] [n_tiles]"""
 import sys
 
 NAMES = {
-    0: ["top", "wait-empty(A)", "loads issued", "wait-rempty"],
-    1: ["top", "wait-tempty", "wait-full(first)", "mma issued", "commits"],
+    0: ["top", "wait-empty(A)", "loads issued", "wait-rempty/last-empty"],
+    1: ["top", "wait-tempty", "wait-full(first)", "wait-full(last)", "commits", "wait-full(2nd)"],
     2: ["top", "wait-tfull", "body done", "arrived", "pre-bar", "post-bar", "end"],
     3: ["top", "wait-tfull", "body done", "arrived", "pre-bar", "post-bar", "end"],
 }
