@@ -160,6 +160,35 @@ int pl_pack_thin_conv_weight_i8(const int8_t* w_ohwi, int8_t* w_thin, int K, int
                                 int C, pl_stream_t stream);
 int pl_thin_conv2d_i8_nhwc(const int8_t* x, const int8_t* w_thin, void* y,
                            const pl_conv_desc* d, const pl_epilogue* e, pl_stream_t stream);
+/* thin first layers with stride 2, space-to-depth form (the fast path for 7x7/s2/p3 and 3x3/s2/p1
+ * stems): the input lives as 16-byte "s2d pixels" = 2x2 original pixels x 4 channels (byte order
+ * dy, dx, c), [N][HP][WS] with zero borders, written by pl_quantize_nchw_f32_to_s2d_i8 into a buffer
+ * of pl_s2d_geometry(...).bytes that the caller zero-filled once.  A stride-2 R x S conv is then a
+ * stride-1 TA x TB-tap conv over 16-byte pixels; every output row's A operand is TA contiguous
+ * spans of the buffer (1-D bulk copies) that the tensor core reads in place through overlapping
+ * un-swizzled descriptors -- no im2col and no gather.  Same arithmetic as pl_conv2d_i8_nhwc on the
+ * original NHWC tensor (the replaced reference path is the same ConvComputeInt8,
+ * lite/kernels/cuda/conv_compute.cc:55-106).  Supported: stride 2x2, dilation 1, C <= 4, even H/W,
+ * pad_t == pad_l, R == S, Q <= 128 and at most 4 taps per axis after the 2x2 fold. */
+typedef struct pl_s2d_geometry {
+  int supported;
+  int HP, WS;        /* padded s2d rows / 16-byte pixels per row */
+  int pad_s;         /* border rows / pixels in front (top and left) */
+  int shift;         /* original tap r sits at s2d tap a, sub-row dy with r = 2a + dy - shift */
+  int TA, TB;        /* tap rows, taps per row (even) */
+  int P, Q;          /* output size */
+  size_t bytes;      /* buffer size incl. the read-ahead slack after the last row */
+} pl_s2d_geometry;
+pl_s2d_geometry pl_s2d_conv_geometry(int N, int H, int W, int C, int R, int S, int stride_h, int stride_w,
+                                     int pad_t, int pad_b, int pad_l, int pad_r, int dil_h, int dil_w);
+int pl_quantize_nchw_f32_to_s2d_i8(const float* x, int8_t* y_s2d, int N, int C, int H, int W,
+                                   const pl_s2d_geometry* g, float scale, int round_mode, pl_stream_t stream);
+size_t pl_s2d_conv_packed_weight_bytes(int K, const pl_s2d_geometry* g);
+int pl_pack_s2d_conv_weight_i8(const int8_t* w_ohwi, int8_t* w_s2d, int K, int R, int S, int C,
+                               const pl_s2d_geometry* g, pl_stream_t stream);
+/* d describes the ORIGINAL conv (H, W, C, R, S, strides, pads; ldx is ignored) */
+int pl_s2d_conv2d_i8(const int8_t* x_s2d, const int8_t* w_s2d, void* y, const pl_conv_desc* d,
+                     const pl_epilogue* e, pl_stream_t stream);
 /* plain layout transforms; elem_bytes 1 or 4; ld = NHWC pixel pitch (elements) */
 int pl_nchw_to_nhwc(const void* x, void* y, int N, int C, int H, int W, int ld,
                     int elem_bytes, pl_stream_t stream);

@@ -36,6 +36,11 @@ class ConvDesc(C.Structure):
         "pad_t", "pad_b", "pad_l", "pad_r", "dil_h", "dil_w", "groups")]
 
 
+class S2dGeometry(C.Structure):
+    _fields_ = [("supported", C.c_int), ("HP", C.c_int), ("WS", C.c_int), ("pad_s", C.c_int), ("shift", C.c_int),
+                ("TA", C.c_int), ("TB", C.c_int), ("P", C.c_int), ("Q", C.c_int), ("bytes", C.c_size_t)]
+
+
 def build(verbose=False):
     """Compile the CUDA library in-tree for sm_100a (nvcc cross-compiles without a GPU)."""
     out = subprocess.run(["make", "-C", os.path.join(HERE, "csrc"), "-j8"],
@@ -59,6 +64,8 @@ def lib():
         L.pl_launch_count.restype = C.c_int64
         L.pl_version.restype = C.c_char_p
         L.pl_conv_packed_weight_bytes.restype = C.c_size_t
+        L.pl_s2d_conv_geometry.restype = S2dGeometry
+        L.pl_s2d_conv_packed_weight_bytes.restype = C.c_size_t
         _lib = L
     return _lib
 
@@ -272,6 +279,52 @@ def thin_conv2d(x, w_thin, K, R, S, Cc, scale, bias, strides=(1, 1), pads=(0, 0,
     e = make_epilogue(scale, bias, act, act_arg, out, rnd)
     _check(lib().pl_thin_conv2d_i8_nhwc(_ptr(x), _ptr(w_thin), _ptr(y), C.byref(d), C.byref(e), _stream()),
            "pl_thin_conv2d_i8_nhwc")
+    return y
+
+
+def s2d_geometry(N, H, W, Cc, R, S, strides, pads, dil=(1, 1)):
+    """Space-to-depth form of a stride-2 thin stem (include/pl_int8.h: pl_s2d_geometry); .supported == 0
+    when the conv does not qualify."""
+    return lib().pl_s2d_conv_geometry(N, H, W, Cc, R, S, strides[0], strides[1], pads[0], pads[1], pads[2],
+                                      pads[3], dil[0], dil[1])
+
+
+def s2d_input_buffer(g, device):
+    """Zero-filled buffer for the s2d input (the borders must stay zero)."""
+    return torch.zeros(g.bytes, dtype=torch.int8, device=device)
+
+
+def quantize_nchw_to_s2d(x, scale, g, y=None, rnd=ROUND_ARM):
+    N, Cc, H, W = x.shape
+    if y is None:
+        y = s2d_input_buffer(g, x.device)
+    _check(lib().pl_quantize_nchw_f32_to_s2d_i8(_ptr(x.contiguous()), _ptr(y), N, Cc, H, W, C.byref(g), _f(scale),
+                                                rnd, _stream()), "pl_quantize_nchw_f32_to_s2d_i8")
+    return y
+
+
+def pack_s2d_conv_weight(w_ohwi, g):
+    K, R, S, Cc = w_ohwi.shape
+    out = torch.empty(lib().pl_s2d_conv_packed_weight_bytes(K, C.byref(g)), dtype=torch.int8, device=w_ohwi.device)
+    _check(lib().pl_pack_s2d_conv_weight_i8(_ptr(w_ohwi.contiguous()), _ptr(out), K, R, S, Cc, C.byref(g),
+                                            _stream()), "pl_pack_s2d_conv_weight_i8")
+    return out
+
+
+def s2d_conv2d(x_s2d, w_s2d, N, H, W, Cc, K, R, S, scale, bias, strides=(2, 2), pads=(0, 0, 0, 0), act=ACT_NONE,
+               act_arg=0.0, out=OUT_INT8, rnd=ROUND_ARM, y=None, ldy=None):
+    """Stride-2 thin stem on the space-to-depth input written by quantize_nchw_to_s2d."""
+    P = conv_out_size(H, R, 1, pads[0], pads[1], strides[0])
+    Q = conv_out_size(W, S, 1, pads[2], pads[3], strides[1])
+    ldy = K if ldy is None else ldy
+    if y is None:
+        y = torch.empty((N, P, Q, ldy), dtype=_TORCH_OUT[out], device=x_s2d.device)
+        if ldy != K:
+            y.zero_()
+    d = conv_desc(N, H, W, Cc, K, R, S, strides, pads, (1, 1), 1, 4, ldy)
+    e = make_epilogue(scale, bias, act, act_arg, out, rnd)
+    _check(lib().pl_s2d_conv2d_i8(_ptr(x_s2d), _ptr(w_s2d), _ptr(y), C.byref(d), C.byref(e), _stream()),
+           "pl_s2d_conv2d_i8")
     return y
 
 

@@ -278,6 +278,12 @@ __device__ __forceinline__ void tma_load_4d(uint32_t dst, const void* desc, uint
       "l"(desc), "r"(bar), "r"(c0), "r"(c1), "r"(c2), "r"(c3)
       : "memory");
 }
+// 1-D bulk copy global -> shared (no tensor map): `bytes` contiguous bytes, 16-byte aligned both sides
+__device__ __forceinline__ void bulk_load_1d(uint32_t dst, const void* src, uint32_t bytes, uint32_t bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dst),
+               "l"(src), "r"(bytes), "r"(bar)
+               : "memory");
+}
 __device__ __forceinline__ void tma_store_4d(const void* desc, uint32_t src, int c0, int c1, int c2, int c3) {
   asm volatile("cp.async.bulk.tensor.4d.global.shared::cta.bulk_group [%0, {%2, %3, %4, %5}], [%1];" ::"l"(desc),
                "r"(src), "r"(c0), "r"(c1), "r"(c2), "r"(c3)
@@ -387,6 +393,14 @@ __host__ __device__ __forceinline__ uint64_t make_smem_desc_base(uint32_t row_by
   const uint64_t layout = row_bytes == 128 ? 2ull : (row_bytes == 64 ? 4ull : 6ull);
   const uint64_t sbo = (8ull * row_bytes) >> 4;  // 8-row core-matrix group pitch
   return (1ull << 16) | (sbo << 32) | (1ull << 46) | (layout << 61);
+}
+// Un-swizzled K-major operand whose rows are 16 bytes apart: a core matrix is 8 rows x 16 bytes
+// (128 contiguous bytes), SBO = 128 B between 8-row groups, and LBO = 16 B between the two 16-byte
+// halves of a K = 32 step -- i.e. the second half of row r IS the first half of row r + 1.  Over a
+// plain array of 16-byte pixels this reads A[r][0..31] = pixels r, r + 1: two horizontally adjacent
+// filter taps of the space-to-depth stem per MMA, with no im2col copy at all.
+__host__ __device__ __forceinline__ uint64_t make_smem_desc_pix16() {
+  return (1ull << 16) | (8ull << 32) | (1ull << 46);
 }
 // instruction descriptor: D=S32, A=B=signed int8, K-major both, M=128
 __host__ __device__ __forceinline__ uint32_t make_idesc_i8(uint32_t n) {

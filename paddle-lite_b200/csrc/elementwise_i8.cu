@@ -229,6 +229,33 @@ quant_nchw_to_word_kernel(const float* __restrict__ x, uint4* __restrict__ y, in
   }
 }
 
+// fp32 NCHW -> int8 space-to-depth pixels (pl_int8.h: pl_s2d_geometry): thread = one 16-byte pixel
+// = 2x2 original pixels x 4 channels; float2 loads (coalesced 8 bytes per lane and row), one
+// 16-byte store.  Only the interior is written: the borders stay zero from the caller's memset.
+__global__ void __launch_bounds__(256)
+quant_nchw_to_s2d_kernel(const float* __restrict__ x, uint4* __restrict__ y, int C, int H, int W, int HP, int WS,
+                         int pad_s, float scale, float inv, int round_mode) {
+  const int n = blockIdx.z, hs = blockIdx.y;
+  const int ws = blockIdx.x * blockDim.x + threadIdx.x;
+  const int Ws = W >> 1;
+  if (ws >= Ws) return;
+  const float* xs = x + (long long)n * C * H * W + (long long)(2 * hs) * W + 2 * ws;
+  int q[2][2][4];
+#pragma unroll
+  for (int c = 0; c < 4; ++c) {
+#pragma unroll
+    for (int dy = 0; dy < 2; ++dy) {
+      float2 f = make_float2(0.f, 0.f);
+      if (c < C) f = __ldg(reinterpret_cast<const float2*>(xs + (long long)c * H * W + dy * W));
+      q[dy][0][c] = c < C ? round_sat_i8(quant_pre(f.x, scale, inv, round_mode), round_mode) : 0;
+      q[dy][1][c] = c < C ? round_sat_i8(quant_pre(f.y, scale, inv, round_mode), round_mode) : 0;
+    }
+  }
+  y[((long long)n * HP + hs + pad_s) * WS + ws + pad_s] =
+      make_uint4(pack4_i8(q[0][0][0], q[0][0][1], q[0][0][2], q[0][0][3]), pack4_i8(q[0][1][0], q[0][1][1], q[0][1][2], q[0][1][3]),
+                 pack4_i8(q[1][0][0], q[1][0][1], q[1][0][2], q[1][0][3]), pack4_i8(q[1][1][0], q[1][1][1], q[1][1][2], q[1][1][3]));
+}
+
 // ------------------------------------------------------------------ pooling
 __global__ void __launch_bounds__(256)
 pool_kernel(const int8_t* __restrict__ x, int ldx, void* __restrict__ y, int ldy, int N, int H, int W,
@@ -594,6 +621,19 @@ extern "C" int pl_quantize_nchw_f32_to_nhwc_i8(const float* x, int8_t* y, int N,
   dim3 grid((unsigned)((HW + 63) / 64), (unsigned)N);
   quant_nchw_to_nhwc_kernel<<<grid, 256, (size_t)64 * ldy, (cudaStream_t)stream>>>(
       x, y, C, HW, ldy, scale, 1.f / scale, round_mode);
+  ++g_launches;
+  return launch_status();
+}
+
+extern "C" int pl_quantize_nchw_f32_to_s2d_i8(const float* x, int8_t* y_s2d, int N, int C, int H, int W,
+                                              const pl_s2d_geometry* g, float scale, int round_mode,
+                                              pl_stream_t stream) {
+  if (!x || !y_s2d || !g || !g->supported || N <= 0 || C <= 0 || C > 4 || !(scale > 0.f)) return PL_ERR_ARG;
+  if ((H & 1) || (W & 1) || N > 65535 || H / 2 > 65535) return PL_ERR_UNSUPPORTED;
+  if (!al16(y_s2d) || (reinterpret_cast<uintptr_t>(x) & 7)) return PL_ERR_ALIGN;
+  dim3 grid((unsigned)((W / 2 + 127) / 128), (unsigned)(H / 2), (unsigned)N);
+  quant_nchw_to_s2d_kernel<<<grid, 128, 0, (cudaStream_t)stream>>>(x, reinterpret_cast<uint4*>(y_s2d), C, H, W, g->HP,
+                                                                  g->WS, g->pad_s, scale, 1.f / scale, round_mode);
   ++g_launches;
   return launch_status();
 }

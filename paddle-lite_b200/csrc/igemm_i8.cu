@@ -62,6 +62,14 @@ struct IgemmParams {
   FastDiv dBands, dWP;
   const uint32_t* xw;  // mode 2: input words [N][H][W]
   int thin_r, thin_sw;
+  // space-to-depth stem (mode 3 with s2d = 1): the input is [N][HP][WS] 16-byte pixels (2x2 original
+  // pixels x 4 channels, zero borders in memory); a tile is one output row (<= 128 pixels); its A
+  // operand is s2d_ta raw row spans of (128 + taps - 1) pixels fetched by 1-D bulk copies and read
+  // through make_smem_desc_pix16 descriptors
+  int s2d, s2d_ta, s2d_kpr;            // tap rows, K = 32 steps per tap row
+  uint32_t s2d_span_bytes, s2d_span_pitch;
+  long long s2d_row_bytes, s2d_img_bytes;
+  const int8_t* xs2d;
   int thin_group;  // thin mode with a resident filter: a ring stage holds all k-blocks of a tile
   int thin_shift;  // window starts `thin_shift` (0 / 1) words left of the first tap: the spare word of the
                    // SW-word window leads, which makes the start even for odd left pads at stride 2
@@ -473,7 +481,25 @@ igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
       int ab = 0;
       uint32_t aph = 0;
       int lt = 0;
-      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++lt) {
+      if (p.s2d) {
+        // one output row per tile: s2d_ta contiguous spans, one bulk copy each
+        const int ta = p.s2d_ta;
+        const uint32_t span = p.s2d_span_bytes, pitch = p.s2d_span_pitch;
+        for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++lt) {
+          PL_TRACE(0, lt, 0);
+          const int img = (int)fdiv((uint32_t)tile, p.dBands);
+          const int p0 = tile - img * p.bands;
+          WAIT(bar_aempty + 8 * ab, aph ^ 1);
+          PL_TRACE(0, lt, 1);
+          mbar_arrive_expect_tx(bar_afull + 8 * ab, p.a_halo_tx);
+          const int8_t* src = p.xs2d + (long long)img * p.s2d_img_bytes + (long long)p0 * p.s2d_row_bytes;
+          uint32_t dst = smem_a + ab * p.a_halo_bytes;
+          for (int a = 0; a < ta; ++a, src += p.s2d_row_bytes, dst += pitch) bulk_load_1d(dst, src, span, bar_afull + 8 * ab);
+          PL_TRACE(0, lt, 2);
+          if (++ab == halo_bufs) { ab = 0; aph ^= 1; }
+        }
+      }
+      for (int tile = blockIdx.x; tile < num_tiles && !p.s2d; tile += gridDim.x, ++lt) {
         PL_TRACE(0, lt, 0);
         const int tn = tile % n_tiles, tm = tile / n_tiles;
         const int n0 = tn * BN;
@@ -611,7 +637,32 @@ igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
       uint32_t aph = 0;
       if (hres) WAIT(bar_bres, 0);
       int lt = 0;
-      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++lt) {
+      if (p.s2d) {
+        const uint64_t desc_a = make_smem_desc_pix16();
+        const int ta = p.s2d_ta, kpr = p.s2d_kpr;
+        const uint32_t pitch16 = p.s2d_span_pitch >> 4;
+        for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++lt) {
+          PL_MTRACE(lt, 0);
+          WAIT(bar_tempty + 8 * as, aphase ^ 1);
+          PL_MTRACE(lt, 1);
+          WAIT(bar_afull + 8 * ab, aph);
+          PL_MTRACE(lt, 2);
+          tc_fence_after();
+          const uint32_t d_tmem = tmem_base + (uint32_t)as * p.acc_stride;
+          uint32_t t_lo = a_lo0 + (uint32_t)ab * halo_step, bb = b_lo0;
+          for (int a = 0; a < ta; ++a, t_lo += pitch16)
+            for (int ks = 0; ks < kpr; ++ks, bb += b_step)  // K = 32: pixels (2 ks, 2 ks + 1) of every row
+              if (!skip_mma)
+                umma_i8(d_tmem, desc_a | (uint64_t)(t_lo + 2u * (uint32_t)ks), desc_hi | (uint64_t)bb, idesc,
+                        (uint32_t)((a | ks) != 0));
+          umma_commit(bar_aempty + 8 * ab);
+          umma_commit(bar_tfull + 8 * as);
+          PL_MTRACE(lt, 4);
+          if (++ab == halo_bufs) { ab = 0; aph ^= 1; }
+          if (++as == p.acc_stages) { as = 0; aphase ^= 1; }
+        }
+      }
+      for (int tile = blockIdx.x; tile < num_tiles && !p.s2d; tile += gridDim.x, ++lt) {
         PL_MTRACE(lt, 0);
         WAIT(bar_tempty + 8 * as, aphase ^ 1);
         PL_MTRACE(lt, 1);
@@ -1118,6 +1169,24 @@ __global__ void pack_thin_weight_kernel(const int8_t* __restrict__ w, int8_t* __
   }
 }
 
+// space-to-depth stem filter packing: OHWI [K,R,S,C<=4] -> [K][TA*TB/2][32 bytes]; k-block
+// (a, b/2) holds s2d taps b, b+1 of tap row a; byte (b&1)*16 + (dy*2+dx)*4 + c of a k-block is the
+// weight of original tap (r, s) = (2a + dy - shift, 2b + dx - shift), zero outside the window
+__global__ void pack_s2d_weight_kernel(const int8_t* __restrict__ w, int8_t* __restrict__ out, int K, int R,
+                                       int S, int C, int TA, int TB, int shift) {
+  const int row_bytes = TA * TB * 16;
+  const long long total = (long long)K * row_bytes;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
+       i += (long long)gridDim.x * blockDim.x) {
+    const int k = (int)(i / row_bytes), byte = (int)(i % row_bytes);
+    const int pix = byte >> 4, sub = byte & 15;
+    const int a = pix / TB, b = pix % TB;
+    const int dy = sub >> 3, dx = (sub >> 2) & 1, c = sub & 3;
+    const int r = 2 * a + dy - shift, s_ = 2 * b + dx - shift;
+    out[i] = (r >= 0 && r < R && s_ >= 0 && s_ < S && c < C) ? w[(((long long)k * R + r) * S + s_) * C + c] : (int8_t)0;
+  }
+}
+
 // --------------------------------------------------------------------------
 // host: tensor maps
 // --------------------------------------------------------------------------
@@ -1388,6 +1457,7 @@ int launch_igemm(const CUtensorMap& ta, const CUtensorMap& tb, IgemmParams& p, p
     }
     extra = p.out_bufs * tile + (p.tma_res ? p.res_bufs * tile : 0);
   }
+  if (p.s2d && !hres) return PL_ERR_UNSUPPORTED;
   if (!p.tma_out) bres01 = false;
   p.b_resident = ((p.mode == 2 && p.n_tiles == 1) || hres || bres01) ? 1 : 0;
   if (p.mode == 2 && p.b_resident && env_int("PL_THIN_NO_GROUP", 0) == 0) {
@@ -1477,6 +1547,10 @@ int common_setup(IgemmParams& p, long long M, int Nout, void* y, int ldy, const 
   p.Nout = Nout;
   p.m_tiles = p.halo_m_tiles > 0 ? p.halo_m_tiles : (int)((M + kBM - 1) / kBM);
   p.BN = pick_bn(Nout, p.m_tiles, driver().sm_count);
+  if (p.s2d) {  // the filter must be resident: one N tile, never narrowed to fill the grid
+    p.BN = 16;
+    while (p.BN < Nout && p.BN < 256) p.BN <<= 1;
+  }
   if (e->residual) {
     // fused-residual launches are bandwidth bound and need smem for the residual ring and
     // the staging buffers: thin reductions take a finer K-block so that three mainloop
@@ -1695,6 +1769,97 @@ extern "C" int pl_thin_conv2d_i8_nhwc(const int8_t* x, const int8_t* w_thin, voi
   p.tx_bytes = (uint32_t)(p.BN * p.BK);  // only the filter tile arrives by TMA
   CUtensorMap tb;
   rc = encode_2d(&tb, w_thin, (uint64_t)nkb * 32, (uint64_t)d->K, (uint64_t)nkb * 32, p.BK, p.BN);
+  if (rc) return rc;
+  return launch_igemm(tb, tb, p, stream);
+}
+
+// ---- stride-2 thin stems in space-to-depth form -------------------------------------------------
+extern "C" pl_s2d_geometry pl_s2d_conv_geometry(int N, int H, int W, int C, int R, int S, int stride_h,
+                                                int stride_w, int pad_t, int pad_b, int pad_l, int pad_r,
+                                                int dil_h, int dil_w) {
+  pl_s2d_geometry g{};
+  if (N <= 0 || H <= 0 || W <= 0 || C < 1 || C > 4 || R != S || R < 1 || stride_h != 2 || stride_w != 2 ||
+      dil_h != 1 || dil_w != 1 || (H & 1) || (W & 1) || pad_t != pad_l || pad_t < 0 || pad_b < 0 || pad_r < 0)
+    return g;
+  g.P = pl_conv_out_size(H, R, 1, pad_t, pad_b, 2);
+  g.Q = pl_conv_out_size(W, S, 1, pad_l, pad_r, 2);
+  if (g.P <= 0 || g.Q <= 0 || g.Q > kBM) return g;
+  g.pad_s = (pad_t + 1) / 2;
+  g.shift = 2 * g.pad_s - pad_t;
+  g.TA = (g.shift + R + 1) / 2;
+  g.TB = (g.TA + 1) / 2 * 2;
+  if (g.TA > 4) return g;
+  const int Hs = H / 2, Ws = W / 2;
+  // last s2d row / pixel any window touches
+  const int last_r = (g.P - 1) + g.TA - 1, last_c = (g.Q - 1) + g.TB - 1;  // in padded coordinates
+  g.HP = last_r + 1 > Hs + g.pad_s ? last_r + 1 : Hs + g.pad_s;
+  g.WS = last_c + 1 > Ws + g.pad_s ? last_c + 1 : Ws + g.pad_s;
+  // a tile always fetches 128 + TB - 1 pixels from the start of a row: slack after the last row
+  g.bytes = ((size_t)N * g.HP * g.WS + (size_t)(kBM + g.TB)) * 16;
+  g.supported = 1;
+  return g;
+}
+
+extern "C" size_t pl_s2d_conv_packed_weight_bytes(int K, const pl_s2d_geometry* g) {
+  if (K <= 0 || !g || !g->supported) return 0;
+  return (size_t)K * g->TA * g->TB * 16;
+}
+
+extern "C" int pl_pack_s2d_conv_weight_i8(const int8_t* w_ohwi, int8_t* w_s2d, int K, int R, int S, int C,
+                                          const pl_s2d_geometry* g, pl_stream_t stream) {
+  if (!w_ohwi || !w_s2d || K <= 0 || !g || !g->supported || C < 1 || C > 4) return PL_ERR_ARG;
+  const long long total = (long long)K * g->TA * g->TB * 16;
+  const int blocks = (int)((total + 255) / 256 > 1024 ? 1024 : (total + 255) / 256);
+  pack_s2d_weight_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(w_ohwi, w_s2d, K, R, S, C, g->TA, g->TB, g->shift);
+  ++g_launches;
+  return launch_status();
+}
+
+extern "C" int pl_s2d_conv2d_i8(const int8_t* x_s2d, const int8_t* w_s2d, void* y, const pl_conv_desc* d,
+                                const pl_epilogue* e, pl_stream_t stream) {
+  if (!x_s2d || !w_s2d || !y || !d) return PL_ERR_ARG;
+  int rc = check_epi(e);
+  if (rc) return rc;
+  if (!driver().ok) return PL_ERR_DRIVER;
+  if (driver().cc_major != 10) return PL_ERR_DEVICE;
+  if (d->groups != 1 || e->residual) return PL_ERR_UNSUPPORTED;
+  if (d->K <= 0 || d->ldy < d->K) return PL_ERR_ARG;
+  const pl_s2d_geometry g = pl_s2d_conv_geometry(d->N, d->H, d->W, d->C, d->R, d->S, d->stride_h, d->stride_w,
+                                                 d->pad_t, d->pad_b, d->pad_l, d->pad_r, d->dil_h, d->dil_w);
+  if (!g.supported) return PL_ERR_UNSUPPORTED;
+  if ((reinterpret_cast<uintptr_t>(x_s2d) & 15) || (reinterpret_cast<uintptr_t>(w_s2d) & 15)) return PL_ERR_ALIGN;
+  if ((long long)d->N * g.P * g.Q >= (1ll << 31)) return PL_ERR_UNSUPPORTED;
+  IgemmParams p{};
+  p.mode = 3;
+  p.s2d = 1;
+  p.BK = 32;
+  const int nkb = g.TA * g.TB / 2;
+  p.halo_m_tiles = d->N * g.P;  // one output row per tile
+  rc = common_setup(p, (long long)d->N * g.P * g.Q, d->K, y, d->ldy, e, nkb * 32, 1);
+  if (rc) return rc;
+  if (p.n_tiles != 1) return PL_ERR_UNSUPPORTED;  // the filter must be resident (K <= 256 outputs)
+  p.Q = g.Q;
+  p.P = g.P;
+  p.PQ = g.P * g.Q;
+  p.S = 1;
+  p.R = 1;
+  p.hk = 1;
+  p.WP = kBM;
+  p.bands = g.P;
+  p.dBands = make_fastdiv((uint32_t)g.P);
+  p.dWP = make_fastdiv((uint32_t)kBM);
+  p.s2d_ta = g.TA;
+  p.s2d_kpr = g.TB / 2;
+  p.s2d_span_bytes = (uint32_t)((kBM + g.TB - 1) * 16);
+  p.s2d_span_pitch = (p.s2d_span_bytes + 127u) / 128u * 128u;
+  p.s2d_row_bytes = (long long)g.WS * 16;
+  p.s2d_img_bytes = (long long)g.HP * g.WS * 16;
+  p.xs2d = x_s2d;
+  p.a_halo_tx = (uint32_t)g.TA * p.s2d_span_bytes;
+  p.a_halo_bytes = ((uint32_t)g.TA * p.s2d_span_pitch + 1023u) / 1024u * 1024u;
+  p.tx_bytes = (uint32_t)(p.BN * p.BK);
+  CUtensorMap tb;
+  rc = encode_2d(&tb, w_s2d, (uint64_t)nkb * 32, (uint64_t)d->K, (uint64_t)nkb * 32, p.BK, p.BN);
   if (rc) return rc;
   return launch_igemm(tb, tb, p, stream);
 }

@@ -196,9 +196,22 @@ class DeviceNet:
         self._weights_to_device()
 
     # -- one-off (PrepareForRun) ------------------------------------------------
+    def _s2d_geometry(self, op, n):
+        H, W, _ = self.prog.shapes[op.src]
+        return pl.s2d_geometry(n, H, W, op.C, op.k, op.k, (op.stride, op.stride), (op.pad,) * 4)
+
     def _weights_to_device(self):
+        self.s2d_src = {}  # tensor name -> stem conv that reads it in space-to-depth form
+        quant_dsts = {op.dst for op in self.prog.ops if op.kind == "quant_in"}
         for op in self.prog.ops:
-            if op.kind == "conv" and op.C <= 4 and pl.thin_conv_supported(op.k, op.k, op.C) and not _FORCE_IM2COL:
+            readers = [o for o in self.prog.ops if op.get("src") in (o.get("src"), o.get("src2"), o.get("res"))]
+            if (op.kind == "conv" and op.C <= 4 and op.src in quant_dsts and len(readers) == 1 and not _FORCE_IM2COL
+                    and not os.environ.get("PL_NO_S2D") and self._s2d_geometry(op, self.batch).supported):
+                # stride-2 thin stem: space-to-depth input, spans bulk-copied and read in place by the MMA
+                op["_wp"] = pl.pack_s2d_conv_weight(torch.from_numpy(op.w).to(self.dev), self._s2d_geometry(op, self.batch))
+                op["_s2d"] = True
+                self.s2d_src[op.src] = op
+            elif op.kind == "conv" and op.C <= 4 and pl.thin_conv_supported(op.k, op.k, op.C) and not _FORCE_IM2COL:
                 # thin first layer, direct: window words gathered on chip by the conv kernel
                 op["_wp"] = pl.pack_thin_conv_weight(torch.from_numpy(op.w).to(self.dev))
                 op["_thin"] = True
@@ -246,8 +259,13 @@ class DeviceNet:
             if op.kind == "quant_in":
                 op.out_scale = float(x_nchw.abs().max().item()) / 127.0
                 C_in = x_nchw.shape[1]
-                vals[op.dst] = pl.quantize_nchw_to_nhwc(x_nchw.contiguous(), op.out_scale,
-                                                        4 if C_in <= 4 else rup(C_in, 16))
+                if op.dst in self.s2d_src:
+                    vals[op.dst] = pl.quantize_nchw_to_s2d(x_nchw.contiguous(), op.out_scale,
+                                                           self._s2d_geometry(self.s2d_src[op.dst], n))
+                    vals[op.dst]._pl_n = n
+                else:
+                    vals[op.dst] = pl.quantize_nchw_to_nhwc(x_nchw.contiguous(), op.out_scale,
+                                                            4 if C_in <= 4 else rup(C_in, 16))
                 scales[op.dst] = op.out_scale
             elif op.kind in ("conv", "dwconv"):
                 op.in_scale = scales[op.src]
@@ -294,6 +312,11 @@ class DeviceNet:
             return pl.dwconv2d(x, op._wp, sf, bf, op.k, op.k, (op.stride, op.stride), (op.pad,) * 4,
                                (1, 1), _ACT[op.act], argf, out, y=y, Cc=C)
         K = op.K
+        if op.get("_s2d"):
+            H, W, _ = self.prog.shapes[op.src]
+            return pl.s2d_conv2d(x, op._wp, x._pl_n, H, W, C, K, op.k, op.k, sf, bf, (op.stride, op.stride),
+                                 (op.pad,) * 4, _ACT[op.act], argf, out, y=y,
+                                 ldy=(rup(K, 16) if out == pl.OUT_INT8 else K))
         if C <= 4 and op.get("_thin"):
             return pl.thin_conv2d(x, op._wp, K, op.k, op.k, C, sf, bf, (op.stride, op.stride), (op.pad,) * 4,
                                   _ACT[op.act], argf, out, y=y, ldy=(rup(K, 16) if out == pl.OUT_INT8 else K))
@@ -332,14 +355,22 @@ class DeviceNet:
         """Pre-computes folded scales and output buffers; builds the launch list."""
         assert self.calibrated, "calibrate() or load scales first"
         self.layers = []
+        self.s2d_bufs = {}
         for op in self.prog.ops:
-            if op.kind == "quant_in":
+            if op.kind == "quant_in" and op.dst in self.s2d_src:
+                g = self._s2d_geometry(self.s2d_src[op.dst], self.batch)
+                y = pl.s2d_input_buffer(g, self.dev)  # zero borders, written once here
+                y._pl_n = self.batch
+                self.s2d_bufs[op.dst] = (y, g)
+                self.layers.append((op, lambda op=op, y=y, g=g: pl.quantize_nchw_to_s2d(
+                    self.input, op.out_scale, g, y=y)))
+            elif op.kind == "quant_in":
                 y = self._buf(op.dst)
                 self.layers.append((op, lambda op=op, y=y: pl.quantize_nchw_to_nhwc(
                     self.input, op.out_scale, y.shape[-1], y=y)))
             elif op.kind in ("conv", "dwconv"):
                 sf, bf, argf = self._fold(op, op.K, op.out_fp32)
-                x = self._buf(op.src)
+                x = self.s2d_bufs[op.src][0] if op.src in self.s2d_bufs else self._buf(op.src)
                 y = self._buf(op.dst, torch.float32 if op.out_fp32 else torch.int8)
                 out = pl.OUT_FP32 if op.out_fp32 else pl.OUT_INT8
                 res = self._buf(op.res) if op.get("res") else None
@@ -364,6 +395,14 @@ class DeviceNet:
                 self.layers.append((op, lambda op=op, A=A, y=y, sf=sf, bf=bf:
                                     pl.gemm(A, op._wp, sf, bf, out=pl.OUT_FP32, y=y, K=op.K)))
         return self
+
+    def s2d_as_nhwc(self, name):
+        """Host copy of a space-to-depth input buffer, unfolded to int8 NHWC [N,H,W,4] (for checks)."""
+        y, g = self.s2d_bufs[name]
+        H, W, _ = self.prog.shapes[name]
+        img = y[: self.batch * g.HP * g.WS * 16].view(self.batch, g.HP, g.WS, 2, 2, 4).cpu().numpy()
+        img = img[:, g.pad_s:g.pad_s + H // 2, g.pad_s:g.pad_s + W // 2]
+        return img.transpose(0, 1, 3, 2, 4, 5).reshape(self.batch, H, W, 4)
 
     def run(self):
         for _, fn in self.layers:

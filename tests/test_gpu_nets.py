@@ -34,6 +34,9 @@ def _check(builder, batch, res, graph):
         if dtype == torch.int8 and name in vals:
             C = prog.shapes[name][2]
             assert np.array_equal(buf.cpu().numpy()[..., :C], vals[name]), f"tensor {name} differs"
+    for name in net.s2d_bufs:  # stem input kept in space-to-depth form
+        C = prog.shapes[name][2]
+        assert np.array_equal(net.s2d_as_nhwc(name)[..., :C], vals[name]), f"tensor {name} (s2d) differs"
     np.testing.assert_allclose(got, want, rtol=1e-5, atol=0)
     assert np.array_equal(got, want)
     assert np.isfinite(got).all() and np.std(got) > 0

@@ -545,3 +545,68 @@ def test_thin_direct_rejects_unsupported(pl):
     assert not pl.thin_conv_supported(3, 3, 8)
     assert not pl.thin_conv_supported(9, 9, 3)
     assert not pl.thin_conv_supported(3, 3, 3, (2, 2))
+
+
+# ---- stride-2 thin stems in space-to-depth form (bulk-copied spans, overlapping descriptors) ----
+S2D_CASES = [
+    # N, H, W, C, K, R, stride, pads(t,b,l,r)
+    (2, 32, 32, 3, 64, 7, 2, (3, 3, 3, 3)),      # ResNet stem (scaled down)
+    (3, 30, 34, 3, 32, 3, 2, (1, 1, 1, 1)),      # MobileNet stem
+    (1, 64, 224, 3, 64, 7, 2, (3, 3, 3, 3)),     # full-width rows (Q = 112)
+    (2, 20, 256, 4, 16, 3, 2, (1, 1, 1, 1)),     # Q = 128: every accumulator row is an output
+    (1, 18, 22, 1, 24, 5, 2, (2, 2, 2, 2)),      # even pad: shift 0, 3 tap rows padded to 4 taps per row
+    (4, 12, 16, 2, 130, 3, 2, (1, 0, 1, 0)),     # no bottom / right pad, K not a multiple of 16
+    (1, 16, 16, 3, 8, 3, 2, (0, 0, 0, 0)),       # no padding at all
+]
+
+
+@pytest.mark.parametrize("case", S2D_CASES)
+@pytest.mark.parametrize("mode", ["int8_relu", "int8_none", "fp32", "int32"])
+def test_s2d_stem_conv(pl, case, mode):
+    N, H, W, Cc, K, R, st, pads = case
+    rng = np.random.default_rng(sum(case[:7]) + len(mode))
+    g = pl.s2d_geometry(N, H, W, Cc, R, R, (st, st), pads)
+    assert g.supported
+    xf = rng.uniform(-1, 1, (N, Cc, H, W)).astype(np.float32)
+    in_scale = 1 / 127
+    x = orc.nchw_to_nhwc(orc.quantize(xf, in_scale))  # what the s2d quantiser must hold, in NHWC
+    w = rng.integers(-127, 128, (K, R, R, Cc), dtype=np.int8)
+    ws = ((1 + np.arange(K) % 7) / (7 * 127)).astype(np.float32)
+    bias = rng.uniform(-1, 1, K).astype(np.float32)
+    out = {"int8_relu": orc.OUT_INT8, "int8_none": orc.OUT_INT8, "fp32": orc.OUT_FP32, "int32": orc.OUT_INT32}[mode]
+    act = orc.ACT_RELU if mode == "int8_relu" else orc.ACT_NONE
+    sf, bf, _ = orc.fold_scales(ws, K, in_scale, Cc * R * R / 127 / 4, orc.OUT_INT8 if out == orc.OUT_INT8 else orc.OUT_FP32, bias)
+    want = orc.conv2d(x, w, sf, bf, (st, st), pads, act=act, out=out)
+    xs = pl.quantize_nchw_to_s2d(dev(xf), in_scale, g)
+    wp = pl.pack_s2d_conv_weight(dev(w), g)
+    got = host(pl.s2d_conv2d(xs, wp, N, H, W, Cc, K, R, R, dev(sf), dev(bf), (st, st), pads, act=act, out=out))
+    if out == orc.OUT_FP32:
+        np.testing.assert_allclose(got, want, rtol=1e-5, atol=1e-6)
+    else:
+        assert np.array_equal(got, want)
+
+
+def test_s2d_quantiser_layout(pl):
+    """The 16-byte pixel is (dy, dx, c) of a 2x2 block; borders stay zero."""
+    rng = np.random.default_rng(11)
+    N, Cc, H, W = 2, 3, 8, 12
+    g = pl.s2d_geometry(N, H, W, Cc, 7, 7, (2, 2), (3, 3, 3, 3))
+    xf = rng.uniform(-1, 1, (N, Cc, H, W)).astype(np.float32)
+    q = orc.quantize(xf, 1 / 127)
+    buf = host(pl.quantize_nchw_to_s2d(dev(xf), 1 / 127, g))
+    img = buf[: N * g.HP * g.WS * 16].reshape(N, g.HP, g.WS, 2, 2, 4)
+    want = np.zeros_like(img)
+    for dy in range(2):
+        for dx in range(2):
+            want[:, g.pad_s:g.pad_s + H // 2, g.pad_s:g.pad_s + W // 2, dy, dx, :Cc] = \
+                q[:, :, dy::2, dx::2].transpose(0, 2, 3, 1)
+    assert np.array_equal(img, want)
+    assert not buf[N * g.HP * g.WS * 16:].any()
+
+
+def test_s2d_geometry_rejects(pl):
+    assert not pl.s2d_geometry(1, 32, 32, 3, 7, 7, (1, 1), (3, 3, 3, 3)).supported      # stride 1
+    assert not pl.s2d_geometry(1, 31, 32, 3, 7, 7, (2, 2), (3, 3, 3, 3)).supported      # odd height
+    assert not pl.s2d_geometry(1, 32, 32, 8, 3, 3, (2, 2), (1, 1, 1, 1)).supported      # not thin
+    assert not pl.s2d_geometry(1, 32, 600, 3, 3, 3, (2, 2), (1, 1, 1, 1)).supported     # Q > 128
+    assert not pl.s2d_geometry(1, 32, 32, 3, 9, 9, (2, 2), (4, 4, 4, 4)).supported      # 5 taps per axis
