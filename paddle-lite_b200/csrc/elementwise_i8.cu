@@ -229,31 +229,52 @@ quant_nchw_to_word_kernel(const float* __restrict__ x, uint4* __restrict__ y, in
   }
 }
 
-// fp32 NCHW -> int8 space-to-depth pixels (pl_int8.h: pl_s2d_geometry): thread = one 16-byte pixel
-// = 2x2 original pixels x 4 channels; float2 loads (coalesced 8 bytes per lane and row), one
-// 16-byte store.  Only the interior is written: the borders stay zero from the caller's memset.
+// fp32 NCHW -> int8 space-to-depth pixels (pl_int8.h: pl_s2d_geometry): thread = TWO adjacent
+// 16-byte pixels (4 original columns x 2 rows x 4 channels): float4 loads (one per channel and row),
+// one 32-byte store.  W % 4 != 0 leaves a last single pixel per row to the float2 path.  Only the
+// interior is written: the borders stay zero from the caller's memset.
 __global__ void __launch_bounds__(256)
 quant_nchw_to_s2d_kernel(const float* __restrict__ x, uint4* __restrict__ y, int C, int H, int W, int HP, int WS,
                          int pad_s, float scale, float inv, int round_mode) {
-  const int n = blockIdx.z, hs = blockIdx.y;
-  const int ws = blockIdx.x * blockDim.x + threadIdx.x;
-  const int Ws = W >> 1;
-  if (ws >= Ws) return;
+  const int n = blockIdx.y;
+  const int Ws = W >> 1, Hs = H >> 1, Wp = (Ws + 1) >> 1;  // pixel pairs per row
+  const int item = blockIdx.x * blockDim.x + threadIdx.x;
+  if (item >= Hs * Wp) return;
+  const int hs = item / Wp, wp = item - hs * Wp;
+  const int ws = 2 * wp;
+  const bool two = ws + 1 < Ws;
   const float* xs = x + (long long)n * C * H * W + (long long)(2 * hs) * W + 2 * ws;
-  int q[2][2][4];
+  int q[2][4][4];  // [dy][column 0..3][c]
 #pragma unroll
   for (int c = 0; c < 4; ++c) {
 #pragma unroll
     for (int dy = 0; dy < 2; ++dy) {
-      float2 f = make_float2(0.f, 0.f);
-      if (c < C) f = __ldg(reinterpret_cast<const float2*>(xs + (long long)c * H * W + dy * W));
+      float4 f = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (c < C) {
+        const float* p = xs + (long long)c * H * W + dy * W;
+        if (two && (W & 3) == 0) {
+          f = __ldg(reinterpret_cast<const float4*>(p));
+        } else {
+          const float2 a = __ldg(reinterpret_cast<const float2*>(p));
+          f.x = a.x; f.y = a.y;
+          if (two) { const float2 b2 = __ldg(reinterpret_cast<const float2*>(p + 2)); f.z = b2.x; f.w = b2.y; }
+        }
+      }
       q[dy][0][c] = c < C ? round_sat_i8(quant_pre(f.x, scale, inv, round_mode), round_mode) : 0;
       q[dy][1][c] = c < C ? round_sat_i8(quant_pre(f.y, scale, inv, round_mode), round_mode) : 0;
+      q[dy][2][c] = c < C ? round_sat_i8(quant_pre(f.z, scale, inv, round_mode), round_mode) : 0;
+      q[dy][3][c] = c < C ? round_sat_i8(quant_pre(f.w, scale, inv, round_mode), round_mode) : 0;
     }
   }
-  y[((long long)n * HP + hs + pad_s) * WS + ws + pad_s] =
-      make_uint4(pack4_i8(q[0][0][0], q[0][0][1], q[0][0][2], q[0][0][3]), pack4_i8(q[0][1][0], q[0][1][1], q[0][1][2], q[0][1][3]),
-                 pack4_i8(q[1][0][0], q[1][0][1], q[1][0][2], q[1][0][3]), pack4_i8(q[1][1][0], q[1][1][1], q[1][1][2], q[1][1][3]));
+  uint4* out = y + ((long long)n * HP + hs + pad_s) * WS + ws + pad_s;
+#pragma unroll
+  for (int h = 0; h < 2; ++h) {
+    if (h == 1 && !two) break;
+    out[h] = make_uint4(pack4_i8(q[0][2 * h][0], q[0][2 * h][1], q[0][2 * h][2], q[0][2 * h][3]),
+                        pack4_i8(q[0][2 * h + 1][0], q[0][2 * h + 1][1], q[0][2 * h + 1][2], q[0][2 * h + 1][3]),
+                        pack4_i8(q[1][2 * h][0], q[1][2 * h][1], q[1][2 * h][2], q[1][2 * h][3]),
+                        pack4_i8(q[1][2 * h + 1][0], q[1][2 * h + 1][1], q[1][2 * h + 1][2], q[1][2 * h + 1][3]));
+  }
 }
 
 // ------------------------------------------------------------------ pooling
@@ -469,6 +490,7 @@ static void launch_pool4(int V, int KF, unsigned grid, cudaStream_t st, const ui
   if (V == 4 && KF == 3) launch_pdl(pool4_kernel<POOL, 4, 3>, dim3(grid), dim3(256), 0, st, PL_POOL_ARGS);
   else if (V == 4) launch_pdl(pool4_kernel<POOL, 4, 0>, dim3(grid), dim3(256), 0, st, PL_POOL_ARGS);
   else if (KF == 3) launch_pdl(pool4_kernel<POOL, 1, 3>, dim3(grid), dim3(256), 0, st, PL_POOL_ARGS);
+  else if (KF == 7) launch_pdl(pool4_kernel<POOL, 1, 7>, dim3(grid), dim3(256), 0, st, PL_POOL_ARGS);
   else launch_pdl(pool4_kernel<POOL, 1, 0>, dim3(grid), dim3(256), 0, st, PL_POOL_ARGS);
 #undef PL_POOL_ARGS
 }
@@ -629,10 +651,11 @@ extern "C" int pl_quantize_nchw_f32_to_s2d_i8(const float* x, int8_t* y_s2d, int
                                               const pl_s2d_geometry* g, float scale, int round_mode,
                                               pl_stream_t stream) {
   if (!x || !y_s2d || !g || !g->supported || N <= 0 || C <= 0 || C > 4 || !(scale > 0.f)) return PL_ERR_ARG;
-  if ((H & 1) || (W & 1) || N > 65535 || H / 2 > 65535) return PL_ERR_UNSUPPORTED;
-  if (!al16(y_s2d) || (reinterpret_cast<uintptr_t>(x) & 7)) return PL_ERR_ALIGN;
-  dim3 grid((unsigned)((W / 2 + 127) / 128), (unsigned)(H / 2), (unsigned)N);
-  quant_nchw_to_s2d_kernel<<<grid, 128, 0, (cudaStream_t)stream>>>(x, reinterpret_cast<uint4*>(y_s2d), C, H, W, g->HP,
+  if ((H & 1) || (W & 1) || N > 65535) return PL_ERR_UNSUPPORTED;
+  if (!al16(y_s2d) || (reinterpret_cast<uintptr_t>(x) & 15)) return PL_ERR_ALIGN;
+  const long long items = (long long)(H / 2) * ((W / 2 + 1) / 2);
+  dim3 grid((unsigned)((items + 255) / 256), (unsigned)N);
+  quant_nchw_to_s2d_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(x, reinterpret_cast<uint4*>(y_s2d), C, H, W, g->HP,
                                                                   g->WS, g->pad_s, scale, 1.f / scale, round_mode);
   ++g_launches;
   return launch_status();
@@ -657,7 +680,9 @@ extern "C" int pl_pool2d_i8_nhwc(const int8_t* x, int ldx, void* y, int ldy, int
                    (long long)N * P * Q * ((Cw + 3) / 4) >= 148ll * 2048 * 2)
                       ? 4
                       : 1;
-    const int KF = (kh == 3 && kw == 3) ? 3 : 0;
+    // 7x7 (the global pools of ResNet / MobileNet at 224): word-wide, all 49 taps in flight per thread
+    // (the runtime loop serialised ~49 memory latencies: 17 us for 26 MB)
+    const int KF = (kh == 3 && kw == 3) ? 3 : ((kh == 7 && kw == 7 && V == 1) ? 7 : 0);
     const int groups = (Cw + V - 1) / V;
     const long long witems = (long long)N * P * Q * groups;
     // whole-word stores need the pad channels of the last word to be addressable

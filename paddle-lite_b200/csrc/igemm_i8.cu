@@ -40,6 +40,7 @@ static constexpr int kMaxAccStages = 4;   // TMEM accumulators in flight (512 co
 static constexpr int kMaxTmaStages = 12;  // TMA-fed modes
 static constexpr int kMaxStages = 28;  // thin mode: 4 KB A stages, the gather runs up to 4 tiles ahead
 static constexpr int kMaxResBufs = 6;   // depth of the TMA residual ring
+static constexpr int kMaxOutBufs = 4;   // output staging tiles (small tiles: the TMA store's read-out latency spans several tile periods)
 static constexpr int kMaxHaloBufs = 4;  // mode 3: input halo tiles in flight (p.halo_bufs of them)
 
 enum { EPI_GENERIC = 0, EPI_I8_RELU = 1, EPI_I8_SIGNED = 2, EPI_I8_RELU_RES = 3 };
@@ -338,7 +339,7 @@ igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
   constexpr int kBarRFull = kBarTEmpty + kMaxAccStages, kBarREmpty = kBarRFull + kMaxResBufs;
   constexpr int kBarAFull = kBarREmpty + kMaxResBufs, kBarAEmpty = kBarAFull + kMaxHaloBufs;
   constexpr int kBarBRes = kBarAEmpty + kMaxHaloBufs, kBarStaged = kBarBRes + 1, kBarOFree = kBarStaged + kMaxResBufs;
-  __shared__ __align__(8) uint64_t bars[kBarOFree + 2];
+  __shared__ __align__(8) uint64_t bars[kBarOFree + kMaxOutBufs];
   __shared__ uint32_t tmem_base_slot;
 
   const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
@@ -403,7 +404,7 @@ igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
       mbar_init(bar_tempty + 8 * s, EW);  // one arrival per epilogue warp
     }
     for (int s = 0; s < kMaxResBufs; ++s) mbar_init(bar_staged + 8 * s, EW);
-    for (int s = 0; s < 2; ++s) mbar_init(bar_ofree + 8 * s, 1);
+    for (int s = 0; s < kMaxOutBufs; ++s) mbar_init(bar_ofree + 8 * s, 1);
     for (int s = 0; s < kMaxHaloBufs; ++s) {
       mbar_init(bar_afull + 8 * s, 1);
       mbar_init(bar_aempty + 8 * s, 1);
@@ -1450,8 +1451,11 @@ int launch_igemm(const CUtensorMap& ta, const CUtensorMap& tb, IgemmParams& p, p
       }
     } else {
       p.out_bufs = 1;
-      if (left >= tile && env_int("PL_IGEMM_OUT_BUFS", 2) >= 2) {
-        p.out_bufs = 2;
+      // small tiles turn over faster than a TMA store is read out: up to 4 staging buffers
+      int want_out = env_int("PL_IGEMM_OUT_BUFS", tile <= 16 * 1024 ? 4 : 2);
+      if (want_out > kMaxOutBufs) want_out = kMaxOutBufs;
+      while (p.out_bufs < want_out && left >= tile) {
+        ++p.out_bufs;
         left -= tile;
       }
     }

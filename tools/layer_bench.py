@@ -18,6 +18,8 @@ LAYERS = {
     # name: (H, W, C, K, k, stride, pad, act, residual)
     "stem7x7": (224, 224, 3, 64, 7, 2, 3, "relu", False),
     "stem3x3": (224, 224, 3, 32, 3, 2, 1, "relu", False),
+    "stem7x7_s2d": (224, 224, 3, 64, 7, 2, 3, "relu", "s2d"),
+    "stem3x3_s2d": (224, 224, 3, 32, 3, 2, 1, "relu", "s2d"),
     "r2_1x1_64_256": (56, 56, 64, 256, 1, 1, 0, "none", False),
     "r2_1x1_64_256_res": (56, 56, 64, 256, 1, 1, 0, "relu", True),
     "r2_1x1_64_64": (56, 56, 64, 64, 1, 1, 0, "relu", False),
@@ -56,8 +58,14 @@ def bench(name, batch, iters, nsets):
     sc = torch.full((K,), 1e-3, device=dev)
     bs = torch.zeros((K,), device=dev)
     dw = res == "dw"
-    thin = (not dw) and C <= 4
-    if dw:
+    s2d = res == "s2d"
+    thin = (not dw) and (not s2d) and C <= 4
+    if s2d:
+        geo = pl.s2d_geometry(batch, H, W, C, k, k, (st, st), (pad,) * 4)
+        xf = torch.rand((batch, C, H, W), device=dev, generator=g) * 2 - 1
+        xs = [pl.quantize_nchw_to_s2d(xf, 1 / 127, geo) for _ in range(nsets)]
+        w = pl.pack_s2d_conv_weight(torch.randint(-127, 128, (K, k, k, C), dtype=torch.int8, device=dev, generator=g), geo)
+    elif dw:
         w = torch.randint(-127, 128, (K, k, k), dtype=torch.int8, device=dev, generator=g)
     elif thin:
         w = pl.pack_thin_conv_weight(torch.randint(-127, 128, (K, k, k, C), dtype=torch.int8, device=dev, generator=g))
@@ -67,7 +75,9 @@ def bench(name, batch, iters, nsets):
 
     def run(i):
         j = i % nsets
-        if dw:
+        if s2d:
+            pl.s2d_conv2d(xs[j], w, batch, H, W, C, K, k, k, sc, bs, (st, st), (pad,) * 4, act=ACT[act], y=ys[j])
+        elif dw:
             pl.dwconv2d(xs[j], w, sc, bs, k, k, (st, st), (pad,) * 4, act=ACT[act], y=ys[j], Cc=C)
         elif thin:
             pl.thin_conv2d(xs[j], w, K, k, k, C, sc, bs, (st, st), (pad,) * 4, act=ACT[act], y=ys[j])
