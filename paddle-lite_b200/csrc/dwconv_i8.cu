@@ -10,6 +10,8 @@
 // Fast path (3x3, stride 1 or 2, dilation 1): see dw3x3s1_kernel / dw3x3s2_kernel.
 // Generic path (any R,S,stride,dilation): one dp4a per MAC against a byte-masked
 // weight word.
+#include <cstdlib>
+
 #include "common.cuh"
 
 namespace pl {
@@ -296,6 +298,101 @@ __global__ void __launch_bounds__(256, RB <= 2 ? 4 : 2) dw3x3s1_kernel(const DwP
   }
 }
 
+// ---- stride 1, vertical streaming: T = 4 output columns, a band of BR output rows per thread ----
+// The block-of-rows kernel above re-does the per-item work (item decode, filter unpack, column
+// setup, scale / bias loads: ~120 instructions) for every 64 output bytes and is instruction-issue
+// bound (ncu: 17 thread-instructions per output byte, 63% issue utilisation at 2.3 TB/s).  Here a
+// thread walks down its 4-column strip: every input row is loaded and byte-transposed ONCE, feeds
+// the three output rows in flight (accumulator slots rotate through a 3x unrolled loop), the next
+// row's loads are issued before the current row's math, and each finished output row leaves through
+// the packed epilogue.  ~10 instructions per output byte.
+template <bool FAST>
+__global__ void __launch_bounds__(256, 2) dw3x3s1v_kernel(const DwParams p, const int BR) {
+  pdl_launch_dependents();
+  const uint32_t idx = blockIdx.x * 256u + threadIdx.x;
+  if (idx >= (uint32_t)p.items) return;
+  const DwItem it = dw_item(p, idx, BR, 4);
+  const int c0 = it.c0;
+  const int ih0 = it.p0 - p.pt;
+  const uint32_t* img = reinterpret_cast<const uint32_t*>(p.x + c0) + (uint32_t)(it.n * p.H) * (uint32_t)p.rowpitch_w;
+  const uint32_t* cp[6];
+  uint32_t cm[6];
+  dw_columns<6>(p, img, it.q0 - p.pl_, cp, cm);
+  uint32_t wa[3][4], wb[3][4];
+  dw_load_filter(p, c0, wa);
+#pragma unroll
+  for (int r = 0; r < 3; ++r)
+#pragma unroll
+    for (int j = 0; j < 4; ++j) wb[r][j] = wa[r][j] << 8;
+  float4 sc, bs;
+  dw_load_scale_bias(p, c0, sc, bs);
+  pdl_wait();  // filter / scales are constant; the input comes from the previous kernel
+  int acc[3][4][4];
+#pragma unroll
+  for (int o = 0; o < 3; ++o)
+#pragma unroll
+    for (int q = 0; q < 4; ++q)
+#pragma unroll
+      for (int j = 0; j < 4; ++j) acc[o][q][j] = kDwMagic;
+  const int rows = BR + 2;
+  auto load_row = [&](int i, uint32_t (&d)[6]) {
+    const int ih = ih0 + i;
+    const int ihc = min(max(ih, 0), p.H - 1);
+    const uint32_t rm = (ih == ihc) ? 0xffffffffu : 0u;
+    const uint32_t roff = (uint32_t)(ihc * p.rowpitch_w);
+#pragma unroll
+    for (int k = 0; k < 6; ++k) d[k] = __ldg(cp[k] + roff) & cm[k] & rm;
+  };
+  uint32_t xw[6];
+  load_row(0, xw);
+  const uint32_t pix0 = (uint32_t)((it.n * p.P + it.p0) * p.Q + it.q0);
+  for (int i = 0; i < rows; i += 3) {
+#pragma unroll
+    for (int u = 0; u < 3; ++u) {
+      const int ii = i + u;
+      if (ii >= rows) break;
+      uint32_t nx[6];
+      if (ii + 1 < rows) load_row(ii + 1, nx);
+      uint32_t ta[4], tb[4];
+      dw_transpose(xw[0], xw[1], xw[2], xw[3], ta);  // columns 0..3 -> outputs 0, 1
+      dw_transpose(xw[2], xw[3], xw[4], xw[5], tb);  // columns 2..5 -> outputs 2, 3
+#pragma unroll
+      for (int r = 0; r < 3; ++r) {
+        const int o = ii - r;               // output row (relative to the band) this input row feeds with filter row r
+        constexpr int kSlotBase = 3;
+        const int slot = (u - r + kSlotBase) % 3;  // compile-time: u and r are unrolled
+        if (o >= 0 && o < BR) {
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            acc[slot][0][j] = __dp4a((int)ta[j], (int)wa[r][j], acc[slot][0][j]);
+            acc[slot][1][j] = __dp4a((int)ta[j], (int)wb[r][j], acc[slot][1][j]);
+            acc[slot][2][j] = __dp4a((int)tb[j], (int)wa[r][j], acc[slot][2][j]);
+            acc[slot][3][j] = __dp4a((int)tb[j], (int)wb[r][j], acc[slot][3][j]);
+          }
+        }
+      }
+      if (ii >= 2) {  // output row ii - 2 has all three filter rows
+        const int o = ii - 2;
+        constexpr int dummy = 0;
+        (void)dummy;
+        const int slot = (u + 1) % 3;
+        if (it.p0 + o < p.P) {
+          const uint32_t pix = pix0 + (uint32_t)(o * p.Q);
+#pragma unroll
+          for (int q = 0; q < 4; ++q)
+            if (it.q0 + q < p.Q) dw_finish4<FAST>(p, acc[slot][q], sc, bs, p.hi_bits, pix + q, c0);
+        }
+#pragma unroll
+        for (int q = 0; q < 4; ++q)
+#pragma unroll
+          for (int j = 0; j < 4; ++j) acc[slot][q][j] = kDwMagic;
+      }
+#pragma unroll
+      for (int k = 0; k < 6; ++k) xw[k] = nx[k];
+    }
+  }
+}
+
 // ---- stride 2: T = 2 output columns, RB output rows, window (2*RB+1) x 5 words ----
 template <int RB, bool FAST>
 __global__ void __launch_bounds__(256, 4) dw3x3s2_kernel(const DwParams p) {
@@ -467,6 +564,18 @@ extern "C" int pl_dwconv2d_i8_nhwc(const int8_t* x, const int8_t* w_crs, void* y
     auto items_for = [&](int rb) { return (long long)d->N * ((P + rb - 1) / rb) * p.strips * p.CG; };
     int RB = 2;
     if (s1 && items_for(4) >= (long long)sms * 2048 * 2) RB = 4;
+    // stride 1: vertical streaming with the tallest band that still leaves ~2 waves of threads
+    // (measured on B200: 1.7 TB/s against 2.5 TB/s for the block-of-rows kernel -- one prefetched row per
+    // thread leaves only ~12 KB of loads in flight per SM -- so it stays an experiment: PL_DW_STREAM=1)
+    static const bool dw_stream = [] { const char* v = getenv("PL_DW_STREAM"); return v && v[0] == '1'; }();
+    bool stream_s1 = s1 && dw_stream;
+    if (stream_s1) {
+      RB = 4;
+      for (int cand : {56, 28, 14, 8}) {
+        if (cand <= P && items_for(cand) >= (long long)sms * 512 * 2) { RB = cand; break; }
+      }
+      if (P < 4) stream_s1 = false, RB = 2;
+    }
     p.bands = (P + RB - 1) / RB;
     p.items = items_for(RB);
     p.dCG = make_fastdiv((uint32_t)p.CG);
@@ -475,7 +584,10 @@ extern "C" int pl_dwconv2d_i8_nhwc(const int8_t* x, const int8_t* w_crs, void* y
     p.ldxw = d->ldx / 4;
     p.rowpitch_w = d->W * p.ldxw;
     const unsigned grid = (unsigned)((p.items + 255) / 256);
-    if (s1) {
+    if (stream_s1) {
+      if (fe) launch_pdl(dw3x3s1v_kernel<true>, dim3(grid), dim3(256), 0, st, p, RB);
+      else launch_pdl(dw3x3s1v_kernel<false>, dim3(grid), dim3(256), 0, st, p, RB);
+    } else if (s1) {
       if (RB == 4) {
         if (fe) launch_pdl(dw3x3s1_kernel<4, true>, dim3(grid), dim3(256), 0, st, p);
         else launch_pdl(dw3x3s1_kernel<4, false>, dim3(grid), dim3(256), 0, st, p);
