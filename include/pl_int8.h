@@ -127,6 +127,16 @@ int pl_conv2d_i8_nhwc(const int8_t* x, const int8_t* w_packed, void* y,
 int pl_gemm_i8(const int8_t* A, int lda, const int8_t* Bt, int ldb, void* C,
                int ldc, int M, int N, int K, const pl_epilogue* e,
                pl_stream_t stream);
+/* Column-parallel (N-split) GEMM fused with the all-gather of its output columns (BASELINE config 5;
+ * no counterpart in the reference, which has no multi-GPU path): same as pl_gemm_i8, and every
+ * output tile is ALSO written to n_peers other buffers C_peers[i] (same shape/pitch as C: normally the
+ * same column block of the full [M, N_total] result on every other GPU, reached through NVLink peer
+ * mappings).  The stores are issued tile by tile by the kernel's TMA store warp, so the transfer
+ * overlaps the mainloop; the caller only synchronises the ranks afterwards.  int8 output only.
+ * maps_dev: 64-byte aligned device scratch of n_peers * 128 bytes. */
+int pl_gemm_i8_peers(const int8_t* A, int lda, const int8_t* Bt, int ldb, void* C, void* const* C_peers,
+                     int n_peers, void* maps_dev, int ldc, int M, int N, int K, const pl_epilogue* e,
+                     pl_stream_t stream);
 
 /* ---- bandwidth-bound paths (16-byte int8 vectors, no tensor cores) --------- */
 /* depthwise conv: groups == C == K, filter [C,R,S,1] as given by the reference */

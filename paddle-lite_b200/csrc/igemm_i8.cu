@@ -71,6 +71,11 @@ struct IgemmParams {
   uint32_t s2d_span_bytes, s2d_span_pitch;
   long long s2d_row_bytes, s2d_img_bytes;
   const int8_t* xs2d;
+  // N-split GEMM fused with its all-gather: the store warp writes every staged tile to the local C
+  // and to the same tile of n_peers peer C buffers (NVLink peer memory) through tensor maps that
+  // live in global memory -- the transfer overlaps the mainloop tile by tile, no collective call
+  const CUtensorMap* peer_maps;
+  int n_peers;
   int thin_group;  // thin mode with a resident filter: a ring stage holds all k-blocks of a tile
   int thin_shift;  // window starts `thin_shift` (0 / 1) words left of the first tap: the spare word of the
                    // SW-word window leads, which makes the start even for odd left pads at stride 2
@@ -906,6 +911,9 @@ igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
           } else {
             for (int j = 0; j < p.panels; ++j)
               tma_store_2d(&tmap_y, out_tile + (uint32_t)(j * kBM * p.PW), n0 + j * p.PW, tm * kBM);
+            for (int pe = 0; pe < p.n_peers; ++pe)
+              for (int j = 0; j < p.panels; ++j)
+                tma_store_2d(p.peer_maps + pe, out_tile + (uint32_t)(j * kBM * p.PW), n0 + j * p.PW, tm * kBM);
           }
           bulk_commit_group();
           bulk_wait_group_read<0>();
@@ -1462,6 +1470,7 @@ int launch_igemm(const CUtensorMap& ta, const CUtensorMap& tb, IgemmParams& p, p
     extra = p.out_bufs * tile + (p.tma_res ? p.res_bufs * tile : 0);
   }
   if (p.s2d && !hres) return PL_ERR_UNSUPPORTED;
+  if (p.n_peers > 0 && !p.tma_out) return PL_ERR_UNSUPPORTED;
   if (!p.tma_out) bres01 = false;
   p.b_resident = ((p.mode == 2 && p.n_tiles == 1) || hres || bres01) ? 1 : 0;
   if (p.mode == 2 && p.b_resident && env_int("PL_THIN_NO_GROUP", 0) == 0) {
@@ -1866,6 +1875,47 @@ extern "C" int pl_s2d_conv2d_i8(const int8_t* x_s2d, const int8_t* w_s2d, void* 
   rc = encode_2d(&tb, w_s2d, (uint64_t)nkb * 32, (uint64_t)d->K, (uint64_t)nkb * 32, p.BK, p.BN);
   if (rc) return rc;
   return launch_igemm(tb, tb, p, stream);
+}
+
+// N-split GEMM whose output tiles are also stored into peer GPUs' C buffers (see IgemmParams::peer_maps)
+extern "C" int pl_gemm_i8_peers(const int8_t* A, int lda, const int8_t* Bt, int ldb, void* C, void* const* C_peers,
+                                int n_peers, void* maps_dev, int ldc, int M, int N, int K, const pl_epilogue* e,
+                                pl_stream_t stream) {
+  if (!A || !Bt || !C || M <= 0 || N <= 0 || K <= 0 || lda < K || ldb < K || ldc < N || n_peers < 0 || n_peers > 15 ||
+      (n_peers > 0 && (!C_peers || !maps_dev)))
+    return PL_ERR_ARG;
+  int rc = check_epi(e);
+  if (rc) return rc;
+  if (!driver().ok) return PL_ERR_DRIVER;
+  if (driver().cc_major != 10) return PL_ERR_DEVICE;
+  if ((reinterpret_cast<uintptr_t>(A) & 15) || (reinterpret_cast<uintptr_t>(Bt) & 15) || (lda % 16) || (ldb % 16) ||
+      (reinterpret_cast<uintptr_t>(maps_dev) & 63))
+    return PL_ERR_ALIGN;
+  IgemmParams p{};
+  p.BK = pl_conv_block_k(K);
+  p.mode = 0;
+  rc = common_setup(p, M, N, C, ldc, e, K, 1);
+  if (rc) return rc;
+  CUtensorMap ta, tb;
+  rc = encode_2d(&ta, A, (uint64_t)K, (uint64_t)M, (uint64_t)lda, p.BK, kBM);
+  if (rc) return rc;
+  rc = encode_2d(&tb, Bt, (uint64_t)K, (uint64_t)N, (uint64_t)ldb, p.BK, p.BN);
+  if (rc) return rc;
+  if (n_peers > 0) {
+    // the peer stores exist only on the TMA-store epilogues (int8 out): same tile geometry as the local map
+    if (e->out_dtype != PL_OUT_INT8 || !p.vec_ok) return PL_ERR_UNSUPPORTED;
+    const int PW = p.BN < 128 ? p.BN : 128;
+    CUtensorMap maps[15];
+    for (int i = 0; i < n_peers; ++i) {
+      if (!C_peers[i] || (reinterpret_cast<uintptr_t>(C_peers[i]) & 15)) return PL_ERR_ALIGN;
+      rc = encode_2d(&maps[i], C_peers[i], (uint64_t)N, (uint64_t)M, (uint64_t)ldc, PW, kBM);
+      if (rc) return rc;
+    }
+    PL_CUDA_OK(cudaMemcpyAsync(maps_dev, maps, sizeof(CUtensorMap) * n_peers, cudaMemcpyHostToDevice, (cudaStream_t)stream));
+    p.peer_maps = reinterpret_cast<const CUtensorMap*>(maps_dev);
+    p.n_peers = n_peers;
+  }
+  return launch_igemm(ta, tb, p, stream);
 }
 
 extern "C" int pl_gemm_i8(const int8_t* A, int lda, const int8_t* Bt, int ldb, void* C, int ldc,

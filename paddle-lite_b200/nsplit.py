@@ -95,3 +95,30 @@ class NSplitGemm:
         if self.world == 1:
             return c[:, :self.N]
         return gather_columns(c, self.N, self.group)
+
+    # -- fused GEMM + all-gather over NVLink peer memory (int8 out) --------------------------------
+    def fused_setup(self, M):
+        """Allocates the full result [M, world * per] in symmetric memory (every rank maps every other
+        rank's buffer) and the device scratch for the peer tensor maps."""
+        import torch.distributed._symmetric_memory as symm_mem
+        assert self.out_dtype == self.pl.OUT_INT8, "peer stores exist on the int8 TMA-store epilogue only"
+        full = symm_mem.empty((M, self.world * self.per), dtype=torch.int8, device=self.device)
+        hdl = symm_mem.rendezvous(full, self.group if self.group is not None else dist.group.WORLD)
+        off = self.rank * self.per  # this rank's column block inside everybody's result
+        self._full, self._hdl, self._fM = full, hdl, M
+        self._peer_ptrs = [int(hdl.buffer_ptrs[r]) + off for r in range(self.world) if r != self.rank]
+        self._maps = torch.empty(128 * 16, dtype=torch.uint8, device=self.device)
+        return full
+
+    def fused(self, A_dev):
+        """C[M, N] on every rank: each rank's GEMM kernel TMA-stores its output tiles into its own result
+        buffer and straight into the peers' (NVLink), overlapped with the mainloop; one device-side barrier
+        of the ranks afterwards.  No collective call, no de-interleaving copy."""
+        M = A_dev.shape[0]
+        if getattr(self, "_fM", None) != M:
+            self.fused_setup(M)
+        y = self._full[:, self.rank * self.per:(self.rank + 1) * self.per]
+        self.pl.gemm_peers(A_dev, self.bt, self.scale, self.bias, y, self._peer_ptrs, self._maps, self.act,
+                           self.act_arg, N=self.per, K=self.K)
+        self._hdl.barrier()
+        return self._full[:, :self.N]

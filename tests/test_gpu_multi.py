@@ -46,6 +46,13 @@ def _worker(rank, world, port, M, K, N, out_fp32, q):
         got = g(Ad).cpu().numpy()
         want = orc.gemm(A, B, scale, bias, act=orc.ACT_RELU, out=out)
         ok = np.array_equal(got, want) if not out_fp32 else np.allclose(got, want, rtol=1e-5, atol=1e-6)
+        if not out_fp32:
+            # fused GEMM + all-gather: tiles TMA-stored into the peers' results over NVLink
+            for _ in range(2):
+                fused = g.fused(Ad)
+                torch.cuda.synchronize()
+                ok = ok and np.array_equal(fused.cpu().numpy(), want)
+                dist.barrier()
         q.put((rank, bool(ok), got.shape))
     finally:
         dist.destroy_process_group()

@@ -53,10 +53,14 @@ def main():
             iters = max(3, min(200, int(2e12 / (2.0 * M * N * K / world + 1))))
             ms_local = time_ms(lambda: op.local(A), iters)
             ms_full = time_ms(lambda: op(A), iters)
-            t = torch.tensor([ms_local, ms_full], device="cuda")
+            ms_fused = 0.0
+            if world > 1 and out == pl.OUT_INT8:
+                op.fused_setup(M)
+                ms_fused = time_ms(lambda: op.fused(A), iters)
+            t = torch.tensor([ms_local, ms_full, ms_fused], device="cuda")
             if world > 1:
                 dist.all_reduce(t, op=dist.ReduceOp.MAX)
-            ms_local, ms_full = t.tolist()
+            ms_local, ms_full, ms_fused = t.tolist()
             if rank == 0:
                 ops = 2.0 * M * N * K
                 eb = 1 if out == pl.OUT_INT8 else 4
@@ -65,6 +69,8 @@ def main():
                     "shape": [M, N, K], "out": "int8" if eb == 1 else "fp32", "n_gpus": world,
                     "ms_gemm": round(ms_local, 4), "ms_with_gather": round(ms_full, 4),
                     "tops_gemm": round(ops / ms_local / 1e9, 1), "tops_with_gather": round(ops / ms_full / 1e9, 1),
+                    "ms_fused_peer_store": round(ms_fused, 4) if ms_fused else None,
+                    "tops_fused_peer_store": round(ops / ms_fused / 1e9, 1) if ms_fused else None,
                     "gbs_gemm": round(byts / world / ms_local / 1e6, 1),
                     "frac_mma_peak": None if not peak else round(ops / world / ms_local / 1e9 / peak, 3),
                     "mma_peak_tops": peak}), flush=True)
