@@ -610,3 +610,15 @@ def test_s2d_geometry_rejects(pl):
     assert not pl.s2d_geometry(1, 32, 32, 8, 3, 3, (2, 2), (1, 1, 1, 1)).supported      # not thin
     assert not pl.s2d_geometry(1, 32, 600, 3, 3, 3, (2, 2), (1, 1, 1, 1)).supported     # Q > 128
     assert not pl.s2d_geometry(1, 32, 32, 3, 9, 9, (2, 2), (4, 4, 4, 4)).supported      # 5 taps per axis
+
+
+def test_humanseg_model_layers(pl):
+    """BASELINE config 3: every distinct conv2d / depthwise_conv2d shape of the shipped
+    humanseg_shfv75_0119_quant `__model__` (channels 3/9/18/36/72/144 -> padded pitches, s2d stem, 3x3 s1/s2
+    depthwise), bit-exact against the oracle.  Shapes: tests/golden/humanseg_layers.json."""
+    import importlib.util
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    spec = importlib.util.spec_from_file_location("humanseg_layers", os.path.join(root, "tools", "humanseg_layers.py"))
+    mod = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mod)
+    assert mod.check(batch=2) == 20
