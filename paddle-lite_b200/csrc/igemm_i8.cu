@@ -21,6 +21,7 @@
 #include <cuda.h>
 #include <cstdio>
 #include <cstdlib>
+#include <type_traits>
 #include <vector>
 #include <cudaTypedefs.h>
 
@@ -74,6 +75,11 @@ struct IgemmParams {
   // N-split GEMM fused with its all-gather: the store warp writes every staged tile to the local C
   // and to the same tile of n_peers peer C buffers (NVLink peer memory) through tensor maps that
   // live in global memory -- the transfer overlaps the mainloop tile by tile, no collective call
+  // narrow tiles: the 16 epilogue warps split into `epi_groups` groups that take alternate tiles, each
+  // warp walking more 16-column units of its own tile (TMEM loads pipelined) -- the fixed per-tile
+  // cost of the epilogue chain (waits, fences, arrivals: ~900 cycles) is then paid by 1/groups of the
+  // warps per tile instead of all of them
+  int epi_groups;
   const CUtensorMap* peer_maps;
   int n_peers;
   int thin_group;  // thin mode with a resident filter: a ring stage holds all k-blocks of a tile
@@ -406,9 +412,9 @@ igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
     }
     for (int s = 0; s < kMaxAccStages; ++s) {
       mbar_init(bar_tfull + 8 * s, 1);
-      mbar_init(bar_tempty + 8 * s, EW);  // one arrival per epilogue warp
+      mbar_init(bar_tempty + 8 * s, EW / p.epi_groups);  // one arrival per epilogue warp of the tile's group
     }
-    for (int s = 0; s < kMaxResBufs; ++s) mbar_init(bar_staged + 8 * s, EW);
+    for (int s = 0; s < kMaxResBufs; ++s) mbar_init(bar_staged + 8 * s, EW / p.epi_groups);
     for (int s = 0; s < kMaxOutBufs; ++s) mbar_init(bar_ofree + 8 * s, 1);
     for (int s = 0; s < kMaxHaloBufs; ++s) {
       mbar_init(bar_afull + 8 * s, 1);
@@ -932,7 +938,7 @@ igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
     const int cq = (warp - 2) >> 2;
     const int etid = (warp - 2) * 32 + lane;
     constexpr bool kFast = (EPI != EPI_GENERIC);  // int8 paths: swizzled smem staging + TMA store
-    constexpr int CQ = EW / 4;  // warps per TMEM lane quarter = column groups
+    constexpr int CQ = EW / 4;  // warps per TMEM lane quarter
     const int units = p.BN >> 4;
     // accumulator row of this thread -> row of the (dense) output tile.  Halo mode computes
     // on the padded grid: row i is output (i / WP, i % WP) of the band, rows in the pad
@@ -949,12 +955,6 @@ igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
     }
     const uint32_t rowoff = (uint32_t)(jrow * p.PW);
     const uint32_t swx = (rowoff >> 7) & p.swz_mask;
-    int as = 0;
-    uint32_t aphase = 0;
-    int rb = 0;
-    uint32_t rphase = 0;
-    int ob = 0;
-    uint32_t ophase = 0;
     int sbuf = 0;  // per-tile scale / bias buffer (very wide outputs only)
     // folded scale / bias live in smem.  Normally the vectors of every n-tile are staged once
     // here; a global load per tile would sit on the epilogue's critical path (the tile rate of
@@ -979,10 +979,23 @@ igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
     }
     pdl_wait();  // the generic path reads the residual / writes y with plain global accesses
     asm volatile("bar.sync 1, %0;" ::"n"(32 * EW) : "memory");
-    int lt = 0;
+    // the tile loop is instantiated for the two group layouts in use (compile-time unit stride):
+    // one group of all warps, or CQ groups of four warps (one warp per TMEM lane quarter)
+    auto epilogue_loop = [&](auto cqn_tag) {
+    constexpr int cqn = decltype(cqn_tag)::value;  // column groups inside one tile group
+    constexpr int G = CQ / cqn;                    // tile-alternating groups
+    const int egroup = cq / cqn, cqp = cq - egroup * cqn;
+    int lt = egroup;  // local tile counter of this CTA: group g takes tiles g, g + G, ...
     const int trole = (warp == 2 && lane == 0) ? 2 : ((warp == 1 + EW && lane == 0) ? 3 : -1);
 #define PL_ETRACE(e) do { if (trole >= 0) PL_TRACE(trole, lt, e); } while (0)
-    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++lt) {
+    const int res_bufs_ = p.res_bufs > 0 ? p.res_bufs : 1, out_bufs_ = p.out_bufs > 0 ? p.out_bufs : 1;
+    // ring positions of local tile `lt` (the groups interleave on every ring): start at lt = egroup, then
+    // advance by G per tile -- kept incrementally, a runtime % and / per ring and tile costs more than
+    // the groups save on wide tiles
+    int as = egroup % p.acc_stages, rb = egroup % res_bufs_, ob = egroup % out_bufs_;
+    uint32_t aphase = (uint32_t)(egroup / p.acc_stages) & 1u, rphase = (uint32_t)(egroup / res_bufs_) & 1u,
+             ophase = (uint32_t)(egroup / out_bufs_) & 1u;
+    for (int tile = blockIdx.x + egroup * (int)gridDim.x; tile < num_tiles; tile += G * (int)gridDim.x, lt += G) {
       PL_ETRACE(0);
       const int tn = tile % p.n_tiles, tm = tile / p.n_tiles;
       long long row = (long long)tm * kBM + arow;  // output pixel index (generic epilogue)
@@ -1015,14 +1028,14 @@ igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
       // TMEM reads are double buffered: unit i+1 is in flight while unit i runs through the ALUs
       uint32_t accb[2][16];
       const bool skip_epi = (PL_DBG_FLAGS_V & 1) != 0;
-      if (cq < units && !skip_epi) tmem_ld_32x32b_x16(t_addr + (uint32_t)(cq * 16), accb[0]);
+      if (cqp < units && !skip_epi) tmem_ld_32x32b_x16(t_addr + (uint32_t)(cqp * 16), accb[0]);
 #pragma unroll
       for (int i = 0; i < 16 / CQ; ++i) {
-        const int u = cq + CQ * i;
+        const int u = cqp + cqn * i;
         if (u < units && !skip_epi) {  // warp-uniform
           tmem_ld_wait();
-          if (i < 16 / CQ - 1 && u + CQ < units)
-            tmem_ld_32x32b_x16(t_addr + (uint32_t)((u + CQ) * 16), accb[(i + 1) & 1]);
+          if (i < 16 / CQ - 1 && u + cqn < units)
+            tmem_ld_32x32b_x16(t_addr + (uint32_t)((u + cqn) * 16), accb[(i + 1) & 1]);
           uint32_t(&acc)[16] = accb[i & 1];
           const uint32_t col = (uint32_t)(u * 16);
           if (kFast && !rvalid) {
@@ -1067,12 +1080,14 @@ igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
         else if (kFast) mbar_arrive(bar_staged + 8 * ob);
       }
       PL_ETRACE(3);
-      if (++as == p.acc_stages) { as = 0; aphase ^= 1; }
+      as += G;
+      while (as >= p.acc_stages) { as -= p.acc_stages; aphase ^= 1u; }
       if (EPI == EPI_I8_RELU_RES) {
-        if (++rb == p.res_bufs) { rb = 0; rphase ^= 1; }
-      }
-      if (kFast) {
-        if (++ob == p.out_bufs) { ob = 0; ophase ^= 1; }
+        rb += G;
+        while (rb >= res_bufs_) { rb -= res_bufs_; rphase ^= 1u; }
+      } else if (kFast) {
+        ob += G;
+        while (ob >= out_bufs_) { ob -= out_bufs_; ophase ^= 1u; }
       }
       if (!p.sb_all) {
         // very wide outputs: next tile's scale / bias into the other buffer, published by a
@@ -1083,6 +1098,9 @@ igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
       }
       PL_ETRACE(6);
     }
+    };  // epilogue_loop
+    if (p.epi_groups > 1) epilogue_loop(std::integral_constant<int, 1>{});
+    else epilogue_loop(std::integral_constant<int, CQ>{});
   }
 
   tc_fence_before();
@@ -1468,6 +1486,20 @@ int launch_igemm(const CUtensorMap& ta, const CUtensorMap& tb, IgemmParams& p, p
       }
     }
     extra = p.out_bufs * tile + (p.tma_res ? p.res_bufs * tile : 0);
+  }
+  p.epi_groups = 1;
+  if (p.tma_out && p.sb_all) {
+    const int cq = (p.mode == 2 ? kThinEpiWarps : kEpiWarps) / 4;  // warps per TMEM lane quarter
+    const int per_warp_max = 16 / cq;                               // unrolled unit slots of one warp
+    const int units = p.BN / 16;
+    int cqn_min = (units + per_warp_max - 1) / per_warp_max;
+    if (cqn_min < 1) cqn_min = 1;
+    int g = cq / cqn_min;
+    if (units > env_int("PL_EPI_GROUPS_MAX_UNITS", 4)) g = 1;  // measured: BN >= 128 tiles lose a few % with groups
+    const int bufs = p.tma_res ? p.res_bufs : p.out_bufs;
+    while (g > 1 && (g > bufs || g > p.acc_stages || (cq % g) != 0)) g >>= 1;
+    if (g != cq || env_int("PL_EPI_GROUPS", 4) <= 1) g = 1;  // the kernel instantiates 1 group or `cq` groups
+    p.epi_groups = g;
   }
   if (p.s2d && !hres) return PL_ERR_UNSUPPORTED;
   if (p.n_peers > 0 && !p.tma_out) return PL_ERR_UNSUPPORTED;
