@@ -317,6 +317,18 @@ __device__ __forceinline__ void issue_taps(uint32_t d_tmem, uint64_t da0, uint64
                        db0 + (uint64_t)((r * S_ + sx) * b_step), idesc, fresh && r == 0 && sx == 0);
 }
 
+// all MMAs of one space-to-depth tile (TA tap rows x KPR K=32 steps), fully unrolled
+template <int TA, int KPR>
+__device__ __forceinline__ void issue_s2d(uint32_t d_tmem, uint64_t da0, uint64_t db0, uint32_t idesc,
+                                          uint32_t pitch16, uint32_t b_step) {
+#pragma unroll
+  for (int a = 0; a < TA; ++a)
+#pragma unroll
+    for (int ks = 0; ks < KPR; ++ks)
+      umma_i8(d_tmem, da0 + (uint64_t)(a * pitch16 + 2u * ks), db0 + (uint64_t)((a * KPR + ks) * b_step), idesc,
+              (uint32_t)((a | ks) != 0));
+}
+
 // timeline tracing: role r, local tile t (first 64 tiles of CTA 0), event e (0..7)
 // Debug knobs (timeline trace, PL_DBG_FLAGS ablations, descriptor experiments) exist only in
 // builds made with -DPL_DEBUG_KNOBS (tools/build_variant.sh dbg "-DPL_DEBUG_KNOBS"): even
@@ -662,11 +674,17 @@ igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
           tc_fence_after();
           const uint32_t d_tmem = tmem_base + (uint32_t)as * p.acc_stride;
           uint32_t t_lo = a_lo0 + (uint32_t)ab * halo_step, bb = b_lo0;
-          for (int a = 0; a < ta; ++a, t_lo += pitch16)
-            for (int ks = 0; ks < kpr; ++ks, bb += b_step)  // K = 32: pixels (2 ks, 2 ks + 1) of every row
-              if (!skip_mma)
+          if (skip_mma) {
+          } else if (ta == 4 && kpr == 2) {  // 7x7 / p3 stem
+            issue_s2d<4, 2>(d_tmem, desc_a | (uint64_t)t_lo, desc_hi | (uint64_t)bb, idesc, pitch16, b_step);
+          } else if (ta == 2 && kpr == 1) {  // 3x3 / p1 stem
+            issue_s2d<2, 1>(d_tmem, desc_a | (uint64_t)t_lo, desc_hi | (uint64_t)bb, idesc, pitch16, b_step);
+          } else {
+            for (int a = 0; a < ta; ++a, t_lo += pitch16)
+              for (int ks = 0; ks < kpr; ++ks, bb += b_step)  // K = 32: pixels (2 ks, 2 ks + 1) of every row
                 umma_i8(d_tmem, desc_a | (uint64_t)(t_lo + 2u * (uint32_t)ks), desc_hi | (uint64_t)bb, idesc,
                         (uint32_t)((a | ks) != 0));
+          }
           umma_commit(bar_aempty + 8 * ab);
           umma_commit(bar_tfull + 8 * as);
           PL_MTRACE(lt, 4);
