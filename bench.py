@@ -368,7 +368,13 @@ def layer_roofline(net, prog, batch, nets, torch):
         tj = json.load(open(tpath)).get(f"{prog.name}_b{batch}")
         if tj:
             traffic = tj["igemm_dram_bytes_per_launch"]
-    roof.update({"traffic": traffic, "algorithmic_bytes_per_launch": tc_bytes / n_tc, "kernel": "igemm_i8_kernel", "launches_per_step": n_tc,
+    try:
+        probe = round(nets.pl.measure_i8_mma_peak(), 1)  # back-to-back tcgen05.mma.kind::i8, all SMs
+    except Exception:
+        probe = None
+    roof.update({"tensor_peak_tops_probe": probe,
+                 "tensor_frac_of_probe": (tc_ops / (tc_ms * 1e-3) / 1e12 / probe) if probe else None,
+                 "traffic": traffic, "algorithmic_bytes_per_launch": tc_bytes / n_tc, "kernel": "igemm_i8_kernel", "launches_per_step": n_tc,
                  "avg_launch_ms": tc_ms / n_tc, "share_of_step": tc_ms / total_ms, "peak_source": src,
                  "tensor_tops": tc_ops / (tc_ms * 1e-3) / 1e12, "tensor_peak_tops_2x_bf16": i8_peak,
                  "hbm_gbs": tc_bytes / (tc_ms * 1e-3) / 1e9,
