@@ -80,6 +80,11 @@ struct IgemmParams {
   // cost of the epilogue chain (waits, fences, arrivals: ~900 cycles) is then paid by 1/groups of the
   // warps per tile instead of all of them
   int epi_groups;
+  // long-K GEMMs: a tile is a PAIR of 128-row blocks (256 x BN) that share every B stage -- two MMAs per
+  // K step into two TMEM accumulators (all 512 columns at BN = 256).  L2 -> SM bytes per MAC drop by a
+  // third (the bound of these launches); the epilogue of a pair no longer overlaps the
+  // next mainloop, which long K amortises
+  int mpair;
   const CUtensorMap* peer_maps;
   int n_peers;
   int thin_group;  // thin mode with a resident filter: a ring stage holds all k-blocks of a tile
@@ -382,6 +387,7 @@ igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
   const uint32_t smem_out = smem_base + p.out_stage_off;
   const uint32_t smem_res = smem_base + p.res_stage_off;
   const uint32_t tile_bytes = (uint32_t)(kBM * p.BN);
+  const uint32_t obuf_bytes = tile_bytes << p.mpair;  // output staging buffer: one tile, or the two of a pair
   float* const s_scale = reinterpret_cast<float*>(smem_raw + (smem_base - smem_u32(smem_raw)) + p.sb_off);
   float* const s_bias = s_scale + p.sb_n;
 
@@ -574,7 +580,7 @@ igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
     for (int tile = blockIdx.x; tile < num_tiles && !(TR > 0 && p.b_resident) && mode != 3; tile += gridDim.x, ++lt) {
       PL_TRACE(0, lt, 0);
       const int tn = tile % n_tiles, tm = tile / n_tiles;
-      const int m0 = tm * kBM, n0 = tn * BN;
+      const int m0 = (tm * kBM) << p.mpair, n0 = tn * BN;  // pairs: one 256-row box
       if (EPI == EPI_I8_RELU_RES) {
         // residual tile first: it is the largest load of a 1x1 expand layer
         WAIT(bar_rempty + 8 * rb, rphase ^ 1);
@@ -796,7 +802,11 @@ igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
             if (PL_DBG_BASEOFF_V) da |= (uint64_t)((start >> 7) & 7u) << 49;
           }
           if (leader) {
-            if (!skip_mma) issue_kblock_n(ksteps, d_tmem, da, db, idesc, kb == 0);
+            if (!skip_mma) {
+              issue_kblock_n(ksteps, d_tmem, da, db, idesc, kb == 0);
+              if (p.mpair)  // second 128-row block of the stage, same B, second accumulator
+                issue_kblock_n(ksteps, d_tmem + (uint32_t)p.BN, da + (uint64_t)((kBM * p.BK) >> 4), db, idesc, kb == 0);
+            }
             umma_commit(empty_b);
             if (kb == num_kb - 1) umma_commit(bar_tfull + 8 * as);
           }
@@ -924,7 +934,7 @@ igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
       for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
         const int tn = tile % p.n_tiles, tm = tile / p.n_tiles;
         const int n0 = tn * p.BN;
-        const uint32_t out_tile = (kInPlace ? smem_res : smem_out) + (uint32_t)ob * tile_bytes;
+        const uint32_t out_tile = (kInPlace ? smem_res : smem_out) + (uint32_t)ob * (kInPlace ? tile_bytes : obuf_bytes);
         WAIT(bar_staged + 8 * ob, ophase);
         if (!(PL_DBG_FLAGS_V & 16)) {
           if (halo) {  // box = PW channels x Q pixels x hk rows of one image; rows >= P are clipped
@@ -933,11 +943,15 @@ igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
             for (int j = 0; j < p.panels; ++j)
               tma_store_4d(&tmap_y, out_tile + (uint32_t)(j * kBM * p.PW), n0 + j * p.PW, 0, hp0, himg);
           } else {
-            for (int j = 0; j < p.panels; ++j)
-              tma_store_2d(&tmap_y, out_tile + (uint32_t)(j * kBM * p.PW), n0 + j * p.PW, tm * kBM);
-            for (int pe = 0; pe < p.n_peers; ++pe)
+            for (int sub = 0; sub <= p.mpair; ++sub) {
+              const uint32_t src = out_tile + (uint32_t)sub * tile_bytes;
+              const int mrow = ((tm << p.mpair) + sub) * kBM;
               for (int j = 0; j < p.panels; ++j)
-                tma_store_2d(p.peer_maps + pe, out_tile + (uint32_t)(j * kBM * p.PW), n0 + j * p.PW, tm * kBM);
+                tma_store_2d(&tmap_y, src + (uint32_t)(j * kBM * p.PW), n0 + j * p.PW, mrow);
+              for (int pe = 0; pe < p.n_peers; ++pe)
+                for (int j = 0; j < p.panels; ++j)
+                  tma_store_2d(p.peer_maps + pe, src + (uint32_t)(j * kBM * p.PW), n0 + j * p.PW, mrow);
+            }
           }
           bulk_commit_group();
           bulk_wait_group_read<0>();
@@ -957,7 +971,7 @@ igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
     const int etid = (warp - 2) * 32 + lane;
     constexpr bool kFast = (EPI != EPI_GENERIC);  // int8 paths: swizzled smem staging + TMA store
     constexpr int CQ = EW / 4;  // warps per TMEM lane quarter
-    const int units = p.BN >> 4;
+    const int units = (p.BN >> 4) << p.mpair;  // 16-column units of the accumulator stage (both blocks of a pair)
     // accumulator row of this thread -> row of the (dense) output tile.  Halo mode computes
     // on the padded grid: row i is output (i / WP, i % WP) of the band, rows in the pad
     // columns or beyond the band carry garbage and are dropped here
@@ -1040,7 +1054,7 @@ igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
       tc_fence_after();
       const uint32_t t_addr = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)as * p.acc_stride;
       const uint32_t res_base = smem_res + (uint32_t)rb * tile_bytes + rowoff;
-      const uint32_t out_tile = smem_out + (uint32_t)ob * tile_bytes;
+      const uint32_t out_tile = smem_out + (uint32_t)ob * obuf_bytes;
       // fused residual: each 16-byte chunk of the output replaces the residual chunk it was computed from
       const uint32_t out_base = EPI == EPI_I8_RELU_RES ? res_base : out_tile + rowoff;
       // TMEM reads are double buffered: unit i+1 is in flight while unit i runs through the ALUs
@@ -1048,14 +1062,17 @@ igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
       const bool skip_epi = (PL_DBG_FLAGS_V & 1) != 0;
       if (cqp < units && !skip_epi) tmem_ld_32x32b_x16(t_addr + (uint32_t)(cqp * 16), accb[0]);
 #pragma unroll
-      for (int i = 0; i < 16 / CQ; ++i) {
+      for (int i = 0; i < 32 / CQ; ++i) {  // 16 / CQ slots per 128-row block, two blocks in a pair
         const int u = cqp + cqn * i;
         if (u < units && !skip_epi) {  // warp-uniform
           tmem_ld_wait();
-          if (i < 16 / CQ - 1 && u + cqn < units)
+          if (i < 32 / CQ - 1 && u + cqn < units)
             tmem_ld_32x32b_x16(t_addr + (uint32_t)((u + cqn) * 16), accb[(i + 1) & 1]);
           uint32_t(&acc)[16] = accb[i & 1];
-          const uint32_t col = (uint32_t)(u * 16);
+          const uint32_t colt = (uint32_t)(u * 16);                       // TMEM column of the unit
+          const uint32_t sub = (p.mpair && colt >= (uint32_t)p.BN) ? 1u : 0u;  // 128-row block of a pair
+          const uint32_t col = colt - sub * (uint32_t)p.BN;              // output column inside the tile
+          const uint32_t sbase = sub * tile_bytes;
           if (kFast && !rvalid) {
             // padded-grid row without an output pixel
           } else if (kFast) {
@@ -1064,7 +1081,7 @@ igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
             const uint32_t soff = (col >> p.pw_shift) * (uint32_t)(kBM * p.PW) +
                                   ((((col & (uint32_t)(p.PW - 1)) >> 4) ^ swx) << 4);
             uint4 rw = make_uint4(0, 0, 0, 0);
-            if (EPI == EPI_I8_RELU_RES) rw = ld_shared_v4(res_base + soff);
+            if (EPI == EPI_I8_RELU_RES) rw = ld_shared_v4(res_base + soff);  // (pairs never carry a residual)
             const uint32_t rws[4] = {rw.x, rw.y, rw.z, rw.w};
             uint32_t w[4];
 #pragma unroll
@@ -1078,7 +1095,7 @@ igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
               else
                 w[q4] = quad_i8_signed(acc + 4 * q4, sc, bi);
             }
-            st_shared_v4(out_base + soff, w[0], w[1], w[2], w[3]);
+            st_shared_v4(out_base + sbase + soff, w[0], w[1], w[2], w[3]);
           } else if (row < p.M && n0 + (int)col < p.Nout) {
             store_group16(p, acc, row, n0 + (int)col, &s_scale[sb0 + col], &s_bias[sb0 + col]);
           }
@@ -1429,7 +1446,7 @@ int launch_igemm(const CUtensorMap& ta, const CUtensorMap& tb, IgemmParams& p, p
   p.sb_n = p.sb_all ? n_cover : 512;
   const int sb_bytes = (p.sb_n * 8 + 1023) / 1024 * 1024;
   const int budget = 219 * 1024 - sb_bytes;  // static smem is now only the barriers
-  const int tile = kBM * p.BN;
+  const int tile = (kBM * p.BN) << p.mpair;  // staging buffer (both blocks of a pair)
   const int stage_bytes = (int)(p.a_stage_bytes + p.b_stage_bytes);
   p.out_bufs = 0;
   p.res_bufs = 2;
@@ -1441,7 +1458,7 @@ int launch_igemm(const CUtensorMap& ta, const CUtensorMap& tb, IgemmParams& p, p
   // same N tile, so that filter slice can stay in smem for the kernel's lifetime (the per-tile
   // re-read of B from L2 is what bounds the short-K layers: B is 2x the A bytes at BN = 256)
   bool bres01 = (p.mode == 0 || p.mode == 1) && epi != EPI_GENERIC && env_int("PL_IGEMM_NO_BRES01", 0) == 0 &&
-                tiles >= 2 * grid && p.n_tiles <= 16;
+                tiles >= 2 * grid && p.n_tiles <= 16 && !p.mpair;
   if (bres01) {
     const int g = grid - grid % p.n_tiles;
     const int bbytes = p.num_kb * (int)p.b_stage_bytes;
@@ -1927,6 +1944,33 @@ extern "C" int pl_s2d_conv2d_i8(const int8_t* x_s2d, const int8_t* w_s2d, void* 
   return launch_igemm(tb, tb, p, stream);
 }
 
+// long-K GEMM: switch the launch to 256 x 256 tile pairs (IgemmParams::mpair) when it qualifies
+static void maybe_enable_mpair(IgemmParams& p, const pl_epilogue* e, int K) {
+  const bool fast = e->out_dtype == PL_OUT_INT8 && e->round_mode == PL_ROUND_ARM && p.vec_ok && e->scale &&
+                    !e->residual && tma_epilogue_enabled() &&
+                    (e->act == PL_ACT_NONE || e->act == PL_ACT_RELU || (e->act == PL_ACT_RELU6 && e->act_arg > 0.f));
+  if (!fast || p.mode != 0 || p.BN != 256 || p.m_tiles < 2 || env_int("PL_NO_MPAIR", 0)) return;
+  if (!env_int("PL_MPAIR_FORCE", 0)) {
+    // the pair has a single accumulator stage (its epilogue is exposed), so K must be long enough
+    // to hide it, and the coarser work unit must not cost a wave
+    const long long sms = driver().sm_count;
+    const long long tiles = (long long)p.m_tiles * p.n_tiles, pairs = (long long)((p.m_tiles + 1) / 2) * p.n_tiles;
+    const long long w1 = (tiles + sms - 1) / sms, w2 = 2 * ((pairs + sms - 1) / sms);
+    if (K < env_int("PL_MPAIR_MIN_K", 4096) || tiles < 2 * sms || w2 > w1) return;
+  }
+  p.mpair = 1;
+  p.BK = 64;  // 32 KB stages: four of them beside the 64 KB staging buffer
+  p.cblocks = (K + p.BK - 1) / p.BK;  // the K tail is zero-filled by TMA
+  p.num_kb = p.cblocks;
+  p.m_tiles = (p.m_tiles + 1) / 2;
+  p.a_stage_bytes = (uint32_t)(2 * kBM * p.BK);
+  p.b_stage_bytes = (uint32_t)(p.BN * p.BK);
+  p.tx_bytes = p.a_stage_bytes + p.b_stage_bytes;
+  p.acc_stride = 2u * (uint32_t)p.BN;
+  p.acc_stages = 1;
+  p.tmem_cols = 512;
+}
+
 // N-split GEMM whose output tiles are also stored into peer GPUs' C buffers (see IgemmParams::peer_maps)
 extern "C" int pl_gemm_i8_peers(const int8_t* A, int lda, const int8_t* Bt, int ldb, void* C, void* const* C_peers,
                                 int n_peers, void* maps_dev, int ldc, int M, int N, int K, const pl_epilogue* e,
@@ -1946,8 +1990,9 @@ extern "C" int pl_gemm_i8_peers(const int8_t* A, int lda, const int8_t* Bt, int 
   p.mode = 0;
   rc = common_setup(p, M, N, C, ldc, e, K, 1);
   if (rc) return rc;
+  maybe_enable_mpair(p, e, K);
   CUtensorMap ta, tb;
-  rc = encode_2d(&ta, A, (uint64_t)K, (uint64_t)M, (uint64_t)lda, p.BK, kBM);
+  rc = encode_2d(&ta, A, (uint64_t)K, (uint64_t)M, (uint64_t)lda, p.BK, kBM << p.mpair);
   if (rc) return rc;
   rc = encode_2d(&tb, Bt, (uint64_t)K, (uint64_t)N, (uint64_t)ldb, p.BK, p.BN);
   if (rc) return rc;
@@ -1984,8 +2029,9 @@ extern "C" int pl_gemm_i8(const int8_t* A, int lda, const int8_t* Bt, int ldb, v
   p.mode = 0;
   rc = common_setup(p, M, N, C, ldc, e, K, 1);
   if (rc) return rc;
+  maybe_enable_mpair(p, e, K);
   CUtensorMap ta, tb;
-  rc = encode_2d(&ta, A, (uint64_t)K, (uint64_t)M, (uint64_t)lda, p.BK, kBM);
+  rc = encode_2d(&ta, A, (uint64_t)K, (uint64_t)M, (uint64_t)lda, p.BK, kBM << p.mpair);
   if (rc) return rc;
   rc = encode_2d(&tb, Bt, (uint64_t)K, (uint64_t)N, (uint64_t)ldb, p.BK, p.BN);
   if (rc) return rc;

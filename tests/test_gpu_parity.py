@@ -300,6 +300,23 @@ def test_gemm_parity(pl, mnk):
     assert np.array_equal(got, want)
 
 
+@pytest.mark.parametrize("mnk", [(640, 512, 2080), (1000, 300, 4096), (256, 256, 64)])
+def test_gemm_tile_pair_mode(pl, mnk, monkeypatch):
+    """Long-K GEMMs run as 256 x 256 tile pairs (one B stage feeds two accumulators); the
+    heuristic only picks it for large problems, so force it here on ragged small ones."""
+    monkeypatch.setenv("PL_MPAIR_FORCE", "1")
+    M, N, K = mnk
+    rng = np.random.default_rng(M + N + K)
+    A = rng.integers(-127, 128, (M, K), dtype=np.int8)
+    Bt = rng.integers(-127, 128, (N, K), dtype=np.int8)
+    s = ((rng.random(N, dtype=np.float32) + 0.5) / 127 / 127 * (64.0 / K) * 8).astype(np.float32)
+    b = rng.standard_normal(N).astype(np.float32)
+    for act, oact in ((pl.ACT_RELU, orc.ACT_RELU), (pl.ACT_NONE, orc.ACT_NONE)):
+        want = orc.gemm(A, Bt, s, b, b_is_nk=True, act=oact, out=orc.OUT_INT8)
+        got = host(pl.gemm(dev(A), dev(Bt), dev(s), dev(b), act=act, out=pl.OUT_INT8))
+        assert np.array_equal(got, want)
+
+
 def test_gemm_fc_weight_layout(pl):
     """fc keeps W as [K,N] (lite/kernels/cuda/fc_compute.cu:199-353); it is transposed
     once (PrepareForRun) with pl_transpose_i8 and then used K-major."""
