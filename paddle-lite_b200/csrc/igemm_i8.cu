@@ -971,7 +971,6 @@ igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
     const int etid = (warp - 2) * 32 + lane;
     constexpr bool kFast = (EPI != EPI_GENERIC);  // int8 paths: swizzled smem staging + TMA store
     constexpr int CQ = EW / 4;  // warps per TMEM lane quarter
-    const int units = (p.BN >> 4) << p.mpair;  // 16-column units of the accumulator stage (both blocks of a pair)
     // accumulator row of this thread -> row of the (dense) output tile.  Halo mode computes
     // on the padded grid: row i is output (i / WP, i % WP) of the band, rows in the pad
     // columns or beyond the band carry garbage and are dropped here
@@ -1013,7 +1012,10 @@ igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
     asm volatile("bar.sync 1, %0;" ::"n"(32 * EW) : "memory");
     // the tile loop is instantiated for the two group layouts in use (compile-time unit stride):
     // one group of all warps, or CQ groups of four warps (one warp per TMEM lane quarter)
-    auto epilogue_loop = [&](auto cqn_tag) {
+    auto epilogue_loop = [&](auto cqn_tag, auto pair_tag) {
+    constexpr bool kPair = decltype(pair_tag)::value;  // 256 x BN tile pairs: two accumulators per stage
+    constexpr int kSlots = (kPair ? 32 : 16) / CQ;     // unrolled unit slots of one warp
+    const int units = kPair ? 2 * (p.BN >> 4) : (p.BN >> 4);  // 16-column units of one accumulator stage
     constexpr int cqn = decltype(cqn_tag)::value;  // column groups inside one tile group
     constexpr int G = CQ / cqn;                    // tile-alternating groups
     const int egroup = cq / cqn, cqp = cq - egroup * cqn;
@@ -1030,7 +1032,7 @@ igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
     for (int tile = blockIdx.x + egroup * (int)gridDim.x; tile < num_tiles; tile += G * (int)gridDim.x, lt += G) {
       PL_ETRACE(0);
       const int tn = tile % p.n_tiles, tm = tile / p.n_tiles;
-      long long row = (long long)tm * kBM + arow;  // output pixel index (generic epilogue)
+      long long row = (long long)(kPair ? 2 * tm : tm) * kBM + arow;  // output pixel index (generic epilogue)
       int himg = 0, hp0 = 0;
       if (halo) {
         himg = (int)fdiv((uint32_t)tm, p.dBands);
@@ -1062,15 +1064,15 @@ igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
       const bool skip_epi = (PL_DBG_FLAGS_V & 1) != 0;
       if (cqp < units && !skip_epi) tmem_ld_32x32b_x16(t_addr + (uint32_t)(cqp * 16), accb[0]);
 #pragma unroll
-      for (int i = 0; i < 32 / CQ; ++i) {  // 16 / CQ slots per 128-row block, two blocks in a pair
+      for (int i = 0; i < kSlots; ++i) {
         const int u = cqp + cqn * i;
         if (u < units && !skip_epi) {  // warp-uniform
           tmem_ld_wait();
-          if (i < 32 / CQ - 1 && u + cqn < units)
+          if (i < kSlots - 1 && u + cqn < units)
             tmem_ld_32x32b_x16(t_addr + (uint32_t)((u + cqn) * 16), accb[(i + 1) & 1]);
           uint32_t(&acc)[16] = accb[i & 1];
           const uint32_t colt = (uint32_t)(u * 16);                       // TMEM column of the unit
-          const uint32_t sub = (p.mpair && colt >= (uint32_t)p.BN) ? 1u : 0u;  // 128-row block of a pair
+          const uint32_t sub = (kPair && colt >= (uint32_t)p.BN) ? 1u : 0u;  // 128-row block of a pair
           const uint32_t col = colt - sub * (uint32_t)p.BN;              // output column inside the tile
           const uint32_t sbase = sub * tile_bytes;
           if (kFast && !rvalid) {
@@ -1096,8 +1098,8 @@ igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
                 w[q4] = quad_i8_signed(acc + 4 * q4, sc, bi);
             }
             st_shared_v4(out_base + sbase + soff, w[0], w[1], w[2], w[3]);
-          } else if (row < p.M && n0 + (int)col < p.Nout) {
-            store_group16(p, acc, row, n0 + (int)col, &s_scale[sb0 + col], &s_bias[sb0 + col]);
+          } else if (row + (long long)(sub * kBM) < p.M && n0 + (int)col < p.Nout) {
+            store_group16(p, acc, row + (long long)(sub * kBM), n0 + (int)col, &s_scale[sb0 + col], &s_bias[sb0 + col]);
           }
         }
       }
@@ -1134,8 +1136,16 @@ igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
       PL_ETRACE(6);
     }
     };  // epilogue_loop
-    if (p.epi_groups > 1) epilogue_loop(std::integral_constant<int, 1>{});
-    else epilogue_loop(std::integral_constant<int, CQ>{});
+    bool pair_done = false;
+    if constexpr (TR == 0 && (EPI == EPI_I8_RELU || EPI == EPI_I8_SIGNED)) {
+      if (p.mpair) {
+        epilogue_loop(std::integral_constant<int, CQ>{}, std::true_type{});
+        pair_done = true;
+      }
+    }
+    if (pair_done) {
+    } else if (p.epi_groups > 1) epilogue_loop(std::integral_constant<int, 1>{}, std::false_type{});
+    else epilogue_loop(std::integral_constant<int, CQ>{}, std::false_type{});
   }
 
   tc_fence_before();
@@ -1431,6 +1441,8 @@ int launch_igemm(const CUtensorMap& ta, const CUtensorMap& tb, IgemmParams& p, p
       epi = EPI_I8_SIGNED;
     }
   }
+  // (tile pairs storing straight from registers through the generic epilogue, to trade the 64 KB of staging
+  // for two more mainloop stages, measured 2.5x slower at 4096^3: the exposed epilogue dominates)
   // int8 fast paths leave through swizzled smem panels + TMA stores (and take the
   // residual in through TMA loads): vec_ok already guarantees the 16-byte rules
   CUtensorMap ty{}, tr{};
@@ -1945,10 +1957,12 @@ extern "C" int pl_s2d_conv2d_i8(const int8_t* x_s2d, const int8_t* w_s2d, void* 
 }
 
 // long-K GEMM: switch the launch to 256 x 256 tile pairs (IgemmParams::mpair) when it qualifies
-static void maybe_enable_mpair(IgemmParams& p, const pl_epilogue* e, int K) {
+static void maybe_enable_mpair(IgemmParams& p, const pl_epilogue* e, int K, bool peers) {
+  // pairs leave through the staged int8 epilogues + TMA stores only
   const bool fast = e->out_dtype == PL_OUT_INT8 && e->round_mode == PL_ROUND_ARM && p.vec_ok && e->scale &&
                     !e->residual && tma_epilogue_enabled() &&
                     (e->act == PL_ACT_NONE || e->act == PL_ACT_RELU || (e->act == PL_ACT_RELU6 && e->act_arg > 0.f));
+  (void)peers;
   if (!fast || p.mode != 0 || p.BN != 256 || p.m_tiles < 2 || env_int("PL_NO_MPAIR", 0)) return;
   if (!env_int("PL_MPAIR_FORCE", 0)) {
     // the pair has a single accumulator stage (its epilogue is exposed), so K must be long enough
@@ -1990,7 +2004,7 @@ extern "C" int pl_gemm_i8_peers(const int8_t* A, int lda, const int8_t* Bt, int 
   p.mode = 0;
   rc = common_setup(p, M, N, C, ldc, e, K, 1);
   if (rc) return rc;
-  maybe_enable_mpair(p, e, K);
+  maybe_enable_mpair(p, e, K, n_peers > 0);
   CUtensorMap ta, tb;
   rc = encode_2d(&ta, A, (uint64_t)K, (uint64_t)M, (uint64_t)lda, p.BK, kBM << p.mpair);
   if (rc) return rc;
@@ -2029,7 +2043,7 @@ extern "C" int pl_gemm_i8(const int8_t* A, int lda, const int8_t* Bt, int ldb, v
   p.mode = 0;
   rc = common_setup(p, M, N, C, ldc, e, K, 1);
   if (rc) return rc;
-  maybe_enable_mpair(p, e, K);
+  maybe_enable_mpair(p, e, K, false);
   CUtensorMap ta, tb;
   rc = encode_2d(&ta, A, (uint64_t)K, (uint64_t)M, (uint64_t)lda, p.BK, kBM << p.mpair);
   if (rc) return rc;

@@ -7,7 +7,7 @@ echo "== pair mode"; timeout 600 python tools/gemm_sweep.py $S 2>&1 | grep '"int
 import sys,json
 for l in sys.stdin:
     d=json.loads(l); print({k:d[k] for k in d if k in ('shape','ms_gemm','tops_gemm','frac_mma_peak')})"
-echo "== single tiles"; PL_NO_MPAIR=1 timeout 600 python tools/gemm_sweep.py $S 2>&1 | grep '"int8"' | python -c "
+echo "== staged pair"; PL_MPAIR_STAGED=1 timeout 600 python tools/gemm_sweep.py $S 2>&1 | grep '"int8"' | python -c "
 import sys,json
 for l in sys.stdin:
     d=json.loads(l); print({k:d[k] for k in d if k in ('shape','ms_gemm','tops_gemm','frac_mma_peak')})"
