@@ -217,6 +217,26 @@ int pl_add_i8(const int8_t* a, const int8_t* b, void* y, int64_t n, float sa,
               float sb, int act, float act_arg, int out_dtype, int round_mode,
               pl_stream_t stream);
 
+/* ---- channel movement between int8 NHWC ops ---------------
+ * Pure byte moves (the reference's NCHW memcpy loops become per-pixel moves), so a
+ * ShuffleNet-style network stays int8-NHWC-resident between convs.  `pixels` = N*H*W,
+ * every pitch in elements.  Chunks of 16 / 4 / 1 bytes are picked from the alignment of
+ * pointers, pitches and channel boundaries.  At most 8 parts.
+ *   pl_concat_i8_nhwc           lite/backends/arm/math/concat.h:29-60 (axis = channels)
+ *   pl_split_i8_nhwc            lite/backends/arm/math/split.cc:54-83
+ *   pl_shuffle_channel_i8_nhwc  lite/backends/arm/math/shuffle_channel.cc:24-76:
+ *                               out[j * group + i] = in[i * (C / group) + j]; x != y
+ *   pl_relu_i8                  lite/kernels/cuda/relu_compute.cu:23-33 on the integers,
+ *                               y = min(max(x, 0), hi); hi = 127 is plain relu, a smaller
+ *                               hi is relu6 at the caller's quantised 6 / scale */
+int pl_concat_i8_nhwc(int n_in, const int8_t* const* xs, const int* cs, const int* ldxs,
+                      int8_t* y, int ldy, int64_t pixels, pl_stream_t stream);
+int pl_split_i8_nhwc(const int8_t* x, int ldx, int n_out, int8_t* const* ys, const int* cs,
+                     const int* ldys, int64_t pixels, pl_stream_t stream);
+int pl_shuffle_channel_i8_nhwc(const int8_t* x, int ldx, int8_t* y, int ldy, int C, int group,
+                               int64_t pixels, pl_stream_t stream);
+int pl_relu_i8(const int8_t* x, int8_t* y, int64_t n, int hi, pl_stream_t stream);
+
 /* ---- introspection ---------------------------------------------------------- */
 /* number of kernels this library has launched in this process (bench.py's
  * gpu_launches claim) */

@@ -22,6 +22,81 @@ int orc_num_threads(void) {
 #endif
 }
 
+/*
+ * concat along the channel axis of NCHW tensors: lite/backends/arm/math/concat.h:29-60
+ * (concat_func, axis = 1): per input, per image, one memcpy of C_k * H * W elements
+ * to the running channel offset.  inner_bytes = H * W * sizeof(T).
+ */
+int orc_concat_nchw(int n_in, const void* const* xs, const int* cs, void* y,
+                    int N, int64_t inner_bytes) {
+  int64_t ctot = 0, off = 0;
+  for (int k = 0; k < n_in; ++k) ctot += cs[k];
+  for (int k = 0; k < n_in; ++k) {
+    const char* src = (const char*)xs[k];
+    char* dst = (char*)y + off * inner_bytes;
+    const int64_t in_sum = (int64_t)cs[k] * inner_bytes;
+    for (int n = 0; n < N; ++n) {
+      memcpy(dst, src, (size_t)in_sum);
+      dst += ctot * inner_bytes;
+      src += in_sum;
+    }
+    off += cs[k];
+  }
+  return 0;
+}
+
+/* split along the channel axis: lite/backends/arm/math/split.cc:54-83 (axis = 1) */
+int orc_split_nchw(const void* x, int n_out, void* const* ys, const int* cs,
+                   int N, int64_t inner_bytes) {
+  int64_t ctot = 0, off = 0;
+  for (int k = 0; k < n_out; ++k) ctot += cs[k];
+  for (int k = 0; k < n_out; ++k) {
+    const char* src = (const char*)x + off * inner_bytes;
+    char* dst = (char*)ys[k];
+    const int64_t out_after = (int64_t)cs[k] * inner_bytes;
+    for (int n = 0; n < N; ++n) {
+      memcpy(dst, src, (size_t)out_after);
+      src += ctot * inner_bytes;
+      dst += out_after;
+    }
+    off += cs[k];
+  }
+  return 0;
+}
+
+/*
+ * shuffle_channel: lite/backends/arm/math/shuffle_channel.cc:24-76 and the baseline of
+ * lite/tests/kernels/shuffle_channel_compute_test.cc:38-66:
+ *   out channel (j * group + i) = in channel (i * (C / group) + j)
+ */
+int orc_shuffle_channel_nchw(const void* x, void* y, int group, int N, int C,
+                             int64_t spatial_bytes) {
+  if (group <= 0 || C % group) return -1;
+  const int group_col = C / group;
+  for (int n = 0; n < N; ++n) {
+    const char* in = (const char*)x + (int64_t)n * C * spatial_bytes;
+    char* out = (char*)y + (int64_t)n * C * spatial_bytes;
+    for (int i = 0; i < group; ++i)
+      for (int j = 0; j < group_col; ++j)
+        memcpy(out + (int64_t)(j * group + i) * spatial_bytes,
+               in + (int64_t)(i * group_col + j) * spatial_bytes, (size_t)spatial_bytes);
+  }
+  return 0;
+}
+
+/*
+ * relu on int8 with a symmetric scale: max(x, 0) commutes with the quantiser, so it is
+ * lite/kernels/cuda/relu_compute.cu:23-33 (ReluKernel: x >= 0 ? x : 0) on the integers;
+ * hi < 127 clips like relu6 at the caller's quantised 6 / scale.
+ */
+int orc_relu_i8(const int8_t* x, int8_t* y, int64_t n, int hi) {
+  for (int64_t i = 0; i < n; ++i) {
+    int v = x[i] > 0 ? x[i] : 0;
+    y[i] = (int8_t)(v > hi ? hi : v);
+  }
+  return 0;
+}
+
 /* lite/operators/conv_op.cc:42-53 ConvOutputSize */
 int orc_conv_out_size(int in, int k, int dil, int pad0, int pad1, int stride) {
   const int dkernel = dil * (k - 1) + 1;

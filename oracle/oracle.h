@@ -110,6 +110,16 @@ int orc_pool2d_i8_nhwc(const int8_t* x, void* y, int N, int H, int W, int C,
 int orc_add_i8(const int8_t* a, const int8_t* b, void* y, int64_t n, float sa,
                float sb, int act, float act_arg, int out_dtype, int round_mode);
 
+/* ---- channel movement between int8 ops, NCHW like the reference:
+ * pure byte moves, so the int8 versions are the reference's memcpy loops on 1-byte elements */
+int orc_concat_nchw(int n_in, const void* const* xs, const int* cs, void* y,
+                    int N, int64_t inner_bytes);
+int orc_split_nchw(const void* x, int n_out, void* const* ys, const int* cs,
+                   int N, int64_t inner_bytes);
+int orc_shuffle_channel_nchw(const void* x, void* y, int group, int N, int C,
+                             int64_t spatial_bytes);
+int orc_relu_i8(const int8_t* x, int8_t* y, int64_t n, int hi);
+
 int orc_conv_out_size(int in, int k, int dil, int pad0, int pad1, int stride);
 int orc_num_threads(void);
 

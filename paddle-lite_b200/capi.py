@@ -389,6 +389,74 @@ def add(a, b, sa, sb, act=ACT_NONE, act_arg=0.0, out=OUT_INT8, rnd=ROUND_ARM, y=
     return y
 
 
+def _view(t, Cc):
+    """(pointer, channels, pixel pitch) of an NHWC tensor or a channel slice of one (a
+    slice t[..., a:b] is a pointer offset + the wide pitch)"""
+    assert t.stride(-1) == 1 and t.dim() >= 2
+    ld = t.stride(-2)
+    for d in range(t.dim() - 2):  # the pixels must be evenly spaced
+        assert t.stride(d) == t.stride(d + 1) * t.shape[d + 1], "pixel dims must be dense"
+    return t.data_ptr(), (t.shape[-1] if Cc is None else Cc), ld
+
+
+def _pixels(t):
+    n = 1
+    for d in t.shape[:-1]:
+        n *= d
+    return n
+
+
+def concat(xs, y=None):
+    """int8 NHWC concat along channels (lite/backends/arm/math/concat.h:29-60, axis = C)"""
+    views = [_view(x, None) for x in xs]
+    ctot = sum(v[1] for v in views)
+    if y is None:
+        y = torch.empty(tuple(xs[0].shape[:-1]) + (ctot,), dtype=torch.int8, device=xs[0].device)
+    yp, _, ldy = _view(y, None)
+    n = len(xs)
+    ptrs = (C.c_void_p * n)(*[v[0] for v in views])
+    cs = (C.c_int * n)(*[v[1] for v in views])
+    lds = (C.c_int * n)(*[v[2] for v in views])
+    _check(lib().pl_concat_i8_nhwc(n, ptrs, cs, lds, C.c_void_p(yp), ldy, C.c_int64(_pixels(xs[0])), _stream()),
+           "pl_concat_i8_nhwc")
+    return y
+
+
+def split(x, sections, ys=None):
+    """int8 NHWC split along channels (lite/backends/arm/math/split.cc:54-83)"""
+    xp, _, ldx = _view(x, None)
+    if ys is None:
+        ys = [torch.empty(tuple(x.shape[:-1]) + (c,), dtype=torch.int8, device=x.device) for c in sections]
+    views = [_view(t, None) for t in ys]
+    n = len(ys)
+    ptrs = (C.c_void_p * n)(*[v[0] for v in views])
+    cs = (C.c_int * n)(*sections)
+    lds = (C.c_int * n)(*[v[2] for v in views])
+    _check(lib().pl_split_i8_nhwc(C.c_void_p(xp), ldx, n, ptrs, cs, lds, C.c_int64(_pixels(x)), _stream()),
+           "pl_split_i8_nhwc")
+    return ys
+
+
+def shuffle_channel(x, group, y=None):
+    """int8 NHWC shuffle_channel (lite/backends/arm/math/shuffle_channel.cc:24-76)"""
+    xp, Cc, ldx = _view(x, None)
+    if y is None:
+        y = torch.empty(tuple(x.shape), dtype=torch.int8, device=x.device)
+    yp, _, ldy = _view(y, None)
+    _check(lib().pl_shuffle_channel_i8_nhwc(C.c_void_p(xp), ldx, C.c_void_p(yp), ldy, Cc, group,
+                                            C.c_int64(_pixels(x)), _stream()), "pl_shuffle_channel_i8_nhwc")
+    return y
+
+
+def relu_i8(x, hi=127, y=None):
+    """relu / quantised relu6 on a dense int8 tensor"""
+    assert x.is_contiguous()
+    if y is None:
+        y = torch.empty_like(x)
+    _check(lib().pl_relu_i8(_ptr(x), _ptr(y), C.c_int64(x.numel()), hi, _stream()), "pl_relu_i8")
+    return y
+
+
 def i8_mma_peak(ctas, iters, bn=256):
     out = torch.zeros(4, dtype=torch.int32, device="cuda")
     _check(lib().pl_i8_mma_peak(ctas, iters, bn, _ptr(out), _stream()), "pl_i8_mma_peak")

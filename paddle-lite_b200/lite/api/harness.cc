@@ -317,4 +317,58 @@ int plk_run_add(void* x, void* y, void* out, float x_scale, float y_scale, float
   PLK_CATCH
 }
 
+int plk_run_concat(void* const* xs, int n, void* out, int axis) {
+  PLK_TRY
+  ops::ConcatParam p;
+  for (int i = 0; i < n; ++i) p.x.push_back(T(xs[i]));
+  p.output = T(out);
+  p.axis = axis;
+  auto k = CreateKernel("concat", TARGET(kCUDA), PRECISION(kInt8), DATALAYOUT(kNHWC), PRECISION(kInt8));
+  k->SetParam(p);
+  LaunchAndSync(k.get(), 1);
+  PLK_CATCH
+}
+
+int plk_run_split(void* x, void* const* outs, int n, int axis, int num, const int* sections, int n_sections) {
+  PLK_TRY
+  ops::SplitParam p;
+  p.x = T(x);
+  for (int i = 0; i < n; ++i) p.output.push_back(T(outs[i]));
+  p.axis = axis;
+  p.num = num;
+  p.sections.assign(sections, sections + n_sections);
+  auto k = CreateKernel("split", TARGET(kCUDA), PRECISION(kInt8), DATALAYOUT(kNHWC), PRECISION(kInt8));
+  k->SetParam(p);
+  LaunchAndSync(k.get(), 1);
+  PLK_CATCH
+}
+
+int plk_run_shuffle_channel(void* x, void* out, int group) {
+  PLK_TRY
+  ops::ShuffleChannelParam p;
+  p.X = T(x);
+  p.Out = T(out);
+  p.group = group;
+  auto k = CreateKernel("shuffle_channel", TARGET(kCUDA), PRECISION(kInt8), DATALAYOUT(kNHWC), PRECISION(kInt8));
+  k->SetParam(p);
+  LaunchAndSync(k.get(), 1);
+  PLK_CATCH
+}
+
+int plk_run_relu(void* x, void* out, int relu6, float clip, float input_scale) {
+  PLK_TRY
+  ops::ActivationParam p;
+  p.X = T(x);
+  p.Out = T(out);
+  p.has_active = true;
+  p.active_type = relu6 ? ActivationType::kRelu6 : ActivationType::kRelu;
+  p.Relu_clipped_coef = clip;
+  p.enable_int8 = true;
+  p.input_scale = p.output_scale = input_scale;
+  auto k = CreateKernel(relu6 ? "relu6" : "relu", TARGET(kCUDA), PRECISION(kInt8), DATALAYOUT(kNHWC), PRECISION(kInt8));
+  k->SetParam(p);
+  LaunchAndSync(k.get(), 1);
+  PLK_CATCH
+}
+
 }  // extern "C"

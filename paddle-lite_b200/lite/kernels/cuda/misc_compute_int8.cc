@@ -158,6 +158,102 @@ class ElementwiseAddInt8 : public KernelLite<TARGET(kCUDA), PRECISION(kInt8), DA
   }
 };
 
+// ---- channel movement between int8 NHWC ops (no calib / layout round trip inside a network) ----
+// The op descs keep the model's NCHW axis numbering: channels are axis 1 (or -3); the tensors
+// themselves are NHWC, so the reference's per-image memcpy loops (lite/backends/arm/math/concat.h:29-60,
+// split.cc:54-83, shuffle_channel.cc:24-76) become per-pixel byte moves in the library.
+inline bool IsChannelAxis(int axis) { return axis == 1 || axis == -3; }
+
+class ConcatComputeInt8 : public KernelLite<TARGET(kCUDA), PRECISION(kInt8), DATALAYOUT(kNHWC)> {
+ public:
+  using param_t = operators::ConcatParam;
+  void Run() override {
+    auto& param = this->Param<param_t>();
+    CHECK(IsChannelAxis(param.axis)) << "int8 NHWC concat: channel axis only, got axis " << param.axis;
+    CHECK(!param.x.empty() && param.x.size() <= 8u) << "int8 NHWC concat takes 1..8 inputs";
+    const auto& d0 = param.x[0]->dims();
+    CHECK_EQ(d0.size(), 4u);
+    std::vector<const int8_t*> ptrs;
+    std::vector<int> cs;
+    int64_t ctot = 0;
+    for (auto* t : param.x) {
+      const auto& d = t->dims();
+      CHECK(d.size() == 4u && d[0] == d0[0] && d[1] == d0[1] && d[2] == d0[2]) << "concat inputs differ outside the channel axis";
+      ptrs.push_back(t->template data<int8_t>());
+      cs.push_back(static_cast<int>(d[3]));
+      ctot += d[3];
+    }
+    param.output->Resize(DDim({d0[0], d0[1], d0[2], ctot}));
+    auto* y = param.output->template mutable_data<int8_t>(TARGET(kCUDA));
+    PL_CALL(pl_concat_i8_nhwc(static_cast<int>(ptrs.size()), ptrs.data(), cs.data(), cs.data(), y, static_cast<int>(ctot),
+                              d0[0] * d0[1] * d0[2], StreamOf(ctx_.get())));
+  }
+};
+
+class SplitComputeInt8 : public KernelLite<TARGET(kCUDA), PRECISION(kInt8), DATALAYOUT(kNHWC)> {
+ public:
+  using param_t = operators::SplitParam;
+  void Run() override {
+    auto& param = this->Param<param_t>();
+    CHECK(IsChannelAxis(param.axis)) << "int8 NHWC split: channel axis only, got axis " << param.axis;
+    const auto& d = param.x->dims();
+    CHECK_EQ(d.size(), 4u);
+    const int C = static_cast<int>(d[3]);
+    std::vector<int> cs = param.sections;
+    if (cs.empty()) {  // `num` equal parts (lite/operators/split_op.cc InferShape)
+      CHECK(param.num > 0 && C % param.num == 0) << "split: num " << param.num << " does not divide C " << C;
+      cs.assign(param.num, C / param.num);
+    }
+    CHECK(cs.size() == param.output.size() && cs.size() <= 8u) << "split: sections vs outputs";
+    int sum = 0;
+    std::vector<int8_t*> ptrs;
+    for (size_t k = 0; k < cs.size(); ++k) {
+      sum += cs[k];
+      param.output[k]->Resize(DDim({d[0], d[1], d[2], cs[k]}));
+      ptrs.push_back(param.output[k]->template mutable_data<int8_t>(TARGET(kCUDA)));
+    }
+    CHECK_EQ(sum, C);
+    PL_CALL(pl_split_i8_nhwc(param.x->template data<int8_t>(), C, static_cast<int>(cs.size()), ptrs.data(), cs.data(),
+                             cs.data(), d[0] * d[1] * d[2], StreamOf(ctx_.get())));
+  }
+};
+
+class ShuffleChannelComputeInt8 : public KernelLite<TARGET(kCUDA), PRECISION(kInt8), DATALAYOUT(kNHWC)> {
+ public:
+  using param_t = operators::ShuffleChannelParam;
+  void Run() override {
+    auto& param = this->Param<param_t>();
+    const auto& d = param.X->dims();
+    CHECK_EQ(d.size(), 4u);
+    const int C = static_cast<int>(d[3]);
+    CHECK(param.group > 0 && C % param.group == 0) << "shuffle_channel: group " << param.group << " vs C " << C;
+    param.Out->Resize(d);
+    PL_CALL(pl_shuffle_channel_i8_nhwc(param.X->template data<int8_t>(), C,
+                                       param.Out->template mutable_data<int8_t>(TARGET(kCUDA)), C, C, param.group,
+                                       d[0] * d[1] * d[2], StreamOf(ctx_.get())));
+  }
+};
+
+// relu / relu6 on int8 with the input's scale kept (max(x, 0) commutes with a symmetric quantiser;
+// relu6 clips at round(6 / scale)): lite/kernels/cuda/relu_compute.cu:23-33 on the integers
+class ReluComputeInt8 : public KernelLite<TARGET(kCUDA), PRECISION(kInt8), DATALAYOUT(kNHWC)> {
+ public:
+  using param_t = operators::ActivationParam;
+  void Run() override {
+    auto& param = this->Param<param_t>();
+    int hi = 127;
+    if (param.active_type == lite_api::ActivationType::kRelu6) {
+      const float q = param.Relu_clipped_coef / param.input_scale;
+      hi = q >= 127.f ? 127 : static_cast<int>(q + 0.5f);
+    } else {
+      CHECK(param.active_type == lite_api::ActivationType::kRelu) << "int8 activation: relu / relu6 only";
+    }
+    param.Out->Resize(param.X->dims());
+    PL_CALL(pl_relu_i8(param.X->template data<int8_t>(), param.Out->template mutable_data<int8_t>(TARGET(kCUDA)),
+                       param.X->numel(), hi, StreamOf(ctx_.get())));
+  }
+};
+
 }  // namespace cuda
 }  // namespace kernels
 }  // namespace lite
@@ -236,3 +332,25 @@ REGISTER_LITE_KERNEL(elementwise_add, kCUDA, kInt8, kNHWC, AddI8F32, fp32_out)
     .BindInput("Y", {LiteType::GetTensorTy(TARGET(kCUDA), PRECISION(kInt8), DATALAYOUT(kNHWC))})
     .BindOutput("Out", {LiteType::GetTensorTy(TARGET(kCUDA), PRECISION(kFloat), DATALAYOUT(kNHWC))})
     .Finalize();
+#define PL_I8_NHWC LiteType::GetTensorTy(TARGET(kCUDA), PRECISION(kInt8), DATALAYOUT(kNHWC))
+REGISTER_LITE_KERNEL(concat, kCUDA, kInt8, kNHWC, plk::ConcatComputeInt8, int8_nhwc)
+    .BindInput("X", {PL_I8_NHWC})
+    .BindOutput("Out", {PL_I8_NHWC})
+    .Finalize();
+REGISTER_LITE_KERNEL(split, kCUDA, kInt8, kNHWC, plk::SplitComputeInt8, int8_nhwc)
+    .BindInput("X", {PL_I8_NHWC})
+    .BindOutput("Out", {PL_I8_NHWC})
+    .Finalize();
+REGISTER_LITE_KERNEL(shuffle_channel, kCUDA, kInt8, kNHWC, plk::ShuffleChannelComputeInt8, int8_nhwc)
+    .BindInput("X", {PL_I8_NHWC})
+    .BindOutput("Out", {PL_I8_NHWC})
+    .Finalize();
+REGISTER_LITE_KERNEL(relu, kCUDA, kInt8, kNHWC, plk::ReluComputeInt8, int8_nhwc)
+    .BindInput("X", {PL_I8_NHWC})
+    .BindOutput("Out", {PL_I8_NHWC})
+    .Finalize();
+REGISTER_LITE_KERNEL(relu6, kCUDA, kInt8, kNHWC, plk::ReluComputeInt8, int8_nhwc)
+    .BindInput("X", {PL_I8_NHWC})
+    .BindOutput("Out", {PL_I8_NHWC})
+    .Finalize();
+#undef PL_I8_NHWC

@@ -33,6 +33,9 @@ struct ActivationParam : ParamBase {
   bool has_active{false};
   float Leaky_relu_alpha{0};
   float Relu_clipped_coef{6};
+  // not in the reference's ActivationParam: the int8 relu6 kernel needs the scale of X (= scale of
+  // Out) to place the clip; the precision-cast pass extension fills it in
+  WITH_INT8_CONFIG
 };
 
 struct ConvParam : ParamBase {
@@ -126,6 +129,27 @@ struct ElementwiseParam : ParamBase {
   float x_input_scale{1.0};
   float y_input_scale{1.0};
   std::string act_type{""};  // fusion_elementwise_add_activation
+};
+
+// lite/operators/op_params.h:369-389 (ConcatParam), 590-612 (SplitParam), 258-263 (ShuffleChannelParam)
+struct ConcatParam : ParamBase {
+  std::vector<lite::Tensor*> x{};
+  lite::Tensor* output{};
+  int axis{0};  // the model's (NCHW) axis: 1 = channels
+};
+
+struct SplitParam : ParamBase {
+  lite::Tensor* x{};
+  std::vector<lite::Tensor*> output{};
+  int axis{-1};
+  int num{0};
+  std::vector<int> sections;
+};
+
+struct ShuffleChannelParam : ParamBase {
+  const lite::Tensor* X{};
+  lite::Tensor* Out{};
+  int group{1};
 };
 
 }  // namespace operators

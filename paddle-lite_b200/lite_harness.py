@@ -193,3 +193,33 @@ def run_add(x, y, x_scale, y_scale, out_scale, act="", out_int8=True):
     _ck(lib().plk_run_add(tx.h, ty.h, out.h, C.c_float(x_scale), C.c_float(y_scale), C.c_float(out_scale),
                           act.encode(), int(out_int8)))
     return out.numpy()
+
+
+def _ha(tensors):
+    return (C.c_void_p * len(tensors))(*[t.h for t in tensors])
+
+
+def run_concat(xs, axis=1):
+    """xs: int8 NHWC arrays; axis is the model's (NCHW) axis, 1 = channels"""
+    ts, out = [Tensor(x) for x in xs], Tensor()
+    _ck(lib().plk_run_concat(_ha(ts), len(ts), out.h, axis))
+    return out.numpy()
+
+
+def run_split(x, axis=1, num=0, sections=()):
+    n = len(sections) if sections else num
+    tx, outs = Tensor(x), [Tensor() for _ in range(n)]
+    _ck(lib().plk_run_split(tx.h, _ha(outs), n, axis, num, _ia(list(sections) or [0]), len(sections)))
+    return [o.numpy() for o in outs]
+
+
+def run_shuffle_channel(x, group):
+    tx, out = Tensor(x), Tensor()
+    _ck(lib().plk_run_shuffle_channel(tx.h, out.h, group))
+    return out.numpy()
+
+
+def run_relu(x, relu6=False, clip=6.0, input_scale=1.0):
+    tx, out = Tensor(x), Tensor()
+    _ck(lib().plk_run_relu(tx.h, out.h, int(relu6), C.c_float(clip), C.c_float(input_scale)))
+    return out.numpy()

@@ -190,6 +190,48 @@ def add(a, b, sa, sb, act=ACT_NONE, act_arg=0.0, out=OUT_INT8, rnd=ROUND_ARM):
     return y
 
 
+def _ptr_array(arrs):
+    return (C.c_void_p * len(arrs))(*[a.ctypes.data for a in arrs])
+
+
+def concat_nchw(xs):
+    """concat along axis 1 of NCHW arrays (any dtype)"""
+    xs = [np.ascontiguousarray(x) for x in xs]
+    N = xs[0].shape[0]
+    inner = int(np.prod(xs[0].shape[2:])) * xs[0].itemsize
+    cs = (C.c_int * len(xs))(*[x.shape[1] for x in xs])
+    y = np.empty((N, sum(x.shape[1] for x in xs)) + xs[0].shape[2:], xs[0].dtype)
+    lib().orc_concat_nchw(len(xs), _ptr_array(xs), cs, _p(y), N, C.c_int64(inner))
+    return y
+
+
+def split_nchw(x, sections):
+    x = np.ascontiguousarray(x)
+    N = x.shape[0]
+    inner = int(np.prod(x.shape[2:])) * x.itemsize
+    ys = [np.empty((N, c) + x.shape[2:], x.dtype) for c in sections]
+    cs = (C.c_int * len(ys))(*sections)
+    lib().orc_split_nchw(_p(x), len(ys), _ptr_array(ys), cs, N, C.c_int64(inner))
+    return ys
+
+
+def shuffle_channel_nchw(x, group):
+    x = np.ascontiguousarray(x)
+    N, Cc = x.shape[:2]
+    y = np.empty_like(x)
+    rc = lib().orc_shuffle_channel_nchw(_p(x), _p(y), group, N, Cc,
+                                        C.c_int64(int(np.prod(x.shape[2:])) * x.itemsize))
+    assert rc == 0
+    return y
+
+
+def relu_i8(x, hi=127):
+    x = np.ascontiguousarray(x, np.int8)
+    y = np.empty_like(x)
+    lib().orc_relu_i8(_p(x), _p(y), C.c_int64(x.size), hi)
+    return y
+
+
 # ---- the reference's own naive math (oracle/_ref) ---------------------------
 def ref_conv_acc_nchw(x_nchw, w_oihw, strides, pads_hw, dil, groups):
     r = ref()

@@ -233,3 +233,47 @@ def test_elementwise_add(lh, act, out_int8):
         np.testing.assert_array_equal(got, want)
     else:
         np.testing.assert_allclose(got, want, rtol=1e-6)
+
+
+# ---- channel movement kernels, through the registry ----------------
+def _nchw(x):
+    return np.ascontiguousarray(np.moveaxis(x, -1, 1))
+
+
+def _nhwc(x):
+    return np.ascontiguousarray(np.moveaxis(x, 1, -1))
+
+
+@pytest.mark.parametrize("cs", [(36, 36), (64, 64), (9, 18, 3)])
+def test_concat_and_split_kernels(lh, cs):
+    rng = np.random.default_rng(sum(cs))
+    xs = [_rand_i8(rng, (2, 12, 12, c), -128, 127) for c in cs]
+    want = _nhwc(orc.concat_nchw([_nchw(x) for x in xs]))
+    got = lh.run_concat(xs, axis=1)
+    np.testing.assert_array_equal(got, want)
+    parts = lh.run_split(want, axis=1, sections=cs)
+    for p, x in zip(parts, xs):
+        np.testing.assert_array_equal(p, x)
+    if len(set(cs)) == 1:  # `num` equal parts
+        for p, x in zip(lh.run_split(want, axis=1, num=len(cs)), xs):
+            np.testing.assert_array_equal(p, x)
+    with pytest.raises(lh.LiteError):
+        lh.run_concat(xs, axis=2)  # only the channel axis keeps NHWC tensors resident
+
+
+@pytest.mark.parametrize("C,group", [(72, 2), (16, 4), (18, 2), (144, 2)])
+def test_shuffle_channel_kernel(lh, C, group):
+    rng = np.random.default_rng(C + group)
+    x = _rand_i8(rng, (2, 12, 12, C), -128, 127)
+    want = _nhwc(orc.shuffle_channel_nchw(_nchw(x), group))
+    np.testing.assert_array_equal(lh.run_shuffle_channel(x, group), want)
+    with pytest.raises(lh.LiteError):
+        lh.run_shuffle_channel(x, 5)
+
+
+def test_relu_kernels(lh):
+    rng = np.random.default_rng(23)
+    x = _rand_i8(rng, (2, 9, 9, 40), -128, 127)
+    np.testing.assert_array_equal(lh.run_relu(x), orc.relu_i8(x))
+    # relu6 on a tensor of scale 0.1: the clip sits at round(6 / 0.1) = 60
+    np.testing.assert_array_equal(lh.run_relu(x, relu6=True, clip=6.0, input_scale=0.1), orc.relu_i8(x, 60))

@@ -160,3 +160,40 @@ def test_fold_scales_rules():
     sf, bf, six = orc.fold_scales(ws[:1], 3, 0.1, 0.4, orc.OUT_FP32, None, orc.ACT_RELU6, 6.0)
     assert np.array_equal(sf, np.full(3, ws[0] * np.float32(0.1), np.float32))
     assert np.array_equal(bf, np.zeros(3, np.float32)) and six == 6.0
+
+
+# ---- channel movement: the oracle's NCHW loops pinned on the baselines the
+# reference's own tests use (lite/tests/kernels/shuffle_channel_compute_test.cc:38-66 is the
+# memcpy permutation below; concat_compute_test.cc / split are plain axis-1 concatenation)
+@pytest.mark.parametrize("shape,group", [((10, 16, 4, 4), 4), ((2, 72, 3, 5), 2), ((1, 12, 2, 2), 3),
+                                         ((1, 6, 1, 1), 1), ((1, 6, 1, 1), 6)])
+def test_shuffle_channel_oracle_vs_reference_baseline(shape, group):
+    rng = np.random.default_rng(shape[1] + group)
+    x = rng.integers(-128, 128, shape, dtype=np.int8)
+    N, Cc, H, W = shape
+    want = np.empty_like(x)
+    for n in range(N):  # the reference test's RunBaseline, element for element
+        for i in range(group):
+            for j in range(Cc // group):
+                want[n, j * group + i] = x[n, i * (Cc // group) + j]
+    got = orc.shuffle_channel_nchw(x, group)
+    assert np.array_equal(got, want)
+    assert np.array_equal(got, x.reshape(N, group, Cc // group, H, W).transpose(0, 2, 1, 3, 4).reshape(shape))
+    xf = x.astype(np.float32)  # the reference kernel is fp32: same movement on 4-byte elements
+    assert np.array_equal(orc.shuffle_channel_nchw(xf, group), want.astype(np.float32))
+
+
+@pytest.mark.parametrize("cs", [(2, 3), (64, 64), (9, 18, 3), (5,)])
+def test_concat_split_oracle_vs_numpy(cs):
+    rng = np.random.default_rng(sum(cs))
+    xs = [rng.integers(-128, 128, (3, c, 4, 5), dtype=np.int8) for c in cs]
+    y = orc.concat_nchw(xs)
+    assert np.array_equal(y, np.concatenate(xs, axis=1))
+    for p, x in zip(orc.split_nchw(y, list(cs)), xs):
+        assert np.array_equal(p, x)
+
+
+def test_relu_i8_oracle():
+    x = np.arange(-128, 128, dtype=np.int8)
+    assert np.array_equal(orc.relu_i8(x), np.maximum(x, 0))
+    assert np.array_equal(orc.relu_i8(x, 47), np.clip(x, 0, 47))

@@ -22,6 +22,8 @@ def test_registered_kernels(lh):
         assert f"{op}/fp32_to_int8/cuda/int8_t/NCHW" in ks and f"{op}/int8_to_fp32/cuda/int8_t/NCHW" in ks
     for op in ("layout", "layout_once"):
         assert f"{op}/int8_nchw2nhwc/cuda/int8_t/NCHW" in ks and f"{op}/nhwc2nchw/cuda/float/NCHW" in ks
+    for op in ("concat", "split", "shuffle_channel", "relu", "relu6"):
+        assert f"{op}/int8_nhwc/cuda/int8_t/NHWC" in ks
     for op in ("io_copy", "io_copy_once"):
         assert f"{op}/host_to_device/cuda/any/any" in ks and f"{op}/device_to_host/cuda/any/any" in ks
 
