@@ -9,6 +9,7 @@
 #include <vector>
 
 #include "lite/core/mir/static_kernel_pick.h"
+#include "lite/core/mir/type_cast_plan.h"
 #include "lite/core/op_registry.h"
 #include "lite/kernels/cuda/int8_common.h"
 
@@ -314,6 +315,25 @@ int plk_run_add(void* x, void* y, void* out, float x_scale, float y_scale, float
                         out_int8 ? PRECISION(kInt8) : PRECISION(kFloat));
   k->SetParam(p);
   LaunchAndSync(k.get(), 1);
+  PLK_CATCH
+}
+
+// kernel pick + io_copy / calib / layout insertion for a small graph (text form of
+// mir::ParseMiniGraph); `extension` = transparent ops inherit int8,
+// `reference_decls` adds the reference's own fp32 registrations as fall-backs
+int plk_plan_types(const char* graph_text, int extension, int reference_decls, char* out, int cap) {
+  PLK_TRY
+  const mir::MiniGraph g = mir::ParseMiniGraph(graph_text ? graph_text : "");
+  std::vector<mir::KernelDeclLite> decls = mir::RegisteredDecls();
+  if (reference_decls)
+    for (const auto& d : mir::ReferenceFp32Decls()) decls.push_back(d);
+  const std::vector<Place> places = {Place(TARGET(kCUDA), PRECISION(kInt8), DATALAYOUT(kNHWC)),
+                                     Place(TARGET(kCUDA), PRECISION(kInt8), DATALAYOUT(kNCHW)),
+                                     Place(TARGET(kCUDA), PRECISION(kFloat), DATALAYOUT(kNCHW)),
+                                     Place(TARGET(kHost), PRECISION(kFloat), DATALAYOUT(kNCHW))};
+  const std::string text = mir::PlanToText(g, mir::PlanTypes(g, places, decls, extension != 0));
+  if (static_cast<int>(text.size()) + 1 > cap) LITE_FATAL("plan text does not fit") << text.size();
+  std::memcpy(out, text.c_str(), text.size() + 1);
   PLK_CATCH
 }
 

@@ -223,3 +223,22 @@ def run_relu(x, relu6=False, clip=6.0, input_scale=1.0):
     tx, out = Tensor(x), Tensor()
     _ck(lib().plk_run_relu(tx.h, out.h, int(relu6), C.c_float(clip), C.c_float(input_scale)))
     return out.numpy()
+
+
+def plan_types(ops, extension=True, reference_decls=True):
+    """ops: [(type, [inputs], [outputs], enable_int8)] in topological order, "feed" / "fetch" at the
+    boundary.  Returns {"picked": [...], "casts": [(kind, var, consumer, from, to, bytes)], "inside": n,
+    "bytes_per_elem": total} from the miniature type passes (lite/core/mir/type_cast_plan.h)."""
+    text = "\n".join(f"{t};{','.join(i)};{','.join(o)};{int(q)}" for t, i, o, q in ops)
+    buf = C.create_string_buffer(1 << 16)
+    _ck(lib().plk_plan_types(text.encode(), int(extension), int(reference_decls), buf, len(buf)))
+    res = {"picked": [], "casts": [], "inside": 0, "bytes_per_elem": 0}
+    for ln in buf.value.decode().splitlines():
+        f = ln.split()
+        if f[0] == "op":
+            res["picked"].append(f[3])
+        elif f[0] == "cast":
+            res["casts"].append((f[1], f[2], f[4], f[5], f[7], int(f[9])))
+        elif f[0] == "casts":
+            res["inside"], res["bytes_per_elem"] = int(f[3]), int(f[5])
+    return res

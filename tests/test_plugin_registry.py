@@ -46,3 +46,77 @@ def test_errors_surface_like_check_failures(lh):
     import numpy as np
     with pytest.raises(lh.LiteError):
         lh.Tensor(np.zeros((2, 2), np.float64))
+
+
+# ---- miniature type passes (lite/core/mir/type_cast_plan.h) -------------------
+def _shufflenet_unit():
+    """feed -> conv (int8) -> split -> [x1 | x2 -> 1x1 -> dw3x3 -> 1x1] -> concat -> shuffle_channel -> conv -> fetch
+    (the stride-1 unit of humanseg_shfv75's ShuffleNet-v2 backbone)"""
+    return [
+        ("feed", [], ["image"], False),
+        ("conv2d", ["image"], ["c0"], True),
+        ("split", ["c0"], ["x1", "x2"], False),
+        ("conv2d", ["x2"], ["b1"], True),
+        ("depthwise_conv2d", ["b1"], ["b2"], True),
+        ("conv2d", ["b2"], ["b3"], True),
+        ("concat", ["x1", "b3"], ["cat"], False),
+        ("shuffle_channel", ["cat"], ["sh"], False),
+        ("conv2d", ["sh"], ["c1"], True),
+        ("fetch", ["c1"], [], False),
+    ]
+
+
+def test_type_plan_keeps_shufflenet_unit_int8_resident(lh):
+    ops = _shufflenet_unit()
+    ext = lh.plan_types(ops, extension=True)
+    # every op between feed and fetch runs an int8 NHWC kernel of this library
+    assert ext["picked"][1] == "conv2d/int8_out/cuda/int8_t/NHWC"
+    assert ext["picked"][2] == "split/int8_nhwc/cuda/int8_t/NHWC"
+    assert ext["picked"][6] == "concat/int8_nhwc/cuda/int8_t/NHWC"
+    assert ext["picked"][7] == "shuffle_channel/int8_nhwc/cuda/int8_t/NHWC"
+    assert ext["picked"][8] == "conv2d/fp32_out/cuda/int8_t/NHWC"  # its consumer is fetch
+    assert ext["inside"] == 0
+    kinds = [(c[0], c[1]) for c in ext["casts"]]
+    assert kinds == [("io_copy", "image"), ("calib", "image"), ("layout", "image"),
+                     ("io_copy", "c1"), ("layout", "c1")] or \
+        kinds == [("io_copy", "image"), ("calib", "image"), ("layout", "image"), ("io_copy", "c1")]
+
+
+def test_type_plan_without_extension_round_trips(lh):
+    """The reference's behaviour: split / concat / shuffle_channel have no enable_int8, so the convs
+    around them fall to fp32_out and calib / layout / io_copy nodes appear inside the block."""
+    ops = _shufflenet_unit()
+    ref = lh.plan_types(ops, extension=False)
+    assert ref["picked"][2].startswith("split/def/host")          # ARM-only kernel in the reference
+    assert ref["picked"][7].startswith("shuffle_channel/def/host")
+    assert ref["picked"][6] == "concat/def/cuda/float/NCHW"
+    assert ref["picked"][1] == "conv2d/fp32_out/cuda/int8_t/NHWC"  # consumer split is not int8
+    assert ref["inside"] >= 8
+    ext = lh.plan_types(ops, extension=True)
+    assert ref["bytes_per_elem"] - ext["bytes_per_elem"] >= 40     # per-element traffic of the round trips
+
+
+def test_type_plan_resnet_block_and_fp32_tail(lh):
+    ops = [
+        ("feed", [], ["x"], False),
+        ("conv2d", ["x"], ["a"], True),
+        ("conv2d", ["a"], ["b"], True),
+        ("elementwise_add", ["b", "a"], ["s"], True),
+        ("relu", ["s"], ["r"], False),
+        ("pool2d", ["r"], ["p"], True),
+        ("softmax", ["p"], ["y"], False),   # fp32-only tail op
+        ("fetch", ["y"], [], False),
+    ]
+    plan = lh.plan_types(ops, extension=True)
+    assert plan["picked"][3] == "elementwise_add/int8_out/cuda/int8_t/NHWC"
+    assert plan["picked"][4] == "relu/int8_nhwc/cuda/int8_t/NHWC"
+    assert plan["picked"][5] == "pool2d/fp32_out/cuda/int8_t/NHWC"   # softmax consumes fp32
+    assert plan["picked"][6] == "softmax/def/cuda/float/NCHW"
+    inside = [c for c in plan["casts"] if c[1] not in ("x", "y")]
+    assert [(c[0], c[1]) for c in inside] == [("layout", "p")]         # NHWC -> NCHW for softmax, no calib
+    # a relu whose consumer is fp32 cannot stay int8: the extension must not claim it
+    ops2 = [("feed", [], ["x"], False), ("conv2d", ["x"], ["a"], True), ("relu", ["a"], ["r"], False),
+            ("softmax", ["r"], ["y"], False), ("fetch", ["y"], [], False)]
+    plan2 = lh.plan_types(ops2, extension=True)
+    assert plan2["picked"][2] == "relu/def/cuda/float/NCHW"
+    assert plan2["picked"][1] == "conv2d/fp32_out/cuda/int8_t/NHWC"
