@@ -4,7 +4,7 @@ ResNet-50 int8 224x224, batch 256 per GPU, batch-sharded over N GPUs (no collect
 the per-image path), synthetic random-init weights and inputs.
 
   python bench.py [--gpus N] [--steps K] [--warmup W] [--impl b200|reference]
-                  [--net resnet50|mobilenet_v1] [--batch B]
+                  [--net resnet50|mobilenet_v1|shufflenet_v2_like] [--batch B]
 
 A "step" is one pass of the whole int8 network (calib+layout -> convs/pool/add -> fc)
 over one batch.  `value` is device-resident throughput (inputs in HBM), `e2e` goes
@@ -35,7 +35,7 @@ def parse():
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--net", default="resnet50", choices=["resnet50", "mobilenet_v1"])
+    ap.add_argument("--net", default="resnet50", choices=["resnet50", "mobilenet_v1", "shufflenet_v2_like"])
     ap.add_argument("--batch", type=int, default=None, help="images per GPU (default 256; mobilenet 64)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--cpu-seconds", type=float, default=15.0)
@@ -336,6 +336,8 @@ def layer_roofline(net, prog, batch, nets, torch):
             byts = batch * (H * W * C + P * Q * K)
         elif op.kind == "add":
             byts = batch * 3 * H * W * C
+        elif op.kind == "cat_shuffle":
+            byts = batch * 2 * P * Q * K
         elif op.kind == "quant_in":
             byts = batch * (H * W * C * 4 + P * Q * 16)
         table.append({"i": i, "kind": op.kind, "in": [H, W, C], "out": [P, Q, K], "k": op.get("k"),

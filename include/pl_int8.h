@@ -236,6 +236,10 @@ int pl_split_i8_nhwc(const int8_t* x, int ldx, int n_out, int8_t* const* ys, con
 int pl_shuffle_channel_i8_nhwc(const int8_t* x, int ldx, int8_t* y, int ldy, int C, int group,
                                int64_t pixels, pl_stream_t stream);
 int pl_relu_i8(const int8_t* x, int8_t* y, int64_t n, int hi, pl_stream_t stream);
+/* concat(a, b) + shuffle_channel(group 2) in one pass (the tail of a ShuffleNet-v2 unit:
+ * concat.h:29-60 followed by shuffle_channel.cc:24-76): y[2j] = a[j], y[2j+1] = b[j], j < c_half */
+int pl_concat_shuffle2_i8_nhwc(const int8_t* a, int lda, const int8_t* b, int ldb, int8_t* y,
+                               int ldy, int c_half, int64_t pixels, pl_stream_t stream);
 
 /* ---- introspection ---------------------------------------------------------- */
 /* number of kernels this library has launched in this process (bench.py's

@@ -152,18 +152,20 @@ def conv2d(x, w_packed, K, R, S, scale, bias, strides=(1, 1), pads=(0, 0, 0, 0),
            act=ACT_NONE, act_arg=0.0, out=OUT_INT8, rnd=ROUND_ARM, y=None, Cc=None, ldy=None,
            residual=None, res_scale=0.0):
     """x: [N,H,W,ldx] int8 device tensor (logical channels Cc <= ldx)."""
-    N, H, W, ldx = x.shape
-    Cc = ldx if Cc is None else Cc
+    N, H, W, Cx = x.shape
+    ldx = x.stride(-2)  # a channel slice of a wider buffer keeps the wide pitch
+    Cc = Cx if Cc is None else Cc
     P = conv_out_size(H, R, dil[0], pads[0], pads[1], strides[0])
     Q = conv_out_size(W, S, dil[1], pads[2], pads[3], strides[1])
-    ldy = K if ldy is None else ldy
+    if ldy is None:
+        ldy = K if y is None else y.stride(-2)
     if y is None:
         y = torch.empty((N, P, Q, ldy), dtype=_TORCH_OUT[out], device=x.device)
         if ldy != K:
             y.zero_()
     d = conv_desc(N, H, W, Cc, K, R, S, strides, pads, dil, 1, ldx, ldy)
     e = make_epilogue(scale, bias, act, act_arg, out, rnd, residual,
-                      0 if residual is None else residual.shape[-1], res_scale)
+                      0 if residual is None else residual.stride(-2), res_scale)
     _check(lib().pl_conv2d_i8_nhwc(_ptr(x), _ptr(w_packed), _ptr(y), C.byref(d), C.byref(e), _stream()),
            "pl_conv2d_i8_nhwc")
     return y
@@ -171,13 +173,14 @@ def conv2d(x, w_packed, K, R, S, scale, bias, strides=(1, 1), pads=(0, 0, 0, 0),
 
 def dwconv2d(x, w_crs, scale, bias, R, S, strides=(1, 1), pads=(0, 0, 0, 0), dil=(1, 1), act=ACT_NONE,
              act_arg=0.0, out=OUT_INT8, rnd=ROUND_ARM, y=None, Cc=None):
-    N, H, W, ldx = x.shape
-    Cc = ldx if Cc is None else Cc
+    N, H, W, Cx = x.shape
+    ldx = x.stride(-2)
+    Cc = Cx if Cc is None else Cc
     P = conv_out_size(H, R, dil[0], pads[0], pads[1], strides[0])
     Q = conv_out_size(W, S, dil[1], pads[2], pads[3], strides[1])
     if y is None:
-        y = torch.zeros((N, P, Q, ldx), dtype=_TORCH_OUT[out], device=x.device)
-    d = conv_desc(N, H, W, Cc, Cc, R, S, strides, pads, dil, Cc, ldx, y.shape[-1])
+        y = torch.zeros((N, P, Q, Cx), dtype=_TORCH_OUT[out], device=x.device)
+    d = conv_desc(N, H, W, Cc, Cc, R, S, strides, pads, dil, Cc, ldx, y.stride(-2))
     e = make_epilogue(scale, bias, act, act_arg, out, rnd)
     _check(lib().pl_dwconv2d_i8_nhwc(_ptr(x), _ptr(w_crs), _ptr(y), C.byref(d), C.byref(e), _stream()),
            "pl_dwconv2d_i8_nhwc")
@@ -445,6 +448,19 @@ def shuffle_channel(x, group, y=None):
     yp, _, ldy = _view(y, None)
     _check(lib().pl_shuffle_channel_i8_nhwc(C.c_void_p(xp), ldx, C.c_void_p(yp), ldy, Cc, group,
                                             C.c_int64(_pixels(x)), _stream()), "pl_shuffle_channel_i8_nhwc")
+    return y
+
+
+def concat_shuffle2(a, b, y=None):
+    """concat(a, b) along channels + shuffle_channel(group 2) fused: y[..., 2j] = a[..., j], y[..., 2j+1] = b[..., j]"""
+    ap, ca, lda = _view(a, None)
+    bp, cb, ldb = _view(b, None)
+    assert ca == cb
+    if y is None:
+        y = torch.empty(tuple(a.shape[:-1]) + (2 * ca,), dtype=torch.int8, device=a.device)
+    yp, _, ldy = _view(y, None)
+    _check(lib().pl_concat_shuffle2_i8_nhwc(C.c_void_p(ap), lda, C.c_void_p(bp), ldb, C.c_void_p(yp), ldy, ca,
+                                            C.c_int64(_pixels(a)), _stream()), "pl_concat_shuffle2_i8_nhwc")
     return y
 
 

@@ -73,32 +73,38 @@ __global__ void __launch_bounds__(256) concat_split_kernel(const Parts parts, in
   }
 }
 
-// shuffle_channel, group == 2 (ShuffleNet v2): output bytes 2j, 2j+1 = halves' byte j.
-// W output bytes per thread from W/2 bytes of each half, interleaved with byte permutes.
+// shuffle_channel, group == 2 (ShuffleNet v2): output bytes 2j, 2j+1 = byte j of the two halves.
+// W output bytes per thread from W/2 bytes of each half, interleaved with byte permutes.  The halves
+// are two row pointers: the same tensor (plain shuffle_channel) or two tensors (concat + shuffle fused)
 template <int W>
-__global__ void __launch_bounds__(256) shuffle2_kernel(const int8_t* __restrict__ x, int ldx, int8_t* __restrict__ y,
-                                                       int ldy, int cg, const FastDiv dChunks, const uint32_t chunks,
+__global__ void __launch_bounds__(256) shuffle2_kernel(const int8_t* __restrict__ xa, int lda,
+                                                       const int8_t* __restrict__ xb, int ldb, int8_t* __restrict__ y,
+                                                       int ldy, const FastDiv dChunks, const uint32_t chunks,
                                                        const uint32_t items) {
   pdl_launch_dependents();
   pdl_wait();
   for (uint32_t i = blockIdx.x * 256u + threadIdx.x; i < items; i += gridDim.x * 256u) {
     const uint32_t pix = fdiv(i, dChunks);
     const int ch = (int)(i - pix * chunks);
-    const int8_t* row = x + (long long)pix * ldx;
+    const int8_t* ra = xa + (long long)pix * lda + ch * (W / 2);
+    const int8_t* rb = xb + (long long)pix * ldb + ch * (W / 2);
     int8_t* out = y + (long long)pix * ldy + ch * W;
     if (W == 16) {
-      const uint2 a = *reinterpret_cast<const uint2*>(row + ch * 8);
-      const uint2 b = *reinterpret_cast<const uint2*>(row + cg + ch * 8);
+      const uint2 a = *reinterpret_cast<const uint2*>(ra);
+      const uint2 b = *reinterpret_cast<const uint2*>(rb);
       uint4 o;
       o.x = __byte_perm(a.x, b.x, 0x5140);
       o.y = __byte_perm(a.x, b.x, 0x7362);
       o.z = __byte_perm(a.y, b.y, 0x5140);
       o.w = __byte_perm(a.y, b.y, 0x7362);
       *reinterpret_cast<uint4*>(out) = o;
-    } else {  // W == 4
-      const uint32_t a = *reinterpret_cast<const uint16_t*>(row + ch * 2);
-      const uint32_t b = *reinterpret_cast<const uint16_t*>(row + cg + ch * 2);
+    } else if (W == 4) {
+      const uint32_t a = *reinterpret_cast<const uint16_t*>(ra);
+      const uint32_t b = *reinterpret_cast<const uint16_t*>(rb);
       *reinterpret_cast<uint32_t*>(out) = __byte_perm(a, b, 0x5140);
+    } else {  // W == 2: no alignment at all
+      out[0] = ra[0];
+      out[1] = rb[0];
     }
   }
 }
@@ -270,10 +276,40 @@ extern "C" int pl_shuffle_channel_i8_nhwc(const int8_t* x, int ldx, int8_t* y, i
     int8_t* ys = y + p0 * ldy;
     const uint32_t items = (uint32_t)(np * chunks);
     const int grid = grid_for_items(items);
-    if (two && W == 16) launch_pdl(shuffle2_kernel<16>, grid, 256, 0, (cudaStream_t)stream, xs, ldx, ys, ldy, cg, d, chunks, items);
-    else if (two) launch_pdl(shuffle2_kernel<4>, grid, 256, 0, (cudaStream_t)stream, xs, ldx, ys, ldy, cg, d, chunks, items);
+    if (two && W == 16) launch_pdl(shuffle2_kernel<16>, grid, 256, 0, (cudaStream_t)stream, xs, ldx, xs + cg, ldx, ys, ldy, d, chunks, items);
+    else if (two) launch_pdl(shuffle2_kernel<4>, grid, 256, 0, (cudaStream_t)stream, xs, ldx, xs + cg, ldx, ys, ldy, d, chunks, items);
     else if (W == 4) launch_pdl(shuffle_any_kernel<4>, grid, 256, 0, (cudaStream_t)stream, xs, ldx, ys, ldy, cg, dg, group, d, chunks, items);
     else launch_pdl(shuffle_any_kernel<1>, grid, 256, 0, (cudaStream_t)stream, xs, ldx, ys, ldy, cg, dg, group, d, chunks, items);
+    ++g_launches;
+  }
+  return launch_status();
+}
+
+// concat(a, b) along channels followed by shuffle_channel(group 2) in one pass: the tail of every
+// ShuffleNet-v2 unit.  out[2j] = a[j], out[2j + 1] = b[j]; 2 bytes of traffic per element instead of 4
+extern "C" int pl_concat_shuffle2_i8_nhwc(const int8_t* a, int lda, const int8_t* b, int ldb, int8_t* y, int ldy,
+                                          int c_half, int64_t pixels, pl_stream_t stream) {
+  if (!a || !b || !y || c_half <= 0 || lda < c_half || ldb < c_half || ldy < 2 * c_half || pixels < 0) return PL_ERR_ARG;
+  if (pixels == 0) return PL_OK;
+  int W = 2;
+  if (c_half % 8 == 0 && aligned(a, 8) && aligned(b, 8) && lda % 8 == 0 && ldb % 8 == 0 && aligned(y, 16) && ldy % 16 == 0)
+    W = 16;
+  else if (c_half % 2 == 0 && aligned(a, 2) && aligned(b, 2) && lda % 2 == 0 && ldb % 2 == 0 && aligned(y, 4) &&
+           ldy % 4 == 0)
+    W = 4;
+  const uint32_t chunks = (uint32_t)(2 * c_half / W);
+  const FastDiv d = make_fastdiv(chunks);
+  const int64_t slab = ((1ll << 31) - 1) / chunks;
+  for (int64_t p0 = 0; p0 < pixels; p0 += slab) {
+    const int64_t np = pixels - p0 < slab ? pixels - p0 : slab;
+    const uint32_t items = (uint32_t)(np * chunks);
+    const int grid = grid_for_items(items);
+    const int8_t* as = a + p0 * lda;
+    const int8_t* bs = b + p0 * ldb;
+    int8_t* ys = y + p0 * ldy;
+    if (W == 16) launch_pdl(shuffle2_kernel<16>, grid, 256, 0, (cudaStream_t)stream, as, lda, bs, ldb, ys, ldy, d, chunks, items);
+    else if (W == 4) launch_pdl(shuffle2_kernel<4>, grid, 256, 0, (cudaStream_t)stream, as, lda, bs, ldb, ys, ldy, d, chunks, items);
+    else launch_pdl(shuffle2_kernel<2>, grid, 256, 0, (cudaStream_t)stream, as, lda, bs, ldb, ys, ldy, d, chunks, items);
     ++g_launches;
   }
   return launch_status();

@@ -38,6 +38,7 @@ class Builder:
         self.rng = np.random.default_rng(seed)
         self.ops = []
         self.shapes = {"input": in_shape}  # name -> (H, W, C)   (per image)
+        self.views = {}  # name -> (parent, c0, c1): a channel slice (pointer offset + the parent's pitch)
         self.n_tensors = 0
 
     def _new(self, shape):
@@ -52,7 +53,27 @@ class Builder:
         self.ops.append(Op(kind="quant_in", src="input", dst=out, out_scale=None))
         return out
 
-    def conv(self, src, K, k, stride, pad, act="relu", depthwise=False, out_fp32=False, res=None):
+    def slice(self, src, c0, c1):
+        """Channel slice [c0, c1) of a tensor: free (split is a view in NHWC with an explicit pitch)."""
+        H, W, C = self.shapes[src]
+        assert 0 <= c0 < c1 <= C and src not in self.views
+        self.n_tensors += 1
+        name = f"t{self.n_tensors}"
+        self.shapes[name] = (H, W, c1 - c0)
+        self.views[name] = (src, c0, c1)
+        return name
+
+    def cat_shuffle(self, a, b):
+        """concat(a, b) along channels + shuffle_channel(group 2): the tail of a ShuffleNet-v2 unit.
+        Pure byte movement, so both inputs must carry the same scale (see conv(out_scale_like=))."""
+        H, W, C = self.shapes[a]
+        assert self.shapes[b] == (H, W, C)
+        out = self._new((H, W, 2 * C))
+        self.ops.append(Op(kind="cat_shuffle", src=a, src2=b, dst=out, in_scale=None, out_scale=None))
+        return out
+
+    def conv(self, src, K, k, stride, pad, act="relu", depthwise=False, out_fp32=False, res=None,
+             out_scale_like=None):
         H, W, C = self.shapes[src]
         P = (H + 2 * pad - k) // stride + 1
         Q = (W + 2 * pad - k) // stride + 1
@@ -63,7 +84,8 @@ class Builder:
         out = self._new((P, Q, K))
         self.ops.append(Op(kind="dwconv" if depthwise else "conv", src=src, dst=out, w=w, w_scale=w_scale,
                            bias=bias, k=k, stride=stride, pad=pad, act=act, K=K, C=C,
-                           in_scale=None, out_scale=None, out_fp32=out_fp32, res=res, res_scale=None))
+                           in_scale=None, out_scale=None, out_fp32=out_fp32, res=res, res_scale=None,
+                           out_scale_like=out_scale_like))
         return out
 
     def pool(self, src, k, stride, pad, typ, global_pooling=False):
@@ -106,6 +128,37 @@ def mobilenet_v1(seed=1234, act="relu", res=224):
         C = b.shapes[t][2]
         t = b.conv(t, C, 3, s, 1, act, depthwise=True)
         t = b.conv(t, K, 1, 1, 0, act)
+    t = b.pool(t, 7, 1, 0, "avg", global_pooling=True)
+    b.fc(t, 1000)
+    return b
+
+
+def shufflenet_v2_like(seed=1234, res=224, width=(128, 256, 512), repeats=(4, 8, 4)):
+    """ShuffleNet-v2 topology (the backbone family of humanseg_shfv75_0119_quant) with channel counts that keep
+    every half a multiple of 16 bytes: 3x3 s2 stem + max pool, three stages of one stride-2 unit + stride-1
+    units, 1x1 head, gap, fc.  Stride-1 unit: split (free views) -> [x1 | x2 -> 1x1 -> dw3x3 -> 1x1] ->
+    concat + shuffle_channel(2) (one fused pass); stride-2 unit: both branches see the whole input."""
+    b = Builder("shufflenet_v2_like", seed, (res, res, 3))
+    t = b.quant_in()
+    t = b.conv(t, 32, 3, 2, 1, "relu")
+    t = b.pool(t, 3, 2, 1, "max")
+    for C, rep in zip(width, repeats):
+        half = C // 2
+        Cin = b.shapes[t][2]
+        # stride-2 unit
+        l = b.conv(t, Cin, 3, 2, 1, "none", depthwise=True)
+        l = b.conv(l, half, 1, 1, 0, "relu")
+        r = b.conv(t, half, 1, 1, 0, "relu")
+        r = b.conv(r, half, 3, 2, 1, "none", depthwise=True)
+        r = b.conv(r, half, 1, 1, 0, "relu", out_scale_like=l)
+        t = b.cat_shuffle(l, r)
+        for _ in range(rep - 1):
+            x1, x2 = b.slice(t, 0, half), b.slice(t, half, C)
+            r = b.conv(x2, half, 1, 1, 0, "relu")
+            r = b.conv(r, half, 3, 1, 1, "none", depthwise=True)
+            r = b.conv(r, half, 1, 1, 0, "relu", out_scale_like=x1)
+            t = b.cat_shuffle(x1, r)
+    t = b.conv(t, 1024, 1, 1, 0, "relu")
     t = b.pool(t, 7, 1, 0, "avg", global_pooling=True)
     b.fc(t, 1000)
     return b
@@ -168,6 +221,8 @@ def program_bytes(prog):
             act += H * W * C + P * Q * K
         elif op.kind == "add":
             act += 3 * H * W * C
+        elif op.kind == "cat_shuffle":
+            act += 2 * P * Q * K
         elif op.kind == "fc":
             act += op.K + op.N * 4
             wts += op.w.size + 8 * op.N
@@ -234,6 +289,9 @@ class DeviceNet:
         torch.cuda.synchronize()
 
     def _buf(self, name, dtype=torch.int8):
+        if name in self.prog.views:  # a channel slice of its parent's buffer
+            parent, c0, c1 = self.prog.views[name]
+            return self._buf(parent, dtype)[..., c0:c1]
         key = (name, dtype)
         if key not in self.bufs:
             H, W, C = self.prog.shapes[name]
@@ -253,8 +311,17 @@ class DeviceNet:
         """Propagates scales layer by layer: out_scale = absmax(fp32 output)/127."""
         assert x_nchw.shape[0] <= self.batch
         n = x_nchw.shape[0]
-        scales = {}
-        vals = {}
+        class _Views(dict):  # a channel slice reads its parent's value / scale
+            def __init__(self, views, sl):
+                super().__init__()
+                self.views, self.sl = views, sl
+
+            def __missing__(self, k):
+                parent, c0, c1 = self.views[k]
+                return self[parent][..., c0:c1] if self.sl else self[parent]
+
+        scales = _Views(self.prog.views, False)
+        vals = _Views(self.prog.views, True)
         for op in self.prog.ops:
             if op.kind == "quant_in":
                 op.out_scale = float(x_nchw.abs().max().item()) / 127.0
@@ -275,6 +342,8 @@ class DeviceNet:
                 sf, bf, argf = self._fold(op, op.K, True)
                 y = self._exec_conv(op, vals[op.src], sf, bf, argf, pl.OUT_FP32, None, res, op.res_scale)
                 op.out_scale = max(float(y.abs().max().item()), 1e-6) / 127.0
+                if op.get("out_scale_like"):  # shares a concat with that tensor: requantise to its scale
+                    op.out_scale = scales[op.out_scale_like]
                 sf, bf, argf = self._fold(op, op.K, op.out_fp32)
                 vals[op.dst] = self._exec_conv(op, vals[op.src], sf, bf, argf,
                                                pl.OUT_FP32 if op.out_fp32 else pl.OUT_INT8, None, res,
@@ -291,6 +360,11 @@ class DeviceNet:
                 op.out_scale = max(float(y.abs().max().item()), 1e-6) / 127.0
                 vals[op.dst] = pl.add(vals[op.src], vals[op.src2], op.a_scale / op.out_scale,
                                       op.b_scale / op.out_scale, _ACT[op.act])
+                scales[op.dst] = op.out_scale
+            elif op.kind == "cat_shuffle":
+                assert scales[op.src] == scales[op.src2], "concat inputs must share a scale"
+                op.in_scale = op.out_scale = scales[op.src]
+                vals[op.dst] = pl.concat_shuffle2(vals[op.src], vals[op.src2])
                 scales[op.dst] = op.out_scale
             elif op.kind == "fc":
                 op.in_scale = scales[op.src]
@@ -385,6 +459,9 @@ class DeviceNet:
                 sa, sb = op.a_scale / op.out_scale, op.b_scale / op.out_scale
                 self.layers.append((op, lambda op=op, a=a, b2=b2, y=y, sa=sa, sb=sb:
                                     pl.add(a, b2, sa, sb, _ACT[op.act], y=y)))
+            elif op.kind == "cat_shuffle":
+                a, b2, y = self._buf(op.src), self._buf(op.src2), self._buf(op.dst)
+                self.layers.append((op, lambda a=a, b2=b2, y=y: pl.concat_shuffle2(a, b2, y=y)))
             elif op.kind == "fc":
                 sf, bf, _ = pl.fold_scales(op.w_scale, op.N, op.in_scale, 1.0, pl.OUT_FP32, op.bias)
                 sf, bf = torch.from_numpy(sf).to(self.dev), torch.from_numpy(bf).to(self.dev)

@@ -30,7 +30,12 @@ def _conv_reference(x, op, sf, bf, act, arg, out):
 
 def run_program(prog, x_nchw, engine="oracle", keep=False, timings=None):
     """x_nchw: fp32 [N,3,H,W].  Returns fp32 logits [N,1000] (and all tensors if keep)."""
-    vals = {}
+    class _Vals(dict):  # channel slices (prog.views) read their parent
+        def __missing__(self, k):
+            parent, c0, c1 = prog.views[k]
+            return np.ascontiguousarray(self[parent][..., c0:c1])
+
+    vals = _Vals()
     for op in prog.ops:
         t0 = time.perf_counter()
         if op.kind == "quant_in":
@@ -60,6 +65,10 @@ def run_program(prog, x_nchw, engine="oracle", keep=False, timings=None):
         elif op.kind == "add":
             vals[op.dst] = orc.add(vals[op.src], vals[op.src2], op.a_scale / op.out_scale,
                                    op.b_scale / op.out_scale, _ACT[op.act])
+        elif op.kind == "cat_shuffle":
+            # the reference's two ops, on NCHW: concat (axis 1) then shuffle_channel (group 2)
+            cat = orc.concat_nchw([np.moveaxis(vals[op.src], -1, 1), np.moveaxis(vals[op.src2], -1, 1)])
+            vals[op.dst] = np.ascontiguousarray(np.moveaxis(orc.shuffle_channel_nchw(cat, 2), 1, -1))
         elif op.kind == "fc":
             x = vals[op.src]
             A = np.ascontiguousarray(x.reshape(x.shape[0], -1))

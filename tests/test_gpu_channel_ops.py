@@ -151,3 +151,20 @@ def test_shufflenet_unit_round_trip_full_size(pl):
     assert torch.equal(back, wide)
     r = pl.relu_i8(wide)
     assert torch.equal(r, torch.clamp(wide, min=0))
+
+
+@pytest.mark.parametrize("pix,ch", [((2, 7, 9), 64), ((1, 24, 24), 18), ((3, 5, 5), 9), ((2, 4, 4), 8)])
+def test_concat_shuffle2_equals_the_two_reference_ops(pl, pix, ch):
+    """pl_concat_shuffle2_i8_nhwc = concat (axis C) then shuffle_channel(group 2), in one pass
+    (16-byte, 4-byte and unaligned flavours)."""
+    rng = np.random.default_rng(ch)
+    a, b = rand_i8(rng, pix + (ch,)), rand_i8(rng, pix + (ch,))
+    want = nhwc(orc.shuffle_channel_nchw(orc.concat_nchw([nchw(a), nchw(b)]), 2))
+    got = host(pl.concat_shuffle2(dev(a), dev(b)))
+    assert np.array_equal(got, want)
+    assert np.array_equal(got[..., 0::2], a) and np.array_equal(got[..., 1::2], b)
+    # sources as channel slices of one wider tensor (the stride-1 unit reads x1 from its own input)
+    wide = rand_i8(rng, pix + (4 * ch,))
+    wd = dev(wide)
+    got = host(pl.concat_shuffle2(wd[..., :ch], wd[..., 2 * ch:3 * ch]))
+    assert np.array_equal(got[..., 0::2], wide[..., :ch]) and np.array_equal(got[..., 1::2], wide[..., 2 * ch:3 * ch])

@@ -75,3 +75,13 @@ def test_reference_engine_equals_oracle_engine(pl):
     a = net_oracle.run_program(prog, x.numpy(), engine="oracle")
     b = net_oracle.run_program(prog, x.numpy(), engine="reference")
     assert np.array_equal(a, b)
+
+
+def test_shufflenet_v2_like_small(pl):
+    """ShuffleNet-v2 topology: split as channel-slice views, fused concat + shuffle_channel, everything int8
+    NHWC resident between the stem calib and the fc."""
+    _check(_nets().shufflenet_v2_like, 2, 64, graph=True)
+
+
+def test_shufflenet_v2_like_224(pl):
+    _check(_nets().shufflenet_v2_like, 1, 224, graph=False)

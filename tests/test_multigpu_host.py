@@ -112,7 +112,7 @@ def test_bench_reference_arm_runs_every_net():
     import subprocess
     import sys
     root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
-    for net in ("resnet50", "mobilenet_v1"):
+    for net in ("resnet50", "mobilenet_v1", "shufflenet_v2_like"):
         out = subprocess.run([sys.executable, os.path.join(root, "bench.py"), "--impl", "reference", "--net", net,
                               "--steps", "1", "--warmup", "0"], capture_output=True, text=True, timeout=300)
         assert out.returncode == 0, out.stderr[-2000:]
