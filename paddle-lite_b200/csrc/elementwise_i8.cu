@@ -383,9 +383,14 @@ pool4_kernel(const uint32_t* __restrict__ x, int ldxw, void* __restrict__ y, int
   const int h1 = min(hs + kh, H), w1 = min(ws + kw, W);
   const int h0 = max(hs, 0), w0 = max(ws, 0);
   const uint32_t* img = x + (size_t)n * (size_t)(H * W) * (size_t)ldxw + cw;
-  uint32_t a01[V], a23[V];  // channel pairs (0,1) and (2,3) of each word as 16-bit lanes
+  // avg: channel pairs (0,1) and (2,3) of each word as 16-bit lane sums; max: a01 holds the packed
+  // int8 maxima (one VMAX4 per tap and word instead of two unpacks + two 16-bit maxima)
+  uint32_t a01[V], a23[V];
 #pragma unroll
-  for (int v = 0; v < V; ++v) a01[v] = a23[v] = (POOL == PL_POOL_MAX) ? 0xff80ff80u : 0u;
+  for (int v = 0; v < V; ++v) {
+    a01[v] = (POOL == PL_POOL_MAX) ? 0x80808080u : 0u;
+    a23[v] = 0u;
+  }
   auto load = [&](int h, int w, uint32_t (&d)[V]) {
     const uint32_t* p = img + (uint32_t)((h * W + w) * ldxw);
     if (V == 4) {
@@ -399,8 +404,7 @@ pool4_kernel(const uint32_t* __restrict__ x, int ldxw, void* __restrict__ y, int
 #pragma unroll
     for (int v = 0; v < V; ++v) {
       if (POOL == PL_POOL_MAX) {
-        a01[v] = __vmaxs2(a01[v], prmt_e(d[v], 0u, 0x9180));  // {b0, sign, b1, sign}
-        a23[v] = __vmaxs2(a23[v], prmt_e(d[v], 0u, 0xB3A2));
+        a01[v] = __vmaxs4(a01[v], d[v]);
       } else {
         const uint32_t b = d[v] ^ 0x80808080u;  // biased to unsigned: lanes cannot carry into each other
         a01[v] += prmt_e(b, 0u, 0x4140);
@@ -436,14 +440,32 @@ pool4_kernel(const uint32_t* __restrict__ x, int ldxw, void* __restrict__ y, int
   const int cnt_in = (h1 - h0) * (w1 - w0);
   const int cnt = exclusive ? cnt_in : kh * kw;
   const size_t obase = ((size_t)u * dQ.d + oq) * (size_t)ldy;  // u = n * P + op
+  if (POOL == PL_POOL_MAX && V == 4 && out_dtype == PL_OUT_INT8 && rescale == 1.0f && round_mode == PL_ROUND_ARM &&
+      word_store && cw * 4 + 16 <= C) {
+    int8_t* out = reinterpret_cast<int8_t*>(y) + obase + cw * 4;
+    if ((reinterpret_cast<uintptr_t>(out) & 15) == 0) {  // one 16-byte store (see the per-word path below)
+      *reinterpret_cast<uint4*>(out) =
+          make_uint4(__vmaxs4(a01[0], 0x81818181u), __vmaxs4(a01[V > 1 ? 1 : 0], 0x81818181u),
+                     __vmaxs4(a01[V > 2 ? 2 : 0], 0x81818181u), __vmaxs4(a01[V > 3 ? 3 : 0], 0x81818181u));
+      return;
+    }
+  }
 #pragma unroll
   for (int v = 0; v < V; ++v) {
     int e[4];
     if (POOL == PL_POOL_MAX) {
-      e[0] = (int)(short)(a01[v] & 0xffffu);
-      e[1] = (int)(short)(a01[v] >> 16);
-      e[2] = (int)(short)(a23[v] & 0xffffu);
-      e[3] = (int)(short)(a23[v] >> 16);
+      // same scale in and out (the usual max pool): (float)max * 1.0f rounds to max itself, and the
+      // ARM convention clamps at -127
+      if (out_dtype == PL_OUT_INT8 && rescale == 1.0f && round_mode == PL_ROUND_ARM && word_store &&
+          (cw + v) * 4 + 4 <= C) {
+        *reinterpret_cast<uint32_t*>(reinterpret_cast<int8_t*>(y) + obase + (cw + v) * 4) =
+            __vmaxs4(a01[v], 0x81818181u);
+        continue;
+      }
+      e[0] = (int)(int8_t)(a01[v] & 0xffu);
+      e[1] = (int)(int8_t)((a01[v] >> 8) & 0xffu);
+      e[2] = (int)(int8_t)((a01[v] >> 16) & 0xffu);
+      e[3] = (int)(int8_t)(a01[v] >> 24);
     } else {
       e[0] = (int)(a01[v] & 0xffffu) - 128 * cnt_in;
       e[1] = (int)(a01[v] >> 16) - 128 * cnt_in;

@@ -450,6 +450,21 @@ def test_pool_parity(pl, case, out):
     assert np.array_equal(got[..., :Cc], want)
 
 
+@pytest.mark.parametrize("shape", [(2, 112, 112, 64), (1, 96, 96, 36), (2, 9, 9, 24), (1, 10, 10, 9)])
+def test_max_pool_same_scale(pl, shape):
+    """rescale == 1 (the scale-preserving max pool of every net here) takes the packed path: the result is
+    the window maximum itself, clamped at -127 like the ARM requantiser (inputs include -128)."""
+    N, H, W, Cc = shape
+    rng = np.random.default_rng(Cc)
+    x = rng.integers(-128, 128, shape, dtype=np.int8)
+    x[:, ::3, ::3, :] = -128  # whole windows of -128 at the borders
+    want = orc.pool2d(x, (3, 3), (2, 2), (1, 1, 1, 1), orc.POOL_MAX, True, 1.0, orc.OUT_INT8)
+    ld = rup(Cc, 16)
+    got = host(pl.pool2d(dev(pad_c(x, ld)), (3, 3), (2, 2), (1, 1, 1, 1), orc.POOL_MAX, True, 1.0, orc.OUT_INT8, Cc=Cc))
+    assert np.array_equal(got[..., :Cc], want)
+    assert want.min() >= -127
+
+
 @pytest.mark.parametrize("n", [1, 16, 1000, 256 * 56 * 56 * 4 + 5])
 def test_residual_add_parity(pl, n):
     rng = np.random.default_rng(n)
