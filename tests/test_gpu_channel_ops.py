@@ -168,3 +168,20 @@ def test_concat_shuffle2_equals_the_two_reference_ops(pl, pix, ch):
     wd = dev(wide)
     got = host(pl.concat_shuffle2(wd[..., :ch], wd[..., 2 * ch:3 * ch]))
     assert np.array_equal(got[..., 0::2], wide[..., :ch]) and np.array_equal(got[..., 1::2], wide[..., 2 * ch:3 * ch])
+
+
+def test_concat_and_shuffle_beyond_2g_items(pl):
+    """Maximum sizes: more than 2^31 work items (unaligned 1 + 2 channel parts -> byte chunks) go out in
+    slabs of whole pixels; checked against torch on the device (size-independent property: concat = cat)."""
+    pixels = (1 << 31) // 3 + 1000  # 3 byte-items per pixel -> just over 2^31 items
+    g = torch.Generator(device=DEV).manual_seed(11)
+    a = torch.randint(-128, 128, (pixels, 1), dtype=torch.int8, device=DEV, generator=g)
+    b = torch.randint(-128, 128, (pixels, 2), dtype=torch.int8, device=DEV, generator=g)
+    y = pl.concat([a, b])
+    assert y.shape == (pixels, 3)
+    assert torch.equal(y[:, :1], a) and torch.equal(y[:, 1:], b)
+    pa, pb = pl.split(y, [1, 2])
+    assert torch.equal(pa, a) and torch.equal(pb, b)
+    del pa, pb, a, b
+    sh = pl.shuffle_channel(y, 3)  # group == C: identity permutation through the bytewise path
+    assert torch.equal(sh, y)
