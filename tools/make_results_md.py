@@ -25,7 +25,10 @@ out.append("## Networks (bench.py, CUDA graph, device-resident `value`; `e2e` = 
 out.append("| run | img/s (device) | ms/step | img/s (e2e) | TOP/s | igemm roofline | CPU reference img/s (cores) |")
 out.append("|---|---:|---:|---:|---:|---|---:|")
 for name, f in (("ResNet-50 int8 b256", "bench_resnet50_b256.json"), ("MobileNetV1 int8 b64", "bench_mobilenet_b64.json"),
-                ("MobileNetV1 int8 b1", "bench_mobilenet_b1.json")):
+                ("MobileNetV1 int8 b1", "bench_mobilenet_b1.json"),
+                ("ShuffleNet-v2-like int8 b64 (SURVEY 8f rank 1 ops)", "bench_shufflenet_b64.json")):
+    if not os.path.exists(os.path.join(O, f)):
+        continue
     l = last_json(os.path.join(O, f))
     r = l["roofline"]
     cb = l.get("cpu_baseline")
@@ -52,6 +55,18 @@ for ln in open(os.path.join(O, "layers_b256.txt")):
     gbs = float(ln.split("GB/s=")[1].split()[0])
     out.append(f"| {f[0]} | {ms:.4f} | {tops:.0f} | {100 * tops / peak:.0f} | {gbs:.0f} | {100 * gbs / HBM:.0f} |")
 out.append("")
+
+if os.path.exists(os.path.join(O, "channel_ops.jsonl")):
+    out.append("## int8 NHWC channel movement kernels (`tools/channel_ops_bench.py`; 2 bytes per element)\n")
+    out.append("| op | tensor | MB moved | us | GB/s | fraction of HBM peak |\n|---|---|---:|---:|---:|---:|")
+    for ln in open(os.path.join(O, "channel_ops.jsonl")):
+        if not ln.startswith("{"):
+            continue
+        j = json.loads(ln)
+        if j["MB_moved"] < 100:
+            continue  # the small humanseg shapes time the Python call, not the kernel
+        out.append(f"| {j['op']} | {j['shape']} x {j['channels']} | {j['MB_moved']} | {j['us']} | {j['GB/s']} | {j['frac_hbm_peak']} |")
+    out.append("")
 
 out.append("## Config 5: int8 GEMM sweep, one GPU (`tools/gemm_sweep.py`)\n")
 out.append("| M x N x K | out | ms | TOP/s | % of tensor peak | GB/s |\n|---|---|---:|---:|---:|---:|")
