@@ -85,6 +85,9 @@ struct IgemmParams {
   // third (the bound of these launches); the epilogue of a pair no longer overlaps the
   // next mainloop, which long K amortises
   int mpair;
+  // fp32 out, act none / relu, no residual, 16-byte aligned rows: the generic instantiation converts and
+  // stores its 16 columns inline (four 16-byte stores per thread) instead of calling store_group16
+  int f32_fast;
   const CUtensorMap* peer_maps;
   int n_peers;
   int thin_group;  // thin mode with a resident filter: a ring stage holds all k-blocks of a tile
@@ -1106,6 +1109,26 @@ igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
                 w[q4] = quad_i8_signed(acc + 4 * q4, sc, bi);
             }
             st_shared_v4(out_base + sbase + soff, w[0], w[1], w[2], w[3]);
+          } else if (p.f32_fast && row + (long long)(sub * kBM) < p.M && n0 + (int)col + 16 <= p.Nout) {
+            float* out = reinterpret_cast<float*>(p.y) + (row + (long long)(sub * kBM)) * p.ldy + n0 + (int)col;
+            const bool relu = p.epi.act == PL_ACT_RELU;
+#pragma unroll
+            for (int q4 = 0; q4 < 4; ++q4) {
+              const float4 sc = *reinterpret_cast<const float4*>(&s_scale[sb0 + col + 4 * q4]);
+              const float4 bi = *reinterpret_cast<const float4*>(&s_bias[sb0 + col + 4 * q4]);
+              float4 v;
+              v.x = __fmaf_rn(__int2float_rn((int)acc[4 * q4 + 0]), sc.x, bi.x);
+              v.y = __fmaf_rn(__int2float_rn((int)acc[4 * q4 + 1]), sc.y, bi.y);
+              v.z = __fmaf_rn(__int2float_rn((int)acc[4 * q4 + 2]), sc.z, bi.z);
+              v.w = __fmaf_rn(__int2float_rn((int)acc[4 * q4 + 3]), sc.w, bi.w);
+              if (relu) {
+                v.x = v.x > 0.f ? v.x : 0.f;
+                v.y = v.y > 0.f ? v.y : 0.f;
+                v.z = v.z > 0.f ? v.z : 0.f;
+                v.w = v.w > 0.f ? v.w : 0.f;
+              }
+              *reinterpret_cast<float4*>(out + 4 * q4) = v;
+            }
           } else if (row + (long long)(sub * kBM) < p.M && n0 + (int)col < p.Nout) {
             store_group16(p, acc, row + (long long)(sub * kBM), n0 + (int)col, &s_scale[sb0 + col], &s_bias[sb0 + col]);
           }
@@ -1451,6 +1474,11 @@ int launch_igemm(const CUtensorMap& ta, const CUtensorMap& tb, IgemmParams& p, p
   }
   // (tile pairs storing straight from registers through the generic epilogue, to trade the 64 KB of staging
   // for two more mainloop stages, measured 2.5x slower at 4096^3: the exposed epilogue dominates)
+  p.f32_fast = (epi == EPI_GENERIC && e.out_dtype == PL_OUT_FP32 && e.round_mode == PL_ROUND_ARM && p.vec_ok &&
+                e.scale && !e.residual && (e.act == PL_ACT_NONE || e.act == PL_ACT_RELU) &&
+                env_int("PL_NO_F32_FAST", 0) == 0)
+                   ? 1
+                   : 0;
   // int8 fast paths leave through swizzled smem panels + TMA stores (and take the
   // residual in through TMA loads): vec_ok already guarantees the 16-byte rules
   CUtensorMap ty{}, tr{};
