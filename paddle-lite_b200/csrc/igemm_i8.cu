@@ -1168,7 +1168,7 @@ igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
     }
     };  // epilogue_loop
     bool pair_done = false;
-    if constexpr (TR == 0 && (EPI == EPI_I8_RELU || EPI == EPI_I8_SIGNED)) {
+    if constexpr (TR == 0 && (EPI == EPI_I8_RELU || EPI == EPI_I8_SIGNED || EPI == EPI_GENERIC)) {
       if (p.mpair) {
         epilogue_loop(std::integral_constant<int, CQ>{}, std::true_type{});
         pair_done = true;
@@ -1998,15 +1998,20 @@ static void maybe_enable_mpair(IgemmParams& p, const pl_epilogue* e, int K, bool
   const bool fast = e->out_dtype == PL_OUT_INT8 && e->round_mode == PL_ROUND_ARM && p.vec_ok && e->scale &&
                     !e->residual && tma_epilogue_enabled() &&
                     (e->act == PL_ACT_NONE || e->act == PL_ACT_RELU || (e->act == PL_ACT_RELU6 && e->act_arg > 0.f));
-  (void)peers;
-  if (!fast || p.mode != 0 || p.BN != 256 || p.m_tiles < 2 || env_int("PL_NO_MPAIR", 0)) return;
+  // fp32 out (act none / relu): the pair stores straight from registers (IgemmParams::f32_fast), no staging
+  const bool f32 = !peers && e->out_dtype == PL_OUT_FP32 && e->round_mode == PL_ROUND_ARM && p.vec_ok && e->scale &&
+                   !e->residual && (e->act == PL_ACT_NONE || e->act == PL_ACT_RELU) && env_int("PL_NO_F32_FAST", 0) == 0 &&
+                   env_int("PL_MPAIR_F32", 1) != 0;
+  if ((!fast && !f32) || p.mode != 0 || p.BN != 256 || p.m_tiles < 2 || env_int("PL_NO_MPAIR", 0)) return;
   if (!env_int("PL_MPAIR_FORCE", 0)) {
     // the pair has a single accumulator stage (its epilogue is exposed), so K must be long enough
     // to hide it, and the coarser work unit must not cost a wave
     const long long sms = driver().sm_count;
     const long long tiles = (long long)p.m_tiles * p.n_tiles, pairs = (long long)((p.m_tiles + 1) / 2) * p.n_tiles;
     const long long w1 = (tiles + sms - 1) / sms, w2 = 2 * ((pairs + sms - 1) / sms);
-    if (K < env_int("PL_MPAIR_MIN_K", 4096) || tiles < 2 * sms || w2 > w1) return;
+    // (the exposed fp32 epilogue of a pair is twice as long: 4096^3 loses 12 %, 8192^3 gains 12 %)
+    const int min_k = fast ? env_int("PL_MPAIR_MIN_K", 4096) : env_int("PL_MPAIR_MIN_K_F32", 8192);
+    if (K < min_k || tiles < 2 * sms || w2 > w1) return;
   }
   p.mpair = 1;
   p.BK = 64;  // 32 KB stages: four of them beside the 64 KB staging buffer

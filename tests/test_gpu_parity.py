@@ -317,9 +317,11 @@ def test_gemm_tile_pair_mode(pl, mnk, monkeypatch):
         assert np.array_equal(got, want)
     acc = host(pl.gemm(dev(A), dev(Bt), None, None, out=pl.OUT_INT32))
     assert np.array_equal(acc, A.astype(np.int32) @ Bt.astype(np.int32).T)
-    want = orc.gemm(A, Bt, s, b, b_is_nk=True, act=orc.ACT_RELU, out=orc.OUT_FP32)
-    got = host(pl.gemm(dev(A), dev(Bt), dev(s), dev(b), act=pl.ACT_RELU, out=pl.OUT_FP32))
-    assert np.array_equal(got, want)
+    # fp32 out also runs as pairs (stored straight from registers), act none and relu
+    for act, oact in ((pl.ACT_RELU, orc.ACT_RELU), (pl.ACT_NONE, orc.ACT_NONE)):
+        want = orc.gemm(A, Bt, s, b, b_is_nk=True, act=oact, out=orc.OUT_FP32)
+        got = host(pl.gemm(dev(A), dev(Bt), dev(s), dev(b), act=act, out=pl.OUT_FP32))
+        assert np.array_equal(got, want)
 
 
 def test_gemm_fc_weight_layout(pl):
