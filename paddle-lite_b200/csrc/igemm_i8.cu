@@ -1385,13 +1385,24 @@ uint32_t pow2_cols(int n) {
   return c;
 }
 
+int env_int(const char* name, int dflt);
+
 int pick_bn(int Nout, int m_tiles, int sms) {
   // widest tile that does not over-cover Nout, narrowed until the grid fills the SMs
   const int n16 = (Nout + 15) / 16 * 16;
   int cap = 256;
   while (cap > 16 && cap / 2 >= n16) cap >>= 1;
   int bn = cap;
-  while (bn > 16 && m_tiles * ((Nout + bn - 1) / bn) < sms) bn >>= 1;
+  // (stop when the grid already covers most SMs and the next halving would only add a second, partial wave:
+  // a skinny 4096 x 4096 GEMM is latency bound per CTA, 128 CTAs of N = 32 finish in half the time of 256 of N = 16)
+  const int fill = env_int("PL_BN_FILL_PCT", 60);
+  while (bn > 16) {
+    const int tiles = m_tiles * ((Nout + bn - 1) / bn);
+    if (tiles >= sms) break;
+    const int next = m_tiles * ((Nout + bn / 2 - 1) / (bn / 2));
+    if (next > sms && tiles * 100 >= sms * fill) break;
+    bn >>= 1;
+  }
   return bn;
 }
 
