@@ -85,6 +85,10 @@ struct IgemmParams {
   // third (the bound of these launches); the epilogue of a pair no longer overlaps the
   // next mainloop, which long K amortises
   int mpair;
+  // tile order of long-K GEMMs (mode 0, streamed B): bands of group_m tile rows are walked column by column,
+  // so that one wave of CTAs touches ~sqrt(SMs) A row blocks and B column blocks instead of 2-5 and all of B
+  // (8192^3: 24 % of the L2 requests missed to DRAM with the row-major order)
+  int group_m;
   // fp32 out, act none / relu, no residual, 16-byte aligned rows: the generic instantiation converts and
   // stores its 16 columns inline (four 16-byte stores per thread) instead of calling store_group16
   int f32_fast;
@@ -367,7 +371,24 @@ __device__ __forceinline__ void issue_s2d(uint32_t d_tmem, uint64_t da0, uint64_
   } while (0)
 #endif
 
-template <int EPI, int TR = 0, int TSW = 0>
+// GROUPED is a kernel template flag: the banded order lives in its own instantiations (the large GEMMs);
+// sharing one kernel behind a runtime branch cost the conv nets 1.7 %
+template <bool GROUPED>
+__device__ __forceinline__ void tile_mn(const IgemmParams& p, int tile, int& tm, int& tn) {
+  if (GROUPED) {
+    const int per_band = p.group_m * p.n_tiles;
+    const int band = tile / per_band, within = tile - band * per_band;
+    const int left = p.m_tiles - band * p.group_m;
+    const int rows = left < p.group_m ? left : p.group_m;
+    tn = within / rows;
+    tm = band * p.group_m + within - tn * rows;
+  } else {
+    tn = tile % p.n_tiles;
+    tm = tile / p.n_tiles;
+  }
+}
+
+template <int EPI, int TR = 0, int TSW = 0, bool GROUPED = false>
 __global__ void __launch_bounds__(TR > 0 ? kThinThreads : kThreads, 1)
 igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
                 const __grid_constant__ CUtensorMap tmap_b,
@@ -590,7 +611,9 @@ igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
     int lt = 0;
     for (int tile = blockIdx.x; tile < num_tiles && !(TR > 0 && p.b_resident) && mode != 3; tile += gridDim.x, ++lt) {
       PL_TRACE(0, lt, 0);
-      const int tn = tile % n_tiles, tm = tile / n_tiles;
+      int tn_, tm_;
+      tile_mn<GROUPED>(p, tile, tm_, tn_);
+      const int tn = tn_, tm = tm_;
       const int m0 = (tm * kBM) << p.mpair, n0 = tn * BN;  // pairs: one 256-row box
       if (EPI == EPI_I8_RELU_RES) {
         // residual tile first: it is the largest load of a 1x1 expand layer
@@ -943,7 +966,9 @@ igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
       int ob = 0;
       uint32_t ophase = 0;
       for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
-        const int tn = tile % p.n_tiles, tm = tile / p.n_tiles;
+        int tn_, tm_;
+        tile_mn<GROUPED>(p, tile, tm_, tn_);
+        const int tn = tn_, tm = tm_;
         const int n0 = tn * p.BN;
         const uint32_t out_tile = (kInPlace ? smem_res : smem_out) + (uint32_t)ob * (kInPlace ? tile_bytes : obuf_bytes);
         WAIT(bar_staged + 8 * ob, ophase);
@@ -1004,7 +1029,9 @@ igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
     // into two 256-entry buffers, filled during the previous tile.
     auto stage_scale_bias = [&](int t, int buf) {
       if (etid < p.BN) {
-        const int n = (t % p.n_tiles) * p.BN + etid;
+        int ttm, ttn;
+        tile_mn<GROUPED>(p, t, ttm, ttn);
+        const int n = ttn * p.BN + etid;
         const bool ok = n < p.Nout && p.epi.scale != nullptr;
         s_scale[buf * 256 + etid] = ok ? __ldg(p.epi.scale + n) : 0.f;
         s_bias[buf * 256 + etid] = (ok && p.epi.bias) ? __ldg(p.epi.bias + n) : 0.f;
@@ -1042,7 +1069,9 @@ igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
              ophase = (uint32_t)(egroup / out_bufs_) & 1u;
     for (int tile = blockIdx.x + egroup * (int)gridDim.x; tile < num_tiles; tile += G * (int)gridDim.x, lt += G) {
       PL_ETRACE(0);
-      const int tn = tile % p.n_tiles, tm = tile / p.n_tiles;
+      int tn_, tm_;
+      tile_mn<GROUPED>(p, tile, tm_, tn_);
+      const int tn = tn_, tm = tm_;
       long long row = (long long)(kPair ? 2 * tm : tm) * kBM + arow;  // output pixel index (generic epilogue)
       int himg = 0, hp0 = 0;
       if (halo) {
@@ -1406,13 +1435,13 @@ int pick_bn(int Nout, int m_tiles, int sms) {
   return bn;
 }
 
-template <int EPI, int TR = 0, int TSW = 0>
+template <int EPI, int TR = 0, int TSW = 0, bool GROUPED = false>
 int launch_one(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& ty, const CUtensorMap& tr,
                const IgemmParams& p, int grid, size_t smem, pl_stream_t stream) {
   static bool configured = false;  // one process drives one GPU
   if (!configured) {
     // 227 KB is the per-CTA limit for static + dynamic shared memory together
-    PL_CUDA_OK(cudaFuncSetAttribute(igemm_i8_kernel<EPI, TR, TSW>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    PL_CUDA_OK(cudaFuncSetAttribute(igemm_i8_kernel<EPI, TR, TSW, GROUPED>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                     (int)(221 * 1024)));
     configured = true;
   }
@@ -1426,7 +1455,7 @@ int launch_one(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& 
     PL_CUDA_OK(cudaMemsetAsync(dbuf, 0, n * sizeof(long long), (cudaStream_t)stream));
     IgemmParams q = p;
     q.trace = dbuf;
-    igemm_i8_kernel<EPI, TR, TSW><<<grid, threads, smem, (cudaStream_t)stream>>>(ta, tb, ty, tr, q);
+    igemm_i8_kernel<EPI, TR, TSW, GROUPED><<<grid, threads, smem, (cudaStream_t)stream>>>(ta, tb, ty, tr, q);
     ++g_launches;
     PL_CUDA_OK(cudaStreamSynchronize((cudaStream_t)stream));
     std::vector<long long> h(n);
@@ -1444,7 +1473,7 @@ int launch_one(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& 
     }
     return launch_status();
   }
-  launch_pdl(igemm_i8_kernel<EPI, TR, TSW>, dim3(grid), dim3(threads), smem, (cudaStream_t)stream, ta, tb, ty, tr, p);
+  launch_pdl(igemm_i8_kernel<EPI, TR, TSW, GROUPED>, dim3(grid), dim3(threads), smem, (cudaStream_t)stream, ta, tb, ty, tr, p);
   ++g_launches;
   return launch_status();
 }
@@ -1598,6 +1627,17 @@ int launch_igemm(const CUtensorMap& ta, const CUtensorMap& tb, IgemmParams& p, p
   if (p.s2d && !hres) return PL_ERR_UNSUPPORTED;
   if (p.n_peers > 0 && !p.tma_out) return PL_ERR_UNSUPPORTED;
   if (!p.tma_out) bres01 = false;
+  {
+    // measured (tools/gemm_sweep.py): bands of 16 rows for 8192^3 / 16384^3 (2621 -> 2797, 2531 -> 2880 TOP/s),
+    // 8 when there are fewer than 32 tile rows; no effect at 4096^3
+    int gm = env_int("PL_GROUP_M", 0);
+    if (gm == 0) gm = p.m_tiles >= 32 ? 16 : 8;
+    // (only with >= 6 waves of tiles: 4096^3 with fp32 out loses 7 % when its 3.5 waves are banded)
+    p.group_m = (p.mode == 0 && !bres01 && !p.s2d && gm > 1 && p.num_kb * p.BK >= 2048 && p.n_tiles >= 8 &&
+                 p.m_tiles >= 2 * gm && (tiles >= 6 * driver().sm_count || env_int("PL_GROUP_M", 0) > 0))
+                    ? gm
+                    : 1;
+  }
   p.b_resident = ((p.mode == 2 && p.n_tiles == 1) || hres || bres01) ? 1 : 0;
   if (p.mode == 2 && p.b_resident && env_int("PL_THIN_NO_GROUP", 0) == 0) {
     p.thin_group = 1;
@@ -1659,6 +1699,14 @@ int launch_igemm(const CUtensorMap& ta, const CUtensorMap& tb, IgemmParams& p, p
       default: return PL_ERR_UNSUPPORTED;
     }
 #undef PL_THIN_CASE
+  }
+  if (p.group_m > 1) {  // large GEMMs only (mode 0, streamed B): their own instantiations
+    switch (epi) {
+      case EPI_I8_RELU: return launch_one<EPI_I8_RELU, 0, 0, true>(ta, tb, ty, tr, p, grid, smem, stream);
+      case EPI_I8_SIGNED: return launch_one<EPI_I8_SIGNED, 0, 0, true>(ta, tb, ty, tr, p, grid, smem, stream);
+      case EPI_GENERIC: return launch_one<EPI_GENERIC, 0, 0, true>(ta, tb, ty, tr, p, grid, smem, stream);
+      default: p.group_m = 1; break;  // (fused residual: row-major order)
+    }
   }
   switch (epi) {
     case EPI_I8_RELU: return launch_one<EPI_I8_RELU>(ta, tb, ty, tr, p, grid, smem, stream);

@@ -324,6 +324,28 @@ def test_gemm_tile_pair_mode(pl, mnk, monkeypatch):
         assert np.array_equal(got, want)
 
 
+@pytest.mark.parametrize("pairs", [False, True])
+def test_gemm_grouped_tile_order(pl, pairs, monkeypatch):
+    """Long-K GEMMs walk their tiles in bands of group_m rows (L2 locality); 20 tile rows in bands of 8 leave
+    a ragged last band of 4 (2 with pairs: bands of 4), the last row itself is ragged (M % 128 != 0)."""
+    monkeypatch.setenv("PL_GROUP_M", "4" if pairs else "8")
+    if pairs:
+        monkeypatch.setenv("PL_MPAIR_FORCE", "1")
+    else:
+        monkeypatch.setenv("PL_NO_MPAIR", "1")
+    M, N, K = 2482, 2048, 2048
+    rng = np.random.default_rng(77)
+    A = rng.integers(-127, 128, (M, K), dtype=np.int8)
+    Bt = rng.integers(-127, 128, (N, K), dtype=np.int8)
+    s = ((rng.random(N, dtype=np.float32) + 0.5) / 127 / 127 * (64.0 / K) * 8).astype(np.float32)
+    b = rng.standard_normal(N).astype(np.float32)
+    want = orc.gemm(A, Bt, s, b, b_is_nk=True, act=orc.ACT_RELU, out=orc.OUT_INT8)
+    got = host(pl.gemm(dev(A), dev(Bt), dev(s), dev(b), act=pl.ACT_RELU, out=pl.OUT_INT8))
+    assert np.array_equal(got, want)
+    monkeypatch.setenv("PL_GROUP_M", "1")  # and the row-major order gives the same bytes
+    assert np.array_equal(host(pl.gemm(dev(A), dev(Bt), dev(s), dev(b), act=pl.ACT_RELU, out=pl.OUT_INT8)), want)
+
+
 def test_gemm_fc_weight_layout(pl):
     """fc keeps W as [K,N] (lite/kernels/cuda/fc_compute.cu:199-353); it is transposed
     once (PrepareForRun) with pl_transpose_i8 and then used K-major."""
