@@ -1632,9 +1632,11 @@ int launch_igemm(const CUtensorMap& ta, const CUtensorMap& tb, IgemmParams& p, p
     // 8 when there are fewer than 32 tile rows; no effect at 4096^3
     int gm = env_int("PL_GROUP_M", 0);
     if (gm == 0) gm = p.m_tiles >= 32 ? 16 : 8;
-    // (only with >= 6 waves of tiles: 4096^3 with fp32 out loses 7 % when its 3.5 waves are banded)
-    p.group_m = (p.mode == 0 && !bres01 && !p.s2d && gm > 1 && p.num_kb * p.BK >= 2048 && p.n_tiles >= 8 &&
-                 p.m_tiles >= 2 * gm && (tiles >= 6 * driver().sm_count || env_int("PL_GROUP_M", 0) > 0))
+    // only when B (N x K bytes) cannot stay in L2 next to a wave's A rows: with B <= 32 MB the row-major
+    // order already re-uses all of it and banding loses 7 % (8192 x 4096 x 8192, 4096^3)
+    const long long b_total = (long long)p.Nout * p.num_kb * p.BK;
+    p.group_m = (p.mode == 0 && !bres01 && !p.s2d && gm > 1 && p.n_tiles >= 8 && p.m_tiles >= 2 * gm &&
+                 (b_total >= (48ll << 20) || env_int("PL_GROUP_M", 0) > 0))
                     ? gm
                     : 1;
   }
