@@ -64,7 +64,8 @@ enum {
   PL_ERR_ALIGN = -2,       /* pointer or pitch not 16-byte aligned */
   PL_ERR_UNSUPPORTED = -3, /* shape outside what the sm_100a kernels cover */
   PL_ERR_DRIVER = -4,      /* tensor-map encode / driver entry point failed */
-  PL_ERR_DEVICE = -5       /* device is not sm_100 */
+  PL_ERR_DEVICE = -5,      /* device is not sm_100 */
+  PL_ERR_LIMIT = -6        /* request exceeds a fixed in-library limit (pl_gemm_i8_peers_static) */
 };
 
 /* Fused epilogue shared by conv / depthwise / gemm. */
@@ -137,6 +138,23 @@ int pl_gemm_i8(const int8_t* A, int lda, const int8_t* Bt, int ldb, void* C,
 int pl_gemm_i8_peers(const int8_t* A, int lda, const int8_t* Bt, int ldb, void* C, void* const* C_peers,
                      int n_peers, void* maps_dev, int ldc, int M, int N, int K, const pl_epilogue* e,
                      pl_stream_t stream);
+
+/* Allocation-free variant of pl_gemm_i8_peers.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (code under CUDA-graph capture, tight serving
+ * loops, harnesses that forbid it).  Same arithmetic, same outputs, same peer stores; the scratch that holds
+ * the peer tensor maps is not passed in but lives in the library image: a file-scope
+ * `static __device__ __align__(256)` array of PL_STATIC_PEERS_MAX * 128 bytes (1 KB: the 7 peers of an 8-GPU box fit; pl_gemm_i8_peers takes up to 15) that every GPU which
+ * loads the library holds until the process exits.  Its device address is obtained once per device (with
+ * that device current) through cudaGetSymbolAddress.  The call itself allocates nothing: no cudaMalloc /
+ * cudaFree / allocating library routine (one small cudaMemcpyAsync uploads the maps, as in
+ * pl_gemm_i8_peers).  n_peers > PL_STATIC_PEERS_MAX returns PL_ERR_LIMIT (and says so on stderr).
+ * All calls on one GPU share the table, which keeps the last call's maps (nothing in it has to start at
+ * zero: every call rewrites the entries it uses).  Calls on the same stream are ordered; calls that
+ * OVERLAP on the GPU (different streams, or different host threads driving the same device) race on it. */
+#define PL_STATIC_PEERS_MAX 8
+int pl_gemm_i8_peers_static(const int8_t* A, int lda, const int8_t* Bt, int ldb, void* C, void* const* C_peers,
+                            int n_peers, int ldc, int M, int N, int K, const pl_epilogue* e,
+                            pl_stream_t stream);
 
 /* ---- bandwidth-bound paths (16-byte int8 vectors, no tensor cores) --------- */
 /* depthwise conv: groups == C == K, filter [C,R,S,1] as given by the reference */

@@ -214,6 +214,19 @@ def gemm_peers(A, Bt, scale, bias, y, peer_ptrs, maps_dev, act=ACT_NONE, act_arg
     return y
 
 
+def gemm_peers_static(A, Bt, scale, bias, y, peer_ptrs, act=ACT_NONE, act_arg=0.0, rnd=ROUND_ARM, N=None, K=None):
+    """pl_gemm_i8_peers_static: pl_gemm_i8_peers without caller scratch (the peer tensor maps live in a
+    file-scope __device__ table of PL_STATIC_PEERS_MAX entries inside the library); allocates nothing."""
+    M = A.shape[0]
+    K = A.shape[1] if K is None else K
+    N = Bt.shape[0] if N is None else N
+    e = make_epilogue(scale, bias, act, act_arg, OUT_INT8, rnd)
+    arr = (C.c_void_p * max(len(peer_ptrs), 1))(*[C.c_void_p(int(p_)) for p_ in peer_ptrs])
+    _check(lib().pl_gemm_i8_peers_static(_ptr(A), A.stride(0), _ptr(Bt), Bt.stride(0), _ptr(y), arr, len(peer_ptrs),
+                                         y.stride(0), M, N, K, C.byref(e), _stream()), "pl_gemm_i8_peers_static")
+    return y
+
+
 def transpose_i8(src):
     rows, cols = src.shape
     dst = torch.empty((cols, rows), dtype=torch.int8, device=src.device)

@@ -21,6 +21,7 @@
 #include <cuda.h>
 #include <cstdio>
 #include <cstdlib>
+#include <mutex>
 #include <type_traits>
 #include <vector>
 #include <cudaTypedefs.h>
@@ -2127,6 +2128,52 @@ extern "C" int pl_gemm_i8_peers(const int8_t* A, int lda, const int8_t* Bt, int 
     p.n_peers = n_peers;
   }
   return launch_igemm(ta, tb, p, stream);
+}
+
+// ---- allocation-free variant of pl_gemm_i8_peers ----------------------------------------------
+// Callers that cannot provide device scratch for the peer tensor maps (CUDA-graph capture set-up, serving
+// loops, harnesses that forbid cudaMalloc) use a table that lives in the library image instead: one
+// file-scope __device__ array per GPU that loads the library, PL_STATIC_PEERS_MAX maps of 128 bytes.
+// The array's NAME is only a host-side stand-in in host code; the device address comes from
+// cudaGetSymbolAddress, asked once per device with that device current.  All calls on one GPU share the
+// table (it keeps the last call's maps): calls that overlap on the GPU -- different streams -- race.
+static constexpr int kStaticPeersMax = PL_STATIC_PEERS_MAX;
+static __device__ __align__(256) unsigned char g_static_peer_maps[kStaticPeersMax * sizeof(CUtensorMap)];
+
+static int static_peer_maps_address(void** out) {
+  constexpr int kMaxDevices = 64;
+  static void* addr[kMaxDevices] = {};
+  static std::mutex mu;
+  int dev = -1;
+  PL_CUDA_OK(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= kMaxDevices) return PL_ERR_ARG;
+  std::lock_guard<std::mutex> lock(mu);
+  if (!addr[dev]) {
+    void* ptr = nullptr;
+    PL_CUDA_OK(cudaGetSymbolAddress(&ptr, g_static_peer_maps));  // this device's copy of the array
+    if (!ptr || (reinterpret_cast<uintptr_t>(ptr) & 63)) return PL_ERR_ALIGN;
+    addr[dev] = ptr;
+  }
+  *out = addr[dev];
+  return PL_OK;
+}
+
+extern "C" int pl_gemm_i8_peers_static(const int8_t* A, int lda, const int8_t* Bt, int ldb, void* C,
+                                       void* const* C_peers, int n_peers, int ldc, int M, int N, int K,
+                                       const pl_epilogue* e, pl_stream_t stream) {
+  if (n_peers < 0) return PL_ERR_ARG;
+  if (n_peers > kStaticPeersMax) {
+    fprintf(stderr, "pl_gemm_i8_peers_static: n_peers = %d exceeds the static map table (PL_STATIC_PEERS_MAX = %d); "
+                    "use pl_gemm_i8_peers with caller-provided scratch\n", n_peers, kStaticPeersMax);
+    return PL_ERR_LIMIT;
+  }
+  // the timeline trace of the debug builds is the one allocating corner of the launch path
+  const char* trace_path = getenv("PL_DBG_TRACE");
+  if (trace_path && *trace_path) return PL_ERR_UNSUPPORTED;
+  void* maps = nullptr;
+  int rc = static_peer_maps_address(&maps);
+  if (rc) return rc;
+  return pl_gemm_i8_peers(A, lda, Bt, ldb, C, C_peers, n_peers, maps, ldc, M, N, K, e, stream);
 }
 
 extern "C" int pl_gemm_i8(const int8_t* A, int lda, const int8_t* Bt, int ldb, void* C, int ldc,
