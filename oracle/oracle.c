@@ -14,6 +14,12 @@
 #include <omp.h>
 #endif
 
+/* bench.py --impl reference under torchrun inherits OMP_NUM_THREADS=1: the CPU arm sets its
+ * thread count explicitly */
+void orc_set_num_threads(int n) {
+  if (n > 0) omp_set_num_threads(n);
+}
+
 int orc_num_threads(void) {
 #ifdef _OPENMP
   return omp_get_max_threads();

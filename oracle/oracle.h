@@ -20,9 +20,22 @@
  *       text only for ARM, so the epilogue is pinned by restatement + the
  *       calib goldens (lite/kernels/arm/calib_compute_test.cc:37-69,
  *       lite/kernels/cuda/calib_compute_cuda_test.cc:35-46).
- *   mul / matmul / pool2d / elementwise_add int8 : no reference kernel exists on
- *       any target -- "parity unpinned", defined here by analogy (SURVEY 8a
- *       rows a7/a10/a11).
+ *       Since round 2 the last step -- saturate_cast<int8_t>(roundf(v)) -- is the
+ *       reference's own object code: saturate.h is compiled into oracle/_ref
+ *       (ref_saturate_cast_i8_f32) and orc_round_sat_i8 is checked against it on
+ *       every tie and every float neighbour of a tie (tests/test_oracle.py).
+ *   pool2d int8 : window / exclusive / average semantics pinned against the
+ *       reference's fp32 golden pool_compute_ref
+ *       (lite/kernels/cuda/pool_compute_test.cc:150-249, compiled from where it
+ *       lies into oracle/_ref/libref_extra.so) on the dequantised integers: max
+ *       and avg are identical in fp32, the int8 output is its requantisation.
+ *   mul / matmul int8 : accumulators pinned against the kernels-test baseline
+ *       matrix_mul + transpose (lite/tests/kernels/matmul_compute_test.cc:23-46)
+ *       for all four transpose combinations and the all-ones vector of
+ *       lite/kernels/cuda/matmul_compute_test.cc:33-95; the int8 epilogue is the
+ *       fc one.  No reference int8 mul/matmul kernel exists on any target.
+ *   elementwise_add int8, fused residual : no reference kernel exists on any
+ *       target -- "parity unpinned", defined here by analogy.
  *
  * All tensors are host pointers.  Activations are NHWC, filters OHWI
  * ([K, R, S, C/groups]) -- the kCUDA int8 layout of

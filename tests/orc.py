@@ -54,6 +54,23 @@ def ref():
     return _ref
 
 
+_ref_extra = None
+
+
+def ref_extra():
+    """Golden functions that live inside reference test files (pool_compute_ref, matrix_mul)."""
+    global _ref_extra
+    if _ref_extra is None:
+        _ref_extra = _load(os.path.join(ODIR, "_ref", "libref_extra.so"))
+    return _ref_extra
+
+
+def set_num_threads(n):
+    lib().orc_set_num_threads(int(n))
+    if ref() is not None and hasattr(ref(), "ref_set_num_threads"):
+        ref().ref_set_num_threads(int(n))
+
+
 def _p(a):
     return None if a is None else a.ctypes.data_as(C.c_void_p)
 
@@ -260,3 +277,75 @@ def ref_gemm_acc(A, B, trans_a=False, trans_b=False):
     r.ref_basic_gemm_i8(int(trans_a), int(trans_b), M, N, K, _p(A), A.shape[1],
                         _p(B), B.shape[1], _p(c), N)
     return c
+
+
+def ref_saturate_i8(v):
+    """saturate_cast<int8_t>(float) of lite/backends/arm/math/saturate.h:144-147, elementwise."""
+    r = ref()
+    assert r is not None
+    v = np.ascontiguousarray(v, np.float32)
+    out = np.empty(v.shape, np.int8)
+    r.ref_saturate_cast_i8_f32_n(_p(v), _p(out), C.c_longlong(v.size))
+    return out
+
+
+def ref_pool_nchw(x_nchw_f32, ksize, strides, pads, is_avg, exclusive=True, global_pooling=False, out_hw=None):
+    """pool_compute_ref of lite/kernels/cuda/pool_compute_test.cc:150-249 (fp32 NCHW)."""
+    r = ref_extra()
+    assert r is not None
+    x = np.ascontiguousarray(x_nchw_f32, np.float32)
+    N, Cc, H, W = x.shape
+    pt, pb, pl_, pr = pads
+    if global_pooling:
+        oh, ow = 1, 1
+    elif out_hw:
+        oh, ow = out_hw
+    else:
+        oh = (H + pt + pb - ksize[0]) // strides[0] + 1
+        ow = (W + pl_ + pr - ksize[1]) // strides[1] + 1
+    y = np.zeros((N, Cc, oh, ow), np.float32)
+    r.ref_pool_compute(_p(x), _p(y), N, Cc, H, W, oh, ow, ksize[0], ksize[1], strides[0], strides[1], pt, pb,
+                       pl_, pr, int(is_avg), int(exclusive), int(global_pooling))
+    return y
+
+
+def ref_matmul_f32(x, y, trans_x=False, trans_y=False, alpha=1.0):
+    """mul_low_efficiency's recipe (lite/tests/kernels/matmul_compute_test.cc:48-112) on the reference's
+    own matrix_mul / transpose: 2-D x, y."""
+    r = ref_extra()
+    assert r is not None
+    x = np.ascontiguousarray(x, np.float32)
+    y = np.ascontiguousarray(y, np.float32)
+    if trans_x:
+        xt = np.empty((x.shape[1], x.shape[0]), np.float32)
+        r.ref_transpose(x.shape[0], x.shape[1], _p(x), _p(xt))
+        x = xt
+    if trans_y:
+        yt = np.empty((y.shape[1], y.shape[0]), np.float32)
+        r.ref_transpose(y.shape[0], y.shape[1], _p(y), _p(yt))
+        y = yt
+    m, k = x.shape
+    n = y.shape[1]
+    out = np.empty((m, n), np.float32)
+    r.ref_matrix_mul(m, k, n, _f(alpha), _p(x), _p(y), _p(out))
+    return out
+
+
+def ref_deconv_nchw(x, w, bias, strides, pads, dil=(1, 1), group=1, relu=False):
+    """deconv_basic<float,float> of naive_math_impl.h:540-642.  x [N,Cin,H,W], w [Cin, Cout/g, kh, kw];
+    pads = (top, bottom, left, right)."""
+    r = ref()
+    assert r is not None
+    x = np.ascontiguousarray(x, np.float32)
+    w = np.ascontiguousarray(w, np.float32)
+    N, Cin, H, W = x.shape
+    _, cog, kh, kw = w.shape
+    Cout = cog * group
+    oh = (H - 1) * strides[0] - pads[0] - pads[1] + dil[0] * (kh - 1) + 1
+    ow = (W - 1) * strides[1] - pads[2] - pads[3] + dil[1] * (kw - 1) + 1
+    y = np.zeros((N, Cout, oh, ow), np.float32)
+    b = None if bias is None else np.ascontiguousarray(bias, np.float32)
+    r.ref_deconv_basic_f32(_p(x), _p(y), N, Cout, oh, ow, Cin, H, W, _p(w), _p(b), group, kw, kh, strides[1],
+                           strides[0], dil[1], dil[0], pads[2], pads[3], pads[0], pads[1], int(b is not None),
+                           int(relu))
+    return y

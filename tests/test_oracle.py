@@ -197,3 +197,91 @@ def test_relu_i8_oracle():
     x = np.arange(-128, 128, dtype=np.int8)
     assert np.array_equal(orc.relu_i8(x), np.maximum(x, 0))
     assert np.array_equal(orc.relu_i8(x, 47), np.clip(x, 0, 47))
+
+
+# ---- round 2: pins against more of the reference's own object code (oracle/_ref) -------------
+needs_ref = pytest.mark.skipif(orc.ref() is None or not hasattr(orc.ref(), "ref_saturate_cast_i8_f32_n"),
+                               reason="oracle/_ref not built (needs /root/reference)")
+needs_ref_extra = pytest.mark.skipif(orc.ref_extra() is None, reason="oracle/_ref/libref_extra.so not built")
+
+
+@needs_ref
+def test_round_saturate_is_the_references_saturate_cast():
+    """orc_round_sat_i8 (ARM convention) == max(saturate_cast<int8_t>(v), -127) with the reference's own
+    saturate.h:144-147 compiled into oracle/_ref: every tie k + 0.5, both float neighbours of every tie,
+    the clamp edges, and random values."""
+    ties = np.arange(-300, 300, dtype=np.float32) + np.float32(0.5)
+    vals = np.concatenate([ties, np.nextafter(ties, np.float32(np.inf)), np.nextafter(ties, np.float32(-np.inf)),
+                           np.arange(-300, 301, dtype=np.float32),
+                           np.array([0.0, -0.0, 126.5, 127.49999, 127.5, -126.5, -127.5, -127.49999, -128.5, 1e6, -1e6,
+                                     0.49999997, -0.49999997], np.float32),
+                           np.random.default_rng(3).uniform(-140, 140, 200000).astype(np.float32)])
+    want = np.maximum(orc.ref_saturate_i8(vals).astype(np.int32), -127).astype(np.int8)
+    L = orc.lib()
+    got = np.array([L.orc_round_sat_i8(orc._f(v), orc.ROUND_ARM) for v in vals[:3000]], np.int8)
+    assert np.array_equal(got, want[:3000])
+    # the vector path the kernels are compared with: quantize with scale 1 is round + saturate
+    assert np.array_equal(orc.quantize(vals, 1.0, orc.ROUND_ARM), want)
+
+
+@needs_ref_extra
+@pytest.mark.parametrize("k,s,p", [((3, 3), (2, 2), (1, 1, 1, 1)), ((2, 2), (2, 2), (0, 0, 0, 0)),
+                                   ((3, 3), (1, 1), (1, 1, 1, 1)), ((5, 3), (2, 1), (2, 2, 1, 1)),
+                                   ((7, 7), (1, 1), (0, 0, 0, 0))])
+@pytest.mark.parametrize("avg,exclusive", [(False, True), (True, True), (True, False)])
+def test_pool_oracle_vs_reference_pool_compute_ref(k, s, p, avg, exclusive):
+    """int8 pooling = the reference's fp32 golden on the integers: fp32 output identical, int8 output its
+    requantisation (lite/kernels/cuda/pool_compute_test.cc:150-249 compiled where it lies)."""
+    rng = np.random.default_rng(11)
+    x = rng.integers(-128, 128, (2, 9, 11, 5), dtype=np.int8)  # NHWC
+    ref = orc.ref_pool_nchw(x.transpose(0, 3, 1, 2).astype(np.float32), k, s, p, avg, exclusive)
+    ref = ref.transpose(0, 2, 3, 1)
+    typ = orc.POOL_AVG if avg else orc.POOL_MAX
+    got = orc.pool2d(x, k, s, p, typ, exclusive, 1.0, orc.OUT_FP32)
+    assert np.array_equal(got, ref)
+    for rescale in (1.0, 0.37):
+        q = orc.pool2d(x, k, s, p, typ, exclusive, rescale, orc.OUT_INT8)
+        want = orc.quantize(ref * np.float32(rescale), 1.0)
+        assert np.array_equal(q, want)
+
+
+@needs_ref_extra
+def test_pool_oracle_global_vs_reference():
+    rng = np.random.default_rng(12)
+    x = rng.integers(-128, 128, (3, 7, 7, 6), dtype=np.int8)
+    for avg in (False, True):
+        ref = orc.ref_pool_nchw(x.transpose(0, 3, 1, 2).astype(np.float32), (7, 7), (1, 1), (0, 0, 0, 0), avg,
+                                global_pooling=True).transpose(0, 2, 3, 1)
+        got = orc.pool2d(x, (7, 7), (1, 1), (0, 0, 0, 0), orc.POOL_AVG if avg else orc.POOL_MAX, True, 1.0,
+                         orc.OUT_FP32, global_pooling=True)
+        assert np.array_equal(got, ref)
+
+
+@needs_ref_extra
+@pytest.mark.parametrize("tx,ty", [(False, False), (False, True), (True, False), (True, True)])
+def test_matmul_acc_vs_reference_matrix_mul(tx, ty):
+    """int32 accumulators of the int8 mul / matmul contract == the kernels-test baseline (matrix_mul +
+    transpose, lite/tests/kernels/matmul_compute_test.cc:23-112) for every transpose combination; small
+    K keeps the fp32 baseline exact."""
+    rng = np.random.default_rng(21)
+    M, K, N = 13, 40, 9
+    X = rng.integers(-127, 128, (K, M) if tx else (M, K), dtype=np.int8)
+    Y = rng.integers(-127, 128, (N, K) if ty else (K, N), dtype=np.int8)
+    ref = orc.ref_matmul_f32(X.astype(np.float32), Y.astype(np.float32), tx, ty, 1.0)
+    acc = orc.gemm(X, Y, None, None, trans_a=tx, b_is_nk=ty, out=orc.OUT_INT32)
+    assert np.array_equal(acc.astype(np.float32), ref)
+    # alpha folds into the per-column scale: fp32 out within 1e-5 relative of the baseline with alpha
+    alpha = 0.25
+    sc = np.full(N, alpha, np.float32)
+    got = orc.gemm(X, Y, sc, None, trans_a=tx, b_is_nk=ty, out=orc.OUT_FP32)
+    ref_a = orc.ref_matmul_f32(X.astype(np.float32), Y.astype(np.float32), tx, ty, alpha)
+    assert np.allclose(got, ref_a, rtol=1e-5, atol=1e-6)
+
+
+def test_matmul_kat_all_ones():
+    """lite/kernels/cuda/matmul_compute_test.cc:33-95: x [4,1,2] ones, y [4,1,2] ones, transpose_Y -> 2."""
+    x = np.ones((4, 1, 2), np.int8)
+    y = np.ones((4, 1, 2), np.int8)
+    for b in range(4):
+        acc = orc.gemm(x[b], y[b], None, None, b_is_nk=True, out=orc.OUT_INT32)
+        assert acc.shape == (1, 1) and int(acc[0, 0]) == 2
