@@ -139,6 +139,12 @@ int pl_gemm_i8_peers(const int8_t* A, int lda, const int8_t* Bt, int ldb, void* 
                      int n_peers, void* maps_dev, int ldc, int M, int N, int K, const pl_epilogue* e,
                      pl_stream_t stream);
 
+/* One-off set-up for repeated / captured launches: encodes the peer maps for (C, ldc, M, N, K, e) and uploads
+ * them synchronously into maps_dev.  Afterwards pl_gemm_i8_peers may be called with C_peers == NULL (and the
+ * same n_peers, maps_dev, shape and epilogue): the call is then a single kernel launch -- nothing is encoded
+ * or copied, so it can be captured in a CUDA graph. */
+int pl_gemm_i8_peers_prepare(void* C, void* const* C_peers, int n_peers, void* maps_dev, int ldc, int M, int N,
+                             int K, const pl_epilogue* e);
 /* Allocation-free variant of pl_gemm_i8_peers.  NO COUNTERPART IN THE REFERENCE: added
  * for callers that cannot call cudaMalloc (code under CUDA-graph capture, tight serving
  * loops, harnesses that forbid it).  Same arithmetic, same outputs, same peer stores; the scratch that holds
@@ -211,6 +217,16 @@ pl_s2d_geometry pl_s2d_conv_geometry(int N, int H, int W, int C, int R, int S, i
                                      int pad_t, int pad_b, int pad_l, int pad_r, int dil_h, int dil_w);
 int pl_quantize_nchw_f32_to_s2d_i8(const float* x, int8_t* y_s2d, int N, int C, int H, int W,
                                    const pl_s2d_geometry* g, float scale, int round_mode, pl_stream_t stream);
+/* Narrow feeds of the same entry (the fp32 NCHW tensor is 154 MB per 256 images: PCIe-bound end to end).
+ * f16: q = calib((float)x).  u8: the image normalisation the reference applies on the host,
+ * x = ((float)u8 - mean[c]) * norm[c] (lite/utils/cv/image2tensor.cc, `(pixel - mean) * scale`), then the
+ * same calib step (lite/kernels/cuda/calib_compute.cu:27-95); mean / norm are HOST arrays of C floats.
+ * x must be aligned to 4 elements (8 / 4 bytes). */
+int pl_quantize_nchw_f16_to_s2d_i8(const void* x_f16, int8_t* y_s2d, int N, int C, int H, int W,
+                                   const pl_s2d_geometry* g, float scale, int round_mode, pl_stream_t stream);
+int pl_quantize_nchw_u8_to_s2d_i8(const uint8_t* x_u8, int8_t* y_s2d, int N, int C, int H, int W,
+                                  const pl_s2d_geometry* g, const float* mean, const float* norm, float scale,
+                                  int round_mode, pl_stream_t stream);
 size_t pl_s2d_conv_packed_weight_bytes(int K, const pl_s2d_geometry* g);
 int pl_pack_s2d_conv_weight_i8(const int8_t* w_ohwi, int8_t* w_s2d, int K, int R, int S, int C,
                                const pl_s2d_geometry* g, pl_stream_t stream);

@@ -208,10 +208,23 @@ def gemm_peers(A, Bt, scale, bias, y, peer_ptrs, maps_dev, act=ACT_NONE, act_arg
     K = A.shape[1] if K is None else K
     N = Bt.shape[0] if N is None else N
     e = make_epilogue(scale, bias, act, act_arg, OUT_INT8, rnd)
-    arr = (C.c_void_p * max(len(peer_ptrs), 1))(*[C.c_void_p(int(p_)) for p_ in peer_ptrs])
-    _check(lib().pl_gemm_i8_peers(_ptr(A), A.stride(0), _ptr(Bt), Bt.stride(0), _ptr(y), arr, len(peer_ptrs),
+    if isinstance(peer_ptrs, int):  # maps already uploaded by gemm_peers_prepare: launch only
+        arr, n_peers = None, peer_ptrs
+    else:
+        arr = (C.c_void_p * max(len(peer_ptrs), 1))(*[C.c_void_p(int(p_)) for p_ in peer_ptrs])
+        n_peers = len(peer_ptrs)
+    _check(lib().pl_gemm_i8_peers(_ptr(A), A.stride(0), _ptr(Bt), Bt.stride(0), _ptr(y), arr, n_peers,
                                   _ptr(maps_dev), y.stride(0), M, N, K, C.byref(e), _stream()), "pl_gemm_i8_peers")
     return y
+
+
+def gemm_peers_prepare(y, peer_ptrs, maps_dev, scale, bias, M, N, K, act=ACT_NONE, act_arg=0.0, rnd=ROUND_ARM):
+    """pl_gemm_i8_peers_prepare: one-off synchronous upload of the peer tensor maps; later gemm_peers calls pass
+    peer_ptrs = len(peer_ptrs) (an int) and are a single kernel launch."""
+    e = make_epilogue(scale, bias, act, act_arg, OUT_INT8, rnd)
+    arr = (C.c_void_p * len(peer_ptrs))(*[C.c_void_p(int(p_)) for p_ in peer_ptrs])
+    _check(lib().pl_gemm_i8_peers_prepare(_ptr(y), arr, len(peer_ptrs), _ptr(maps_dev), y.stride(0), M, N, K,
+                                          C.byref(e)), "pl_gemm_i8_peers_prepare")
 
 
 def gemm_peers_static(A, Bt, scale, bias, y, peer_ptrs, act=ACT_NONE, act_arg=0.0, rnd=ROUND_ARM, N=None, K=None):
@@ -323,12 +336,26 @@ def s2d_input_buffer(g, device):
     return torch.zeros(g.bytes, dtype=torch.int8, device=device)
 
 
-def quantize_nchw_to_s2d(x, scale, g, y=None, rnd=ROUND_ARM):
+def quantize_nchw_to_s2d(x, scale, g, y=None, rnd=ROUND_ARM, mean=None, norm=None):
+    """fp32 / fp16 / uint8 NCHW (by dtype of `x`) -> int8 space-to-depth input.  uint8 feeds take the image
+    normalisation x = (u8 - mean[c]) * norm[c] (host sequences of C floats) in front of the calib step."""
     N, Cc, H, W = x.shape
     if y is None:
         y = s2d_input_buffer(g, x.device)
-    _check(lib().pl_quantize_nchw_f32_to_s2d_i8(_ptr(x.contiguous()), _ptr(y), N, Cc, H, W, C.byref(g), _f(scale),
-                                                rnd, _stream()), "pl_quantize_nchw_f32_to_s2d_i8")
+    x = x.contiguous()
+    if x.dtype == torch.float32:
+        _check(lib().pl_quantize_nchw_f32_to_s2d_i8(_ptr(x), _ptr(y), N, Cc, H, W, C.byref(g), _f(scale),
+                                                    rnd, _stream()), "pl_quantize_nchw_f32_to_s2d_i8")
+    elif x.dtype == torch.float16:
+        _check(lib().pl_quantize_nchw_f16_to_s2d_i8(_ptr(x), _ptr(y), N, Cc, H, W, C.byref(g), _f(scale),
+                                                    rnd, _stream()), "pl_quantize_nchw_f16_to_s2d_i8")
+    elif x.dtype == torch.uint8:
+        m = (C.c_float * Cc)(*[float(v) for v in (mean if mean is not None else [0.0] * Cc)])
+        s_ = (C.c_float * Cc)(*[float(v) for v in (norm if norm is not None else [1.0] * Cc)])
+        _check(lib().pl_quantize_nchw_u8_to_s2d_i8(_ptr(x), _ptr(y), N, Cc, H, W, C.byref(g), m, s_, _f(scale),
+                                                   rnd, _stream()), "pl_quantize_nchw_u8_to_s2d_i8")
+    else:
+        raise TypeError(f"unsupported feed dtype {x.dtype}")
     return y
 
 

@@ -11,6 +11,8 @@
 //   layout      [N,C,HW] <-> [N,HW,C]  lite/backends/cuda/math/transpose.cu:31-184
 //   pool / add  no int8 kernel in the reference;
 //               window rules of lite/kernels/cuda/pool_compute.cu:28-130
+#include <cuda_fp16.h>
+
 #include "common.cuh"
 
 namespace pl {
@@ -229,13 +231,64 @@ quant_nchw_to_word_kernel(const float* __restrict__ x, uint4* __restrict__ y, in
   }
 }
 
-// fp32 NCHW -> int8 space-to-depth pixels (pl_int8.h: pl_s2d_geometry): thread = TWO adjacent
-// 16-byte pixels (4 original columns x 2 rows x 4 channels): float4 loads (one per channel and row),
-// one 32-byte store.  W % 4 != 0 leaves a last single pixel per row to the float2 path.  Only the
+// fp32 / fp16 / uint8 NCHW -> int8 space-to-depth pixels (pl_int8.h: pl_s2d_geometry): thread = TWO adjacent
+// 16-byte pixels (4 original columns x 2 rows x 4 channels): one 16 / 8 / 4-byte load per channel and row,
+// one 32-byte store.  W % 4 != 0 leaves a last single pixel per row to the half-width path.  Only the
 // interior is written: the borders stay zero from the caller's memset.
+// uint8 feeds carry the image normalisation of lite/utils/cv/image2tensor.cc (x = (u8 - mean[c]) * norm[c])
+// in front of the calib step, so a camera / decoder buffer needs a quarter of the fp32 tensor's PCIe bytes.
+struct FeedAffine {
+  float mean[4], norm[4];
+};
+template <typename TIn>
+__device__ __forceinline__ void feed_load(const TIn* p, bool four, bool vec4, float4& f);
+template <>
+__device__ __forceinline__ void feed_load<float>(const float* p, bool four, bool vec4, float4& f) {
+  if (four && vec4) {
+    f = __ldg(reinterpret_cast<const float4*>(p));
+  } else {
+    const float2 a = __ldg(reinterpret_cast<const float2*>(p));
+    f.x = a.x; f.y = a.y;
+    if (four) { const float2 b2 = __ldg(reinterpret_cast<const float2*>(p + 2)); f.z = b2.x; f.w = b2.y; }
+  }
+}
+template <>
+__device__ __forceinline__ void feed_load<__half>(const __half* p, bool four, bool vec4, float4& f) {
+  if (four && vec4) {
+    const uint2 u = __ldg(reinterpret_cast<const uint2*>(p));
+    const float2 a = __half22float2(*reinterpret_cast<const __half2*>(&u.x));
+    const float2 b2 = __half22float2(*reinterpret_cast<const __half2*>(&u.y));
+    f = make_float4(a.x, a.y, b2.x, b2.y);
+  } else {
+    const uint32_t u = __ldg(reinterpret_cast<const uint32_t*>(p));
+    const float2 a = __half22float2(*reinterpret_cast<const __half2*>(&u));
+    f.x = a.x; f.y = a.y;
+    if (four) {
+      const uint32_t v = __ldg(reinterpret_cast<const uint32_t*>(p + 2));
+      const float2 b2 = __half22float2(*reinterpret_cast<const __half2*>(&v));
+      f.z = b2.x; f.w = b2.y;
+    }
+  }
+}
+template <>
+__device__ __forceinline__ void feed_load<uint8_t>(const uint8_t* p, bool four, bool vec4, float4& f) {
+  if (four && vec4) {
+    const uint32_t u = __ldg(reinterpret_cast<const uint32_t*>(p));
+    f = make_float4((float)(u & 255u), (float)((u >> 8) & 255u), (float)((u >> 16) & 255u), (float)(u >> 24));
+  } else {
+    const uint32_t u = __ldg(reinterpret_cast<const uint16_t*>(p));
+    f.x = (float)(u & 255u); f.y = (float)(u >> 8);
+    if (four) {
+      const uint32_t v = __ldg(reinterpret_cast<const uint16_t*>(p + 2));
+      f.z = (float)(v & 255u); f.w = (float)(v >> 8);
+    }
+  }
+}
+
+template <typename TIn, bool AFFINE>
 __global__ void __launch_bounds__(256)
-quant_nchw_to_s2d_kernel(const float* __restrict__ x, uint4* __restrict__ y, int C, int H, int W, int HP, int WS,
-                         int pad_s, float scale, float inv, int round_mode) {
+quant_nchw_to_s2d_kernel(const TIn* __restrict__ x, uint4* __restrict__ y, int C, int H, int W, int HP, int WS,
+                         int pad_s, float scale, float inv, int round_mode, FeedAffine aff) {
   const int n = blockIdx.y;
   const int Ws = W >> 1, Hs = H >> 1, Wp = (Ws + 1) >> 1;  // pixel pairs per row
   const int item = blockIdx.x * blockDim.x + threadIdx.x;
@@ -243,7 +296,7 @@ quant_nchw_to_s2d_kernel(const float* __restrict__ x, uint4* __restrict__ y, int
   const int hs = item / Wp, wp = item - hs * Wp;
   const int ws = 2 * wp;
   const bool two = ws + 1 < Ws;
-  const float* xs = x + (long long)n * C * H * W + (long long)(2 * hs) * W + 2 * ws;
+  const TIn* xs = x + (long long)n * C * H * W + (long long)(2 * hs) * W + 2 * ws;
   int q[2][4][4];  // [dy][column 0..3][c]
 #pragma unroll
   for (int c = 0; c < 4; ++c) {
@@ -251,13 +304,12 @@ quant_nchw_to_s2d_kernel(const float* __restrict__ x, uint4* __restrict__ y, int
     for (int dy = 0; dy < 2; ++dy) {
       float4 f = make_float4(0.f, 0.f, 0.f, 0.f);
       if (c < C) {
-        const float* p = xs + (long long)c * H * W + dy * W;
-        if (two && (W & 3) == 0) {
-          f = __ldg(reinterpret_cast<const float4*>(p));
-        } else {
-          const float2 a = __ldg(reinterpret_cast<const float2*>(p));
-          f.x = a.x; f.y = a.y;
-          if (two) { const float2 b2 = __ldg(reinterpret_cast<const float2*>(p + 2)); f.z = b2.x; f.w = b2.y; }
+        feed_load<TIn>(xs + (long long)c * H * W + dy * W, two, (W & 3) == 0, f);
+        if (AFFINE) {
+          f.x = (f.x - aff.mean[c]) * aff.norm[c];
+          f.y = (f.y - aff.mean[c]) * aff.norm[c];
+          f.z = (f.z - aff.mean[c]) * aff.norm[c];
+          f.w = (f.w - aff.mean[c]) * aff.norm[c];
         }
       }
       q[dy][0][c] = c < C ? round_sat_i8(quant_pre(f.x, scale, inv, round_mode), round_mode) : 0;
@@ -669,18 +721,44 @@ extern "C" int pl_quantize_nchw_f32_to_nhwc_i8(const float* x, int8_t* y, int N,
   return launch_status();
 }
 
+template <typename TIn, bool AFFINE>
+static int launch_quant_s2d(const TIn* x, int8_t* y_s2d, int N, int C, int H, int W, const pl_s2d_geometry* g,
+                            float scale, int round_mode, const FeedAffine& aff, pl_stream_t stream) {
+  if (!x || !y_s2d || !g || !g->supported || N <= 0 || C <= 0 || C > 4 || !(scale > 0.f)) return PL_ERR_ARG;
+  if ((H & 1) || (W & 1) || N > 65535) return PL_ERR_UNSUPPORTED;
+  // rows are read with 4-element vector loads when W % 4 == 0: the base must be aligned to that vector
+  if (!al16(y_s2d) || (reinterpret_cast<uintptr_t>(x) & (4 * sizeof(TIn) - 1))) return PL_ERR_ALIGN;
+  const long long items = (long long)(H / 2) * ((W / 2 + 1) / 2);
+  dim3 grid((unsigned)((items + 255) / 256), (unsigned)N);
+  quant_nchw_to_s2d_kernel<TIn, AFFINE><<<grid, 256, 0, (cudaStream_t)stream>>>(
+      x, reinterpret_cast<uint4*>(y_s2d), C, H, W, g->HP, g->WS, g->pad_s, scale, 1.f / scale, round_mode, aff);
+  ++g_launches;
+  return launch_status();
+}
+
 extern "C" int pl_quantize_nchw_f32_to_s2d_i8(const float* x, int8_t* y_s2d, int N, int C, int H, int W,
                                               const pl_s2d_geometry* g, float scale, int round_mode,
                                               pl_stream_t stream) {
-  if (!x || !y_s2d || !g || !g->supported || N <= 0 || C <= 0 || C > 4 || !(scale > 0.f)) return PL_ERR_ARG;
-  if ((H & 1) || (W & 1) || N > 65535) return PL_ERR_UNSUPPORTED;
-  if (!al16(y_s2d) || (reinterpret_cast<uintptr_t>(x) & 15)) return PL_ERR_ALIGN;
-  const long long items = (long long)(H / 2) * ((W / 2 + 1) / 2);
-  dim3 grid((unsigned)((items + 255) / 256), (unsigned)N);
-  quant_nchw_to_s2d_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(x, reinterpret_cast<uint4*>(y_s2d), C, H, W, g->HP,
-                                                                  g->WS, g->pad_s, scale, 1.f / scale, round_mode);
-  ++g_launches;
-  return launch_status();
+  return launch_quant_s2d<float, false>(x, y_s2d, N, C, H, W, g, scale, round_mode, FeedAffine{}, stream);
+}
+
+extern "C" int pl_quantize_nchw_f16_to_s2d_i8(const void* x_f16, int8_t* y_s2d, int N, int C, int H, int W,
+                                              const pl_s2d_geometry* g, float scale, int round_mode,
+                                              pl_stream_t stream) {
+  return launch_quant_s2d<__half, false>(reinterpret_cast<const __half*>(x_f16), y_s2d, N, C, H, W, g, scale,
+                                         round_mode, FeedAffine{}, stream);
+}
+
+extern "C" int pl_quantize_nchw_u8_to_s2d_i8(const uint8_t* x_u8, int8_t* y_s2d, int N, int C, int H, int W,
+                                             const pl_s2d_geometry* g, const float* mean, const float* norm,
+                                             float scale, int round_mode, pl_stream_t stream) {
+  if (!mean || !norm || C <= 0 || C > 4) return PL_ERR_ARG;
+  FeedAffine aff{};
+  for (int c = 0; c < C; ++c) {
+    aff.mean[c] = mean[c];
+    aff.norm[c] = norm[c];
+  }
+  return launch_quant_s2d<uint8_t, true>(x_u8, y_s2d, N, C, H, W, g, scale, round_mode, aff, stream);
 }
 
 extern "C" int pl_pool2d_i8_nhwc(const int8_t* x, int ldx, void* y, int ldy, int N, int H, int W, int C,

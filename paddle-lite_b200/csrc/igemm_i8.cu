@@ -2092,8 +2092,10 @@ static void maybe_enable_mpair(IgemmParams& p, const pl_epilogue* e, int K, bool
 extern "C" int pl_gemm_i8_peers(const int8_t* A, int lda, const int8_t* Bt, int ldb, void* C, void* const* C_peers,
                                 int n_peers, void* maps_dev, int ldc, int M, int N, int K, const pl_epilogue* e,
                                 pl_stream_t stream) {
+  // C_peers == NULL with n_peers > 0: the maps in maps_dev were written by pl_gemm_i8_peers_prepare
+  // (the launch is then one kernel, nothing is encoded or copied: capturable in a CUDA graph)
   if (!A || !Bt || !C || M <= 0 || N <= 0 || K <= 0 || lda < K || ldb < K || ldc < N || n_peers < 0 || n_peers > 15 ||
-      (n_peers > 0 && (!C_peers || !maps_dev)))
+      (n_peers > 0 && !maps_dev))
     return PL_ERR_ARG;
   int rc = check_epi(e);
   if (rc) return rc;
@@ -2116,18 +2118,47 @@ extern "C" int pl_gemm_i8_peers(const int8_t* A, int lda, const int8_t* Bt, int 
   if (n_peers > 0) {
     // the peer stores exist only on the TMA-store epilogues (int8 out): same tile geometry as the local map
     if (e->out_dtype != PL_OUT_INT8 || !p.vec_ok) return PL_ERR_UNSUPPORTED;
-    const int PW = p.BN < 128 ? p.BN : 128;
-    CUtensorMap maps[15];
-    for (int i = 0; i < n_peers; ++i) {
-      if (!C_peers[i] || (reinterpret_cast<uintptr_t>(C_peers[i]) & 15)) return PL_ERR_ALIGN;
-      rc = encode_2d(&maps[i], C_peers[i], (uint64_t)N, (uint64_t)M, (uint64_t)ldc, PW, kBM);
-      if (rc) return rc;
+    if (C_peers) {
+      const int PW = p.BN < 128 ? p.BN : 128;
+      CUtensorMap maps[15];
+      for (int i = 0; i < n_peers; ++i) {
+        if (!C_peers[i] || (reinterpret_cast<uintptr_t>(C_peers[i]) & 15)) return PL_ERR_ALIGN;
+        rc = encode_2d(&maps[i], C_peers[i], (uint64_t)N, (uint64_t)M, (uint64_t)ldc, PW, kBM);
+        if (rc) return rc;
+      }
+      PL_CUDA_OK(cudaMemcpyAsync(maps_dev, maps, sizeof(CUtensorMap) * n_peers, cudaMemcpyHostToDevice, (cudaStream_t)stream));
     }
-    PL_CUDA_OK(cudaMemcpyAsync(maps_dev, maps, sizeof(CUtensorMap) * n_peers, cudaMemcpyHostToDevice, (cudaStream_t)stream));
     p.peer_maps = reinterpret_cast<const CUtensorMap*>(maps_dev);
     p.n_peers = n_peers;
   }
   return launch_igemm(ta, tb, p, stream);
+}
+
+// One-off set-up of the peer tensor maps for launches with C_peers == NULL: same tile geometry as the launch
+// computes for (C, ldc, M, N, K, e); the upload is synchronous (the maps come from the stack).
+extern "C" int pl_gemm_i8_peers_prepare(void* C, void* const* C_peers, int n_peers, void* maps_dev, int ldc, int M,
+                                        int N, int K, const pl_epilogue* e) {
+  if (!C || !C_peers || !maps_dev || n_peers <= 0 || n_peers > 15 || M <= 0 || N <= 0 || K <= 0 || ldc < N)
+    return PL_ERR_ARG;
+  int rc = check_epi(e);
+  if (rc) return rc;
+  if (!driver().ok) return PL_ERR_DRIVER;
+  if (reinterpret_cast<uintptr_t>(maps_dev) & 63) return PL_ERR_ALIGN;
+  IgemmParams p{};
+  p.BK = pl_conv_block_k(K);
+  p.mode = 0;
+  rc = common_setup(p, M, N, C, ldc, e, K, 1);
+  if (rc) return rc;
+  if (e->out_dtype != PL_OUT_INT8 || !p.vec_ok) return PL_ERR_UNSUPPORTED;
+  const int PW = p.BN < 128 ? p.BN : 128;
+  CUtensorMap maps[15];
+  for (int i = 0; i < n_peers; ++i) {
+    if (!C_peers[i] || (reinterpret_cast<uintptr_t>(C_peers[i]) & 15)) return PL_ERR_ALIGN;
+    rc = encode_2d(&maps[i], C_peers[i], (uint64_t)N, (uint64_t)M, (uint64_t)ldc, PW, kBM);
+    if (rc) return rc;
+  }
+  PL_CUDA_OK(cudaMemcpy(maps_dev, maps, sizeof(CUtensorMap) * n_peers, cudaMemcpyHostToDevice));
+  return PL_OK;
 }
 
 // ---- allocation-free variant of pl_gemm_i8_peers ----------------------------------------------

@@ -79,16 +79,16 @@ int plk_tensor_assign(void* t, int precision, int target, const int64_t* dims, i
   const bool cuda = target == static_cast<int>(TARGET(kCUDA));
   switch (static_cast<PrecisionType>(precision)) {
     case PRECISION(kInt8):
-      cuda ? T(t)->Assign<int8_t, TARGET(kCUDA)>(static_cast<const int8_t*>(host), d)
-           : T(t)->Assign<int8_t, TARGET(kHost)>(static_cast<const int8_t*>(host), d);
+      cuda ? T(t)->Assign<int8_t, paddle::lite::DDim, TARGET(kCUDA)>(static_cast<const int8_t*>(host), d)
+           : T(t)->Assign<int8_t, paddle::lite::DDim, TARGET(kHost)>(static_cast<const int8_t*>(host), d);
       break;
     case PRECISION(kInt32):
-      cuda ? T(t)->Assign<int32_t, TARGET(kCUDA)>(static_cast<const int32_t*>(host), d)
-           : T(t)->Assign<int32_t, TARGET(kHost)>(static_cast<const int32_t*>(host), d);
+      cuda ? T(t)->Assign<int32_t, paddle::lite::DDim, TARGET(kCUDA)>(static_cast<const int32_t*>(host), d)
+           : T(t)->Assign<int32_t, paddle::lite::DDim, TARGET(kHost)>(static_cast<const int32_t*>(host), d);
       break;
     case PRECISION(kFloat):
-      cuda ? T(t)->Assign<float, TARGET(kCUDA)>(static_cast<const float*>(host), d)
-           : T(t)->Assign<float, TARGET(kHost)>(static_cast<const float*>(host), d);
+      cuda ? T(t)->Assign<float, paddle::lite::DDim, TARGET(kCUDA)>(static_cast<const float*>(host), d)
+           : T(t)->Assign<float, paddle::lite::DDim, TARGET(kHost)>(static_cast<const float*>(host), d);
       break;
     default: LITE_FATAL("precision") << precision;
   }
@@ -105,7 +105,7 @@ int plk_tensor_to_host(void* t, void* dst, int64_t cap) {
   PLK_TRY
   CHECK_LE(static_cast<int64_t>(T(t)->memory_size()), cap);
   TargetWrapperCuda::DeviceSync();
-  T(t)->CopyToHost(dst);
+  paddle::lite::kernels::cuda::DownloadBytes(T(t), dst, T(t)->memory_size());
   PLK_CATCH
 }
 
@@ -302,7 +302,7 @@ int plk_run_pool(void* x, void* out, const char* type, const int* ksize, const i
 int plk_run_add(void* x, void* y, void* out, float x_scale, float y_scale, float out_scale, const char* act,
                 int out_int8) {
   PLK_TRY
-  ops::ElementwiseParam p;
+  ops::FusionElementwiseActivationParam p;
   p.X = T(x);
   p.Y = T(y);
   p.Out = T(out);
@@ -311,7 +311,7 @@ int plk_run_add(void* x, void* y, void* out, float x_scale, float y_scale, float
   p.y_input_scale = y_scale;
   p.output_scale = out_scale;
   p.act_type = act ? act : "";
-  auto k = CreateKernel("elementwise_add", TARGET(kCUDA), PRECISION(kInt8), DATALAYOUT(kNHWC),
+  auto k = CreateKernel("fusion_elementwise_add_activation", TARGET(kCUDA), PRECISION(kInt8), DATALAYOUT(kNHWC),
                         out_int8 ? PRECISION(kInt8) : PRECISION(kFloat));
   k->SetParam(p);
   LaunchAndSync(k.get(), 1);

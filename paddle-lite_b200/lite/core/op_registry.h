@@ -17,6 +17,8 @@
 #include "lite/core/kernel.h"
 #include "lite/core/type_system.h"
 
+using LiteType = paddle::lite::Type;  // lite/core/op_registry.h:31
+
 namespace paddle {
 namespace lite {
 

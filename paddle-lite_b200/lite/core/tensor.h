@@ -75,14 +75,6 @@ class Buffer {
   TargetType target_{TARGET(kHost)};
 };
 
-template <typename T>
-struct PrecisionOf;
-template <> struct PrecisionOf<float> { static constexpr PrecisionType v = PRECISION(kFloat); };
-template <> struct PrecisionOf<int8_t> { static constexpr PrecisionType v = PRECISION(kInt8); };
-template <> struct PrecisionOf<int32_t> { static constexpr PrecisionType v = PRECISION(kInt32); };
-template <> struct PrecisionOf<int64_t> { static constexpr PrecisionType v = PRECISION(kInt64); };
-template <> struct PrecisionOf<uint8_t> { static constexpr PrecisionType v = PRECISION(kUInt8); };
-
 class Tensor {
  public:
   Tensor() : buffer_(std::make_shared<Buffer>()) {}
@@ -97,7 +89,7 @@ class Tensor {
 
   template <typename T>
   T* mutable_data(TargetType target = TARGET(kHost)) {
-    precision_ = PrecisionOf<T>::v;
+    precision_ = lite_api::PrecisionTypeTrait<T>::Type();
     target_ = target;
     memory_size_ = static_cast<size_t>(numel()) * sizeof(T);
     buffer_->ResetLazy(target, memory_size_);
@@ -109,22 +101,15 @@ class Tensor {
   }
   const void* raw_data() const { return buffer_->data(); }
 
-  // host -> this tensor on `Target` (Tensor::Assign<T, DDim, Target> in the reference)
-  template <typename T, TargetType Target>
-  void Assign(const T* src, const DDim& dims) {
+  // host -> this tensor on `Target` (lite/core/tensor.h:106-113: Assign<DType, DimT, Target>)
+  template <typename T, typename DimT, TargetType Target>
+  void Assign(const T* src, const DimT& dims) {
     Resize(dims);
     T* dst = mutable_data<T>(Target);
     if (Target == TARGET(kCUDA))
       TargetWrapperCuda::MemcpySync(dst, src, memory_size_, IoDirection::HtoD);
     else
       std::memcpy(dst, src, memory_size_);
-  }
-  // device/host -> host copy of the payload
-  void CopyToHost(void* dst) const {
-    if (target_ == TARGET(kCUDA))
-      TargetWrapperCuda::MemcpySync(dst, buffer_->data(), memory_size_, IoDirection::DtoH);
-    else
-      std::memcpy(dst, buffer_->data(), memory_size_);
   }
   void ShareDataWith(const Tensor& o) {
     buffer_ = o.buffer_;

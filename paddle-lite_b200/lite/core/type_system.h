@@ -15,13 +15,14 @@ struct Type {
   TargetType target{TARGET(kUnk)};
   PrecisionType precision{PRECISION(kUnk)};
   DataLayoutType layout{DATALAYOUT(kUnk)};
-};
-
-struct LiteType {
+  Type() = default;
+  Type(TargetType t, PrecisionType p, DataLayoutType l) : target(t), precision(p), layout(l) {}
+  // lite/core/type_system.h:107-118 (returns a const Type* there; the kernel sources only ever write
+  // `{LiteType::GetTensorTy(...)}` inside BindInput / BindOutput, which both forms accept)
   static Type GetTensorTy(TargetType t, PrecisionType p = PRECISION(kFloat), DataLayoutType l = DATALAYOUT(kNCHW),
                           int device = 0) {
     (void)device;
-    return Type{t, p, l};
+    return Type(t, p, l);
   }
 };
 

@@ -1,6 +1,7 @@
 // Place / enum vocabulary of the plugin boundary.  Values are the reference's
 // (lite/api/paddle_place.h:45-114) so that serialized kernel keys stay compatible.
 #pragma once
+#include <cstdint>
 #include <string>
 
 namespace paddle {
@@ -51,6 +52,25 @@ inline const char* DataLayoutToStr(DataLayoutType l) {
     default: return "unk";
   }
 }
+
+// lite/api/paddle_place.h:147-175
+template <typename T>
+struct PrecisionTypeTrait {
+  constexpr static PrecisionType Type() { return PrecisionType::kUnk; }
+};
+#define PL_DEFINE_PRECISION_TRAIT(cpp_type, precision_type)                         \
+  template <>                                                                      \
+  struct PrecisionTypeTrait<cpp_type> {                                            \
+    constexpr static PrecisionType Type() { return PrecisionType::precision_type; } \
+  }
+PL_DEFINE_PRECISION_TRAIT(bool, kBool);
+PL_DEFINE_PRECISION_TRAIT(float, kFloat);
+PL_DEFINE_PRECISION_TRAIT(uint8_t, kUInt8);
+PL_DEFINE_PRECISION_TRAIT(int8_t, kInt8);
+PL_DEFINE_PRECISION_TRAIT(int16_t, kInt16);
+PL_DEFINE_PRECISION_TRAIT(int, kInt32);
+PL_DEFINE_PRECISION_TRAIT(int64_t, kInt64);
+#undef PL_DEFINE_PRECISION_TRAIT
 
 struct Place {
   TargetType target{TargetType::kUnk};

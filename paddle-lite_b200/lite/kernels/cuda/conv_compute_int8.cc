@@ -57,12 +57,12 @@ void ConvComputeInt8<Ptype_out>::PrepareForRun() {
     path_ = kThinIm2col;
     ldA_ = static_cast<int>(RoundUp(R * S * 4, 16));
     std::vector<int8_t> w(static_cast<size_t>(param.filter->numel()));
-    param.filter->CopyToHost(w.data());
+    DownloadBytes(param.filter, w.data(), w.size());
     std::vector<int8_t> bt(static_cast<size_t>(K) * ldA_, 0);
     for (int64_t k = 0; k < K; ++k)
       for (int64_t t = 0; t < R * S; ++t)
         for (int64_t c = 0; c < C; ++c) bt[k * ldA_ + t * 4 + c] = w[(k * R * S + t) * C + c];
-    packed_filter_.Assign<int8_t, TARGET(kCUDA)>(bt.data(), DDim({K, ldA_}));
+    packed_filter_.Assign<int8_t, lite::DDim, TARGET(kCUDA)>(bt.data(), DDim(std::vector<int64_t>{K, ldA_}));
   } else if (param.groups == 1) {
     path_ = kDense;
     const size_t bytes = pl_conv_packed_weight_bytes(static_cast<int>(K), static_cast<int>(R), static_cast<int>(S),
@@ -183,6 +183,5 @@ using ConvInt8Fp32 = paddle::lite::kernels::cuda::ConvComputeInt8<PRECISION(kFlo
       .BindOutput("Output", {LiteType::GetTensorTy(TARGET(kCUDA), PRECISION(kInt8), DATALAYOUT(kNHWC))})      \
       .Finalize();
 
-using paddle::lite::LiteType;
 REGISTER_CONV_INT8(conv2d)
 REGISTER_CONV_INT8(depthwise_conv2d)

@@ -214,7 +214,6 @@ class MatMulComputeInt8 : public KernelLite<TARGET(kCUDA), PRECISION(kInt8), DAT
 }  // namespace paddle
 
 namespace plk = paddle::lite::kernels::cuda;
-using paddle::lite::LiteType;
 using FcI8I8 = plk::FcComputeInt8<PRECISION(kInt8)>;
 using FcI8F32 = plk::FcComputeInt8<PRECISION(kFloat)>;
 using MulI8I8 = plk::MulComputeInt8<PRECISION(kInt8)>;

@@ -4,6 +4,7 @@
 // private copies like lite/kernels/arm/conv_gemmlike.cc:250-258), activation
 // decoding, and the C-ABI include (the "lite/backends/cuda/math" int8 entry points).
 #pragma once
+#include <cstring>
 #include <vector>
 
 #include "include/pl_int8.h"
@@ -11,13 +12,30 @@
 #include "lite/core/tensor.h"
 #include "lite/operators/op_params.h"
 
+// C-ABI status codes of include/pl_int8.h are CHECKed like CUDA_CALL (lite/backends/cuda/cuda_utils.h)
+#ifndef PL_CALL
+#define PL_CALL(expr)                                                          \
+  do {                                                                         \
+    int rc__ = (expr);                                                         \
+    CHECK_EQ(rc__, 0) << "pl_int8: " #expr " failed with status " << rc__;     \
+  } while (0)
+#endif
+
 namespace paddle {
 namespace lite {
 namespace kernels {
 namespace cuda {
 
 inline void UploadFloats(Tensor* t, const std::vector<float>& v) {
-  t->Assign<float, TARGET(kCUDA)>(v.data(), DDim({static_cast<int64_t>(v.size())}));
+  t->Assign<float, lite::DDim, TARGET(kCUDA)>(v.data(), DDim(std::vector<int64_t>{static_cast<int64_t>(v.size())}));
+}
+
+// payload of a kCUDA / host tensor -> host memory
+inline void DownloadBytes(const Tensor* t, void* dst, size_t bytes) {
+  if (t->target() == TARGET(kCUDA))
+    TargetWrapperCuda::MemcpySync(dst, t->raw_data(), bytes, IoDirection::DtoH);
+  else
+    std::memcpy(dst, t->raw_data(), bytes);
 }
 
 inline std::vector<float> DownloadFloats(const Tensor* t) {

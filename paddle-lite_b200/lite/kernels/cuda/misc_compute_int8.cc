@@ -40,7 +40,7 @@ class CalibComputeInt8ToFp32 : public KernelLite<TARGET(kCUDA), PRECISION(kInt8)
 };
 
 template <typename T, bool ToNHWC>
-class LayoutCompute : public KernelLite<TARGET(kCUDA), PrecisionOf<T>::v, DATALAYOUT(kNCHW)> {
+class LayoutCompute : public KernelLite<TARGET(kCUDA), lite_api::PrecisionTypeTrait<T>::Type(), DATALAYOUT(kNCHW)> {
  public:
   using param_t = operators::LayoutParam;
   void Run() override {
@@ -138,14 +138,20 @@ class PoolComputeInt8 : public KernelLite<TARGET(kCUDA), PRECISION(kInt8), DATAL
   }
 };
 
-template <PrecisionType Ptype_out>
+// elementwise_add (ElementwiseParam) and fusion_elementwise_add_activation
+// (FusionElementwiseActivationParam: + act_type), lite/operators/op_params.h:643-680
+template <PrecisionType Ptype_out, typename ParamT>
 class ElementwiseAddInt8 : public KernelLite<TARGET(kCUDA), PRECISION(kInt8), DATALAYOUT(kNHWC)> {
  public:
-  using param_t = operators::ElementwiseParam;
+  using param_t = ParamT;
+  static int ActOf(const operators::ElementwiseParam&) { return PL_ACT_NONE; }
+  static int ActOf(const operators::FusionElementwiseActivationParam& p) {
+    CHECK(p.act_type == "" || p.act_type == "relu") << "int8 fused elementwise_add: relu only";
+    return p.act_type == "relu" ? PL_ACT_RELU : PL_ACT_NONE;
+  }
   void Run() override {
-    auto& param = this->Param<param_t>();
+    auto& param = this->template Param<param_t>();
     CHECK(param.X->dims() == param.Y->dims()) << "int8 elementwise_add needs equal shapes (residual add)";
-    CHECK(param.act_type == "" || param.act_type == "relu");
     param.Out->Resize(param.X->dims());
     const bool out_int8 = Ptype_out == PRECISION(kInt8);
     void* y = out_int8 ? static_cast<void*>(param.Out->template mutable_data<int8_t>(TARGET(kCUDA)))
@@ -153,10 +159,11 @@ class ElementwiseAddInt8 : public KernelLite<TARGET(kCUDA), PRECISION(kInt8), DA
     const float sa = out_int8 ? param.x_input_scale / param.output_scale : param.x_input_scale;
     const float sb = out_int8 ? param.y_input_scale / param.output_scale : param.y_input_scale;
     PL_CALL(pl_add_i8(param.X->template data<int8_t>(), param.Y->template data<int8_t>(), y, param.X->numel(), sa, sb,
-                      param.act_type == "relu" ? PL_ACT_RELU : PL_ACT_NONE, 0.f, out_int8 ? PL_OUT_INT8 : PL_OUT_FP32,
-                      PL_ROUND_ARM, StreamOf(ctx_.get())));
+                      ActOf(param), 0.f, out_int8 ? PL_OUT_INT8 : PL_OUT_FP32, PL_ROUND_ARM,
+                      StreamOf(this->ctx_.get())));
   }
 };
+
 
 // ---- channel movement between int8 NHWC ops (no calib / layout round trip inside a network) ----
 // The op descs keep the model's NCHW axis numbering: channels are axis 1 (or -3); the tensors
@@ -260,15 +267,16 @@ class ReluComputeInt8 : public KernelLite<TARGET(kCUDA), PRECISION(kInt8), DATAL
 }  // namespace paddle
 
 namespace plk = paddle::lite::kernels::cuda;
-using paddle::lite::LiteType;
 using NCHW2NHWCInt8 = plk::LayoutCompute<int8_t, true>;
 using NHWC2NCHWInt8 = plk::LayoutCompute<int8_t, false>;
 using NCHW2NHWCFp32 = plk::LayoutCompute<float, true>;
 using NHWC2NCHWFp32 = plk::LayoutCompute<float, false>;
 using PoolI8I8 = plk::PoolComputeInt8<PRECISION(kInt8)>;
 using PoolI8F32 = plk::PoolComputeInt8<PRECISION(kFloat)>;
-using AddI8I8 = plk::ElementwiseAddInt8<PRECISION(kInt8)>;
-using AddI8F32 = plk::ElementwiseAddInt8<PRECISION(kFloat)>;
+using AddI8I8 = plk::ElementwiseAddInt8<PRECISION(kInt8), paddle::lite::operators::ElementwiseParam>;
+using AddI8F32 = plk::ElementwiseAddInt8<PRECISION(kFloat), paddle::lite::operators::ElementwiseParam>;
+using AddActI8I8 = plk::ElementwiseAddInt8<PRECISION(kInt8), paddle::lite::operators::FusionElementwiseActivationParam>;
+using AddActI8F32 = plk::ElementwiseAddInt8<PRECISION(kFloat), paddle::lite::operators::FusionElementwiseActivationParam>;
 
 #define REG_CALIB(op__)                                                                             \
   REGISTER_LITE_KERNEL(op__, kCUDA, kInt8, kNCHW, plk::CalibComputeFp32ToInt8, fp32_to_int8)         \
@@ -328,6 +336,16 @@ REGISTER_LITE_KERNEL(elementwise_add, kCUDA, kInt8, kNHWC, AddI8I8, int8_out)
     .BindOutput("Out", {LiteType::GetTensorTy(TARGET(kCUDA), PRECISION(kInt8), DATALAYOUT(kNHWC))})
     .Finalize();
 REGISTER_LITE_KERNEL(elementwise_add, kCUDA, kInt8, kNHWC, AddI8F32, fp32_out)
+    .BindInput("X", {LiteType::GetTensorTy(TARGET(kCUDA), PRECISION(kInt8), DATALAYOUT(kNHWC))})
+    .BindInput("Y", {LiteType::GetTensorTy(TARGET(kCUDA), PRECISION(kInt8), DATALAYOUT(kNHWC))})
+    .BindOutput("Out", {LiteType::GetTensorTy(TARGET(kCUDA), PRECISION(kFloat), DATALAYOUT(kNHWC))})
+    .Finalize();
+REGISTER_LITE_KERNEL(fusion_elementwise_add_activation, kCUDA, kInt8, kNHWC, AddActI8I8, int8_out)
+    .BindInput("X", {LiteType::GetTensorTy(TARGET(kCUDA), PRECISION(kInt8), DATALAYOUT(kNHWC))})
+    .BindInput("Y", {LiteType::GetTensorTy(TARGET(kCUDA), PRECISION(kInt8), DATALAYOUT(kNHWC))})
+    .BindOutput("Out", {LiteType::GetTensorTy(TARGET(kCUDA), PRECISION(kInt8), DATALAYOUT(kNHWC))})
+    .Finalize();
+REGISTER_LITE_KERNEL(fusion_elementwise_add_activation, kCUDA, kInt8, kNHWC, AddActI8F32, fp32_out)
     .BindInput("X", {LiteType::GetTensorTy(TARGET(kCUDA), PRECISION(kInt8), DATALAYOUT(kNHWC))})
     .BindInput("Y", {LiteType::GetTensorTy(TARGET(kCUDA), PRECISION(kInt8), DATALAYOUT(kNHWC))})
     .BindOutput("Out", {LiteType::GetTensorTy(TARGET(kCUDA), PRECISION(kFloat), DATALAYOUT(kNHWC))})

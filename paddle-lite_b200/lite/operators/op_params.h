@@ -128,7 +128,11 @@ struct ElementwiseParam : ParamBase {
   WITH_INT8_CONFIG
   float x_input_scale{1.0};
   float y_input_scale{1.0};
-  std::string act_type{""};  // fusion_elementwise_add_activation
+};
+
+// lite/operators/op_params.h:678-680
+struct FusionElementwiseActivationParam : public ElementwiseParam {
+  std::string act_type;
 };
 
 // lite/operators/op_params.h:369-389 (ConcatParam), 590-612 (SplitParam), 258-263 (ShuffleChannelParam)

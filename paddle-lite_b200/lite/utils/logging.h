@@ -49,9 +49,4 @@ struct Voidify {
     cudaError_t e__ = (expr);                                                            \
     if (e__ != cudaSuccess) LITE_FATAL("CUDA:") << cudaGetErrorString(e__) << " in " #expr; \
   } while (0)
-// C-ABI status codes of include/pl_int8.h are CHECKed the same way
-#define PL_CALL(expr)                                                     \
-  do {                                                                    \
-    int rc__ = (expr);                                                    \
-    if (rc__ != 0) LITE_FATAL("pl_int8:") << #expr << " returned " << rc__; \
-  } while (0)
+

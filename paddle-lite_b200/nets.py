@@ -238,7 +238,11 @@ class DeviceNet:
     activation scales (abs-max / 127 on a calibration batch, computed with the fp32-out
     kernels); `run()` enqueues the int8 network on the current stream."""
 
-    def __init__(self, prog, batch, device="cuda"):
+    FEEDS = {"f32": torch.float32, "f16": torch.float16, "u8": torch.uint8}
+
+    def __init__(self, prog, batch, device="cuda", feed="f32", mean=None, norm=None):
+        """feed: element type of the NCHW input tensor.  "u8" is a raw image: the entry kernel applies
+        x = (u8 - mean[c]) * norm[c] (the reference's host-side image2tensor step) before the calib."""
         self.prog = prog
         self.batch = batch
         self.dev = device
@@ -246,7 +250,10 @@ class DeviceNet:
         self.layers = []
         self.graph = None
         H, W, C = prog.shapes["input"]
-        self.input = torch.zeros((batch, C, H, W), dtype=torch.float32, device=device)  # NCHW fp32
+        self.feed = feed
+        self.mean = list(mean) if mean is not None else [0.0] * C
+        self.norm = list(norm) if norm is not None else [1.0] * C
+        self.input = torch.zeros((batch, C, H, W), dtype=self.FEEDS[feed], device=device)  # NCHW
         self.calibrated = all(op.get("out_scale", 1.0) is not None or op.kind == "fc" for op in prog.ops)
         self._weights_to_device()
 
@@ -324,13 +331,20 @@ class DeviceNet:
         vals = _Views(self.prog.views, True)
         for op in self.prog.ops:
             if op.kind == "quant_in":
-                op.out_scale = float(x_nchw.abs().max().item()) / 127.0
+                xf = x_nchw.float()
+                if self.feed == "u8":
+                    C_ = xf.shape[1]
+                    xf = (xf - torch.tensor(self.mean, device=xf.device).view(1, C_, 1, 1)) * \
+                        torch.tensor(self.norm, device=xf.device).view(1, C_, 1, 1)
+                op.out_scale = float(xf.abs().max().item()) / 127.0
                 C_in = x_nchw.shape[1]
                 if op.dst in self.s2d_src:
                     vals[op.dst] = pl.quantize_nchw_to_s2d(x_nchw.contiguous(), op.out_scale,
-                                                           self._s2d_geometry(self.s2d_src[op.dst], n))
+                                                           self._s2d_geometry(self.s2d_src[op.dst], n),
+                                                           mean=self.mean, norm=self.norm)
                     vals[op.dst]._pl_n = n
                 else:
+                    assert self.feed == "f32", "narrow feeds exist for the space-to-depth stems only"
                     vals[op.dst] = pl.quantize_nchw_to_nhwc(x_nchw.contiguous(), op.out_scale,
                                                             4 if C_in <= 4 else rup(C_in, 16))
                 scales[op.dst] = op.out_scale
@@ -437,8 +451,9 @@ class DeviceNet:
                 y._pl_n = self.batch
                 self.s2d_bufs[op.dst] = (y, g)
                 self.layers.append((op, lambda op=op, y=y, g=g: pl.quantize_nchw_to_s2d(
-                    self.input, op.out_scale, g, y=y)))
+                    self.input, op.out_scale, g, y=y, mean=self.mean, norm=self.norm)))
             elif op.kind == "quant_in":
+                assert self.feed == "f32", "narrow feeds exist for the space-to-depth stems only"
                 y = self._buf(op.dst)
                 self.layers.append((op, lambda op=op, y=y: pl.quantize_nchw_to_nhwc(
                     self.input, op.out_scale, y.shape[-1], y=y)))
@@ -496,8 +511,22 @@ class DeviceNet:
         self.graph = g
         return self
 
-    def replay(self):
-        self.graph.replay()
+    def capture_inputs(self, n=2):
+        """One CUDA graph per fp32 input buffer (`self.inputs[i]`): a feeder can copy batch i+1 from pinned
+        host memory straight into the other buffer while graph i runs -- no staging copy on the device.
+        The graphs differ only in the pointer their first kernel reads; every activation buffer is shared."""
+        self.inputs = [self.input] + [torch.zeros_like(self.input) for _ in range(n - 1)]
+        self.graphs = []
+        first = self.input
+        for buf in self.inputs:
+            self.input = buf
+            self.capture()
+            self.graphs.append(self.graph)
+        self.input, self.graph = first, self.graphs[0]
+        return self
+
+    def replay(self, i=None):
+        (self.graph if i is None else self.graphs[i]).replay()
         return self.output
 
     def forward(self, x_nchw):

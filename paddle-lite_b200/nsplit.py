@@ -99,26 +99,48 @@ class NSplitGemm:
     # -- fused GEMM + all-gather over NVLink peer memory (int8 out) --------------------------------
     def fused_setup(self, M):
         """Allocates the full result [M, world * per] in symmetric memory (every rank maps every other
-        rank's buffer) and the device scratch for the peer tensor maps."""
+        rank's buffer) -- TWO of them, used alternately -- and uploads the peer tensor maps of both once
+        (pl_gemm_i8_peers_prepare), so that a fused() call is one kernel launch + one device-side barrier.
+
+        Why two buffers: rank A's call n+1 stores into rank B's result while B may still be reading the
+        result of call n (nothing orders A's peer stores after B's consumer).  With alternating buffers the
+        stores of call n+2 are the first to touch buffer (n mod 2) again, and A cannot start call n+2 before
+        it has passed the barrier of call n+1, which B only enters after its consumer of call n (stream
+        order on B).  No extra barrier is needed."""
         import torch.distributed._symmetric_memory as symm_mem
         assert self.out_dtype == self.pl.OUT_INT8, "peer stores exist on the int8 TMA-store epilogue only"
-        full = symm_mem.empty((M, self.world * self.per), dtype=torch.int8, device=self.device)
-        hdl = symm_mem.rendezvous(full, self.group if self.group is not None else dist.group.WORLD)
+        grp = self.group if self.group is not None else dist.group.WORLD
         off = self.rank * self.per  # this rank's column block inside everybody's result
-        self._full, self._hdl, self._fM = full, hdl, M
-        self._peer_ptrs = [int(hdl.buffer_ptrs[r]) + off for r in range(self.world) if r != self.rank]
-        self._maps = torch.empty(128 * 16, dtype=torch.uint8, device=self.device)
-        return full
+        self._fulls, self._hdls, self._maps, self._ys = [], [], [], []
+        self._n_peers = self.world - 1
+        for _ in range(2):
+            full = symm_mem.empty((M, self.world * self.per), dtype=torch.int8, device=self.device)
+            hdl = symm_mem.rendezvous(full, grp)
+            peer_ptrs = [int(hdl.buffer_ptrs[r]) + off for r in range(self.world) if r != self.rank]
+            maps = torch.empty(128 * 16, dtype=torch.uint8, device=self.device)
+            y = full[:, off:off + self.per]
+            if peer_ptrs:
+                self.pl.gemm_peers_prepare(y, peer_ptrs, maps, self.scale, self.bias, M, self.per, self.K,
+                                           self.act, self.act_arg)
+            self._fulls.append(full)
+            self._hdls.append(hdl)
+            self._maps.append(maps)
+            self._ys.append(y)
+        self._fM, self._turn = M, 0
+        self._full = self._fulls[0]
+        return self._fulls[0]
 
     def fused(self, A_dev):
         """C[M, N] on every rank: each rank's GEMM kernel TMA-stores its output tiles into its own result
         buffer and straight into the peers' (NVLink), overlapped with the mainloop; one device-side barrier
-        of the ranks afterwards.  No collective call, no de-interleaving copy."""
+        of the ranks afterwards.  No collective call, no de-interleaving copy.  The returned view is valid
+        until the second next fused() call (two result buffers alternate, see fused_setup)."""
         M = A_dev.shape[0]
         if getattr(self, "_fM", None) != M:
             self.fused_setup(M)
-        y = self._full[:, self.rank * self.per:(self.rank + 1) * self.per]
-        self.pl.gemm_peers(A_dev, self.bt, self.scale, self.bias, y, self._peer_ptrs, self._maps, self.act,
-                           self.act_arg, N=self.per, K=self.K)
-        self._hdl.barrier()
-        return self._full[:, :self.N]
+        t = self._turn
+        self._turn ^= 1
+        self.pl.gemm_peers(A_dev, self.bt, self.scale, self.bias, self._ys[t], self._n_peers, self._maps[t],
+                           self.act, self.act_arg, N=self.per, K=self.K)
+        self._hdls[t].barrier()
+        return self._fulls[t][:, :self.N]

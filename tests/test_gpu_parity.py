@@ -665,6 +665,36 @@ def test_s2d_quantiser_layout(pl):
     assert not buf[N * g.HP * g.WS * 16:].any()
 
 
+@pytest.mark.parametrize("W", [12, 10, 224])
+@pytest.mark.parametrize("feed", ["f16", "u8"])
+def test_s2d_quantiser_narrow_feeds(pl, feed, W):
+    """fp16 / uint8 feeds of the s2d entry kernel == the oracle's calib on the same fp32 values (u8: after the
+    image normalisation (u8 - mean) * norm of lite/utils/cv/image2tensor.cc, evaluated in fp32)."""
+    rng = np.random.default_rng(13)
+    N, Cc, H = 2, 3, 8
+    g = pl.s2d_geometry(N, H, W, Cc, 7, 7, (2, 2), (3, 3, 3, 3))
+    if feed == "f16":
+        xh = rng.uniform(-1, 1, (N, Cc, H, W)).astype(np.float16)
+        xf = xh.astype(np.float32)
+        scale = 1 / 127
+        buf = host(pl.quantize_nchw_to_s2d(dev(xh), scale, g))
+    else:
+        xu = rng.integers(0, 256, (N, Cc, H, W), dtype=np.uint8)
+        mean = np.array([123.675, 116.28, 103.53], np.float32)
+        norm = (1.0 / np.array([58.395, 57.12, 57.375], np.float32)).astype(np.float32)
+        xf = (xu.astype(np.float32) - mean.reshape(1, 3, 1, 1)) * norm.reshape(1, 3, 1, 1)
+        scale = float(np.abs(xf).max()) / 127
+        buf = host(pl.quantize_nchw_to_s2d(dev(xu), scale, g, mean=mean, norm=norm))
+    q = orc.quantize(xf, scale)
+    img = buf[: N * g.HP * g.WS * 16].reshape(N, g.HP, g.WS, 2, 2, 4)
+    want = np.zeros_like(img)
+    for dy in range(2):
+        for dx in range(2):
+            want[:, g.pad_s:g.pad_s + H // 2, g.pad_s:g.pad_s + W // 2, dy, dx, :Cc] = \
+                q[:, :, dy::2, dx::2].transpose(0, 2, 3, 1)
+    assert np.array_equal(img, want)
+
+
 def test_s2d_geometry_rejects(pl):
     assert not pl.s2d_geometry(1, 32, 32, 3, 7, 7, (1, 1), (3, 3, 3, 3)).supported      # stride 1
     assert not pl.s2d_geometry(1, 31, 32, 3, 7, 7, (2, 2), (3, 3, 3, 3)).supported      # odd height

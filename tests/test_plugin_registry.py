@@ -120,3 +120,18 @@ def test_type_plan_resnet_block_and_fp32_tail(lh):
     plan2 = lh.plan_types(ops2, extension=True)
     assert plan2["picked"][2] == "relu/def/cuda/float/NCHW"
     assert plan2["picked"][1] == "conv2d/fp32_out/cuda/int8_t/NHWC"
+
+
+def test_kernel_sources_compile_against_reference_headers():
+    """The drop-in claim: the kernel class sources compile byte for byte against the reference's own
+    lite/core / lite/operators headers (tools/check_dropin.sh; only the CMake-generated version.h and the
+    documented MatMulParam / ActivationParam int8-config edit come from outside the reference tree)."""
+    import os
+    import subprocess
+    ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    if not os.path.isdir("/root/reference/lite/core"):
+        pytest.skip("reference tree not present on this machine")
+    out = subprocess.run(["bash", os.path.join(ROOT, "tools", "check_dropin.sh"), "/root/reference"],
+                         capture_output=True, text=True)
+    assert out.returncode == 0, out.stdout + out.stderr
+    assert out.stdout.count("ok  ") == 3
