@@ -278,6 +278,13 @@ __device__ __forceinline__ void tma_load_4d(uint32_t dst, const void* desc, uint
       "l"(desc), "r"(bar), "r"(c0), "r"(c1), "r"(c2), "r"(c3)
       : "memory");
 }
+__device__ __forceinline__ void tma_load_3d(uint32_t dst, const void* desc, uint32_t bar, int c0, int c1, int c2) {
+  asm volatile(
+      "cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes"
+      " [%0], [%1, {%3, %4, %5}], [%2];" ::"r"(dst),
+      "l"(desc), "r"(bar), "r"(c0), "r"(c1), "r"(c2)
+      : "memory");
+}
 // 1-D bulk copy global -> shared (no tensor map): `bytes` contiguous bytes, 16-byte aligned both sides
 __device__ __forceinline__ void bulk_load_1d(uint32_t dst, const void* src, uint32_t bytes, uint32_t bar) {
   asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dst),

@@ -10,7 +10,9 @@
 // Fast path (3x3, stride 1 or 2, dilation 1): see dw3x3s1_kernel / dw3x3s2_kernel.
 // Generic path (any R,S,stride,dilation): one dp4a per MAC against a byte-masked
 // weight word.
+#include <cuda.h>
 #include <cstdlib>
+#include <cudaTypedefs.h>
 
 #include "common.cuh"
 
@@ -157,6 +159,30 @@ __device__ __forceinline__ void dw_finish4(const DwParams& p, const int (&acc)[4
     const float s4[4] = {sc.x, sc.y, sc.z, sc.w}, b4[4] = {bs.x, bs.y, bs.z, bs.w};
     dw_store4(p, raw, s4, b4, (long long)pix, c0);
   }
+}
+
+// FAST epilogue of 4 channels of one output pixel straight to a word pointer (the staged kernel keeps a row
+// pointer per item instead of re-deriving pixel * pitch + channel for every pixel)
+__device__ __forceinline__ void dw_finish4_ptr(const int (&acc)[4], const float4 sc, const float4 bs, uint32_t hi_bits,
+                                               uint32_t* dst) {
+  const uint64_t off = dw_pk2(-12582912.f, -12582912.f);
+  const uint64_t f01 = dw_fadd2_rn(dw_pk2(__int_as_float(acc[0]), __int_as_float(acc[1])), off);
+  const uint64_t f23 = dw_fadd2_rn(dw_pk2(__int_as_float(acc[2]), __int_as_float(acc[3])), off);
+  const uint64_t v01 = dw_ffma2(f01, dw_pk2(sc.x, sc.y), dw_pk2(bs.x, bs.y));
+  const uint64_t v23 = dw_ffma2(f23, dw_pk2(sc.z, sc.w), dw_pk2(bs.z, bs.w));
+  float v0, v1, v2, v3;
+  dw_upk2(v01, v0, v1);
+  dw_upk2(v23, v2, v3);
+  const int c0_ = __vimin_s32_relu(__float_as_int(v0), (int)hi_bits);
+  const int c1_ = __vimin_s32_relu(__float_as_int(v1), (int)hi_bits);
+  const int c2_ = __vimin_s32_relu(__float_as_int(v2), (int)hi_bits);
+  const int c3_ = __vimin_s32_relu(__float_as_int(v3), (int)hi_bits);
+  const uint64_t big = dw_pk2(32768.5f, 32768.5f);
+  const uint64_t u01 = dw_fadd2_rm(dw_pk2(__int_as_float(c0_), __int_as_float(c1_)), big);
+  const uint64_t u23 = dw_fadd2_rm(dw_pk2(__int_as_float(c2_), __int_as_float(c3_)), big);
+  const uint32_t p01 = prmt((uint32_t)u01, (uint32_t)(u01 >> 32), 0x0051);
+  const uint32_t p23 = prmt((uint32_t)u23, (uint32_t)(u23 >> 32), 0x0051);
+  *dst = prmt(p01, p23, 0x5410);
 }
 
 struct DwItem {
@@ -456,6 +482,249 @@ __global__ void __launch_bounds__(256, 4) dw3x3s2_kernel(const DwParams p) {
 }
 
 // ---------------------------------------------------------------------------
+// 3x3 stride 1 / 2, shared-memory staged (the default fast path since round 2)
+//
+// The register-window kernels above are instruction-issue bound (ncu: 17 thread-instructions per output
+// byte, 63 % issue utilisation at 2.3 TB/s): per-item decode, clamped addresses, row / column masks and
+// 32-bit global loads.  Here a persistent CTA walks tiles of TR output rows x TQ output columns x CC
+// channels.  One 4-D TMA box per tile brings the input rows WITH their halo into shared memory
+// (hardware zero fill = the padding: no masks, no clamps), a ring of 2-4 boxes per CTA keeps >= 64 KB
+// of loads in flight per SM whatever the thread count, and every thread streams DOWN its strip of 4 (2)
+// output columns x 4 channels: each input row is read from shared memory and byte-transposed once,
+// feeds the three output rows in flight (accumulator slots rotate through the unrolled loop), and each
+// finished output row leaves through the packed epilogue.  ~8 thread-instructions per output byte.
+// ---------------------------------------------------------------------------
+struct DwTile {
+  int TR, strips, quads, CC, BW, BH;
+  int ctiles, rtiles, qtiles, tiles;
+  int stages;
+  int groups, RG;   // row groups of a tile (thread = strip x quad x group) and output rows per group
+  int merged;       // the tensor map is {W * C / 8 (8-byte elements), H, N}: whole pixel rows are contiguous
+  uint32_t stage_bytes, stage_pitch;
+  FastDiv dC, dQ, dR, dQuads, dItems;
+};
+
+static constexpr int kDwStagesMax = 4;
+
+template <int STRIDE>
+__device__ __forceinline__ void dw_tile_coords(const DwParams& p, const DwTile& t, uint32_t tile, int& n, int& p0,
+                                               int& q0, int& cbase) {
+  uint32_t rest = fdiv(tile, t.dC);
+  cbase = (int)(tile - rest * t.dC.d) * t.CC;
+  uint32_t u = fdiv(rest, t.dQ);
+  q0 = (int)(rest - u * t.dQ.d) * t.strips * (STRIDE == 1 ? 4 : 2);
+  rest = u;
+  u = fdiv(rest, t.dR);
+  p0 = (int)(rest - u * t.dR.d) * t.TR;
+  n = (int)u;
+}
+
+static constexpr int kDwConsumerWarps = 7;
+static constexpr int kDwThreads = 32 * (kDwConsumerWarps + 1);  // + the TMA producer warp
+// (8 warps = 2 per scheduler: two CTAs of up to 128 registers per thread fit the 16 K registers of an SMSP;
+// 9 warps did not -- ncu launch__occupancy_limit_registers 1)
+
+template <int STRIDE, bool FAST>
+__global__ void __launch_bounds__(kDwThreads, 2)
+dw3x3_tma_kernel(const __grid_constant__ CUtensorMap tx, const DwParams p, const DwTile t) {
+  extern __shared__ __align__(128) uint8_t dw_smem[];
+  __shared__ __align__(8) uint64_t full_bar[kDwStagesMax], empty_bar[kDwStagesMax];
+  pdl_launch_dependents();
+  const uint32_t sbase = (smem_u32(dw_smem) + 127u) & ~127u;
+  const uint8_t* gbase = dw_smem + (sbase - smem_u32(dw_smem));
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < t.stages; ++s) {
+      mbar_init(smem_u32(&full_bar[s]), 1);
+      mbar_init(smem_u32(&empty_bar[s]), kDwConsumerWarps);
+    }
+    fence_barrier_init();
+    tma_prefetch_desc(&tx);
+  }
+  __syncthreads();
+  pdl_wait();  // the input comes from the previous kernel
+  const int warp = threadIdx.x >> 5;
+  if (warp == kDwConsumerWarps) {
+    // ---- producer: one lane keeps the ring of input boxes full; no block-wide barrier anywhere ----
+    if ((threadIdx.x & 31) == 0) {
+      uint32_t it = 0;
+      for (uint32_t tile = blockIdx.x; tile < (uint32_t)t.tiles; tile += gridDim.x, ++it) {
+        const int slot = (int)(it % (uint32_t)t.stages);
+        if (it >= (uint32_t)t.stages) mbar_wait(smem_u32(&empty_bar[slot]), ((it / (uint32_t)t.stages) - 1u) & 1u);
+        int n, p0, q0, cbase;
+        dw_tile_coords<STRIDE>(p, t, tile, n, p0, q0, cbase);
+        const uint32_t bar = smem_u32(&full_bar[slot]);
+        const uint32_t dst = sbase + (uint32_t)slot * t.stage_pitch;
+        mbar_arrive_expect_tx(bar, t.stage_bytes);
+        if (t.merged)  // rows of BW whole pixels: {(W * C) / 8, H, N} in 8-byte elements
+          tma_load_3d(dst, &tx, bar, (q0 * STRIDE - p.pl_) * (p.C >> 3), p0 * STRIDE - p.pt, n);
+        else
+          tma_load_4d(dst, &tx, bar, cbase, q0 * STRIDE - p.pl_, p0 * STRIDE - p.pt, n);
+      }
+    }
+    return;
+  }
+  // ---- consumers: a thread owns (row group, strip, channel quad) for the whole kernel.  The grid is a multiple
+  // of ctiles and the channel chunk is the fastest tile index, so a CTA always sees the same channel chunk:
+  // filter, scale and bias are loaded ONCE (they were re-read per tile: ncu long_scoreboard ~1 per issue) ----
+  const int n_items = t.strips * t.quads;
+  const uint32_t grp = fdiv(threadIdx.x, t.dItems);
+  const int item = (int)threadIdx.x - (int)grp * n_items;
+  const uint32_t strip = fdiv((uint32_t)item, t.dQuads);
+  const int quad = item - (int)strip * t.quads;
+  const int cbase0 = (int)(blockIdx.x % (uint32_t)t.ctiles) * t.CC;
+  const int c0 = cbase0 + quad * 4;
+  const bool active = (int)grp < t.groups && c0 < p.C;
+  uint32_t wa[3][4];
+  float4 sc, bs;
+  if (active) {
+    dw_load_filter(p, c0, wa);
+    dw_load_scale_bias(p, c0, sc, bs);
+  } else {
+#pragma unroll
+    for (int r = 0; r < 3; ++r)
+#pragma unroll
+      for (int j = 0; j < 4; ++j) wa[r][j] = 0;
+    sc = bs = make_float4(0.f, 0.f, 0.f, 0.f);
+  }
+  const uint32_t ldyw = (uint32_t)p.ldy >> 2;  // FAST launches: int8 output addressed in 32-bit words
+  const uint32_t colw = (uint32_t)t.CC / 4u, roww = (uint32_t)t.BW * colw;
+  // word offset of this thread's window inside a stage: first row of its group, first column of its strip
+  const uint32_t win_off = (uint32_t)grp * (uint32_t)(t.RG * STRIDE) * roww + strip * 4u * colw + (uint32_t)quad;
+  uint32_t it = 0;
+  for (uint32_t tile = blockIdx.x; tile < (uint32_t)t.tiles; tile += gridDim.x, ++it) {
+    const int slot = (int)(it % (uint32_t)t.stages);
+    const uint32_t parity = (it / (uint32_t)t.stages) & 1u;
+    int n, p0, q0, cbase;
+    dw_tile_coords<STRIDE>(p, t, tile, n, p0, q0, cbase);
+    mbar_wait(smem_u32(&full_bar[slot]), parity);
+    const uint8_t* st = gbase + (size_t)slot * t.stage_pitch;
+    const int oq0 = q0 + (int)strip * (STRIDE == 1 ? 4 : 2);
+    const int pg0 = p0 + (int)grp * t.RG;  // first output row of this thread's group
+    int rows_out = min(min(t.RG, t.TR - (int)grp * t.RG), p.P - pg0);
+    if (!active || oq0 >= p.Q) rows_out = 0;
+    if (rows_out > 0) {
+      const uint32_t pix0 = (uint32_t)((n * p.P + pg0) * p.Q + oq0);
+      // whole strip inside the image: no per-pixel column checks
+      const bool full_strip = oq0 + (STRIDE == 1 ? 4 : 2) <= p.Q;
+      uint32_t* orow = reinterpret_cast<uint32_t*>(reinterpret_cast<int8_t*>(p.y) + c0) + (size_t)pix0 * ldyw;
+      const size_t orow_step = (size_t)p.Q * ldyw;
+      auto finish = [&](const int (&acc)[4], int q, uint32_t pix) {
+        if (FAST) {
+          if (full_strip || oq0 + q < p.Q) dw_finish4_ptr(acc, sc, bs, p.hi_bits, orow + (size_t)q * ldyw);
+        } else {
+          if (oq0 + q < p.Q) dw_finish4<false>(p, acc, sc, bs, p.hi_bits, pix + q, c0);
+        }
+      };
+      const uint32_t* win = reinterpret_cast<const uint32_t*>(st) + win_off;
+      const int magic = kDwMagic;
+      if (STRIDE == 1) {
+        // input-stationary: three transposed input rows stay in registers (slots rotate through the
+        // 3x unrolled loop); every output row is 3 dp4a per output and channel off the float magic, then
+        // the packed epilogue -- accumulators live for one pixel only
+        uint32_t wb[3][4];
+#pragma unroll
+        for (int r = 0; r < 3; ++r)
+#pragma unroll
+          for (int j = 0; j < 4; ++j) wb[r][j] = wa[r][j] << 8;
+        uint32_t T[3][8];
+        auto load_row = [&](int ii, uint32_t (&d)[8]) {
+          const uint32_t* rp = win + (uint32_t)ii * roww;
+          uint32_t xw[6];
+#pragma unroll
+          for (int k = 0; k < 6; ++k) xw[k] = rp[(uint32_t)k * colw];
+          uint32_t ta[4], tb[4];
+          dw_transpose(xw[0], xw[1], xw[2], xw[3], ta);  // columns 0..3 -> outputs 0, 1
+          dw_transpose(xw[2], xw[3], xw[4], xw[5], tb);  // columns 2..5 -> outputs 2, 3
+#pragma unroll
+          for (int j = 0; j < 4; ++j) { d[j] = ta[j]; d[4 + j] = tb[j]; }
+        };
+        load_row(0, T[0]);
+        load_row(1, T[1]);
+        for (int o = 0; o < rows_out; o += 3) {
+#pragma unroll
+          for (int u = 0; u < 3; ++u) {
+            if (o + u >= rows_out) break;
+            load_row(o + u + 2, T[(u + 2) % 3]);
+            const uint32_t pix = pix0 + (uint32_t)((o + u) * p.Q);
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+              int acc[4];
+#pragma unroll
+              for (int j = 0; j < 4; ++j) {
+                const int tj = (q >> 1) * 4 + j;  // outputs 0, 1 read ta, outputs 2, 3 read tb
+                int a_ = __dp4a((int)T[u % 3][tj], (int)((q & 1) ? wb[0][j] : wa[0][j]), magic);
+                a_ = __dp4a((int)T[(u + 1) % 3][tj], (int)((q & 1) ? wb[1][j] : wa[1][j]), a_);
+                acc[j] = __dp4a((int)T[(u + 2) % 3][tj], (int)((q & 1) ? wb[2][j] : wa[2][j]), a_);
+              }
+              finish(acc, q, pix);
+            }
+            orow += orow_step;
+          }
+        }
+      } else {
+        // stride 2: window of 5 input columns -> 2 output columns; output m reads input rows 2m, 2m + 1, 2m + 2
+        // (row 2m + 2 is carried over as the next output's first row)
+        uint32_t wb[3][4], wc[3][4];
+#pragma unroll
+        for (int r = 0; r < 3; ++r)
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            wb[r][j] = wa[r][j] << 16;                                 // taps 0, 1 on transposed columns 2, 3
+            wc[r][j] = ((wa[r][j] >> 16) & 0xffu) << (8 * j);          // tap 2 on channel j of column 4
+          }
+        uint32_t T[3][5];  // [slot][transposed columns 0..3 of channel j | raw column 4]
+        auto load_row = [&](int ii, uint32_t (&d)[5]) {
+          const uint32_t* rp = win + (uint32_t)ii * roww;
+          uint32_t xw[5];
+#pragma unroll
+          for (int k = 0; k < 5; ++k) xw[k] = rp[(uint32_t)k * colw];
+          uint32_t ta[4];
+          dw_transpose(xw[0], xw[1], xw[2], xw[3], ta);
+#pragma unroll
+          for (int j = 0; j < 4; ++j) d[j] = ta[j];
+          d[4] = xw[4];
+        };
+        load_row(0, T[0]);
+        for (int m = 0; m < rows_out; m += 2) {
+#pragma unroll
+          for (int u = 0; u < 2; ++u) {
+            if (m + u >= rows_out) break;
+            // slots: u = 0: rows (T0, T1, T2), u = 1: rows (T2, T1, T0)
+            const int sa = u == 0 ? 0 : 2, sb_ = 1, sc_ = u == 0 ? 2 : 0;
+            load_row(2 * (m + u) + 1, T[sb_]);
+            load_row(2 * (m + u) + 2, T[sc_]);
+            const uint32_t pix = pix0 + (uint32_t)((m + u) * p.Q);
+#pragma unroll
+            for (int q = 0; q < 2; ++q) {
+              int acc[4];
+#pragma unroll
+              for (int j = 0; j < 4; ++j) {
+                int a_ = magic;
+                const int rows3[3] = {sa, sb_, sc_};
+#pragma unroll
+                for (int r = 0; r < 3; ++r) {
+                  if (q == 0) {
+                    a_ = __dp4a((int)T[rows3[r]][j], (int)wa[r][j], a_);
+                  } else {
+                    a_ = __dp4a((int)T[rows3[r]][j], (int)wb[r][j], a_);
+                    a_ = __dp4a((int)T[rows3[r]][4], (int)wc[r][j], a_);
+                  }
+                }
+                acc[j] = a_;
+              }
+              finish(acc, q, pix);
+            }
+            orow += orow_step;
+          }
+        }
+      }
+    }
+    __syncwarp();
+    if ((threadIdx.x & 31) == 0) mbar_arrive(smem_u32(&empty_bar[slot]));  // this warp is done with the slot
+  }
+}
+
+// ---------------------------------------------------------------------------
 // generic path
 // ---------------------------------------------------------------------------
 __global__ void __launch_bounds__(256) dw_generic_kernel(const DwParams p, int CGB, int aligned) {
@@ -512,6 +781,44 @@ __global__ void __launch_bounds__(256) dw_generic_kernel(const DwParams p, int C
 
 using namespace pl;
 
+// tensor map of the int8 NHWC input {C, W, H, N} with a box {bc, bw, bh, 1}; no swizzle; out-of-bounds
+// box elements (the padding, the channel tail) read as zero
+static PFN_cuTensorMapEncodeTiled_v12000 dw_encode_fn() {
+  static PFN_cuTensorMapEncodeTiled_v12000 fn = [] {
+    cudaDriverEntryPointQueryResult q;
+    void* f = nullptr;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &f, cudaEnableDefault, &q) != cudaSuccess ||
+        q != cudaDriverEntryPointSuccess)
+      f = nullptr;
+    return reinterpret_cast<PFN_cuTensorMapEncodeTiled_v12000>(f);
+  }();
+  return fn;
+}
+static int dw_encode_input(CUtensorMap* m, const void* base, int C, int W, int H, int N, int ld, int bc, int bw,
+                           int bh) {
+  cuuint64_t dims[4] = {(cuuint64_t)C, (cuuint64_t)W, (cuuint64_t)H, (cuuint64_t)N};
+  cuuint64_t strides[3] = {(cuuint64_t)ld, (cuuint64_t)ld * W, (cuuint64_t)ld * W * H};
+  cuuint32_t box[4] = {(cuuint32_t)bc, (cuuint32_t)bw, (cuuint32_t)bh, 1};
+  cuuint32_t estr[4] = {1, 1, 1, 1};
+  CUresult r = dw_encode_fn()(m, CU_TENSOR_MAP_DATA_TYPE_UINT8, 4, const_cast<void*>(base), dims, strides, box, estr,
+                              CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE,
+                              CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  return r == CUDA_SUCCESS ? PL_OK : PL_ERR_DRIVER;
+}
+
+// dense thin tensors (ldx == C < 128): {W * C / 8, H, N} in 8-byte elements, box {bw * C / 8, bh, 1}: one box row is a
+// whole run of bw pixels (>= 128 bytes) instead of bw rows of C bytes
+static int dw_encode_rows(CUtensorMap* m, const void* base, int C, int W, int H, int N, int bw, int bh) {
+  cuuint64_t dims[3] = {(cuuint64_t)W * C / 8, (cuuint64_t)H, (cuuint64_t)N};
+  cuuint64_t strides[2] = {(cuuint64_t)W * C, (cuuint64_t)W * C * H};
+  cuuint32_t box[3] = {(cuuint32_t)(bw * C / 8), (cuuint32_t)bh, 1};
+  cuuint32_t estr[3] = {1, 1, 1};
+  CUresult r = dw_encode_fn()(m, CU_TENSOR_MAP_DATA_TYPE_INT64, 3, const_cast<void*>(base), dims, strides, box, estr,
+                              CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE,
+                              CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  return r == CUDA_SUCCESS ? PL_OK : PL_ERR_DRIVER;
+}
+
 extern "C" int pl_dwconv2d_i8_nhwc(const int8_t* x, const int8_t* w_crs, void* y,
                                    const pl_conv_desc* d, const pl_epilogue* e, pl_stream_t stream) {
   if (!x || !w_crs || !y || !d || !e) return PL_ERR_ARG;
@@ -560,6 +867,90 @@ extern "C" int pl_dwconv2d_i8_nhwc(const int8_t* x, const int8_t* w_crs, void* y
     const int s1 = d->stride_h == 1;
     const int T = s1 ? 4 : 2;
     p.strips = (Q + T - 1) / T;
+    // shared-memory staged kernel: needs a TMA-addressable input (16-byte pixels) and 4-byte channel quads
+    static const bool no_tma = [] { const char* v = getenv("PL_DW_NO_TMA"); return v && v[0] == '1'; }();
+    if (!no_tma && d->ldx % 16 == 0 && (reinterpret_cast<uintptr_t>(x) & 15) == 0 && dw_encode_fn()) {
+      DwTile t{};
+      const int strips_all = p.strips;
+      const int items_max = 32 * kDwConsumerWarps;
+      const int c16 = (d->C + 15) / 16 * 16;
+      // TMA costs ~5 cycles per box ROW whatever its length: 32-byte rows (C = 32) run at 6 B/cycle/SM.  So the
+      // innermost box extent is >= 128 bytes: a 128-channel chunk, or -- for thinner dense tensors -- whole pixel
+      // rows through a map whose innermost dimension is W * C (8-byte elements, at most 256 per box)
+      t.merged = (d->C < 128 && d->ldx == d->C && d->C % 16 == 0 && ((long long)d->W * d->C) % 16 == 0) ? 1 : 0;
+      t.CC = d->C >= 128 ? 128 : c16;
+      t.quads = t.CC / 4;
+      t.ctiles = (d->C + t.CC - 1) / t.CC;
+      int smax = items_max / t.quads;
+      if (smax < 1) smax = 1;
+      if (t.merged) {
+        const int bw_max = 2048 / d->C;  // 256 elements of 8 bytes
+        const int sm_ = s1 ? (bw_max - 2) / 4 : ((bw_max - 1) / 2) / 2;
+        if (sm_ < smax) smax = sm_;
+      } else {
+        const int sm_ = s1 ? (256 - 2) / 4 : ((256 - 1) / 2) / 2;
+        if (sm_ < smax) smax = sm_;
+      }
+      bool ok = smax >= 1;
+      if (ok) {
+        // balanced column tiles: the fewest tiles that cover the row, equal widths
+        t.qtiles = (strips_all + smax - 1) / smax;
+        t.strips = (strips_all + t.qtiles - 1) / t.qtiles;
+        const int TQ = t.strips * T;
+        t.BW = s1 ? TQ + 2 : 2 * TQ + 1;
+        const int rowbytes = t.BW * t.CC;
+        const int items = t.strips * t.quads;
+        t.groups = items_max / items;
+        if (t.groups > 4) t.groups = 4;
+        if (t.groups < 1) t.groups = 1;
+        const int budget = 36 * 1024;
+        int tr = s1 ? budget / rowbytes - 2 : (budget / rowbytes - 1) / 2;
+        if (tr > P) tr = P;
+        if (tr > 32) tr = 32;
+        if (tr < 1) tr = 1;
+        auto tiles_for = [&](int r) { return (long long)d->N * ((P + r - 1) / r) * t.qtiles * t.ctiles; };
+        while (tr > 4 && tiles_for(tr) < 4ll * sms) --tr;
+        if (t.groups > tr) t.groups = tr;
+        t.RG = (tr + t.groups - 1) / t.groups;
+        t.TR = tr;
+        t.BH = s1 ? tr + 2 : 2 * tr + 1;
+        t.rtiles = (P + tr - 1) / tr;
+        const long long tiles = tiles_for(tr);
+        t.stage_bytes = (uint32_t)(rowbytes * t.BH);
+        t.stage_pitch = (t.stage_bytes + 127u) / 128u * 128u;
+        int stages = (int)((108u * 1024u) / t.stage_pitch);
+        if (stages > kDwStagesMax) stages = kDwStagesMax;
+        ok = tiles < (1ll << 31) && t.BH <= 256 && stages >= 2;
+        if (ok) {
+          t.tiles = (int)tiles;
+          t.stages = stages;
+          t.dC = make_fastdiv((uint32_t)t.ctiles);
+          t.dQ = make_fastdiv((uint32_t)t.qtiles);
+          t.dR = make_fastdiv((uint32_t)t.rtiles);
+          t.dQuads = make_fastdiv((uint32_t)t.quads);
+          t.dItems = make_fastdiv((uint32_t)items);
+          CUtensorMap tx;
+          const int rc = t.merged ? dw_encode_rows(&tx, x, d->C, d->W, d->H, d->N, t.BW, t.BH)
+                                  : dw_encode_input(&tx, x, d->C, d->W, d->H, d->N, d->ldx, t.CC, t.BW, t.BH);
+          if (rc == PL_OK) {
+            const size_t smem = (size_t)t.stages * t.stage_pitch + 128;
+            // a multiple of ctiles, so that a CTA keeps its channel chunk (and its filter registers)
+            int grid = t.tiles < 2 * sms ? t.tiles : 2 * sms;
+            grid -= grid % t.ctiles;
+            if (grid < t.ctiles) grid = t.ctiles;
+            auto go = [&](auto kern) {
+              cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(112 * 1024));
+              cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
+              launch_pdl(kern, dim3((unsigned)grid), dim3(kDwThreads), smem, st, tx, p, t);
+            };
+            if (s1) { if (fe) go(dw3x3_tma_kernel<1, true>); else go(dw3x3_tma_kernel<1, false>); }
+            else    { if (fe) go(dw3x3_tma_kernel<2, true>); else go(dw3x3_tma_kernel<2, false>); }
+            ++g_launches;
+            return launch_status();
+          }
+        }
+      }
+    }
     // taller bands reuse more rows per thread; keep at least ~2 full waves of threads
     auto items_for = [&](int rb) { return (long long)d->N * ((P + rb - 1) / rb) * p.strips * p.CG; };
     int RB = 2;

@@ -375,6 +375,18 @@ DW_CASES = [
     (1, 16, 16, 32, 5, 2, 2, 1),
     (1, 16, 16, 16, 3, 1, 2, 2),     # dilation (generic path)
     (1, 7, 7, 1024, 3, 1, 1, 1),
+    # shared-memory staged kernel: several tiles per CTA (ring reuse), column tiles (Q > 128), channel
+    # chunks with a tail, bands with a ragged last row block, pad 0, asymmetric sizes
+    (9, 56, 56, 128, 3, 1, 1, 1),
+    (9, 56, 56, 128, 3, 2, 1, 1),
+    (2, 20, 150, 48, 3, 1, 1, 1),
+    (2, 21, 290, 24, 3, 2, 1, 1),
+    (3, 37, 41, 336, 3, 1, 1, 1),
+    (3, 37, 41, 336, 3, 2, 1, 1),
+    (2, 30, 30, 40, 3, 1, 0, 1),
+    (2, 31, 29, 40, 3, 2, 0, 1),
+    (40, 14, 14, 512, 3, 1, 1, 1),
+    (40, 14, 14, 512, 3, 2, 1, 1),
 ]
 
 
