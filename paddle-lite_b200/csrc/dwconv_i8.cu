@@ -164,7 +164,7 @@ __device__ __forceinline__ void dw_finish4(const DwParams& p, const int (&acc)[4
 // FAST epilogue of 4 channels of one output pixel straight to a word pointer (the staged kernel keeps a row
 // pointer per item instead of re-deriving pixel * pitch + channel for every pixel)
 __device__ __forceinline__ void dw_finish4_ptr(const int (&acc)[4], const float4 sc, const float4 bs, uint32_t hi_bits,
-                                               uint32_t* dst) {
+                                               uint32_t* dst, bool ok) {
   const uint64_t off = dw_pk2(-12582912.f, -12582912.f);
   const uint64_t f01 = dw_fadd2_rn(dw_pk2(__int_as_float(acc[0]), __int_as_float(acc[1])), off);
   const uint64_t f23 = dw_fadd2_rn(dw_pk2(__int_as_float(acc[2]), __int_as_float(acc[3])), off);
@@ -182,7 +182,8 @@ __device__ __forceinline__ void dw_finish4_ptr(const int (&acc)[4], const float4
   const uint64_t u23 = dw_fadd2_rm(dw_pk2(__int_as_float(c2_), __int_as_float(c3_)), big);
   const uint32_t p01 = prmt((uint32_t)u01, (uint32_t)(u01 >> 32), 0x0051);
   const uint32_t p23 = prmt((uint32_t)u23, (uint32_t)(u23 >> 32), 0x0051);
-  *dst = prmt(p01, p23, 0x5410);
+  const uint32_t v = prmt(p01, p23, 0x5410);
+  if (ok) *dst = v;  // a predicated store: the math above stays branch-free
 }
 
 struct DwItem {
@@ -587,6 +588,7 @@ dw3x3_tma_kernel(const __grid_constant__ CUtensorMap tx, const DwParams p, const
     sc = bs = make_float4(0.f, 0.f, 0.f, 0.f);
   }
   const uint32_t ldyw = (uint32_t)p.ldy >> 2;  // FAST launches: int8 output addressed in 32-bit words
+  const uint32_t hi_bits = p.hi_bits;
   const uint32_t colw = (uint32_t)t.CC / 4u, roww = (uint32_t)t.BW * colw;
   // word offset of this thread's window inside a stage: first row of its group, first column of its strip
   const uint32_t win_off = (uint32_t)grp * (uint32_t)(t.RG * STRIDE) * roww + strip * 4u * colw + (uint32_t)quad;
@@ -610,7 +612,7 @@ dw3x3_tma_kernel(const __grid_constant__ CUtensorMap tx, const DwParams p, const
       const size_t orow_step = (size_t)p.Q * ldyw;
       auto finish = [&](const int (&acc)[4], int q, uint32_t pix) {
         if (FAST) {
-          if (full_strip || oq0 + q < p.Q) dw_finish4_ptr(acc, sc, bs, p.hi_bits, orow + (size_t)q * ldyw);
+          dw_finish4_ptr(acc, sc, bs, hi_bits, orow + (size_t)q * ldyw, full_strip || oq0 + q < p.Q);
         } else {
           if (oq0 + q < p.Q) dw_finish4<false>(p, acc, sc, bs, p.hi_bits, pix + q, c0);
         }
