@@ -246,6 +246,12 @@ int pl_pool2d_i8_nhwc(const int8_t* x, int ldx, void* y, int ldy, int N, int H,
                       int pl, int P, int Q, int pool_type, int exclusive,
                       float rescale, int out_dtype, int round_mode,
                       pl_stream_t stream);
+/* adaptive pooling (PoolParam::adaptive: ksize is the OUTPUT size P x Q): window
+ * [floor(i * in / out), ceil((i + 1) * in / out)) per axis, avg divides by the window size
+ * (lite/kernels/cuda/pool_compute.cu:69-106, 150-187); values as pl_pool2d_i8_nhwc. */
+int pl_adaptive_pool2d_i8_nhwc(const int8_t* x, int ldx, void* y, int ldy, int N, int H, int W, int C, int P,
+                               int Q, int pool_type, float rescale, int out_dtype, int round_mode,
+                               pl_stream_t stream);
 /* y = q(act(fmaf((float)a, sa, (float)b * sb))) -- the ResNet residual add */
 int pl_add_i8(const int8_t* a, const int8_t* b, void* y, int64_t n, float sa,
               float sb, int act, float act_arg, int out_dtype, int round_mode,
@@ -279,6 +285,9 @@ int pl_concat_shuffle2_i8_nhwc(const int8_t* a, int lda, const int8_t* b, int ld
 /* number of kernels this library has launched in this process (bench.py's
  * gpu_launches claim) */
 int64_t pl_launch_count(void);
+/* developer knobs (PL_* environment variables) are read once per process and cached; this drops the cache so
+ * that a changed environment is seen by the next launch (tests that A/B two code paths call it) */
+void pl_refresh_knobs(void);
 const char* pl_version(void);
 /* tensor-pipe micro-benchmark: issues `iters` back-to-back 128xBNx32
  * tcgen05.mma kind::i8 per CTA on `ctas` CTAs from resident smem; returns 0

@@ -461,6 +461,42 @@ int orc_pool2d_i8_nhwc(const int8_t* x, void* y, int N, int H, int W, int C,
 }
 
 /*
+ * adaptive int8 NHWC pooling (PoolParam::adaptive, ksize = output size): window
+ * [floor(i * in / out), ceil((i + 1) * in / out)) per axis, avg divides by the window
+ * size -- lite/kernels/cuda/pool_compute.cu:69-106 (max), :150-187 (avg).  Value rules
+ * as orc_pool2d_i8_nhwc.
+ */
+int orc_adaptive_pool2d_i8_nhwc(const int8_t* x, void* y, int N, int H, int W, int C, int P, int Q, int pool_type,
+                                float rescale, int out_dtype, int round_mode) {
+#pragma omp parallel for collapse(2) schedule(static)
+  for (int n = 0; n < N; ++n) {
+    for (int p = 0; p < P; ++p) {
+      for (int q = 0; q < Q; ++q) {
+        const int h0 = (p * H) / P, h1 = ((p + 1) * H + P - 1) / P;
+        const int w0 = (q * W) / Q, w1 = ((q + 1) * W + Q - 1) / Q;
+        const int cnt = (h1 - h0) * (w1 - w0);
+        for (int c = 0; c < C; ++c) {
+          int32_t sum = 0, mx = -128;
+          for (int h = h0; h < h1; ++h)
+            for (int w = w0; w < w1; ++w) {
+              int32_t v = x[(((int64_t)n * H + h) * W + w) * C + c];
+              sum += v;
+              if (v > mx) mx = v;
+            }
+          const float v = pool_type == ORC_POOL_MAX ? (float)mx * rescale : ((float)sum / (float)cnt) * rescale;
+          const int64_t o = (((int64_t)n * P + p) * Q + q) * C + c;
+          if (out_dtype == ORC_OUT_FP32)
+            ((float*)y)[o] = v;
+          else
+            ((int8_t*)y)[o] = orc_round_sat_i8(v, round_mode);
+        }
+      }
+    }
+  }
+  return 0;
+}
+
+/*
  * int8 residual add + act + requant.  PARITY UNPINNED (the
  * reference's elementwise_add_int8_kernel takes fp32 inputs and is dead code).
  *   v = fma((float)a, sa, (float)b * sb), sa = a_scale/out_scale, sb likewise

@@ -150,8 +150,9 @@ def conv_desc(N, H, W, Cc, K, R, S, strides=(1, 1), pads=(0, 0, 0, 0), dil=(1, 1
 
 def conv2d(x, w_packed, K, R, S, scale, bias, strides=(1, 1), pads=(0, 0, 0, 0), dil=(1, 1),
            act=ACT_NONE, act_arg=0.0, out=OUT_INT8, rnd=ROUND_ARM, y=None, Cc=None, ldy=None,
-           residual=None, res_scale=0.0):
-    """x: [N,H,W,ldx] int8 device tensor (logical channels Cc <= ldx)."""
+           residual=None, res_scale=0.0, groups=1):
+    """x: [N,H,W,ldx] int8 device tensor (logical channels Cc <= ldx).  groups > 1: w_packed was packed from
+    OHWI [K, R, S, Cc / groups]."""
     N, H, W, Cx = x.shape
     ldx = x.stride(-2)  # a channel slice of a wider buffer keeps the wide pitch
     Cc = Cx if Cc is None else Cc
@@ -163,7 +164,7 @@ def conv2d(x, w_packed, K, R, S, scale, bias, strides=(1, 1), pads=(0, 0, 0, 0),
         y = torch.empty((N, P, Q, ldy), dtype=_TORCH_OUT[out], device=x.device)
         if ldy != K:
             y.zero_()
-    d = conv_desc(N, H, W, Cc, K, R, S, strides, pads, dil, 1, ldx, ldy)
+    d = conv_desc(N, H, W, Cc, K, R, S, strides, pads, dil, groups, ldx, ldy)
     e = make_epilogue(scale, bias, act, act_arg, out, rnd, residual,
                       0 if residual is None else residual.stride(-2), res_scale)
     _check(lib().pl_conv2d_i8_nhwc(_ptr(x), _ptr(w_packed), _ptr(y), C.byref(d), C.byref(e), _stream()),
@@ -421,6 +422,16 @@ def pool2d(x, ksize, strides, pads, pool_type, exclusive=True, rescale=1.0, out=
     _check(lib().pl_pool2d_i8_nhwc(_ptr(x), ldx, _ptr(y), y.shape[-1], N, H, W, Cc, kh, kw, strides[0],
                                    strides[1], pt, pl_, P, Q, pool_type, int(exclusive), _f(rescale), out,
                                    rnd, _stream()), "pl_pool2d_i8_nhwc")
+    return y
+
+
+def adaptive_pool2d(x, out_hw, pool_type, rescale=1.0, out=OUT_INT8, rnd=ROUND_ARM, Cc=None):
+    N, H, W, Cx = x.shape
+    Cc = Cx if Cc is None else Cc
+    P, Q = out_hw
+    y = torch.zeros((N, P, Q, Cx), dtype=_TORCH_OUT[out], device=x.device)
+    _check(lib().pl_adaptive_pool2d_i8_nhwc(_ptr(x), x.stride(-2), _ptr(y), y.stride(-2), N, H, W, Cc, P, Q, pool_type,
+                                            _f(rescale), out, rnd, _stream()), "pl_adaptive_pool2d_i8_nhwc")
     return y
 
 

@@ -10,7 +10,7 @@
 #include <cstdlib>
 
 namespace pl {
-unsigned long long g_launches = 0;
+std::atomic<unsigned long long> g_launches{0};
 
 bool pdl_enabled() {
   static const bool on = [] {
@@ -21,7 +21,7 @@ bool pdl_enabled() {
 }
 }  // namespace pl
 
-extern "C" int64_t pl_launch_count(void) { return (int64_t)pl::g_launches; }
+extern "C" int64_t pl_launch_count(void) { return (int64_t)pl::g_launches.load(std::memory_order_relaxed); }
 
 extern "C" const char* pl_version(void) { return "paddle-lite_b200 int8 hot path 0.1 (sm_100a)"; }
 

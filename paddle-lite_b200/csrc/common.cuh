@@ -10,6 +10,7 @@
 // Built with -fmad=false: the only fused multiply-adds are the explicit
 // __fmaf_rn below, so the CPU oracle (fmaf, -ffp-contract=off) matches bit for bit.
 #pragma once
+#include <atomic>
 #include <cuda_runtime.h>
 #include <stdint.h>
 
@@ -17,7 +18,7 @@
 
 namespace pl {
 
-extern unsigned long long g_launches;  // host-side launch counter (capi.cu)
+extern std::atomic<unsigned long long> g_launches;  // host-side launch counter (capi.cu)
 
 #define PL_CUDA_OK(expr)                         \
   do {                                           \

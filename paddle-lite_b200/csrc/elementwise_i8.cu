@@ -761,6 +761,54 @@ extern "C" int pl_quantize_nchw_u8_to_s2d_i8(const uint8_t* x_u8, int8_t* y_s2d,
   return launch_quant_s2d<uint8_t, true>(x_u8, y_s2d, N, C, H, W, g, scale, round_mode, aff, stream);
 }
 
+// adaptive pooling (PoolParam::adaptive, lite/kernels/cuda/pool_compute.cu:69-187): one thread per output
+// element, window [floor(i * in / out), ceil((i + 1) * in / out)); consecutive threads take consecutive channels
+__global__ void __launch_bounds__(256)
+adaptive_pool_kernel(const int8_t* __restrict__ x, int ldx, void* __restrict__ y, int ldy, int N, int H, int W, int C,
+                     int P, int Q, int pool_type, float rescale, int out_dtype, int round_mode) {
+  const long long total = (long long)N * P * Q * C;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total;
+       i += (long long)gridDim.x * blockDim.x) {
+    const int c = (int)(i % C);
+    long long t = i / C;
+    const int q = (int)(t % Q);
+    t /= Q;
+    const int p = (int)(t % P);
+    const int n = (int)(t / P);
+    const int h0 = (p * H) / P, h1 = ((p + 1) * H + P - 1) / P;
+    const int w0 = (q * W) / Q, w1 = ((q + 1) * W + Q - 1) / Q;
+    int sum = 0, mx = -128;
+    for (int h = h0; h < h1; ++h)
+      for (int w = w0; w < w1; ++w) {
+        const int v = __ldg(x + (((long long)n * H + h) * W + w) * ldx + c);
+        sum += v;
+        mx = v > mx ? v : mx;
+      }
+    const float cnt = (float)((h1 - h0) * (w1 - w0));
+    const float v = pool_type == PL_POOL_MAX ? (float)mx * rescale : __fdiv_rn((float)sum, cnt) * rescale;
+    const long long o = (((long long)n * P + p) * Q + q) * ldy + c;
+    if (out_dtype == PL_OUT_FP32)
+      reinterpret_cast<float*>(y)[o] = v;
+    else
+      reinterpret_cast<int8_t*>(y)[o] = (int8_t)round_sat_i8(v, round_mode);
+  }
+}
+
+extern "C" int pl_adaptive_pool2d_i8_nhwc(const int8_t* x, int ldx, void* y, int ldy, int N, int H, int W, int C,
+                                          int P, int Q, int pool_type, float rescale, int out_dtype, int round_mode,
+                                          pl_stream_t stream) {
+  if (!x || !y || N <= 0 || H <= 0 || W <= 0 || C <= 0 || P <= 0 || Q <= 0 || ldx < C || ldy < C) return PL_ERR_ARG;
+  if (out_dtype != PL_OUT_INT8 && out_dtype != PL_OUT_FP32) return PL_ERR_ARG;
+  if (pool_type != PL_POOL_MAX && pool_type != PL_POOL_AVG) return PL_ERR_ARG;
+  const long long total = (long long)N * P * Q * C;
+  long long blocks = (total + 255) / 256;
+  if (blocks > 148 * 16) blocks = 148 * 16;
+  adaptive_pool_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(x, ldx, y, ldy, N, H, W, C, P, Q, pool_type,
+                                                                          rescale, out_dtype, round_mode);
+  ++g_launches;
+  return launch_status();
+}
+
 extern "C" int pl_pool2d_i8_nhwc(const int8_t* x, int ldx, void* y, int ldy, int N, int H, int W, int C,
                                  int kh, int kw, int sh, int sw, int pt, int pl_, int P, int Q,
                                  int pool_type, int exclusive, float rescale, int out_dtype,

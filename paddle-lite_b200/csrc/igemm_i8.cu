@@ -1335,7 +1335,15 @@ struct DriverFns {
 };
 
 DriverFns& driver() {
-  static DriverFns d = [] {
+  // entry points are process-wide; SM count / compute capability belong to the CURRENT device
+  static DriverFns per_dev[64];
+  static bool ready[64] = {};
+  static std::mutex mu;
+  int dev = 0;
+  cudaGetDevice(&dev);
+  dev &= 63;
+  std::lock_guard<std::mutex> lock(mu);
+  if (!ready[dev]) {
     DriverFns f;
     cudaDriverEntryPointQueryResult q;
     void* fn = nullptr;
@@ -1346,15 +1354,14 @@ DriverFns& driver() {
     if (cudaGetDriverEntryPoint("cuTensorMapEncodeIm2col", &fn, cudaEnableDefault, &q) == cudaSuccess &&
         q == cudaDriverEntryPointSuccess)
       f.im2col = reinterpret_cast<PFN_cuTensorMapEncodeIm2col_v12000>(fn);
-    int dev = 0;
-    cudaGetDevice(&dev);
     cudaDeviceGetAttribute(&f.sm_count, cudaDevAttrMultiProcessorCount, dev);
     cudaDeviceGetAttribute(&f.cc_major, cudaDevAttrComputeCapabilityMajor, dev);
     cudaDriverGetVersion(&f.driver_version);
     f.ok = f.tiled && f.im2col;
-    return f;
-  }();
-  return d;
+    per_dev[dev] = f;
+    ready[dev] = true;
+  }
+  return per_dev[dev];
 }
 
 CUtensorMapSwizzle swizzle_for(int bk) {
@@ -1439,7 +1446,11 @@ int pick_bn(int Nout, int m_tiles, int sms) {
 template <int EPI, int TR = 0, int TSW = 0, bool GROUPED = false>
 int launch_one(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& ty, const CUtensorMap& tr,
                const IgemmParams& p, int grid, size_t smem, pl_stream_t stream) {
-  static bool configured = false;  // one process drives one GPU
+  // cudaFuncSetAttribute is per DEVICE: one flag per device ordinal (a process may drive several GPUs)
+  static bool configured_dev[64] = {};
+  int dev_ = 0;
+  cudaGetDevice(&dev_);
+  bool& configured = configured_dev[dev_ & 63];
   if (!configured) {
     // 227 KB is the per-CTA limit for static + dynamic shared memory together
     PL_CUDA_OK(cudaFuncSetAttribute(igemm_i8_kernel<EPI, TR, TSW, GROUPED>, cudaFuncAttributeMaxDynamicSharedMemorySize,
@@ -1447,7 +1458,7 @@ int launch_one(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& 
     configured = true;
   }
   const int threads = TR > 0 ? kThinThreads : kThreads;
-  const char* trace_path = getenv("PL_DBG_TRACE");
+  const char* trace_path = env_int("PL_DBG_TRACE_ON", 0) ? getenv("PL_DBG_TRACE") : nullptr;
   if (trace_path && *trace_path) {
     // debugging aid: synchronous launch, CTA 0's timeline written as text (role tile e0..e7)
     static long long* dbuf = nullptr;
@@ -1479,18 +1490,38 @@ int launch_one(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& 
   return launch_status();
 }
 
+// Developer knobs (PL_*): read from the environment ONCE per knob and process, not ~20 getenv calls per launch
+// (the kernel classes run eagerly, layer by layer).  pl_refresh_knobs() drops the cache -- tests that flip a knob
+// between two launches call it.  Keyed by the address of the name literal.
+struct KnobCache {
+  static constexpr int kMax = 64;
+  const char* name[kMax];
+  int val[kMax];
+  bool set[kMax];
+  int n = 0;
+  std::mutex mu;
+};
+KnobCache& knobs() {
+  static KnobCache k;
+  return k;
+}
 int env_int(const char* name, int dflt) {
+  KnobCache& k = knobs();
+  std::lock_guard<std::mutex> lock(k.mu);
+  for (int i = 0; i < k.n; ++i)
+    if (k.name[i] == name) return k.set[i] ? k.val[i] : dflt;
   const char* v = getenv(name);
-  return (v && *v) ? atoi(v) : dflt;
+  const bool set = v && *v;
+  const int val = set ? atoi(v) : 0;
+  if (k.n < KnobCache::kMax) {
+    k.name[k.n] = name;
+    k.val[k.n] = val;
+    k.set[k.n] = set;
+    ++k.n;
+  }
+  return set ? val : dflt;
 }
-
-bool tma_epilogue_enabled() {
-  static const bool on = [] {
-    const char* v = getenv("PL_IGEMM_NO_TMA_EPI");
-    return !(v && v[0] == '1');
-  }();
-  return on;
-}
+bool tma_epilogue_enabled() { return env_int("PL_IGEMM_NO_TMA_EPI", 0) != 1; }
 
 int launch_igemm(const CUtensorMap& ta, const CUtensorMap& tb, IgemmParams& p, pl_stream_t stream) {
   const int tiles = p.m_tiles * p.n_tiles;
@@ -1776,6 +1807,10 @@ int common_setup(IgemmParams& p, long long M, int Nout, void* y, int ldy, const 
 // C-ABI
 // ============================================================================
 using namespace pl;
+namespace pl {
+int launch_gemv_i8(const int8_t* A, int lda, const int8_t* Bt, int ldb, void* C, int ldc, int M, int N, int K,
+                   const pl_epilogue* e, pl_stream_t stream);
+}
 
 extern "C" int pl_conv_block_k(int C) { return C > 64 ? 128 : (C > 32 ? 64 : 32); }
 
@@ -1797,14 +1832,11 @@ extern "C" int pl_pack_conv_weight_i8(const int8_t* w_ohwi, int8_t* w_packed, in
   return launch_status();
 }
 
-extern "C" int pl_conv2d_i8_nhwc(const int8_t* x, const int8_t* w_packed, void* y,
-                                 const pl_conv_desc* d, const pl_epilogue* e, pl_stream_t stream) {
-  if (!x || !w_packed || !y || !d) return PL_ERR_ARG;
-  int rc = check_epi(e);
-  if (rc) return rc;
-  if (!driver().ok) return PL_ERR_DRIVER;
-  if (driver().cc_major != 10) return PL_ERR_DEVICE;
-  if (d->groups != 1) return PL_ERR_UNSUPPORTED;
+// one dense (groups == 1) launch; allow_halo = false keeps stride-1 windows on the im2col TMA path
+static int conv2d_dense(const int8_t* x, const int8_t* w_packed, void* y, const pl_conv_desc* d, const pl_epilogue* e,
+                        pl_stream_t stream, bool allow_halo, bool* used_halo) {
+  *used_halo = false;
+  int rc;
   if (d->N <= 0 || d->H <= 0 || d->W <= 0 || d->C <= 0 || d->K <= 0 || d->R <= 0 || d->S <= 0 ||
       d->stride_h <= 0 || d->stride_w <= 0 || d->dil_h <= 0 || d->dil_w <= 0 || d->ldx < d->C ||
       d->ldy < d->K)
@@ -1829,7 +1861,7 @@ extern "C" int pl_conv2d_i8_nhwc(const int8_t* x, const int8_t* w_packed, void* 
   // tile well enough; everything else keeps the im2col TMA path
   const int WP = Q + d->S - 1;
   const int hk = WP <= kBM ? kBM / WP : 0;
-  bool halo = !as_gemm && d->stride_h == 1 && d->stride_w == 1 && d->dil_h == 1 && d->dil_w == 1 && hk >= 1 &&
+  bool halo = allow_halo && !as_gemm && d->stride_h == 1 && d->stride_w == 1 && d->dil_h == 1 && d->dil_w == 1 && hk >= 1 &&
               WP <= 256 && hk + d->R - 1 <= 256 && Q <= 256 && env_int("PL_IGEMM_NO_HALO", 0) == 0 &&
               d->W + d->pad_l + d->pad_r == WP;
   int bands = 0;
@@ -1839,6 +1871,7 @@ extern "C" int pl_conv2d_i8_nhwc(const int8_t* x, const int8_t* w_packed, void* 
     if (eff < 0.6) halo = false;
   }
   if (halo) p.halo_m_tiles = d->N * bands;
+  *used_halo = halo;
   rc = common_setup(p, (long long)d->N * P * Q, d->K, y, d->ldy, e, d->C, d->R * d->S);
   if (rc) return rc;
   CUtensorMap ta, tb;
@@ -1884,6 +1917,47 @@ extern "C" int pl_conv2d_i8_nhwc(const int8_t* x, const int8_t* w_packed, void* 
   rc = encode_2d(&tb, w_packed, wrow, (uint64_t)d->K, wrow, p.BK, p.BN);
   if (rc) return rc;
   return launch_igemm(ta, tb, p, stream);
+}
+
+extern "C" int pl_conv2d_i8_nhwc(const int8_t* x, const int8_t* w_packed, void* y,
+                                 const pl_conv_desc* d, const pl_epilogue* e, pl_stream_t stream) {
+  if (!x || !w_packed || !y || !d) return PL_ERR_ARG;
+  int rc = check_epi(e);
+  if (rc) return rc;
+  if (!driver().ok) return PL_ERR_DRIVER;
+  if (driver().cc_major != 10) return PL_ERR_DEVICE;
+  if (d->groups < 1 || d->C % d->groups || d->K % d->groups) return PL_ERR_ARG;
+  auto one = [&](const int8_t* xg, const int8_t* wg, void* yg, const pl_conv_desc* dg, const pl_epilogue* eg) {
+    bool used_halo = false;
+    int r = conv2d_dense(xg, wg, yg, dg, eg, stream, true, &used_halo);
+    // halo mode is chosen from the geometry; when its two input buffers + the filter ring do not fit the
+    // shared memory (e.g. 5x5 / 7x7 stride 1 with C >= 128 on wide images) the im2col path takes the layer
+    if (r == PL_ERR_UNSUPPORTED && used_halo) r = conv2d_dense(xg, wg, yg, dg, eg, stream, false, &used_halo);
+    return r;
+  };
+  if (d->groups == 1) return one(x, w_packed, y, d, e);
+  // 1 < groups < C (lite/kernels/arm/conv_gemmlike.cc:84-264 loops over the groups the same way): group g reads
+  // the channel slice [g * C/G, +C/G) of every pixel (pointer offset + the full pitch), the filter rows
+  // [g * K/G, +K/G) of the packed filter (packed with C = C/G) and writes the output slice [g * K/G, +K/G)
+  const int G = d->groups, Cg = d->C / G, Kg = d->K / G;
+  if (Cg % 16) return PL_ERR_UNSUPPORTED;  // every group's slice must start on a 16-byte boundary (TMA)
+  if (e->residual) return PL_ERR_UNSUPPORTED;
+  const int bk = pl_conv_block_k(Cg);
+  const size_t wrow = (size_t)d->R * d->S * ((Cg + bk - 1) / bk * bk);
+  const size_t yb = e->out_dtype == PL_OUT_INT8 ? 1 : 4;
+  for (int g = 0; g < G; ++g) {
+    pl_conv_desc dg = *d;
+    dg.groups = 1;
+    dg.C = Cg;
+    dg.K = Kg;
+    pl_epilogue eg = *e;
+    if (eg.scale) eg.scale += (size_t)g * Kg;
+    if (eg.bias) eg.bias += (size_t)g * Kg;
+    rc = one(x + (size_t)g * Cg, w_packed + (size_t)g * Kg * wrow,
+             reinterpret_cast<char*>(y) + (size_t)g * Kg * yb, &dg, &eg);
+    if (rc) return rc;
+  }
+  return PL_OK;
 }
 
 // ---- thin first layers: direct conv on one-word-per-pixel input ------------------
@@ -2199,12 +2273,17 @@ extern "C" int pl_gemm_i8_peers_static(const int8_t* A, int lda, const int8_t* B
     return PL_ERR_LIMIT;
   }
   // the timeline trace of the debug builds is the one allocating corner of the launch path
-  const char* trace_path = getenv("PL_DBG_TRACE");
-  if (trace_path && *trace_path) return PL_ERR_UNSUPPORTED;
+  if (env_int("PL_DBG_TRACE_ON", 0)) return PL_ERR_UNSUPPORTED;
   void* maps = nullptr;
   int rc = static_peer_maps_address(&maps);
   if (rc) return rc;
   return pl_gemm_i8_peers(A, lda, Bt, ldb, C, C_peers, n_peers, maps, ldc, M, N, K, e, stream);
+}
+
+extern "C" void pl_refresh_knobs(void) {
+  KnobCache& k = knobs();
+  std::lock_guard<std::mutex> lock(k.mu);
+  k.n = 0;
 }
 
 extern "C" int pl_gemm_i8(const int8_t* A, int lda, const int8_t* Bt, int ldb, void* C, int ldc,
@@ -2218,6 +2297,11 @@ extern "C" int pl_gemm_i8(const int8_t* A, int lda, const int8_t* Bt, int ldb, v
   if ((reinterpret_cast<uintptr_t>(A) & 15) || (reinterpret_cast<uintptr_t>(Bt) & 15) || (lda % 16) ||
       (ldb % 16))
     return PL_ERR_ALIGN;
+  // batch-1 .. batch-8 fc: a weight-streaming kernel (gemv_i8.cu) instead of a 1/128-full tensor-core tile
+  if (M <= 8 && env_int("PL_NO_GEMV", 0) == 0) {
+    rc = launch_gemv_i8(A, lda, Bt, ldb, C, ldc, M, N, K, e, stream);
+    if (rc != -100) return rc;
+  }
   IgemmParams p{};
   p.BK = pl_conv_block_k(K);
   p.mode = 0;

@@ -288,7 +288,8 @@ int plk_run_pool(void* x, void* out, const char* type, const int* ksize, const i
   p.paddings = std::make_shared<std::vector<int>>(pads, pads + 4);
   p.global_pooling = global_pooling != 0;
   p.exclusive = exclusive != 0;
-  p.ceil_mode = ceil_mode != 0;
+  p.ceil_mode = (ceil_mode & 1) != 0;
+  p.adaptive = (ceil_mode & 2) != 0;  // bit 1 of the flag word: PoolParam::adaptive (ksize = output size)
   p.enable_int8 = true;
   p.input_scale = input_scale;
   p.output_scale = output_scale;

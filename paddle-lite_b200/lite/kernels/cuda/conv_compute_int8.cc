@@ -63,18 +63,20 @@ void ConvComputeInt8<Ptype_out>::PrepareForRun() {
       for (int64_t t = 0; t < R * S; ++t)
         for (int64_t c = 0; c < C; ++c) bt[k * ldA_ + t * 4 + c] = w[(k * R * S + t) * C + c];
     packed_filter_.Assign<int8_t, lite::DDim, TARGET(kCUDA)>(bt.data(), DDim(std::vector<int64_t>{K, ldA_}));
-  } else if (param.groups == 1) {
+  } else if (param.groups == C && K == C && Cg == 1) {
+    path_ = kDepthwise;
+  } else {
+    // dense, or 1 < groups < C (the C-ABI loops over the groups like lite/kernels/arm/conv_gemmlike.cc:84-264):
+    // the filter is packed with its own channel count C / groups
+    CHECK(param.groups == 1 || Cg % 16 == 0)
+        << "grouped int8 conv needs 16-byte aligned channel slices (C / groups = " << Cg << ")";
     path_ = kDense;
     const size_t bytes = pl_conv_packed_weight_bytes(static_cast<int>(K), static_cast<int>(R), static_cast<int>(S),
-                                                     static_cast<int>(C));
+                                                     static_cast<int>(Cg));
     packed_filter_.Resize(DDim({static_cast<int64_t>(bytes)}));
     PL_CALL(pl_pack_conv_weight_i8(param.filter->data<int8_t>(), packed_filter_.mutable_data<int8_t>(TARGET(kCUDA)),
-                                   static_cast<int>(K), static_cast<int>(R), static_cast<int>(S), static_cast<int>(C),
+                                   static_cast<int>(K), static_cast<int>(R), static_cast<int>(S), static_cast<int>(Cg),
                                    reinterpret_cast<pl_stream_t>(stream)));
-  } else {
-    CHECK(param.groups == C && K == C && Cg == 1)
-        << "grouped int8 conv other than depthwise is not supported (groups=" << param.groups << ")";
-    path_ = kDepthwise;
   }
 }
 

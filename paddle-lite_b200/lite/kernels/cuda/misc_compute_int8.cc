@@ -109,9 +109,21 @@ class PoolComputeInt8 : public KernelLite<TARGET(kCUDA), PRECISION(kInt8), DATAL
     auto& param = this->Param<param_t>();
     const auto& d = param.x->dims();  // NHWC
     CHECK_EQ(d.size(), 4u);
-    CHECK(!param.adaptive) << "adaptive int8 pooling is not supported";
     CHECK(param.pooling_type == "max" || param.pooling_type == "avg") << "pooling_type " << param.pooling_type;
     const int N = (int)d[0], H = (int)d[1], W = (int)d[2], C = (int)d[3];
+    if (param.adaptive && !param.global_pooling) {
+      // ksize is the output size (lite/kernels/cuda/pool_compute.cu:256-350, lite/operators/pool_op.cc)
+      const int P = param.ksize.at(0), Q = param.ksize.at(1);
+      param.output->Resize(DDim({N, P, Q, C}));
+      const bool o8 = Ptype_out == PRECISION(kInt8);
+      void* ya = o8 ? static_cast<void*>(param.output->template mutable_data<int8_t>(TARGET(kCUDA)))
+                    : static_cast<void*>(param.output->template mutable_data<float>(TARGET(kCUDA)));
+      PL_CALL(pl_adaptive_pool2d_i8_nhwc(param.x->template data<int8_t>(), C, ya, C, N, H, W, C, P, Q,
+                                         param.pooling_type == "max" ? PL_POOL_MAX : PL_POOL_AVG,
+                                         o8 ? param.input_scale / param.output_scale : param.input_scale,
+                                         o8 ? PL_OUT_INT8 : PL_OUT_FP32, PL_ROUND_ARM, StreamOf(this->ctx_.get())));
+      return;
+    }
     int kh = param.ksize.at(0), kw = param.ksize.at(1);
     int pt = 0, pb = 0, pl = 0, pr = 0;
     if (param.paddings && param.paddings->size() == 4) {

@@ -180,10 +180,10 @@ def run_io_copy_roundtrip(x):
 
 
 def run_pool(x, pooling_type, ksize, strides, pads, input_scale, output_scale, global_pooling=False, exclusive=True,
-             ceil_mode=False, out_int8=True):
+             ceil_mode=False, out_int8=True, adaptive=False):
     tx, out = Tensor(x), Tensor()
     _ck(lib().plk_run_pool(tx.h, out.h, pooling_type.encode(), _ia(ksize), _ia(strides), _ia(pads),
-                           int(global_pooling), int(exclusive), int(ceil_mode), C.c_float(input_scale),
+                           int(global_pooling), int(exclusive), int(ceil_mode) | (2 if adaptive else 0), C.c_float(input_scale),
                            C.c_float(output_scale), int(out_int8)))
     return out.numpy()
 

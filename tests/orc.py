@@ -198,6 +198,15 @@ def pool2d(x, ksize, strides, pads, pool_type, exclusive=True, rescale=1.0,
     return y
 
 
+def adaptive_pool2d(x, out_hw, pool_type, rescale=1.0, out=OUT_INT8, rnd=ROUND_ARM):
+    x = np.ascontiguousarray(x, np.int8)
+    N, H, W, Cc = x.shape
+    P, Q = out_hw
+    y = np.empty((N, P, Q, Cc), _NP_OUT[out])
+    lib().orc_adaptive_pool2d_i8_nhwc(_p(x), _p(y), N, H, W, Cc, P, Q, pool_type, _f(rescale), out, rnd)
+    return y
+
+
 def add(a, b, sa, sb, act=ACT_NONE, act_arg=0.0, out=OUT_INT8, rnd=ROUND_ARM):
     a = np.ascontiguousarray(a, np.int8)
     b = np.ascontiguousarray(b, np.int8)

@@ -209,6 +209,54 @@ HALO_CASES = [
 ]
 
 
+@pytest.mark.parametrize("case", [
+    # stride-1 windows whose halo buffers + filter ring do not fit the shared memory: the launch falls back to the
+    # im2col path instead of failing (round-1 advisor finding)
+    (2, 96, 96, 128, 256, 5, 5, 1, (2, 2, 2, 2), 1),
+    (1, 40, 110, 128, 256, 7, 7, 1, (3, 3, 3, 3), 1),
+    (1, 30, 120, 192, 64, 5, 5, 1, (2, 2, 2, 2), 1),
+])
+@pytest.mark.parametrize("out", ["int8", "fp32"])
+def test_conv_halo_falls_back_when_smem_is_short(pl, case, out):
+    x, w, ws, bias, si, so = conv_inputs(case, 71)
+    N, H, W, Cc, K, R, S, st, pads, dl = case
+    o = orc.OUT_INT8 if out == "int8" else orc.OUT_FP32
+    sf, bf, _ = orc.fold_scales(ws, K, si, so, o, bias)
+    want = orc.conv2d(x, w, sf, bf, (st, st), pads, (dl, dl), 1, orc.ACT_RELU, 0.0, o)
+    got = host(pl.conv2d(dev(pad_c(x, rup(Cc, 16))), pl.pack_conv_weight(dev(w)), K, R, S, dev(sf), dev(bf),
+                         (st, st), pads, (dl, dl), orc.ACT_RELU, 0.0, o, Cc=Cc))
+    if o == orc.OUT_FP32:
+        assert np.allclose(got, want, rtol=1e-5, atol=1e-6)
+    else:
+        assert np.array_equal(got, want)
+
+
+@pytest.mark.parametrize("case", [
+    # N, H, W, C, K, R, stride, pad, groups  (1 < groups < C: lite/kernels/arm/conv_gemmlike.cc:84-264)
+    (2, 14, 14, 64, 64, 3, 1, 1, 4),
+    (1, 28, 28, 128, 96, 1, 1, 0, 2),
+    (1, 15, 17, 96, 48, 3, 2, 1, 3),
+    (3, 8, 8, 256, 512, 3, 1, 1, 8),
+])
+@pytest.mark.parametrize("out", ["int8", "fp32", "int32"])
+def test_grouped_dense_conv(pl, case, out):
+    N, H, W, Cc, K, R, st, pd, G = case
+    rng = np.random.default_rng(hash(case) & 0xFFFF)
+    x = rng.integers(-127, 128, (N, H, W, Cc), dtype=np.int8)
+    w = rng.integers(-127, 128, (K, R, R, Cc // G), dtype=np.int8)
+    ws = ((1 + np.arange(K) % 7) / (7 * 127)).astype(np.float32)
+    bias = rng.uniform(-1, 1, K).astype(np.float32)
+    o = {"int8": orc.OUT_INT8, "fp32": orc.OUT_FP32, "int32": orc.OUT_INT32}[out]
+    sf, bf, _ = orc.fold_scales(ws, K, 1 / 127, (Cc // G) * R * R / 127 / 4, o if o != orc.OUT_INT32 else orc.OUT_FP32, bias)
+    want = orc.conv2d(x, w, sf, bf, (st, st), (pd,) * 4, (1, 1), G, orc.ACT_RELU, 0.0, o)
+    got = host(pl.conv2d(dev(x), pl.pack_conv_weight(dev(w)), K, R, R, dev(sf), dev(bf), (st, st), (pd,) * 4, (1, 1),
+                         orc.ACT_RELU, 0.0, o, Cc=Cc, groups=G))
+    if o == orc.OUT_FP32:
+        assert np.allclose(got, want, rtol=1e-5, atol=1e-6)
+    else:
+        assert np.array_equal(got, want)
+
+
 @pytest.mark.parametrize("case", HALO_CASES)
 @pytest.mark.parametrize("mode", ["int32", "int8_relu", "fp32_res", "int8_res"])
 def test_conv_halo_reuse_path(pl, case, mode, monkeypatch):
@@ -241,7 +289,12 @@ def test_conv_halo_reuse_path(pl, case, mode, monkeypatch):
     assert got.shape == want.shape
     assert np.array_equal(got, want)
     monkeypatch.setenv("PL_IGEMM_NO_HALO", "1")
-    assert np.array_equal(go(), want)
+    pl.lib().pl_refresh_knobs()  # knobs are cached per process
+    try:
+        assert np.array_equal(go(), want)
+    finally:
+        monkeypatch.delenv("PL_IGEMM_NO_HALO")
+        pl.lib().pl_refresh_knobs()
 
 
 def test_conv_writes_into_channel_slice(pl):
@@ -725,3 +778,40 @@ def test_humanseg_model_layers(pl):
     mod = importlib.util.module_from_spec(spec)
     spec.loader.exec_module(mod)
     assert mod.check(batch=2) == 20
+
+
+@pytest.mark.parametrize("shape,out_hw", [((2, 14, 14, 64), (3, 3)), ((1, 7, 9, 20), (2, 4)), ((3, 10, 10, 33), (1, 1)),
+                                          ((1, 5, 5, 16), (5, 5)), ((2, 13, 6, 48), (4, 6))])
+@pytest.mark.parametrize("typ", ["max", "avg"])
+@pytest.mark.parametrize("out", ["int8", "fp32"])
+def test_adaptive_pool(pl, shape, out_hw, typ, out):
+    """PoolParam::adaptive (lite/kernels/cuda/pool_compute.cu:69-187 index rules) on int8 NHWC."""
+    rng = np.random.default_rng(31)
+    x = rng.integers(-128, 128, shape, dtype=np.int8)
+    t = orc.POOL_MAX if typ == "max" else orc.POOL_AVG
+    o = orc.OUT_INT8 if out == "int8" else orc.OUT_FP32
+    want = orc.adaptive_pool2d(x, out_hw, t, 0.61, o)
+    got = host(pl.adaptive_pool2d(dev(x), out_hw, t, 0.61, o))
+    assert np.array_equal(got, want)
+
+
+@pytest.mark.parametrize("M,K,N", [(1, 4096, 4096), (1, 1024, 1000), (2, 2048, 1000), (3, 100, 33), (4, 777, 130),
+                                   (5, 1600, 64), (8, 4111, 257), (1, 16, 4), (1, 65600, 8)])
+@pytest.mark.parametrize("out", ["int8", "fp32", "int32"])
+def test_gemv_skinny_m(pl, M, K, N, out):
+    """M <= 8 takes the weight-streaming kernel (gemv_i8.cu): K tails with garbage in A's pad bytes, N tails,
+    k-splits across the warps of a CTA.  Same contract as the tensor-core GEMM."""
+    rng = np.random.default_rng(M * 1000 + N)
+    ldk = rup(K, 16)
+    A = rng.integers(-127, 128, (M, ldk), dtype=np.int8)       # pad bytes are NOT zero
+    Bt = np.zeros((N, ldk), np.int8)
+    Bt[:, :K] = rng.integers(-127, 128, (N, K), dtype=np.int8)
+    scale = (rng.random(N) * 2e-3 / np.sqrt(K) + 1e-5).astype(np.float32)
+    bias = rng.standard_normal(N).astype(np.float32)
+    o = {"int8": orc.OUT_INT8, "fp32": orc.OUT_FP32, "int32": orc.OUT_INT32}[out]
+    want = orc.gemm(A[:, :K], Bt[:, :K], scale, bias, b_is_nk=True, act=orc.ACT_RELU, out=o)
+    got = host(pl.gemm(dev(A), dev(Bt), dev(scale), dev(bias), act=pl.ACT_RELU, out=o, K=K))
+    if o == orc.OUT_FP32:
+        assert np.allclose(got, want, rtol=1e-5, atol=1e-6)
+    else:
+        assert np.array_equal(got, want)

@@ -99,11 +99,18 @@ def test_depthwise_registered_under_conv2d_too(lh):
                op="conv2d")
 
 
+@pytest.mark.parametrize("out_int8", [True, False])
+def test_grouped_conv_through_the_registry(lh, out_int8):
+    # 1 < groups < C through ConvComputeInt8 (the reference's int8 conv takes any groups, conv_gemmlike.cc:84-264)
+    _conv_case(lh, np.random.default_rng(12), 2, 12, 12, 64, 96, 3, 3, (1, 1), (1, 1, 1, 1), (1, 1), 2, 1, 0.0, out_int8)
+    _conv_case(lh, np.random.default_rng(13), 1, 9, 9, 128, 64, 1, 1, (1, 1), (0, 0, 0, 0), (1, 1), 4, 0, 0.0, out_int8)
+
+
 def test_conv2d_errors(lh):
     rng = np.random.default_rng(3)
-    x, w = _rand_i8(rng, (1, 8, 8, 32)), _rand_i8(rng, (32, 3, 3, 16))
-    with pytest.raises(lh.LiteError, match="group"):
-        lh.run_conv("conv2d", x, w, None, 0.1, [0.1], 0.1, groups=2)
+    x, w = _rand_i8(rng, (1, 8, 8, 32)), _rand_i8(rng, (32, 3, 3, 8))
+    with pytest.raises(lh.LiteError, match="group"):  # C / groups = 8: slices not 16-byte aligned
+        lh.run_conv("conv2d", x, w, None, 0.1, [0.1], 0.1, groups=4)
     w = _rand_i8(rng, (32, 3, 3, 32))
     with pytest.raises(lh.LiteError, match="weight_scale"):
         lh.run_conv("conv2d", x, w, None, 0.1, [0.1, 0.2], 0.1)
@@ -277,3 +284,13 @@ def test_relu_kernels(lh):
     np.testing.assert_array_equal(lh.run_relu(x), orc.relu_i8(x))
     # relu6 on a tensor of scale 0.1: the clip sits at round(6 / 0.1) = 60
     np.testing.assert_array_equal(lh.run_relu(x, relu6=True, clip=6.0, input_scale=0.1), orc.relu_i8(x, 60))
+
+
+@pytest.mark.parametrize("typ", ["max", "avg"])
+def test_adaptive_pool_through_the_registry(lh, typ):
+    """PoolParam::adaptive (ksize = output size, lite/kernels/cuda/pool_compute.cu:256-350)."""
+    rng = np.random.default_rng(41)
+    x = _rand_i8(rng, (2, 13, 9, 24))
+    want = orc.adaptive_pool2d(x, (4, 3), orc.POOL_MAX if typ == "max" else orc.POOL_AVG, 0.02 / 0.03, orc.OUT_INT8)
+    got = lh.run_pool(x, typ, [4, 3], [1, 1], [0, 0, 0, 0], 0.02, 0.03, adaptive=True)
+    np.testing.assert_array_equal(got, want)

@@ -285,3 +285,23 @@ def test_matmul_kat_all_ones():
     for b in range(4):
         acc = orc.gemm(x[b], y[b], None, None, b_is_nk=True, out=orc.OUT_INT32)
         assert acc.shape == (1, 1) and int(acc[0, 0]) == 2
+
+
+def test_adaptive_pool_index_rule():
+    """floor / ceil window rule of lite/kernels/cuda/pool_compute.cu:89-94 restated in numpy (double arithmetic as
+    the reference computes it); P == H reproduces the identity, P == 1 the global pool."""
+    rng = np.random.default_rng(17)
+    x = rng.integers(-127, 128, (2, 11, 7, 5), dtype=np.int8)  # -128 would hit the ARM -127 floor
+    for P, Q in ((3, 2), (11, 7), (1, 1), (4, 5)):
+        for typ in (orc.POOL_MAX, orc.POOL_AVG):
+            got = orc.adaptive_pool2d(x, (P, Q), typ, 1.0, orc.OUT_FP32)
+            want = np.empty_like(got)
+            for p_ in range(P):
+                h0, h1 = int(np.floor(p_ * 11 / P)), int(np.ceil((p_ + 1) * 11 / P))
+                for q_ in range(Q):
+                    w0, w1 = int(np.floor(q_ * 7 / Q)), int(np.ceil((q_ + 1) * 7 / Q))
+                    win = x[:, h0:h1, w0:w1, :].astype(np.float32)
+                    want[:, p_, q_, :] = win.max((1, 2)) if typ == orc.POOL_MAX else \
+                        (win.sum((1, 2)) / np.float32((h1 - h0) * (w1 - w0))).astype(np.float32)
+            assert np.array_equal(got, want)
+    assert np.array_equal(orc.adaptive_pool2d(x, (11, 7), orc.POOL_MAX, 1.0, orc.OUT_INT8), x)
