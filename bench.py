@@ -282,7 +282,10 @@ def build_net(ctx, net_name, batch, feed="f32"):
     if feed == "u8":
         kw = {"mean": IMAGENET_MEAN, "norm": IMAGENET_NORM}
     x_host = host_input(ctx, prog, batch, feed)
-    net = ctx.nets.DeviceNet(prog, batch, device=ctx.dev, feed=feed, **kw)
+    if net_name == "humanseg":
+        net = importlib_model(ctx).GraphNet(prog, batch, device=ctx.dev, feed=feed, **kw)
+    else:
+        net = ctx.nets.DeviceNet(prog, batch, device=ctx.dev, feed=feed, **kw)
     if not net.calibrated:
         net.calibrate(x_host[:min(4, batch)].to(ctx.dev))
     net.bind()

@@ -281,6 +281,33 @@ int pl_relu_i8(const int8_t* x, int8_t* y, int64_t n, int hi, pl_stream_t stream
 int pl_concat_shuffle2_i8_nhwc(const int8_t* a, int lda, const int8_t* b, int ldb, int8_t* y,
                                int ldy, int c_half, int64_t pixels, pl_stream_t stream);
 
+/* ---- fp32 ops a quantised model keeps between / after its int8 convs -----------
+ * NHWC fp32, pitches in elements.
+ *   pl_channel_gather_f32_nhwc   dst[p, j] = srcs[table[j][0]][p * ld + table[j][1]]: any chain of concat
+ *                                (lite/backends/arm/math/concat.h:29-60), shuffle_channel (shuffle_channel.cc:24-76)
+ *                                and split (split.cc:54-83) composed into one channel map, at most 16 sources;
+ *                                out_dtype PL_OUT_INT8 also applies the calib that follows such a chain in a
+ *                                quantised model (lite/kernels/cuda/calib_compute.cu:27-95: x * (1 / scale), half
+ *                                away, [-127, 127]).  table_dev: C x 2 int32 on the device.
+ *   pl_conv2d_transpose_f32_nhwc lite/kernels/arm/conv_transpose_compute.cc:1-230 (golden deconv_basic,
+ *                                lite/tests/utils/naive_math_impl.h:540-642); w as the reference stores it
+ *                                [Cin, Cout, kh, kw]; dilation 1, groups 1; optional fused relu and a quantised
+ *                                (int8) output for a quantised consumer
+ *   pl_add_f32                   lite/backends/cuda/math/elementwise.cu (tensor + tensor, optional relu)
+ *   pl_softmax_f32_nhwc          lite/kernels/cuda/softmax_compute.cu, over the channels of every pixel
+ *   pl_scale_f32                 lite/kernels/cuda/scale_compute.cc */
+int pl_channel_gather_f32_nhwc(int n_src, const float* const* srcs, const int* src_ld, const int32_t* table_dev,
+                               void* dst, int ldd, int C, int64_t pixels, int out_dtype, float scale, int round_mode,
+                               pl_stream_t stream);
+int pl_conv2d_transpose_f32_nhwc(const float* x, const float* w_iohw, const float* bias, void* y, int N, int H, int W,
+                                 int Cin, int Cout, int kh, int kw, int stride_h, int stride_w, int pad_t, int pad_l,
+                                 int P, int Q, int ldy, int act, float act_arg, int out_dtype, float out_scale,
+                                 int round_mode, pl_stream_t stream);
+int pl_add_f32(const float* a, const float* b, float* y, int64_t n, int act, pl_stream_t stream);
+int pl_softmax_f32_nhwc(const float* x, float* y, int64_t pixels, int C, int ldx, int ldy, pl_stream_t stream);
+int pl_scale_f32(const float* x, float* y, int64_t n, float scale, float bias, int bias_after_scale,
+                 pl_stream_t stream);
+
 /* ---- introspection ---------------------------------------------------------- */
 /* number of kernels this library has launched in this process (bench.py's
  * gpu_launches claim) */

@@ -497,6 +497,46 @@ int orc_adaptive_pool2d_i8_nhwc(const int8_t* x, void* y, int N, int H, int W, i
 }
 
 /*
+ * conv2d_transpose fp32 NHWC, gather form with a FIXED accumulation order (kh, kw ascending, then ci ascending,
+ * one fmaf each, bias added last): the value is what lite/tests/utils/naive_math_impl.h:540-642 (deconv_basic:
+ * gemm + col2im) computes up to fp32 summation order -- tests/test_oracle.py checks the two within 1e-5 -- and
+ * the order is pinned because a quantised consumer follows this op in the shipped segmentation model.
+ * w: [Cin, Cout, kh, kw] (the reference's layout), dilation 1, groups 1.  out_scale > 0: int8 output through the
+ * ARM calib (x * (1 / scale), half away, [-127, 127]).
+ */
+int orc_conv2d_transpose_f32_nhwc(const float* x, const float* w, const float* bias, void* y, int N, int H, int W,
+                                  int Ci, int Co, int kh, int kw, int sh, int sw, int pt, int pl, int P, int Q,
+                                  int relu, float out_scale) {
+  const float inv = out_scale > 0.f ? 1.f / out_scale : 0.f;
+#pragma omp parallel for collapse(2) schedule(static)
+  for (int n = 0; n < N; ++n)
+    for (int p = 0; p < P; ++p)
+      for (int q = 0; q < Q; ++q)
+        for (int co = 0; co < Co; ++co) {
+          float acc = 0.f;
+          for (int r = 0; r < kh; ++r) {
+            const int th = p + pt - r;
+            if (th < 0 || th % sh || th / sh >= H) continue;
+            for (int s = 0; s < kw; ++s) {
+              const int tw = q + pl - s;
+              if (tw < 0 || tw % sw || tw / sw >= W) continue;
+              const float* xp = x + (((int64_t)n * H + th / sh) * W + tw / sw) * Ci;
+              for (int ci = 0; ci < Ci; ++ci)
+                acc = fmaf(xp[ci], w[(((int64_t)ci * Co + co) * kh + r) * kw + s], acc);
+            }
+          }
+          float v = acc + (bias ? bias[co] : 0.f);
+          if (relu) v = v > 0.f ? v : 0.f;
+          const int64_t o = (((int64_t)n * P + p) * Q + q) * Co + co;
+          if (out_scale > 0.f)
+            ((int8_t*)y)[o] = orc_round_sat_i8(inv * v, ORC_ROUND_ARM);
+          else
+            ((float*)y)[o] = v;
+        }
+  return 0;
+}
+
+/*
  * int8 residual add + act + requant.  PARITY UNPINNED (the
  * reference's elementwise_add_int8_kernel takes fp32 inputs and is dead code).
  *   v = fma((float)a, sa, (float)b * sb), sa = a_scale/out_scale, sb likewise

@@ -542,3 +542,45 @@ def measure_i8_mma_peak(iters=20000, bn=256):
     b.record()
     torch.cuda.synchronize()
     return ctas * iters * 8 * 2.0 * 128 * bn * 32 / (a.elapsed_time(b) * 1e-3) / 1e12  # 8 K=32 MMAs per iteration
+
+
+# ---- fp32 ops between / after the int8 convs of a quantised model (fp32_tail.cu) -------------------------
+def channel_gather(srcs, table_dev, C_dst, y, out=OUT_FP32, scale=0.0, rnd=ROUND_ARM):
+    """srcs: fp32 NHWC device tensors of equal N, H, W; table_dev: int32 [C_dst, 2] (source index, channel);
+    y: fp32 [N,H,W,C_dst] or int8 [N,H,W,ld] written in place."""
+    n = len(srcs)
+    ptrs = (C.c_void_p * n)(*[C.c_void_p(s.data_ptr()) for s in srcs])
+    lds = (C.c_int * n)(*[int(s.stride(-2)) for s in srcs])
+    pixels = srcs[0].shape[0] * srcs[0].shape[1] * srcs[0].shape[2]
+    _check(lib().pl_channel_gather_f32_nhwc(n, ptrs, lds, _ptr(table_dev), _ptr(y), int(y.stride(-2)), C_dst,
+                                            C.c_int64(pixels), out, _f(scale), rnd, _stream()),
+           "pl_channel_gather_f32_nhwc")
+    return y
+
+
+def conv2d_transpose_f32(x, w_iohw, bias, stride, pad, y, Cout, act=ACT_NONE, out=OUT_FP32, out_scale=0.0):
+    N, H, W, Ci = x.shape
+    kh, kw = w_iohw.shape[2], w_iohw.shape[3]
+    P, Q = y.shape[1], y.shape[2]
+    _check(lib().pl_conv2d_transpose_f32_nhwc(_ptr(x), _ptr(w_iohw), _ptr(bias), _ptr(y), N, H, W, Ci, Cout, kh, kw,
+                                              stride, stride, pad, pad, P, Q, int(y.stride(-2)), act, _f(0.0), out,
+                                              _f(out_scale), ROUND_ARM, _stream()), "pl_conv2d_transpose_f32_nhwc")
+    return y
+
+
+def add_f32(a, b, y, act=ACT_NONE):
+    _check(lib().pl_add_f32(_ptr(a), _ptr(b), _ptr(y), C.c_int64(a.numel()), act, _stream()), "pl_add_f32")
+    return y
+
+
+def softmax_f32(x, y):
+    pixels = x.numel() // x.shape[-1]
+    _check(lib().pl_softmax_f32_nhwc(_ptr(x), _ptr(y), C.c_int64(pixels), x.shape[-1], int(x.stride(-2)),
+                                     int(y.stride(-2)), _stream()), "pl_softmax_f32_nhwc")
+    return y
+
+
+def scale_f32(x, y, scale, bias, bias_after_scale=True):
+    _check(lib().pl_scale_f32(_ptr(x), _ptr(y), C.c_int64(x.numel()), _f(scale), _f(bias), int(bias_after_scale),
+                              _stream()), "pl_scale_f32")
+    return y

@@ -207,6 +207,21 @@ def adaptive_pool2d(x, out_hw, pool_type, rescale=1.0, out=OUT_INT8, rnd=ROUND_A
     return y
 
 
+def conv2d_transpose_f32(x_nhwc, w_iohw, bias, strides, pads_tl, relu=False, out_scale=0.0):
+    """x [N,H,W,Cin] fp32, w [Cin,Cout,kh,kw]; pads_tl = (top, left); symmetric pads assumed for the output size."""
+    x = np.ascontiguousarray(x_nhwc, np.float32)
+    w = np.ascontiguousarray(w_iohw, np.float32)
+    N, H, W, Ci = x.shape
+    _, Co, kh, kw = w.shape
+    P = (H - 1) * strides[0] - 2 * pads_tl[0] + kh
+    Q = (W - 1) * strides[1] - 2 * pads_tl[1] + kw
+    y = np.empty((N, P, Q, Co), np.int8 if out_scale > 0 else np.float32)
+    b = None if bias is None else np.ascontiguousarray(bias, np.float32)
+    lib().orc_conv2d_transpose_f32_nhwc(_p(x), _p(w), _p(b), _p(y), N, H, W, Ci, Co, kh, kw, strides[0], strides[1],
+                                        pads_tl[0], pads_tl[1], P, Q, int(relu), _f(out_scale))
+    return y
+
+
 def add(a, b, sa, sb, act=ACT_NONE, act_arg=0.0, out=OUT_INT8, rnd=ROUND_ARM):
     a = np.ascontiguousarray(a, np.int8)
     b = np.ascontiguousarray(b, np.int8)
