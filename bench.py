@@ -346,7 +346,7 @@ def measure_net(ctx, net_name, batch, steps, warmup, clocks=False, e2e=True, pro
     ck = sampler.stop() if sampler else None
     macs = nets.program_macs(prog)
     rec = {"ms_per_step": ms / steps, "img_s": ctx.world * batch * steps / (ms * 1e-3), "batch_per_gpu": batch,
-           "launches_per_step": len(net.layers),
+           "launches_per_step": len(launch_order(net)),
            "tops": 2 * sum(macs.values()) * batch * ctx.world * steps / (ms * 1e-3) / 1e12}
     if ck is not None:
         rec["clocks"] = ck
@@ -414,6 +414,11 @@ def layer_bytes_ops(op, prog, batch):
     return ops, byts
 
 
+def launch_order(net):
+    """layer index of every launch of one step (a sub-batched schedule launches a layer once per chunk)"""
+    return net.launch_order() if hasattr(net, "launch_order") else list(range(len(net.layers)))
+
+
 def layer_times(ctx, net, prog, batch, ms_per_step):
     """Per-launch time INSIDE the graph replay: exclusive time of every kernel record,
     end_i - max(start_i, end_{i-1}) (programmatic dependent launch lets kernel i+1 start while kernel i
@@ -425,12 +430,13 @@ def layer_times(ctx, net, prog, batch, ms_per_step):
     per = None
     src = "cupti kernel records of graph replays (exclusive time), scaled to the CUDA-event step time"
     recs = kernel_records(ctx, net.replay, reps)
-    if recs is not None and len(recs) == L * reps:
+    order = launch_order(net)
+    if recs is not None and len(recs) == len(order) * reps:
         per = [0.0] * L
         for r in range(reps):
             prev_end = None
-            for i in range(L):
-                _, st, en = recs[r * L + i]
+            for j, i in enumerate(order):
+                _, st, en = recs[r * len(order) + j]
                 per[i] += (en - (st if prev_end is None else max(st, prev_end))) / 1e3
                 prev_end = en if prev_end is None else max(prev_end, en)
         per = [v / reps for v in per]
@@ -673,7 +679,7 @@ def run_b200(args):
     batch = args.batch or default_batch(args.net)
     n0 = ctx.pl.launch_count()
     rec, prog, net, x_host, table = measure_net(ctx, args.net, batch, args.steps, args.warmup, clocks=True)
-    launches_per_step = len(net.layers)
+    launches_per_step = len(launch_order(net))
     ms_per_step = rec["ms_per_step"]
     roof = headline_roofline(ctx, table, prog, batch, ms_per_step)
     if args.breakdown and rank == 0:

@@ -315,6 +315,10 @@ int64_t pl_launch_count(void);
 /* developer knobs (PL_* environment variables) are read once per process and cached; this drops the cache so
  * that a changed environment is seen by the next launch (tests that A/B two code paths call it) */
 void pl_refresh_knobs(void);
+/* the tile plan of the calling thread's most recent tensor-core launch (conv / gemm), for tests and benches that
+ * must know which code path ran: plan[0..9] = {mode, BN, BK, stages, cta_pairs, tile_pairs, band_rows, grid,
+ * filter_resident, epilogue variant}; returns the number of ints written (<= n) */
+int pl_last_igemm_plan(int* plan, int n);
 const char* pl_version(void);
 /* tensor-pipe micro-benchmark: issues `iters` back-to-back 128xBNx32
  * tcgen05.mma kind::i8 per CTA on `ctas` CTAs from resident smem; returns 0

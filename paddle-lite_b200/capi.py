@@ -95,6 +95,20 @@ def launch_count():
     return int(lib().pl_launch_count())
 
 
+PLAN_KEYS = ("mode", "BN", "BK", "stages", "cta_pairs", "tile_pairs", "band_rows", "grid", "filter_resident", "epi")
+
+
+def last_igemm_plan():
+    """Tile plan of this thread's most recent conv / gemm launch (pl_last_igemm_plan)."""
+    buf = (C.c_int * len(PLAN_KEYS))()
+    n = lib().pl_last_igemm_plan(buf, len(PLAN_KEYS))
+    return dict(zip(PLAN_KEYS[:n], list(buf)[:n]))
+
+
+def refresh_knobs():
+    lib().pl_refresh_knobs()
+
+
 def conv_out_size(i, k, d, p0, p1, s):
     return (i + p0 + p1 - (d * (k - 1) + 1)) // s + 1
 

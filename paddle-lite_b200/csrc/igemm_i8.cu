@@ -86,6 +86,11 @@ struct IgemmParams {
   // third (the bound of these launches); the epilogue of a pair no longer overlaps the
   // next mainloop, which long K amortises
   int mpair;
+  // CTA pairs (kernel template flag CTA2): clusters of two CTAs run MMAs of M = 256 (cta_group::2); every CTA
+  // loads its own A rows and HALF of each B block, so the L2 -> SM operand bytes per MAC drop by a third at
+  // BN = 256 and the filter of a 3x3 halo layer is fetched once per pair instead of once per CTA.  m_tiles
+  // then counts pair rows
+  int cta2;
   // tile order of long-K GEMMs (mode 0, streamed B): bands of group_m tile rows are walked column by column,
   // so that one wave of CTAs touches ~sqrt(SMs) A row blocks and B column blocks instead of 2-5 and all of B
   // (8192^3: 24 % of the L2 requests missed to DRAM with the row-major order)
@@ -313,18 +318,29 @@ __device__ __noinline__ void store_group16(const IgemmParams& p, const uint32_t*
 // stage buffers in the 32-byte-swizzled K-major layout the MMA descriptors expect.  One
 // k-block (32 bytes) = 32 / (4 * TSW) filter rows.  No im2col matrix ever exists in HBM.
 // k-steps of one k-block, unrolled: descriptors advance by 32 bytes (2 x 16-byte units)
-template <int KS>
+template <bool CTA2>
+__device__ __forceinline__ void umma_i8_t(uint32_t d_tmem, uint64_t da, uint64_t db, uint32_t idesc, uint32_t acc) {
+  if (CTA2) umma_i8_2sm(d_tmem, da, db, idesc, acc);
+  else umma_i8(d_tmem, da, db, idesc, acc);
+}
+template <bool CTA2>
+__device__ __forceinline__ void umma_commit_t(uint32_t bar) {
+  if (CTA2) umma_commit_2sm(bar);  // the barrier at this offset in both CTAs of the pair
+  else umma_commit(bar);
+}
+template <int KS, bool CTA2 = false>
 __device__ __forceinline__ void issue_kblock(uint32_t d_tmem, uint64_t da, uint64_t db, uint32_t idesc,
                                              bool fresh) {
 #pragma unroll
   for (int k = 0; k < KS; ++k)
-    umma_i8(d_tmem, da + (uint64_t)(k * 2), db + (uint64_t)(k * 2), idesc, (uint32_t)(!(fresh && k == 0)));
+    umma_i8_t<CTA2>(d_tmem, da + (uint64_t)(k * 2), db + (uint64_t)(k * 2), idesc, (uint32_t)(!(fresh && k == 0)));
 }
+template <bool CTA2 = false>
 __device__ __forceinline__ void issue_kblock_n(int ksteps, uint32_t d_tmem, uint64_t da, uint64_t db,
                                                uint32_t idesc, bool fresh) {
-  if (ksteps == 4) issue_kblock<4>(d_tmem, da, db, idesc, fresh);
-  else if (ksteps == 2) issue_kblock<2>(d_tmem, da, db, idesc, fresh);
-  else issue_kblock<1>(d_tmem, da, db, idesc, fresh);
+  if (ksteps == 4) issue_kblock<4, CTA2>(d_tmem, da, db, idesc, fresh);
+  else if (ksteps == 2) issue_kblock<2, CTA2>(d_tmem, da, db, idesc, fresh);
+  else issue_kblock<1, CTA2>(d_tmem, da, db, idesc, fresh);
 }
 // all taps of a resident R x S filter against one halo tile: one straight run of MMAs
 template <int R_, int S_, int KS>
@@ -374,8 +390,10 @@ __device__ __forceinline__ void issue_s2d(uint32_t d_tmem, uint64_t da0, uint64_
 
 // GROUPED is a kernel template flag: the banded order lives in its own instantiations (the large GEMMs);
 // sharing one kernel behind a runtime branch cost the conv nets 1.7 %
-template <bool GROUPED>
-__device__ __forceinline__ void tile_mn(const IgemmParams& p, int tile, int& tm, int& tn) {
+// CTA2: `tile` indexes a PAIR of 128-row blocks (p.m_tiles counts pair rows); the CTA of cluster rank `rank`
+// owns block 2 * tm + rank of it
+template <bool GROUPED, bool CTA2 = false>
+__device__ __forceinline__ void tile_mn(const IgemmParams& p, int tile, int& tm, int& tn, int rank = 0) {
   if (GROUPED) {
     const int per_band = p.group_m * p.n_tiles;
     const int band = tile / per_band, within = tile - band * per_band;
@@ -387,9 +405,10 @@ __device__ __forceinline__ void tile_mn(const IgemmParams& p, int tile, int& tm,
     tn = tile % p.n_tiles;
     tm = tile / p.n_tiles;
   }
+  if (CTA2) tm = 2 * tm + rank;
 }
 
-template <int EPI, int TR = 0, int TSW = 0, bool GROUPED = false>
+template <int EPI, int TR = 0, int TSW = 0, bool GROUPED = false, bool CTA2 = false>
 __global__ void __launch_bounds__(TR > 0 ? kThinThreads : kThreads, 1)
 igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
                 const __grid_constant__ CUtensorMap tmap_b,
@@ -439,6 +458,10 @@ igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
 #endif
   const int lane = threadIdx.x & 31;
   const int num_tiles = p.m_tiles * p.n_tiles;
+  // CTA pairs: both CTAs of a cluster walk the same sequence of pair tiles
+  const int cta_rank = CTA2 ? (int)cluster_ctarank() : 0;
+  const int tile0 = CTA2 ? (int)(blockIdx.x >> 1) : (int)blockIdx.x;
+  const int tstride = CTA2 ? (int)(gridDim.x >> 1) : (int)gridDim.x;
 #if defined(PL_EXP_POLL) && defined(PL_DEBUG_KNOBS)
   const bool poll_waits = (PL_DBG_FLAGS_V & 256) != 0;
   auto WAIT = [&](uint32_t bar, uint32_t parity) {
@@ -463,7 +486,8 @@ igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
     }
     for (int s = 0; s < kMaxAccStages; ++s) {
       mbar_init(bar_tfull + 8 * s, 1);
-      mbar_init(bar_tempty + 8 * s, EW / p.epi_groups);  // one arrival per epilogue warp of the tile's group
+      // one arrival per epilogue warp of the tile's group (pairs: of both CTAs, on the leader's barrier)
+      mbar_init(bar_tempty + 8 * s, (CTA2 ? 2 : 1) * (EW / p.epi_groups));
     }
     for (int s = 0; s < kMaxResBufs; ++s) mbar_init(bar_staged + 8 * s, EW / p.epi_groups);
     for (int s = 0; s < kMaxOutBufs; ++s) mbar_init(bar_ofree + 8 * s, 1);
@@ -481,13 +505,22 @@ igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
     fence_barrier_init();
   }
   if (warp == 1) {
-    tmem_alloc(smem_u32(&tmem_base_slot), p.tmem_cols);
-    tmem_relinquish();
+    if (CTA2) {
+      tmem_alloc_2sm(smem_u32(&tmem_base_slot), p.tmem_cols);
+      tmem_relinquish_2sm();
+    } else {
+      tmem_alloc(smem_u32(&tmem_base_slot), p.tmem_cols);
+      tmem_relinquish();
+    }
   }
   tc_fence_before();
-  __syncthreads();
+  if (CTA2) cluster_sync_all();  // the peer's barriers are initialised before anything signals them
+  else __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = tmem_base_slot;
+  // pair mode: the barriers the LEADER's MMA thread waits on (full, afull, tempty) live in the leader CTA;
+  // loads of both CTAs complete on them, the peer's epilogue warps arrive on them remotely
+  const uint32_t lead_delta = CTA2 ? mapa_shared(bar_full, 0) - bar_full : 0u;
 
   // Warps 0 and 1 hand their whole loop nest to ONE lane chosen by elect.sync: the compiler
   // then knows a single thread is active and keeps the loop state and every TMA / MMA operand
@@ -548,7 +581,7 @@ igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
         // one output row per tile: s2d_ta contiguous spans, one bulk copy each
         const int ta = p.s2d_ta;
         const uint32_t span = p.s2d_span_bytes, pitch = p.s2d_span_pitch;
-        for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++lt) {
+        for (int tile = tile0; tile < num_tiles; tile += tstride, ++lt) {
           PL_TRACE(0, lt, 0);
           const int img = (int)fdiv((uint32_t)tile, p.dBands);
           const int p0 = tile - img * p.bands;
@@ -562,10 +595,11 @@ igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
           if (++ab == halo_bufs) { ab = 0; aph ^= 1; }
         }
       }
-      for (int tile = blockIdx.x; tile < num_tiles && !p.s2d; tile += gridDim.x, ++lt) {
+      for (int tile = tile0; tile < num_tiles && !p.s2d; tile += tstride, ++lt) {
         PL_TRACE(0, lt, 0);
-        const int tn = tile % n_tiles, tm = tile / n_tiles;
+        const int tn = tile % n_tiles, tm = CTA2 ? 2 * (tile / n_tiles) + cta_rank : tile / n_tiles;
         const int n0 = tn * BN;
+        // (pairs: the block past the last one reads image N -- all zero fill, nothing stored)
         const int img = (int)fdiv((uint32_t)tm, p.dBands);
         const int p0 = (tm - img * p.bands) * p.hk;
         if (EPI == EPI_I8_RELU_RES) {
@@ -582,7 +616,11 @@ igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
           WAIT(bar_aempty + 8 * ab, aph ^ 1);
           PL_TRACE(0, lt, 1);
           {
-            if (PL_DBG_FLAGS_V & 8) {
+            if (CTA2) {  // both halo tiles complete on the leader's barrier
+              if (cta_rank == 0) mbar_arrive_expect_tx(bar_afull + 8 * ab, 2u * p.a_halo_tx);
+              tma_load_4d_2sm(smem_a + ab * p.a_halo_bytes, &tmap_a, bar_afull + 8 * ab + lead_delta, cbk, -p.pl_,
+                              p0 - p.pt, img);
+            } else if (PL_DBG_FLAGS_V & 8) {
               mbar_arrive(bar_afull + 8 * ab);
             } else {
               mbar_arrive_expect_tx(bar_afull + 8 * ab, p.a_halo_tx);
@@ -595,7 +633,10 @@ igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
           for (int tap = 0; tap < RS && !hres; ++tap) {
             WAIT(empty_b, phase ^ 1);
             {
-              if (PL_DBG_FLAGS_V & 4) {
+              if (CTA2) {  // this CTA's half of the filter block, completing on the leader's barrier
+                if (cta_rank == 0) mbar_arrive_expect_tx(full_b, 2u * tx);
+                tma_load_2d_2sm(dst_b, &tmap_b, full_b + lead_delta, kc, n0 + cta_rank * (BN >> 1));
+              } else if (PL_DBG_FLAGS_V & 4) {
                 mbar_arrive(full_b);
               } else {
                 mbar_arrive_expect_tx(full_b, tx);
@@ -608,12 +649,18 @@ igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
           }
         }
       }
+      if (CTA2) {  // (see the tail of the stage ring below)
+        for (int i = 0; i < halo_bufs; ++i) {
+          WAIT(bar_aempty + 8 * ab, aph ^ 1);
+          if (++ab == halo_bufs) { ab = 0; aph ^= 1; }
+        }
+      }
     }
     int lt = 0;
-    for (int tile = blockIdx.x; tile < num_tiles && !(TR > 0 && p.b_resident) && mode != 3; tile += gridDim.x, ++lt) {
+    for (int tile = tile0; tile < num_tiles && !(TR > 0 && p.b_resident) && mode != 3; tile += tstride, ++lt) {
       PL_TRACE(0, lt, 0);
       int tn_, tm_;
-      tile_mn<GROUPED>(p, tile, tm_, tn_);
+      tile_mn<GROUPED, CTA2>(p, tile, tm_, tn_, cta_rank);
       const int tn = tn_, tm = tm_;
       const int m0 = (tm * kBM) << p.mpair, n0 = tn * BN;  // pairs: one 256-row box
       if (EPI == EPI_I8_RELU_RES) {
@@ -641,7 +688,14 @@ igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
       for (int kb = 0; kb < num_kb; ++kb) {
         WAIT(empty_b, phase ^ 1);
         if (kb == 0) PL_TRACE(0, lt, 1);
-        {
+        if (CTA2) {
+          // own 128 (256) rows of A + own half of the B block, all completing on the leader's barrier
+          if (cta_rank == 0) mbar_arrive_expect_tx(full_b, 2u * tx);
+          const uint32_t fsig = full_b + lead_delta;
+          if (mode == 1) tma_load_im2col_4d_2sm(dst_a, &tmap_a, fsig, cbk, bw, bh, bn, offw, offh);
+          else tma_load_2d_2sm(dst_a, &tmap_a, fsig, kc, m0);
+          tma_load_2d_2sm(dst_b, &tmap_b, fsig, kc, n0 + cta_rank * (BN >> 1));
+        } else {
           mbar_arrive_expect_tx(full_b, tx);
           if (TR > 0) {
             // A arrives from the gather warps
@@ -667,6 +721,15 @@ igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
       }
       PL_TRACE(0, lt, 2);
     }
+    if (CTA2) {
+      // tail: every stage this CTA filled has been consumed (its multicast commit has landed here) before the
+      // CTA can leave -- no arrival may target the barriers of a CTA that has exited
+      for (int i = 0; i < stages; ++i) {
+        WAIT(empty_b, phase ^ 1);
+        ++stage; empty_b += 8;
+        if (stage == stages) { stage = 0; phase ^= 1; empty_b = bar_empty; }
+      }
+    }
     }
   } else if (warp == 1) {
     // ===================== MMA issuer =====================
@@ -675,10 +738,11 @@ igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
     // lane is ~30% slower on the 3x3 layers.)  The issue cost per MMA is what bounds the
     // short-K layers, so the k-steps of a block and the taps of a resident 3x3 filter are
     // fully unrolled (issue_kblock / issue_taps).
-    if (elect_one()) {
+    // (pairs: only the leader CTA issues; its MMAs run on both SMs)
+    if ((!CTA2 || cta_rank == 0) && elect_one()) {
     constexpr bool leader = true;
 #define PL_MTRACE(t, e) do { if (leader) PL_TRACE(1, t, e); } while (0)
-    const uint32_t idesc = make_idesc_i8((uint32_t)p.BN);
+    const uint32_t idesc = make_idesc_i8((uint32_t)p.BN, CTA2 ? 256u : 128u);
     const uint64_t desc_hi = make_smem_desc_base((uint32_t)p.BK);
     const int ksteps = p.BK / 32, stages = p.stages, num_kb = p.num_kb;
     const uint32_t a_step = p.a_stage_bytes >> 4, b_step = p.b_stage_bytes >> 4;
@@ -706,7 +770,7 @@ igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
         const uint64_t desc_a = make_smem_desc_pix16();
         const int ta = p.s2d_ta, kpr = p.s2d_kpr;
         const uint32_t pitch16 = p.s2d_span_pitch >> 4;
-        for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++lt) {
+        for (int tile = tile0; tile < num_tiles; tile += tstride, ++lt) {
           PL_MTRACE(lt, 0);
           WAIT(bar_tempty + 8 * as, aphase ^ 1);
           PL_MTRACE(lt, 1);
@@ -723,17 +787,17 @@ igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
           } else {
             for (int a = 0; a < ta; ++a, t_lo += pitch16)
               for (int ks = 0; ks < kpr; ++ks, bb += b_step)  // K = 32: pixels (2 ks, 2 ks + 1) of every row
-                umma_i8(d_tmem, desc_a | (uint64_t)(t_lo + 2u * (uint32_t)ks), desc_hi | (uint64_t)bb, idesc,
+                umma_i8_t<CTA2>(d_tmem, desc_a | (uint64_t)(t_lo + 2u * (uint32_t)ks), desc_hi | (uint64_t)bb, idesc,
                         (uint32_t)((a | ks) != 0));
           }
-          umma_commit(bar_aempty + 8 * ab);
-          umma_commit(bar_tfull + 8 * as);
+          umma_commit_t<CTA2>(bar_aempty + 8 * ab);
+          umma_commit_t<CTA2>(bar_tfull + 8 * as);
           PL_MTRACE(lt, 4);
           if (++ab == halo_bufs) { ab = 0; aph ^= 1; }
           if (++as == p.acc_stages) { as = 0; aphase ^= 1; }
         }
       }
-      for (int tile = blockIdx.x; tile < num_tiles && !p.s2d; tile += gridDim.x, ++lt) {
+      for (int tile = tile0; tile < num_tiles && !p.s2d; tile += tstride, ++lt) {
         PL_MTRACE(lt, 0);
         WAIT(bar_tempty + 8 * as, aphase ^ 1);
         PL_MTRACE(lt, 1);
@@ -753,8 +817,8 @@ igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
             else if (ksteps == 2) issue_taps<3, 3, 2>(d_tmem, da0, db0, idesc, tap_step, row_pitch, b_step, cb == 0);
             else issue_taps<3, 3, 1>(d_tmem, da0, db0, idesc, tap_step, row_pitch, b_step, cb == 0);
             b_lo += 9 * b_step;
-            umma_commit(bar_aempty + 8 * ab);
-            if (cb == cblocks - 1) umma_commit(bar_tfull + 8 * as);
+            umma_commit_t<CTA2>(bar_aempty + 8 * ab);
+            if (cb == cblocks - 1) umma_commit_t<CTA2>(bar_tfull + 8 * as);
           }
           for (int tap = 0; tap < RS && !(hres && RS == 9 && S == 3 && !skip_mma); ++tap) {
             if (!hres) {  // streamed filter: one ring stage per tap
@@ -763,11 +827,11 @@ igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
             }
             const uint64_t da = desc_hi | (uint64_t)t_lo, db = desc_hi | (uint64_t)b_lo;
             if (leader) {
-              if (!skip_mma) issue_kblock_n(ksteps, d_tmem, da, db, idesc, (cb | tap) == 0);
-              if (!hres) umma_commit(empty_b);
+              if (!skip_mma) issue_kblock_n<CTA2>(ksteps, d_tmem, da, db, idesc, (cb | tap) == 0);
+              if (!hres) umma_commit_t<CTA2>(empty_b);
               if (tap == RS - 1) {
-                umma_commit(bar_aempty + 8 * ab);
-                if (cb == cblocks - 1) umma_commit(bar_tfull + 8 * as);
+                umma_commit_t<CTA2>(bar_aempty + 8 * ab);
+                if (cb == cblocks - 1) umma_commit_t<CTA2>(bar_tfull + 8 * as);
               }
             }
             t_lo += tap_step;
@@ -790,7 +854,7 @@ igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
       // fence, a straight run of MMAs, two commits per tile
       constexpr int RPK_ = 8 / (TSW > 0 ? TSW : 8), NKB_ = ((TR > 0 ? TR : 1) + RPK_ - 1) / RPK_;
       constexpr uint32_t kb_step = (uint32_t)(kBM * 32) >> 4;
-      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++lt) {
+      for (int tile = tile0; tile < num_tiles; tile += tstride, ++lt) {
         PL_MTRACE(lt, 0);
         WAIT(bar_tempty + 8 * as, aphase ^ 1);
         PL_MTRACE(lt, 1);
@@ -802,19 +866,19 @@ igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
         if (!skip_mma) {
 #pragma unroll
           for (int kb = 0; kb < NKB_; ++kb)
-            umma_i8(d_tmem, desc_hi | (uint64_t)(a_lo + (uint32_t)kb * kb_step),
+            umma_i8_t<CTA2>(d_tmem, desc_hi | (uint64_t)(a_lo + (uint32_t)kb * kb_step),
                     desc_hi | (uint64_t)(b_lo0 + (uint32_t)kb * b_step), idesc, (uint32_t)(kb > 0));
         }
-        umma_commit(empty_b);
-        umma_commit(bar_tfull + 8 * as);
+        umma_commit_t<CTA2>(empty_b);
+        umma_commit_t<CTA2>(bar_tfull + 8 * as);
         ++stage; full_b += 8; empty_b += 8; a_lo += a_step;
         if (stage == stages) { stage = 0; phase ^= 1; full_b = bar_full; empty_b = bar_empty; a_lo = a_lo0; }
         PL_MTRACE(lt, 4);
         if (++as == p.acc_stages) { as = 0; aphase ^= 1; }
       }
     }
-    for (int tile = blockIdx.x; tile < num_tiles && !(TR == 0 && p.mode == 3) && !(TR > 0 && p.thin_group);
-         tile += gridDim.x, ++lt) {
+    for (int tile = tile0; tile < num_tiles && !(TR == 0 && p.mode == 3) && !(TR > 0 && p.thin_group);
+         tile += tstride, ++lt) {
       PL_MTRACE(lt, 0);
       WAIT(bar_tempty + 8 * as, aphase ^ 1);
       PL_MTRACE(lt, 1);
@@ -838,12 +902,12 @@ igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
           }
           if (leader) {
             if (!skip_mma) {
-              issue_kblock_n(ksteps, d_tmem, da, db, idesc, kb == 0);
+              issue_kblock_n<CTA2>(ksteps, d_tmem, da, db, idesc, kb == 0);
               if (p.mpair)  // second 128-row block of the stage, same B, second accumulator
-                issue_kblock_n(ksteps, d_tmem + (uint32_t)p.BN, da + (uint64_t)((kBM * p.BK) >> 4), db, idesc, kb == 0);
+                issue_kblock_n<CTA2>(ksteps, d_tmem + (uint32_t)p.BN, da + (uint64_t)((kBM * p.BK) >> 4), db, idesc, kb == 0);
             }
-            umma_commit(empty_b);
-            if (kb == num_kb - 1) umma_commit(bar_tfull + 8 * as);
+            umma_commit_t<CTA2>(empty_b);
+            if (kb == num_kb - 1) umma_commit_t<CTA2>(bar_tfull + 8 * as);
           }
         }
         ++stage; full_b += 8; empty_b += 8; a_lo += a_step; b_lo += b_step;
@@ -871,7 +935,7 @@ igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
     pdl_wait();
     uint32_t base_st = 0, base_ph = 0;  // ring stage / phase of this tile's k-block 0
     int glt = 0;
-    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++glt) {
+    for (int tile = tile0; tile < num_tiles; tile += tstride, ++glt) {
       if (g == 0) PL_TRACE(0, glt, 0);
       const int tm = tile / p.n_tiles;
       const uint32_t m = (uint32_t)(tm * kBM + prow);
@@ -966,9 +1030,9 @@ igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
       const int nbufs = kInPlace ? p.res_bufs : p.out_bufs;
       int ob = 0;
       uint32_t ophase = 0;
-      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+      for (int tile = tile0; tile < num_tiles; tile += tstride) {
         int tn_, tm_;
-        tile_mn<GROUPED>(p, tile, tm_, tn_);
+        tile_mn<GROUPED, CTA2>(p, tile, tm_, tn_, cta_rank);
         const int tn = tn_, tm = tm_;
         const int n0 = tn * p.BN;
         const uint32_t out_tile = (kInPlace ? smem_res : smem_out) + (uint32_t)ob * (kInPlace ? tile_bytes : obuf_bytes);
@@ -1044,8 +1108,8 @@ igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
         s_scale[n] = ok ? __ldg(p.epi.scale + n) : 0.f;
         s_bias[n] = (ok && p.epi.bias) ? __ldg(p.epi.bias + n) : 0.f;
       }
-    } else if ((int)blockIdx.x < num_tiles) {
-      stage_scale_bias(blockIdx.x, 0);
+    } else if (tile0 < num_tiles) {
+      stage_scale_bias(tile0, 0);
     }
     pdl_wait();  // the generic path reads the residual / writes y with plain global accesses
     asm volatile("bar.sync 1, %0;" ::"n"(32 * EW) : "memory");
@@ -1068,10 +1132,10 @@ igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
     int as = egroup % p.acc_stages, rb = egroup % res_bufs_, ob = egroup % out_bufs_;
     uint32_t aphase = (uint32_t)(egroup / p.acc_stages) & 1u, rphase = (uint32_t)(egroup / res_bufs_) & 1u,
              ophase = (uint32_t)(egroup / out_bufs_) & 1u;
-    for (int tile = blockIdx.x + egroup * (int)gridDim.x; tile < num_tiles; tile += G * (int)gridDim.x, lt += G) {
+    for (int tile = tile0 + egroup * tstride; tile < num_tiles; tile += G * tstride, lt += G) {
       PL_ETRACE(0);
       int tn_, tm_;
-      tile_mn<GROUPED>(p, tile, tm_, tn_);
+      tile_mn<GROUPED, CTA2>(p, tile, tm_, tn_, cta_rank);
       const int tn = tn_, tm = tm_;
       long long row = (long long)(kPair ? 2 * tm : tm) * kBM + arow;  // output pixel index (generic epilogue)
       int himg = 0, hp0 = 0;
@@ -1173,7 +1237,8 @@ igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
       if (kFast && !(PL_DBG_FLAGS_V & 64)) fence_proxy_async();  // this thread's st.shared -> visible to the TMA engine
       __syncwarp();
       if (lane == 0) {
-        mbar_arrive(bar_tempty + 8 * as);
+        if (CTA2) mbar_arrive_cluster(bar_tempty + 8 * as + lead_delta);  // the leader's MMA thread waits for both CTAs
+        else mbar_arrive(bar_tempty + 8 * as);
         if (EPI == EPI_I8_RELU_RES) mbar_arrive(bar_staged + 8 * rb);
         else if (kFast) mbar_arrive(bar_staged + 8 * ob);
       }
@@ -1191,7 +1256,7 @@ igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
         // very wide outputs: next tile's scale / bias into the other buffer, published by a
         // barrier of the epilogue warps (this mode keeps the warps in step)
         sbuf ^= 1;
-        if (tile + (int)gridDim.x < num_tiles) stage_scale_bias(tile + gridDim.x, sbuf);
+        if (tile + tstride < num_tiles) stage_scale_bias(tile + tstride, sbuf);
         asm volatile("bar.sync 2, %0;" ::"n"(32 * EW) : "memory");
       }
       PL_ETRACE(6);
@@ -1210,10 +1275,12 @@ igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
   }
 
   tc_fence_before();
-  __syncthreads();
+  if (CTA2) cluster_sync_all();  // neither CTA's smem / TMEM / barriers go away while the other still uses them
+  else __syncthreads();
   if (warp == 1) {
     tc_fence_after();
-    tmem_dealloc(tmem_base, p.tmem_cols);
+    if (CTA2) tmem_dealloc_2sm(tmem_base, p.tmem_cols);
+    else tmem_dealloc(tmem_base, p.tmem_cols);
   }
 }
 
@@ -1423,10 +1490,13 @@ uint32_t pow2_cols(int n) {
 }
 
 int env_int(const char* name, int dflt);
+static inline bool trace_enabled() { return env_int("PL_DBG_TRACE_ON", 0) != 0; }
 
 int pick_bn(int Nout, int m_tiles, int sms) {
   // widest tile that does not over-cover Nout, narrowed until the grid fills the SMs
   const int n16 = (Nout + 15) / 16 * 16;
+  const int forced = env_int("PL_FORCE_BN", 0);  // tests: wide tiles on problems small enough for the oracle
+  if (forced >= 16 && forced <= 256 && (forced & (forced - 1)) == 0) return forced;
   int cap = 256;
   while (cap > 16 && cap / 2 >= n16) cap >>= 1;
   int bn = cap;
@@ -1443,7 +1513,7 @@ int pick_bn(int Nout, int m_tiles, int sms) {
   return bn;
 }
 
-template <int EPI, int TR = 0, int TSW = 0, bool GROUPED = false>
+template <int EPI, int TR = 0, int TSW = 0, bool GROUPED = false, bool CTA2 = false>
 int launch_one(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& ty, const CUtensorMap& tr,
                const IgemmParams& p, int grid, size_t smem, pl_stream_t stream) {
   // cudaFuncSetAttribute is per DEVICE: one flag per device ordinal (a process may drive several GPUs)
@@ -1453,12 +1523,19 @@ int launch_one(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& 
   bool& configured = configured_dev[dev_ & 63];
   if (!configured) {
     // 227 KB is the per-CTA limit for static + dynamic shared memory together
-    PL_CUDA_OK(cudaFuncSetAttribute(igemm_i8_kernel<EPI, TR, TSW, GROUPED>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                    (int)(221 * 1024)));
+    PL_CUDA_OK(cudaFuncSetAttribute(igemm_i8_kernel<EPI, TR, TSW, GROUPED, CTA2>,
+                                    cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(221 * 1024)));
     configured = true;
   }
+  if (CTA2) {
+    if (trace_enabled()) return PL_ERR_UNSUPPORTED;
+    launch_pdl_cluster(igemm_i8_kernel<EPI, TR, TSW, GROUPED, CTA2>, dim3(grid), dim3(kThreads), smem,
+                       (cudaStream_t)stream, 2, ta, tb, ty, tr, p);
+    ++g_launches;
+    return launch_status();
+  }
   const int threads = TR > 0 ? kThinThreads : kThreads;
-  const char* trace_path = env_int("PL_DBG_TRACE_ON", 0) ? getenv("PL_DBG_TRACE") : nullptr;
+  const char* trace_path = trace_enabled() ? getenv("PL_DBG_TRACE") : nullptr;
   if (trace_path && *trace_path) {
     // debugging aid: synchronous launch, CTA 0's timeline written as text (role tile e0..e7)
     static long long* dbuf = nullptr;
@@ -1523,9 +1600,68 @@ int env_int(const char* name, int dflt) {
 }
 bool tma_epilogue_enabled() { return env_int("PL_IGEMM_NO_TMA_EPI", 0) != 1; }
 
-int launch_igemm(const CUtensorMap& ta, const CUtensorMap& tb, IgemmParams& p, pl_stream_t stream) {
+// the B operand as the caller encoded it (K-major [rows, cols] bytes, pitch ld): pair launches re-encode its
+// tensor map with a box of BN / 2 rows
+struct BSpec {
+  const void* base;
+  uint64_t cols, rows, ld;
+};
+
+// clusters of two CTAs that can be resident at once (normally SMs / 2), per device
+int max_pair_clusters();
+
+extern thread_local int g_last_plan[10];
+
+// CTA pairs pay where the operand stream from L2 bounds the launch: long reductions
+// whose filter slice cannot stay resident in one CTA's shared memory.  Measured on B200 (tools/gpu_cta2_ab.sh):
+// +4..10 % on the ResNet-50 layers with K_red >= 1024 (14x14 / 7x7 and the stride-2 3x3s), 57 -> 64 %, 63 -> 70 %
+// and 60 -> 71 % of the tensor peak on 4096^3, 8192^3 and 8192 x 4096 x 8192; launches that keep their filter
+// resident lose 20-50 % when they give that up, K_red = 512 is a wash.
+bool want_cta_pairs(const IgemmParams& p) {
+  const int knob = env_int("PL_CTA2", 1);  // 0 never, 1 auto, 2 whenever the launch qualifies
+  const bool legal = knob > 0 && (p.mode == 0 || p.mode == 1 || (p.mode == 3 && !p.s2d)) && p.BN >= 64 &&
+                     (p.BN % 32) == 0 && p.m_tiles >= 2 && !trace_enabled() && max_pair_clusters() > 0;
+  if (!legal) return false;
+  if (knob >= 2) return true;
+  const long long kred = (long long)p.num_kb * p.BK;
+  if (kred < env_int("PL_CTA2_MIN_K", 1024) || p.BN < env_int("PL_CTA2_MIN_BN", 128)) return false;
+  // would the single-CTA launch keep its filter resident?  (same tests as below, on the single-CTA geometry)
+  const long long fbytes = (long long)p.num_kb * p.b_stage_bytes;
+  const int sms = driver().sm_count;
+  const int tiles = p.m_tiles * p.n_tiles;
+  const int n_cover = p.n_tiles * p.BN;
+  const long long budget = 219 * 1024 - ((n_cover <= 2048 ? n_cover : 512) * 8 + 1023) / 1024 * 1024;
+  const long long staging = (long long)kBM * p.BN * (p.epi.residual ? 2 : 1);
+  if (p.mode == 3 && p.n_tiles == 1 && 2ll * p.a_halo_bytes + fbytes + staging <= budget) return false;
+  if (p.mode != 3 && !p.mpair && tiles >= 2 * sms && p.n_tiles <= 16 && fbytes <= 64 * 1024 &&
+      p.epi.out_dtype == PL_OUT_INT8)
+    return false;
+  return true;
+}
+
+int launch_igemm(const CUtensorMap& ta, const CUtensorMap& tb_in, IgemmParams& p, pl_stream_t stream,
+                 const BSpec* bs = nullptr) {
+  CUtensorMap tb = tb_in;
+  p.cta2 = 0;
+  {
+    if (bs && want_cta_pairs(p)) {
+      const uint32_t half = (uint32_t)((p.BN / 2) * p.BK);
+      if (encode_2d(&tb, bs->base, bs->cols, bs->rows, bs->ld, p.BK, p.BN / 2) == PL_OK) {
+        p.cta2 = 1;
+        p.m_tiles = (p.m_tiles + 1) / 2;
+        p.b_stage_bytes = (half + 1023u) / 1024u * 1024u;
+        p.tx_bytes = p.mode == 3 ? half : p.a_stage_bytes + half;  // per CTA; the leader's barrier expects both
+      } else {
+        tb = tb_in;
+      }
+    }
+  }
   const int tiles = p.m_tiles * p.n_tiles;
   int grid = tiles < driver().sm_count ? tiles : driver().sm_count;
+  if (p.cta2) {
+    const int clusters = tiles < max_pair_clusters() ? tiles : max_pair_clusters();
+    grid = 2 * clusters;
+  }
   // epilogue specialisation (ragged edges inside a fast-path launch use the generic code)
   const EpiParams& e = p.epi;
   int epi = EPI_GENERIC;
@@ -1572,13 +1708,13 @@ int launch_igemm(const CUtensorMap& ta, const CUtensorMap& tb, IgemmParams& p, p
   p.res_bufs = 2;
   int extra = 0;
   // halo mode with a single N tile keeps the whole packed filter in smem when it fits
-  bool hres = p.mode == 3 && p.n_tiles == 1 && env_int("PL_IGEMM_NO_HRES", 0) == 0 &&
+  bool hres = p.mode == 3 && p.n_tiles == 1 && !p.cta2 && env_int("PL_IGEMM_NO_HRES", 0) == 0 &&
               2 * (int)p.a_halo_bytes + p.num_kb * (int)p.b_stage_bytes <= budget;
   // TMA-fed GEMM / im2col modes: when the grid is a multiple of n_tiles every CTA keeps seeing the
   // same N tile, so that filter slice can stay in smem for the kernel's lifetime (the per-tile
   // re-read of B from L2 is what bounds the short-K layers: B is 2x the A bytes at BN = 256)
   bool bres01 = (p.mode == 0 || p.mode == 1) && epi != EPI_GENERIC && env_int("PL_IGEMM_NO_BRES01", 0) == 0 &&
-                tiles >= 2 * grid && p.n_tiles <= 16 && !p.mpair;
+                tiles >= 2 * grid && p.n_tiles <= 16 && !p.mpair && !p.cta2;
   if (bres01) {
     const int g = grid - grid % p.n_tiles;
     const int bbytes = p.num_kb * (int)p.b_stage_bytes;
@@ -1617,7 +1753,7 @@ int launch_igemm(const CUtensorMap& ta, const CUtensorMap& tb, IgemmParams& p, p
     }
     if (bres01 && left < 0) {
       bres01 = false;
-      grid = tiles < driver().sm_count ? tiles : driver().sm_count;
+      grid = tiles < driver().sm_count ? tiles : driver().sm_count;  // (never a pair launch: bres01 excludes them)
       main_min = min_stages * stage_bytes;
       left = budget - main_min - fixed;
     }
@@ -1734,6 +1870,26 @@ int launch_igemm(const CUtensorMap& ta, const CUtensorMap& tb, IgemmParams& p, p
     }
 #undef PL_THIN_CASE
   }
+  {
+    const int plan[10] = {p.mode, p.BN, p.BK, p.stages, p.cta2, p.mpair, p.group_m, grid, p.b_resident, epi};
+    for (int i = 0; i < 10; ++i) g_last_plan[i] = plan[i];
+  }
+  if (p.cta2) {
+    if (p.group_m > 1) {
+      switch (epi) {
+        case EPI_I8_RELU: return launch_one<EPI_I8_RELU, 0, 0, true, true>(ta, tb, ty, tr, p, grid, smem, stream);
+        case EPI_I8_SIGNED: return launch_one<EPI_I8_SIGNED, 0, 0, true, true>(ta, tb, ty, tr, p, grid, smem, stream);
+        case EPI_GENERIC: return launch_one<EPI_GENERIC, 0, 0, true, true>(ta, tb, ty, tr, p, grid, smem, stream);
+        default: p.group_m = 1; break;
+      }
+    }
+    switch (epi) {
+      case EPI_I8_RELU: return launch_one<EPI_I8_RELU, 0, 0, false, true>(ta, tb, ty, tr, p, grid, smem, stream);
+      case EPI_I8_RELU_RES: return launch_one<EPI_I8_RELU_RES, 0, 0, false, true>(ta, tb, ty, tr, p, grid, smem, stream);
+      case EPI_I8_SIGNED: return launch_one<EPI_I8_SIGNED, 0, 0, false, true>(ta, tb, ty, tr, p, grid, smem, stream);
+      default: return launch_one<EPI_GENERIC, 0, 0, false, true>(ta, tb, ty, tr, p, grid, smem, stream);
+    }
+  }
   if (p.group_m > 1) {  // large GEMMs only (mode 0, streamed B): their own instantiations
     switch (epi) {
       case EPI_I8_RELU: return launch_one<EPI_I8_RELU, 0, 0, true>(ta, tb, ty, tr, p, grid, smem, stream);
@@ -1748,6 +1904,36 @@ int launch_igemm(const CUtensorMap& ta, const CUtensorMap& tb, IgemmParams& p, p
     case EPI_I8_SIGNED: return launch_one<EPI_I8_SIGNED>(ta, tb, ty, tr, p, grid, smem, stream);
     default: return launch_one<EPI_GENERIC>(ta, tb, ty, tr, p, grid, smem, stream);
   }
+}
+
+thread_local int g_last_plan[10] = {};
+
+int max_pair_clusters() {
+  static int cached[64] = {};
+  int dev = 0;
+  cudaGetDevice(&dev);
+  int& c = cached[dev & 63];
+  if (c == 0) {
+    auto kern = igemm_i8_kernel<EPI_I8_RELU, 0, 0, false, true>;
+    c = -1;
+    if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(221 * 1024)) == cudaSuccess) {
+      cudaLaunchConfig_t cfg{};
+      cfg.gridDim = dim3(2 * driver().sm_count);
+      cfg.blockDim = dim3(kThreads);
+      cfg.dynamicSmemBytes = 221 * 1024;
+      cudaLaunchAttribute at[1];
+      at[0].id = cudaLaunchAttributeClusterDimension;
+      at[0].val.clusterDim.x = 2;
+      at[0].val.clusterDim.y = 1;
+      at[0].val.clusterDim.z = 1;
+      cfg.attrs = at;
+      cfg.numAttrs = 1;
+      int n = 0;
+      if (cudaOccupancyMaxActiveClusters(&n, kern, &cfg) == cudaSuccess && n > 0) c = n;
+    }
+    cudaGetLastError();
+  }
+  return c > 0 ? c : 0;
 }
 
 int check_epi(const pl_epilogue* e) {
@@ -1916,7 +2102,8 @@ static int conv2d_dense(const int8_t* x, const int8_t* w_packed, void* y, const 
   const uint64_t wrow = (uint64_t)d->R * d->S * cpad;
   rc = encode_2d(&tb, w_packed, wrow, (uint64_t)d->K, wrow, p.BK, p.BN);
   if (rc) return rc;
-  return launch_igemm(ta, tb, p, stream);
+  const BSpec bs{w_packed, wrow, (uint64_t)d->K, wrow};
+  return launch_igemm(ta, tb, p, stream, &bs);
 }
 
 extern "C" int pl_conv2d_i8_nhwc(const int8_t* x, const int8_t* w_packed, void* y,
@@ -2139,6 +2326,11 @@ static void maybe_enable_mpair(IgemmParams& p, const pl_epilogue* e, int K, bool
                    !e->residual && (e->act == PL_ACT_NONE || e->act == PL_ACT_RELU) && env_int("PL_NO_F32_FAST", 0) == 0 &&
                    env_int("PL_MPAIR_F32", 1) != 0;
   if ((!fast && !f32) || p.mode != 0 || p.BN != 256 || p.m_tiles < 2 || env_int("PL_NO_MPAIR", 0)) return;
+  // CTA pairs move the same bytes per MAC as a tile pair and keep two accumulator stages (the epilogue stays
+  // hidden): 8192^3 62.7 -> 70.3 % of the tensor peak, both together 57 % (BK = 64 rows halve the TMA rate)
+  // (from K = 16384 the exposed epilogue of a 512 x 256 cluster tile is small enough: 16384^3 65.8 -> 70.0 %)
+  const bool with_pairs = want_cta_pairs(p);
+  if (with_pairs && K < env_int("PL_CTA2_MPAIR_MIN_K", 16384)) return;
   if (!env_int("PL_MPAIR_FORCE", 0)) {
     // the pair has a single accumulator stage (its epilogue is exposed), so K must be long enough
     // to hide it, and the coarser work unit must not cost a wave
@@ -2150,7 +2342,7 @@ static void maybe_enable_mpair(IgemmParams& p, const pl_epilogue* e, int K, bool
     if (K < min_k || tiles < 2 * sms || w2 > w1) return;
   }
   p.mpair = 1;
-  p.BK = 64;  // 32 KB stages: four of them beside the 64 KB staging buffer
+  p.BK = with_pairs ? 128 : 64;  // 32 KB stages: four of them beside the 64 KB staging buffer (pairs: 48 KB stages)
   p.cblocks = (K + p.BK - 1) / p.BK;  // the K tail is zero-filled by TMA
   p.num_kb = p.cblocks;
   p.m_tiles = (p.m_tiles + 1) / 2;
@@ -2205,7 +2397,8 @@ extern "C" int pl_gemm_i8_peers(const int8_t* A, int lda, const int8_t* Bt, int 
     p.peer_maps = reinterpret_cast<const CUtensorMap*>(maps_dev);
     p.n_peers = n_peers;
   }
-  return launch_igemm(ta, tb, p, stream);
+  const BSpec bs{Bt, (uint64_t)K, (uint64_t)N, (uint64_t)ldb};
+  return launch_igemm(ta, tb, p, stream, &bs);
 }
 
 // One-off set-up of the peer tensor maps for launches with C_peers == NULL: same tile geometry as the launch
@@ -2280,6 +2473,13 @@ extern "C" int pl_gemm_i8_peers_static(const int8_t* A, int lda, const int8_t* B
   return pl_gemm_i8_peers(A, lda, Bt, ldb, C, C_peers, n_peers, maps, ldc, M, N, K, e, stream);
 }
 
+extern "C" int pl_last_igemm_plan(int* plan, int n) {
+  if (!plan || n <= 0) return 0;
+  const int m = n < 10 ? n : 10;
+  for (int i = 0; i < m; ++i) plan[i] = g_last_plan[i];
+  return m;
+}
+
 extern "C" void pl_refresh_knobs(void) {
   KnobCache& k = knobs();
   std::lock_guard<std::mutex> lock(k.mu);
@@ -2313,7 +2513,8 @@ extern "C" int pl_gemm_i8(const int8_t* A, int lda, const int8_t* Bt, int ldb, v
   if (rc) return rc;
   rc = encode_2d(&tb, Bt, (uint64_t)K, (uint64_t)N, (uint64_t)ldb, p.BK, p.BN);
   if (rc) return rc;
-  return launch_igemm(ta, tb, p, stream);
+  const BSpec bs{Bt, (uint64_t)K, (uint64_t)N, (uint64_t)ldb};
+  return launch_igemm(ta, tb, p, stream, &bs);
 }
 
 // same probe with the operand layout of a 32 / 64 / 128-byte K-block (SWIZZLE_32B / 64B / 128B

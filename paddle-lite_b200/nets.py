@@ -439,44 +439,66 @@ class DeviceNet:
                          op.in_scale / op.out_scale, pl.OUT_INT8, Cc=C, y=y)
 
     # -- bind + run ---------------------------------------------------------------
-    def bind(self):
-        """Pre-computes folded scales and output buffers; builds the launch list."""
+    def bind(self, schedule=None):
+        """Pre-computes folded scales and output buffers; builds the launch list.  Every entry runs its op on
+        the images [i0, i1) of the batch (images are independent units on this path).
+
+        schedule: [(first_op, last_op, chunks), ...] -- the ops of a segment run chunk by chunk (all ops on
+        images [0, B/chunks), then on the next slice, ...) so that the activations between them stay in the
+        126 MB L2 instead of making a round trip through HBM at full batch.  Default: PL_SUBBATCH
+        ("first-last:chunks,..."), else every op once on the whole batch."""
         assert self.calibrated, "calibrate() or load scales first"
         self.layers = []
         self.s2d_bufs = {}
+        self.schedule = self._parse_schedule(schedule)
+        B = self.batch
         for op in self.prog.ops:
             if op.kind == "quant_in" and op.dst in self.s2d_src:
                 g = self._s2d_geometry(self.s2d_src[op.dst], self.batch)
                 y = pl.s2d_input_buffer(g, self.dev)  # zero borders, written once here
                 y._pl_n = self.batch
                 self.s2d_bufs[op.dst] = (y, g)
-                self.layers.append((op, lambda op=op, y=y, g=g: pl.quantize_nchw_to_s2d(
-                    self.input, op.out_scale, g, y=y, mean=self.mean, norm=self.norm)))
+                img = g.HP * g.WS * 16
+                self.layers.append((op, lambda i0=0, i1=B, op=op, y=y, g=g, img=img: pl.quantize_nchw_to_s2d(
+                    self.input[i0:i1], op.out_scale, g, y=y[i0 * img:], mean=self.mean, norm=self.norm)))
             elif op.kind == "quant_in":
                 assert self.feed == "f32", "narrow feeds exist for the space-to-depth stems only"
                 y = self._buf(op.dst)
-                self.layers.append((op, lambda op=op, y=y: pl.quantize_nchw_to_nhwc(
-                    self.input, op.out_scale, y.shape[-1], y=y)))
+                self.layers.append((op, lambda i0=0, i1=B, op=op, y=y: pl.quantize_nchw_to_nhwc(
+                    self.input[i0:i1], op.out_scale, y.shape[-1], y=y[i0:i1])))
             elif op.kind in ("conv", "dwconv"):
                 sf, bf, argf = self._fold(op, op.K, op.out_fp32)
-                x = self.s2d_bufs[op.src][0] if op.src in self.s2d_bufs else self._buf(op.src)
                 y = self._buf(op.dst, torch.float32 if op.out_fp32 else torch.int8)
                 out = pl.OUT_FP32 if op.out_fp32 else pl.OUT_INT8
                 res = self._buf(op.res) if op.get("res") else None
                 rs = self._res_scale(op)
-                self.layers.append((op, lambda op=op, x=x, y=y, sf=sf, bf=bf, argf=argf, out=out, res=res, rs=rs:
-                                    self._exec_conv(op, x, sf, bf, argf, out, y, res, rs)))
+                if op.src in self.s2d_bufs:
+                    xs, g = self.s2d_bufs[op.src]
+                    img = g.HP * g.WS * 16
+
+                    def fn(i0=0, i1=B, op=op, xs=xs, img=img, y=y, sf=sf, bf=bf, argf=argf, out=out):
+                        x = xs[i0 * img:]
+                        x._pl_n = i1 - i0
+                        return self._exec_conv(op, x, sf, bf, argf, out, y[i0:i1], None, 0.0)
+                    self.layers.append((op, fn))
+                else:
+                    x = self._buf(op.src)
+                    self.layers.append((op, lambda i0=0, i1=B, op=op, x=x, y=y, sf=sf, bf=bf, argf=argf, out=out,
+                                        res=res, rs=rs:
+                                        self._exec_conv(op, x[i0:i1], sf, bf, argf, out, y[i0:i1],
+                                                        None if res is None else res[i0:i1], rs)))
             elif op.kind == "pool":
                 x, y = self._buf(op.src), self._buf(op.dst)
-                self.layers.append((op, lambda op=op, x=x, y=y: self._exec_pool(op, x, y)))
+                self.layers.append((op, lambda i0=0, i1=B, op=op, x=x, y=y: self._exec_pool(op, x[i0:i1], y[i0:i1])))
             elif op.kind == "add":
                 a, b2, y = self._buf(op.src), self._buf(op.src2), self._buf(op.dst)
                 sa, sb = op.a_scale / op.out_scale, op.b_scale / op.out_scale
-                self.layers.append((op, lambda op=op, a=a, b2=b2, y=y, sa=sa, sb=sb:
-                                    pl.add(a, b2, sa, sb, _ACT[op.act], y=y)))
+                self.layers.append((op, lambda i0=0, i1=B, op=op, a=a, b2=b2, y=y, sa=sa, sb=sb:
+                                    pl.add(a[i0:i1], b2[i0:i1], sa, sb, _ACT[op.act], y=y[i0:i1])))
             elif op.kind == "cat_shuffle":
                 a, b2, y = self._buf(op.src), self._buf(op.src2), self._buf(op.dst)
-                self.layers.append((op, lambda a=a, b2=b2, y=y: pl.concat_shuffle2(a, b2, y=y)))
+                self.layers.append((op, lambda i0=0, i1=B, a=a, b2=b2, y=y:
+                                    pl.concat_shuffle2(a[i0:i1], b2[i0:i1], y=y[i0:i1])))
             elif op.kind == "fc":
                 sf, bf, _ = pl.fold_scales(op.w_scale, op.N, op.in_scale, 1.0, pl.OUT_FP32, op.bias)
                 sf, bf = torch.from_numpy(sf).to(self.dev), torch.from_numpy(bf).to(self.dev)
@@ -484,9 +506,32 @@ class DeviceNet:
                 A = x.view(self.batch, -1)
                 y = self._buf(op.dst, torch.float32).view(self.batch, op.N)
                 self.output = y
-                self.layers.append((op, lambda op=op, A=A, y=y, sf=sf, bf=bf:
-                                    pl.gemm(A, op._wp, sf, bf, out=pl.OUT_FP32, y=y, K=op.K)))
+                self.layers.append((op, lambda i0=0, i1=B, op=op, A=A, y=y, sf=sf, bf=bf:
+                                    pl.gemm(A[i0:i1], op._wp, sf, bf, out=pl.OUT_FP32, y=y[i0:i1], K=op.K)))
         return self
+
+    def _parse_schedule(self, schedule):
+        n = len(self.prog.ops)
+        if schedule is None:
+            env = os.environ.get("PL_SUBBATCH", "")
+            schedule = []
+            for part in filter(None, env.split(",")):
+                rng, chunks = part.split(":")
+                lo, hi = rng.split("-")
+                schedule.append((int(lo), int(hi), int(chunks)))
+        segs, at = [], 0
+        for lo, hi, chunks in sorted(schedule):
+            hi = min(hi, n - 1)
+            chunks = max(1, min(int(chunks), self.batch))
+            if lo < at or lo > hi:
+                continue
+            if lo > at:
+                segs.append((at, lo - 1, 1))
+            segs.append((lo, hi, chunks))
+            at = hi + 1
+        if at < n:
+            segs.append((at, n - 1, 1))
+        return segs
 
     def s2d_as_nhwc(self, name):
         """Host copy of a space-to-depth input buffer, unfolded to int8 NHWC [N,H,W,4] (for checks)."""
@@ -496,9 +541,21 @@ class DeviceNet:
         img = img[:, g.pad_s:g.pad_s + H // 2, g.pad_s:g.pad_s + W // 2]
         return img.transpose(0, 1, 3, 2, 4, 5).reshape(self.batch, H, W, 4)
 
+    def launch_order(self):
+        """Layer index of every launch of one step, in execution order (chunked segments repeat their ops)."""
+        order = []
+        for lo, hi, chunks in self.schedule:
+            for _ in range(chunks):
+                order.extend(range(lo, hi + 1))
+        return order
+
     def run(self):
-        for _, fn in self.layers:
-            fn()
+        B = self.batch
+        for lo, hi, chunks in self.schedule:
+            for c in range(chunks):
+                i0, i1 = c * B // chunks, (c + 1) * B // chunks
+                for _, fn in self.layers[lo:hi + 1]:
+                    fn(i0, i1)
         return self.output
 
     def capture(self):

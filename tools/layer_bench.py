@@ -98,8 +98,13 @@ def bench(name, batch, iters, nsets):
     cg = 1 if dw else C
     ops = 2.0 * batch * P * P * K * k * k * cg
     byts = batch * (H * W * C + P * P * K * (2 if res is True else 1)) + K * k * k * cg
+    plan = ""
+    if not dw:
+        q = pl.last_igemm_plan()
+        plan = (f" plan: mode {q['mode']} BN {q['BN']} BK {q['BK']} stages {q['stages']} pairs {q['cta_pairs']}"
+                f" resident {q['filter_resident']} grid {q['grid']}")
     print(f"{name:24s} b{batch} ms={ms:.4f} TOPS={ops / ms / 1e9:8.1f} GB/s={byts / ms / 1e6:8.1f} "
-          f"(bytes {byts / 1e6:.1f} MB)", flush=True)
+          f"(bytes {byts / 1e6:.1f} MB){plan}", flush=True)
 
 
 if __name__ == "__main__":
