@@ -139,6 +139,25 @@ int plk_pick(const char* op, int enable_int8, int n_cons, const int* cons_int8, 
   PLK_CATCH
 }
 
+// KernelGrade of every candidate of `op` on the given valid places (triples target, precision, layout), best first:
+// newline separated "score op/alias/target/precision/layout" (static_kernel_pick_pass.h:53-215, cc:66-84)
+int plk_score_kernels(const char* op, int n_places, const int* places3, int enable_int8, int n_in, const char* const* in_args,
+                      const int* in_prec, char* buf, int cap) {
+  PLK_TRY
+  std::vector<Place> places;
+  for (int i = 0; i < n_places; ++i)
+    places.emplace_back(static_cast<TargetType>(places3[3 * i]), static_cast<PrecisionType>(places3[3 * i + 1]),
+                        static_cast<DataLayoutType>(places3[3 * i + 2]));
+  std::map<std::string, PrecisionType> in_types;
+  for (int i = 0; i < n_in; ++i) in_types[in_args[i]] = static_cast<PrecisionType>(in_prec[i]);
+  std::string s;
+  for (auto& c : mir::ScoreKernels(op, places, enable_int8 != 0, in_types))
+    s += std::to_string(static_cast<long long>(c.score)) + " " + c.kernel->SerializedKernelType() + "\n";
+  CHECK_LT(static_cast<int>(s.size()), cap);
+  std::memcpy(buf, s.c_str(), s.size() + 1);
+  PLK_CATCH
+}
+
 int plk_run_conv(const char* op, void* x, void* filter, void* bias, void* residual, void* out, const int* strides,
                  const int* pads, const int* dil, int groups, int act_type, float act_coef, float input_scale,
                  const float* wscale, int n_ws, float output_scale, float residual_scale, int out_int8, int launches) {

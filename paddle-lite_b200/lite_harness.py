@@ -114,6 +114,22 @@ def pick(op, enable_int8, consumers_int8, consumer_scales=None):
     return buf.value.decode(), os_.value
 
 
+def score_kernels(op, places, enable_int8, in_types=None):
+    """KernelGrade of every candidate of `op`, best first: [(score, 'op/alias/target/precision/layout')].
+    places: [(target, precision, layout)] ints of lite/api/paddle_place.h; in_types: {argument: precision}."""
+    flat = _ia([v for p in places for v in p])
+    in_types = in_types or {}
+    names = (C.c_char_p * max(len(in_types), 1))(*[k.encode() for k in in_types])
+    precs = _ia(list(in_types.values())) if in_types else None
+    buf = C.create_string_buffer(1 << 14)
+    _ck(lib().plk_score_kernels(op.encode(), len(places), flat, int(enable_int8), len(in_types), names, precs, buf, len(buf)))
+    out = []
+    for line in buf.value.decode().splitlines():
+        sc, key = line.split(" ", 1)
+        out.append((int(sc), key))
+    return out
+
+
 def run_conv(op, x, w, bias, input_scale, weight_scale, output_scale, strides=(1, 1), pads=(0, 0, 0, 0),
              dil=(1, 1), groups=1, act=0, act_coef=0.0, out_int8=True, residual=None, residual_scale=1.0,
              launches=1):

@@ -1,6 +1,7 @@
 """CPU-side checks of the plugin boundary (no GPU): the kernels the north_star names
 are registered under the reference's keys, and the miniature static_kernel_pick obeys
 the reference's int8_out / fp32_out rule (lite/core/mir/static_kernel_pick_pass.cc:93-166)."""
+import numpy as np
 import pytest
 
 
@@ -135,3 +136,65 @@ def test_kernel_sources_compile_against_reference_headers():
                          capture_output=True, text=True)
     assert out.returncode == 0, out.stdout + out.stderr
     assert out.stdout.count("ok  ") == 3
+
+
+# ---- KernelGrade (lite/core/mir/static_kernel_pick_pass.h:53-215) ------------------------------------------
+# enum values of lite/api/paddle_place.h
+T_X86, T_CUDA, T_ARM = 2, 3, 4
+P_FLOAT, P_INT8, P_ANY = 1, 2, 4
+L_NCHW, L_ANY, L_NHWC = 1, 2, 3
+
+
+def _grade(places, kplace, enable_int8, type_match=True):
+    """the reference's arithmetic, by hand: kMax = 255, integer division per factor, best weighted place"""
+    best = -1.0
+    n = len(places)
+    for i, (t, p, l) in enumerate(places):
+        w = (n - i) / n
+        s = 0
+        if t == kplace[0]:
+            s += 255 // 1
+        if (p == kplace[1] or kplace[1] == P_ANY or p == P_ANY) and not (kplace[1] == P_INT8 and not enable_int8):
+            s += 255 // 2
+        if l == kplace[2] or kplace[2] == L_ANY or l == L_ANY:
+            s += 255 // 4
+        if not enable_int8 and type_match:
+            s *= 2
+        best = max(best, np.float32(w) * np.float32(s))
+    return int(best)
+
+
+def test_kernel_grade_scores(lh):
+    import numpy as np  # noqa: F401
+    cuda_i8 = (T_CUDA, P_INT8, L_NHWC)
+    # one place: target + precision + layout = 255 + 127 + 63
+    sc = lh.score_kernels("conv2d", [cuda_i8], True)
+    assert sc and all(s == 445 for s, _ in sc)
+    assert {k.split("/")[1] for _, k in sc} == {"int8_out", "fp32_out"}
+    # place order is preference: the same kernels behind an x86 place score half
+    sc2 = lh.score_kernels("conv2d", [(T_X86, P_FLOAT, L_NCHW), cuda_i8], True)
+    assert all(s == _grade([(T_X86, P_FLOAT, L_NCHW), cuda_i8], cuda_i8, True) == 222 for s, _ in sc2)
+    # three places, the kernel's own place last: weight 1/3 there, but target-only matches earlier score more
+    pl3 = [(T_CUDA, P_FLOAT, L_NCHW), (T_ARM, P_FLOAT, L_NCHW), cuda_i8]
+    want = _grade(pl3, cuda_i8, True)
+    assert want == 255 and all(s == want for s, _ in lh.score_kernels("conv2d", pl3, True))
+    # an op without enable_int8: int8 kernels get no precision score, and the sum doubles on a type match
+    sc3 = lh.score_kernels("conv2d", [cuda_i8], False)
+    assert all(s == (255 + 63) * 2 for s, _ in sc3)
+    sc4 = lh.score_kernels("conv2d", [cuda_i8], False, {"Input": P_FLOAT})  # declared int8 input, fp32 variable
+    assert all(s == 255 + 63 for s, _ in sc4)
+    # kAny / kAny kernels (io_copy) are reached through the expanded places and match every place
+    sc5 = lh.score_kernels("io_copy", [cuda_i8, (T_CUDA, P_FLOAT, L_NCHW)], False)
+    assert sc5 and all(s == 445 * 2 for s, _ in sc5)
+
+
+def test_kernel_grade_tie_order_and_pick(lh):
+    """equal scores keep the candidate order of the expanded std::set<Place> (stable sort), and the int8 rule then
+    takes the first candidate whose declared outputs have the wanted precision"""
+    places = [(T_CUDA, P_INT8, L_NHWC), (T_CUDA, P_FLOAT, L_NCHW)]
+    sc = lh.score_kernels("conv2d", places, True)
+    assert [s for s, _ in sc] == sorted([s for s, _ in sc], reverse=True)
+    key, scale = lh.pick("conv2d", True, [True], [0.5])
+    assert key == "conv2d/int8_out/cuda/int8_t/NHWC" and scale == 0.5
+    key, _ = lh.pick("conv2d", True, [False])
+    assert key == "conv2d/fp32_out/cuda/int8_t/NHWC"
