@@ -672,6 +672,34 @@ def bench_sustained(ctx, net, batch, seconds, ms_per_step):
             "img_s": ctx.world * batch * steps / (ms * 1e-3), "clocks": ck}
 
 
+def bench_plugin(ctx, prog, net, batch, x_host, steps, warmup):
+    """The same program, the same end-to-end loop, but through the reference-facing plugin surface: every op is a
+    KernelLite instance from KernelRegistry run by Launch() (libpl_lite_kernels.so; lite_net.PluginNet), with the
+    reference's op chain calib -> layout -> conv in front instead of the fused entry kernel."""
+    import importlib
+    torch = ctx.torch
+    lite_net = importlib.import_module("paddle_lite_b200.lite_net")
+    pnet = lite_net.PluginNet(prog, batch)
+    x_dev = x_host.cuda()
+    pnet.inputs[0].copy_(x_dev)
+    net.input.copy_(x_dev)
+    same = bool(torch.equal(pnet.run(0), net.replay()))  # logits of both paths, bit for bit
+    pnet.capture()
+    for _ in range(3):
+        pnet.replay(0)
+    ctx.barrier()
+    ms = ctx.timed(lambda: pnet.replay(0), steps)
+    rec = e2e_loop(ctx, pnet, x_host, steps, warmup)
+    rec["input"] = rec["input"].replace("the network's", "the plugin program's")
+    rec.update({"path": "KernelRegistry -> KernelLite::Launch (libpl_lite_kernels.so), one CUDA graph around the "
+                        "instruction loop", "instructions_per_step": pnet.n_instructions,
+                "ms_per_step_device": ms / steps, "img_s_device": ctx.world * batch * steps / (ms * 1e-3),
+                "logits_identical_to_c_abi_path": same})
+    del pnet
+    torch.cuda.empty_cache()
+    return rec
+
+
 def run_b200(args):
     ctx = Ctx()
     torch = ctx.torch
@@ -701,16 +729,21 @@ def run_b200(args):
     extras = not args.no_extras
     if extras:
         line["sustained"] = bench_sustained(ctx, net, batch, 2.0, ms_per_step)
+        if args.net in ("resnet50", "mobilenet_v1"):
+            try:
+                line["e2e_plugin"] = bench_plugin(ctx, prog, net, batch, x_host, args.steps, args.warmup)
+            except Exception as exc:
+                line["e2e_plugin"] = {"error": repr(exc)}
         # the same end-to-end loop with narrower host feeds (the entry kernel reads fp16 / uint8 directly)
         for feed in ("f16", "u8"):
             try:
-                del net
+                net = None
                 torch.cuda.empty_cache()
                 _, net, xh = build_net(ctx, args.net, batch, feed)
                 line[f"e2e_{feed}"] = e2e_loop(ctx, net, xh, args.steps, args.warmup)
             except Exception as exc:
                 line[f"e2e_{feed}"] = {"error": repr(exc)}
-        del net
+        net = None
         torch.cuda.empty_cache()
         nets_rec = {}
         if args.net == "resnet50":

@@ -227,6 +227,15 @@ int pl_quantize_nchw_f16_to_s2d_i8(const void* x_f16, int8_t* y_s2d, int N, int 
 int pl_quantize_nchw_u8_to_s2d_i8(const uint8_t* x_u8, int8_t* y_s2d, int N, int C, int H, int W,
                                   const pl_s2d_geometry* g, const float* mean, const float* norm, float scale,
                                   int round_mode, pl_stream_t stream);
+/* the same entry for an int8 NHWC tensor that already exists (C <= 4, pixel pitch ldx): the reference's op chain
+ * calib -> layout -> conv ends here when the conv is a stride-2 stem.  Replaces the per-Run widening of the pixel
+ * pitch in front of cudnn's int8 conv (lite/backends/cuda/math/cudnn_conv.cc:329-337 needs C % 4 == 0). */
+int pl_nhwc_i8_to_s2d_i8(const int8_t* x, int ldx, int8_t* y_s2d, int N, int C, int H, int W,
+                         const pl_s2d_geometry* g, pl_stream_t stream);
+/* channel pitch change of an int8 NHWC tensor, pad channels zero ([pixels][ld_src] -> [pixels][ld_dst],
+ * ld_dst % 4 == 0): how a kernel class stages an activation with C % 16 != 0 at a TMA-legal pitch
+ * (lite/kernels/cuda/conv_compute.cc has no such case: cudnn int8 rejects those shapes) */
+int pl_repitch_i8_nhwc(const int8_t* x, int ld_src, int8_t* y, int ld_dst, int64_t pixels, int C, pl_stream_t stream);
 size_t pl_s2d_conv_packed_weight_bytes(int K, const pl_s2d_geometry* g);
 int pl_pack_s2d_conv_weight_i8(const int8_t* w_ohwi, int8_t* w_s2d, int K, int R, int S, int C,
                                const pl_s2d_geometry* g, pl_stream_t stream);

@@ -374,6 +374,28 @@ def quantize_nchw_to_s2d(x, scale, g, y=None, rnd=ROUND_ARM, mean=None, norm=Non
     return y
 
 
+def nhwc_to_s2d(x, g, Cc=None, y=None):
+    """int8 NHWC [N,H,W,ld] (Cc <= 4 logical channels) -> space-to-depth input buffer (pl_nhwc_i8_to_s2d_i8)"""
+    N, H, W, ld = x.shape
+    Cc = ld if Cc is None else Cc
+    if y is None:
+        y = s2d_input_buffer(g, x.device)
+    _check(lib().pl_nhwc_i8_to_s2d_i8(_ptr(x), x.stride(-2), _ptr(y), N, Cc, H, W, C.byref(g), _stream()),
+           "pl_nhwc_i8_to_s2d_i8")
+    return y
+
+
+def repitch(x, ld_dst, Cc=None):
+    """int8 [..., ld_src] -> [..., ld_dst] with zero pad channels (pl_repitch_i8_nhwc)"""
+    ld_src = x.shape[-1]
+    Cc = ld_src if Cc is None else Cc
+    pixels = x.numel() // ld_src
+    y = torch.empty(tuple(x.shape[:-1]) + (ld_dst,), dtype=torch.int8, device=x.device)
+    _check(lib().pl_repitch_i8_nhwc(_ptr(x), ld_src, _ptr(y), ld_dst, C.c_int64(pixels), Cc, _stream()),
+           "pl_repitch_i8_nhwc")
+    return y
+
+
 def pack_s2d_conv_weight(w_ohwi, g):
     K, R, S, Cc = w_ohwi.shape
     out = torch.empty(lib().pl_s2d_conv_packed_weight_bytes(K, C.byref(g)), dtype=torch.int8, device=w_ohwi.device)

@@ -329,6 +329,77 @@ quant_nchw_to_s2d_kernel(const TIn* __restrict__ x, uint4* __restrict__ y, int C
   }
 }
 
+// int8 NHWC (C <= 4 channels, pixel pitch ldx) -> space-to-depth pixels: the entry of the stride-2 stems when the
+// int8 tensor already exists (the reference's op chain calib -> layout -> conv of a kCUDA int8 model; the fused
+// quantiser above is the one-launch form of the same thing).  Thread = one 16-byte s2d pixel = 2 x 2 original
+// pixels; only the interior is written, the borders stay zero from the caller's one-off memset.
+__global__ void __launch_bounds__(256)
+nhwc_i8_to_s2d_kernel(const int8_t* __restrict__ x, uint4* __restrict__ y, int C, int ldx, int H, int W, int HP,
+                      int WS, int pad_s) {
+  const int n = blockIdx.y;
+  const int Ws = W >> 1, Hs = H >> 1;
+  const int item = blockIdx.x * blockDim.x + threadIdx.x;
+  if (item >= Hs * Ws) return;
+  const int hs = item / Ws, ws = item - hs * Ws;
+  const int8_t* p = x + (((long long)n * H + 2 * hs) * W + 2 * ws) * ldx;
+  uint32_t w[4];
+#pragma unroll
+  for (int dy = 0; dy < 2; ++dy)
+#pragma unroll
+    for (int dx = 0; dx < 2; ++dx) {
+      const int8_t* q = p + ((long long)dy * W + dx) * ldx;
+      uint32_t v = 0;
+#pragma unroll
+      for (int c = 0; c < 4; ++c)
+        if (c < C) v |= (uint32_t)(uint8_t)__ldg(q + c) << (8 * c);
+      w[dy * 2 + dx] = v;
+    }
+  y[((long long)n * HP + hs + pad_s) * WS + ws + pad_s] = make_uint4(w[0], w[1], w[2], w[3]);
+}
+
+extern "C" int pl_nhwc_i8_to_s2d_i8(const int8_t* x, int ldx, int8_t* y_s2d, int N, int C, int H, int W,
+                                    const pl_s2d_geometry* g, pl_stream_t stream) {
+  if (!x || !y_s2d || !g || !g->supported || N <= 0 || C <= 0 || C > 4 || ldx < C) return PL_ERR_ARG;
+  if ((H & 1) || (W & 1) || N > 65535) return PL_ERR_UNSUPPORTED;
+  if ((reinterpret_cast<uintptr_t>(y_s2d) & 15)) return PL_ERR_ALIGN;
+  const long long items = (long long)(H / 2) * (W / 2);
+  dim3 grid((unsigned)((items + 255) / 256), (unsigned)N);
+  nhwc_i8_to_s2d_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(x, reinterpret_cast<uint4*>(y_s2d), C, ldx, H, W, g->HP,
+                                                                g->WS, g->pad_s);
+  ++g_launches;
+  return launch_status();
+}
+
+// channel pitch change of an int8 NHWC tensor: [pixels][ld_src] (C logical channels) -> [pixels][ld_dst], pad
+// channels written as zeros.  One thread per 4-byte word of the destination.  (The kernel classes stage an
+// activation whose channel count is not a multiple of 16 at a TMA-legal pitch with this; a 2-D memcpy of 9- or
+// 18-byte rows runs at a few GB/s.)
+__global__ void __launch_bounds__(256)
+repitch_i8_kernel(const int8_t* __restrict__ x, uint32_t* __restrict__ y, long long pixels, int C, int ld_src,
+                  int words_dst) {
+  const long long total = pixels * words_dst;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+    const long long pix = i / words_dst;
+    const int c0 = (int)(i - pix * words_dst) * 4;
+    const int8_t* p = x + pix * ld_src + c0;
+    uint32_t v = 0;
+#pragma unroll
+    for (int c = 0; c < 4; ++c)
+      if (c0 + c < C) v |= (uint32_t)(uint8_t)__ldg(p + c) << (8 * c);
+    y[i] = v;
+  }
+}
+
+extern "C" int pl_repitch_i8_nhwc(const int8_t* x, int ld_src, int8_t* y, int ld_dst, int64_t pixels, int C,
+                                  pl_stream_t stream) {
+  if (!x || !y || pixels <= 0 || C <= 0 || ld_src < C || ld_dst < C || (ld_dst & 3)) return PL_ERR_ARG;
+  if (reinterpret_cast<uintptr_t>(y) & 3) return PL_ERR_ALIGN;
+  repitch_i8_kernel<<<grid_for(pixels * (ld_dst / 4), 256), 256, 0, (cudaStream_t)stream>>>(
+      x, reinterpret_cast<uint32_t*>(y), pixels, C, ld_src, ld_dst / 4);
+  ++g_launches;
+  return launch_status();
+}
+
 // ------------------------------------------------------------------ pooling
 __global__ void __launch_bounds__(256)
 pool_kernel(const int8_t* __restrict__ x, int ldx, void* __restrict__ y, int ldy, int N, int H, int W,
@@ -662,11 +733,52 @@ extern "C" int pl_transpose_i8(const int8_t* src, int ld_src, int8_t* dst, int l
   return launch_transpose<int8_t>(src, dst, 1, rows, cols, ld_src, ld_dst, 0, 0, (cudaStream_t)stream);
 }
 
+// int8 [N][C][HW] -> [N][HW][ld] for C <= 4 (the image feed of a quantised net after its calib): a 64 x 64 tile
+// transpose would use 3 of its 64 rows.  Thread = 4 consecutive pixels: one 32-bit load per channel plane, the
+// 4 * ld output bytes assembled in registers (pad channels zero) and stored as words when the pitch allows.
+__global__ void __launch_bounds__(256)
+nchw_to_nhwc_thin_i8_kernel(const int8_t* __restrict__ x, int8_t* __restrict__ y, int C, long long HW, int ld) {
+  const int n = blockIdx.y;
+  const long long q4 = (long long)blockIdx.x * blockDim.x + threadIdx.x;  // group of 4 pixels
+  if (q4 * 4 >= HW) return;
+  const int8_t* xs = x + (long long)n * C * HW + q4 * 4;
+  uint32_t plane[4] = {0, 0, 0, 0};
+#pragma unroll
+  for (int c = 0; c < 4; ++c)
+    if (c < C) plane[c] = __ldg(reinterpret_cast<const uint32_t*>(xs + (long long)c * HW));
+  int8_t* out = y + ((long long)n * HW + q4 * 4) * ld;
+  uint8_t b[16];
+#pragma unroll
+  for (int p = 0; p < 4; ++p)
+#pragma unroll
+    for (int c = 0; c < 4; ++c) b[p * 4 + c] = (uint8_t)(plane[c] >> (8 * p));
+  if (ld == 4) {
+    *reinterpret_cast<uint4*>(out) = *reinterpret_cast<const uint4*>(b);
+  } else if (ld == 3) {  // 12 contiguous bytes, 4-byte aligned (4 pixels x 3)
+    const uint32_t w0 = b[0] | (b[1] << 8) | (b[2] << 16) | ((uint32_t)b[4] << 24);
+    const uint32_t w1 = b[5] | (b[6] << 8) | (b[8] << 16) | ((uint32_t)b[9] << 24);
+    const uint32_t w2 = b[10] | (b[12] << 8) | (b[13] << 16) | ((uint32_t)b[14] << 24);
+    uint32_t* o = reinterpret_cast<uint32_t*>(out);
+    o[0] = w0; o[1] = w1; o[2] = w2;
+  } else {
+#pragma unroll
+    for (int p = 0; p < 4; ++p)
+      for (int c = 0; c < ld; ++c) out[p * ld + c] = c < 4 ? (int8_t)b[p * 4 + c] : (int8_t)0;
+  }
+}
+
 extern "C" int pl_nchw_to_nhwc(const void* x, void* y, int N, int C, int H, int W, int ld,
                                int elem_bytes, pl_stream_t stream) {
   if (!x || !y || N <= 0 || C <= 0 || H <= 0 || W <= 0 || ld < C) return PL_ERR_ARG;
   const long long HW = (long long)H * W;
   if (HW > 0x7fffffffLL) return PL_ERR_UNSUPPORTED;
+  if (elem_bytes == 1 && C <= 4 && (HW % 4) == 0 && N <= 65535 && (reinterpret_cast<uintptr_t>(x) & 3) == 0 &&
+      (reinterpret_cast<uintptr_t>(y) & 15) == 0 && (ld == C || ld == 4)) {
+    dim3 grid((unsigned)((HW / 4 + 255) / 256), (unsigned)N);
+    nchw_to_nhwc_thin_i8_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>((const int8_t*)x, (int8_t*)y, C, HW, ld);
+    ++g_launches;
+    return launch_status();
+  }
   int rc;
   // [N][C][HW] -> [N][HW][ld]
   if (elem_bytes == 1)

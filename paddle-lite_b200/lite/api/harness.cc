@@ -49,7 +49,24 @@ static std::unique_ptr<KernelBase> CreateKernel(const std::string& op, TargetTyp
   return nullptr;
 }
 
-static void LaunchAndSync(KernelBase* k, int launches) {
+// A runtime program (lite/core/program.cc:265-315 RuntimeProgram::Run): instructions = kernel instances with their
+// params bound, launched in order on ONE exec stream.  While a program is recording (plk_program_begin ..
+// plk_program_end) every plk_run_* call appends its kernel to the program instead of launching it.
+struct Program {
+  std::vector<std::unique_ptr<KernelBase>> insts;
+  cudaStream_t stream{nullptr};
+};
+static thread_local Program* g_recording = nullptr;
+
+static void LaunchAndSync(std::unique_ptr<KernelBase>& kp, int launches) {
+  if (g_recording) {
+    std::unique_ptr<KernelContext> c(new KernelContext);
+    c->As<CUDAContext>().SetExecStream(g_recording->stream);
+    kp->SetContext(std::move(c));
+    g_recording->insts.push_back(std::move(kp));
+    return;
+  }
+  KernelBase* k = kp.get();
   std::unique_ptr<KernelContext> ctx(new KernelContext);
   auto& cuda = ctx->As<CUDAContext>();
   cudaStream_t s;
@@ -98,6 +115,9 @@ int plk_tensor_ndim(void* t) { return static_cast<int>(T(t)->dims().size()); }
 void plk_tensor_dims(void* t, int64_t* out) {
   for (size_t i = 0; i < T(t)->dims().size(); ++i) out[i] = T(t)->dims()[i];
 }
+// declared precision of a tensor that a not-yet-run instruction will produce (a recording program picks the
+// consumer's kernel from it, as the type passes do from the producer's declaration)
+void plk_tensor_set_precision(void* t, int precision) { T(t)->set_precision(static_cast<PrecisionType>(precision)); }
 int plk_tensor_precision(void* t) { return static_cast<int>(T(t)->precision()); }
 int plk_tensor_target(void* t) { return static_cast<int>(T(t)->target()); }
 int64_t plk_tensor_bytes(void* t) { return static_cast<int64_t>(T(t)->memory_size()); }
@@ -108,6 +128,61 @@ int plk_tensor_to_host(void* t, void* dst, int64_t cap) {
   paddle::lite::kernels::cuda::DownloadBytes(T(t), dst, T(t)->memory_size());
   PLK_CATCH
 }
+
+// tensor over caller-owned device memory (a torch allocation in the benches): dims + precision + the pointer
+int plk_tensor_share_external(void* t, int precision, const int64_t* dims, int ndim, void* data, int64_t bytes) {
+  PLK_TRY
+  T(t)->Resize(std::vector<int64_t>(dims, dims + ndim));
+  T(t)->set_precision(static_cast<PrecisionType>(precision));
+  T(t)->ShareExternalMemory(data, static_cast<size_t>(bytes), TARGET(kCUDA));
+  PLK_CATCH
+}
+void* plk_tensor_raw(void* t) { return const_cast<void*>(T(t)->raw_data()); }
+// host <-> device copies of a tensor's bytes on a caller-provided stream (pinned host memory: asynchronous)
+int plk_tensor_copy_from_host_async(void* t, const void* src, int64_t bytes, void* stream) {
+  PLK_TRY
+  CHECK_LE(static_cast<size_t>(bytes), T(t)->memory_size());
+  CUDA_CALL(cudaMemcpyAsync(const_cast<void*>(T(t)->raw_data()), src, static_cast<size_t>(bytes), cudaMemcpyHostToDevice,
+                            static_cast<cudaStream_t>(stream)));
+  PLK_CATCH
+}
+int plk_tensor_copy_to_host_async(void* t, void* dst, int64_t bytes, void* stream) {
+  PLK_TRY
+  CHECK_LE(static_cast<size_t>(bytes), T(t)->memory_size());
+  CUDA_CALL(cudaMemcpyAsync(dst, T(t)->raw_data(), static_cast<size_t>(bytes), cudaMemcpyDeviceToHost,
+                            static_cast<cudaStream_t>(stream)));
+  PLK_CATCH
+}
+
+// ---- runtime program: record plk_run_* calls, then Launch() them in order ----
+void* plk_program_begin(void* stream) {
+  auto* p = new Program;
+  p->stream = static_cast<cudaStream_t>(stream);
+  g_recording = p;
+  return p;
+}
+int plk_program_end() {
+  g_recording = nullptr;
+  return 0;
+}
+// move every instruction to another exec stream (a CUDA-graph capture stream, another torch stream)
+int plk_program_set_stream(void* prog, void* stream) {
+  PLK_TRY
+  auto* p = static_cast<Program*>(prog);
+  p->stream = static_cast<cudaStream_t>(stream);
+  for (auto& k : p->insts) k->mutable_context()->As<CUDAContext>().SetExecStream(p->stream);
+  PLK_CATCH
+}
+int plk_program_size(void* prog) { return static_cast<int>(static_cast<Program*>(prog)->insts.size()); }
+// Instruction::Run for every instruction (KernelBase::Launch: PrepareForRun on the first call, then Run)
+int plk_program_run(void* prog, int sync) {
+  PLK_TRY
+  auto* p = static_cast<Program*>(prog);
+  for (auto& k : p->insts) k->Launch();
+  if (sync) TargetWrapperCuda::StreamSync(p->stream);
+  PLK_CATCH
+}
+void plk_program_destroy(void* prog) { delete static_cast<Program*>(prog); }
 
 // newline separated "op/alias/target/precision/layout"
 int plk_list_kernels(char* buf, int cap) {
@@ -189,7 +264,7 @@ int plk_run_conv(const char* op, void* x, void* filter, void* bias, void* residu
   auto k = CreateKernel(op, TARGET(kCUDA), PRECISION(kInt8), DATALAYOUT(kNHWC),
                         out_int8 ? PRECISION(kInt8) : PRECISION(kFloat));
   k->SetParam(p);
-  LaunchAndSync(k.get(), launches);
+  LaunchAndSync(k, launches);
   PLK_CATCH
 }
 
@@ -210,7 +285,7 @@ int plk_run_fc(void* x, void* w, void* bias, void* out, int in_num_col_dims, con
   auto k = CreateKernel("fc", TARGET(kCUDA), PRECISION(kInt8), DATALAYOUT(kNCHW),
                         out_int8 ? PRECISION(kInt8) : PRECISION(kFloat));
   k->SetParam(p);
-  LaunchAndSync(k.get(), launches);
+  LaunchAndSync(k, launches);
   PLK_CATCH
 }
 
@@ -230,7 +305,7 @@ int plk_run_mul(void* x, void* y, void* out, int x_cols, int y_cols, float input
   auto k = CreateKernel("mul", TARGET(kCUDA), PRECISION(kInt8), DATALAYOUT(kNCHW),
                         out_int8 ? PRECISION(kInt8) : PRECISION(kFloat));
   k->SetParam(p);
-  LaunchAndSync(k.get(), 1);
+  LaunchAndSync(k, 1);
   PLK_CATCH
 }
 
@@ -251,7 +326,7 @@ int plk_run_matmul(void* x, void* y, void* out, int tx, int ty, float alpha, flo
   auto k = CreateKernel("matmul", TARGET(kCUDA), PRECISION(kInt8), DATALAYOUT(kNCHW),
                         out_int8 ? PRECISION(kInt8) : PRECISION(kFloat));
   k->SetParam(p);
-  LaunchAndSync(k.get(), 1);
+  LaunchAndSync(k, 1);
   PLK_CATCH
 }
 
@@ -264,7 +339,7 @@ int plk_run_calib(void* in, void* out, float scale, int to_int8) {
   auto k = CreateKernel("calib", TARGET(kCUDA), PRECISION(kInt8), DATALAYOUT(kNCHW), PRECISION(kUnk),
                         to_int8 ? "fp32_to_int8" : "int8_to_fp32");
   k->SetParam(p);
-  LaunchAndSync(k.get(), 1);
+  LaunchAndSync(k, 1);
   PLK_CATCH
 }
 
@@ -278,7 +353,7 @@ int plk_run_layout(void* in, void* out, int to_nhwc) {
                         PRECISION(kUnk),
                         std::string(i8 ? "int8_" : "") + (to_nhwc ? "nchw2nhwc" : "nhwc2nchw"));
   k->SetParam(p);
-  LaunchAndSync(k.get(), 1);
+  LaunchAndSync(k, 1);
   PLK_CATCH
 }
 
@@ -290,7 +365,7 @@ int plk_run_io_copy(void* in, void* out, int h2d) {
   auto k = CreateKernel("io_copy", TARGET(kCUDA), PRECISION(kAny), DATALAYOUT(kAny), PRECISION(kUnk),
                         h2d ? "host_to_device" : "device_to_host");
   k->SetParam(p);
-  LaunchAndSync(k.get(), 1);
+  LaunchAndSync(k, 1);
   PLK_CATCH
 }
 
@@ -315,7 +390,7 @@ int plk_run_pool(void* x, void* out, const char* type, const int* ksize, const i
   auto k = CreateKernel("pool2d", TARGET(kCUDA), PRECISION(kInt8), DATALAYOUT(kNHWC),
                         out_int8 ? PRECISION(kInt8) : PRECISION(kFloat));
   k->SetParam(p);
-  LaunchAndSync(k.get(), 1);
+  LaunchAndSync(k, 1);
   PLK_CATCH
 }
 
@@ -334,7 +409,7 @@ int plk_run_add(void* x, void* y, void* out, float x_scale, float y_scale, float
   auto k = CreateKernel("fusion_elementwise_add_activation", TARGET(kCUDA), PRECISION(kInt8), DATALAYOUT(kNHWC),
                         out_int8 ? PRECISION(kInt8) : PRECISION(kFloat));
   k->SetParam(p);
-  LaunchAndSync(k.get(), 1);
+  LaunchAndSync(k, 1);
   PLK_CATCH
 }
 
@@ -365,7 +440,7 @@ int plk_run_concat(void* const* xs, int n, void* out, int axis) {
   p.axis = axis;
   auto k = CreateKernel("concat", TARGET(kCUDA), PRECISION(kInt8), DATALAYOUT(kNHWC), PRECISION(kInt8));
   k->SetParam(p);
-  LaunchAndSync(k.get(), 1);
+  LaunchAndSync(k, 1);
   PLK_CATCH
 }
 
@@ -379,7 +454,7 @@ int plk_run_split(void* x, void* const* outs, int n, int axis, int num, const in
   p.sections.assign(sections, sections + n_sections);
   auto k = CreateKernel("split", TARGET(kCUDA), PRECISION(kInt8), DATALAYOUT(kNHWC), PRECISION(kInt8));
   k->SetParam(p);
-  LaunchAndSync(k.get(), 1);
+  LaunchAndSync(k, 1);
   PLK_CATCH
 }
 
@@ -391,7 +466,7 @@ int plk_run_shuffle_channel(void* x, void* out, int group) {
   p.group = group;
   auto k = CreateKernel("shuffle_channel", TARGET(kCUDA), PRECISION(kInt8), DATALAYOUT(kNHWC), PRECISION(kInt8));
   k->SetParam(p);
-  LaunchAndSync(k.get(), 1);
+  LaunchAndSync(k, 1);
   PLK_CATCH
 }
 
@@ -407,7 +482,7 @@ int plk_run_relu(void* x, void* out, int relu6, float clip, float input_scale) {
   p.input_scale = p.output_scale = input_scale;
   auto k = CreateKernel(relu6 ? "relu6" : "relu", TARGET(kCUDA), PRECISION(kInt8), DATALAYOUT(kNHWC), PRECISION(kInt8));
   k->SetParam(p);
-  LaunchAndSync(k.get(), 1);
+  LaunchAndSync(k, 1);
   PLK_CATCH
 }
 

@@ -58,10 +58,19 @@ class Buffer {
   void* data() const { return data_; }
   TargetType target() const { return target_; }
   size_t space() const { return space_; }
+  // caller-owned memory (lite_api::Tensor::ShareExternalMemory, lite/api/paddle_api.h:62-65): never freed here;
+  // the caller keeps it valid for as long as the tensor is used
+  void ShareExternal(void* data, size_t size, TargetType target) {
+    Free();
+    data_ = data;
+    space_ = size;
+    target_ = target;
+    external_ = true;
+  }
 
  private:
   void Free() {
-    if (data_) {
+    if (data_ && !external_) {
       if (target_ == TARGET(kCUDA))
         TargetWrapperCuda::Free(data_);
       else
@@ -69,7 +78,9 @@ class Buffer {
     }
     data_ = nullptr;
     space_ = 0;
+    external_ = false;
   }
+  bool external_{false};
   void* data_{nullptr};
   size_t space_{0};
   TargetType target_{TARGET(kHost)};
@@ -110,6 +121,11 @@ class Tensor {
       TargetWrapperCuda::MemcpySync(dst, src, memory_size_, IoDirection::HtoD);
     else
       std::memcpy(dst, src, memory_size_);
+  }
+  void ShareExternalMemory(void* data, size_t memory_size, TargetType target) {
+    buffer_->ShareExternal(data, memory_size, target);
+    target_ = target;
+    memory_size_ = memory_size;
   }
   void ShareDataWith(const Tensor& o) {
     buffer_ = o.buffer_;

@@ -40,7 +40,23 @@ void ConvComputeInt8<Ptype_out>::PrepareForRun() {
   epi_.Fold(param.weight_scale, static_cast<int>(K), param.input_scale, param.output_scale, out_int8, param.bias, act,
             arg);
 
-  if (param.groups == 1 && C <= 4 &&
+  const auto& xd0 = param.x->dims();
+  const pl_s2d_geometry g1 =
+      (param.groups == 1 && C <= 4 && !param.residualData)
+          ? pl_s2d_conv_geometry(1, static_cast<int>(xd0[1]), static_cast<int>(xd0[2]), static_cast<int>(C),
+                                 static_cast<int>(R), static_cast<int>(S), param.strides[0], param.strides[1],
+                                 (*param.paddings)[0], (*param.paddings)[1], (*param.paddings)[2], (*param.paddings)[3],
+                                 (*param.dilations)[0], (*param.dilations)[1])
+          : pl_s2d_geometry{};
+  if (g1.supported && K <= 256) {
+    // stride-2 thin stem (ResNet 7x7 / MobileNet 3x3): the input is re-read as 16-byte space-to-depth pixels and the
+    // conv runs as a stride-1 conv over them on the tensor cores (pl_int8.h)
+    path_ = kThinS2d;
+    packed_filter_.Resize(DDim({static_cast<int64_t>(pl_s2d_conv_packed_weight_bytes(static_cast<int>(K), &g1))}));
+    PL_CALL(pl_pack_s2d_conv_weight_i8(param.filter->data<int8_t>(), packed_filter_.mutable_data<int8_t>(TARGET(kCUDA)),
+                                       static_cast<int>(K), static_cast<int>(R), static_cast<int>(S), static_cast<int>(C),
+                                       &g1, reinterpret_cast<pl_stream_t>(stream)));
+  } else if (param.groups == 1 && C <= 4 &&
       pl_thin_conv_supported(static_cast<int>(R), static_cast<int>(S), static_cast<int>(C), (*param.dilations)[0],
                              (*param.dilations)[1]) &&
       !param.residualData) {
@@ -121,6 +137,21 @@ void ConvComputeInt8<Ptype_out>::Run() {
     return;
   }
   const int64_t pixels = N * xd[1] * xd[2];
+  if (path_ == kThinS2d) {
+    const pl_s2d_geometry g = pl_s2d_conv_geometry(d.N, d.H, d.W, d.C, d.R, d.S, d.stride_h, d.stride_w, d.pad_t, d.pad_b,
+                                                   d.pad_l, d.pad_r, d.dil_h, d.dil_w);
+    CHECK(g.supported);
+    s2d_in_.Resize(DDim({static_cast<int64_t>(g.bytes)}));
+    int8_t* xs = s2d_in_.mutable_data<int8_t>(TARGET(kCUDA));
+    if (g.bytes != s2d_bytes_) {  // (re)sized: the borders are zero from here on, only the interior is rewritten
+      CUDA_CALL(cudaMemsetAsync(xs, 0, g.bytes, ctx.exec_stream()));
+      s2d_bytes_ = g.bytes;
+    }
+    PL_CALL(pl_nhwc_i8_to_s2d_i8(x, static_cast<int>(C), xs, d.N, d.C, d.H, d.W, &g, stream));
+    d.ldx = 4;
+    PL_CALL(pl_s2d_conv2d_i8(xs, packed_filter_.data<int8_t>(), y, &d, &e, stream));
+    return;
+  }
   if (path_ == kThinIm2col || path_ == kThinDirect) {
     // widen the pixel pitch to one word
     x_padded_.Resize(DDim({pixels, 4}));
@@ -128,9 +159,7 @@ void ConvComputeInt8<Ptype_out>::Run() {
     if (C == 4) {
       xp = const_cast<int8_t*>(x);
     } else {
-      CUDA_CALL(cudaMemsetAsync(xp, 0, static_cast<size_t>(pixels) * 4, ctx.exec_stream()));
-      CUDA_CALL(cudaMemcpy2DAsync(xp, 4, x, static_cast<size_t>(C), static_cast<size_t>(C),
-                                  static_cast<size_t>(pixels), cudaMemcpyDeviceToDevice, ctx.exec_stream()));
+      PL_CALL(pl_repitch_i8_nhwc(x, static_cast<int>(C), xp, 4, pixels, static_cast<int>(C), stream));
     }
     if (path_ == kThinDirect) {
       d.ldx = 4;
@@ -150,8 +179,7 @@ void ConvComputeInt8<Ptype_out>::Run() {
     const int64_t ld = RoundUp(C, 16);
     x_padded_.Resize(DDim({pixels, ld}));
     int8_t* xp = x_padded_.mutable_data<int8_t>(TARGET(kCUDA));
-    CUDA_CALL(cudaMemcpy2DAsync(xp, static_cast<size_t>(ld), x, static_cast<size_t>(C), static_cast<size_t>(C),
-                                static_cast<size_t>(pixels), cudaMemcpyDeviceToDevice, ctx.exec_stream()));
+    PL_CALL(pl_repitch_i8_nhwc(x, static_cast<int>(C), xp, static_cast<int>(ld), pixels, static_cast<int>(C), stream));
     x = xp;
     d.ldx = static_cast<int>(ld);
   }

@@ -19,12 +19,14 @@ class ConvComputeInt8 : public KernelLite<TARGET(kCUDA), PRECISION(kInt8), DATAL
   virtual ~ConvComputeInt8() = default;
 
  private:
-  enum Path { kDense, kDepthwise, kThinIm2col, kThinDirect };
+  enum Path { kDense, kDepthwise, kThinIm2col, kThinDirect, kThinS2d };
   Path path_{kDense};
   FoldedEpilogue epi_;
   Tensor packed_filter_;  // dense: tcgen05 K-blocked packing; thin: [K, ldA] or the direct-kernel packing
   Tensor x_padded_;       // input copied to a 16-byte channel pitch when C % 16 != 0
   Tensor im2col_;         // thin first layers (C <= 4)
+  Tensor s2d_in_;         // stride-2 thin stems: the input as space-to-depth pixels (zero borders, written once)
+  size_t s2d_bytes_{0};
   int ldA_{0};
 };
 

@@ -392,7 +392,9 @@ class DeviceNet:
     def _res_scale(self, op):
         if not op.get("res"):
             return 0.0
-        return op.res_scale if op.out_fp32 else op.res_scale / op.out_scale
+        # single-precision division, as the kernel class computes it from its float attributes
+        # (conv_compute_int8.cc: scale_in_eltwise / output_scale): both paths then feed identical epilogue inputs
+        return op.res_scale if op.out_fp32 else float(np.float32(op.res_scale) / np.float32(op.out_scale))
 
     def _exec_conv(self, op, x, sf, bf, argf, out, y, res=None, res_scale=0.0):
         C = op.C

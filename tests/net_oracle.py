@@ -48,7 +48,7 @@ def run_program(prog, x_nchw, engine="oracle", keep=False, timings=None):
                                            out, op.bias, act, arg)
             x = vals[op.src]
             if op.get("res"):
-                rs = op.res_scale if op.out_fp32 else op.res_scale / op.out_scale
+                rs = op.res_scale if op.out_fp32 else float(np.float32(op.res_scale) / np.float32(op.out_scale))
                 g = op.K if op.kind == "dwconv" else 1
                 vals[op.dst] = orc.conv2d(x, op.w, sf, bf, (op.stride, op.stride), (op.pad,) * 4, (1, 1), g,
                                           act, argf, out, residual=vals[op.res], res_scale=rs)

@@ -490,6 +490,15 @@ def test_rounding_every_tie_and_edge(pl):
         assert np.array_equal(got, orc.quantize(vals, 1.0, r))
 
 
+@pytest.mark.parametrize("shape", [(2, 3, 16, 18), (3, 4, 8, 8), (2, 1, 6, 6), (1, 2, 10, 14), (2, 3, 224, 224)])
+def test_layout_thin_int8(pl, shape):
+    """image feeds (C <= 4, HW % 4 == 0) take the thin int8 layout kernel: dense pitch and one-word pitch"""
+    x8 = np.random.default_rng(sum(shape)).integers(-128, 128, shape, dtype=np.int8)
+    assert np.array_equal(host(pl.nchw_to_nhwc(dev(x8))), orc.nchw_to_nhwc(x8))
+    y4 = host(pl.nchw_to_nhwc(dev(x8), 4))
+    assert np.array_equal(y4[..., : shape[1]], orc.nchw_to_nhwc(x8)) and not y4[..., shape[1]:].any()
+
+
 @pytest.mark.parametrize("shape", [(2, 3, 17, 19), (1, 64, 56, 56), (3, 72, 12, 12), (1, 1000, 1, 1)])
 def test_layout_transforms(pl, shape):
     rng = np.random.default_rng(sum(shape))
@@ -815,3 +824,27 @@ def test_gemv_skinny_m(pl, M, K, N, out):
         assert np.allclose(got, want, rtol=1e-5, atol=1e-6)
     else:
         assert np.array_equal(got, want)
+
+
+@pytest.mark.parametrize("case", [(2, 32, 32, 3, 7, 3), (3, 20, 28, 3, 3, 1), (1, 16, 16, 4, 7, 3), (2, 12, 12, 1, 3, 1)])
+def test_nhwc_to_s2d_matches_fused_quantiser(pl, case):
+    """the int8 entry of the space-to-depth stems (plugin chain calib -> layout -> conv) writes the very bytes the
+    fused fp32 quantiser writes"""
+    N, H, W, Cc, k, pad = case
+    rng = np.random.default_rng(3)
+    xf = rng.uniform(-1, 1, (N, Cc, H, W)).astype(np.float32)
+    g = pl.s2d_geometry(N, H, W, Cc, k, k, (2, 2), (pad,) * 4)
+    assert g.supported
+    want = host(pl.quantize_nchw_to_s2d(dev(xf), 1 / 127, g))
+    q = orc.nchw_to_nhwc(orc.quantize(xf, 1 / 127))  # int8 NHWC, dense C channels
+    got = host(pl.nhwc_to_s2d(dev(q), g))
+    assert np.array_equal(got, want)
+
+
+@pytest.mark.parametrize("C,ld", [(3, 4), (9, 16), (18, 32), (72, 80), (16, 16), (5, 8)])
+def test_repitch(pl, C, ld):
+    rng = np.random.default_rng(C)
+    x = rng.integers(-128, 128, (3, 5, 7, C), dtype=np.int8)
+    got = host(pl.repitch(dev(x), ld))
+    assert got.shape == (3, 5, 7, ld)
+    assert np.array_equal(got[..., :C], x) and not got[..., C:].any()
