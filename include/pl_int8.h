@@ -336,6 +336,9 @@ int pl_i8_mma_peak(int ctas, int iters, int bn, int32_t* out, pl_stream_t stream
 /* same, with the operand layout of a 32 / 64 / 128-byte K block (one iteration = row_bytes/32
  * MMAs): measures how the smem swizzle mode and N change the cost of one tcgen05.mma */
 int pl_i8_mma_probe(int ctas, int iters, int bn, int row_bytes, int32_t* out, pl_stream_t stream);
+/* the same for CTA pairs (clusters of two CTAs, tcgen05.mma.cta_group::2 with M = 256, B split over the two
+ * CTAs' shared memories): `ctas` must be even; one MMA counts 2 x 128 x bn x 32 MACs */
+int pl_i8_mma_probe_pairs(int ctas, int iters, int bn, int row_bytes, int32_t* out, pl_stream_t stream);
 
 #ifdef __cplusplus
 }

@@ -525,8 +525,11 @@ static constexpr int kDwThreads = 32 * (kDwConsumerWarps + 1);  // + the TMA pro
 // (8 warps = 2 per scheduler: two CTAs of up to 128 registers per thread fit the 16 K registers of an SMSP;
 // 9 warps did not -- ncu launch__occupancy_limit_registers 1)
 
+#ifndef PL_DW_CTAS
+#define PL_DW_CTAS 2  // resident CTAs per SM the register budget is cut for (experiment: 3 -> 80 registers)
+#endif
 template <int STRIDE, bool FAST>
-__global__ void __launch_bounds__(kDwThreads, 2)
+__global__ void __launch_bounds__(kDwThreads, PL_DW_CTAS)
 dw3x3_tma_kernel(const __grid_constant__ CUtensorMap tx, const DwParams p, const DwTile t) {
   extern __shared__ __align__(128) uint8_t dw_smem[];
   __shared__ __align__(8) uint64_t full_bar[kDwStagesMax], empty_bar[kDwStagesMax];
@@ -608,11 +611,14 @@ dw3x3_tma_kernel(const __grid_constant__ CUtensorMap tx, const DwParams p, const
       const uint32_t pix0 = (uint32_t)((n * p.P + pg0) * p.Q + oq0);
       // whole strip inside the image: no per-pixel column checks
       const bool full_strip = oq0 + (STRIDE == 1 ? 4 : 2) <= p.Q;
-      uint32_t* orow = reinterpret_cast<uint32_t*>(reinterpret_cast<int8_t*>(p.y) + c0) + (size_t)pix0 * ldyw;
-      const size_t orow_step = (size_t)p.Q * ldyw;
+      // 32-bit word offsets from the (uniform) base of y: one integer add per pixel instead of a 64-bit pointer
+      // chain (the host takes this kernel only when the output has fewer than 2^32 words)
+      uint32_t* const ybase = reinterpret_cast<uint32_t*>(p.y);
+      uint32_t orow = pix0 * ldyw + ((uint32_t)c0 >> 2);
+      const uint32_t orow_step = (uint32_t)p.Q * ldyw;
       auto finish = [&](const int (&acc)[4], int q, uint32_t pix) {
         if (FAST) {
-          dw_finish4_ptr(acc, sc, bs, hi_bits, orow + (size_t)q * ldyw, full_strip || oq0 + q < p.Q);
+          dw_finish4_ptr(acc, sc, bs, hi_bits, ybase + (orow + (uint32_t)q * ldyw), full_strip || oq0 + q < p.Q);
         } else {
           if (oq0 + q < p.Q) dw_finish4<false>(p, acc, sc, bs, p.hi_bits, pix + q, c0);
         }
@@ -905,7 +911,7 @@ extern "C" int pl_dwconv2d_i8_nhwc(const int8_t* x, const int8_t* w_crs, void* y
         t.groups = items_max / items;
         if (t.groups > 4) t.groups = 4;
         if (t.groups < 1) t.groups = 1;
-        const int budget = 36 * 1024;
+        const int budget = (PL_DW_CTAS == 2 ? 36 : 32) * 1024;
         int tr = s1 ? budget / rowbytes - 2 : (budget / rowbytes - 1) / 2;
         if (tr > P) tr = P;
         if (tr > 32) tr = 32;
@@ -920,9 +926,10 @@ extern "C" int pl_dwconv2d_i8_nhwc(const int8_t* x, const int8_t* w_crs, void* y
         const long long tiles = tiles_for(tr);
         t.stage_bytes = (uint32_t)(rowbytes * t.BH);
         t.stage_pitch = (t.stage_bytes + 127u) / 128u * 128u;
-        int stages = (int)((108u * 1024u) / t.stage_pitch);
+        int stages = (int)(((PL_DW_CTAS == 2 ? 108u : 72u) * 1024u) / t.stage_pitch);
         if (stages > kDwStagesMax) stages = kDwStagesMax;
-        ok = tiles < (1ll << 31) && t.BH <= 256 && stages >= 2;
+        ok = tiles < (1ll << 31) && t.BH <= 256 && stages >= 2 &&
+             (long long)d->N * P * Q * (d->ldy / 4) < (1ll << 32);  // 32-bit output word offsets
         if (ok) {
           t.tiles = (int)tiles;
           t.stages = stages;
@@ -937,7 +944,7 @@ extern "C" int pl_dwconv2d_i8_nhwc(const int8_t* x, const int8_t* w_crs, void* y
           if (rc == PL_OK) {
             const size_t smem = (size_t)t.stages * t.stage_pitch + 128;
             // a multiple of ctiles, so that a CTA keeps its channel chunk (and its filter registers)
-            int grid = t.tiles < 2 * sms ? t.tiles : 2 * sms;
+            int grid = t.tiles < PL_DW_CTAS * sms ? t.tiles : PL_DW_CTAS * sms;
             grid -= grid % t.ctiles;
             if (grid < t.ctiles) grid = t.ctiles;
             auto go = [&](auto kern) {

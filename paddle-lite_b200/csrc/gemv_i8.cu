@@ -1,4 +1,5 @@
-// gemv_i8.cu -- skinny int8 GEMM (M <= 8: batch-1 .. batch-8 fc / mul / matmul) as a bandwidth kernel.
+// gemv_i8.cu -- skinny int8 GEMM (batch-1 .. batch-64 fc / mul / matmul) as a bandwidth kernel: 8 rows of A per
+// CTA row (blockIdx.y), the weights re-read from L2 by every row group.
 //
 // Replaces the role of lite/backends/arm/math/gemv_arm_int8.cc:25-143 (gemv_int8: one output per weight
 // row, K split over NEON lanes, write_gemv_out epilogue).  With M <= 8 the weights Bt[N, K] are read once and
@@ -41,6 +42,8 @@ __global__ void __launch_bounds__(32 * kGemvWarps) gemv_i8_kernel(const GemvPara
   const int c_begin = ks * cps;
   const int c_end = min(chunks, c_begin + cps);
   const int tail = p.K & 15;  // bytes of the last chunk that belong to K (0 = all 16)
+  const int m0 = (int)blockIdx.y * 8;  // this CTA row's 8 rows of A / C (MT == 8 whenever gridDim.y > 1)
+  const int Mloc = min(p.M - m0, MT);
   int acc[MT][kGemvRows];
 #pragma unroll
   for (int m = 0; m < MT; ++m)
@@ -71,8 +74,8 @@ __global__ void __launch_bounds__(32 * kGemvWarps) gemv_i8_kernel(const GemvPara
       }
 #pragma unroll
       for (int m = 0; m < MT; ++m) {
-        if (m < p.M) {
-          const int4 a = __ldg(reinterpret_cast<const int4*>(p.A + (size_t)m * p.lda) + c);
+        if (m < Mloc) {
+          const int4 a = __ldg(reinterpret_cast<const int4*>(p.A + (size_t)(m0 + m) * p.lda) + c);
 #pragma unroll
           for (int r = 0; r < kGemvRows; ++r) {
             int s = acc[m][r];
@@ -100,9 +103,9 @@ __global__ void __launch_bounds__(32 * kGemvWarps) gemv_i8_kernel(const GemvPara
   int sum = 0;
   for (int s = 0; s < p.ks; ++s) sum += red[warp + s][lane];
   const int m = lane / kGemvRows, n = n0 + lane % kGemvRows;
-  if (m >= p.M || n >= p.N) return;
+  if (m >= Mloc || n >= p.N) return;
   const EpiParams& e = p.epi;
-  const size_t o = (size_t)m * p.ldc + n;
+  const size_t o = (size_t)(m0 + m) * p.ldc + n;
   if (e.out_dtype == PL_OUT_INT32) {
     reinterpret_cast<int*>(p.C)[o] = sum;
     return;
@@ -114,17 +117,18 @@ __global__ void __launch_bounds__(32 * kGemvWarps) gemv_i8_kernel(const GemvPara
     reinterpret_cast<int8_t*>(p.C)[o] = (int8_t)round_sat_i8(v, e.round_mode);
 }
 
-// M <= 8, no fused residual: returns PL_OK after launching, or -100 when the shape is not for this kernel
+// M <= 64, no fused residual: returns PL_OK after launching, or -100 when the shape is not for this kernel
 int launch_gemv_i8(const int8_t* A, int lda, const int8_t* Bt, int ldb, void* C, int ldc, int M, int N, int K,
                    const pl_epilogue* e, pl_stream_t stream) {
-  if (M > 8 || e->residual) return -100;
+  if (M > 64 || e->residual) return -100;
   {
     // measured on B200 (tools/gemv_time.py): this kernel streams weights at 4.1-5.9 TB/s for M = 1 but is
     // dp4a-bound at ~13 GMAC/us as M grows (8 x 16384^2: 137 us against 57 us on the tensor cores, whose skinny
     // launches have a ~17 us floor and stream at ~4.7 TB/s); take whichever the model predicts faster
     const double nk = (double)N * K;
     const double t_gemv = fmax(nk / 5.5e6, (double)M * nk / 13e6);
-    const double t_tc = fmax(17.0, nk / 4.7e6);
+    // (small tensor-core GEMMs: 10.7 us for 64 x 1000 x 1024 in isolation, 16 us inside MobileNetV1)
+    const double t_tc = fmax(M <= 8 ? 17.0 : 11.0, nk / 4.7e6);
     if (t_gemv > t_tc) return -100;
   }
   GemvParams p{};
@@ -137,8 +141,9 @@ int launch_gemv_i8(const int8_t* A, int lda, const int8_t* Bt, int ldb, void* C,
   const int chunks = (K + 15) / 16;
   // split K over the warps of a CTA while the row blocks alone leave warps idle and every split still
   // streams at least 1 KB (64 chunks) per weight row
+  const unsigned gy = (unsigned)((M + 7) / 8);
   int ks = 1;
-  while (ks < kGemvWarps && (long long)units * ks < 2ll * sms * kGemvWarps && chunks / (ks * 2) >= 64) ks *= 2;
+  while (ks < kGemvWarps && (long long)units * ks * gy < 2ll * sms * kGemvWarps && chunks / (ks * 2) >= 64) ks *= 2;
   p.ks = ks;
   const int upc = kGemvWarps / ks;
   const unsigned grid = (unsigned)((units + upc - 1) / upc);
@@ -146,7 +151,7 @@ int launch_gemv_i8(const int8_t* A, int lda, const int8_t* Bt, int ldb, void* C,
   if (M <= 1) launch_pdl(gemv_i8_kernel<1>, dim3(grid), dim3(32 * kGemvWarps), 0, st, p);
   else if (M <= 2) launch_pdl(gemv_i8_kernel<2>, dim3(grid), dim3(32 * kGemvWarps), 0, st, p);
   else if (M <= 4) launch_pdl(gemv_i8_kernel<4>, dim3(grid), dim3(32 * kGemvWarps), 0, st, p);
-  else launch_pdl(gemv_i8_kernel<8>, dim3(grid), dim3(32 * kGemvWarps), 0, st, p);
+  else launch_pdl(gemv_i8_kernel<8>, dim3(grid, gy), dim3(32 * kGemvWarps), 0, st, p);
   ++g_launches;
   return launch_status();
 }

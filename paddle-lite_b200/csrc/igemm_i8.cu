@@ -1060,7 +1060,9 @@ igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
         mbar_arrive(kInPlace ? bar_rempty + 8 * ob : bar_ofree + 8 * ob);
         if (++ob == nbufs) { ob = 0; ophase ^= 1; }
       }
+#ifndef PL_EXP_NO_FINAL_WAIT
       bulk_wait_group<0>();
+#endif
     }
     __syncwarp();
   } else {
@@ -1338,6 +1340,60 @@ __global__ void __launch_bounds__(128, 1) i8_mma_peak_kernel(int iters, int bn, 
   if (warp == 0) {
     tc_fence_after();
     tmem_dealloc(tmem, 512);
+  }
+}
+
+// the same probe for CTA pairs: clusters of two CTAs, the leader issues M = 256 MMAs whose B operand (bn rows) is
+// split over the two CTAs' shared memories; counts as 2 x (128 x bn x 32) per instruction
+__global__ void __launch_bounds__(128, 1) i8_mma_peak_pair_kernel(int iters, int bn, int32_t* out, int row_bytes) {
+  extern __shared__ uint8_t smem_raw[];
+  __shared__ __align__(8) uint64_t bar;
+  __shared__ uint32_t tmem_slot;
+  const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+  const uint32_t sa = base, sb = base + 128 * 128;
+  for (uint32_t i = threadIdx.x; i < (128u + (uint32_t)bn / 2u) * 128u / 4u; i += blockDim.x)
+    asm volatile("st.shared.b32 [%0], %1;" ::"r"(base + 4 * i), "r"(0x01010101u));
+  fence_proxy_async();
+  const int warp = threadIdx.x >> 5;
+  const uint32_t rank = cluster_ctarank();
+  if (threadIdx.x == 0) {
+    mbar_init(smem_u32(&bar), 1);
+    fence_barrier_init();
+  }
+  if (warp == 0) {
+    tmem_alloc_2sm(smem_u32(&tmem_slot), 512);
+    tmem_relinquish_2sm();
+  }
+  tc_fence_before();
+  cluster_sync_all();
+  tc_fence_after();
+  const uint32_t tmem = tmem_slot;
+  if (rank == 0 && warp == 0 && elect_one()) {
+    const uint32_t idesc = make_idesc_i8((uint32_t)bn, 256u);
+    const uint64_t hi = make_smem_desc_base((uint32_t)row_bytes);
+    const uint64_t da = hi | (uint64_t)((sa >> 4) & 0x3fff), db = hi | (uint64_t)((sb >> 4) & 0x3fff);
+    const uint32_t kmask = (uint32_t)(row_bytes / 32 - 1);
+    for (int i = 0; i < iters; ++i) {
+      const uint32_t d = tmem + (uint32_t)((i & 1) * bn);
+#pragma unroll
+      for (uint32_t k = 0; k < 8; ++k) {
+        const uint64_t ko = (uint64_t)(2u * (k & kmask));
+        umma_i8_2sm(d, da + ko, db + ko, idesc, (uint32_t)(i > 1 || k > 0));
+      }
+    }
+    umma_commit_2sm(smem_u32(&bar));
+  }
+  mbar_wait(smem_u32(&bar), 0);
+  tc_fence_after();
+  uint32_t r[16];
+  tmem_ld_32x32b_x16(tmem + ((uint32_t)(warp * 32) << 16), r);
+  tmem_ld_wait();
+  if (threadIdx.x == 0 && blockIdx.x == 0) out[0] = (int32_t)r[0];
+  tc_fence_before();
+  cluster_sync_all();
+  if (warp == 0) {
+    tc_fence_after();
+    tmem_dealloc_2sm(tmem, 512);
   }
 }
 
@@ -1958,6 +2014,15 @@ int common_setup(IgemmParams& p, long long M, int Nout, void* y, int ldy, const 
     p.BN = 16;
     while (p.BN < Nout && p.BN < 256) p.BN <<= 1;
   }
+  {
+    // a 256-wide tile whose filter slice (K_red x 256 bytes) cannot stay resident in shared memory, while a 128-wide
+    // one (<= 64 KB) can: the resident slice wins (r5 1x1 512 -> 2048 + residual: 25.8 -> 21.6 us at b256)
+    const long long kred = (long long)taps * cpad;
+    const int nt128 = (Nout + 127) / 128;
+    if (p.BN == 256 && p.halo_m_tiles == 0 && !p.s2d && p.mode != 2 && e->out_dtype == PL_OUT_INT8 && kred * 256 > 64 * 1024 && kred * 128 <= 64 * 1024 &&
+        nt128 <= 16 && (long long)p.m_tiles * nt128 >= 2ll * driver().sm_count && env_int("PL_NO_BN128_RES", 0) == 0)
+      p.BN = 128;
+  }
   if (e->residual) {
     // fused-residual launches are bandwidth bound and need smem for the residual ring and
     // the staging buffers: thin reductions take a finer K-block so that three mainloop
@@ -2497,8 +2562,9 @@ extern "C" int pl_gemm_i8(const int8_t* A, int lda, const int8_t* Bt, int ldb, v
   if ((reinterpret_cast<uintptr_t>(A) & 15) || (reinterpret_cast<uintptr_t>(Bt) & 15) || (lda % 16) ||
       (ldb % 16))
     return PL_ERR_ALIGN;
-  // batch-1 .. batch-8 fc: a weight-streaming kernel (gemv_i8.cu) instead of a 1/128-full tensor-core tile
-  if (M <= 8 && env_int("PL_NO_GEMV", 0) == 0) {
+  // batch-1 .. batch-64 fc: a weight-streaming kernel (gemv_i8.cu) instead of a mostly empty tensor-core tile
+  // (it declines, -100, when its cost model favours the tensor cores)
+  if (M <= 64 && env_int("PL_NO_GEMV", 0) == 0) {
     rc = launch_gemv_i8(A, lda, Bt, ldb, C, ldc, M, N, K, e, stream);
     if (rc != -100) return rc;
   }
@@ -2526,6 +2592,29 @@ extern "C" int pl_i8_mma_probe(int ctas, int iters, int bn, int row_bytes, int32
   const size_t smem = (size_t)(128 + bn) * 128 + 1024;
   PL_CUDA_OK(cudaFuncSetAttribute(i8_mma_peak_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   i8_mma_peak_kernel<<<ctas, 128, smem, (cudaStream_t)stream>>>(iters, bn, out, row_bytes);
+  ++g_launches;
+  return launch_status();
+}
+
+extern "C" int pl_i8_mma_probe_pairs(int ctas, int iters, int bn, int row_bytes, int32_t* out, pl_stream_t stream) {
+  if (ctas <= 0 || (ctas & 1) || iters <= 0 || bn < 32 || bn > 256 || (bn % 32) || !out ||
+      (row_bytes != 32 && row_bytes != 64 && row_bytes != 128))
+    return PL_ERR_ARG;
+  const size_t smem = (size_t)(128 + bn / 2) * 128 + 1024;
+  PL_CUDA_OK(cudaFuncSetAttribute(i8_mma_peak_pair_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = dim3((unsigned)ctas);
+  cfg.blockDim = dim3(128);
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = (cudaStream_t)stream;
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributeClusterDimension;
+  at[0].val.clusterDim.x = 2;
+  at[0].val.clusterDim.y = 1;
+  at[0].val.clusterDim.z = 1;
+  cfg.attrs = at;
+  cfg.numAttrs = 1;
+  PL_CUDA_OK(cudaLaunchKernelEx(&cfg, i8_mma_peak_pair_kernel, iters, bn, out, row_bytes));
   ++g_launches;
   return launch_status();
 }

@@ -6,7 +6,7 @@ set -e
 cd "$(dirname "$0")/../paddle-lite_b200/csrc"
 NAME=$1; FLAGS=$2
 mkdir -p ../variants /tmp/plv_$NAME
-for f in igemm_i8 dwconv_i8 elementwise_i8 channel_ops_i8 capi; do
+for f in igemm_i8 gemv_i8 dwconv_i8 elementwise_i8 channel_ops_i8 fp32_tail capi; do
   /usr/local/cuda/bin/nvcc -O3 -std=c++17 -gencode arch=compute_100a,code=sm_100a -lineinfo -fmad=false -Xcompiler -fPIC $FLAGS -c $f.cu -o /tmp/plv_$NAME/$f.o &
 done
 wait

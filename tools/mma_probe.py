@@ -25,3 +25,19 @@ for rb in (128, 64, 32):
         cyc = ms * 1e-3 * clk / mmas
         tops = sms * mmas * 2.0 * 128 * bn * 32 / (ms * 1e-3) / 1e12
         print(f"row_bytes={rb:3d} N={bn:3d}: {cyc:7.1f} cycles/MMA  {tops:7.1f} TOPS", flush=True)
+
+print("CTA pairs (cta_group::2, M = 256; B half per CTA):")
+for bn in (256, 128, 64):
+    iters = 4000
+    lib.pl_i8_mma_probe_pairs(sms, 200, bn, 128, C.c_void_p(out.data_ptr()), None)
+    torch.cuda.synchronize()
+    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    a.record()
+    rc = lib.pl_i8_mma_probe_pairs(sms, iters, bn, 128, C.c_void_p(out.data_ptr()), None)
+    b.record()
+    torch.cuda.synchronize()
+    ms = a.elapsed_time(b)
+    mmas = iters * 8
+    cyc = ms * 1e-3 * clk / mmas
+    tops = (sms // 2) * mmas * 2.0 * 256 * bn * 32 / (ms * 1e-3) / 1e12
+    print(f"pairs rc={rc} N={bn:3d}: {cyc:7.1f} cycles/MMA  {tops:7.1f} TOPS", flush=True)
