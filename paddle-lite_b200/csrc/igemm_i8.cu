@@ -42,7 +42,7 @@ static constexpr int kMaxAccStages = 4;   // TMEM accumulators in flight (512 co
 static constexpr int kMaxTmaStages = 12;  // TMA-fed modes
 static constexpr int kMaxStages = 28;  // thin mode: 4 KB A stages, the gather runs up to 4 tiles ahead
 static constexpr int kMaxResBufs = 6;   // depth of the TMA residual ring
-static constexpr int kMaxOutBufs = 4;   // output staging tiles (small tiles: the TMA store's read-out latency spans several tile periods)
+static constexpr int kMaxOutBufs = 8;   // output staging tiles (small tiles: the TMA store's read-out latency spans several tile periods)
 static constexpr int kMaxHaloBufs = 4;  // mode 3: input halo tiles in flight (p.halo_bufs of them)
 
 enum { EPI_GENERIC = 0, EPI_I8_RELU = 1, EPI_I8_SIGNED = 2, EPI_I8_RELU_RES = 3 };
@@ -98,6 +98,7 @@ struct IgemmParams {
   // fp32 out, act none / relu, no residual, 16-byte aligned rows: the generic instantiation converts and
   // stores its 16 columns inline (four 16-byte stores per thread) instead of calling store_group16
   int f32_fast;
+  int store_defer;  // store groups the store warp leaves in flight before it releases a staging buffer (0..4)
   const CUtensorMap* peer_maps;
   int n_peers;
   int thin_group;  // thin mode with a resident filter: a ring stage holds all k-blocks of a tile
@@ -343,14 +344,14 @@ __device__ __forceinline__ void issue_kblock_n(int ksteps, uint32_t d_tmem, uint
   else issue_kblock<1, CTA2>(d_tmem, da, db, idesc, fresh);
 }
 // all taps of a resident R x S filter against one halo tile: one straight run of MMAs
-template <int R_, int S_, int KS>
+template <int R_, int S_, int KS, bool CTA2 = false>
 __device__ __forceinline__ void issue_taps(uint32_t d_tmem, uint64_t da0, uint64_t db0, uint32_t idesc,
                                            uint32_t tap_step, uint32_t row_pitch, uint32_t b_step, bool fresh) {
 #pragma unroll
   for (int r = 0; r < R_; ++r)
 #pragma unroll
     for (int sx = 0; sx < S_; ++sx)
-      issue_kblock<KS>(d_tmem, da0 + (uint64_t)(r * row_pitch + sx * tap_step),
+      issue_kblock<KS, CTA2>(d_tmem, da0 + (uint64_t)(r * row_pitch + sx * tap_step),
                        db0 + (uint64_t)((r * S_ + sx) * b_step), idesc, fresh && r == 0 && sx == 0);
 }
 
@@ -418,7 +419,9 @@ igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
   constexpr int kBarTFull = 2 * kMaxStages, kBarTEmpty = kBarTFull + kMaxAccStages;
   constexpr int kBarRFull = kBarTEmpty + kMaxAccStages, kBarREmpty = kBarRFull + kMaxResBufs;
   constexpr int kBarAFull = kBarREmpty + kMaxResBufs, kBarAEmpty = kBarAFull + kMaxHaloBufs;
-  constexpr int kBarBRes = kBarAEmpty + kMaxHaloBufs, kBarStaged = kBarBRes + 1, kBarOFree = kBarStaged + kMaxResBufs;
+  // (`staged` serves the residual ring or the output staging buffers, whichever the launch uses)
+  constexpr int kMaxStaged = kMaxResBufs > kMaxOutBufs ? kMaxResBufs : kMaxOutBufs;
+  constexpr int kBarBRes = kBarAEmpty + kMaxHaloBufs, kBarStaged = kBarBRes + 1, kBarOFree = kBarStaged + kMaxStaged;
   __shared__ __align__(8) uint64_t bars[kBarOFree + kMaxOutBufs];
   __shared__ uint32_t tmem_base_slot;
 
@@ -489,7 +492,7 @@ igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
       // one arrival per epilogue warp of the tile's group (pairs: of both CTAs, on the leader's barrier)
       mbar_init(bar_tempty + 8 * s, (CTA2 ? 2 : 1) * (EW / p.epi_groups));
     }
-    for (int s = 0; s < kMaxResBufs; ++s) mbar_init(bar_staged + 8 * s, EW / p.epi_groups);
+    for (int s = 0; s < kMaxStaged; ++s) mbar_init(bar_staged + 8 * s, EW / p.epi_groups);
     for (int s = 0; s < kMaxOutBufs; ++s) mbar_init(bar_ofree + 8 * s, 1);
     for (int s = 0; s < kMaxHaloBufs; ++s) {
       mbar_init(bar_afull + 8 * s, 1);
@@ -567,11 +570,14 @@ igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
       if (hres) {
         // single N tile and the packed filter fits: every filter block is loaded exactly once
         // (channel block major, tap minor: the order the MMA loop walks them)
-        mbar_arrive_expect_tx(bar_bres, (uint32_t)num_kb * tx);
+        // (pairs: every CTA keeps ITS half of the filter rows; both halves complete on the leader's barrier)
+        if (!CTA2 || cta_rank == 0) mbar_arrive_expect_tx(bar_bres, (CTA2 ? 2u : 1u) * (uint32_t)num_kb * tx);
         uint32_t d = smem_b;
         for (int cbk = 0; cbk < cspan; cbk += BK)
-          for (int tap = 0, kc = cbk; tap < RS; ++tap, kc += cspan, d += b_bytes)
-            tma_load_2d(d, &tmap_b, bar_bres, kc, 0);
+          for (int tap = 0, kc = cbk; tap < RS; ++tap, kc += cspan, d += b_bytes) {
+            if (CTA2) tma_load_2d_2sm(d, &tmap_b, bar_bres + lead_delta, kc, cta_rank * (BN >> 1));
+            else tma_load_2d(d, &tmap_b, bar_bres, kc, 0);
+          }
       }
       pdl_wait();
       int ab = 0;
@@ -813,9 +819,9 @@ igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
           if (hres && RS == 9 && S == 3 && !skip_mma) {
             const uint64_t da0 = desc_hi | (uint64_t)t_lo, db0 = desc_hi | (uint64_t)b_lo;
             const uint32_t row_pitch = (uint32_t)(p.WP * p.BK) >> 4;
-            if (ksteps == 4) issue_taps<3, 3, 4>(d_tmem, da0, db0, idesc, tap_step, row_pitch, b_step, cb == 0);
-            else if (ksteps == 2) issue_taps<3, 3, 2>(d_tmem, da0, db0, idesc, tap_step, row_pitch, b_step, cb == 0);
-            else issue_taps<3, 3, 1>(d_tmem, da0, db0, idesc, tap_step, row_pitch, b_step, cb == 0);
+            if (ksteps == 4) issue_taps<3, 3, 4, CTA2>(d_tmem, da0, db0, idesc, tap_step, row_pitch, b_step, cb == 0);
+            else if (ksteps == 2) issue_taps<3, 3, 2, CTA2>(d_tmem, da0, db0, idesc, tap_step, row_pitch, b_step, cb == 0);
+            else issue_taps<3, 3, 1, CTA2>(d_tmem, da0, db0, idesc, tap_step, row_pitch, b_step, cb == 0);
             b_lo += 9 * b_step;
             umma_commit_t<CTA2>(bar_aempty + 8 * ab);
             if (cb == cblocks - 1) umma_commit_t<CTA2>(bar_tfull + 8 * as);
@@ -1028,8 +1034,19 @@ igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
       const bool halo = (TR == 0) && p.mode == 3;
       constexpr bool kInPlace = EPI == EPI_I8_RELU_RES;  // the output sits in the residual ring
       const int nbufs = kInPlace ? p.res_bufs : p.out_bufs;
-      int ob = 0;
+      // A buffer goes back to the epilogue (producer) only once its TMA store has READ it out; waiting for that
+      // after every tile made this one thread the tile clock of the narrow layers (~700-1000 cycles of read-out
+      // latency per tile).  Up to `defer` = nbufs - 2 store groups stay in flight instead: the buffer of tile
+      // i - defer is released after tile i's stores are committed, and two buffers always remain for the
+      // epilogue groups that are writing
+      const int defer = p.store_defer;
+      int ob = 0, rel = 0, pending = 0;
       uint32_t ophase = 0;
+      auto release = [&]() {
+        mbar_arrive(kInPlace ? bar_rempty + 8 * rel : bar_ofree + 8 * rel);
+        if (++rel == nbufs) rel = 0;
+        --pending;
+      };
       for (int tile = tile0; tile < num_tiles; tile += tstride) {
         int tn_, tm_;
         tile_mn<GROUPED, CTA2>(p, tile, tm_, tn_, cta_rank);
@@ -1055,11 +1072,22 @@ igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
             }
           }
           bulk_commit_group();
-          bulk_wait_group_read<0>();
         }
-        mbar_arrive(kInPlace ? bar_rempty + 8 * ob : bar_ofree + 8 * ob);
+        ++pending;
+        if (pending > defer) {
+          switch (defer) {
+            case 0: bulk_wait_group_read<0>(); break;
+            case 1: bulk_wait_group_read<1>(); break;
+            case 2: bulk_wait_group_read<2>(); break;
+            case 3: bulk_wait_group_read<3>(); break;
+            default: bulk_wait_group_read<4>(); break;
+          }
+          release();
+        }
         if (++ob == nbufs) { ob = 0; ophase ^= 1; }
       }
+      bulk_wait_group_read<0>();
+      while (pending > 0) release();
 #ifndef PL_EXP_NO_FINAL_WAIT
       bulk_wait_group<0>();
 #endif
@@ -1289,14 +1317,16 @@ igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
 // --------------------------------------------------------------------------
 // tensor-pipe micro-benchmark: back-to-back MMAs on resident smem operands
 // --------------------------------------------------------------------------
-__global__ void __launch_bounds__(128, 1) i8_mma_peak_kernel(int iters, int bn, int32_t* out, int row_bytes) {
+__global__ void __launch_bounds__(128, 1) i8_mma_peak_kernel(int iters, int bn, int32_t* out, int row_bytes,
+                                                             int a_shift_rows) {
   extern __shared__ uint8_t smem_raw[];
   __shared__ __align__(8) uint64_t bar;
   __shared__ uint32_t tmem_slot;
   const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
-  const uint32_t sa = base, sb = base + 128 * 128;
+  // (a_shift_rows: the A descriptor starts that many rows into the tile, as the halo-mode taps do)
+  const uint32_t sa = base + (uint32_t)(a_shift_rows * row_bytes), sb = base + 160 * 128;
   // deterministic small operands so the checksum is reproducible
-  for (uint32_t i = threadIdx.x; i < (128u + (uint32_t)bn) * 128u / 4u; i += blockDim.x)
+  for (uint32_t i = threadIdx.x; i < (160u + (uint32_t)bn) * 128u / 4u; i += blockDim.x)
     asm volatile("st.shared.b32 [%0], %1;" ::"r"(base + 4 * i), "r"(0x01010101u));
   fence_proxy_async();
   const int warp = threadIdx.x >> 5;
@@ -1680,7 +1710,6 @@ bool want_cta_pairs(const IgemmParams& p) {
   if (!legal) return false;
   if (knob >= 2) return true;
   const long long kred = (long long)p.num_kb * p.BK;
-  if (kred < env_int("PL_CTA2_MIN_K", 1024) || p.BN < env_int("PL_CTA2_MIN_BN", 128)) return false;
   // would the single-CTA launch keep its filter resident?  (same tests as below, on the single-CTA geometry)
   const long long fbytes = (long long)p.num_kb * p.b_stage_bytes;
   const int sms = driver().sm_count;
@@ -1688,7 +1717,18 @@ bool want_cta_pairs(const IgemmParams& p) {
   const int n_cover = p.n_tiles * p.BN;
   const long long budget = 219 * 1024 - ((n_cover <= 2048 ? n_cover : 512) * 8 + 1023) / 1024 * 1024;
   const long long staging = (long long)kBM * p.BN * (p.epi.residual ? 2 : 1);
-  if (p.mode == 3 && p.n_tiles == 1 && 2ll * p.a_halo_bytes + fbytes + staging <= budget) return false;
+  if (p.mode == 3 && p.n_tiles == 1) {
+    // halo launches with the whole filter in shared memory: a pair keeps HALF of it per CTA.  At N <= 128 the operand
+    // reads of the MMAs alone need ~122 B/cycle of the SM's 128 B/cycle shared-memory bandwidth (A 4 KB + B N x 32 B
+    // per 67-cycle MMA); in a pair a CTA serves its A and half of B (90 B/cycle), which leaves room for the TMA
+    // writes and the epilogue's staging traffic (profiles/r02_ncu_layers.md: pipe 95 % occupied, 49 % delivered)
+    const long long half = (long long)p.num_kb * (((long long)(p.BN / 2) * p.BK + 1023) / 1024 * 1024);
+    const int hres_knob = env_int("PL_CTA2_HRES", 1);  // 0 off, 1 BN >= 128, 2 BN >= 64
+    if (2ll * p.a_halo_bytes + half + staging <= budget && hres_knob > 0 && p.BN >= (hres_knob >= 2 ? 64 : 128))
+      return true;
+    if (2ll * p.a_halo_bytes + fbytes + staging <= budget) return false;
+  }
+  if (kred < env_int("PL_CTA2_MIN_K", 1024) || p.BN < env_int("PL_CTA2_MIN_BN", 128)) return false;
   if (p.mode != 3 && !p.mpair && tiles >= 2 * sms && p.n_tiles <= 16 && fbytes <= 64 * 1024 &&
       p.epi.out_dtype == PL_OUT_INT8)
     return false;
@@ -1764,7 +1804,7 @@ int launch_igemm(const CUtensorMap& ta, const CUtensorMap& tb_in, IgemmParams& p
   p.res_bufs = 2;
   int extra = 0;
   // halo mode with a single N tile keeps the whole packed filter in smem when it fits
-  bool hres = p.mode == 3 && p.n_tiles == 1 && !p.cta2 && env_int("PL_IGEMM_NO_HRES", 0) == 0 &&
+  bool hres = p.mode == 3 && p.n_tiles == 1 && env_int("PL_IGEMM_NO_HRES", 0) == 0 &&
               2 * (int)p.a_halo_bytes + p.num_kb * (int)p.b_stage_bytes <= budget;
   // TMA-fed GEMM / im2col modes: when the grid is a multiple of n_tiles every CTA keeps seeing the
   // same N tile, so that filter slice can stay in smem for the kernel's lifetime (the per-tile
@@ -1825,7 +1865,8 @@ int launch_igemm(const CUtensorMap& ta, const CUtensorMap& tb_in, IgemmParams& p
     } else {
       p.out_bufs = 1;
       // small tiles turn over faster than a TMA store is read out: up to 4 staging buffers
-      int want_out = env_int("PL_IGEMM_OUT_BUFS", tile <= 16 * 1024 ? 4 : 2);
+      // (narrow tiles: 8 buffers, 4 of them with their stores in flight -- stem 7x7 134.7 -> 118.6 us)
+      int want_out = env_int("PL_IGEMM_OUT_BUFS", tile <= 8 * 1024 ? 8 : (tile <= 16 * 1024 ? 4 : 2));
       if (want_out > kMaxOutBufs) want_out = kMaxOutBufs;
       while (p.out_bufs < want_out && left >= tile) {
         ++p.out_bufs;
@@ -1833,6 +1874,16 @@ int launch_igemm(const CUtensorMap& ta, const CUtensorMap& tb_in, IgemmParams& p
       }
     }
     extra = p.out_bufs * tile + (p.tma_res ? p.res_bufs * tile : 0);
+    {
+      const int nb = p.tma_res ? p.res_bufs : p.out_bufs;
+      // deferred release pays only with many small buffers; the in-place residual ring must hand its buffers back
+      // at once (its next residual load waits for them: 87 -> 182 us on r2 1x1 64->256+res with 4 in flight)
+      int d = env_int("PL_STORE_DEFER", -1);
+      if (d < 0) d = (!p.tma_res && nb >= 8) ? 4 : 0;
+      if (d > nb - 1) d = nb - 1;
+      if (d > 4) d = 4;
+      p.store_defer = d < 0 ? 0 : d;
+    }
   }
   p.epi_groups = 1;
   if (p.tma_out && p.sb_all) {
@@ -2586,12 +2637,14 @@ extern "C" int pl_gemm_i8(const int8_t* A, int lda, const int8_t* Bt, int ldb, v
 // same probe with the operand layout of a 32 / 64 / 128-byte K-block (SWIZZLE_32B / 64B / 128B
 // descriptors): one iteration issues row_bytes / 32 MMAs of 128 x bn x 32
 extern "C" int pl_i8_mma_probe(int ctas, int iters, int bn, int row_bytes, int32_t* out, pl_stream_t stream) {
-  if (ctas <= 0 || iters <= 0 || bn < 16 || bn > 256 || (bn % 16) || !out ||
-      (row_bytes != 32 && row_bytes != 64 && row_bytes != 128))
-    return PL_ERR_ARG;
-  const size_t smem = (size_t)(128 + bn) * 128 + 1024;
+  if (ctas <= 0 || iters <= 0 || bn < 16 || bn > 256 || (bn % 16) || !out) return PL_ERR_ARG;
+  // row_bytes may carry an A start shift in rows in bits 8.. (row_bytes | shift << 8): halo-mode tap starts
+  const int shift = row_bytes >> 8;
+  row_bytes &= 0xff;
+  if (shift < 0 || shift > 31 || (row_bytes != 32 && row_bytes != 64 && row_bytes != 128)) return PL_ERR_ARG;
+  const size_t smem = (size_t)(160 + bn) * 128 + 1024;
   PL_CUDA_OK(cudaFuncSetAttribute(i8_mma_peak_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  i8_mma_peak_kernel<<<ctas, 128, smem, (cudaStream_t)stream>>>(iters, bn, out, row_bytes);
+  i8_mma_peak_kernel<<<ctas, 128, smem, (cudaStream_t)stream>>>(iters, bn, out, row_bytes, shift);
   ++g_launches;
   return launch_status();
 }
@@ -2621,10 +2674,10 @@ extern "C" int pl_i8_mma_probe_pairs(int ctas, int iters, int bn, int row_bytes,
 
 extern "C" int pl_i8_mma_peak(int ctas, int iters, int bn, int32_t* out, pl_stream_t stream) {
   if (ctas <= 0 || iters <= 0 || bn < 16 || bn > 256 || (bn % 16) || !out) return PL_ERR_ARG;
-  const size_t smem = (size_t)(128 + bn) * 128 + 1024;
+  const size_t smem = (size_t)(160 + bn) * 128 + 1024;
   PL_CUDA_OK(cudaFuncSetAttribute(i8_mma_peak_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                   (int)smem));
-  i8_mma_peak_kernel<<<ctas, 128, smem, (cudaStream_t)stream>>>(iters, bn, out, 128);
+  i8_mma_peak_kernel<<<ctas, 128, smem, (cudaStream_t)stream>>>(iters, bn, out, 128, 0);
   ++g_launches;
   return launch_status();
 }
