@@ -1723,7 +1723,7 @@ bool want_cta_pairs(const IgemmParams& p) {
     // per 67-cycle MMA); in a pair a CTA serves its A and half of B (90 B/cycle), which leaves room for the TMA
     // writes and the epilogue's staging traffic (profiles/r02_ncu_layers.md: pipe 95 % occupied, 49 % delivered)
     const long long half = (long long)p.num_kb * (((long long)(p.BN / 2) * p.BK + 1023) / 1024 * 1024);
-    const int hres_knob = env_int("PL_CTA2_HRES", 1);  // 0 off, 1 BN >= 128, 2 BN >= 64
+    const int hres_knob = env_int("PL_CTA2_HRES", 0);  // 0 off (default: measured neutral), 1 BN >= 128, 2 BN >= 64
     if (2ll * p.a_halo_bytes + half + staging <= budget && hres_knob > 0 && p.BN >= (hres_knob >= 2 ? 64 : 128))
       return true;
     if (2ll * p.a_halo_bytes + fbytes + staging <= budget) return false;

@@ -153,3 +153,18 @@ def test_conv_pairs_fused_residual(pl, knobs, case):
     plan = pl.last_igemm_plan()
     assert plan["cta_pairs"] == 1 and plan["epi"] == 3, plan
     assert np.array_equal(got, want)
+
+
+def test_halo_pairs_with_resident_half_filter(pl, knobs):
+    """PL_CTA2_HRES: a halo launch whose filter fits in shared memory runs as pairs, each CTA keeping half of it"""
+    knobs(PL_CTA2_HRES=2, PL_FORCE_BN=128)
+    geo = (3, 28, 28, 128, 128, 3, 3, 1, (1, 1, 1, 1), 1)
+    N, H, W, Cc, K, R, S, st, pads, dl = geo
+    x, w, ws, bias, si, so = conv_inputs(geo, 47)
+    sf, bf, _ = orc.fold_scales(ws, K, si, so, orc.OUT_INT8, bias, orc.ACT_RELU, 0.0)
+    want = orc.conv2d(x, w, sf, bf, (st, st), pads, (dl, dl), 1, orc.ACT_RELU, 0.0, orc.OUT_INT8)
+    got = host(pl.conv2d(dev(x), pl.pack_conv_weight(dev(w)), K, R, S, dev(sf), dev(bf), (st, st), pads, (dl, dl),
+                         pl.ACT_RELU, 0.0, pl.OUT_INT8, Cc=Cc))
+    plan = pl.last_igemm_plan()
+    assert plan["cta_pairs"] == 1 and plan["filter_resident"] == 1 and plan["mode"] == 3, plan
+    assert np.array_equal(got, want)
