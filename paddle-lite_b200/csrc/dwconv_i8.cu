@@ -14,6 +14,8 @@
 #include <cstdlib>
 #include <cudaTypedefs.h>
 
+#include <type_traits>
+
 #include "common.cuh"
 
 namespace pl {
@@ -520,7 +522,10 @@ __device__ __forceinline__ void dw_tile_coords(const DwParams& p, const DwTile& 
   n = (int)u;
 }
 
-static constexpr int kDwConsumerWarps = 7;
+#ifndef PL_DW_WARPS
+#define PL_DW_WARPS 7
+#endif
+static constexpr int kDwConsumerWarps = PL_DW_WARPS;
 static constexpr int kDwThreads = 32 * (kDwConsumerWarps + 1);  // + the TMA producer warp
 // (8 warps = 2 per scheduler: two CTAs of up to 128 registers per thread fit the 16 K registers of an SMSP;
 // 9 warps did not -- ncu launch__occupancy_limit_registers 1)
@@ -528,7 +533,9 @@ static constexpr int kDwThreads = 32 * (kDwConsumerWarps + 1);  // + the TMA pro
 #ifndef PL_DW_CTAS
 #define PL_DW_CTAS 2  // resident CTAs per SM the register budget is cut for (experiment: 3 -> 80 registers)
 #endif
-template <int STRIDE, bool FAST>
+// CCW > 0: the channel chunk (in words) is a compile-time constant, so the six (five) window loads of a row take
+// immediate offsets
+template <int STRIDE, bool FAST, int CCW = 0>
 __global__ void __launch_bounds__(kDwThreads, PL_DW_CTAS)
 dw3x3_tma_kernel(const __grid_constant__ CUtensorMap tx, const DwParams p, const DwTile t) {
   extern __shared__ __align__(128) uint8_t dw_smem[];
@@ -592,7 +599,7 @@ dw3x3_tma_kernel(const __grid_constant__ CUtensorMap tx, const DwParams p, const
   }
   const uint32_t ldyw = (uint32_t)p.ldy >> 2;  // FAST launches: int8 output addressed in 32-bit words
   const uint32_t hi_bits = p.hi_bits;
-  const uint32_t colw = (uint32_t)t.CC / 4u, roww = (uint32_t)t.BW * colw;
+  const uint32_t colw = CCW > 0 ? (uint32_t)CCW : (uint32_t)t.CC / 4u, roww = (uint32_t)t.BW * colw;
   // word offset of this thread's window inside a stage: first row of its group, first column of its strip
   const uint32_t win_off = (uint32_t)grp * (uint32_t)(t.RG * STRIDE) * roww + strip * 4u * colw + (uint32_t)quad;
   uint32_t it = 0;
@@ -611,6 +618,10 @@ dw3x3_tma_kernel(const __grid_constant__ CUtensorMap tx, const DwParams p, const
       const uint32_t pix0 = (uint32_t)((n * p.P + pg0) * p.Q + oq0);
       // whole strip inside the image: no per-pixel column checks
       const bool full_strip = oq0 + (STRIDE == 1 ? 4 : 2) <= p.Q;
+      // whole strips take a copy of the loop without per-pixel store predicates (most strips are whole: the
+      // predicated copy costs ~12 instructions per output row in predicate and descriptor set-up)
+      auto run_tile = [&](auto full_tag) {
+      constexpr bool FULLS = decltype(full_tag)::value;
       // 32-bit word offsets from the (uniform) base of y: one integer add per pixel instead of a 64-bit pointer
       // chain (the host takes this kernel only when the output has fewer than 2^32 words)
       uint32_t* const ybase = reinterpret_cast<uint32_t*>(p.y);
@@ -618,7 +629,7 @@ dw3x3_tma_kernel(const __grid_constant__ CUtensorMap tx, const DwParams p, const
       const uint32_t orow_step = (uint32_t)p.Q * ldyw;
       auto finish = [&](const int (&acc)[4], int q, uint32_t pix) {
         if (FAST) {
-          dw_finish4_ptr(acc, sc, bs, hi_bits, ybase + (orow + (uint32_t)q * ldyw), full_strip || oq0 + q < p.Q);
+          dw_finish4_ptr(acc, sc, bs, hi_bits, ybase + (orow + (uint32_t)q * ldyw), FULLS || oq0 + q < p.Q);
         } else {
           if (oq0 + q < p.Q) dw_finish4<false>(p, acc, sc, bs, p.hi_bits, pix + q, c0);
         }
@@ -726,6 +737,10 @@ dw3x3_tma_kernel(const __grid_constant__ CUtensorMap tx, const DwParams p, const
           }
         }
       }
+    
+      };
+      if (full_strip) run_tile(std::true_type{});
+      else run_tile(std::false_type{});
     }
     __syncwarp();
     if ((threadIdx.x & 31) == 0) mbar_arrive(smem_u32(&empty_bar[slot]));  // this warp is done with the slot
@@ -911,7 +926,7 @@ extern "C" int pl_dwconv2d_i8_nhwc(const int8_t* x, const int8_t* w_crs, void* y
         t.groups = items_max / items;
         if (t.groups > 4) t.groups = 4;
         if (t.groups < 1) t.groups = 1;
-        const int budget = (PL_DW_CTAS == 2 ? 36 : 32) * 1024;
+        const int budget = (PL_DW_CTAS == 2 ? 36 : (PL_DW_CTAS == 1 ? 48 : 32)) * 1024;
         int tr = s1 ? budget / rowbytes - 2 : (budget / rowbytes - 1) / 2;
         if (tr > P) tr = P;
         if (tr > 32) tr = 32;
@@ -926,7 +941,7 @@ extern "C" int pl_dwconv2d_i8_nhwc(const int8_t* x, const int8_t* w_crs, void* y
         const long long tiles = tiles_for(tr);
         t.stage_bytes = (uint32_t)(rowbytes * t.BH);
         t.stage_pitch = (t.stage_bytes + 127u) / 128u * 128u;
-        int stages = (int)(((PL_DW_CTAS == 2 ? 108u : 72u) * 1024u) / t.stage_pitch);
+        int stages = (int)(((PL_DW_CTAS == 2 ? 108u : (PL_DW_CTAS == 1 ? 200u : 72u)) * 1024u) / t.stage_pitch);
         if (stages > kDwStagesMax) stages = kDwStagesMax;
         ok = tiles < (1ll << 31) && t.BH <= 256 && stages >= 2 &&
              (long long)d->N * P * Q * (d->ldy / 4) < (1ll << 32);  // 32-bit output word offsets
@@ -948,12 +963,25 @@ extern "C" int pl_dwconv2d_i8_nhwc(const int8_t* x, const int8_t* w_crs, void* y
             grid -= grid % t.ctiles;
             if (grid < t.ctiles) grid = t.ctiles;
             auto go = [&](auto kern) {
-              cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(112 * 1024));
+              cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                   (int)((PL_DW_CTAS == 1 ? 210 : 112) * 1024));
               cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
               launch_pdl(kern, dim3((unsigned)grid), dim3(kDwThreads), smem, st, tx, p, t);
             };
-            if (s1) { if (fe) go(dw3x3_tma_kernel<1, true>); else go(dw3x3_tma_kernel<1, false>); }
-            else    { if (fe) go(dw3x3_tma_kernel<2, true>); else go(dw3x3_tma_kernel<2, false>); }
+            const int ccw = t.CC / 4;
+            if (s1) {
+              if (!fe) go(dw3x3_tma_kernel<1, false>);
+              else if (ccw == 32) go(dw3x3_tma_kernel<1, true, 32>);
+              else if (ccw == 16) go(dw3x3_tma_kernel<1, true, 16>);
+              else if (ccw == 8) go(dw3x3_tma_kernel<1, true, 8>);
+              else go(dw3x3_tma_kernel<1, true>);
+            } else {
+              if (!fe) go(dw3x3_tma_kernel<2, false>);
+              else if (ccw == 32) go(dw3x3_tma_kernel<2, true, 32>);
+              else if (ccw == 16) go(dw3x3_tma_kernel<2, true, 16>);
+              else if (ccw == 8) go(dw3x3_tma_kernel<2, true, 8>);
+              else go(dw3x3_tma_kernel<2, true>);
+            }
             ++g_launches;
             return launch_status();
           }
