@@ -194,6 +194,32 @@ def run_reference(args):
 # ----------------------------------------------------------------------------
 # B200 arm
 # ----------------------------------------------------------------------------
+def bind_to_gpu_numa_node(local_rank):
+    """Pin this rank (and so its pinned host buffers, first touched after this call) to the CPUs of the NUMA node its GPU
+    hangs off: with 8 ranks feeding 8 GPUs the H2D copies then cross no socket link.  Best effort: returns the node
+    or None when the topology files are not there."""
+    try:
+        import torch
+        bus = torch.cuda.get_device_properties(local_rank).pci_bus_id
+        dom = torch.cuda.get_device_properties(local_rank).pci_domain_id
+        dev = torch.cuda.get_device_properties(local_rank).pci_device_id
+        path = f"/sys/bus/pci/devices/{dom:04x}:{bus:02x}:{dev:02x}.0/numa_node"
+        node = int(open(path).read().strip())
+        if node < 0:
+            return None
+        cpus = set()
+        for part in open(f"/sys/devices/system/node/node{node}/cpulist").read().strip().split(","):
+            lo, _, hi = part.partition("-")
+            cpus.update(range(int(lo), int(hi or lo) + 1))
+        cpus &= os.sched_getaffinity(0)
+        if cpus:
+            os.sched_setaffinity(0, cpus)
+            return node
+    except Exception:
+        pass
+    return None
+
+
 class Ctx:
     """Process-wide plumbing: rank, device, barrier, max-over-ranks."""
 
@@ -210,6 +236,7 @@ class Ctx:
         assert torch.cuda.is_available(), "bench.py --impl b200 needs a GPU (there is no CPU fallback)"
         torch.cuda.set_device(self.local)
         self.dev = f"cuda:{self.local}"
+        self.numa = bind_to_gpu_numa_node(self.local) if self.world > 1 else None
         if self.world > 1:
             dist.init_process_group("nccl", device_id=torch.device("cuda", self.local))
         self.pkg = ge.load_package()
@@ -720,6 +747,7 @@ def run_b200(args):
             "scaling": "weak", "vs_baseline": None, "dtype": "int8", "data": "synthetic",
             "config": {"workload": workload_name(args.net, batch, H), "global_batch": batch * world,
                        "parallelism": f"batch-sharded x{world}, no collective", "cuda_graph": True,
+                       "numa_node_of_rank0": ctx.numa,
                        "l2": f"per-step working set ({(ctx.nets.program_bytes(prog)[0] * batch + ctx.nets.program_bytes(prog)[1]) / 1e6:.0f} MB of activations + weights) "
                              "exceeds the 126 MB L2; consecutive steps replay the whole network, no flush needed",
                        "gmac_per_image": sum(macs.values()) / 1e9},
