@@ -680,10 +680,24 @@ def bench_nsplit(ctx):
         fused = op.fused(A)
         ctx.barrier()
         ok_fused = bool(torch.equal(fused, single))
-        ok = ctx.min_over_ranks(float(ok_nccl and ok_fused))[0] == 1.0
+        # the same through the NVSwitch multicast address: one multimem.st stream instead of G - 1 peer stores
+        ms_mcast, ok_mcast = None, True
+        try:
+            if op.mcast_supported():
+                for _ in range(3):
+                    fused = op.fused_mcast(A)
+                ms_mcast = ctx.timed(lambda: op.fused_mcast(A), iters) / iters
+                fused = op.fused_mcast(A)
+                ctx.barrier()
+                ok_mcast = bool(torch.equal(fused, single))
+        except Exception as exc:  # pragma: no cover - depends on the box
+            sys.stderr.write(f"[bench] multicast N-split unavailable: {exc!r}\n")
+            ms_mcast = None
+        ok = ctx.min_over_ranks(float(ok_nccl and ok_fused and ok_mcast))[0] == 1.0
         ops = 2.0 * M * N * K
+        best = min(v for v in (ms_fused, ms_mcast) if v is not None)
         out.append({"M": M, "N": N, "K": K, "n_gpus": ctx.world, "ms_local": ms_local, "ms_nccl_gather": ms_nccl,
-                    "ms_fused_peer": ms_fused, "tops_fused": ops / ms_fused / 1e9,
+                    "ms_fused_peer": ms_fused, "ms_fused_multicast": ms_mcast, "tops_fused": ops / best / 1e9,
                     "bit_exact_vs_single_gpu": ok})
         del op, single, A, B, fused, gathered
         torch.cuda.empty_cache()

@@ -317,6 +317,15 @@ int pl_softmax_f32_nhwc(const float* x, float* y, int64_t pixels, int C, int ldx
 int pl_scale_f32(const float* x, float* y, int64_t n, float scale, float bias, int bias_after_scale,
                  pl_stream_t stream);
 
+/* N-split GEMM fused with its all-gather through NVSwitch multicast (NVLS): every staged int8 output tile is copied
+ * with multimem.st to `C_mc`, the MULTICAST address of this rank's column block; the switch writes it into the
+ * same block of every rank bound to the multicast object (this one included).  One copy of the block leaves the
+ * GPU instead of one per peer.  `C` is the rank's own (unicast) view of the block: used for the alignment rules
+ * only, never written by this call.  int8 output, no fused residual.  Replaces, like pl_gemm_i8_peers, the
+ * all-gather a column-parallel fc would run after lite/kernels/arm/fc_compute.cc:117-164. */
+int pl_gemm_i8_mcast(const int8_t* A, int lda, const int8_t* Bt, int ldb, void* C, void* C_mc, int ldc, int M, int N,
+                     int K, const pl_epilogue* e, pl_stream_t stream);
+
 /* ---- introspection ---------------------------------------------------------- */
 /* number of kernels this library has launched in this process (bench.py's
  * gpu_launches claim) */

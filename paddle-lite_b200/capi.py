@@ -233,6 +233,18 @@ def gemm_peers(A, Bt, scale, bias, y, peer_ptrs, maps_dev, act=ACT_NONE, act_arg
     return y
 
 
+def gemm_mcast(A, Bt, scale, bias, y, mc_ptr, act=ACT_NONE, act_arg=0.0, rnd=ROUND_ARM, N=None, K=None):
+    """pl_gemm_i8_mcast: int8-out GEMM whose tiles leave through the NVSwitch multicast address `mc_ptr` (an int:
+    the multicast VA of the column block `y` views in this rank's copy of the full result)."""
+    M = A.shape[0]
+    K = A.shape[1] if K is None else K
+    N = Bt.shape[0] if N is None else N
+    e = make_epilogue(scale, bias, act, act_arg, OUT_INT8, rnd)
+    _check(lib().pl_gemm_i8_mcast(_ptr(A), A.stride(0), _ptr(Bt), Bt.stride(0), _ptr(y), C.c_void_p(int(mc_ptr)),
+                                  y.stride(0), M, N, K, C.byref(e), _stream()), "pl_gemm_i8_mcast")
+    return y
+
+
 def gemm_peers_prepare(y, peer_ptrs, maps_dev, scale, bias, M, N, K, act=ACT_NONE, act_arg=0.0, rnd=ROUND_ARM):
     """pl_gemm_i8_peers_prepare: one-off synchronous upload of the peer tensor maps; later gemm_peers calls pass
     peer_ptrs = len(peer_ptrs) (an int) and are a single kernel launch."""

@@ -485,6 +485,14 @@ __device__ __forceinline__ void umma_commit_2sm(uint32_t bar) {
       : "memory");
 }
 
+// one 16-byte store through an NVSwitch multicast address: the switch replicates it into the same offset of every
+// GPU bound to the multicast object (NVLS).  The .f32 type only names the vector layout: the bits are copied.
+__device__ __forceinline__ void multimem_st_v4(void* mc_addr, uint4 v) {
+  asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(mc_addr), "r"(v.x), "r"(v.y),
+               "r"(v.z), "r"(v.w)
+               : "memory");
+}
+
 // SM100 shared-memory matrix descriptor for a K-major operand tile whose rows
 // are `row_bytes` (32 / 64 / 128) wide and swizzled with the matching TMA
 // swizzle mode.  Fields (cute/arch/mma_sm100_desc.hpp): start>>4 [0,14),

@@ -101,6 +101,10 @@ struct IgemmParams {
   int store_defer;  // store groups the store warp leaves in flight before it releases a staging buffer (0..4)
   const CUtensorMap* peer_maps;
   int n_peers;
+  // N-split GEMM fused with its all-gather through NVSwitch multicast: the store warp copies every staged tile to
+  // the MULTICAST address of this rank's column block with multimem.st -- one store leaves the GPU, the switch
+  // writes it into every rank's result (own included): 1/(G-1) of the peer-store variant's NVLink egress
+  int8_t* mc_out;
   int thin_group;  // thin mode with a resident filter: a ring stage holds all k-blocks of a tile
   int thin_shift;  // window starts `thin_shift` (0 / 1) words left of the first tap: the spare word of the
                    // SW-word window leads, which makes the start even for odd left pads at stride 2
@@ -1029,7 +1033,42 @@ igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
     // One elected lane turns every staged tile into TMA stores.  The epilogue warps never
     // meet at a block barrier: they hand a staging buffer over through `staged` (one arrival
     // per warp) and get it back through `ofree` once the store has read it out.
-    if (EPI != EPI_GENERIC && p.tma_out && elect_one()) {
+    if (EPI != EPI_GENERIC && p.tma_out && p.mc_out != nullptr) {
+      // multicast variant (mode 0 GEMMs only): the whole warp copies the swizzled staging panels row by row,
+      // lane = (row & 3, 16-byte chunk); rows >= M and columns >= Nout are dropped here (no hardware clipping)
+      pdl_wait();
+      const int nbufs = p.out_bufs;
+      int ob = 0;
+      uint32_t ophase = 0;
+      const uint32_t chunk = (uint32_t)lane & 7u, rsub = (uint32_t)lane >> 3;
+      for (int tile = tile0; tile < num_tiles; tile += tstride) {
+        int tn_, tm_;
+        tile_mn<GROUPED, CTA2>(p, tile, tm_, tn_, cta_rank);
+        const int n0 = tn_ * p.BN;
+        const uint32_t out_tile = smem_out + (uint32_t)ob * obuf_bytes;
+        if (lane == 0) WAIT(bar_staged + 8 * ob, ophase);
+        __syncwarp();
+        for (int sub = 0; sub <= p.mpair; ++sub) {
+          const long long mrow = (long long)((tm_ << p.mpair) + sub) * kBM;
+          for (int j = 0; j < p.panels; ++j) {
+            const uint32_t panel = out_tile + (uint32_t)sub * tile_bytes + (uint32_t)(j * kBM * p.PW);
+            const int col = n0 + j * p.PW + (int)chunk * 16;
+            const uint32_t cpr = (uint32_t)p.PW >> 4;  // 16-byte chunks per panel row
+            if (chunk < cpr && col < p.Nout) {
+              for (uint32_t r = rsub; r < (uint32_t)kBM; r += 4) {
+                if (mrow + r >= p.M) break;
+                const uint32_t swx = ((r * (uint32_t)p.PW) >> 7) & p.swz_mask;  // as the epilogue staged it
+                const uint4 v = ld_shared_v4(panel + r * (uint32_t)p.PW + ((chunk ^ swx) << 4));
+                multimem_st_v4(p.mc_out + (mrow + r) * (long long)p.ldy + col, v);
+              }
+            }
+          }
+        }
+        __syncwarp();
+        if (lane == 0) mbar_arrive(bar_ofree + 8 * ob);
+        if (++ob == nbufs) { ob = 0; ophase ^= 1; }
+      }
+    } else if (EPI != EPI_GENERIC && p.tma_out && elect_one()) {
       pdl_wait();
       const bool halo = (TR == 0) && p.mode == 3;
       constexpr bool kInPlace = EPI == EPI_I8_RELU_RES;  // the output sits in the residual ring
@@ -1900,7 +1939,7 @@ int launch_igemm(const CUtensorMap& ta, const CUtensorMap& tb_in, IgemmParams& p
     p.epi_groups = g;
   }
   if (p.s2d && !hres) return PL_ERR_UNSUPPORTED;
-  if (p.n_peers > 0 && !p.tma_out) return PL_ERR_UNSUPPORTED;
+  if ((p.n_peers > 0 || p.mc_out) && !p.tma_out) return PL_ERR_UNSUPPORTED;
   if (!p.tma_out) bres01 = false;
   {
     // measured (tools/gemm_sweep.py): bands of 16 rows for 8192^3 / 16384^3 (2621 -> 2797, 2531 -> 2880 TOP/s),
@@ -2515,6 +2554,38 @@ extern "C" int pl_gemm_i8_peers(const int8_t* A, int lda, const int8_t* Bt, int 
   }
   const BSpec bs{Bt, (uint64_t)K, (uint64_t)N, (uint64_t)ldb};
   return launch_igemm(ta, tb, p, stream, &bs);
+}
+
+// N-split GEMM whose output tiles leave through an NVSwitch multicast address (IgemmParams::mc_out): C is this
+// rank's own view of its column block (alignment checks, never written by this call), C_mc the multicast address
+// of the same block -- every rank bound to the multicast object, this one included, receives the tiles
+extern "C" int pl_gemm_i8_mcast(const int8_t* A, int lda, const int8_t* Bt, int ldb, void* C, void* C_mc, int ldc,
+                                int M, int N, int K, const pl_epilogue* e, pl_stream_t stream) {
+  if (!A || !Bt || !C || !C_mc || M <= 0 || N <= 0 || K <= 0 || lda < K || ldb < K || ldc < N) return PL_ERR_ARG;
+  int rc = check_epi(e);
+  if (rc) return rc;
+  if (!driver().ok) return PL_ERR_DRIVER;
+  if (driver().cc_major != 10) return PL_ERR_DEVICE;
+  if ((reinterpret_cast<uintptr_t>(A) & 15) || (reinterpret_cast<uintptr_t>(Bt) & 15) || (lda % 16) || (ldb % 16) ||
+      (reinterpret_cast<uintptr_t>(C_mc) & 15) || (ldc % 16))
+    return PL_ERR_ALIGN;
+  if (e->out_dtype != PL_OUT_INT8 || e->residual) return PL_ERR_UNSUPPORTED;
+  IgemmParams p{};
+  p.BK = pl_conv_block_k(K);
+  p.mode = 0;
+  rc = common_setup(p, M, N, C, ldc, e, K, 1);
+  if (rc) return rc;
+  if (!p.vec_ok) return PL_ERR_UNSUPPORTED;
+  maybe_enable_mpair(p, e, K, true);
+  CUtensorMap ta, tb;
+  rc = encode_2d(&ta, A, (uint64_t)K, (uint64_t)M, (uint64_t)lda, p.BK, kBM << p.mpair);
+  if (rc) return rc;
+  rc = encode_2d(&tb, Bt, (uint64_t)K, (uint64_t)N, (uint64_t)ldb, p.BK, p.BN);
+  if (rc) return rc;
+  p.mc_out = reinterpret_cast<int8_t*>(C_mc);
+  const BSpec bs{Bt, (uint64_t)K, (uint64_t)N, (uint64_t)ldb};
+  rc = launch_igemm(ta, tb, p, stream, &bs);
+  return rc;
 }
 
 // One-off set-up of the peer tensor maps for launches with C_peers == NULL: same tile geometry as the launch

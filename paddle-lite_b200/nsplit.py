@@ -130,6 +130,29 @@ class NSplitGemm:
         self._full = self._fulls[0]
         return self._fulls[0]
 
+    def mcast_supported(self):
+        """NVSwitch multicast (NVLS) is available for this group's symmetric memory"""
+        if getattr(self, "_fM", None) is None:
+            return False
+        return all(int(h.multicast_ptr) != 0 for h in self._hdls)
+
+    def fused_mcast(self, A_dev):
+        """Like fused(), but every staged tile leaves the GPU ONCE, through the multicast address of the result
+        buffer (multimem.st in the GEMM's store warp): the switch replicates it into all ranks' results, own
+        included.  NVLink egress per GPU is the size of its column block, not (G - 1) times that."""
+        M = A_dev.shape[0]
+        if getattr(self, "_fM", None) != M:
+            self.fused_setup(M)
+        t = self._turn
+        self._turn ^= 1
+        mc = int(self._hdls[t].multicast_ptr)
+        if mc == 0:
+            raise RuntimeError("this group's symmetric memory has no multicast mapping (no NVLS)")
+        self.pl.gemm_mcast(A_dev, self.bt, self.scale, self.bias, self._ys[t], mc + self.rank * self.per,
+                           self.act, self.act_arg, N=self.per, K=self.K)
+        self._hdls[t].barrier()
+        return self._fulls[t][:, :self.N]
+
     def fused(self, A_dev):
         """C[M, N] on every rank: each rank's GEMM kernel TMA-stores its output tiles into its own result
         buffer and straight into the peers' (NVLink), overlapped with the mainloop; one device-side barrier

@@ -53,13 +53,25 @@ def _worker(rank, world, port, M, K, N, out_fp32, q):
                 torch.cuda.synchronize()
                 ok = ok and np.array_equal(fused.cpu().numpy(), want)
                 dist.barrier()
-        q.put((rank, bool(ok), got.shape))
+            # the same through the NVSwitch multicast address (multimem.st in the store warp), where the box has NVLS
+            mc = "skipped"
+            if g.mcast_supported():
+                mc = True
+                for _ in range(2):
+                    fused = g.fused_mcast(Ad)
+                    torch.cuda.synchronize()
+                    mc = mc and np.array_equal(fused.cpu().numpy(), want)
+                    dist.barrier()
+                ok = ok and mc
+            got = (got.shape, mc)
+        q.put((rank, bool(ok), got if isinstance(got, tuple) else got.shape))
     finally:
         dist.destroy_process_group()
 
 
 @pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs 2 GPUs")
-@pytest.mark.parametrize("M,K,N,out_fp32", [(64, 512, 1000, False), (256, 1024, 4096, True), (7, 100, 33, False)])
+@pytest.mark.parametrize("M,K,N,out_fp32", [(64, 512, 1000, False), (256, 1024, 4096, True), (7, 100, 33, False),
+                                            (1000, 2048, 1536, False)])
 def test_nsplit_gemm_nccl(M, K, N, out_fp32):
     import torch.multiprocessing as mp
     world = 2
