@@ -693,12 +693,34 @@ def bench_nsplit(ctx):
         except Exception as exc:  # pragma: no cover - depends on the box
             sys.stderr.write(f"[bench] multicast N-split unavailable: {exc!r}\n")
             ms_mcast = None
+        # fp32 results: NCCL gather against multicast stores from the epilogue registers
+        f32 = {}
+        try:
+            opf = ns.NSplitGemm(pl, B.numpy(), scale.numpy(), bias.numpy(), pl.OUT_FP32)
+            single_f = pl.gemm(A, B.t().contiguous().to(ctx.dev), scale.to(ctx.dev), bias.to(ctx.dev), out=pl.OUT_FP32)
+            for _ in range(2):
+                opf.local(A)
+            f32["ms_local"] = ctx.timed(lambda: opf.local(A), iters) / iters
+            for _ in range(2):
+                opf(A)
+            f32["ms_nccl_gather"] = ctx.timed(lambda: opf(A), iters) / iters
+            opf.fused_setup(M)
+            if opf.mcast_supported():
+                for _ in range(2):
+                    opf.fused_mcast(A)
+                f32["ms_fused_multicast"] = ctx.timed(lambda: opf.fused_mcast(A), iters) / iters
+                r_ = opf.fused_mcast(A)
+                ctx.barrier()
+                f32["bit_exact_vs_single_gpu"] = ctx.min_over_ranks(float(torch.equal(r_, single_f)))[0] == 1.0
+            del opf, single_f
+        except Exception as exc:  # pragma: no cover
+            f32["error"] = repr(exc)
         ok = ctx.min_over_ranks(float(ok_nccl and ok_fused and ok_mcast))[0] == 1.0
         ops = 2.0 * M * N * K
         best = min(v for v in (ms_fused, ms_mcast) if v is not None)
         out.append({"M": M, "N": N, "K": K, "n_gpus": ctx.world, "ms_local": ms_local, "ms_nccl_gather": ms_nccl,
                     "ms_fused_peer": ms_fused, "ms_fused_multicast": ms_mcast, "tops_fused": ops / best / 1e9,
-                    "bit_exact_vs_single_gpu": ok})
+                    "bit_exact_vs_single_gpu": ok, "fp32_out": f32})
         del op, single, A, B, fused, gathered
         torch.cuda.empty_cache()
     return out

@@ -326,6 +326,12 @@ int pl_scale_f32(const float* x, float* y, int64_t n, float scale, float bias, i
 int pl_gemm_i8_mcast(const int8_t* A, int lda, const int8_t* Bt, int ldb, void* C, void* C_mc, int ldc, int M, int N,
                      int K, const pl_epilogue* e, pl_stream_t stream);
 
+/* rows x row_bytes block of device memory -> the NVSwitch multicast address of the same block (coalesced
+ * multimem.st): the all-gather step for N-split results that have no staged epilogue (fp32 out): every rank
+ * broadcasts its own column block after a plain pl_gemm_i8.  16-byte alignment of both bases, pitches and the row. */
+int pl_mcast_copy_2d(const void* src, int64_t ld_src_bytes, void* dst_mc, int64_t ld_dst_bytes, int64_t rows,
+                     int64_t row_bytes, pl_stream_t stream);
+
 /* ---- introspection ---------------------------------------------------------- */
 /* number of kernels this library has launched in this process (bench.py's
  * gpu_launches claim) */

@@ -233,16 +233,26 @@ def gemm_peers(A, Bt, scale, bias, y, peer_ptrs, maps_dev, act=ACT_NONE, act_arg
     return y
 
 
-def gemm_mcast(A, Bt, scale, bias, y, mc_ptr, act=ACT_NONE, act_arg=0.0, rnd=ROUND_ARM, N=None, K=None):
-    """pl_gemm_i8_mcast: int8-out GEMM whose tiles leave through the NVSwitch multicast address `mc_ptr` (an int:
-    the multicast VA of the column block `y` views in this rank's copy of the full result)."""
+def gemm_mcast(A, Bt, scale, bias, y, mc_ptr, act=ACT_NONE, act_arg=0.0, rnd=ROUND_ARM, N=None, K=None, out=OUT_INT8):
+    """pl_gemm_i8_mcast: GEMM (int8 or fp32 out) whose tiles leave through the NVSwitch multicast address `mc_ptr`
+    (an int: the multicast VA of the column block `y` views in this rank's copy of the full result)."""
     M = A.shape[0]
     K = A.shape[1] if K is None else K
     N = Bt.shape[0] if N is None else N
-    e = make_epilogue(scale, bias, act, act_arg, OUT_INT8, rnd)
+    e = make_epilogue(scale, bias, act, act_arg, out, rnd)
     _check(lib().pl_gemm_i8_mcast(_ptr(A), A.stride(0), _ptr(Bt), Bt.stride(0), _ptr(y), C.c_void_p(int(mc_ptr)),
                                   y.stride(0), M, N, K, C.byref(e), _stream()), "pl_gemm_i8_mcast")
     return y
+
+
+def mcast_copy_2d(src, mc_ptr, ld_dst_bytes):
+    """pl_mcast_copy_2d: broadcast the 2-D device tensor `src` (a strided view is fine) to the multicast address
+    `mc_ptr` (int) with row pitch `ld_dst_bytes`."""
+    rows, cols = src.shape
+    esz = src.element_size()
+    _check(lib().pl_mcast_copy_2d(_ptr(src), C.c_int64(src.stride(0) * esz), C.c_void_p(int(mc_ptr)),
+                                  C.c_int64(ld_dst_bytes), C.c_int64(rows), C.c_int64(cols * esz), _stream()),
+           "pl_mcast_copy_2d")
 
 
 def gemm_peers_prepare(y, peer_ptrs, maps_dev, scale, bias, M, N, K, act=ACT_NONE, act_arg=0.0, rnd=ROUND_ARM):

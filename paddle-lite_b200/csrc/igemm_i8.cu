@@ -2569,6 +2569,8 @@ extern "C" int pl_gemm_i8_mcast(const int8_t* A, int lda, const int8_t* Bt, int 
   if ((reinterpret_cast<uintptr_t>(A) & 15) || (reinterpret_cast<uintptr_t>(Bt) & 15) || (lda % 16) || (ldb % 16) ||
       (reinterpret_cast<uintptr_t>(C_mc) & 15) || (ldc % 16))
     return PL_ERR_ALIGN;
+  // (fp32 results: multimem.st straight from the epilogue registers -- 16-byte pieces of 32 different rows per warp
+  // store -- measured 10x slower than the GEMM itself; they take pl_mcast_copy_2d after a plain pl_gemm_i8 instead)
   if (e->out_dtype != PL_OUT_INT8 || e->residual) return PL_ERR_UNSUPPORTED;
   IgemmParams p{};
   p.BK = pl_conv_block_k(K);
@@ -2586,6 +2588,41 @@ extern "C" int pl_gemm_i8_mcast(const int8_t* A, int lda, const int8_t* Bt, int 
   const BSpec bs{Bt, (uint64_t)K, (uint64_t)N, (uint64_t)ldb};
   rc = launch_igemm(ta, tb, p, stream, &bs);
   return rc;
+}
+
+// rows x row_bytes block: local memory -> the multicast address of the same block (coalesced 16-byte multimem.st:
+// 512 contiguous bytes per warp store).  The all-gather step of an N-split GEMM whose result type has no staged
+// epilogue (fp32): every rank broadcasts its own column block, the switch writes it into all ranks' results.
+__global__ void __launch_bounds__(256) mcast_copy_kernel(const uint8_t* __restrict__ src, long long ld_src, uint8_t* mc,
+                                                        long long ld_dst, long long rows, int chunks_per_row) {
+  pdl_launch_dependents();
+  pdl_wait();
+  const long long total = rows * chunks_per_row;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+    const long long r = i / chunks_per_row;
+    const long long c = i - r * chunks_per_row;
+    const uint4 v = *reinterpret_cast<const uint4*>(src + r * ld_src + c * 16);
+    multimem_st_v4(mc + r * ld_dst + c * 16, v);
+  }
+}
+
+extern "C" int pl_mcast_copy_2d(const void* src, int64_t ld_src_bytes, void* dst_mc, int64_t ld_dst_bytes, int64_t rows,
+                                int64_t row_bytes, pl_stream_t stream) {
+  if (!src || !dst_mc || rows <= 0 || row_bytes <= 0 || ld_src_bytes < row_bytes || ld_dst_bytes < row_bytes)
+    return PL_ERR_ARG;
+  if ((reinterpret_cast<uintptr_t>(src) & 15) || (reinterpret_cast<uintptr_t>(dst_mc) & 15) || (row_bytes & 15) ||
+      (ld_src_bytes & 15) || (ld_dst_bytes & 15))
+    return PL_ERR_ALIGN;
+  if (driver().cc_major != 10) return PL_ERR_DEVICE;
+  const long long total = rows * (row_bytes / 16);
+  long long blocks = (total + 255) / 256;
+  const long long cap = (long long)driver().sm_count * 8;
+  if (blocks > cap) blocks = cap;
+  launch_pdl(mcast_copy_kernel, dim3((unsigned)blocks), dim3(256), 0, (cudaStream_t)stream,
+             reinterpret_cast<const uint8_t*>(src), (long long)ld_src_bytes, reinterpret_cast<uint8_t*>(dst_mc),
+             (long long)ld_dst_bytes, (long long)rows, (int)(row_bytes / 16));
+  ++g_launches;
+  return launch_status();
 }
 
 // One-off set-up of the peer tensor maps for launches with C_peers == NULL: same tile geometry as the launch

@@ -108,18 +108,20 @@ class NSplitGemm:
         it has passed the barrier of call n+1, which B only enters after its consumer of call n (stream
         order on B).  No extra barrier is needed."""
         import torch.distributed._symmetric_memory as symm_mem
-        assert self.out_dtype == self.pl.OUT_INT8, "peer stores exist on the int8 TMA-store epilogue only"
+        int8 = self.out_dtype == self.pl.OUT_INT8  # (fp32 results: the multicast variant only)
+        tdt = torch.int8 if int8 else torch.float32
+        esz = 1 if int8 else 4
         grp = self.group if self.group is not None else dist.group.WORLD
         off = self.rank * self.per  # this rank's column block inside everybody's result
         self._fulls, self._hdls, self._maps, self._ys = [], [], [], []
         self._n_peers = self.world - 1
         for _ in range(2):
-            full = symm_mem.empty((M, self.world * self.per), dtype=torch.int8, device=self.device)
+            full = symm_mem.empty((M, self.world * self.per), dtype=tdt, device=self.device)
             hdl = symm_mem.rendezvous(full, grp)
-            peer_ptrs = [int(hdl.buffer_ptrs[r]) + off for r in range(self.world) if r != self.rank]
+            peer_ptrs = [int(hdl.buffer_ptrs[r]) + off * esz for r in range(self.world) if r != self.rank]
             maps = torch.empty(128 * 16, dtype=torch.uint8, device=self.device)
             y = full[:, off:off + self.per]
-            if peer_ptrs:
+            if peer_ptrs and int8:
                 self.pl.gemm_peers_prepare(y, peer_ptrs, maps, self.scale, self.bias, M, self.per, self.K,
                                            self.act, self.act_arg)
             self._fulls.append(full)
@@ -148,8 +150,17 @@ class NSplitGemm:
         mc = int(self._hdls[t].multicast_ptr)
         if mc == 0:
             raise RuntimeError("this group's symmetric memory has no multicast mapping (no NVLS)")
-        self.pl.gemm_mcast(A_dev, self.bt, self.scale, self.bias, self._ys[t], mc + self.rank * self.per,
-                           self.act, self.act_arg, N=self.per, K=self.K)
+        if self.out_dtype == self.pl.OUT_INT8:
+            self.pl.gemm_mcast(A_dev, self.bt, self.scale, self.bias, self._ys[t], mc + self.rank * self.per,
+                               self.act, self.act_arg, N=self.per, K=self.K)
+        else:
+            # fp32: plain GEMM into this rank's block of its own result, then one coalesced multicast broadcast
+            # of that block (multimem.st from the fp32 epilogue's registers is 10x slower: 16-byte pieces of 32
+            # different rows per warp store)
+            y = self._ys[t]
+            self.pl.gemm(A_dev, self.bt, self.scale, self.bias, self.act, self.act_arg, self.out_dtype, y=y, M=M,
+                         N=self.per, K=self.K)
+            self.pl.mcast_copy_2d(y, mc + self.rank * self.per * 4, self.world * self.per * 4)
         self._hdls[t].barrier()
         return self._fulls[t][:, :self.N]
 
@@ -158,6 +169,7 @@ class NSplitGemm:
         buffer and straight into the peers' (NVLink), overlapped with the mainloop; one device-side barrier
         of the ranks afterwards.  No collective call, no de-interleaving copy.  The returned view is valid
         until the second next fused() call (two result buffers alternate, see fused_setup)."""
+        assert self.out_dtype == self.pl.OUT_INT8, "peer stores exist on the int8 TMA-store epilogue only"
         M = A_dev.shape[0]
         if getattr(self, "_fM", None) != M:
             self.fused_setup(M)

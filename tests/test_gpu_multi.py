@@ -64,6 +64,16 @@ def _worker(rank, world, port, M, K, N, out_fp32, q):
                     dist.barrier()
                 ok = ok and mc
             got = (got.shape, mc)
+        elif N % 16 == 0:
+            # fp32 results: 16-byte multimem.st straight from the epilogue registers
+            g.fused_setup(M)
+            if g.mcast_supported() and g.act in (pl.ACT_NONE, pl.ACT_RELU):
+                for _ in range(2):
+                    fused = g.fused_mcast(Ad)
+                    torch.cuda.synchronize()
+                    ok = ok and np.allclose(fused.cpu().numpy(), want, rtol=1e-5, atol=1e-6) and \
+                        np.array_equal(fused.cpu().numpy(), got)
+                    dist.barrier()
         q.put((rank, bool(ok), got if isinstance(got, tuple) else got.shape))
     finally:
         dist.destroy_process_group()
