@@ -340,7 +340,7 @@ int64_t pl_launch_count(void);
  * that a changed environment is seen by the next launch (tests that A/B two code paths call it) */
 void pl_refresh_knobs(void);
 /* the tile plan of the calling thread's most recent tensor-core launch (conv / gemm), for tests and benches that
- * must know which code path ran: plan[0..9] = {mode, BN, BK, stages, cta_pairs, tile_pairs, band_rows, grid,
+ * must know which code path ran: plan[0..9] = {mode, BN, BK, stages | k-blocks per barrier group << 8, cta_pairs, tile_pairs, band_rows, grid,
  * filter_resident, epilogue variant}; returns the number of ints written (<= n) */
 int pl_last_igemm_plan(int* plan, int n);
 const char* pl_version(void);

@@ -102,7 +102,11 @@ def last_igemm_plan():
     """Tile plan of this thread's most recent conv / gemm launch (pl_last_igemm_plan)."""
     buf = (C.c_int * len(PLAN_KEYS))()
     n = lib().pl_last_igemm_plan(buf, len(PLAN_KEYS))
-    return dict(zip(PLAN_KEYS[:n], list(buf)[:n]))
+    d = dict(zip(PLAN_KEYS[:n], list(buf)[:n]))
+    if "stages" in d:  # ring slots per barrier group ride in the second byte
+        d["kgroup"] = (d["stages"] >> 8) & 0xff
+        d["stages"] &= 0xff
+    return d
 
 
 def refresh_knobs():

@@ -98,6 +98,10 @@ struct IgemmParams {
   // fp32 out, act none / relu, no residual, 16-byte aligned rows: the generic instantiation converts and
   // stores its 16 columns inline (four 16-byte stores per thread) instead of calling store_group16
   int f32_fast;
+  // k-block groups (modes 0 / 1, TMA-fed): `kgroup` consecutive ring slots fill under ONE full barrier and are
+  // released by ONE commit -- the MMA thread's wait + fence + commit (~450 cycles) is paid once per group instead of
+  // once per k-block (it exceeds the MMA time of a 128-byte k-block from BN = 128 down: 4 x 67 cycles)
+  int kgroup;
   int store_defer;  // store groups the store warp leaves in flight before it releases a staging buffer (0..4)
   const CUtensorMap* peer_maps;
   int n_peers;
@@ -464,7 +468,10 @@ igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
   const int warp = kStoreWarp - hw_warp;  // both layouts have kStoreWarp + 1 warps
 #endif
   const int lane = threadIdx.x & 31;
-  const int num_tiles = p.m_tiles * p.n_tiles;
+  // (debug builds: 4096 = no tiles at all -- prologue + teardown only; 8192 = return at entry; 1024 = no scale / bias
+  // staging; 512 = no TMEM allocation, only together with 4096)
+  const int num_tiles = (PL_DBG_FLAGS_V & 4096) ? 0 : p.m_tiles * p.n_tiles;
+  if (PL_DBG_FLAGS_V & 8192) return;
   // CTA pairs: both CTAs of a cluster walk the same sequence of pair tiles
   const int cta_rank = CTA2 ? (int)cluster_ctarank() : 0;
   const int tile0 = CTA2 ? (int)(blockIdx.x >> 1) : (int)blockIdx.x;
@@ -511,7 +518,7 @@ igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
     }
     fence_barrier_init();
   }
-  if (warp == 1) {
+  if (warp == 1 && !(PL_DBG_FLAGS_V & 512)) {
     if (CTA2) {
       tmem_alloc_2sm(smem_u32(&tmem_base_slot), p.tmem_cols);
       tmem_relinquish_2sm();
@@ -542,6 +549,7 @@ igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
     const uint32_t tx = p.tx_bytes, a_bytes = p.a_stage_bytes, b_bytes = p.b_stage_bytes;
     const int stages = p.stages, num_kb = p.num_kb, BK = p.BK, S = p.S, cspan = p.cblocks * p.BK;
     const int mode = p.mode, n_tiles = p.n_tiles, BN = p.BN;
+    const int KG = (TR > 0 || p.kgroup < 1) ? 1 : p.kgroup;  // ring slots per barrier group (modes 0 / 1)
     const uint16_t dwv = (uint16_t)p.dw, dhv = (uint16_t)p.dh;
     int stage = 0;
     uint32_t phase = 0;
@@ -695,36 +703,40 @@ igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
       }
       int kc = 0, cbk = 0, sx = 0;      // K coordinate of B, channel offset inside the tap, tap column
       uint16_t offw = 0, offh = 0;      // im2col filter offsets of the tap
-      for (int kb = 0; kb < num_kb; ++kb) {
+      for (int kb = 0; kb < num_kb;) {
+        // one group of KG ring slots (the last group of a tile may be shorter): the barriers of its first slot
+        const int gn = (num_kb - kb) < KG ? (num_kb - kb) : KG;
         WAIT(empty_b, phase ^ 1);
         if (kb == 0) PL_TRACE(0, lt, 1);
-        if (CTA2) {
-          // own 128 (256) rows of A + own half of the B block, all completing on the leader's barrier
-          if (cta_rank == 0) mbar_arrive_expect_tx(full_b, 2u * tx);
-          const uint32_t fsig = full_b + lead_delta;
-          if (mode == 1) tma_load_im2col_4d_2sm(dst_a, &tmap_a, fsig, cbk, bw, bh, bn, offw, offh);
-          else tma_load_2d_2sm(dst_a, &tmap_a, fsig, kc, m0);
-          tma_load_2d_2sm(dst_b, &tmap_b, fsig, kc, n0 + cta_rank * (BN >> 1));
-        } else {
-          mbar_arrive_expect_tx(full_b, tx);
-          if (TR > 0) {
-            // A arrives from the gather warps
-          } else if (mode == 1) {
-            tma_load_im2col_4d(dst_a, &tmap_a, full_b, cbk, bw, bh, bn, offw, offh);
+        // pairs: own 128 (256) rows of A + own half of every B block, all completing on the leader's barrier
+        if (!CTA2 || cta_rank == 0) mbar_arrive_expect_tx(full_b, (CTA2 ? 2u : 1u) * (uint32_t)gn * tx);
+        const uint32_t fsig = CTA2 ? full_b + lead_delta : full_b;
+        uint32_t da_ = dst_a, db_ = dst_b;
+        for (int g = 0; g < gn; ++g, ++kb, da_ += a_bytes, db_ += b_bytes) {
+          if (CTA2) {
+            if (mode == 1) tma_load_im2col_4d_2sm(da_, &tmap_a, fsig, cbk, bw, bh, bn, offw, offh);
+            else tma_load_2d_2sm(da_, &tmap_a, fsig, kc, m0);
+            tma_load_2d_2sm(db_, &tmap_b, fsig, kc, n0 + cta_rank * (BN >> 1));
           } else {
-            tma_load_2d(dst_a, &tmap_a, full_b, kc, m0);
+            if (TR > 0) {
+              // A arrives from the gather warps
+            } else if (mode == 1) {
+              tma_load_im2col_4d(da_, &tmap_a, full_b, cbk, bw, bh, bn, offw, offh);
+            } else {
+              tma_load_2d(da_, &tmap_a, full_b, kc, m0);
+            }
+            if (!bres01) tma_load_2d(db_, &tmap_b, full_b, kc, n0);
           }
-          if (!bres01) tma_load_2d(dst_b, &tmap_b, full_b, kc, n0);
+          kc += BK;
+          cbk += BK;
+          if (cbk == cspan) {
+            cbk = 0;
+            offw += dwv;
+            if (++sx == S) { sx = 0; offw = 0; offh += dhv; }
+          }
         }
-        kc += BK;
-        cbk += BK;
-        if (cbk == cspan) {
-          cbk = 0;
-          offw += dwv;
-          if (++sx == S) { sx = 0; offw = 0; offh += dhv; }
-        }
-        ++stage; full_b += 8; empty_b += 8; dst_a += a_bytes; dst_b += b_bytes;
-        if (stage == stages) {
+        stage += KG; full_b += 8 * KG; empty_b += 8 * KG; dst_a += KG * a_bytes; dst_b += KG * b_bytes;
+        if (stage >= stages) {
           stage = 0; phase ^= 1;
           full_b = bar_full; empty_b = bar_empty; dst_a = smem_a; dst_b = smem_b;
         }
@@ -734,10 +746,11 @@ igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
     if (CTA2) {
       // tail: every stage this CTA filled has been consumed (its multicast commit has landed here) before the
       // CTA can leave -- no arrival may target the barriers of a CTA that has exited
-      for (int i = 0; i < stages; ++i) {
+      const int tail_step = (mode == 3 || TR > 0) ? 1 : KG;
+      for (int i = 0; i < stages; i += tail_step) {
         WAIT(empty_b, phase ^ 1);
-        ++stage; empty_b += 8;
-        if (stage == stages) { stage = 0; phase ^= 1; empty_b = bar_empty; }
+        stage += tail_step; empty_b += 8 * tail_step;
+        if (stage >= stages) { stage = 0; phase ^= 1; empty_b = bar_empty; }
       }
     }
     }
@@ -759,6 +772,7 @@ igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
     const uint32_t a_lo0 = smem_a >> 4, b_lo0 = smem_b >> 4;  // shared addresses < 256 KB: 14 bits
     const bool bres = (TR > 0 || p.mode != 3) && p.b_resident;
     const bool skip_mma = (PL_DBG_FLAGS_V & 2) != 0;
+    const int KG = (TR > 0 || p.kgroup < 1) ? 1 : p.kgroup;
     int stage = 0;
     uint32_t phase = 0;
     uint32_t full_b = bar_full, empty_b = bar_empty, a_lo = a_lo0, b_lo = b_lo0;
@@ -895,33 +909,35 @@ igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
       tc_fence_after();
       const uint32_t d_tmem = tmem_base + (uint32_t)as * p.acc_stride;
       if (bres) b_lo = b_lo0;
-      for (int kb = 0; kb < num_kb; ++kb) {
+      for (int kb = 0; kb < num_kb;) {
+        const int gn = (num_kb - kb) < KG ? (num_kb - kb) : KG;  // k-blocks of this barrier group
         WAIT(full_b, phase);
         if (kb == 0) PL_MTRACE(lt, 2);
-        if (kb == 1) PL_MTRACE(lt, 5);
-        if (kb == num_kb - 1) PL_MTRACE(lt, 3);
+        if (kb == KG) PL_MTRACE(lt, 5);
+        if (kb + gn == num_kb) PL_MTRACE(lt, 3);
         if (TR > 0) fence_proxy_async();  // cp.async (generic proxy) writes of the gather -> tensor core reads
         tc_fence_after();
-        {
-          uint64_t da = desc_hi | (uint64_t)a_lo;
-          const uint64_t db = desc_hi | (uint64_t)b_lo;
+        uint32_t ga = a_lo, gb = b_lo;
+        for (int g = 0; g < gn; ++g, ga += a_step, gb += b_step) {
+          uint64_t da = desc_hi | (uint64_t)ga;
+          const uint64_t db = desc_hi | (uint64_t)gb;
           if (PL_DBG_ASHIFT_V) {  // descriptor-semantics experiment (tools/dbg_rowshift.py)
-            const uint32_t start = (a_lo << 4) + (uint32_t)(PL_DBG_ASHIFT_V * p.BK);
+            const uint32_t start = (ga << 4) + (uint32_t)(PL_DBG_ASHIFT_V * p.BK);
             da = desc_hi | (uint64_t)((start >> 4) & 0x3fff);
             if (PL_DBG_BASEOFF_V) da |= (uint64_t)((start >> 7) & 7u) << 49;
           }
-          if (leader) {
-            if (!skip_mma) {
-              issue_kblock_n<CTA2>(ksteps, d_tmem, da, db, idesc, kb == 0);
-              if (p.mpair)  // second 128-row block of the stage, same B, second accumulator
-                issue_kblock_n<CTA2>(ksteps, d_tmem + (uint32_t)p.BN, da + (uint64_t)((kBM * p.BK) >> 4), db, idesc, kb == 0);
-            }
-            umma_commit_t<CTA2>(empty_b);
-            if (kb == num_kb - 1) umma_commit_t<CTA2>(bar_tfull + 8 * as);
+          if (!skip_mma) {
+            issue_kblock_n<CTA2>(ksteps, d_tmem, da, db, idesc, kb + g == 0);
+            if (p.mpair)  // second 128-row block of the stage, same B, second accumulator
+              issue_kblock_n<CTA2>(ksteps, d_tmem + (uint32_t)p.BN, da + (uint64_t)((kBM * p.BK) >> 4), db, idesc, kb + g == 0);
           }
         }
-        ++stage; full_b += 8; empty_b += 8; a_lo += a_step; b_lo += b_step;
-        if (stage == stages) {
+        kb += gn;
+        umma_commit_t<CTA2>(empty_b);
+        if (kb == num_kb) umma_commit_t<CTA2>(bar_tfull + 8 * as);
+        stage += KG; full_b += 8 * KG; empty_b += 8 * KG; a_lo += KG * a_step;
+        b_lo += (bres ? gn : KG) * b_step;  // resident filter: consecutive k-blocks; ring: the group's slots
+        if (stage >= stages) {
           stage = 0; phase ^= 1;
           full_b = bar_full; empty_b = bar_empty; a_lo = a_lo0;
           if (!bres) b_lo = b_lo0;
@@ -1171,7 +1187,8 @@ igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
         s_bias[buf * 256 + etid] = (ok && p.epi.bias) ? __ldg(p.epi.bias + n) : 0.f;
       }
     };
-    if (p.sb_all) {
+    if (PL_DBG_FLAGS_V & 1024) {
+    } else if (p.sb_all) {
       for (int n = etid; n < p.sb_n; n += 32 * EW) {
         const bool ok = n < p.Nout && p.epi.scale != nullptr;
         s_scale[n] = ok ? __ldg(p.epi.scale + n) : 0.f;
@@ -1346,7 +1363,7 @@ igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
   tc_fence_before();
   if (CTA2) cluster_sync_all();  // neither CTA's smem / TMEM / barriers go away while the other still uses them
   else __syncthreads();
-  if (warp == 1) {
+  if (warp == 1 && !(PL_DBG_FLAGS_V & 512)) {
     tc_fence_after();
     if (CTA2) tmem_dealloc_2sm(tmem_base, p.tmem_cols);
     else tmem_dealloc(tmem_base, p.tmem_cols);
@@ -1989,6 +2006,24 @@ int launch_igemm(const CUtensorMap& ta, const CUtensorMap& tb_in, IgemmParams& p
     ring_bytes = (size_t)stages * stage_bytes;
   }
   if (stages < 2 || (p.mode == 2 && !p.thin_group && stages < p.num_kb)) return PL_ERR_UNSUPPORTED;
+  p.kgroup = 1;
+  if ((p.mode == 0 || p.mode == 1) && p.num_kb >= 2) {
+    // group ring slots until a group's MMAs run >= ~900 cycles (the MMA thread's wait + fence + commit per group
+    // costs ~450), keeping at least two groups in the ring
+    const int cyc = p.BN >= 256 ? 136 : (p.BN >= 128 ? 67 : (p.BN >= 64 ? 50 : 42));
+    const int per_kb = (p.BK / 32) * cyc * (p.mpair ? 2 : 1);
+    // measured (profiles/r02_exp7_kgroup.txt): grouping halves the look-ahead of the ring and LOSES 5-15 % on the
+    // streamed layers and GEMMs (8192^3 68 -> 58 %), small layers do not move -- so one k-block per barrier stays
+    // the default; PL_KGROUP=0 asks for the automatic grouping, 2 / 4 force a group size
+    int g = env_int("PL_KGROUP", 1);
+    if (g <= 0) {
+      g = 1;
+      while (g < 4 && per_kb * g < env_int("PL_KGROUP_CYCLES", 900) && 2 * g <= p.num_kb) g *= 2;
+    }
+    while (g > 1 && stages / g < 2) g >>= 1;
+    p.kgroup = g;
+    stages -= stages % g;
+  }
   p.stages = stages;
   if (p.mode != 3) p.a_region_bytes = (uint32_t)stages * p.a_stage_bytes;
   p.out_stage_off = (uint32_t)ring_bytes;
@@ -2017,7 +2052,7 @@ int launch_igemm(const CUtensorMap& ta, const CUtensorMap& tb_in, IgemmParams& p
 #undef PL_THIN_CASE
   }
   {
-    const int plan[10] = {p.mode, p.BN, p.BK, p.stages, p.cta2, p.mpair, p.group_m, grid, p.b_resident, epi};
+    const int plan[10] = {p.mode, p.BN, p.BK, p.stages | (p.kgroup << 8), p.cta2, p.mpair, p.group_m, grid, p.b_resident, epi};
     for (int i = 0; i < 10; ++i) g_last_plan[i] = plan[i];
   }
   if (p.cta2) {
@@ -2103,6 +2138,17 @@ int common_setup(IgemmParams& p, long long M, int Nout, void* y, int ldy, const 
   if (p.s2d) {  // the filter must be resident: one N tile, never narrowed to fill the grid
     p.BN = 16;
     while (p.BN < Nout && p.BN < 256) p.BN <<= 1;
+  }
+  if (p.halo_m_tiles > 0 && !p.s2d && Nout <= 256 && env_int("PL_HALO_KEEP_NTILE", 1)) {
+    // halo launches that do not fill the SMs: narrowing the tile multiplies the CTAs, but every one of them still
+    // loads the whole halo tile, and the filter stops being resident -- the MMA thread then walks R*S filter
+    // stages (wait + commit, ~450 cycles each: 4000 of the 6500 cycles of a one-tile 3x3 launch, CTA-0 timeline
+    // in profiles/r02_latency.md) instead of issuing all taps in one run.  Keep ONE N tile while its packed
+    // filter fits beside two halo tiles
+    int bn1 = 16;
+    while (bn1 < Nout) bn1 <<= 1;
+    const long long filt = (long long)taps * cpad * bn1;
+    if (bn1 > p.BN && filt <= 150 * 1024) p.BN = bn1;
   }
   {
     // a 256-wide tile whose filter slice (K_red x 256 bytes) cannot stay resident in shared memory, while a 128-wide

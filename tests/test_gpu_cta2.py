@@ -168,3 +168,15 @@ def test_halo_pairs_with_resident_half_filter(pl, knobs):
     plan = pl.last_igemm_plan()
     assert plan["cta_pairs"] == 1 and plan["filter_resident"] == 1 and plan["mode"] == 3, plan
     assert np.array_equal(got, want)
+
+
+@pytest.mark.parametrize("kg", [0, 2, 4])
+def test_kblock_groups(pl, knobs, kg):
+    """PL_KGROUP: several ring slots under one full barrier / one commit (off by default: measured slower), with a
+    short last group, a resident and a streamed filter, single CTAs and pairs"""
+    for cta2, bn, (M, N, K) in ((0, 128, (1000, 256, 640)), (2, 128, (1000, 256, 896)), (0, 64, (40000, 64, 384))):
+        knobs(PL_KGROUP=kg, PL_CTA2=cta2, PL_FORCE_BN=bn, PL_NO_GEMV=1)
+        got, want = gemm_case(pl, M, N, K, "int8", "relu", seed=kg + M)
+        plan = pl.last_igemm_plan()
+        assert plan["kgroup"] >= (2 if kg else 1), plan
+        assert np.array_equal(got, want)

@@ -101,7 +101,7 @@ def bench(name, batch, iters, nsets):
     plan = ""
     if not dw:
         q = pl.last_igemm_plan()
-        plan = (f" plan: mode {q['mode']} BN {q['BN']} BK {q['BK']} stages {q['stages']} pairs {q['cta_pairs']}"
+        plan = (f" plan: mode {q['mode']} BN {q['BN']} BK {q['BK']} stages {q['stages']} kg {q.get('kgroup', 1)} pairs {q['cta_pairs']}"
                 f" resident {q['filter_resident']} grid {q['grid']}")
     print(f"{name:24s} b{batch} ms={ms:.4f} TOPS={ops / ms / 1e9:8.1f} GB/s={byts / ms / 1e6:8.1f} "
           f"(bytes {byts / 1e6:.1f} MB){plan}", flush=True)
