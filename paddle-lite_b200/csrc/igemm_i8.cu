@@ -244,14 +244,14 @@ __device__ __forceinline__ uint32_t quad_i8_signed(const uint32_t* acc, float4 s
   const uint64_t big = pk2(32768.5f, 32768.5f);  // see quad_i8_relu: integer part lands in byte 1
   const uint64_t u01 = fadd2_rm(pk2(fminf(fabsf(v[0]), 127.f), fminf(fabsf(v[1]), 127.f)), big);
   const uint64_t u23 = fadd2_rm(pk2(fminf(fabsf(v[2]), 127.f), fminf(fabsf(v[3]), 127.f)), big);
-  const uint32_t m[4] = {(uint32_t)u01, (uint32_t)(u01 >> 32), (uint32_t)u23, (uint32_t)(u23 >> 32)};
-  uint32_t q[4];
-#pragma unroll
-  for (int j = 0; j < 4; ++j) {
-    const int sg = __float_as_int(v[j]) >> 31;                       // 0 or -1
-    q[j] = (uint32_t)((int)((m[j] >> 8) ^ (uint32_t)sg) - sg);       // conditional negate; low byte is the result
-  }
-  return prmt_(prmt_(q[0], q[1], 0x0040), prmt_(q[2], q[3], 0x0040), 0x5410);
+  // the four magnitudes (byte 1 of each sum) and the four signs (msb of each value, replicated over a byte by the
+  // sign mode of PRMT) as packed bytes; bytes are then negated where the sign byte is 0xff: 0x80 - m never borrows
+  // (m <= 127), and (0x80 - m) ^ 0x80 = -m mod 256 (16 issue slots per quad instead of 25 with per-lane negation)
+  const uint32_t M = prmt_(prmt_((uint32_t)u01, (uint32_t)(u01 >> 32), 0x0051), prmt_((uint32_t)u23, (uint32_t)(u23 >> 32), 0x0051), 0x5410);
+  const uint32_t S = prmt_(prmt_(__float_as_uint(v[0]), __float_as_uint(v[1]), 0x00fb),
+                           prmt_(__float_as_uint(v[2]), __float_as_uint(v[3]), 0x00fb), 0x5410);
+  const uint32_t neg = (0x80808080u - (M & S)) ^ 0x80808080u;  // -m in the negative lanes, 0 elsewhere
+  return neg | (M & ~S);
 }
 
 // generic element (any dtype / act / rounding / residual)
@@ -363,6 +363,28 @@ __device__ __forceinline__ void issue_taps(uint32_t d_tmem, uint64_t da0, uint64
                        db0 + (uint64_t)((r * S_ + sx) * b_step), idesc, fresh && r == 0 && sx == 0);
 }
 
+// The MMA thread is ONE lane: it issues roughly one instruction every 3 cycles, a taken branch costs ~30, an mbarrier
+// wait ~70 even when complete, and the tensor pipe queues only ~8 MMAs behind the running one (tools/sync_probe.cu).
+// Whatever the thread does between the last MMA of a tile and the first of the next beyond 8 MMA times drains the
+// pipe.  Descriptors of a run are therefore walked with immediate / single-register adds from a base that is opaque
+// to the compiler (otherwise the invariant ones get hoisted into vector registers: two R2UR per descriptor and tile).
+__device__ __forceinline__ uint32_t opaque_u32(uint32_t v) {
+  asm volatile("" : "+r"(v));
+  return v;
+}
+// taps [T0, T1) of a resident 3 x 3 filter: A walks the halo tile (next tap: one pixel = 2 * KS units, next filter
+// row: row_pitch), B the resident filter blocks (b_step apart)
+template <int KS, bool CTA2, int T0, int T1>
+__device__ __forceinline__ void issue_taps3_range(uint32_t d_tmem, uint64_t da0, uint64_t db0, uint32_t idesc,
+                                                  uint32_t row_pitch, uint32_t b_step, bool fresh) {
+#pragma unroll
+  for (int tap = T0; tap < T1; ++tap) {
+    const int r = tap / 3, sx = tap - 3 * r;
+    issue_kblock<KS, CTA2>(d_tmem, da0 + (uint64_t)(r * row_pitch) + (uint64_t)(sx * 2 * KS), db0 + (uint64_t)(tap * b_step), idesc,
+                           fresh && tap == 0);
+  }
+}
+
 // all MMAs of one space-to-depth tile (TA tap rows x KPR K=32 steps), fully unrolled
 template <int TA, int KPR>
 __device__ __forceinline__ void issue_s2d(uint32_t d_tmem, uint64_t da0, uint64_t db0, uint32_t idesc,
@@ -373,6 +395,129 @@ __device__ __forceinline__ void issue_s2d(uint32_t d_tmem, uint64_t da0, uint64_
     for (int ks = 0; ks < KPR; ++ks)
       umma_i8(d_tmem, da0 + (uint64_t)(a * pitch16 + 2u * ks), db0 + (uint64_t)((a * KPR + ks) * b_step), idesc,
               (uint32_t)((a | ks) != 0));
+}
+
+// ---- the MMA thread's tile loop for a resident 3 x 3 filter (halo mode) ----
+// Out of line on purpose: inside the kernel body its unrolled runs changed the code layout of the other single-thread
+// role loops (space-to-depth stems +4 %, measured); as a function it has its own registers and sits apart.
+struct Taps3Args {
+  int tile0, tstride, num_tiles, acc_stages, halo_bufs, cblocks, ksteps;
+  uint32_t tmem_base, acc_stride, bar_tempty, bar_tfull, bar_afull, bar_aempty, a_lo0, b_lo0, halo_step, b_step, row_pitch, idesc;
+  uint64_t desc_hi;
+#ifdef PL_DEBUG_KNOBS
+  long long* trace;
+#endif
+};
+#ifdef PL_DEBUG_KNOBS
+#define PL_T3TRACE(t, e) do { if (a.trace != nullptr && (t) < 64) a.trace[(64 + (t)) * 8 + (e)] = clock64(); } while (0)
+#else
+#define PL_T3TRACE(t, e) do { } while (0)
+#endif
+template <bool CTA2>
+__device__ __noinline__ void mma_loop_taps3(const Taps3Args a) {
+  // one straight run of 9 * ksteps MMAs per halo tile (and channel block).  The barrier waits of the NEXT unit are
+  // taken in the middle of the run, while >= 8 MMAs are queued behind the running one, so the thread reaches the next
+  // run with nothing but two commits in between (r2 3x3 64: 52.4 -> 45.1 us at b256)
+  const uint32_t b_step9 = 9u * a.b_step;
+  int as = 0, ab = 0, lt = 0;
+  uint32_t aphase = 0, aph = 0;
+  uint32_t a_cur = a.a_lo0;  // descriptor start of the current halo buffer
+  if (a.tile0 < a.num_tiles) {
+    mbar_wait(a.bar_tempty + 8 * as, aphase ^ 1);
+    mbar_wait(a.bar_afull + 8 * ab, aph);
+  }
+  for (int tile = a.tile0; tile < a.num_tiles; tile += a.tstride, ++lt) {
+    PL_T3TRACE(lt, 0);
+    const uint32_t d_tmem = a.tmem_base + (uint32_t)as * a.acc_stride;
+    int as_n = as + 1;
+    uint32_t aphase_n = aphase;
+    if (as_n == a.acc_stages) { as_n = 0; aphase_n ^= 1; }
+    uint32_t b_cur = opaque_u32(a.b_lo0);
+    for (int cb = 0; cb < a.cblocks; ++cb) {
+      tc_fence_after();
+      if (cb == 0) PL_T3TRACE(lt, 2);
+      const uint64_t da0 = a.desc_hi | (uint64_t)a_cur, db0 = a.desc_hi | (uint64_t)b_cur;
+      const bool last_cb = cb == a.cblocks - 1;
+      int ab_n = ab + 1;
+      uint32_t aph_n = aph, a_nxt = a_cur + a.halo_step;
+      if (ab_n == a.halo_bufs) { ab_n = 0; aph_n ^= 1; a_nxt = a.a_lo0; }
+      const bool more = !last_cb || tile + a.tstride < a.num_tiles;
+#define PL_TAPS3(KS_)                                                                                          \
+  issue_taps3_range<KS_, CTA2, 0, 5>(d_tmem, da0, db0, a.idesc, a.row_pitch, a.b_step, cb == 0);               \
+  if (more && !CTA2) {                                                                                         \
+    if (last_cb) mbar_wait(a.bar_tempty + 8 * as_n, aphase_n ^ 1);                                             \
+    mbar_wait(a.bar_afull + 8 * ab_n, aph_n);                                                                  \
+  }                                                                                                            \
+  issue_taps3_range<KS_, CTA2, 5, 9>(d_tmem, da0, db0, a.idesc, a.row_pitch, a.b_step, false);
+      if (a.ksteps == 4) { PL_TAPS3(4) }
+      else if (a.ksteps == 2) { PL_TAPS3(2) }
+      else { PL_TAPS3(1) }
+#undef PL_TAPS3
+      umma_commit_t<CTA2>(a.bar_aempty + 8 * ab);
+      if (last_cb) umma_commit_t<CTA2>(a.bar_tfull + 8 * as);
+      if (more && CTA2) {  // pairs are bound by the L2 stream: a wait in mid-run would stall MMAs whose operands are there
+        if (last_cb) mbar_wait(a.bar_tempty + 8 * as_n, aphase_n ^ 1);
+        mbar_wait(a.bar_afull + 8 * ab_n, aph_n);
+      }
+      ab = ab_n; aph = aph_n; a_cur = a_nxt;
+      b_cur += b_step9;
+    }
+    PL_T3TRACE(lt, 4);
+    as = as_n; aphase = aphase_n;
+  }
+}
+
+// ---- the MMA thread's tile loop of the space-to-depth stems (out of line like mma_loop_taps3) ----
+struct S2dArgs {
+  int tile0, tstride, num_tiles, acc_stages, halo_bufs, ta, kpr, skip_mma;
+  uint32_t tmem_base, acc_stride, bar_tempty, bar_tfull, bar_afull, bar_aempty, a_lo0, b_lo0, halo_step, b_step, pitch16, idesc;
+  uint64_t desc_hi;
+#ifdef PL_DEBUG_KNOBS
+  long long* trace;
+#endif
+};
+__device__ __noinline__ void mma_loop_s2d(const S2dArgs a) {
+  // a tile is TA x KPR <= 8 MMAs: all of them fit the tensor pipe's queue, so the waits of the next tile follow the
+  // commits directly and run while the queue drains
+  const uint64_t desc_a = make_smem_desc_pix16();
+  int as = 0, ab = 0, lt = 0;
+  uint32_t aphase = 0, aph = 0;
+  uint32_t a_cur = a.a_lo0;
+  if (a.tile0 < a.num_tiles) {
+    mbar_wait(a.bar_tempty + 8 * as, aphase ^ 1);
+    mbar_wait(a.bar_afull + 8 * ab, aph);
+  }
+  for (int tile = a.tile0; tile < a.num_tiles; tile += a.tstride, ++lt) {
+    PL_T3TRACE(lt, 0);
+    const uint32_t d_tmem = a.tmem_base + (uint32_t)as * a.acc_stride;
+    int as_n = as + 1, ab_n = ab + 1;
+    uint32_t aphase_n = aphase, aph_n = aph, a_nxt = a_cur + a.halo_step;
+    if (as_n == a.acc_stages) { as_n = 0; aphase_n ^= 1; }
+    if (ab_n == a.halo_bufs) { ab_n = 0; aph_n ^= 1; a_nxt = a.a_lo0; }
+    tc_fence_after();
+    PL_T3TRACE(lt, 2);
+    const uint32_t b_cur = opaque_u32(a.b_lo0);
+    const uint64_t da0 = desc_a | (uint64_t)a_cur, db0 = a.desc_hi | (uint64_t)b_cur;
+    if (a.skip_mma) {
+    } else if (a.ta == 4 && a.kpr == 2) {  // 7x7 / p3 stem
+      issue_s2d<4, 2>(d_tmem, da0, db0, a.idesc, a.pitch16, a.b_step);
+    } else if (a.ta == 2 && a.kpr == 1) {  // 3x3 / p1 stem
+      issue_s2d<2, 1>(d_tmem, da0, db0, a.idesc, a.pitch16, a.b_step);
+    } else {
+      uint32_t t_lo = a_cur, bb = b_cur;
+      for (int r = 0; r < a.ta; ++r, t_lo += a.pitch16)
+        for (int ks = 0; ks < a.kpr; ++ks, bb += a.b_step)  // K = 32: pixels (2 ks, 2 ks + 1) of every row
+          umma_i8(d_tmem, desc_a | (uint64_t)(t_lo + 2u * (uint32_t)ks), a.desc_hi | (uint64_t)bb, a.idesc, (uint32_t)((r | ks) != 0));
+    }
+    umma_commit(a.bar_aempty + 8 * ab);
+    umma_commit(a.bar_tfull + 8 * as);
+    PL_T3TRACE(lt, 4);
+    if (tile + a.tstride < a.num_tiles) {
+      mbar_wait(a.bar_tempty + 8 * as_n, aphase_n ^ 1);
+      mbar_wait(a.bar_afull + 8 * ab_n, aph_n);
+    }
+    as = as_n; aphase = aphase_n; ab = ab_n; aph = aph_n; a_cur = a_nxt;
+  }
 }
 
 // timeline tracing: role r, local tile t (first 64 tiles of CTA 0), event e (0..7)
@@ -791,37 +936,35 @@ igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
       if (hres) WAIT(bar_bres, 0);
       int lt = 0;
       if (p.s2d) {
-        const uint64_t desc_a = make_smem_desc_pix16();
-        const int ta = p.s2d_ta, kpr = p.s2d_kpr;
-        const uint32_t pitch16 = p.s2d_span_pitch >> 4;
-        for (int tile = tile0; tile < num_tiles; tile += tstride, ++lt) {
-          PL_MTRACE(lt, 0);
-          WAIT(bar_tempty + 8 * as, aphase ^ 1);
-          PL_MTRACE(lt, 1);
-          WAIT(bar_afull + 8 * ab, aph);
-          PL_MTRACE(lt, 2);
-          tc_fence_after();
-          const uint32_t d_tmem = tmem_base + (uint32_t)as * p.acc_stride;
-          uint32_t t_lo = a_lo0 + (uint32_t)ab * halo_step, bb = b_lo0;
-          if (skip_mma) {
-          } else if (ta == 4 && kpr == 2) {  // 7x7 / p3 stem
-            issue_s2d<4, 2>(d_tmem, desc_a | (uint64_t)t_lo, desc_hi | (uint64_t)bb, idesc, pitch16, b_step);
-          } else if (ta == 2 && kpr == 1) {  // 3x3 / p1 stem
-            issue_s2d<2, 1>(d_tmem, desc_a | (uint64_t)t_lo, desc_hi | (uint64_t)bb, idesc, pitch16, b_step);
-          } else {
-            for (int a = 0; a < ta; ++a, t_lo += pitch16)
-              for (int ks = 0; ks < kpr; ++ks, bb += b_step)  // K = 32: pixels (2 ks, 2 ks + 1) of every row
-                umma_i8_t<CTA2>(d_tmem, desc_a | (uint64_t)(t_lo + 2u * (uint32_t)ks), desc_hi | (uint64_t)bb, idesc,
-                        (uint32_t)((a | ks) != 0));
-          }
-          umma_commit_t<CTA2>(bar_aempty + 8 * ab);
-          umma_commit_t<CTA2>(bar_tfull + 8 * as);
-          PL_MTRACE(lt, 4);
-          if (++ab == halo_bufs) { ab = 0; aph ^= 1; }
-          if (++as == p.acc_stages) { as = 0; aphase ^= 1; }
-        }
+        S2dArgs sa;
+        sa.tile0 = tile0; sa.tstride = tstride; sa.num_tiles = num_tiles;
+        sa.tmem_base = tmem_base; sa.acc_stride = p.acc_stride; sa.acc_stages = p.acc_stages;
+        sa.bar_tempty = bar_tempty; sa.bar_tfull = bar_tfull; sa.bar_afull = bar_afull; sa.bar_aempty = bar_aempty;
+        sa.a_lo0 = a_lo0; sa.b_lo0 = b_lo0; sa.halo_step = halo_step; sa.b_step = b_step;
+        sa.pitch16 = p.s2d_span_pitch >> 4;
+        sa.halo_bufs = halo_bufs; sa.ta = p.s2d_ta; sa.kpr = p.s2d_kpr;
+        sa.desc_hi = desc_hi; sa.idesc = idesc; sa.skip_mma = skip_mma ? 1 : 0;
+#ifdef PL_DEBUG_KNOBS
+        sa.trace = blockIdx.x == 0 ? p.trace : nullptr;
+#endif
+        mma_loop_s2d(sa);
       }
-      for (int tile = tile0; tile < num_tiles && !p.s2d; tile += tstride, ++lt) {
+      const bool taps3 = hres && RS == 9 && S == 3 && !skip_mma && !(PL_DBG_FLAGS_V & 128);
+      if (taps3 && !p.s2d) {
+        Taps3Args ta3;
+        ta3.tile0 = tile0; ta3.tstride = tstride; ta3.num_tiles = num_tiles;
+        ta3.tmem_base = tmem_base; ta3.acc_stride = p.acc_stride; ta3.acc_stages = p.acc_stages;
+        ta3.bar_tempty = bar_tempty; ta3.bar_tfull = bar_tfull; ta3.bar_afull = bar_afull; ta3.bar_aempty = bar_aempty;
+        ta3.a_lo0 = a_lo0; ta3.b_lo0 = b_lo0; ta3.halo_step = halo_step; ta3.b_step = b_step;
+        ta3.row_pitch = (uint32_t)(p.WP * p.BK) >> 4;
+        ta3.halo_bufs = halo_bufs; ta3.cblocks = cblocks; ta3.ksteps = ksteps;
+        ta3.desc_hi = desc_hi; ta3.idesc = idesc;
+#ifdef PL_DEBUG_KNOBS
+        ta3.trace = blockIdx.x == 0 ? p.trace : nullptr;
+#endif
+        mma_loop_taps3<CTA2>(ta3);
+      }
+      for (int tile = tile0; tile < num_tiles && !p.s2d && !taps3; tile += tstride, ++lt) {
         PL_MTRACE(lt, 0);
         WAIT(bar_tempty + 8 * as, aphase ^ 1);
         PL_MTRACE(lt, 1);
@@ -834,17 +977,7 @@ igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
           tc_fence_after();
           uint32_t t_lo = a_lo0 + (uint32_t)ab * halo_step;  // descriptor start of tap (0, 0)
           int sx = 0;
-          if (hres && RS == 9 && S == 3 && !skip_mma) {
-            const uint64_t da0 = desc_hi | (uint64_t)t_lo, db0 = desc_hi | (uint64_t)b_lo;
-            const uint32_t row_pitch = (uint32_t)(p.WP * p.BK) >> 4;
-            if (ksteps == 4) issue_taps<3, 3, 4, CTA2>(d_tmem, da0, db0, idesc, tap_step, row_pitch, b_step, cb == 0);
-            else if (ksteps == 2) issue_taps<3, 3, 2, CTA2>(d_tmem, da0, db0, idesc, tap_step, row_pitch, b_step, cb == 0);
-            else issue_taps<3, 3, 1, CTA2>(d_tmem, da0, db0, idesc, tap_step, row_pitch, b_step, cb == 0);
-            b_lo += 9 * b_step;
-            umma_commit_t<CTA2>(bar_aempty + 8 * ab);
-            if (cb == cblocks - 1) umma_commit_t<CTA2>(bar_tfull + 8 * as);
-          }
-          for (int tap = 0; tap < RS && !(hres && RS == 9 && S == 3 && !skip_mma); ++tap) {
+          for (int tap = 0; tap < RS; ++tap) {
             if (!hres) {  // streamed filter: one ring stage per tap
               WAIT(full_b, phase);
               tc_fence_after();
@@ -1203,9 +1336,9 @@ igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
     // one group of all warps, or CQ groups of four warps (one warp per TMEM lane quarter)
     auto epilogue_loop = [&](auto cqn_tag, auto pair_tag) {
     constexpr bool kPair = decltype(pair_tag)::value;  // 256 x BN tile pairs: two accumulators per stage
-    constexpr int kSlots = (kPair ? 32 : 16) / CQ;     // unrolled unit slots of one warp
-    const int units = kPair ? 2 * (p.BN >> 4) : (p.BN >> 4);  // 16-column units of one accumulator stage
     constexpr int cqn = decltype(cqn_tag)::value;  // column groups inside one tile group
+    constexpr int kSlots = (kPair ? 32 : 16) / CQ;  // unrolled unit slots of one warp (cqn = 1: tiles of <= 16 / CQ units)
+    const int units = kPair ? 2 * (p.BN >> 4) : (p.BN >> 4);  // 16-column units of one accumulator stage
     constexpr int G = CQ / cqn;                    // tile-alternating groups
     const int egroup = cq / cqn, cqp = cq - egroup * cqn;
     int lt = egroup;  // local tile counter of this CTA: group g takes tiles g, g + G, ...
@@ -1952,7 +2085,11 @@ int launch_igemm(const CUtensorMap& ta, const CUtensorMap& tb_in, IgemmParams& p
     if (units > env_int("PL_EPI_GROUPS_MAX_UNITS", 4)) g = 1;  // measured: BN >= 128 tiles lose a few % with groups
     const int bufs = p.tma_res ? p.res_bufs : p.out_bufs;
     while (g > 1 && (g > bufs || g > p.acc_stages || (cq % g) != 0)) g >>= 1;
-    if (g != cq || env_int("PL_EPI_GROUPS", 4) <= 1) g = 1;  // the kernel instantiates 1 group or `cq` groups
+    // the kernel instantiates 1 group or `cq` groups.  (Two half-width groups on alternate 256-wide tiles, and on
+    // 128-wide tiles with four accumulator stages, were built and measured for the epilogue-bound 1x1 expand layers:
+    // 5-20 % slower, profiles/r02_epilogue.md -- both accumulator stages are then held by epilogues and the MMA of
+    // the next tile cannot run ahead)
+    if (g != cq || env_int("PL_EPI_GROUPS", 4) <= 1) g = 1;
     p.epi_groups = g;
   }
   if (p.s2d && !hres) return PL_ERR_UNSUPPORTED;

@@ -42,19 +42,20 @@ for bn in (256, 128, 64):
     tops = (sms // 2) * mmas * 2.0 * 256 * bn * 32 / (ms * 1e-3) / 1e12
     print(f"pairs rc={rc} N={bn:3d}: {cyc:7.1f} cycles/MMA  {tops:7.1f} TOPS", flush=True)
 
-print("A descriptor start shifted by whole rows (halo-mode taps), row_bytes=128:")
-for shift in (0, 1, 2, 3, 4, 8, 9):
-    for bn in (256, 128, 64):
-        iters = 4000
-        rb = 128 | (shift << 8)
-        lib.pl_i8_mma_probe(sms, 200, bn, rb, C.c_void_p(out.data_ptr()), None)
-        torch.cuda.synchronize()
-        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        a.record()
-        rc = lib.pl_i8_mma_probe(sms, iters, bn, rb, C.c_void_p(out.data_ptr()), None)
-        b.record()
-        torch.cuda.synchronize()
-        ms = a.elapsed_time(b)
-        mmas = iters * 8
-        cyc = ms * 1e-3 * clk / mmas
-        print(f"shift={shift} rc={rc} N={bn:3d}: {cyc:7.1f} cycles/MMA", flush=True)
+for rbase in (128, 64):
+    print(f"A descriptor start shifted by whole rows (halo-mode taps), row_bytes={rbase}:")
+    for shift in (0, 1, 2, 3, 4, 8, 9):
+        for bn in (256, 128, 64):
+            iters = 4000
+            rb = rbase | (shift << 8)
+            lib.pl_i8_mma_probe(sms, 200, bn, rb, C.c_void_p(out.data_ptr()), None)
+            torch.cuda.synchronize()
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record()
+            rc = lib.pl_i8_mma_probe(sms, iters, bn, rb, C.c_void_p(out.data_ptr()), None)
+            b.record()
+            torch.cuda.synchronize()
+            ms = a.elapsed_time(b)
+            mmas = iters * 8
+            cyc = ms * 1e-3 * clk / mmas
+            print(f"shift={shift} rc={rc} N={bn:3d}: {cyc:7.1f} cycles/MMA", flush=True)

@@ -3,7 +3,7 @@ import json
 import sys
 
 HBM, TENSOR = 6532.9, 4500.0  # GB/s (MEASURED_PEAKS.json), int8 TOP/s (tools/mma_probe.py)
-t = json.load(open(sys.argv[1]))
+t = [r for r in json.load(open(sys.argv[1])) if "ms" in r]  # (the last entry describes the timing source)
 min_ms = float(sys.argv[2]) if len(sys.argv) > 2 else 0.0
 tot = sum(r["ms"] for r in t)
 fl_tot = 0.0
