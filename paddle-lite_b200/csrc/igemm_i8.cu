@@ -63,6 +63,7 @@ struct IgemmParams {
   uint32_t a_halo_bytes, a_halo_tx;
   uint32_t a_region_bytes;   // bytes of the A stage ring / halo buffers in front of the B ring
   FastDiv dBands, dWP;
+  FastDiv dNT;  // n_tiles (set by launch_igemm)
   const uint32_t* xw;  // mode 2: input words [N][H][W]
   int thin_r, thin_sw;
   // space-to-depth stem (mode 3 with s2d = 1): the input is [N][HP][WS] 16-byte pixels (2x2 original
@@ -556,8 +557,9 @@ __device__ __forceinline__ void tile_mn(const IgemmParams& p, int tile, int& tm,
     tn = within / rows;
     tm = band * p.group_m + within - tn * rows;
   } else {
-    tn = tile % p.n_tiles;
-    tm = tile / p.n_tiles;
+    // (a runtime / and % cost ~40 instructions per tile in each of the 18 warps that walk the tile list)
+    tm = (int)fdiv((uint32_t)tile, p.dNT);
+    tn = tile - tm * p.n_tiles;
   }
   if (CTA2) tm = 2 * tm + rank;
 }
@@ -760,7 +762,8 @@ igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
       }
       for (int tile = tile0; tile < num_tiles && !p.s2d; tile += tstride, ++lt) {
         PL_TRACE(0, lt, 0);
-        const int tn = tile % n_tiles, tm = CTA2 ? 2 * (tile / n_tiles) + cta_rank : tile / n_tiles;
+        const int tq = (int)fdiv((uint32_t)tile, p.dNT);
+        const int tn = tile - tq * n_tiles, tm = CTA2 ? 2 * tq + cta_rank : tq;
         const int n0 = tn * BN;
         // (pairs: the block past the last one reads image N -- all zero fill, nothing stored)
         const int img = (int)fdiv((uint32_t)tm, p.dBands);
@@ -1096,7 +1099,7 @@ igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
     int glt = 0;
     for (int tile = tile0; tile < num_tiles; tile += tstride, ++glt) {
       if (g == 0) PL_TRACE(0, glt, 0);
-      const int tm = tile / p.n_tiles;
+      const int tm = (int)fdiv((uint32_t)tile, p.dNT);
       const uint32_t m = (uint32_t)(tm * kBM + prow);
       const bool mok = m < (uint32_t)p.M;
       const uint32_t n = fdiv(mok ? m : 0u, p.dPQ);
@@ -1370,10 +1373,12 @@ igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
       const uint32_t sb0 = p.sb_all ? (uint32_t)n0 : (uint32_t)(sbuf * 256);
       // one lane per warp polls (512 threads polling one mbarrier serialise); the warp-level
       // sync hands the acquired state to the other lanes
+      // (two lanes poll side by side: a wait costs ~70-250 cycles even when its phase is complete)
       if (lane == 0) {
-        if (EPI == EPI_I8_RELU_RES) WAIT(bar_rfull + 8 * rb, rphase);
         WAIT(bar_tfull + 8 * as, aphase);
-        if (kFast && EPI != EPI_I8_RELU_RES) WAIT(bar_ofree + 8 * ob, ophase ^ 1);
+      } else if (lane == 1) {
+        if (EPI == EPI_I8_RELU_RES) WAIT(bar_rfull + 8 * rb, rphase);
+        else if (kFast) WAIT(bar_ofree + 8 * ob, ophase ^ 1);
       }
       __syncwarp();
       PL_ETRACE(1);
@@ -1942,6 +1947,7 @@ int launch_igemm(const CUtensorMap& ta, const CUtensorMap& tb_in, IgemmParams& p
     }
   }
   const int tiles = p.m_tiles * p.n_tiles;
+  p.dNT = make_fastdiv((uint32_t)p.n_tiles);
   int grid = tiles < driver().sm_count ? tiles : driver().sm_count;
   if (p.cta2) {
     const int clusters = tiles < max_pair_clusters() ? tiles : max_pair_clusters();
