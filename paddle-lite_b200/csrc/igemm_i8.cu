@@ -843,9 +843,9 @@ igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
       }
       int bw = 0, bh = 0, bn = 0;
       if (mode == 1) {
-        bn = m0 / p.PQ;
+        bn = (int)fdiv((uint32_t)m0, p.dPQ);
         const int rem = m0 - bn * p.PQ;
-        const int op = rem / p.Q, oq = rem - op * p.Q;
+        const int op = (int)fdiv((uint32_t)rem, p.dQ), oq = rem - op * p.Q;
         bw = oq * p.sw - p.pl_;
         bh = op * p.sh - p.pt;
       }
@@ -2149,6 +2149,8 @@ int launch_igemm(const CUtensorMap& ta, const CUtensorMap& tb_in, IgemmParams& p
     ring_bytes = (size_t)stages * stage_bytes;
   }
   if (stages < 2 || (p.mode == 2 && !p.thin_group && stages < p.num_kb)) return PL_ERR_UNSUPPORTED;
+  // (Moving the MMA thread's accumulator-stage wait into the producer -- it would hold a tile's first load back
+  // instead -- was measured: thin-tile layers +8...+23 %, profiles/r02_mma_thread.md: the producer has no slack either)
   p.kgroup = 1;
   if ((p.mode == 0 || p.mode == 1) && p.num_kb >= 2) {
     // group ring slots until a group's MMAs run >= ~900 cycles (the MMA thread's wait + fence + commit per group
@@ -2433,6 +2435,8 @@ static int conv2d_dense(const int8_t* x, const int8_t* w_packed, void* y, const 
     p.mode = 1;
     p.Q = Q;
     p.PQ = P * Q;
+    p.dQ = make_fastdiv((uint32_t)Q);
+    p.dPQ = make_fastdiv((uint32_t)(P * Q));
     p.S = d->S;
     p.sh = d->stride_h;
     p.sw = d->stride_w;
