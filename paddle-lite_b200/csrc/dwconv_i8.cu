@@ -557,10 +557,11 @@ dw3x3_tma_kernel(const __grid_constant__ CUtensorMap tx, const DwParams p, const
   if (warp == kDwConsumerWarps) {
     // ---- producer: one lane keeps the ring of input boxes full; no block-wide barrier anywhere ----
     if ((threadIdx.x & 31) == 0) {
-      uint32_t it = 0;
-      for (uint32_t tile = blockIdx.x; tile < (uint32_t)t.tiles; tile += gridDim.x, ++it) {
-        const int slot = (int)(it % (uint32_t)t.stages);
-        if (it >= (uint32_t)t.stages) mbar_wait(smem_u32(&empty_bar[slot]), ((it / (uint32_t)t.stages) - 1u) & 1u);
+      // ring position kept incrementally (a runtime % and / per tile is ~60 instructions)
+      int slot = 0;
+      uint32_t round = 0;  // how many times the ring has wrapped
+      for (uint32_t tile = blockIdx.x; tile < (uint32_t)t.tiles; tile += gridDim.x) {
+        if (round > 0) mbar_wait(smem_u32(&empty_bar[slot]), (round - 1u) & 1u);
         int n, p0, q0, cbase;
         dw_tile_coords<STRIDE>(p, t, tile, n, p0, q0, cbase);
         const uint32_t bar = smem_u32(&full_bar[slot]);
@@ -570,6 +571,7 @@ dw3x3_tma_kernel(const __grid_constant__ CUtensorMap tx, const DwParams p, const
           tma_load_3d(dst, &tx, bar, (q0 * STRIDE - p.pl_) * (p.C >> 3), p0 * STRIDE - p.pt, n);
         else
           tma_load_4d(dst, &tx, bar, cbase, q0 * STRIDE - p.pl_, p0 * STRIDE - p.pt, n);
+        if (++slot == t.stages) { slot = 0; ++round; }
       }
     }
     return;
@@ -602,10 +604,11 @@ dw3x3_tma_kernel(const __grid_constant__ CUtensorMap tx, const DwParams p, const
   const uint32_t colw = CCW > 0 ? (uint32_t)CCW : (uint32_t)t.CC / 4u, roww = (uint32_t)t.BW * colw;
   // word offset of this thread's window inside a stage: first row of its group, first column of its strip
   const uint32_t win_off = (uint32_t)grp * (uint32_t)(t.RG * STRIDE) * roww + strip * 4u * colw + (uint32_t)quad;
-  uint32_t it = 0;
-  for (uint32_t tile = blockIdx.x; tile < (uint32_t)t.tiles; tile += gridDim.x, ++it) {
-    const int slot = (int)(it % (uint32_t)t.stages);
-    const uint32_t parity = (it / (uint32_t)t.stages) & 1u;
+  int slot = -1;
+  uint32_t parity = 1u;
+  for (uint32_t tile = blockIdx.x; tile < (uint32_t)t.tiles; tile += gridDim.x) {
+    if (++slot == t.stages) slot = 0;
+    if (slot == 0) parity ^= 1u;
     int n, p0, q0, cbase;
     dw_tile_coords<STRIDE>(p, t, tile, n, p0, q0, cbase);
     mbar_wait(smem_u32(&full_bar[slot]), parity);

@@ -11,6 +11,7 @@
 //   layout      [N,C,HW] <-> [N,HW,C]  lite/backends/cuda/math/transpose.cu:31-184
 //   pool / add  no int8 kernel in the reference;
 //               window rules of lite/kernels/cuda/pool_compute.cu:28-130
+#include <cstdlib>
 #include <cuda_fp16.h>
 
 #include "common.cuh"
@@ -494,8 +495,9 @@ pool4_kernel(const uint32_t* __restrict__ x, int ldxw, void* __restrict__ y, int
              uint32_t total, int exclusive, float rescale, int out_dtype, int round_mode, int word_store) {
   pdl_launch_dependents();
   pdl_wait();
-  const uint32_t idx = blockIdx.x * 256u + threadIdx.x;
-  if (idx >= total) return;
+  // grid-stride over the output items (the host caps the grid at a few resident waves: one short CTA per 256 items
+  // spent most of the 3x3 / s2 pool of the ResNet stem on CTA turnover, 64 us for 256 MB)
+  for (uint32_t idx = blockIdx.x * 256u + threadIdx.x; idx < total; idx += gridDim.x * 256u) [&] {
   uint32_t t = fdiv(idx, dCw);
   const int cw = (int)(idx - t * dCw.d) * V;
   uint32_t u = fdiv(t, dQ);
@@ -623,6 +625,7 @@ pool4_kernel(const uint32_t* __restrict__ x, int ldxw, void* __restrict__ y, int
       }
     }
   }
+  }();
 }
 
 template <int POOL>
@@ -948,7 +951,18 @@ extern "C" int pl_pool2d_i8_nhwc(const int8_t* x, int ldx, void* y, int ldy, int
     // whole-word stores need the pad channels of the last word to be addressable
     const int word_store = (ldy >= Cw * 4) && (ldy % 4 == 0) &&
                            ((reinterpret_cast<uintptr_t>(y) & (out_dtype == PL_OUT_INT8 ? 3 : 15)) == 0);
-    const unsigned grid = (unsigned)((witems + 255) / 256);
+    unsigned grid = (unsigned)((witems + 255) / 256);
+    {
+      // at most PL_POOL_WAVES resident waves of CTAs (8 CTAs of 256 threads per SM); the kernel strides over the rest
+      int sms = 148, dev = 0;
+      cudaGetDevice(&dev);
+      static int sms_of[64] = {};
+      if (sms_of[dev & 63] == 0) cudaDeviceGetAttribute(&sms_of[dev & 63], cudaDevAttrMultiProcessorCount, dev);
+      if (sms_of[dev & 63] > 0) sms = sms_of[dev & 63];
+      static const int waves = getenv("PL_POOL_WAVES") ? atoi(getenv("PL_POOL_WAVES")) : 2;
+      const unsigned cap = (unsigned)(sms * 8 * (waves > 0 ? waves : 1));
+      if (waves > 0 && grid > cap) grid = cap;
+    }
     const FastDiv dCw = make_fastdiv((uint32_t)groups), dQ = make_fastdiv((uint32_t)Q), dP = make_fastdiv((uint32_t)P);
     if (pool_type == PL_POOL_MAX)
       launch_pool4<PL_POOL_MAX>(V, KF, grid, (cudaStream_t)stream, reinterpret_cast<const uint32_t*>(x), ldx / 4, y,
