@@ -95,6 +95,14 @@ typedef struct pl_conv_desc {
   int groups;
 } pl_conv_desc;
 
+/* Scheduling hint, no reference counterpart (the reference's kernels own no tile order): the conv / depthwise /
+ * gemm / pool launches that the CALLING THREAD issues after this call walk their output tiles last-to-first
+ * (reverse != 0) or first-to-last (0, the default).  Results are identical either way.  A runtime that alternates
+ * the order along a chain of layers lets every layer start on the bytes its producer wrote last, which are still in
+ * the 126 MB L2 (ResNet-50 b256: -1 % step time, nets.DeviceNet.bind).  Thread-local; captured CUDA graphs keep the
+ * order they were captured with. */
+void pl_set_tile_order(int reverse);
+
 /* ---- host-side helpers (no device work) ---------------------------------- */
 int pl_conv_out_size(int in, int k, int dil, int pad0, int pad1, int stride);
 /* K-block (bytes of the reduction dim staged per pipeline stage) chosen for C. */

@@ -465,6 +465,11 @@ def nhwc_to_nchw(x, Cc=None):
     return y
 
 
+def set_tile_order(reverse):
+    """Scheduling hint for the next launches of this thread (pl_set_tile_order): walk the output tiles last-to-first"""
+    lib().pl_set_tile_order(int(bool(reverse)))
+
+
 def pool2d(x, ksize, strides, pads, pool_type, exclusive=True, rescale=1.0, out=OUT_INT8,
            rnd=ROUND_ARM, ceil_mode=False, global_pooling=False, Cc=None, y=None):
     N, H, W, ldx = x.shape

@@ -515,4 +515,7 @@ __host__ __device__ __forceinline__ uint32_t make_idesc_i8(uint32_t n, uint32_t 
   return (2u << 4) | (1u << 7) | (1u << 10) | ((n >> 3) << 17) | ((m >> 4) << 24);
 }
 
+// scheduling hint of pl_set_tile_order (igemm_i8.cu): should the next launch of this thread walk its tiles last-to-first?
+bool next_tile_order_reversed();
+
 }  // namespace pl

@@ -500,6 +500,7 @@ __global__ void __launch_bounds__(256, 4) dw3x3s2_kernel(const DwParams p) {
 struct DwTile {
   int TR, strips, quads, CC, BW, BH;
   int ctiles, rtiles, qtiles, tiles;
+  int rev_last;     // tiles - 1 when the tile list is walked last-to-first (pl_set_tile_order), else -1
   int stages;
   int groups, RG;   // row groups of a tile (thread = strip x quad x group) and output rows per group
   int merged;       // the tensor map is {W * C / 8 (8-byte elements), H, N}: whole pixel rows are contiguous
@@ -563,7 +564,7 @@ dw3x3_tma_kernel(const __grid_constant__ CUtensorMap tx, const DwParams p, const
       for (uint32_t tile = blockIdx.x; tile < (uint32_t)t.tiles; tile += gridDim.x) {
         if (round > 0) mbar_wait(smem_u32(&empty_bar[slot]), (round - 1u) & 1u);
         int n, p0, q0, cbase;
-        dw_tile_coords<STRIDE>(p, t, tile, n, p0, q0, cbase);
+        dw_tile_coords<STRIDE>(p, t, t.rev_last >= 0 ? (uint32_t)t.rev_last - tile : tile, n, p0, q0, cbase);
         const uint32_t bar = smem_u32(&full_bar[slot]);
         const uint32_t dst = sbase + (uint32_t)slot * t.stage_pitch;
         mbar_arrive_expect_tx(bar, t.stage_bytes);
@@ -584,7 +585,9 @@ dw3x3_tma_kernel(const __grid_constant__ CUtensorMap tx, const DwParams p, const
   const int item = (int)threadIdx.x - (int)grp * n_items;
   const uint32_t strip = fdiv((uint32_t)item, t.dQuads);
   const int quad = item - (int)strip * t.quads;
-  const int cbase0 = (int)(blockIdx.x % (uint32_t)t.ctiles) * t.CC;
+  // (tiles and the grid are multiples of ctiles: the reversed list keeps one channel chunk per CTA as well)
+  const uint32_t first = t.rev_last >= 0 ? (uint32_t)t.rev_last - blockIdx.x : blockIdx.x;
+  const int cbase0 = (int)(first % (uint32_t)t.ctiles) * t.CC;
   const int c0 = cbase0 + quad * 4;
   const bool active = (int)grp < t.groups && c0 < p.C;
   uint32_t wa[3][4];
@@ -610,7 +613,7 @@ dw3x3_tma_kernel(const __grid_constant__ CUtensorMap tx, const DwParams p, const
     if (++slot == t.stages) slot = 0;
     if (slot == 0) parity ^= 1u;
     int n, p0, q0, cbase;
-    dw_tile_coords<STRIDE>(p, t, tile, n, p0, q0, cbase);
+    dw_tile_coords<STRIDE>(p, t, t.rev_last >= 0 ? (uint32_t)t.rev_last - tile : tile, n, p0, q0, cbase);
     mbar_wait(smem_u32(&full_bar[slot]), parity);
     const uint8_t* st = gbase + (size_t)slot * t.stage_pitch;
     const int oq0 = q0 + (int)strip * (STRIDE == 1 ? 4 : 2);
@@ -950,6 +953,7 @@ extern "C" int pl_dwconv2d_i8_nhwc(const int8_t* x, const int8_t* w_crs, void* y
              (long long)d->N * P * Q * (d->ldy / 4) < (1ll << 32);  // 32-bit output word offsets
         if (ok) {
           t.tiles = (int)tiles;
+          t.rev_last = next_tile_order_reversed() ? t.tiles - 1 : -1;
           t.stages = stages;
           t.dC = make_fastdiv((uint32_t)t.ctiles);
           t.dQ = make_fastdiv((uint32_t)t.qtiles);

@@ -492,12 +492,13 @@ template <int POOL, int V, int KF>
 __global__ void __launch_bounds__(256)
 pool4_kernel(const uint32_t* __restrict__ x, int ldxw, void* __restrict__ y, int ldy, int H, int W, int C,
              int kh, int kw, int sh, int sw, int pt, int pl_, FastDiv dCw, FastDiv dQ, FastDiv dP,
-             uint32_t total, int exclusive, float rescale, int out_dtype, int round_mode, int word_store) {
+             uint32_t total, int exclusive, float rescale, int out_dtype, int round_mode, int word_store, int reversed) {
   pdl_launch_dependents();
   pdl_wait();
   // grid-stride over the output items (the host caps the grid at a few resident waves: one short CTA per 256 items
   // spent most of the 3x3 / s2 pool of the ResNet stem on CTA turnover, 64 us for 256 MB)
-  for (uint32_t idx = blockIdx.x * 256u + threadIdx.x; idx < total; idx += gridDim.x * 256u) [&] {
+  for (uint32_t idx_ = blockIdx.x * 256u + threadIdx.x; idx_ < total; idx_ += gridDim.x * 256u) [&] {
+  const uint32_t idx = reversed ? total - 1u - idx_ : idx_;  // pl_set_tile_order
   uint32_t t = fdiv(idx, dCw);
   const int cw = (int)(idx - t * dCw.d) * V;
   uint32_t u = fdiv(t, dQ);
@@ -633,8 +634,9 @@ static void launch_pool4(int V, int KF, unsigned grid, cudaStream_t st, const ui
                          int H, int W, int C, int kh, int kw, int sh, int sw, int pt, int pl_, FastDiv dCw, FastDiv dQ,
                          FastDiv dP, uint32_t total, int exclusive, float rescale, int out_dtype, int round_mode,
                          int word_store) {
+  const int reversed = next_tile_order_reversed() ? 1 : 0;
 #define PL_POOL_ARGS x, ldxw, y, ldy, H, W, C, kh, kw, sh, sw, pt, pl_, dCw, dQ, dP, total, exclusive, rescale, \
-                     out_dtype, round_mode, word_store
+                     out_dtype, round_mode, word_store, reversed
   if (V == 4 && KF == 3) launch_pdl(pool4_kernel<POOL, 4, 3>, dim3(grid), dim3(256), 0, st, PL_POOL_ARGS);
   else if (V == 4) launch_pdl(pool4_kernel<POOL, 4, 0>, dim3(grid), dim3(256), 0, st, PL_POOL_ARGS);
   else if (KF == 3) launch_pdl(pool4_kernel<POOL, 1, 3>, dim3(grid), dim3(256), 0, st, PL_POOL_ARGS);

@@ -64,6 +64,9 @@ struct IgemmParams {
   uint32_t a_region_bytes;   // bytes of the A stage ring / halo buffers in front of the B ring
   FastDiv dBands, dWP;
   FastDiv dNT;  // n_tiles (set by launch_igemm)
+  // tile order hint (pl_set_tile_order): walk the tile list last-to-first, so that a layer starts on the bytes its
+  // producer wrote last (still in L2); rev_last = number of tiles - 1, or -1 for the forward order
+  int rev_last;
   const uint32_t* xw;  // mode 2: input words [N][H][W]
   int thin_r, thin_sw;
   // space-to-depth stem (mode 3 with s2d = 1): the input is [N][HP][WS] 16-byte pixels (2x2 original
@@ -549,6 +552,7 @@ __device__ __noinline__ void mma_loop_s2d(const S2dArgs a) {
 // owns block 2 * tm + rank of it
 template <bool GROUPED, bool CTA2 = false>
 __device__ __forceinline__ void tile_mn(const IgemmParams& p, int tile, int& tm, int& tn, int rank = 0) {
+  if (p.rev_last >= 0) tile = p.rev_last - tile;
   if (GROUPED) {
     const int per_band = p.group_m * p.n_tiles;
     const int band = tile / per_band, within = tile - band * per_band;
@@ -718,7 +722,9 @@ igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
       // the grid is a multiple of n_tiles: this CTA only ever sees N tile blockIdx.x % n_tiles, whose
       // whole K extent stays in smem (no per-tile filter re-read from L2, A-only ring stages)
       mbar_arrive_expect_tx(bar_bres, (uint32_t)num_kb * (uint32_t)(BN * BK));
-      const int n0r = ((int)blockIdx.x % n_tiles) * BN;
+      int tm0_ = 0, tn0_ = 0;
+      if (tile0 < num_tiles) tile_mn<GROUPED, CTA2>(p, tile0, tm0_, tn0_, cta_rank);  // (honours the tile order hint)
+      const int n0r = tn0_ * BN;
       for (int kb = 0; kb < num_kb; ++kb) tma_load_2d(smem_b + kb * b_bytes, &tmap_b, bar_bres, kb * BK, n0r);
     }
     if (!(TR == 0 && mode == 3)) pdl_wait();
@@ -748,8 +754,9 @@ igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
         const uint32_t span = p.s2d_span_bytes, pitch = p.s2d_span_pitch;
         for (int tile = tile0; tile < num_tiles; tile += tstride, ++lt) {
           PL_TRACE(0, lt, 0);
-          const int img = (int)fdiv((uint32_t)tile, p.dBands);
-          const int p0 = tile - img * p.bands;
+          const int te = p.rev_last >= 0 ? p.rev_last - tile : tile;
+          const int img = (int)fdiv((uint32_t)te, p.dBands);
+          const int p0 = te - img * p.bands;
           WAIT(bar_aempty + 8 * ab, aph ^ 1);
           PL_TRACE(0, lt, 1);
           mbar_arrive_expect_tx(bar_afull + 8 * ab, p.a_halo_tx);
@@ -762,8 +769,9 @@ igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
       }
       for (int tile = tile0; tile < num_tiles && !p.s2d; tile += tstride, ++lt) {
         PL_TRACE(0, lt, 0);
-        const int tq = (int)fdiv((uint32_t)tile, p.dNT);
-        const int tn = tile - tq * n_tiles, tm = CTA2 ? 2 * tq + cta_rank : tq;
+        const int te = p.rev_last >= 0 ? p.rev_last - tile : tile;
+        const int tq = (int)fdiv((uint32_t)te, p.dNT);
+        const int tn = te - tq * n_tiles, tm = CTA2 ? 2 * tq + cta_rank : tq;
         const int n0 = tn * BN;
         // (pairs: the block past the last one reads image N -- all zero fill, nothing stored)
         const int img = (int)fdiv((uint32_t)tm, p.dBands);
@@ -1099,7 +1107,7 @@ igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
     int glt = 0;
     for (int tile = tile0; tile < num_tiles; tile += tstride, ++glt) {
       if (g == 0) PL_TRACE(0, glt, 0);
-      const int tm = (int)fdiv((uint32_t)tile, p.dNT);
+      const int tm = (int)fdiv((uint32_t)(p.rev_last >= 0 ? p.rev_last - tile : tile), p.dNT);
       const uint32_t m = (uint32_t)(tm * kBM + prow);
       const bool mok = m < (uint32_t)p.M;
       const uint32_t n = fdiv(mok ? m : 0u, p.dPQ);
@@ -1670,6 +1678,16 @@ __global__ void pack_s2d_weight_kernel(const int8_t* __restrict__ w, int8_t* __r
 // --------------------------------------------------------------------------
 // host: tensor maps
 // --------------------------------------------------------------------------
+// tile order of the next launches of this thread (pl_set_tile_order); PL_TILE_ZIGZAG=1 (experiments) alternates per launch
+thread_local int g_tile_order = 0;
+thread_local unsigned g_zigzag_count = 0;
+bool next_tile_order_reversed() {
+  static const bool zigzag = getenv("PL_TILE_ZIGZAG") != nullptr && atoi(getenv("PL_TILE_ZIGZAG")) != 0;
+  if (zigzag) return (g_zigzag_count++ & 1u) != 0;
+  return g_tile_order != 0;
+}
+extern "C" void pl_set_tile_order(int reverse) { pl::g_tile_order = reverse ? 1 : 0; }
+
 namespace {
 
 struct DriverFns {
@@ -1948,6 +1966,7 @@ int launch_igemm(const CUtensorMap& ta, const CUtensorMap& tb_in, IgemmParams& p
   }
   const int tiles = p.m_tiles * p.n_tiles;
   p.dNT = make_fastdiv((uint32_t)p.n_tiles);
+  p.rev_last = next_tile_order_reversed() ? tiles - 1 : -1;
   int grid = tiles < driver().sm_count ? tiles : driver().sm_count;
   if (p.cta2) {
     const int clusters = tiles < max_pair_clusters() ? tiles : max_pair_clusters();

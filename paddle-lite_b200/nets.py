@@ -510,6 +510,22 @@ class DeviceNet:
                 self.output = y
                 self.layers.append((op, lambda i0=0, i1=B, op=op, A=A, y=y, sf=sf, bf=bf:
                                     pl.gemm(A[i0:i1], op._wp, sf, bf, out=pl.OUT_FP32, y=y[i0:i1], K=op.K)))
+        # Tile order (pl_set_tile_order): an op walks its output tiles in the opposite direction of the op that wrote
+        # its input, so it starts on the bytes that were written last and are still in the 126 MB L2 (results do not
+        # depend on the order; PL_NET_ZIGZAG=0 keeps every op first-to-last)
+        if os.environ.get("PL_NET_ZIGZAG", "1") != "0":
+            wrote_reversed = {}
+            for k, (op, fn) in enumerate(self.layers):
+                r = (not wrote_reversed.get(op.get("src"), True)) if op.kind != "quant_in" else False
+                wrote_reversed[op.dst] = r
+
+                def ordered(i0=0, i1=B, fn=fn, r=r):
+                    pl.set_tile_order(r)
+                    try:
+                        return fn(i0, i1)
+                    finally:
+                        pl.set_tile_order(False)
+                self.layers[k] = (op, ordered)
         return self
 
     def _parse_schedule(self, schedule):
