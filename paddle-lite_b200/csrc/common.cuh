@@ -287,6 +287,37 @@ __device__ __forceinline__ void tma_load_2d(uint32_t dst, const void* desc, uint
       "l"(desc), "r"(bar), "r"(c0), "r"(c1)
       : "memory");
 }
+// L2 eviction-priority hints for loads of bytes that are read exactly once (a fused residual, the A rows of a
+// launch with one N tile): they leave the cache first, so the tensor being WRITTEN stays for the next layer
+// (the encodings createpolicy.fractional.L2::evict_first / evict_normal .b64 %0, 1.0 return: as constants they can
+// live on the uniform datapath of a single-thread role loop instead of costing two R2UR per TMA instruction)
+static constexpr uint64_t kL2EvictFirst = 0x12F0000000000000ull, kL2EvictNormal = 0x16F0000000000000ull;
+__device__ __forceinline__ uint64_t l2_policy_evict_first() {
+  uint64_t pol;
+  asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(pol));
+  return pol;
+}
+__device__ __forceinline__ uint64_t l2_policy_evict_normal() {
+  uint64_t pol;
+  asm volatile("createpolicy.fractional.L2::evict_normal.b64 %0, 1.0;" : "=l"(pol));
+  return pol;
+}
+__device__ __forceinline__ void tma_load_2d_hint(uint32_t dst, const void* desc, uint32_t bar, int c0, int c1,
+                                                 uint64_t policy) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint"
+      " [%0], [%1, {%3, %4}], [%2], %5;" ::"r"(dst),
+      "l"(desc), "r"(bar), "r"(c0), "r"(c1), "l"(policy)
+      : "memory");
+}
+__device__ __forceinline__ void tma_load_4d_hint(uint32_t dst, const void* desc, uint32_t bar, int c0, int c1,
+                                                 int c2, int c3, uint64_t policy) {
+  asm volatile(
+      "cp.async.bulk.tensor.4d.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint"
+      " [%0], [%1, {%3, %4, %5, %6}], [%2], %7;" ::"r"(dst),
+      "l"(desc), "r"(bar), "r"(c0), "r"(c1), "r"(c2), "r"(c3), "l"(policy)
+      : "memory");
+}
 __device__ __forceinline__ void tma_load_4d(uint32_t dst, const void* desc, uint32_t bar, int c0, int c1,
                                             int c2, int c3) {
   asm volatile(
@@ -294,6 +325,22 @@ __device__ __forceinline__ void tma_load_4d(uint32_t dst, const void* desc, uint
       " [%0], [%1, {%3, %4, %5, %6}], [%2];" ::"r"(dst),
       "l"(desc), "r"(bar), "r"(c0), "r"(c1), "r"(c2), "r"(c3)
       : "memory");
+}
+__device__ __forceinline__ void tma_load_3d_hint(uint32_t dst, const void* desc, uint32_t bar, int c0, int c1, int c2,
+                                                 uint64_t policy) {
+  asm volatile(
+      "cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint"
+      " [%0], [%1, {%3, %4, %5}], [%2], %6;" ::"r"(dst),
+      "l"(desc), "r"(bar), "r"(c0), "r"(c1), "r"(c2), "l"(policy)
+      : "memory");
+}
+// 16-byte read-only load with an L2 eviction hint
+__device__ __forceinline__ uint4 ldg_v4_hint(const void* p, uint64_t policy) {
+  uint4 v;
+  asm volatile("ld.global.nc.L2::cache_hint.v4.u32 {%0, %1, %2, %3}, [%4], %5;"
+               : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w)
+               : "l"(p), "l"(policy));
+  return v;
 }
 __device__ __forceinline__ void tma_load_3d(uint32_t dst, const void* desc, uint32_t bar, int c0, int c1, int c2) {
   asm volatile(
@@ -339,6 +386,16 @@ __device__ __forceinline__ void tma_load_im2col_4d(uint32_t dst, const void* des
       "cp.async.bulk.tensor.4d.shared::cluster.global.im2col.mbarrier::complete_tx::bytes"
       " [%0], [%1, {%3, %4, %5, %6}], [%2], {%7, %8};" ::"r"(dst),
       "l"(desc), "r"(bar), "r"(c), "r"(w), "r"(h), "r"(n), "h"(off_w), "h"(off_h)
+      : "memory");
+}
+
+__device__ __forceinline__ void tma_load_im2col_4d_hint(uint32_t dst, const void* desc, uint32_t bar,
+                                                        int c, int w, int h, int n, uint16_t off_w,
+                                                        uint16_t off_h, uint64_t policy) {
+  asm volatile(
+      "cp.async.bulk.tensor.4d.shared::cluster.global.im2col.mbarrier::complete_tx::bytes.L2::cache_hint"
+      " [%0], [%1, {%3, %4, %5, %6}], [%2], {%7, %8}, %9;" ::"r"(dst),
+      "l"(desc), "r"(bar), "r"(c), "r"(w), "r"(h), "r"(n), "h"(off_w), "h"(off_h), "l"(policy)
       : "memory");
 }
 

@@ -501,6 +501,7 @@ struct DwTile {
   int TR, strips, quads, CC, BW, BH;
   int ctiles, rtiles, qtiles, tiles;
   int rev_last;     // tiles - 1 when the tile list is walked last-to-first (pl_set_tile_order), else -1
+  int l2_hint;      // input boxes are loaded with L2::evict_first (PL_L2_HINTS bit 4)
   int stages;
   int groups, RG;   // row groups of a tile (thread = strip x quad x group) and output rows per group
   int merged;       // the tensor map is {W * C / 8 (8-byte elements), H, N}: whole pixel rows are contiguous
@@ -568,10 +569,15 @@ dw3x3_tma_kernel(const __grid_constant__ CUtensorMap tx, const DwParams p, const
         const uint32_t bar = smem_u32(&full_bar[slot]);
         const uint32_t dst = sbase + (uint32_t)slot * t.stage_pitch;
         mbar_arrive_expect_tx(bar, t.stage_bytes);
-        if (t.merged)  // rows of BW whole pixels: {(W * C) / 8, H, N} in 8-byte elements
-          tma_load_3d(dst, &tx, bar, (q0 * STRIDE - p.pl_) * (p.C >> 3), p0 * STRIDE - p.pt, n);
-        else
-          tma_load_4d(dst, &tx, bar, cbase, q0 * STRIDE - p.pl_, p0 * STRIDE - p.pt, n);
+        // (the input is read once, apart from the halo rows and columns of neighbouring tiles: L2 evict_first, so
+        // that the output stays in the cache for the next layer)
+        if (t.merged) {  // rows of BW whole pixels: {(W * C) / 8, H, N} in 8-byte elements
+          if (t.l2_hint) tma_load_3d_hint(dst, &tx, bar, (q0 * STRIDE - p.pl_) * (p.C >> 3), p0 * STRIDE - p.pt, n, kL2EvictFirst);
+          else tma_load_3d(dst, &tx, bar, (q0 * STRIDE - p.pl_) * (p.C >> 3), p0 * STRIDE - p.pt, n);
+        } else {
+          if (t.l2_hint) tma_load_4d_hint(dst, &tx, bar, cbase, q0 * STRIDE - p.pl_, p0 * STRIDE - p.pt, n, kL2EvictFirst);
+          else tma_load_4d(dst, &tx, bar, cbase, q0 * STRIDE - p.pl_, p0 * STRIDE - p.pt, n);
+        }
         if (++slot == t.stages) { slot = 0; ++round; }
       }
     }
@@ -954,6 +960,12 @@ extern "C" int pl_dwconv2d_i8_nhwc(const int8_t* x, const int8_t* w_crs, void* y
         if (ok) {
           t.tiles = (int)tiles;
           t.rev_last = next_tile_order_reversed() ? t.tiles - 1 : -1;
+          {
+            static const int hints = getenv("PL_L2_HINTS") ? atoi(getenv("PL_L2_HINTS")) : 31;
+            const long long io_b = (long long)d->N * d->H * d->W * d->C + (long long)d->N * P * Q * d->C;
+            static const int min_mb = getenv("PL_L2_HINT_MIN_MB") ? atoi(getenv("PL_L2_HINT_MIN_MB")) : 48;
+            t.l2_hint = ((hints & 16) && io_b >= ((long long)min_mb << 20)) ? 1 : 0;
+          }
           t.stages = stages;
           t.dC = make_fastdiv((uint32_t)t.ctiles);
           t.dQ = make_fastdiv((uint32_t)t.qtiles);

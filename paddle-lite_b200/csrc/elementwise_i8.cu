@@ -498,7 +498,8 @@ pool4_kernel(const uint32_t* __restrict__ x, int ldxw, void* __restrict__ y, int
   // grid-stride over the output items (the host caps the grid at a few resident waves: one short CTA per 256 items
   // spent most of the 3x3 / s2 pool of the ResNet stem on CTA turnover, 64 us for 256 MB)
   for (uint32_t idx_ = blockIdx.x * 256u + threadIdx.x; idx_ < total; idx_ += gridDim.x * 256u) [&] {
-  const uint32_t idx = reversed ? total - 1u - idx_ : idx_;  // pl_set_tile_order
+  const uint32_t idx = (reversed & 1) ? total - 1u - idx_ : idx_;  // pl_set_tile_order
+  const uint64_t pol_ef = l2_policy_evict_first();
   uint32_t t = fdiv(idx, dCw);
   const int cw = (int)(idx - t * dCw.d) * V;
   uint32_t u = fdiv(t, dQ);
@@ -520,7 +521,7 @@ pool4_kernel(const uint32_t* __restrict__ x, int ldxw, void* __restrict__ y, int
   auto load = [&](int h, int w, uint32_t (&d)[V]) {
     const uint32_t* p = img + (uint32_t)((h * W + w) * ldxw);
     if (V == 4) {
-      const uint4 q = __ldg(reinterpret_cast<const uint4*>(p));
+      const uint4 q = (reversed & 2) ? ldg_v4_hint(p, pol_ef) : __ldg(reinterpret_cast<const uint4*>(p));  // (PL_L2_HINTS bit 5)
       d[0] = q.x; d[V > 1 ? 1 : 0] = q.y; d[V > 2 ? 2 : 0] = q.z; d[V > 3 ? 3 : 0] = q.w;
     } else {
       d[0] = __ldg(p);
@@ -634,7 +635,8 @@ static void launch_pool4(int V, int KF, unsigned grid, cudaStream_t st, const ui
                          int H, int W, int C, int kh, int kw, int sh, int sw, int pt, int pl_, FastDiv dCw, FastDiv dQ,
                          FastDiv dP, uint32_t total, int exclusive, float rescale, int out_dtype, int round_mode,
                          int word_store) {
-  const int reversed = next_tile_order_reversed() ? 1 : 0;
+  static const int hints = getenv("PL_L2_HINTS") ? atoi(getenv("PL_L2_HINTS")) : 15;
+  const int reversed = (next_tile_order_reversed() ? 1 : 0) | ((hints & 32) ? 2 : 0);  // bit 1: L2 evict_first loads
 #define PL_POOL_ARGS x, ldxw, y, ldy, H, W, C, kh, kw, sh, sw, pt, pl_, dCw, dQ, dP, total, exclusive, rescale, \
                      out_dtype, round_mode, word_store, reversed
   if (V == 4 && KF == 3) launch_pdl(pool4_kernel<POOL, 4, 3>, dim3(grid), dim3(256), 0, st, PL_POOL_ARGS);

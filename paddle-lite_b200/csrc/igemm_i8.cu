@@ -67,6 +67,7 @@ struct IgemmParams {
   // tile order hint (pl_set_tile_order): walk the tile list last-to-first, so that a layer starts on the bytes its
   // producer wrote last (still in L2); rev_last = number of tiles - 1, or -1 for the forward order
   int rev_last;
+  int l2_hints;  // bit 0: the fused residual is loaded with L2::evict_first, bit 1: the A rows too (one N tile: read once)
   const uint32_t* xw;  // mode 2: input words [N][H][W]
   int thin_r, thin_sw;
   // space-to-depth stem (mode 3 with s2d = 1): the input is [N][HP][WS] 16-byte pixels (2x2 original
@@ -707,6 +708,10 @@ igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
     uint32_t full_b = bar_full, empty_b = bar_empty, dst_a = smem_a, dst_b = smem_b;
     int rb = 0;
     uint32_t rphase = 0;
+    // L2 policies of the residual and the activation loads, chosen once: the loads always take the hinted form (a
+    // branch per load in this thread cost as much as the hints gain)
+    const uint64_t pol_r = (p.l2_hints & 1) ? kL2EvictFirst : kL2EvictNormal;
+    const uint64_t pol_a = (p.l2_hints & 14) ? kL2EvictFirst : kL2EvictNormal;
     if (TR > 0 && p.b_resident) {
       // thin mode, single N tile: every k-block of the filter is loaded exactly once
       {
@@ -767,6 +772,11 @@ igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
           if (++ab == halo_bufs) { ab = 0; aph ^= 1; }
         }
       }
+      // (HINT: the loads always take the hinted TMA form, with the policy chosen once per launch.  A branch per load
+      // cost this thread as much as the hints gain, and a second, plain copy of the loop for small launches moved
+      // the code enough to lose the gain as well: profiles/r02_l2.md)
+      auto halo_tiles = [&](auto hint_tag) {
+      constexpr bool HINT = decltype(hint_tag)::value;
       for (int tile = tile0; tile < num_tiles && !p.s2d; tile += tstride, ++lt) {
         PL_TRACE(0, lt, 0);
         const int te = p.rev_last >= 0 ? p.rev_last - tile : tile;
@@ -780,9 +790,14 @@ igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
           WAIT(bar_rempty + 8 * rb, rphase ^ 1);
           {
             mbar_arrive_expect_tx(bar_rfull + 8 * rb, (uint32_t)(p.hk * p.Q * BN));
-            for (int j = 0; j < p.panels; ++j)
-              tma_load_4d(smem_res + rb * tile_bytes + j * (kBM * p.PW), &tmap_r, bar_rfull + 8 * rb,
-                          n0 + j * p.PW, 0, p0, img);
+            for (int j = 0; j < p.panels; ++j) {
+              if (HINT)
+                tma_load_4d_hint(smem_res + rb * tile_bytes + j * (kBM * p.PW), &tmap_r, bar_rfull + 8 * rb,
+                                 n0 + j * p.PW, 0, p0, img, pol_r);
+              else
+                tma_load_4d(smem_res + rb * tile_bytes + j * (kBM * p.PW), &tmap_r, bar_rfull + 8 * rb,
+                            n0 + j * p.PW, 0, p0, img);
+            }
           }
           if (++rb == p.res_bufs) { rb = 0; rphase ^= 1; }
         }
@@ -798,7 +813,8 @@ igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
               mbar_arrive(bar_afull + 8 * ab);
             } else {
               mbar_arrive_expect_tx(bar_afull + 8 * ab, p.a_halo_tx);
-              tma_load_4d(smem_a + ab * p.a_halo_bytes, &tmap_a, bar_afull + 8 * ab, cbk, -p.pl_, p0 - p.pt, img);
+              if (HINT) tma_load_4d_hint(smem_a + ab * p.a_halo_bytes, &tmap_a, bar_afull + 8 * ab, cbk, -p.pl_, p0 - p.pt, img, pol_a);
+              else tma_load_4d(smem_a + ab * p.a_halo_bytes, &tmap_a, bar_afull + 8 * ab, cbk, -p.pl_, p0 - p.pt, img);
             }
           }
           PL_TRACE(0, lt, 2);
@@ -823,6 +839,8 @@ igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
           }
         }
       }
+      };  // halo_tiles
+      halo_tiles(std::true_type{});
       if (CTA2) {  // (see the tail of the stage ring below)
         for (int i = 0; i < halo_bufs; ++i) {
           WAIT(bar_aempty + 8 * ab, aph ^ 1);
@@ -831,6 +849,8 @@ igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
       }
     }
     int lt = 0;
+    auto gemm_tiles = [&](auto hint_tag) {
+    constexpr bool HINT = decltype(hint_tag)::value;
     for (int tile = tile0; tile < num_tiles && !(TR > 0 && p.b_resident) && mode != 3; tile += tstride, ++lt) {
       PL_TRACE(0, lt, 0);
       int tn_, tm_;
@@ -843,9 +863,14 @@ igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
         PL_TRACE(0, lt, 3);
         {
           mbar_arrive_expect_tx(bar_rfull + 8 * rb, tile_bytes);
-          for (int j = 0; j < p.panels; ++j)
-            tma_load_2d(smem_res + rb * tile_bytes + j * (kBM * p.PW), &tmap_r, bar_rfull + 8 * rb,
-                        n0 + j * p.PW, m0);
+          for (int j = 0; j < p.panels; ++j) {
+            if (HINT)
+              tma_load_2d_hint(smem_res + rb * tile_bytes + j * (kBM * p.PW), &tmap_r, bar_rfull + 8 * rb,
+                               n0 + j * p.PW, m0, pol_r);
+            else
+              tma_load_2d(smem_res + rb * tile_bytes + j * (kBM * p.PW), &tmap_r, bar_rfull + 8 * rb,
+                          n0 + j * p.PW, m0);
+          }
         }
         if (++rb == p.res_bufs) { rb = 0; rphase ^= 1; }
       }
@@ -877,9 +902,11 @@ igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
             if (TR > 0) {
               // A arrives from the gather warps
             } else if (mode == 1) {
-              tma_load_im2col_4d(da_, &tmap_a, full_b, cbk, bw, bh, bn, offw, offh);
+              if (HINT) tma_load_im2col_4d_hint(da_, &tmap_a, full_b, cbk, bw, bh, bn, offw, offh, pol_a);
+              else tma_load_im2col_4d(da_, &tmap_a, full_b, cbk, bw, bh, bn, offw, offh);
             } else {
-              tma_load_2d(da_, &tmap_a, full_b, kc, m0);
+              if (HINT) tma_load_2d_hint(da_, &tmap_a, full_b, kc, m0, pol_a);
+              else tma_load_2d(da_, &tmap_a, full_b, kc, m0);
             }
             if (!bres01) tma_load_2d(db_, &tmap_b, full_b, kc, n0);
           }
@@ -899,6 +926,8 @@ igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
       }
       PL_TRACE(0, lt, 2);
     }
+    };  // gemm_tiles
+    gemm_tiles(std::true_type{});
     if (CTA2) {
       // tail: every stage this CTA filled has been consumed (its multicast commit has landed here) before the
       // CTA can leave -- no arrival may target the barriers of a CTA that has exited
@@ -1967,6 +1996,21 @@ int launch_igemm(const CUtensorMap& ta, const CUtensorMap& tb_in, IgemmParams& p
   const int tiles = p.m_tiles * p.n_tiles;
   p.dNT = make_fastdiv((uint32_t)p.n_tiles);
   p.rev_last = next_tile_order_reversed() ? tiles - 1 : -1;
+  {
+    int knob = env_int("PL_L2_HINTS", 31);
+    {
+      // only where the launch's tensors are large next to the 126 MB L2 (the hinted loop costs thin-tile launches ~1 %)
+      const long long in_b = (long long)p.M * p.cblocks * p.BK, out_b = (long long)p.M * p.Nout;
+      const long long all_b = in_b + out_b * (p.epi.residual ? 2 : 1);
+      if (all_b < (long long)env_int("PL_L2_HINT_MIN_MB", 48) << 20) knob = 0;
+    }
+    // activations are read once per layer (a few times within microseconds where tiles overlap): evict_first keeps
+    // them from displacing the output tensor, which the next layer reads (pairs keep the default: their layers'
+    // tensors fit the L2 anyway).  1 fused residual, 2 A rows of plain GEMMs / 1x1 convs, 4 halo tiles, 8 im2col
+    // (large GEMMs re-read A once per N tile column over a long time and live on those L2 hits: no hint there)
+    p.l2_hints = (knob & 1) | ((knob & 2) && p.mode == 0 && !p.cta2 && p.n_tiles <= 8 ? 2 : 0) | ((knob & 4) && p.mode == 3 && !p.cta2 ? 4 : 0) |
+                 ((knob & 8) && p.mode == 1 && !p.cta2 ? 8 : 0);
+  }
   int grid = tiles < driver().sm_count ? tiles : driver().sm_count;
   if (p.cta2) {
     const int clusters = tiles < max_pair_clusters() ? tiles : max_pair_clusters();
