@@ -39,6 +39,15 @@
  * PL_ROUND_CUDA_LEGACY = clamp [-128,127] + round-half-even
  * (lite/backends/cuda/math/utils.h:61-66).  `scale`/`bias` are the FOLDED
  * vectors (see pl_fold_scales), bias may be NULL.
+ *
+ * Stream ordering: every kernel is launched with programmatic stream serialization and waits
+ * (griddepcontrol.wait) right before its first access to ACTIVATIONS or the residual; packed filters and
+ * the scale / bias vectors are read before that wait, as constants.  That is safe for data produced by
+ * this library's own pack / fold kernels and by host uploads on the same stream (none of them triggers
+ * launch_dependents, so the dependent grid cannot start before they have completed and flushed), and for
+ * anything that completed before the launch.  A caller that writes filters or scales with its OWN kernel
+ * that calls cudaTriggerProgrammaticLaunchCompletion / griddepcontrol.launch_dependents must put an event or
+ * a stream synchronisation between that kernel and the first launch that reads them.
  */
 #ifndef PL_INT8_H_
 #define PL_INT8_H_
