@@ -243,30 +243,29 @@ struct FeedAffine {
 };
 template <typename TIn>
 __device__ __forceinline__ void feed_load(const TIn* p, bool four, bool vec4, float4& f);
-// (streaming loads, ld.global.cs: the feed is read once and should not displace the s2d tensor the stem reads next)
 template <>
 __device__ __forceinline__ void feed_load<float>(const float* p, bool four, bool vec4, float4& f) {
   if (four && vec4) {
-    f = __ldcs(reinterpret_cast<const float4*>(p));
+    f = __ldg(reinterpret_cast<const float4*>(p));
   } else {
-    const float2 a = __ldcs(reinterpret_cast<const float2*>(p));
+    const float2 a = __ldg(reinterpret_cast<const float2*>(p));
     f.x = a.x; f.y = a.y;
-    if (four) { const float2 b2 = __ldcs(reinterpret_cast<const float2*>(p + 2)); f.z = b2.x; f.w = b2.y; }
+    if (four) { const float2 b2 = __ldg(reinterpret_cast<const float2*>(p + 2)); f.z = b2.x; f.w = b2.y; }
   }
 }
 template <>
 __device__ __forceinline__ void feed_load<__half>(const __half* p, bool four, bool vec4, float4& f) {
   if (four && vec4) {
-    const uint2 u = __ldcs(reinterpret_cast<const uint2*>(p));
+    const uint2 u = __ldg(reinterpret_cast<const uint2*>(p));
     const float2 a = __half22float2(*reinterpret_cast<const __half2*>(&u.x));
     const float2 b2 = __half22float2(*reinterpret_cast<const __half2*>(&u.y));
     f = make_float4(a.x, a.y, b2.x, b2.y);
   } else {
-    const uint32_t u = __ldcs(reinterpret_cast<const uint32_t*>(p));
+    const uint32_t u = __ldg(reinterpret_cast<const uint32_t*>(p));
     const float2 a = __half22float2(*reinterpret_cast<const __half2*>(&u));
     f.x = a.x; f.y = a.y;
     if (four) {
-      const uint32_t v = __ldcs(reinterpret_cast<const uint32_t*>(p + 2));
+      const uint32_t v = __ldg(reinterpret_cast<const uint32_t*>(p + 2));
       const float2 b2 = __half22float2(*reinterpret_cast<const __half2*>(&v));
       f.z = b2.x; f.w = b2.y;
     }
@@ -275,13 +274,13 @@ __device__ __forceinline__ void feed_load<__half>(const __half* p, bool four, bo
 template <>
 __device__ __forceinline__ void feed_load<uint8_t>(const uint8_t* p, bool four, bool vec4, float4& f) {
   if (four && vec4) {
-    const uint32_t u = __ldcs(reinterpret_cast<const uint32_t*>(p));
+    const uint32_t u = __ldg(reinterpret_cast<const uint32_t*>(p));
     f = make_float4((float)(u & 255u), (float)((u >> 8) & 255u), (float)((u >> 16) & 255u), (float)(u >> 24));
   } else {
-    const uint32_t u = __ldcs(reinterpret_cast<const uint16_t*>(p));
+    const uint32_t u = __ldg(reinterpret_cast<const uint16_t*>(p));
     f.x = (float)(u & 255u); f.y = (float)(u >> 8);
     if (four) {
-      const uint32_t v = __ldcs(reinterpret_cast<const uint16_t*>(p + 2));
+      const uint32_t v = __ldg(reinterpret_cast<const uint16_t*>(p + 2));
       f.z = (float)(v & 255u); f.w = (float)(v >> 8);
     }
   }
