@@ -292,16 +292,6 @@ __device__ __forceinline__ void tma_load_2d(uint32_t dst, const void* desc, uint
 // (the encodings createpolicy.fractional.L2::evict_first / evict_normal .b64 %0, 1.0 return: as constants they can
 // live on the uniform datapath of a single-thread role loop instead of costing two R2UR per TMA instruction)
 static constexpr uint64_t kL2EvictFirst = 0x12F0000000000000ull, kL2EvictNormal = 0x16F0000000000000ull;
-__device__ __forceinline__ uint64_t l2_policy_evict_first() {
-  uint64_t pol;
-  asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(pol));
-  return pol;
-}
-__device__ __forceinline__ uint64_t l2_policy_evict_normal() {
-  uint64_t pol;
-  asm volatile("createpolicy.fractional.L2::evict_normal.b64 %0, 1.0;" : "=l"(pol));
-  return pol;
-}
 __device__ __forceinline__ void tma_load_2d_hint(uint32_t dst, const void* desc, uint32_t bar, int c0, int c1,
                                                  uint64_t policy) {
   asm volatile(

@@ -499,7 +499,7 @@ pool4_kernel(const uint32_t* __restrict__ x, int ldxw, void* __restrict__ y, int
   // spent most of the 3x3 / s2 pool of the ResNet stem on CTA turnover, 64 us for 256 MB)
   for (uint32_t idx_ = blockIdx.x * 256u + threadIdx.x; idx_ < total; idx_ += gridDim.x * 256u) [&] {
   const uint32_t idx = (reversed & 1) ? total - 1u - idx_ : idx_;  // pl_set_tile_order
-  const uint64_t pol_ef = l2_policy_evict_first();
+  const uint64_t pol_ef = kL2EvictFirst;
   uint32_t t = fdiv(idx, dCw);
   const int cw = (int)(idx - t * dCw.d) * V;
   uint32_t u = fdiv(t, dQ);

@@ -356,18 +356,6 @@ __device__ __forceinline__ void issue_kblock_n(int ksteps, uint32_t d_tmem, uint
   else if (ksteps == 2) issue_kblock<2, CTA2>(d_tmem, da, db, idesc, fresh);
   else issue_kblock<1, CTA2>(d_tmem, da, db, idesc, fresh);
 }
-// all taps of a resident R x S filter against one halo tile: one straight run of MMAs
-template <int R_, int S_, int KS, bool CTA2 = false>
-__device__ __forceinline__ void issue_taps(uint32_t d_tmem, uint64_t da0, uint64_t db0, uint32_t idesc,
-                                           uint32_t tap_step, uint32_t row_pitch, uint32_t b_step, bool fresh) {
-#pragma unroll
-  for (int r = 0; r < R_; ++r)
-#pragma unroll
-    for (int sx = 0; sx < S_; ++sx)
-      issue_kblock<KS, CTA2>(d_tmem, da0 + (uint64_t)(r * row_pitch + sx * tap_step),
-                       db0 + (uint64_t)((r * S_ + sx) * b_step), idesc, fresh && r == 0 && sx == 0);
-}
-
 // The MMA thread is ONE lane: it issues roughly one instruction every 3 cycles, a taken branch costs ~30, an mbarrier
 // wait ~70 even when complete, and the tensor pipe queues only ~8 MMAs behind the running one (tools/sync_probe.cu).
 // Whatever the thread does between the last MMA of a tile and the first of the next beyond 8 MMA times drains the
