@@ -186,6 +186,12 @@ __device__ __forceinline__ uint32_t prmt_(uint32_t a, uint32_t b, uint32_t sel) 
 __device__ __forceinline__ void st_shared_v4(uint32_t addr, uint32_t a, uint32_t b, uint32_t c, uint32_t d) {
   asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(a), "r"(b), "r"(c), "r"(d) : "memory");
 }
+// the same store under a per-lane predicate (no divergence region around the epilogue body for the few padded-grid rows)
+__device__ __forceinline__ void st_shared_v4_if(uint32_t addr, uint32_t a, uint32_t b, uint32_t c, uint32_t d, bool ok) {
+  asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.u32 p, %5, 0;\n\t@p st.shared.v4.b32 [%0], {%1, %2, %3, %4};\n\t}" ::"r"(addr), "r"(a),
+               "r"(b), "r"(c), "r"(d), "r"((uint32_t)ok)
+               : "memory");
+}
 __device__ __forceinline__ uint4 ld_shared_v4(uint32_t addr) {
   uint4 v;
   asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(addr));
@@ -1376,6 +1382,13 @@ igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
     // ring positions of local tile `lt` (the groups interleave on every ring): start at lt = egroup, then
     // advance by G per tile -- kept incrementally, a runtime % and / per ring and tile costs more than
     // the groups save on wide tiles
+    // staging offsets of this warp's unit slots (tile-invariant: computed once, not per unit and tile)
+    uint32_t soffs[kSlots];
+#pragma unroll
+    for (int i = 0; i < kSlots; ++i) {
+      const uint32_t col_ = (uint32_t)((cqp + cqn * i) * 16);
+      soffs[i] = (col_ >> p.pw_shift) * (uint32_t)(kBM * p.PW) + ((((col_ & (uint32_t)(p.PW - 1)) >> 4) ^ swx) << 4);
+    }
     int as = egroup % p.acc_stages, rb = egroup % res_bufs_, ob = egroup % out_bufs_;
     uint32_t aphase = (uint32_t)(egroup / p.acc_stages) & 1u, rphase = (uint32_t)(egroup / res_bufs_) & 1u,
              ophase = (uint32_t)(egroup / out_bufs_) & 1u;
@@ -1429,13 +1442,14 @@ igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
           const uint32_t sub = (kPair && colt >= (uint32_t)p.BN) ? 1u : 0u;  // 128-row block of a pair
           const uint32_t col = colt - sub * (uint32_t)p.BN;              // output column inside the tile
           const uint32_t sbase = sub * tile_bytes;
-          if (kFast && !rvalid) {
-            // padded-grid row without an output pixel
-          } else if (kFast) {
+          if (kFast) {
             // position of this 16-byte chunk inside the swizzled staging panels; rows >= M
-            // and columns >= Nout are computed on zero-filled operands and clipped by the store
-            const uint32_t soff = (col >> p.pw_shift) * (uint32_t)(kBM * p.PW) +
-                                  ((((col & (uint32_t)(p.PW - 1)) >> 4) ^ swx) << 4);
+            // and columns >= Nout are computed on zero-filled operands and clipped by the store.  (Padded-grid rows
+            // without an output pixel run through the arithmetic too and only skip the store: a divergence region
+            // around the body cost every unit three control instructions.)
+            const uint32_t soff = kPair ? (col >> p.pw_shift) * (uint32_t)(kBM * p.PW) +
+                                              ((((col & (uint32_t)(p.PW - 1)) >> 4) ^ swx) << 4)
+                                        : soffs[i];
             uint4 rw = make_uint4(0, 0, 0, 0);
             if (EPI == EPI_I8_RELU_RES) rw = ld_shared_v4(res_base + soff);  // (pairs never carry a residual)
             const uint32_t rws[4] = {rw.x, rw.y, rw.z, rw.w};
@@ -1451,7 +1465,7 @@ igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
               else
                 w[q4] = quad_i8_signed(acc + 4 * q4, sc, bi);
             }
-            st_shared_v4(out_base + sbase + soff, w[0], w[1], w[2], w[3]);
+            st_shared_v4_if(out_base + sbase + soff, w[0], w[1], w[2], w[3], rvalid);
           } else if (p.f32_fast && row + (long long)(sub * kBM) < p.M && n0 + (int)col + 16 <= p.Nout) {
             float* out = reinterpret_cast<float*>(p.y) + (row + (long long)(sub * kBM)) * p.ldy + n0 + (int)col;
             const bool relu = p.epi.act == PL_ACT_RELU;
