@@ -1382,6 +1382,8 @@ igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
     // ring positions of local tile `lt` (the groups interleave on every ring): start at lt = egroup, then
     // advance by G per tile -- kept incrementally, a runtime % and / per ring and tile costs more than
     // the groups save on wide tiles
+    // unit slots this warp fills (launch constant): units cqp, cqp + cqn, ... < units
+    const int n_my = cqp < units ? (units - cqp + cqn - 1) / cqn : 0;
     // staging offsets of this warp's unit slots (tile-invariant: computed once, not per unit and tile)
     uint32_t soffs[kSlots];
 #pragma unroll
@@ -1421,7 +1423,11 @@ igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
       __syncwarp();
       PL_ETRACE(1);
       tc_fence_after();
-      const uint32_t t_addr = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)as * p.acc_stride;
+      // (per-tile bases; every unit slot is a compile-time offset from them)
+      const uint32_t t_addr = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)as * p.acc_stride +
+                              (uint32_t)(cqp * 16);
+      const float* const sc_p = &s_scale[sb0 + (uint32_t)(cqp * 16)];
+      const float* const bi_p = &s_bias[sb0 + (uint32_t)(cqp * 16)];
       const uint32_t res_base = smem_res + (uint32_t)rb * tile_bytes + rowoff;
       const uint32_t out_tile = smem_out + (uint32_t)ob * obuf_bytes;
       // fused residual: each 16-byte chunk of the output replaces the residual chunk it was computed from
@@ -1429,14 +1435,14 @@ igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
       // TMEM reads are double buffered: unit i+1 is in flight while unit i runs through the ALUs
       uint32_t accb[2][16];
       const bool skip_epi = (PL_DBG_FLAGS_V & 1) != 0;
-      if (cqp < units && !skip_epi) tmem_ld_32x32b_x16(t_addr + (uint32_t)(cqp * 16), accb[0]);
+      if (n_my > 0 && !skip_epi) tmem_ld_32x32b_x16(t_addr, accb[0]);
 #pragma unroll
       for (int i = 0; i < kSlots; ++i) {
         const int u = cqp + cqn * i;
-        if (u < units && !skip_epi) {  // warp-uniform
+        if (i < n_my && !skip_epi) {  // warp-uniform
           tmem_ld_wait();
-          if (i < kSlots - 1 && u + cqn < units)
-            tmem_ld_32x32b_x16(t_addr + (uint32_t)((u + cqn) * 16), accb[(i + 1) & 1]);
+          if (i + 1 < kSlots && i + 1 < n_my)
+            tmem_ld_32x32b_x16(t_addr + (uint32_t)(cqn * (i + 1) * 16), accb[(i + 1) & 1]);
           uint32_t(&acc)[16] = accb[i & 1];
           const uint32_t colt = (uint32_t)(u * 16);                       // TMEM column of the unit
           const uint32_t sub = (kPair && colt >= (uint32_t)p.BN) ? 1u : 0u;  // 128-row block of a pair
@@ -1456,8 +1462,10 @@ igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
             uint32_t w[4];
 #pragma unroll
             for (int q4 = 0; q4 < 4; ++q4) {
-              const float4 sc = *reinterpret_cast<const float4*>(&s_scale[sb0 + col + 4 * q4]);
-              const float4 bi = *reinterpret_cast<const float4*>(&s_bias[sb0 + col + 4 * q4]);
+              const float4 sc = kPair ? *reinterpret_cast<const float4*>(&s_scale[sb0 + col + 4 * q4])
+                                      : *reinterpret_cast<const float4*>(sc_p + (cqn * i * 16 + 4 * q4));
+              const float4 bi = kPair ? *reinterpret_cast<const float4*>(&s_bias[sb0 + col + 4 * q4])
+                                      : *reinterpret_cast<const float4*>(bi_p + (cqn * i * 16 + 4 * q4));
               if (EPI == EPI_I8_RELU)
                 w[q4] = quad_i8_relu<false>(acc + 4 * q4, sc, bi, p.hi_bits, 0u, 0.f);
               else if (EPI == EPI_I8_RELU_RES)
