@@ -192,6 +192,11 @@ __device__ __forceinline__ void st_shared_v4_if(uint32_t addr, uint32_t a, uint3
                "r"(b), "r"(c), "r"(d), "r"((uint32_t)ok)
                : "memory");
 }
+__device__ __forceinline__ float4 ld_shared_f4(uint32_t addr) {
+  float4 v;
+  asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(addr));
+  return v;
+}
 __device__ __forceinline__ uint4 ld_shared_v4(uint32_t addr) {
   uint4 v;
   asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(addr));
@@ -1382,6 +1387,9 @@ igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
     // ring positions of local tile `lt` (the groups interleave on every ring): start at lt = egroup, then
     // advance by G per tile -- kept incrementally, a runtime % and / per ring and tile costs more than
     // the groups save on wide tiles
+    // (opaque copies: two registers instead of two constant-bank loads in every unit)
+    const uint32_t hi_bits_r = opaque_u32(p.hi_bits);
+    const float res_scale_r = __uint_as_float(opaque_u32(__float_as_uint(p.epi.res_scale)));
     // unit slots this warp fills (launch constant): units cqp, cqp + cqn, ... < units
     const int n_my = cqp < units ? (units - cqp + cqn - 1) / cqn : 0;
     // staging offsets of this warp's unit slots (tile-invariant: computed once, not per unit and tile)
@@ -1426,8 +1434,9 @@ igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
       // (per-tile bases; every unit slot is a compile-time offset from them)
       const uint32_t t_addr = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)as * p.acc_stride +
                               (uint32_t)(cqp * 16);
-      const float* const sc_p = &s_scale[sb0 + (uint32_t)(cqp * 16)];
-      const float* const bi_p = &s_bias[sb0 + (uint32_t)(cqp * 16)];
+      // (opaque: otherwise the compiler re-derives both addresses in every unit instead of keeping two registers)
+      const uint32_t sc_a = opaque_u32(smem_u32(&s_scale[sb0 + (uint32_t)(cqp * 16)]));
+      const uint32_t bi_a = opaque_u32(smem_u32(&s_bias[sb0 + (uint32_t)(cqp * 16)]));
       const uint32_t res_base = smem_res + (uint32_t)rb * tile_bytes + rowoff;
       const uint32_t out_tile = smem_out + (uint32_t)ob * obuf_bytes;
       // fused residual: each 16-byte chunk of the output replaces the residual chunk it was computed from
@@ -1463,13 +1472,13 @@ igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
 #pragma unroll
             for (int q4 = 0; q4 < 4; ++q4) {
               const float4 sc = kPair ? *reinterpret_cast<const float4*>(&s_scale[sb0 + col + 4 * q4])
-                                      : *reinterpret_cast<const float4*>(sc_p + (cqn * i * 16 + 4 * q4));
+                                      : ld_shared_f4(sc_a + (uint32_t)((cqn * i * 16 + 4 * q4) * 4));
               const float4 bi = kPair ? *reinterpret_cast<const float4*>(&s_bias[sb0 + col + 4 * q4])
-                                      : *reinterpret_cast<const float4*>(bi_p + (cqn * i * 16 + 4 * q4));
+                                      : ld_shared_f4(bi_a + (uint32_t)((cqn * i * 16 + 4 * q4) * 4));
               if (EPI == EPI_I8_RELU)
-                w[q4] = quad_i8_relu<false>(acc + 4 * q4, sc, bi, p.hi_bits, 0u, 0.f);
+                w[q4] = quad_i8_relu<false>(acc + 4 * q4, sc, bi, hi_bits_r, 0u, 0.f);
               else if (EPI == EPI_I8_RELU_RES)
-                w[q4] = quad_i8_relu<true>(acc + 4 * q4, sc, bi, p.hi_bits, rws[q4], p.epi.res_scale);
+                w[q4] = quad_i8_relu<true>(acc + 4 * q4, sc, bi, hi_bits_r, rws[q4], res_scale_r);
               else
                 w[q4] = quad_i8_signed(acc + 4 * q4, sc, bi);
             }
