@@ -91,6 +91,7 @@ struct IgemmParams {
   // third (the bound of these launches); the epilogue of a pair no longer overlaps the
   // next mainloop, which long K amortises
   int mpair;
+  uint32_t pair_sbase;  // staging offset of a pair's second block: a whole tile (GEMM pairs) or Q rows (s2d row pairs)
   // CTA pairs (kernel template flag CTA2): clusters of two CTAs run MMAs of M = 256 (cta_group::2); every CTA
   // loads its own A rows and HALF of each B block, so the L2 -> SM operand bytes per MAC drop by a third at
   // BN = 256 and the filter of a 3x3 halo layer is fetched once per pair instead of once per CTA.  m_tiles
@@ -473,7 +474,7 @@ __device__ __noinline__ void mma_loop_taps3(const Taps3Args a) {
 
 // ---- the MMA thread's tile loop of the space-to-depth stems (out of line like mma_loop_taps3) ----
 struct S2dArgs {
-  int tile0, tstride, num_tiles, acc_stages, halo_bufs, ta, kpr, skip_mma;
+  int tile0, tstride, num_tiles, acc_stages, halo_bufs, ta, kpr, skip_mma, rows, bn;
   uint32_t tmem_base, acc_stride, bar_tempty, bar_tfull, bar_afull, bar_aempty, a_lo0, b_lo0, halo_step, b_step, pitch16, idesc;
   uint64_t desc_hi;
 #ifdef PL_DEBUG_KNOBS
@@ -505,8 +506,11 @@ __device__ __noinline__ void mma_loop_s2d(const S2dArgs a) {
     if (a.skip_mma) {
     } else if (a.ta == 4 && a.kpr == 2) {  // 7x7 / p3 stem
       issue_s2d<4, 2>(d_tmem, da0, db0, a.idesc, a.pitch16, a.b_step);
+      // row pairs: the second output row one span further down, into the accumulator next door
+      if (a.rows == 2) issue_s2d<4, 2>(d_tmem + (uint32_t)a.bn, da0 + (uint64_t)a.pitch16, db0, a.idesc, a.pitch16, a.b_step);
     } else if (a.ta == 2 && a.kpr == 1) {  // 3x3 / p1 stem
       issue_s2d<2, 1>(d_tmem, da0, db0, a.idesc, a.pitch16, a.b_step);
+      if (a.rows == 2) issue_s2d<2, 1>(d_tmem + (uint32_t)a.bn, da0 + (uint64_t)a.pitch16, db0, a.idesc, a.pitch16, a.b_step);
     } else {
       uint32_t t_lo = a_cur, bb = b_cur;
       for (int r = 0; r < a.ta; ++r, t_lo += a.pitch16)
@@ -760,13 +764,14 @@ igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
           PL_TRACE(0, lt, 0);
           const int te = p.rev_last >= 0 ? p.rev_last - tile : tile;
           const int img = (int)fdiv((uint32_t)te, p.dBands);
-          const int p0 = te - img * p.bands;
+          const int p0 = (te - img * p.bands) * p.hk;  // first output row of the tile (row pairs: hk = 2)
           WAIT(bar_aempty + 8 * ab, aph ^ 1);
           PL_TRACE(0, lt, 1);
           mbar_arrive_expect_tx(bar_afull + 8 * ab, p.a_halo_tx);
           const int8_t* src = p.xs2d + (long long)img * p.s2d_img_bytes + (long long)p0 * p.s2d_row_bytes;
           uint32_t dst = smem_a + ab * p.a_halo_bytes;
-          for (int a = 0; a < ta; ++a, src += p.s2d_row_bytes, dst += pitch) bulk_load_1d(dst, src, span, bar_afull + 8 * ab);
+          const int spans = ta + p.hk - 1;  // output row r of the tile reads spans r .. r + ta - 1
+          for (int a = 0; a < spans; ++a, src += p.s2d_row_bytes, dst += pitch) bulk_load_1d(dst, src, span, bar_afull + 8 * ab);
           PL_TRACE(0, lt, 2);
           if (++ab == halo_bufs) { ab = 0; aph ^= 1; }
         }
@@ -982,7 +987,7 @@ igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
         sa.a_lo0 = a_lo0; sa.b_lo0 = b_lo0; sa.halo_step = halo_step; sa.b_step = b_step;
         sa.pitch16 = p.s2d_span_pitch >> 4;
         sa.halo_bufs = halo_bufs; sa.ta = p.s2d_ta; sa.kpr = p.s2d_kpr;
-        sa.desc_hi = desc_hi; sa.idesc = idesc; sa.skip_mma = skip_mma ? 1 : 0;
+        sa.desc_hi = desc_hi; sa.idesc = idesc; sa.skip_mma = skip_mma ? 1 : 0; sa.rows = p.hk; sa.bn = p.BN;
 #ifdef PL_DEBUG_KNOBS
         sa.trace = blockIdx.x == 0 ? p.trace : nullptr;
 #endif
@@ -1456,7 +1461,7 @@ igemm_i8_kernel(const __grid_constant__ CUtensorMap tmap_a,
           const uint32_t colt = (uint32_t)(u * 16);                       // TMEM column of the unit
           const uint32_t sub = (kPair && colt >= (uint32_t)p.BN) ? 1u : 0u;  // 128-row block of a pair
           const uint32_t col = colt - sub * (uint32_t)p.BN;              // output column inside the tile
-          const uint32_t sbase = sub * tile_bytes;
+          const uint32_t sbase = sub * p.pair_sbase;
           if (kFast) {
             // position of this 16-byte chunk inside the swizzled staging panels; rows >= M
             // and columns >= Nout are computed on zero-filled operands and clipped by the store.  (Padded-grid rows
@@ -2014,6 +2019,7 @@ int launch_igemm(const CUtensorMap& ta, const CUtensorMap& tb_in, IgemmParams& p
   }
   const int tiles = p.m_tiles * p.n_tiles;
   p.dNT = make_fastdiv((uint32_t)p.n_tiles);
+  if (p.mpair && p.pair_sbase == 0) p.pair_sbase = (uint32_t)(kBM * p.BN);
   p.rev_last = next_tile_order_reversed() ? tiles - 1 : -1;
   {
     int knob = env_int("PL_L2_HINTS", 31);
@@ -2143,7 +2149,8 @@ int launch_igemm(const CUtensorMap& ta, const CUtensorMap& tb_in, IgemmParams& p
       p.out_bufs = 1;
       // small tiles turn over faster than a TMA store is read out: up to 4 staging buffers
       // (narrow tiles: 8 buffers, 4 of them with their stores in flight -- stem 7x7 134.7 -> 118.6 us)
-      int want_out = env_int("PL_IGEMM_OUT_BUFS", tile <= 8 * 1024 ? 8 : (tile <= 16 * 1024 ? 4 : 2));
+      // (s2d row pairs: 16 KB tiles that turn over as fast as the 8 KB ones -- eight buffers, four stores in flight)
+      int want_out = env_int("PL_IGEMM_OUT_BUFS", (tile <= 8 * 1024 || (p.s2d && p.mpair)) ? 8 : (tile <= 16 * 1024 ? 4 : 2));
       if (want_out > kMaxOutBufs) want_out = kMaxOutBufs;
       while (p.out_bufs < want_out && left >= tile) {
         ++p.out_bufs;
@@ -2177,7 +2184,7 @@ int launch_igemm(const CUtensorMap& ta, const CUtensorMap& tb_in, IgemmParams& p
     // 128-wide tiles with four accumulator stages, were built and measured for the epilogue-bound 1x1 expand layers:
     // 5-20 % slower, profiles/r02_epilogue.md -- both accumulator stages are then held by epilogues and the MMA of
     // the next tile cannot run ahead)
-    if (g != cq || env_int("PL_EPI_GROUPS", 4) <= 1) g = 1;
+    if (g != cq || env_int("PL_EPI_GROUPS", 4) <= 1 || p.mpair) g = 1;  // (pairs: all warps on the one stage)
     p.epi_groups = g;
   }
   if (p.s2d && !hres) return PL_ERR_UNSUPPORTED;
@@ -2738,6 +2745,33 @@ extern "C" int pl_s2d_conv2d_i8(const int8_t* x_s2d, const int8_t* w_s2d, void* 
   p.xs2d = x_s2d;
   p.a_halo_tx = (uint32_t)g.TA * p.s2d_span_bytes;
   p.a_halo_bytes = ((uint32_t)g.TA * p.s2d_span_pitch + 1023u) / 1024u * 1024u;
+  {
+    // Row pairs: two output rows per tile (TA + 1 spans, two accumulators, one hand-off).  A stem tile is 2-8 MMAs
+    // behind ~1000 cycles of per-tile work in every single-thread role (profiles/r02_mma_thread.md): a pair halves
+    // that cost per row.  Needs the staged int8 epilogues (the pair leaves through one 4-D TMA store of two rows).
+    const bool fast = e->out_dtype == PL_OUT_INT8 && e->round_mode == PL_ROUND_ARM && p.vec_ok && e->scale &&
+                      tma_epilogue_enabled() &&
+                      (e->act == PL_ACT_NONE || e->act == PL_ACT_RELU || (e->act == PL_ACT_RELU6 && e->act_arg > 0.f));
+    const bool known = (g.TA == 4 && g.TB == 4) || (g.TA == 2 && g.TB == 2);  // the two unrolled MMA runs (7x7 / 3x3 stems)
+    // measured at b256: the 3x3 stem (BN = 32, 2 MMAs per row) 109.3 -> 92.8 us, the 7x7 stem (BN = 64, 8 MMAs per row)
+    // 113.1 -> 114.4: pairs where a row is at most 32 channels wide (PL_S2D_PAIR: 0 never, 1 that rule, 2 always)
+    const int pair_knob = env_int("PL_S2D_PAIR", 1);
+    if (pair_knob > 0 && (pair_knob >= 2 || p.BN <= 32) && fast && known && g.P % 2 == 0 && g.Q % 8 == 0 && p.BN <= 128) {
+      p.mpair = 1;
+      p.hk = 2;
+      p.halo_m_tiles = d->N * (g.P / 2);
+      p.m_tiles = p.halo_m_tiles;
+      p.bands = g.P / 2;
+      p.dBands = make_fastdiv((uint32_t)(g.P / 2));
+      p.a_halo_tx = (uint32_t)(g.TA + 1) * p.s2d_span_bytes;
+      p.a_halo_bytes = ((uint32_t)(g.TA + 1) * p.s2d_span_pitch + 1023u) / 1024u * 1024u;
+      p.acc_stride = 2u * (uint32_t)p.BN;
+      p.acc_stages = 512 / (int)p.acc_stride;
+      if (p.acc_stages > kMaxAccStages) p.acc_stages = kMaxAccStages;
+      p.tmem_cols = pow2_cols(p.acc_stages * (int)p.acc_stride);
+      p.pair_sbase = (uint32_t)(g.Q * (p.BN < 128 ? p.BN : 128));  // Q staged rows of PW bytes
+    }
+  }
   p.tx_bytes = (uint32_t)(p.BN * p.BK);
   CUtensorMap tb;
   rc = encode_2d(&tb, w_s2d, (uint64_t)nkb * 32, (uint64_t)d->K, (uint64_t)nkb * 32, p.BK, p.BN);
