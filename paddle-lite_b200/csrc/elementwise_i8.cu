@@ -630,6 +630,58 @@ pool4_kernel(const uint32_t* __restrict__ x, int ldxw, void* __restrict__ y, int
   }();
 }
 
+// 3x3 / stride 2 max pooling, two vertically adjacent outputs per thread (16 bytes of channels each): the two windows
+// share one input row, so a thread issues 15 instead of 18 sixteen-byte loads for two outputs (the ResNet stem pool
+// moves 256 MB and is bound by its loads).  Same-scale int8 in and out (max of int8 is exact; the ARM convention clamps
+// at -127).  Items: (image, output row PAIR, output column, 16-byte channel group).
+__global__ void __launch_bounds__(256)
+pool3x3s2_max_pair_kernel(const uint32_t* __restrict__ x, int ldxw, int8_t* __restrict__ y, int ldy, int H, int W,
+                          int pt, int pl_, int P, FastDiv dG, FastDiv dQ, FastDiv dP2, uint32_t total, int reversed) {
+  pdl_launch_dependents();
+  pdl_wait();
+  for (uint32_t idx_ = blockIdx.x * 256u + threadIdx.x; idx_ < total; idx_ += gridDim.x * 256u) {
+    const uint32_t idx = reversed ? total - 1u - idx_ : idx_;
+    uint32_t t = fdiv(idx, dG);
+    const int cw = (int)(idx - t * dG.d) * 4;
+    uint32_t u = fdiv(t, dQ);
+    const int oq = (int)(t - u * dQ.d);
+    const uint32_t n = fdiv(u, dP2);
+    const int op = (int)(u - n * dP2.d) * 2;
+    const int hs = op * 2 - pt, ws = oq * 2 - pl_;
+    const uint32_t* img = x + (size_t)n * (size_t)(H * W) * (size_t)ldxw + cw;
+    uint4 d[5][3];
+#pragma unroll
+    for (int r = 0; r < 5; ++r)
+#pragma unroll
+      for (int c = 0; c < 3; ++c) {
+        const int h = min(max(hs + r, 0), H - 1), w = min(max(ws + c, 0), W - 1);
+        d[r][c] = __ldg(reinterpret_cast<const uint4*>(img + (uint32_t)((h * W + w) * ldxw)));
+      }
+    uint4 a0 = make_uint4(0x80808080u, 0x80808080u, 0x80808080u, 0x80808080u), a1 = a0;
+#pragma unroll
+    for (int r = 0; r < 5; ++r)
+#pragma unroll
+      for (int c = 0; c < 3; ++c) {
+        const bool ok = hs + r >= 0 && hs + r < H && ws + c >= 0 && ws + c < W;
+        if (ok && r <= 2) {
+          a0.x = __vmaxs4(a0.x, d[r][c].x); a0.y = __vmaxs4(a0.y, d[r][c].y);
+          a0.z = __vmaxs4(a0.z, d[r][c].z); a0.w = __vmaxs4(a0.w, d[r][c].w);
+        }
+        if (ok && r >= 2) {
+          a1.x = __vmaxs4(a1.x, d[r][c].x); a1.y = __vmaxs4(a1.y, d[r][c].y);
+          a1.z = __vmaxs4(a1.z, d[r][c].z); a1.w = __vmaxs4(a1.w, d[r][c].w);
+        }
+      }
+    const uint32_t lo = 0x81818181u;  // clamp at -127
+    const size_t o0 = ((size_t)(n * (uint32_t)P + (uint32_t)op) * dQ.d + (uint32_t)oq) * (size_t)ldy + (size_t)cw * 4;
+    *reinterpret_cast<uint4*>(y + o0) =
+        make_uint4(__vmaxs4(a0.x, lo), __vmaxs4(a0.y, lo), __vmaxs4(a0.z, lo), __vmaxs4(a0.w, lo));
+    if (op + 1 < P)
+      *reinterpret_cast<uint4*>(y + o0 + (size_t)dQ.d * (size_t)ldy) =
+          make_uint4(__vmaxs4(a1.x, lo), __vmaxs4(a1.y, lo), __vmaxs4(a1.z, lo), __vmaxs4(a1.w, lo));
+  }
+}
+
 template <int POOL>
 static void launch_pool4(int V, int KF, unsigned grid, cudaStream_t st, const uint32_t* x, int ldxw, void* y, int ldy,
                          int H, int W, int C, int kh, int kw, int sh, int sw, int pt, int pl_, FastDiv dCw, FastDiv dQ,
@@ -968,6 +1020,23 @@ extern "C" int pl_pool2d_i8_nhwc(const int8_t* x, int ldx, void* y, int ldy, int
       if (waves > 0 && grid > cap) grid = cap;
     }
     const FastDiv dCw = make_fastdiv((uint32_t)groups), dQ = make_fastdiv((uint32_t)Q), dP = make_fastdiv((uint32_t)P);
+    {
+      // (ResNet stem pool at b256: 62.4 -> 56.7 us; PL_POOL_PAIR=0 keeps one output per thread)
+      static const int pair_knob = getenv("PL_POOL_PAIR") ? atoi(getenv("PL_POOL_PAIR")) : 1;
+      if (pair_knob && pool_type == PL_POOL_MAX && V == 4 && KF == 3 && sh == 2 && sw == 2 && out_dtype == PL_OUT_INT8 &&
+          rescale == 1.0f && round_mode == PL_ROUND_ARM && C % 16 == 0 && ldy % 16 == 0 &&
+          (reinterpret_cast<uintptr_t>(y) & 15) == 0 && pt >= 0 && pt <= 2 && pl_ >= 0 && pl_ <= 2) {
+        const int P2 = (P + 1) / 2;
+        const long long items = (long long)N * P2 * Q * groups;
+        unsigned g2 = (unsigned)((items + 255) / 256);
+        if (g2 > grid) g2 = grid;  // (grid is already capped at the resident waves)
+        launch_pdl(pool3x3s2_max_pair_kernel, dim3(g2), dim3(256), 0, (cudaStream_t)stream,
+                   reinterpret_cast<const uint32_t*>(x), ldx / 4, reinterpret_cast<int8_t*>(y), ldy, H, W, pt, pl_, P, dCw, dQ,
+                   make_fastdiv((uint32_t)P2), (uint32_t)items, next_tile_order_reversed() ? 1 : 0);
+        ++g_launches;
+        return launch_status();
+      }
+    }
     if (pool_type == PL_POOL_MAX)
       launch_pool4<PL_POOL_MAX>(V, KF, grid, (cudaStream_t)stream, reinterpret_cast<const uint32_t*>(x), ldx / 4, y,
                                 ldy, H, W, C, kh, kw, sh, sw, pt, pl_, dCw, dQ, dP, (uint32_t)witems, exclusive,

@@ -121,3 +121,21 @@ def test_pool_and_gemm_reversed_match_forward(pl):
             pl.set_tile_order(False)
     for f, r in zip(*outs):
         assert np.array_equal(f, r)
+
+
+@pytest.mark.parametrize("shape", [(3, 57, 61, 64), (2, 56, 56, 32), (1, 9, 7, 16), (2, 112, 112, 64)])
+@pytest.mark.parametrize("pad", [0, 1])
+@pytest.mark.parametrize("rev", [False, True])
+def test_max_pool_3x3s2_row_pairs_match_oracle(pl, shape, pad, rev):
+    """the 3x3 / s2 max pool computes two output rows per thread (pool3x3s2_max_pair_kernel): odd and even output heights,
+    with and without padding, both tile orders"""
+    N, H, W, C = shape
+    rng = np.random.default_rng(H + W + C + pad)
+    x = rng.integers(-127, 128, (N, H, W, C), dtype=np.int8)
+    want = orc.pool2d(x, (3, 3), (2, 2), (pad,) * 4, orc.POOL_MAX)
+    pl.set_tile_order(rev)
+    try:
+        got = host(pl.pool2d(dev(x), (3, 3), (2, 2), (pad,) * 4, pl.POOL_MAX))
+    finally:
+        pl.set_tile_order(False)
+    assert np.array_equal(got, want)
